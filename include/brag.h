@@ -1,0 +1,131 @@
+/*
+ * brag.h -- C ABI of the B200-native hybrid-retrieval engine (libbrag.so).
+ *
+ * This is the drop-in boundary for the hot path that the reference delegates to Qdrant:
+ * every entry point below replaces one request the reference's vector-store adapter sends
+ * through `qdrant_session.client` (reference: app/core/vector_store/qdrant/qdrant_handler.py).
+ * The reference has no FFI of its own (it is Python talking HTTP to Qdrant), so the binding a
+ * maintainer adds is the ctypes stub shown in INTEGRATION.md; the Python mirror of
+ * AsyncQdrantClient that uses it is rag_application_b200/client.py.
+ *
+ * Conventions
+ *  - plain pointers and sizes only; no exceptions cross the ABI; every call returns 0 on
+ *    success, non-zero on failure, message via brag_last_error() (thread local).
+ *  - `on_device` != 0 means every data pointer of that call is a device pointer on the
+ *    engine's GPU (no copies, fully stream-ordered); 0 means host pointers (the call copies
+ *    host->device, runs, copies results back and synchronises the stream before returning).
+ *  - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream).
+ *  - ids are int64 "global row ids" = local row + the engine's id offset (row sharding);
+ *    global ids must stay below 2^32.  Result lists are padded with id -1 / score -inf and
+ *    the true length is written to out_counts[b].
+ *  - ranking order everywhere is (score desc, id asc).
+ */
+#ifndef BRAG_H
+#define BRAG_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct brag_engine brag_engine;
+
+enum brag_dtype { BRAG_F32 = 0, BRAG_F16 = 1, BRAG_BF16 = 2 };
+enum brag_rrf_tie { BRAG_TIE_ID = 0, BRAG_TIE_FIRST_SEEN = 1 };
+
+/* Engine lifecycle.  Replaces AsyncQdrantClient(url=...) (qdrant_session.py:21). */
+int brag_create(int device, brag_engine** out);
+int brag_destroy(brag_engine* e);
+const char* brag_last_error(void);
+/* ABI version, for the loader's sanity check. */
+int brag_version(void);
+
+/* Row sharding: global id = local row + offset. */
+int brag_set_id_offset(brag_engine* e, int64_t offset);
+
+/* Corpus upload.  Replaces client.upsert(points) for one named dense vector
+ * (qdrant_handler.py:155-190, schema :57-79).  rows = [n, d] row-major in `dtype`,
+ * already L2-normalised by the caller when the space is COSINE.  The engine copies. */
+int brag_dense_set(brag_engine* e, const char* name, const void* rows, int64_t n, int32_t d,
+                   int32_t dtype, int32_t on_device);
+int brag_dense_drop(brag_engine* e, const char* name);
+
+/* Sparse corpus upload: term-major CSR of the sparse named vector (qdrant_handler.py:80-86,
+ * :163).  term_ptr[V+1] int64, doc_ids[nnz] uint32 ascending inside each term, weights[nnz]
+ * float32.  The engine copies and builds its per-sub-tile offset table. */
+int brag_sparse_set_csr(brag_engine* e, const char* name, const int64_t* term_ptr,
+                        const uint32_t* doc_ids, const float* weights, int64_t n_terms,
+                        int64_t n_docs, int32_t on_device);
+int brag_sparse_drop(brag_engine* e, const char* name);
+
+/* Payload-filter bitmask (bit r set = row r passes).  Replaces query_filter=Filter(...)
+ * (qdrant_handler.py:297,371).  mask_id >= 1; mask_id 0 in a query means "no filter". */
+int brag_mask_set(brag_engine* e, int32_t mask_id, const uint32_t* bits, int64_t nbits,
+                  int32_t on_device);
+
+/* Exact dense top-k over the whole space: a leaf Prefetch(query=vec, using=name, limit=k)
+ * or query_points(query=vec, using=name, limit=k, exact=True) (qdrant_handler.py:311-315,
+ * :335-339, :363-369).  Q = [B, d] float32 (normalised by the caller for COSINE).
+ * Scores are the fp32 re-scored values of the selected rows. */
+int brag_dense_topk(brag_engine* e, const char* name, const float* Q, int32_t B, int32_t k,
+                    int32_t mask_id, float* out_scores, int64_t* out_ids, int32_t* out_counts,
+                    int32_t on_device, void* stream);
+
+/* Candidate-restricted dense re-score: a Prefetch that has children
+ * (qdrant_handler.py:317-329, :341-343, :363-372).  cand = [B, m] global ids, -1 = empty
+ * slot, duplicates allowed (union semantics). */
+int brag_dense_rescore(brag_engine* e, const char* name, const float* Q, int32_t B,
+                       const int64_t* cand, int32_t m, int32_t k, int32_t mask_id,
+                       float* out_scores, int64_t* out_ids, int32_t* out_counts,
+                       int32_t on_device, void* stream);
+
+/* Sparse (BM25) top-k: Prefetch(query=SparseVector, using=name, limit=k)
+ * (qdrant_handler.py:347-354).  Query b owns q_terms/q_vals[q_ptr[b]:q_ptr[b+1]], term rows
+ * strictly ascending; q_vals are float64 (Python floats; IDF already applied by the host).
+ * Only documents sharing >=1 term are candidates. */
+int brag_sparse_topk(brag_engine* e, const char* name, const int32_t* q_ptr,
+                     const int32_t* q_terms, const double* q_vals, int32_t B, int32_t k,
+                     int32_t mask_id, float* out_scores, int64_t* out_ids, int32_t* out_counts,
+                     int32_t on_device, void* stream);
+/* Document frequency of each term row (for Modifier.IDF on the host): df[V] int64, host. */
+int brag_sparse_df(brag_engine* e, const char* name, int64_t* df_host, int64_t n_terms);
+
+/* Reciprocal rank fusion: Prefetch(prefetch=[...], query=FusionQuery(RRF))
+ * (qdrant_handler.py:357-360).  ids = [L, B, kmax], counts = [L, B]; score = sum 1/(2+rank)
+ * in float64; out_scores float64 [B, limit]. */
+int brag_rrf(brag_engine* e, const int64_t* ids, const int32_t* counts, int32_t L, int32_t B,
+             int32_t kmax, int32_t limit, int32_t tie_mode, double* out_scores,
+             int64_t* out_ids, int32_t* out_counts, int32_t on_device, void* stream);
+
+/* k-way merge of per-shard top-k lists after the all-gather:
+ * scores/ids = [G, B, k], counts = [G, B] -> [B, k]. */
+int brag_merge_topk(brag_engine* e, const float* scores, const int64_t* ids,
+                    const int32_t* counts, int32_t G, int32_t B, int32_t k, float* out_scores,
+                    int64_t* out_ids, int32_t* out_counts, int32_t on_device, void* stream);
+
+/* The north_star three-stage path in one call: dense top-k, sparse top-k, RRF(limit=k).
+ * Optional outputs (may be NULL): the two per-stage lists. */
+int brag_hybrid_topk(brag_engine* e, const char* dense_name, const char* sparse_name,
+                     const float* Q, const int32_t* q_ptr, const int32_t* q_terms,
+                     const double* q_vals, int32_t B, int32_t k, int32_t mask_id,
+                     double* out_scores, int64_t* out_ids, int32_t* out_counts,
+                     int32_t on_device, void* stream);
+
+/* Per-stage device timing (CUDA events on the call's stream).  Stages: 0 dense scan,
+ * 1 dense select+rescore, 2 sparse scan, 3 sparse select, 4 rrf, 5 merge.
+ * brag_profile_read returns accumulated ms and launch counts since the last reset and
+ * synchronises the device. */
+#define BRAG_N_STAGES 6
+int brag_profile_enable(brag_engine* e, int32_t on);
+int brag_profile_read(brag_engine* e, double* ms, int64_t* launches, int64_t* kernel_launches_total);
+int brag_profile_reset(brag_engine* e);
+/* Which dense scan kernel brag_dense_topk would pick for batch B: 0 = GEMV stream, 1 = tcgen05. */
+int brag_dense_path(brag_engine* e, const char* name, int32_t B);
+/* Force a path (-1 auto, 0 GEMV, 1 tcgen05) -- used by the parity tests. */
+int brag_force_dense_path(brag_engine* e, int32_t path);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* BRAG_H */

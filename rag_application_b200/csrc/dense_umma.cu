@@ -1,0 +1,341 @@
+// Batched dense exact scan on the 5th-gen tensor cores with the top-k selection fused into the
+// epilogue (reference request qdrant_handler.py:311-315,335-339,363-369
+// issued for a batch of queries).  The [B, N] score matrix is never materialised.
+//
+// S[q, r] = sum_k Q[q, k] * X[r, k]; tile = 128 queries (UMMA M, TMEM lanes) x 256 corpus rows
+// (UMMA N, TMEM columns), K streamed 64 elements (one 128-byte swizzle atom) per pipeline stage.
+//   warp 0      : TMA producer  (cp.async.bulk.tensor -> 128B-swizzled smem, mbarrier tx)
+//   warp 1      : TMEM allocator + single-thread tcgen05.mma issuer (accumulators in TMEM, x2 buffered)
+//   warps 2..5  : epilogue.  Each thread owns ONE query (its TMEM lane): tcgen05.ld 32 columns at a
+//                 time and compare against that query's running k-th-best threshold held in a
+//                 register; the rare survivors go to the thread's candidate list in global memory.
+//                 When a list fills, the warp sorts it in shared memory and tightens the threshold.
+// A CTA is persistent over its contiguous corpus chunk for one block of 128 queries; CTAs that share
+// a chunk (different query blocks) run concurrently so the X tiles are served from L2.
+// Roofline: tensor pipe; flops = 2 * N * d * B.
+#include <cuda.h>
+
+#include <algorithm>
+#include <cstring>
+
+#include "common.cuh"
+#include "kernels.h"
+
+namespace brag {
+
+constexpr int UM_BM = 128;
+constexpr int UM_BN = 256;
+constexpr int UM_BK = 64;
+constexpr int UM_STAGES = 4;
+constexpr int UM_CAP = 512;
+constexpr int UM_THREADS = 192;
+constexpr int UM_A_BYTES = UM_BM * UM_BK * 2;  // 16 KB
+constexpr int UM_B_BYTES = UM_BN * UM_BK * 2;  // 32 KB
+constexpr uint32_t UM_TMEM_COLS = 512;
+
+struct UmSmem {
+    uint8_t a[UM_STAGES][UM_A_BYTES];
+    uint8_t b[UM_STAGES][UM_B_BYTES];
+    uint64_t sortbuf[4][UM_CAP];
+    uint64_t full[UM_STAGES];
+    uint64_t empty[UM_STAGES];
+    uint64_t tfull[2];
+    uint64_t tempty[2];
+    uint32_t tmem_base;
+};
+
+// ------------------------------------------------------------------ PTX wrappers
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    const uint32_t addr = smem_u32(bar);
+    uint32_t done = 0;
+    // bounded wait (~2 s of SM clocks): a protocol bug becomes a trap (error return), not a hung GPU
+    const long long t0 = clock64();
+    while (true) {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(done) : "r"(addr), "r"(parity) : "memory");
+        if (done) return;
+        if (clock64() - t0 > 4000000000ll) __trap();
+    }
+}
+__device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* tmap, int c0, int c1, uint64_t* bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+        ::"r"(smem_u32(smem_dst)), "l"(tmap), "r"(smem_u32(bar)), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc) : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+          "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
+          "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
+          "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+        : "r"(taddr));
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+// K-major, 128-byte swizzle: 8-row groups are 1024 B apart (SBO); LBO unused; version 1; layout 2.
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr) {
+    uint64_t d = 0;
+    d |= (uint64_t)((saddr >> 4) & 0x3FFF);
+    d |= (uint64_t)1 << 16;
+    d |= (uint64_t)(1024 >> 4) << 32;
+    d |= (uint64_t)1 << 46;
+    d |= (uint64_t)2 << 61;
+    return d;
+}
+
+// ------------------------------------------------------------------ epilogue list compaction
+// Sort lane L's candidate list (global memory) in this warp's shared buffer, keep the best
+// k_sel entries (written to dst), and return the new threshold / count to lane L.
+__device__ __forceinline__ void um_compact(unsigned bal, uint64_t* my_list, uint64_t* my_dst, int& cnt, float& thr,
+                                           uint64_t* sbuf, int k_sel, int lane) {
+    while (bal) {
+        const int L = __ffs(bal) - 1;
+        bal &= bal - 1;
+        uint64_t* src = reinterpret_cast<uint64_t*>(__shfl_sync(0xFFFFFFFFu, (unsigned long long)my_list, L));
+        uint64_t* dst = reinterpret_cast<uint64_t*>(__shfl_sync(0xFFFFFFFFu, (unsigned long long)my_dst, L));
+        const int c = __shfl_sync(0xFFFFFFFFu, cnt, L);
+        for (int i = lane; i < UM_CAP; i += 32) sbuf[i] = (i < c) ? __ldcg(src + i) : 0ull;
+        __syncwarp();
+        bitonic_desc(sbuf, UM_CAP, lane, 32, [] { __syncwarp(); });
+        const int nc = min(c, k_sel);
+        if (dst != nullptr)
+            for (int i = lane; i < k_sel; i += 32) __stcg(dst + i, sbuf[i]);
+        const uint64_t kth = sbuf[k_sel - 1];
+        if (lane == L) {
+            cnt = nc;
+            if (nc == k_sel) thr = key_score(kth);
+        }
+        __syncwarp();
+    }
+}
+
+// ------------------------------------------------------------------ the kernel
+__global__ void __launch_bounds__(UM_THREADS, 1)
+dense_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_x,
+                  int64_t n, int d, int B, int n_qblocks, int64_t rows_per_chunk, const uint32_t* __restrict__ mask,
+                  int k_sel, uint32_t idesc, uint64_t* __restrict__ part, uint64_t* __restrict__ scratch) {
+    extern __shared__ uint8_t smem_raw[];
+    UmSmem& S = *reinterpret_cast<UmSmem*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int qblock = blockIdx.x % n_qblocks;
+    const int chunk = blockIdx.x / n_qblocks;
+    const int64_t row_begin = (int64_t)chunk * rows_per_chunk;
+    const int64_t row_end = min(n, row_begin + rows_per_chunk);
+    const int n_tiles = row_end > row_begin ? (int)((row_end - row_begin + UM_BN - 1) / UM_BN) : 0;
+    const int n_kb = d / UM_BK;
+
+    if (warp == 0 && lane == 0) {
+        for (int s = 0; s < UM_STAGES; ++s) { mbar_init(&S.full[s], 1); mbar_init(&S.empty[s], 1); }
+        for (int s = 0; s < 2; ++s) { mbar_init(&S.tfull[s], 1); mbar_init(&S.tempty[s], 4); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&S.tmem_base)), "r"(UM_TMEM_COLS) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = S.tmem_base;
+
+    if (warp == 0) {
+        // ===== TMA producer
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int t = 0; t < n_tiles; ++t) {
+                const int row0 = (int)(row_begin + (int64_t)t * UM_BN);
+                for (int kb = 0; kb < n_kb; ++kb) {
+                    mbar_wait(&S.empty[stage], phase ^ 1);
+                    mbar_expect_tx(&S.full[stage], UM_A_BYTES + UM_B_BYTES);
+                    tma_load_2d(S.a[stage], &tmap_q, kb * UM_BK, qblock * UM_BM, &S.full[stage]);
+                    tma_load_2d(S.b[stage], &tmap_x, kb * UM_BK, row0, &S.full[stage]);
+                    if (++stage == UM_STAGES) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===== MMA issuer (one thread)
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int t = 0; t < n_tiles; ++t) {
+                const int as = t & 1;
+                const uint32_t aphase = (uint32_t)(t >> 1) & 1;
+                mbar_wait(&S.tempty[as], aphase ^ 1);
+                tc_fence_after();
+                const uint32_t tmem_d = tmem_base + (uint32_t)as * UM_BN;
+                for (int kb = 0; kb < n_kb; ++kb) {
+                    mbar_wait(&S.full[stage], phase);
+                    tc_fence_after();
+                    const uint64_t adesc = make_smem_desc(smem_u32(S.a[stage]));
+                    const uint64_t bdesc = make_smem_desc(smem_u32(S.b[stage]));
+#pragma unroll
+                    for (int k = 0; k < UM_BK / 16; ++k) {
+                        // +32 bytes per 16-element K step inside the swizzle atom (>>4 => +2)
+                        umma_f16(tmem_d, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc, (kb | k) ? 1u : 0u);
+                    }
+                    umma_commit(&S.empty[stage]);
+                    if (kb == n_kb - 1) umma_commit(&S.tfull[as]);
+                    if (++stage == UM_STAGES) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+    } else {
+        // ===== epilogue: thread <-> query
+        const int quarter = warp & 3;                 // TMEM lane quarter this warp may access
+        const int qidx = quarter * 32 + lane;         // query within the block
+        const int b = qblock * UM_BM + qidx;
+        const bool q_valid = b < B;
+        uint64_t* my_list = scratch + ((size_t)blockIdx.x * UM_BM + qidx) * UM_CAP;
+        uint64_t* sbuf = S.sortbuf[warp - 2];
+        float thr = q_valid ? -INFINITY : INFINITY;
+        int cnt = 0;
+        for (int t = 0; t < n_tiles; ++t) {
+            const int as = t & 1;
+            const uint32_t aphase = (uint32_t)(t >> 1) & 1;
+            const int64_t row0 = row_begin + (int64_t)t * UM_BN;
+            mbar_wait(&S.tfull[as], aphase);
+            tc_fence_after();
+#pragma unroll 1
+            for (int g = 0; g < UM_BN / 32; ++g) {
+                const unsigned bal = __ballot_sync(0xFFFFFFFFu, cnt > UM_CAP - 32);
+                if (bal) um_compact(bal, my_list, my_list, cnt, thr, sbuf, k_sel, lane);
+                uint32_t v[32];
+                tmem_ld32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(as * UM_BN + g * 32), v);
+#pragma unroll
+                for (int i = 0; i < 32; ++i) {
+                    const float s = __uint_as_float(v[i]);
+                    if (s > thr) {
+                        const int64_t row = row0 + g * 32 + i;
+                        if (row < row_end && mask_test(mask, (uint32_t)row)) {
+                            __stcg(my_list + cnt, make_key(s, (uint32_t)row));
+                            ++cnt;
+                        }
+                    }
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&S.tempty[as]);
+        }
+        // final: every valid query emits its best k_sel keys
+        uint64_t* my_dst = q_valid ? part + ((size_t)chunk * B + b) * k_sel : nullptr;
+        const unsigned bal = __ballot_sync(0xFFFFFFFFu, q_valid);
+        __syncwarp();
+        um_compact(bal, my_list, my_dst, cnt, thr, sbuf, k_sel, lane);
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(UM_TMEM_COLS) : "memory");
+    }
+}
+
+// ------------------------------------------------------------------ host side
+bool dense_umma_supported(int dtype, int d, int64_t n) {
+    return (dtype == 1 || dtype == 2) && d % UM_BK == 0 && d >= UM_BK && n >= 1;
+}
+
+cudaError_t dense_umma_plan(int64_t n, int d, int B, int k_sel, int num_sms, UmmaPlan* plan) {
+    if (k_sel > UM_CAP - 64) return cudaErrorInvalidValue;
+    plan->n_qblocks = (B + UM_BM - 1) / UM_BM;
+    const int64_t n_tiles = (n + UM_BN - 1) / UM_BN;
+    int64_t chunks = std::max<int64_t>(1, num_sms / plan->n_qblocks);
+    if (chunks > n_tiles) chunks = n_tiles;
+    plan->n_chunks = (int)chunks;
+    plan->scratch_bytes = (size_t)plan->n_chunks * plan->n_qblocks * UM_BM * UM_CAP * sizeof(uint64_t);
+    return cudaSuccess;
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode() {
+    static EncodeTiledFn fn = nullptr;
+    if (!fn) {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) != cudaSuccess ||
+            qres != cudaDriverEntryPointSuccess)
+            return nullptr;
+        fn = reinterpret_cast<EncodeTiledFn>(p);
+    }
+    return fn;
+}
+
+// the dtype of the map only matters for OOB fill / element size: both 16-bit types move as raw bits
+cudaError_t make_tmap_2d(void* tmap_out, const void* base, int64_t rows, int d, int box_rows) {
+    EncodeTiledFn enc = get_encode();
+    if (!enc) return cudaErrorNotSupported;
+    CUtensorMap tm;
+    cuuint64_t gdim[2] = {(cuuint64_t)d, (cuuint64_t)rows};
+    cuuint64_t gstride[1] = {(cuuint64_t)d * 2};
+    cuuint32_t box[2] = {(cuuint32_t)UM_BK, (cuuint32_t)box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = enc(&tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gdim, gstride, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return cudaErrorInvalidValue;
+    memcpy(tmap_out, &tm, sizeof(CUtensorMap));
+    return cudaSuccess;
+}
+
+cudaError_t dense_umma_scan(const void* X16, int dtype, int64_t n, int d, const void* Q16, int B,
+                            const uint32_t* mask, int k_sel, uint64_t* part, void* scratch, const UmmaPlan& plan,
+                            void* tmap_x, void* tmap_q, cudaStream_t st) {
+    (void)X16; (void)Q16;
+    static bool attr_set = false;
+    const size_t smem = sizeof(UmSmem) + 1024;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(dense_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        attr_set = true;
+    }
+    CUtensorMap tq, tx;
+    memcpy(&tq, tmap_q, sizeof tq);
+    memcpy(&tx, tmap_x, sizeof tx);
+    const int64_t n_tiles = (n + UM_BN - 1) / UM_BN;
+    const int64_t rows_per_chunk = (n_tiles + plan.n_chunks - 1) / plan.n_chunks * UM_BN;
+    const uint32_t fmt = (dtype == 2) ? 1u : 0u;  // BF16 : F16
+    const uint32_t idesc = (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(UM_BN >> 3) << 17) | ((uint32_t)(UM_BM >> 4) << 24);
+    const int grid = plan.n_chunks * plan.n_qblocks;
+    dense_umma_kernel<<<grid, UM_THREADS, smem, st>>>(tq, tx, n, d, B, plan.n_qblocks, rows_per_chunk, mask, k_sel,
+                                                      idesc, part, reinterpret_cast<uint64_t*>(scratch));
+    return cudaGetLastError();
+}
+
+}  // namespace brag

@@ -1,0 +1,709 @@
+// C ABI of libbrag.so (include/brag.h): engine handle, corpus upload, stage orchestration.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "../../include/brag.h"
+#include "kernels.h"
+
+namespace {
+
+thread_local std::string g_err;
+
+struct BragError : std::runtime_error {
+    using std::runtime_error::runtime_error;
+};
+
+#define CK(expr)                                                                                   \
+    do {                                                                                           \
+        cudaError_t _e = (expr);                                                                   \
+        if (_e != cudaSuccess) {                                                                   \
+            char _b[512];                                                                          \
+            snprintf(_b, sizeof _b, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__); \
+            throw BragError(_b);                                                                   \
+        }                                                                                          \
+    } while (0)
+
+#define REQUIRE(cond, msg)                \
+    do {                                  \
+        if (!(cond)) throw BragError(msg); \
+    } while (0)
+
+struct DevBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+    void* ensure(size_t bytes) {
+        if (bytes > cap) {
+            if (p) CK(cudaFree(p));
+            p = nullptr;
+            cap = 0;
+            size_t want = std::max(bytes, (size_t)256);
+            CK(cudaMalloc(&p, want));
+            cap = want;
+        }
+        return p;
+    }
+    template <typename T> T* as(size_t n) { return reinterpret_cast<T*>(ensure(n * sizeof(T))); }
+    void release() {
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+    }
+};
+
+struct DenseSpace {
+    void* x = nullptr;
+    int64_t n = 0;
+    int d = 0;
+    int dtype = 0;
+    bool umma_ok = false;
+    alignas(64) unsigned char tmap_x[128];
+};
+
+struct SparseSpace {
+    int64_t* term_ptr = nullptr;
+    uint32_t* doc = nullptr;
+    float* w = nullptr;
+    uint32_t* sub_off = nullptr;
+    int64_t V = 0, n_docs = 0, nnz = 0;
+    std::vector<int64_t> term_ptr_host;
+};
+
+struct MaskBuf {
+    uint32_t* bits = nullptr;
+    int64_t nbits = 0;
+};
+
+struct StageEvent {
+    int stage;
+    cudaEvent_t a, b;
+};
+
+}  // namespace
+
+struct brag_engine {
+    int device = 0;
+    int num_sms = 148;
+    int64_t id_offset = 0;
+    int force_path = -1;
+    std::map<std::string, DenseSpace> dense;
+    std::map<std::string, SparseSpace> sparse;
+    std::map<int, MaskBuf> masks;
+    // scratch (grow-only)
+    DevBuf qs, q16, part, tmp_a, tmp_b, keys1, keys2, umma_scratch, work_counter;
+    DevBuf h_in[6], h_out[4];      // staging for host-pointer calls
+    DevBuf hyb_ids, hyb_counts, hyb_scores;
+    alignas(64) unsigned char tmap_q[128];
+    // profiling
+    bool prof = false;
+    std::vector<StageEvent> events;
+    std::vector<cudaEvent_t> pool;
+    double ms[BRAG_N_STAGES] = {0};
+    int64_t stage_launches[BRAG_N_STAGES] = {0};
+    int64_t kernel_launches = 0;
+};
+
+namespace {
+
+struct StageTimer {
+    brag_engine* e;
+    int stage;
+    cudaStream_t st;
+    cudaEvent_t a = nullptr, b = nullptr;
+    StageTimer(brag_engine* e_, int stage_, cudaStream_t st_) : e(e_), stage(stage_), st(st_) {
+        e->stage_launches[stage]++;
+        if (!e->prof) return;
+        a = get();
+        b = get();
+        cudaEventRecord(a, st);
+    }
+    cudaEvent_t get() {
+        if (!e->pool.empty()) { cudaEvent_t ev = e->pool.back(); e->pool.pop_back(); return ev; }
+        cudaEvent_t ev;
+        CK(cudaEventCreate(&ev));
+        return ev;
+    }
+    ~StageTimer() {
+        if (!e->prof || !a) return;
+        cudaEventRecord(b, st);
+        e->events.push_back({stage, a, b});
+    }
+};
+
+void use_device(brag_engine* e) { CK(cudaSetDevice(e->device)); }
+
+int k_select(int k) { return std::min(512, ((k + 32) + 3) / 4 * 4); }
+
+const uint32_t* mask_ptr(brag_engine* e, int mask_id, int64_t need_bits) {
+    if (mask_id == 0) return nullptr;
+    auto it = e->masks.find(mask_id);
+    REQUIRE(it != e->masks.end(), "unknown mask_id");
+    REQUIRE(it->second.nbits >= need_bits, "mask has fewer bits than the space has rows");
+    return it->second.bits;
+}
+
+DenseSpace& dense_space(brag_engine* e, const char* name) {
+    auto it = e->dense.find(name);
+    REQUIRE(it != e->dense.end(), std::string("unknown dense space: ") + name);
+    return it->second;
+}
+SparseSpace& sparse_space(brag_engine* e, const char* name) {
+    auto it = e->sparse.find(name);
+    REQUIRE(it != e->sparse.end(), std::string("unknown sparse space: ") + name);
+    return it->second;
+}
+
+void free_dense(DenseSpace& s) {
+    if (s.x) cudaFree(s.x);
+    s.x = nullptr;
+}
+void free_sparse(SparseSpace& s) {
+    if (s.term_ptr) cudaFree(s.term_ptr);
+    if (s.doc) cudaFree(s.doc);
+    if (s.w) cudaFree(s.w);
+    if (s.sub_off) cudaFree(s.sub_off);
+    s = SparseSpace();
+}
+
+int pick_path(brag_engine* e, const DenseSpace& s, int B) {
+    if (!s.umma_ok) return 0;
+    if (e->force_path == 0) return 0;
+    if (e->force_path == 1) return 1;
+    return B > 8 ? 1 : 0;
+}
+
+// ---- device-pointer implementations -------------------------------------------------------
+void dense_topk_dev(brag_engine* e, DenseSpace& s, const float* Q, int B, int k, const uint32_t* mask,
+                    float* out_scores, int64_t* out_ids, int32_t* out_counts, cudaStream_t st) {
+    REQUIRE(B >= 1 && k >= 1 && k <= 512, "dense_topk: need B >= 1 and 1 <= k <= 512");
+    const int k_sel = k_select(k);
+    const int path = pick_path(e, s, B);
+    float* qs = e->qs.as<float>((size_t)B * s.d);
+    uint64_t* cand = e->keys1.as<uint64_t>((size_t)B * k_sel);
+    uint64_t* cand2 = e->keys2.as<uint64_t>((size_t)B * k_sel);
+    int P = 0;
+    uint64_t* part = nullptr;
+    {
+        StageTimer t(e, 0, st);
+        if (path == 1) {
+            brag::UmmaPlan plan;
+            CK(brag::dense_umma_plan(s.n, s.d, B, k_sel, e->num_sms, &plan));
+            const int Bpad = plan.n_qblocks * 128;
+            void* q16 = e->q16.ensure((size_t)Bpad * s.d * 2);
+            CK(brag::round_queries(Q, B, s.d, s.dtype, qs, q16, Bpad, st));
+            CK(brag::make_tmap_2d(e->tmap_q, q16, Bpad, s.d, 128));
+            P = plan.n_chunks;
+            part = e->part.as<uint64_t>((size_t)P * B * k_sel);
+            void* scratch = e->umma_scratch.ensure(plan.scratch_bytes);
+            CK(brag::dense_umma_scan(s.x, s.dtype, s.n, s.d, q16, B, mask, k_sel, part, scratch, plan, s.tmap_x,
+                                     e->tmap_q, st));
+            e->kernel_launches += 2;
+        } else {
+            CK(brag::round_queries(Q, B, s.d, s.dtype, qs, nullptr, B, st));
+            const int64_t ngroups = (s.n + 31) / 32;
+            int grid = (int)std::min<int64_t>((int64_t)e->num_sms * 2, std::max<int64_t>(1, (ngroups + 15) / 16));
+            P = grid;
+            part = e->part.as<uint64_t>((size_t)P * B * k_sel);
+            int launches = 0;
+            CK(brag::dense_gemv_scan(s.x, s.dtype, s.n, s.d, qs, B, mask, k_sel, part, grid, st, &launches));
+            e->kernel_launches += 1 + launches;
+        }
+    }
+    {
+        StageTimer t(e, 1, st);
+        size_t tmp = brag::merge_tmp_elems(P, B, k_sel);
+        uint64_t* ta = e->tmp_a.as<uint64_t>(tmp);
+        uint64_t* tb = e->tmp_b.as<uint64_t>(tmp);
+        int launches = 0;
+        CK(brag::merge_key_lists(part, P, B, k_sel, ta, tb, cand, k_sel, st, &launches));
+        CK(brag::rescore_keys(s.x, s.dtype, s.n, s.d, qs, B, cand, k_sel, cand2, st));
+        CK(brag::finalize_keys(cand2, B, k_sel, k, false, e->id_offset, out_scores, out_ids, out_counts, st));
+        e->kernel_launches += launches + 2;
+    }
+}
+
+void dense_rescore_dev(brag_engine* e, DenseSpace& s, const float* Q, int B, const int64_t* cand, int m, int k,
+                       const uint32_t* mask, float* out_scores, int64_t* out_ids, int32_t* out_counts,
+                       cudaStream_t st) {
+    REQUIRE(B >= 1 && k >= 1 && m >= 1 && m <= 8192 && k <= 8192, "dense_rescore: need m,k in [1,8192]");
+    StageTimer t(e, 1, st);
+    float* qs = e->qs.as<float>((size_t)B * s.d);
+    uint64_t* keys = e->keys1.as<uint64_t>((size_t)B * m);
+    CK(brag::round_queries(Q, B, s.d, s.dtype, qs, nullptr, B, st));
+    CK(brag::rescore_cands(s.x, s.dtype, s.n, s.d, qs, B, cand, m, e->id_offset, mask, keys, st));
+    CK(brag::finalize_keys(keys, B, m, k, true, e->id_offset, out_scores, out_ids, out_counts, st));
+    e->kernel_launches += 3;
+}
+
+void sparse_topk_dev(brag_engine* e, SparseSpace& s, const int32_t* q_ptr, const int32_t* q_terms,
+                     const double* q_vals, int B, int k, const uint32_t* mask, float* out_scores,
+                     int64_t* out_ids, int32_t* out_counts, cudaStream_t st) {
+    REQUIRE(B >= 1 && k >= 1 && k <= 512, "sparse_topk: need B >= 1 and 1 <= k <= 512");
+    brag::Bm25Plan plan = brag::bm25_plan(s.n_docs, B, e->num_sms);
+    const int P = plan.lists_per_query;
+    uint64_t* part = e->part.as<uint64_t>((size_t)P * B * k);
+    uint64_t* merged = e->keys1.as<uint64_t>((size_t)B * k);
+    int* wc = e->work_counter.as<int>(1);
+    {
+        StageTimer t(e, 2, st);
+        CK(brag::bm25_scan(s.term_ptr, s.doc, s.w, s.sub_off, s.V, s.n_docs, q_ptr, q_terms, q_vals, B, mask, k,
+                           part, plan, wc, st));
+        e->kernel_launches += 1;
+    }
+    {
+        StageTimer t(e, 3, st);
+        size_t tmp = brag::merge_tmp_elems(P, B, k);
+        uint64_t* ta = e->tmp_a.as<uint64_t>(tmp);
+        uint64_t* tb = e->tmp_b.as<uint64_t>(tmp);
+        int launches = 0;
+        CK(brag::merge_key_lists(part, P, B, k, ta, tb, merged, k, st, &launches));
+        CK(brag::finalize_keys(merged, B, k, k, false, e->id_offset, out_scores, out_ids, out_counts, st));
+        e->kernel_launches += launches + 1;
+    }
+}
+
+// ---- host staging helpers -----------------------------------------------------------------
+template <typename T>
+const T* to_dev(DevBuf& buf, const T* host, size_t n, cudaStream_t st) {
+    T* d = buf.as<T>(std::max<size_t>(n, 1));
+    if (n) CK(cudaMemcpyAsync(d, host, n * sizeof(T), cudaMemcpyHostToDevice, st));
+    return d;
+}
+template <typename T>
+void to_host(T* host, const T* dev, size_t n, cudaStream_t st) {
+    if (n && host) CK(cudaMemcpyAsync(host, dev, n * sizeof(T), cudaMemcpyDeviceToHost, st));
+}
+
+template <typename F>
+int guarded(F&& f) {
+    try {
+        f();
+        return 0;
+    } catch (const std::exception& ex) {
+        g_err = ex.what();
+        return 1;
+    } catch (...) {
+        g_err = "unknown error";
+        return 2;
+    }
+}
+
+}  // namespace
+
+// =============================================================================================
+extern "C" {
+
+const char* brag_last_error(void) { return g_err.c_str(); }
+int brag_version(void) { return 1; }
+
+int brag_create(int device, brag_engine** out) {
+    return guarded([&] {
+        REQUIRE(out != nullptr, "brag_create: out is NULL");
+        int count = 0;
+        cudaError_t ce = cudaGetDeviceCount(&count);
+        if (ce != cudaSuccess || count == 0)
+            throw BragError("brag_create: no CUDA device available (this engine has no CPU fallback)");
+        REQUIRE(device >= 0 && device < count, "brag_create: bad device index");
+        CK(cudaSetDevice(device));
+        cudaDeviceProp prop;
+        CK(cudaGetDeviceProperties(&prop, device));
+        REQUIRE(prop.major >= 10, "brag_create: this library is built for sm_100a (B200) only");
+        auto* e = new brag_engine();
+        e->device = device;
+        e->num_sms = prop.multiProcessorCount;
+        *out = e;
+    });
+}
+
+int brag_destroy(brag_engine* e) {
+    return guarded([&] {
+        if (!e) return;
+        cudaSetDevice(e->device);
+        cudaDeviceSynchronize();
+        for (auto& kv : e->dense) free_dense(kv.second);
+        for (auto& kv : e->sparse) free_sparse(kv.second);
+        for (auto& kv : e->masks) if (kv.second.bits) cudaFree(kv.second.bits);
+        DevBuf* bufs[] = {&e->qs, &e->q16, &e->part, &e->tmp_a, &e->tmp_b, &e->keys1, &e->keys2, &e->umma_scratch,
+                          &e->work_counter, &e->hyb_ids, &e->hyb_counts, &e->hyb_scores};
+        for (DevBuf* b : bufs) b->release();
+        for (auto& b : e->h_in) b.release();
+        for (auto& b : e->h_out) b.release();
+        for (auto& ev : e->events) { cudaEventDestroy(ev.a); cudaEventDestroy(ev.b); }
+        for (auto ev : e->pool) cudaEventDestroy(ev);
+        delete e;
+    });
+}
+
+int brag_set_id_offset(brag_engine* e, int64_t offset) {
+    return guarded([&] {
+        REQUIRE(e && offset >= 0, "brag_set_id_offset: bad arguments");
+        e->id_offset = offset;
+    });
+}
+
+int brag_dense_set(brag_engine* e, const char* name, const void* rows, int64_t n, int32_t d, int32_t dtype,
+                   int32_t on_device) {
+    return guarded([&] {
+        REQUIRE(e && name && rows, "brag_dense_set: NULL argument");
+        REQUIRE(dtype >= 0 && dtype <= 2, "brag_dense_set: dtype must be BRAG_F32/F16/BF16");
+        const int esz = dtype == 0 ? 4 : 2;
+        REQUIRE(n >= 1 && n < (int64_t)0xFFFFFFFFll, "brag_dense_set: need 1 <= n < 2^32-1");
+        REQUIRE(d >= 1 && (d * esz) % 16 == 0, "brag_dense_set: row bytes must be a multiple of 16");
+        REQUIRE(d * esz / 16 <= 256, "brag_dense_set: d too large (row > 4096 bytes)");
+        use_device(e);
+        auto it = e->dense.find(name);
+        if (it != e->dense.end()) { CK(cudaDeviceSynchronize()); free_dense(it->second); e->dense.erase(it); }
+        DenseSpace s;
+        s.n = n; s.d = d; s.dtype = dtype;
+        const size_t bytes = (size_t)n * d * esz;
+        CK(cudaMalloc(&s.x, bytes));
+        cudaError_t ce = cudaMemcpy(s.x, rows, bytes, on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice);
+        if (ce != cudaSuccess) { cudaFree(s.x); CK(ce); }
+        s.umma_ok = brag::dense_umma_supported(dtype, d, n);
+        if (s.umma_ok) {
+            cudaError_t te = brag::make_tmap_2d(s.tmap_x, s.x, n, d, 256);
+            if (te != cudaSuccess) s.umma_ok = false;
+        }
+        e->dense[name] = s;
+    });
+}
+
+int brag_dense_drop(brag_engine* e, const char* name) {
+    return guarded([&] {
+        REQUIRE(e && name, "brag_dense_drop: NULL argument");
+        use_device(e);
+        auto it = e->dense.find(name);
+        if (it == e->dense.end()) return;
+        CK(cudaDeviceSynchronize());
+        free_dense(it->second);
+        e->dense.erase(it);
+    });
+}
+
+int brag_sparse_set_csr(brag_engine* e, const char* name, const int64_t* term_ptr, const uint32_t* doc_ids,
+                        const float* weights, int64_t n_terms, int64_t n_docs, int32_t on_device) {
+    return guarded([&] {
+        REQUIRE(e && name && term_ptr, "brag_sparse_set_csr: NULL argument");
+        REQUIRE(n_terms >= 1 && n_docs >= 1 && n_docs < (int64_t)0xFFFFFFFFll, "brag_sparse_set_csr: bad sizes");
+        use_device(e);
+        auto it = e->sparse.find(name);
+        if (it != e->sparse.end()) { CK(cudaDeviceSynchronize()); free_sparse(it->second); e->sparse.erase(it); }
+        SparseSpace s;
+        s.V = n_terms; s.n_docs = n_docs;
+        s.term_ptr_host.resize(n_terms + 1);
+        const cudaMemcpyKind kind = on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
+        CK(cudaMemcpy(s.term_ptr_host.data(), term_ptr, (n_terms + 1) * sizeof(int64_t),
+                      on_device ? cudaMemcpyDeviceToHost : cudaMemcpyHostToHost));
+        REQUIRE(s.term_ptr_host[0] == 0, "brag_sparse_set_csr: term_ptr[0] must be 0");
+        for (int64_t t = 0; t < n_terms; ++t)
+            REQUIRE(s.term_ptr_host[t + 1] >= s.term_ptr_host[t], "brag_sparse_set_csr: term_ptr must be non-decreasing");
+        s.nnz = s.term_ptr_host[n_terms];
+        REQUIRE(s.nnz == 0 || (doc_ids && weights), "brag_sparse_set_csr: NULL postings");
+        try {
+            CK(cudaMalloc(&s.term_ptr, (n_terms + 1) * sizeof(int64_t)));
+            CK(cudaMemcpy(s.term_ptr, term_ptr, (n_terms + 1) * sizeof(int64_t), kind));
+            CK(cudaMalloc(&s.doc, std::max<size_t>(s.nnz, 1) * sizeof(uint32_t)));
+            CK(cudaMalloc(&s.w, std::max<size_t>(s.nnz, 1) * sizeof(float)));
+            if (s.nnz) {
+                CK(cudaMemcpy(s.doc, doc_ids, s.nnz * sizeof(uint32_t), kind));
+                CK(cudaMemcpy(s.w, weights, s.nnz * sizeof(float), kind));
+            }
+            const int64_t ns1 = (n_docs + brag::BM25_SUB - 1) / brag::BM25_SUB + 1;
+            CK(cudaMalloc(&s.sub_off, (size_t)n_terms * ns1 * sizeof(uint32_t)));
+            CK(brag::bm25_build_suboffsets(s.term_ptr, s.doc, n_terms, n_docs, s.sub_off, 0));
+            CK(cudaDeviceSynchronize());
+        } catch (...) {
+            free_sparse(s);
+            throw;
+        }
+        e->sparse[name] = std::move(s);
+    });
+}
+
+int brag_sparse_drop(brag_engine* e, const char* name) {
+    return guarded([&] {
+        REQUIRE(e && name, "brag_sparse_drop: NULL argument");
+        use_device(e);
+        auto it = e->sparse.find(name);
+        if (it == e->sparse.end()) return;
+        CK(cudaDeviceSynchronize());
+        free_sparse(it->second);
+        e->sparse.erase(it);
+    });
+}
+
+int brag_sparse_df(brag_engine* e, const char* name, int64_t* df_host, int64_t n_terms) {
+    return guarded([&] {
+        REQUIRE(e && name && df_host, "brag_sparse_df: NULL argument");
+        SparseSpace& s = sparse_space(e, name);
+        REQUIRE(n_terms == s.V, "brag_sparse_df: n_terms mismatch");
+        for (int64_t t = 0; t < n_terms; ++t) df_host[t] = s.term_ptr_host[t + 1] - s.term_ptr_host[t];
+    });
+}
+
+int brag_mask_set(brag_engine* e, int32_t mask_id, const uint32_t* bits, int64_t nbits, int32_t on_device) {
+    return guarded([&] {
+        REQUIRE(e && bits && mask_id >= 1 && nbits >= 1, "brag_mask_set: bad arguments");
+        use_device(e);
+        MaskBuf& m = e->masks[mask_id];
+        const size_t words = (size_t)((nbits + 31) / 32);
+        if (m.bits) { CK(cudaDeviceSynchronize()); CK(cudaFree(m.bits)); m.bits = nullptr; }
+        // padded so a warp's mask-word read past the last group stays in bounds
+        CK(cudaMalloc(&m.bits, (words + 64) * sizeof(uint32_t)));
+        CK(cudaMemset(m.bits, 0, (words + 64) * sizeof(uint32_t)));
+        CK(cudaMemcpy(m.bits, bits, words * sizeof(uint32_t), on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice));
+        m.nbits = nbits;
+    });
+}
+
+int brag_dense_topk(brag_engine* e, const char* name, const float* Q, int32_t B, int32_t k, int32_t mask_id,
+                    float* out_scores, int64_t* out_ids, int32_t* out_counts, int32_t on_device, void* stream) {
+    return guarded([&] {
+        REQUIRE(e && name && Q && out_scores && out_ids && out_counts, "brag_dense_topk: NULL argument");
+        use_device(e);
+        cudaStream_t st = (cudaStream_t)stream;
+        DenseSpace& s = dense_space(e, name);
+        const uint32_t* mask = mask_ptr(e, mask_id, s.n);
+        if (on_device) {
+            dense_topk_dev(e, s, Q, B, k, mask, out_scores, out_ids, out_counts, st);
+        } else {
+            const float* dq = to_dev(e->h_in[0], Q, (size_t)B * s.d, st);
+            float* ds = e->h_out[0].as<float>((size_t)B * k);
+            int64_t* di = e->h_out[1].as<int64_t>((size_t)B * k);
+            int32_t* dc = e->h_out[2].as<int32_t>(B);
+            dense_topk_dev(e, s, dq, B, k, mask, ds, di, dc, st);
+            to_host(out_scores, ds, (size_t)B * k, st);
+            to_host(out_ids, di, (size_t)B * k, st);
+            to_host(out_counts, dc, (size_t)B, st);
+            CK(cudaStreamSynchronize(st));
+        }
+    });
+}
+
+int brag_dense_rescore(brag_engine* e, const char* name, const float* Q, int32_t B, const int64_t* cand, int32_t m,
+                       int32_t k, int32_t mask_id, float* out_scores, int64_t* out_ids, int32_t* out_counts,
+                       int32_t on_device, void* stream) {
+    return guarded([&] {
+        REQUIRE(e && name && Q && cand && out_scores && out_ids && out_counts, "brag_dense_rescore: NULL argument");
+        use_device(e);
+        cudaStream_t st = (cudaStream_t)stream;
+        DenseSpace& s = dense_space(e, name);
+        const uint32_t* mask = mask_ptr(e, mask_id, s.n);
+        if (on_device) {
+            dense_rescore_dev(e, s, Q, B, cand, m, k, mask, out_scores, out_ids, out_counts, st);
+        } else {
+            const float* dq = to_dev(e->h_in[0], Q, (size_t)B * s.d, st);
+            const int64_t* dcand = to_dev(e->h_in[1], cand, (size_t)B * m, st);
+            float* ds = e->h_out[0].as<float>((size_t)B * k);
+            int64_t* di = e->h_out[1].as<int64_t>((size_t)B * k);
+            int32_t* dc = e->h_out[2].as<int32_t>(B);
+            dense_rescore_dev(e, s, dq, B, dcand, m, k, mask, ds, di, dc, st);
+            to_host(out_scores, ds, (size_t)B * k, st);
+            to_host(out_ids, di, (size_t)B * k, st);
+            to_host(out_counts, dc, (size_t)B, st);
+            CK(cudaStreamSynchronize(st));
+        }
+    });
+}
+
+int brag_sparse_topk(brag_engine* e, const char* name, const int32_t* q_ptr, const int32_t* q_terms,
+                     const double* q_vals, int32_t B, int32_t k, int32_t mask_id, float* out_scores,
+                     int64_t* out_ids, int32_t* out_counts, int32_t on_device, void* stream) {
+    return guarded([&] {
+        REQUIRE(e && name && q_ptr && out_scores && out_ids && out_counts, "brag_sparse_topk: NULL argument");
+        use_device(e);
+        cudaStream_t st = (cudaStream_t)stream;
+        SparseSpace& s = sparse_space(e, name);
+        const uint32_t* mask = mask_ptr(e, mask_id, s.n_docs);
+        if (on_device) {
+            sparse_topk_dev(e, s, q_ptr, q_terms, q_vals, B, k, mask, out_scores, out_ids, out_counts, st);
+        } else {
+            const size_t nt = (size_t)q_ptr[B];
+            for (int b = 0; b < B; ++b) {
+                REQUIRE(q_ptr[b + 1] >= q_ptr[b], "brag_sparse_topk: q_ptr must be non-decreasing");
+                for (int i = q_ptr[b] + 1; i < q_ptr[b + 1]; ++i)
+                    REQUIRE(q_terms[i] > q_terms[i - 1], "brag_sparse_topk: query term rows must be strictly ascending");
+            }
+            const int32_t* dp = to_dev(e->h_in[0], q_ptr, (size_t)B + 1, st);
+            const int32_t* dt = to_dev(e->h_in[1], q_terms, nt, st);
+            const double* dv = to_dev(e->h_in[2], q_vals, nt, st);
+            float* ds = e->h_out[0].as<float>((size_t)B * k);
+            int64_t* di = e->h_out[1].as<int64_t>((size_t)B * k);
+            int32_t* dc = e->h_out[2].as<int32_t>(B);
+            sparse_topk_dev(e, s, dp, dt, dv, B, k, mask, ds, di, dc, st);
+            to_host(out_scores, ds, (size_t)B * k, st);
+            to_host(out_ids, di, (size_t)B * k, st);
+            to_host(out_counts, dc, (size_t)B, st);
+            CK(cudaStreamSynchronize(st));
+        }
+    });
+}
+
+int brag_rrf(brag_engine* e, const int64_t* ids, const int32_t* counts, int32_t L, int32_t B, int32_t kmax,
+             int32_t limit, int32_t tie_mode, double* out_scores, int64_t* out_ids, int32_t* out_counts,
+             int32_t on_device, void* stream) {
+    return guarded([&] {
+        REQUIRE(e && ids && counts && out_scores && out_ids && out_counts, "brag_rrf: NULL argument");
+        REQUIRE(L >= 1 && L <= 16 && B >= 1 && kmax >= 1 && limit >= 1 && (int64_t)L * kmax <= 4096 && limit <= 4096,
+                "brag_rrf: need 1 <= L <= 16, L*kmax <= 4096, limit <= 4096");
+        use_device(e);
+        cudaStream_t st = (cudaStream_t)stream;
+        StageTimer t(e, 4, st);
+        e->kernel_launches += 1;
+        if (on_device) {
+            CK(brag::rrf_fuse(ids, counts, L, B, kmax, limit, tie_mode, out_scores, out_ids, out_counts, st));
+        } else {
+            const int64_t* di = to_dev(e->h_in[0], ids, (size_t)L * B * kmax, st);
+            const int32_t* dc = to_dev(e->h_in[1], counts, (size_t)L * B, st);
+            double* os = e->h_out[0].as<double>((size_t)B * limit);
+            int64_t* oi = e->h_out[1].as<int64_t>((size_t)B * limit);
+            int32_t* oc = e->h_out[2].as<int32_t>(B);
+            CK(brag::rrf_fuse(di, dc, L, B, kmax, limit, tie_mode, os, oi, oc, st));
+            to_host(out_scores, os, (size_t)B * limit, st);
+            to_host(out_ids, oi, (size_t)B * limit, st);
+            to_host(out_counts, oc, (size_t)B, st);
+            CK(cudaStreamSynchronize(st));
+        }
+    });
+}
+
+int brag_merge_topk(brag_engine* e, const float* scores, const int64_t* ids, const int32_t* counts, int32_t G,
+                    int32_t B, int32_t k, float* out_scores, int64_t* out_ids, int32_t* out_counts,
+                    int32_t on_device, void* stream) {
+    return guarded([&] {
+        REQUIRE(e && scores && ids && counts && out_scores && out_ids && out_counts, "brag_merge_topk: NULL argument");
+        REQUIRE(G >= 1 && B >= 1 && k >= 1 && (int64_t)G * k <= 8192, "brag_merge_topk: need G*k <= 8192");
+        use_device(e);
+        cudaStream_t st = (cudaStream_t)stream;
+        StageTimer t(e, 5, st);
+        e->kernel_launches += 1;
+        if (on_device) {
+            CK(brag::merge_scored_lists(scores, ids, counts, G, B, k, out_scores, out_ids, out_counts, st));
+        } else {
+            const float* ds = to_dev(e->h_in[0], scores, (size_t)G * B * k, st);
+            const int64_t* di = to_dev(e->h_in[1], ids, (size_t)G * B * k, st);
+            const int32_t* dc = to_dev(e->h_in[2], counts, (size_t)G * B, st);
+            float* os = e->h_out[0].as<float>((size_t)B * k);
+            int64_t* oi = e->h_out[1].as<int64_t>((size_t)B * k);
+            int32_t* oc = e->h_out[2].as<int32_t>(B);
+            CK(brag::merge_scored_lists(ds, di, dc, G, B, k, os, oi, oc, st));
+            to_host(out_scores, os, (size_t)B * k, st);
+            to_host(out_ids, oi, (size_t)B * k, st);
+            to_host(out_counts, oc, (size_t)B, st);
+            CK(cudaStreamSynchronize(st));
+        }
+    });
+}
+
+int brag_hybrid_topk(brag_engine* e, const char* dense_name, const char* sparse_name, const float* Q,
+                     const int32_t* q_ptr, const int32_t* q_terms, const double* q_vals, int32_t B, int32_t k,
+                     int32_t mask_id, double* out_scores, int64_t* out_ids, int32_t* out_counts, int32_t on_device,
+                     void* stream) {
+    return guarded([&] {
+        REQUIRE(e && dense_name && sparse_name && Q && q_ptr && out_scores && out_ids && out_counts,
+                "brag_hybrid_topk: NULL argument");
+        REQUIRE(k >= 1 && k <= 512, "brag_hybrid_topk: need 1 <= k <= 512");
+        use_device(e);
+        cudaStream_t st = (cudaStream_t)stream;
+        DenseSpace& ds = dense_space(e, dense_name);
+        SparseSpace& ss = sparse_space(e, sparse_name);
+        const uint32_t* mask = mask_ptr(e, mask_id, std::max(ds.n, ss.n_docs));
+        // stage lists live packed as [2][B][k] so RRF reads them in place
+        int64_t* ids = e->hyb_ids.as<int64_t>((size_t)2 * B * k);
+        int32_t* cnts = e->hyb_counts.as<int32_t>((size_t)2 * B);
+        float* scs = e->hyb_scores.as<float>((size_t)2 * B * k);
+        const float* dq = Q;
+        const int32_t *dp = q_ptr, *dt = q_terms;
+        const double* dv = q_vals;
+        double* os = out_scores;
+        int64_t* oi = out_ids;
+        int32_t* oc = out_counts;
+        if (!on_device) {
+            const size_t nt = (size_t)q_ptr[B];
+            dq = to_dev(e->h_in[0], Q, (size_t)B * ds.d, st);
+            dp = to_dev(e->h_in[1], q_ptr, (size_t)B + 1, st);
+            dt = to_dev(e->h_in[2], q_terms, nt, st);
+            dv = to_dev(e->h_in[3], q_vals, nt, st);
+            os = e->h_out[0].as<double>((size_t)B * k);
+            oi = e->h_out[1].as<int64_t>((size_t)B * k);
+            oc = e->h_out[2].as<int32_t>(B);
+        }
+        dense_topk_dev(e, ds, dq, B, k, mask, scs, ids, cnts, st);
+        sparse_topk_dev(e, ss, dp, dt, dv, B, k, mask, scs + (size_t)B * k, ids + (size_t)B * k, cnts + B, st);
+        {
+            StageTimer t(e, 4, st);
+            CK(brag::rrf_fuse(ids, cnts, 2, B, k, k, BRAG_TIE_ID, os, oi, oc, st));
+            e->kernel_launches += 1;
+        }
+        if (!on_device) {
+            to_host(out_scores, os, (size_t)B * k, st);
+            to_host(out_ids, oi, (size_t)B * k, st);
+            to_host(out_counts, oc, (size_t)B, st);
+            CK(cudaStreamSynchronize(st));
+        }
+    });
+}
+
+int brag_profile_enable(brag_engine* e, int32_t on) {
+    return guarded([&] {
+        REQUIRE(e, "NULL engine");
+        e->prof = on != 0;
+    });
+}
+
+int brag_profile_reset(brag_engine* e) {
+    return guarded([&] {
+        REQUIRE(e, "NULL engine");
+        use_device(e);
+        CK(cudaDeviceSynchronize());
+        for (auto& ev : e->events) { e->pool.push_back(ev.a); e->pool.push_back(ev.b); }
+        e->events.clear();
+        for (int i = 0; i < BRAG_N_STAGES; ++i) { e->ms[i] = 0; e->stage_launches[i] = 0; }
+        e->kernel_launches = 0;
+    });
+}
+
+int brag_profile_read(brag_engine* e, double* ms, int64_t* launches, int64_t* kernel_launches_total) {
+    return guarded([&] {
+        REQUIRE(e, "NULL engine");
+        use_device(e);
+        CK(cudaDeviceSynchronize());
+        for (auto& ev : e->events) {
+            float t = 0;
+            CK(cudaEventElapsedTime(&t, ev.a, ev.b));
+            e->ms[ev.stage] += t;
+            e->pool.push_back(ev.a);
+            e->pool.push_back(ev.b);
+        }
+        e->events.clear();
+        for (int i = 0; i < BRAG_N_STAGES; ++i) {
+            if (ms) ms[i] = e->ms[i];
+            if (launches) launches[i] = e->stage_launches[i];
+        }
+        if (kernel_launches_total) *kernel_launches_total = e->kernel_launches;
+    });
+}
+
+int brag_dense_path(brag_engine* e, const char* name, int32_t B) {
+    int path = -1;
+    int rc = guarded([&] {
+        REQUIRE(e && name, "NULL argument");
+        path = pick_path(e, dense_space(e, name), B);
+    });
+    return rc == 0 ? path : -1;
+}
+
+int brag_force_dense_path(brag_engine* e, int32_t path) {
+    return guarded([&] {
+        REQUIRE(e && path >= -1 && path <= 1, "brag_force_dense_path: path must be -1, 0 or 1");
+        e->force_path = path;
+    });
+}
+
+}  // extern "C"

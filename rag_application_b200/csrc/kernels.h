@@ -1,0 +1,66 @@
+// Internal launcher declarations (host side of each kernel family).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace brag {
+
+// ---- dense_gemv.cu
+cudaError_t dense_gemv_scan(const void* X, int dtype, int64_t n, int d, const float* Q, int B,
+                            const uint32_t* mask, int k_sel, uint64_t* part, int grid, cudaStream_t st,
+                            int* launches);
+
+// ---- dense_umma.cu
+struct UmmaPlan {
+    int n_chunks;      // corpus chunks (partial lists per query) = CTAs per query block
+    int n_qblocks;     // ceil(B / 128)
+    size_t scratch_bytes;  // per-(CTA, query) candidate lists in global memory
+};
+bool dense_umma_supported(int dtype, int d, int64_t n);
+cudaError_t dense_umma_plan(int64_t n, int d, int B, int k_sel, int num_sms, UmmaPlan* plan);
+// X16: [n, d] f16/bf16; Q16: [Bpad, d] same dtype (Bpad = n_qblocks*128, zero padded).
+// part: [n_chunks][B][k_sel] keys.
+cudaError_t dense_umma_scan(const void* X16, int dtype, int64_t n, int d, const void* Q16, int B,
+                            const uint32_t* mask, int k_sel, uint64_t* part, void* scratch,
+                            const UmmaPlan& plan, void* tmap_x, void* tmap_q, cudaStream_t st);
+// builds a CUtensorMap (128 bytes) for a [rows, d] 16-bit row-major matrix, box = [box_rows, 64]
+cudaError_t make_tmap_2d(void* tmap_out, const void* base, int64_t rows, int d, int box_rows);
+
+// ---- select.cu
+// multi-level merge of P key lists per query: in [P][B][kk] -> out [B][kout] sorted desc
+cudaError_t merge_key_lists(const uint64_t* in, int P, int B, int kk, uint64_t* tmp_a, uint64_t* tmp_b,
+                            uint64_t* out, int kout, cudaStream_t st, int* launches);
+size_t merge_tmp_elems(int P, int B, int kk);
+// round queries to the storage dtype: Qs f32 (rounded values) and optional 16-bit copy (padded rows zero)
+cudaError_t round_queries(const float* Q, int B, int d, int dtype, float* Qs, void* Q16, int Bpad,
+                          cudaStream_t st);
+// keys_in [B][m] (rows from a scan) -> re-scored keys (f64 accumulate, f32 score), 0 stays 0
+cudaError_t rescore_keys(const void* X, int dtype, int64_t n, int d, const float* Qs, int B,
+                         const uint64_t* keys_in, int m, uint64_t* keys_out, cudaStream_t st);
+// cand [B][m] global ids (-1 empty) -> scored keys with mask filter; duplicates keep one copy
+cudaError_t rescore_cands(const void* X, int dtype, int64_t n, int d, const float* Qs, int B,
+                          const int64_t* cand, int m, int64_t id_offset, const uint32_t* mask,
+                          uint64_t* keys_out, cudaStream_t st);
+// per query: sort m keys desc (optionally dropping duplicates), write first k to outputs
+cudaError_t finalize_keys(const uint64_t* keys, int B, int m, int k, bool dedup, int64_t id_offset,
+                          float* out_scores, int64_t* out_ids, int32_t* out_counts, cudaStream_t st);
+cudaError_t rrf_fuse(const int64_t* ids, const int32_t* counts, int L, int B, int kmax, int limit,
+                     int tie_mode, double* out_scores, int64_t* out_ids, int32_t* out_counts,
+                     cudaStream_t st);
+cudaError_t merge_scored_lists(const float* scores, const int64_t* ids, const int32_t* counts, int G,
+                               int B, int k, float* out_scores, int64_t* out_ids, int32_t* out_counts,
+                               cudaStream_t st);
+
+// ---- bm25.cu
+constexpr int BM25_SUB = 2048;  // documents per warp sub-tile
+cudaError_t bm25_build_suboffsets(const int64_t* term_ptr, const uint32_t* doc, int64_t V, int64_t n_docs,
+                                  uint32_t* sub_off, cudaStream_t st);
+struct Bm25Plan { int splits; int lists_per_query; int grid; };
+Bm25Plan bm25_plan(int64_t n_docs, int B, int num_sms);
+// part: [lists_per_query][B][k_sel]
+cudaError_t bm25_scan(const int64_t* term_ptr, const uint32_t* doc, const float* w, const uint32_t* sub_off,
+                      int64_t V, int64_t n_docs, const int32_t* q_ptr, const int32_t* q_terms,
+                      const double* q_vals, int B, const uint32_t* mask, int k_sel, uint64_t* part,
+                      const Bm25Plan& plan, int* work_counter, cudaStream_t st);
+
+}  // namespace brag

@@ -1,0 +1,384 @@
+// Selection-side kernels: k-way merge of partial (score,row) key lists, candidate re-scoring,
+// reciprocal rank fusion, and the per-shard list merge that follows the all-gather.
+// (e; reference requests qdrant_handler.py:317-329, :357-372.)
+// All of these touch <= a few thousand entries per query: latency-bound, not roofed.
+#include "common.cuh"
+#include "kernels.h"
+
+namespace brag {
+
+constexpr int SEL_THREADS = 512;
+constexpr int SEL_MAX = 8192;  // keys per CTA sort (64 KB of shared memory)
+
+// ------------------------------------------------------------------ merge of key lists
+__global__ void __launch_bounds__(SEL_THREADS)
+merge_keys_kernel(const uint64_t* __restrict__ in, int P, int B, int kk, int GP,
+                  uint64_t* __restrict__ out, int kout) {
+    extern __shared__ __align__(16) uint8_t smem_raw[];
+    uint64_t* a = reinterpret_cast<uint64_t*>(smem_raw);
+    const int b = blockIdx.x, pg = blockIdx.y, tid = threadIdx.x;
+    const int p0 = pg * GP, np = min(GP, P - p0);
+    const int n_in = np * kk;
+    const int n2 = next_pow2(max(n_in, kout));
+    for (int i = tid; i < n2; i += SEL_THREADS) {
+        uint64_t v = 0ull;
+        if (i < n_in) {
+            int p = p0 + i / kk, j = i % kk;
+            v = in[((size_t)p * B + b) * kk + j];
+        }
+        a[i] = v;
+    }
+    __syncthreads();
+    bitonic_desc(a, n2, tid, SEL_THREADS, [] { __syncthreads(); });
+    uint64_t* o = out + ((size_t)pg * B + b) * kout;
+    for (int i = tid; i < kout; i += SEL_THREADS) o[i] = a[i];
+}
+
+size_t merge_tmp_elems(int P, int B, int kk) {
+    int GP = max(2, SEL_MAX / kk);
+    int PG = (P + GP - 1) / GP;
+    return (size_t)PG * B * kk;
+}
+
+cudaError_t merge_key_lists(const uint64_t* in, int P, int B, int kk, uint64_t* tmp_a, uint64_t* tmp_b,
+                            uint64_t* out, int kout, cudaStream_t st, int* launches) {
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(merge_keys_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             SEL_MAX * 8);
+        if (e != cudaSuccess) return e;
+        attr_set = true;
+    }
+    if (kk > SEL_MAX / 2 || kout > SEL_MAX) return cudaErrorInvalidValue;
+    const int GP = max(2, SEL_MAX / kk);
+    const uint64_t* cur = in;
+    uint64_t* bufs[2] = {tmp_a, tmp_b};
+    int which = 0;
+    while (true) {
+        int PG = (P + GP - 1) / GP;
+        bool last = (PG == 1);
+        uint64_t* dst = last ? out : bufs[which];
+        int ko = last ? kout : kk;
+        int n_in = min(GP, P) * kk;
+        int n2 = 1;
+        while (n2 < max(n_in, ko)) n2 <<= 1;
+        merge_keys_kernel<<<dim3(B, PG), SEL_THREADS, (size_t)n2 * 8, st>>>(cur, P, B, kk, GP, dst, ko);
+        cudaError_t e = cudaGetLastError();
+        if (e != cudaSuccess) return e;
+        if (launches) ++*launches;
+        if (last) break;
+        cur = dst;
+        P = PG;
+        which ^= 1;
+    }
+    return cudaSuccess;
+}
+
+// ------------------------------------------------------------------ query rounding
+__global__ void round_queries_kernel(const float* __restrict__ Q, int B, int d, int dtype,
+                                     float* __restrict__ Qs, uint16_t* __restrict__ Q16, int Bpad) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t total = (size_t)Bpad * d;
+    if (i >= total) return;
+    const int b = (int)(i / d);
+    float v = (b < B) ? Q[i] : 0.0f;
+    uint16_t bits = 0;
+    if (dtype == 1) { __half h = __float2half_rn(v); v = __half2float(h); bits = __half_as_ushort(h); }
+    else if (dtype == 2) { __nv_bfloat16 h = __float2bfloat16_rn(v); v = __bfloat162float(h); bits = __bfloat16_as_ushort(h); }
+    if (b < B) Qs[i] = v;
+    if (Q16) Q16[i] = bits;
+}
+
+cudaError_t round_queries(const float* Q, int B, int d, int dtype, float* Qs, void* Q16, int Bpad,
+                          cudaStream_t st) {
+    size_t total = (size_t)Bpad * d;
+    int blocks = (int)((total + 255) / 256);
+    round_queries_kernel<<<blocks, 256, 0, st>>>(Q, B, d, dtype, Qs, reinterpret_cast<uint16_t*>(Q16), Bpad);
+    return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------ re-scoring (f64 accumulate)
+template <int DT>
+__device__ __forceinline__ double row_dot_f64(const uint4* __restrict__ X, int64_t row, int d,
+                                              const float* __restrict__ q, int lane) {
+    constexpr int EPC = (DT == 0) ? 4 : 8;
+    const int C = d / EPC;
+    double acc = 0.0;
+    for (int c = lane; c < C; c += 32) {
+        uint4 v = __ldg(X + (size_t)row * C + c);
+        float f[8];
+        if constexpr (DT == 0) {
+            f[0] = __uint_as_float(v.x); f[1] = __uint_as_float(v.y); f[2] = __uint_as_float(v.z); f[3] = __uint_as_float(v.w);
+        } else {
+            Unpack<DT>::run(v, f);
+        }
+#pragma unroll
+        for (int e = 0; e < EPC; ++e) acc += (double)f[e] * (double)q[c * EPC + e];
+    }
+#pragma unroll
+    for (int off = 16; off >= 1; off >>= 1) acc += __shfl_xor_sync(0xFFFFFFFFu, acc, off);
+    return acc;
+}
+
+__device__ __forceinline__ double row_dot_any(const void* X, int dtype, int64_t row, int d, const float* q,
+                                              int lane) {
+    const uint4* X4 = reinterpret_cast<const uint4*>(X);
+    if (dtype == 0) return row_dot_f64<0>(X4, row, d, q, lane);
+    if (dtype == 1) return row_dot_f64<1>(X4, row, d, q, lane);
+    return row_dot_f64<2>(X4, row, d, q, lane);
+}
+
+__global__ void rescore_keys_kernel(const void* __restrict__ X, int dtype, int64_t n, int d,
+                                    const float* __restrict__ Qs, int B, const uint64_t* __restrict__ keys_in,
+                                    int m, uint64_t* __restrict__ keys_out) {
+    const int64_t w = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (w >= (int64_t)B * m) return;
+    const int b = (int)(w / m);
+    const uint64_t key = keys_in[w];
+    uint64_t out = 0ull;
+    if (key != 0ull) {
+        const uint32_t row = key_row(key);
+        if ((int64_t)row < n) {
+            double s = row_dot_any(X, dtype, row, d, Qs + (size_t)b * d, lane);
+            out = make_key((float)s, row);
+        }
+    }
+    if (lane == 0) keys_out[w] = out;
+}
+
+cudaError_t rescore_keys(const void* X, int dtype, int64_t n, int d, const float* Qs, int B,
+                         const uint64_t* keys_in, int m, uint64_t* keys_out, cudaStream_t st) {
+    int64_t threads = (int64_t)B * m * 32;
+    int blocks = (int)((threads + 255) / 256);
+    rescore_keys_kernel<<<blocks, 256, 0, st>>>(X, dtype, n, d, Qs, B, keys_in, m, keys_out);
+    return cudaGetLastError();
+}
+
+__global__ void rescore_cands_kernel(const void* __restrict__ X, int dtype, int64_t n, int d,
+                                     const float* __restrict__ Qs, int B, const int64_t* __restrict__ cand,
+                                     int m, int64_t id_offset, const uint32_t* __restrict__ mask,
+                                     uint64_t* __restrict__ keys_out) {
+    const int64_t w = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (w >= (int64_t)B * m) return;
+    const int b = (int)(w / m);
+    const int64_t row = cand[w] < 0 ? -1 : cand[w] - id_offset;
+    uint64_t out = 0ull;
+    if (row >= 0 && row < n && mask_test(mask, (uint32_t)row)) {
+        double s = row_dot_any(X, dtype, row, d, Qs + (size_t)b * d, lane);
+        out = make_key((float)s, (uint32_t)row);
+    }
+    if (lane == 0) keys_out[w] = out;
+}
+
+cudaError_t rescore_cands(const void* X, int dtype, int64_t n, int d, const float* Qs, int B,
+                          const int64_t* cand, int m, int64_t id_offset, const uint32_t* mask,
+                          uint64_t* keys_out, cudaStream_t st) {
+    int64_t threads = (int64_t)B * m * 32;
+    int blocks = (int)((threads + 255) / 256);
+    rescore_cands_kernel<<<blocks, 256, 0, st>>>(X, dtype, n, d, Qs, B, cand, m, id_offset, mask, keys_out);
+    return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------ finalize: sort, dedup, unpack
+__global__ void __launch_bounds__(SEL_THREADS)
+finalize_keys_kernel(const uint64_t* __restrict__ keys, int m, int k, int dedup, int64_t id_offset,
+                     float* __restrict__ out_scores, int64_t* __restrict__ out_ids,
+                     int32_t* __restrict__ out_counts) {
+    extern __shared__ __align__(16) uint8_t smem_raw[];
+    uint64_t* a = reinterpret_cast<uint64_t*>(smem_raw);
+    __shared__ int count;
+    const int b = blockIdx.x, tid = threadIdx.x;
+    const int n2 = next_pow2(max(m, k));
+    for (int i = tid; i < n2; i += SEL_THREADS) a[i] = (i < m) ? keys[(size_t)b * m + i] : 0ull;
+    if (tid == 0) count = 0;
+    __syncthreads();
+    bitonic_desc(a, n2, tid, SEL_THREADS, [] { __syncthreads(); });
+    if (dedup) {
+        // equal keys == same row (and same score): keep the first copy
+        uint64_t prev[SEL_MAX / SEL_THREADS];
+        int t = 0;
+        for (int i = tid; i < n2; i += SEL_THREADS, ++t) prev[t] = (i > 0) ? a[i - 1] : ~0ull;
+        __syncthreads();
+        t = 0;
+        for (int i = tid; i < n2; i += SEL_THREADS, ++t) if (a[i] == prev[t]) a[i] = 0ull;
+        __syncthreads();
+        bitonic_desc(a, n2, tid, SEL_THREADS, [] { __syncthreads(); });
+    }
+    for (int i = tid; i < k; i += SEL_THREADS) {
+        uint64_t key = a[i];
+        bool ok = key != 0ull;
+        out_scores[(size_t)b * k + i] = ok ? key_score(key) : -INFINITY;
+        out_ids[(size_t)b * k + i] = ok ? (int64_t)key_row(key) + id_offset : -1;
+        if (ok) atomicAdd(&count, 1);
+    }
+    __syncthreads();
+    if (tid == 0) out_counts[b] = count;
+}
+
+cudaError_t finalize_keys(const uint64_t* keys, int B, int m, int k, bool dedup, int64_t id_offset,
+                          float* out_scores, int64_t* out_ids, int32_t* out_counts, cudaStream_t st) {
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(finalize_keys_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             SEL_MAX * 8);
+        if (e != cudaSuccess) return e;
+        attr_set = true;
+    }
+    int n2 = 1;
+    while (n2 < (m > k ? m : k)) n2 <<= 1;
+    if (n2 > SEL_MAX) return cudaErrorInvalidValue;
+    finalize_keys_kernel<<<B, SEL_THREADS, (size_t)n2 * 8, st>>>(keys, m, k, dedup ? 1 : 0, id_offset,
+                                                               out_scores, out_ids, out_counts);
+    return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------ reciprocal rank fusion
+struct RrfEntry {
+    double s;
+    uint32_t tb;   // tie-break, ascending
+    int32_t src;   // flattened source index
+    __device__ bool operator<(const RrfEntry& o) const { return s < o.s || (s == o.s && tb > o.tb); }
+};
+
+constexpr int RRF_THREADS = 256;
+constexpr int RRF_MAX = 4096;
+
+__global__ void __launch_bounds__(RRF_THREADS)
+rrf_kernel(const int64_t* __restrict__ ids, const int32_t* __restrict__ counts, int L, int B, int kmax,
+           int limit, int tie_mode, double* __restrict__ out_scores, int64_t* __restrict__ out_ids,
+           int32_t* __restrict__ out_counts) {
+    extern __shared__ __align__(16) uint8_t smem_raw[];
+    // layout: entries [n2] (16 B each) | flat ids [E] | flat pos [E]
+    __shared__ int s_off[17];
+    __shared__ int n_unique;
+    const int b = blockIdx.x, tid = threadIdx.x;
+    if (tid == 0) {
+        int o = 0;
+        for (int l = 0; l < L; ++l) { s_off[l] = o; o += min(counts[(size_t)l * B + b], kmax); }
+        s_off[L] = o;
+        n_unique = 0;
+    }
+    __syncthreads();
+    const int E = s_off[L];
+    const int n2 = next_pow2(max(E, max(limit, 1)));
+    RrfEntry* ent = reinterpret_cast<RrfEntry*>(smem_raw);
+    int64_t* fid = reinterpret_cast<int64_t*>(smem_raw + (size_t)n2 * sizeof(RrfEntry));
+    int32_t* fpos = reinterpret_cast<int32_t*>(fid + E);
+    for (int l = 0; l < L; ++l) {
+        const int c = s_off[l + 1] - s_off[l];
+        for (int j = tid; j < c; j += RRF_THREADS) {
+            fid[s_off[l] + j] = ids[((size_t)l * B + b) * kmax + j];
+            fpos[s_off[l] + j] = j;
+        }
+    }
+    __syncthreads();
+    for (int e = tid; e < n2; e += RRF_THREADS) {
+        RrfEntry r;
+        r.s = -1.0; r.tb = 0xFFFFFFFFu; r.src = -1;
+        if (e < E) {
+            const int64_t id = fid[e];
+            double s = 0.0;
+            bool first = true;
+            for (int f = 0; f < E; ++f) {
+                if (fid[f] == id) {
+                    if (f < e) first = false;
+                    s += 1.0 / (double)(2 + fpos[f]);   // list order == upstream accumulation order
+                }
+            }
+            if (first) {
+                r.s = s;
+                r.tb = (tie_mode == 0) ? (uint32_t)id : (uint32_t)e;
+                r.src = e;
+                atomicAdd(&n_unique, 1);
+            }
+        }
+        ent[e] = r;
+    }
+    __syncthreads();
+    bitonic_desc(ent, n2, tid, RRF_THREADS, [] { __syncthreads(); });
+    const int nu = min(n_unique, limit);
+    for (int i = tid; i < limit; i += RRF_THREADS) {
+        const bool ok = i < nu;
+        out_scores[(size_t)b * limit + i] = ok ? ent[i].s : -INFINITY;
+        out_ids[(size_t)b * limit + i] = ok ? fid[ent[i].src] : -1;
+    }
+    if (tid == 0) out_counts[b] = nu;
+}
+
+cudaError_t rrf_fuse(const int64_t* ids, const int32_t* counts, int L, int B, int kmax, int limit,
+                     int tie_mode, double* out_scores, int64_t* out_ids, int32_t* out_counts,
+                     cudaStream_t st) {
+    if (L < 1 || L > 16 || (int64_t)L * kmax > RRF_MAX || limit > RRF_MAX) return cudaErrorInvalidValue;
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(rrf_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             RRF_MAX * (int)sizeof(RrfEntry) + RRF_MAX * 12);
+        if (e != cudaSuccess) return e;
+        attr_set = true;
+    }
+    int E = L * kmax;
+    int n2 = 1;
+    while (n2 < (E > limit ? E : limit)) n2 <<= 1;
+    size_t smem = (size_t)n2 * sizeof(RrfEntry) + (size_t)E * 12;
+    rrf_kernel<<<B, RRF_THREADS, smem, st>>>(ids, counts, L, B, kmax, limit, tie_mode, out_scores, out_ids,
+                                             out_counts);
+    return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------ merge of per-shard lists
+__global__ void __launch_bounds__(SEL_THREADS)
+merge_scored_kernel(const float* __restrict__ scores, const int64_t* __restrict__ ids,
+                    const int32_t* __restrict__ counts, int G, int B, int k, float* __restrict__ out_scores,
+                    int64_t* __restrict__ out_ids, int32_t* __restrict__ out_counts) {
+    extern __shared__ __align__(16) uint8_t smem_raw[];
+    uint64_t* a = reinterpret_cast<uint64_t*>(smem_raw);
+    __shared__ int count;
+    const int b = blockIdx.x, tid = threadIdx.x;
+    const int n_in = G * k;
+    const int n2 = next_pow2(n_in);
+    if (tid == 0) count = 0;
+    for (int i = tid; i < n2; i += SEL_THREADS) {
+        uint64_t v = 0ull;
+        if (i < n_in) {
+            const int g = i / k, j = i % k;
+            if (j < counts[(size_t)g * B + b]) {
+                const size_t src = ((size_t)g * B + b) * k + j;
+                v = make_key(scores[src], (uint32_t)ids[src]);   // global ids < 2^32
+            }
+        }
+        a[i] = v;
+    }
+    __syncthreads();
+    bitonic_desc(a, n2, tid, SEL_THREADS, [] { __syncthreads(); });
+    for (int i = tid; i < k; i += SEL_THREADS) {
+        const uint64_t key = a[i];
+        const bool ok = key != 0ull;
+        out_scores[(size_t)b * k + i] = ok ? key_score(key) : -INFINITY;
+        out_ids[(size_t)b * k + i] = ok ? (int64_t)key_row(key) : -1;
+        if (ok) atomicAdd(&count, 1);
+    }
+    __syncthreads();
+    if (tid == 0) out_counts[b] = count;
+}
+
+cudaError_t merge_scored_lists(const float* scores, const int64_t* ids, const int32_t* counts, int G,
+                               int B, int k, float* out_scores, int64_t* out_ids, int32_t* out_counts,
+                               cudaStream_t st) {
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(merge_scored_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             SEL_MAX * 8);
+        if (e != cudaSuccess) return e;
+        attr_set = true;
+    }
+    int n2 = 1;
+    while (n2 < G * k) n2 <<= 1;
+    if (n2 > SEL_MAX) return cudaErrorInvalidValue;
+    merge_scored_kernel<<<B, SEL_THREADS, (size_t)n2 * 8, st>>>(scores, ids, counts, G, B, k, out_scores,
+                                                             out_ids, out_counts);
+    return cudaGetLastError();
+}
+
+}  // namespace brag

@@ -1,0 +1,242 @@
+"""Python handle over the C ABI (include/brag.h).  Thin: validates shapes, picks host vs device
+pointers, and returns numpy arrays (host calls) or torch CUDA tensors (device calls).
+
+Host calls (numpy in / numpy out) are the reference-facing path: host->device and
+device->host copies happen inside the call.  Device calls (torch CUDA tensors in/out) are
+stream-ordered on torch's current stream and never synchronise."""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional, Sequence, Tuple
+
+import numpy as np
+
+from . import _native
+
+DTYPES = {"f32": 0, "f16": 1, "bf16": 2}
+STAGES = ("dense_scan", "dense_select", "sparse_scan", "sparse_select", "rrf", "merge")
+TIE_ID, TIE_FIRST_SEEN = 0, 1
+
+
+def to_storage(x: np.ndarray, dtype: str) -> np.ndarray:
+    """float32 rows -> storage bits (f32: float32, f16: float16, bf16: uint16 RNE bits)."""
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    if dtype == "f32":
+        return x
+    if dtype == "f16":
+        return x.astype(np.float16)
+    if dtype == "bf16":
+        u = x.view(np.uint32).astype(np.uint64)
+        return (((u + 0x7FFF + ((u >> 16) & 1)) >> 16) & 0xFFFF).astype(np.uint16)
+    raise ValueError(f"unknown storage dtype {dtype!r}")
+
+
+def _is_torch_cuda(t) -> bool:
+    return hasattr(t, "data_ptr") and hasattr(t, "is_cuda") and t.is_cuda
+
+
+def _ptr(a):
+    if a is None:
+        return None
+    if _is_torch_cuda(a):
+        return a.data_ptr()
+    return a.ctypes.data
+
+
+def _stream():
+    import torch
+    return torch.cuda.current_stream().cuda_stream
+
+
+class Engine:
+    """One GPU, one corpus shard.  Fails loudly when libbrag.so or a B200 is missing."""
+
+    def __init__(self, device: int = 0):
+        self._lib = _native.load()
+        h = C.c_void_p()
+        _native.check(self._lib.brag_create(device, C.byref(h)))
+        self._h = h
+        self.device = device
+        self._spaces = {}
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._lib.brag_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ------------------------------------------------------------------ corpus
+    def set_id_offset(self, offset: int):
+        _native.check(self._lib.brag_set_id_offset(self._h, int(offset)))
+
+    def dense_set(self, name: str, rows, dtype: str = "f32"):
+        """rows: numpy float32 [n,d] (converted to `dtype` on the host) or a torch CUDA tensor
+        already in the storage dtype (float32 / float16 / bfloat16)."""
+        if _is_torch_cuda(rows):
+            import torch
+            tmap = {torch.float32: "f32", torch.float16: "f16", torch.bfloat16: "bf16"}
+            dtype = tmap[rows.dtype]
+            rows = rows.contiguous()
+            n, d = rows.shape
+            torch.cuda.current_stream().synchronize()
+            _native.check(self._lib.brag_dense_set(self._h, name.encode(), rows.data_ptr(), n, d, DTYPES[dtype], 1))
+        else:
+            rows = np.asarray(rows)
+            n, d = rows.shape
+            st = to_storage(rows, dtype)
+            _native.check(self._lib.brag_dense_set(self._h, name.encode(), st.ctypes.data, n, d, DTYPES[dtype], 0))
+        self._spaces[name] = (n, d, dtype)
+
+    def dense_drop(self, name: str):
+        _native.check(self._lib.brag_dense_drop(self._h, name.encode()))
+        self._spaces.pop(name, None)
+
+    def sparse_set_csr(self, name: str, term_ptr, doc, w, n_docs: int):
+        if _is_torch_cuda(term_ptr):
+            import torch
+            assert term_ptr.dtype == torch.int64 and doc.dtype in (torch.int32, torch.uint32) and w.dtype == torch.float32
+            term_ptr, doc, w = term_ptr.contiguous(), doc.contiguous(), w.contiguous()
+            torch.cuda.current_stream().synchronize()
+            _native.check(self._lib.brag_sparse_set_csr(self._h, name.encode(), term_ptr.data_ptr(), doc.data_ptr(),
+                                                        w.data_ptr(), term_ptr.numel() - 1, int(n_docs), 1))
+        else:
+            term_ptr = np.ascontiguousarray(term_ptr, dtype=np.int64)
+            doc = np.ascontiguousarray(doc, dtype=np.uint32)
+            w = np.ascontiguousarray(w, dtype=np.float32)
+            _native.check(self._lib.brag_sparse_set_csr(self._h, name.encode(), term_ptr.ctypes.data, doc.ctypes.data,
+                                                        w.ctypes.data, len(term_ptr) - 1, int(n_docs), 0))
+
+    def sparse_drop(self, name: str):
+        _native.check(self._lib.brag_sparse_drop(self._h, name.encode()))
+
+    def sparse_df(self, name: str, n_terms: int) -> np.ndarray:
+        df = np.zeros(n_terms, dtype=np.int64)
+        _native.check(self._lib.brag_sparse_df(self._h, name.encode(), df.ctypes.data, n_terms))
+        return df
+
+    def mask_set(self, mask_id: int, mask):
+        """mask: numpy bool [n] (packed here) / uint32 words, or torch CUDA int32 words."""
+        if _is_torch_cuda(mask):
+            import torch
+            torch.cuda.current_stream().synchronize()
+            _native.check(self._lib.brag_mask_set(self._h, mask_id, mask.data_ptr(), mask.numel() * 32, 1))
+            return
+        mask = np.asarray(mask)
+        if mask.dtype == np.bool_:
+            nbits = len(mask)
+            words = np.packbits(mask, bitorder="little")
+            pad = (-len(words)) % 4
+            if pad:
+                words = np.concatenate([words, np.zeros(pad, np.uint8)])
+            words = words.view(np.uint32)
+        else:
+            words = np.ascontiguousarray(mask, dtype=np.uint32)
+            nbits = len(words) * 32
+        _native.check(self._lib.brag_mask_set(self._h, mask_id, words.ctypes.data, nbits, 0))
+
+    # ------------------------------------------------------------------ queries
+    def _outs(self, B, k, dev, score_dtype="f32"):
+        if dev:
+            import torch
+            d = torch.device("cuda", self.device)
+            sdt = torch.float32 if score_dtype == "f32" else torch.float64
+            return (torch.empty((B, k), dtype=sdt, device=d), torch.empty((B, k), dtype=torch.int64, device=d),
+                    torch.empty((B,), dtype=torch.int32, device=d))
+        sdt = np.float32 if score_dtype == "f32" else np.float64
+        return np.empty((B, k), sdt), np.empty((B, k), np.int64), np.empty((B,), np.int32)
+
+    def dense_topk(self, name: str, Q, k: int, mask_id: int = 0):
+        dev = _is_torch_cuda(Q)
+        Q = Q.contiguous() if dev else np.ascontiguousarray(Q, dtype=np.float32)
+        B = Q.shape[0]
+        s, i, c = self._outs(B, k, dev)
+        _native.check(self._lib.brag_dense_topk(self._h, name.encode(), _ptr(Q), B, k, mask_id, _ptr(s), _ptr(i), _ptr(c),
+                                                int(dev), _stream() if dev else None))
+        return s, i, c
+
+    def dense_rescore(self, name: str, Q, cand, k: int, mask_id: int = 0):
+        dev = _is_torch_cuda(Q)
+        Q = Q.contiguous() if dev else np.ascontiguousarray(Q, dtype=np.float32)
+        cand = cand.contiguous() if dev else np.ascontiguousarray(cand, dtype=np.int64)
+        B, m = cand.shape
+        s, i, c = self._outs(B, k, dev)
+        _native.check(self._lib.brag_dense_rescore(self._h, name.encode(), _ptr(Q), B, _ptr(cand), m, k, mask_id, _ptr(s),
+                                                   _ptr(i), _ptr(c), int(dev), _stream() if dev else None))
+        return s, i, c
+
+    def sparse_topk(self, name: str, q_ptr, q_terms, q_vals, k: int, mask_id: int = 0):
+        dev = _is_torch_cuda(q_ptr)
+        if not dev:
+            q_ptr = np.ascontiguousarray(q_ptr, dtype=np.int32)
+            q_terms = np.ascontiguousarray(q_terms, dtype=np.int32)
+            q_vals = np.ascontiguousarray(q_vals, dtype=np.float64)
+        B = q_ptr.shape[0] - 1
+        s, i, c = self._outs(B, k, dev)
+        _native.check(self._lib.brag_sparse_topk(self._h, name.encode(), _ptr(q_ptr), _ptr(q_terms), _ptr(q_vals), B, k,
+                                                 mask_id, _ptr(s), _ptr(i), _ptr(c), int(dev), _stream() if dev else None))
+        return s, i, c
+
+    def rrf(self, ids, counts, limit: int, tie: int = TIE_ID):
+        """ids [L,B,kmax] int64, counts [L,B] int32 -> (scores f64 [B,limit], ids, counts)."""
+        dev = _is_torch_cuda(ids)
+        if not dev:
+            ids = np.ascontiguousarray(ids, dtype=np.int64)
+            counts = np.ascontiguousarray(counts, dtype=np.int32)
+        L, B, kmax = ids.shape
+        s, i, c = self._outs(B, limit, dev, "f64")
+        _native.check(self._lib.brag_rrf(self._h, _ptr(ids), _ptr(counts), L, B, kmax, limit, tie, _ptr(s), _ptr(i), _ptr(c),
+                                         int(dev), _stream() if dev else None))
+        return s, i, c
+
+    def merge_topk(self, scores, ids, counts):
+        """[G,B,k] per-shard lists -> [B,k]."""
+        dev = _is_torch_cuda(ids)
+        if not dev:
+            scores = np.ascontiguousarray(scores, dtype=np.float32)
+            ids = np.ascontiguousarray(ids, dtype=np.int64)
+            counts = np.ascontiguousarray(counts, dtype=np.int32)
+        G, B, k = ids.shape
+        s, i, c = self._outs(B, k, dev)
+        _native.check(self._lib.brag_merge_topk(self._h, _ptr(scores), _ptr(ids), _ptr(counts), G, B, k, _ptr(s), _ptr(i),
+                                                _ptr(c), int(dev), _stream() if dev else None))
+        return s, i, c
+
+    def hybrid_topk(self, dense_name: str, sparse_name: str, Q, q_ptr, q_terms, q_vals, k: int, mask_id: int = 0):
+        dev = _is_torch_cuda(Q)
+        if not dev:
+            Q = np.ascontiguousarray(Q, dtype=np.float32)
+            q_ptr = np.ascontiguousarray(q_ptr, dtype=np.int32)
+            q_terms = np.ascontiguousarray(q_terms, dtype=np.int32)
+            q_vals = np.ascontiguousarray(q_vals, dtype=np.float64)
+        B = Q.shape[0]
+        s, i, c = self._outs(B, k, dev, "f64")
+        _native.check(self._lib.brag_hybrid_topk(self._h, dense_name.encode(), sparse_name.encode(), _ptr(Q), _ptr(q_ptr),
+                                                 _ptr(q_terms), _ptr(q_vals), B, k, mask_id, _ptr(s), _ptr(i), _ptr(c),
+                                                 int(dev), _stream() if dev else None))
+        return s, i, c
+
+    # ------------------------------------------------------------------ introspection
+    def profile_enable(self, on: bool = True):
+        _native.check(self._lib.brag_profile_enable(self._h, int(on)))
+
+    def profile_reset(self):
+        _native.check(self._lib.brag_profile_reset(self._h))
+
+    def profile_read(self):
+        ms = (C.c_double * len(STAGES))()
+        ln = (C.c_int64 * len(STAGES))()
+        tot = C.c_int64()
+        _native.check(self._lib.brag_profile_read(self._h, ms, ln, C.byref(tot)))
+        return ({s: ms[i] for i, s in enumerate(STAGES)}, {s: ln[i] for i, s in enumerate(STAGES)}, tot.value)
+
+    def dense_path(self, name: str, B: int) -> str:
+        p = self._lib.brag_dense_path(self._h, name.encode(), B)
+        return {0: "gemv", 1: "tcgen05"}.get(p, "?")
+
+    def force_dense_path(self, path: Optional[str]):
+        _native.check(self._lib.brag_force_dense_path(self._h, {None: -1, "gemv": 0, "tcgen05": 1}[path]))

@@ -1,0 +1,284 @@
+"""GPU parity: every C-ABI stage against the CPU oracle on the same seeded inputs.
+
+Bar (BASELINE.json north_star): bit-exact ids / ranks / counts for the integer work (BM25
+candidate sets, RRF ranks, top-k id sets with ties broken by id); dense scores within 1e-3
+relative (observed ~1e-7: candidates are re-scored with float64 accumulation)."""
+import numpy as np
+import pytest
+
+from oracle import oracle as O
+from rag_application_b200 import synth
+
+pytestmark = pytest.mark.gpu
+
+DENSE_RTOL = 1e-3      # tolerance stated by north_star
+TIE_EPS = 4e-7         # |score gap| below which two rows count as a boundary near-tie
+
+
+def check_dense(xs, qs, k, got_s, got_i, got_c, mask=None, id_offset=0):
+    """Compare one query's GPU list with the oracle; near-ties at the k boundary may swap."""
+    n = xs.shape[0]
+    all_s = O.dense_scores(xs, qs)
+    ids = np.arange(n)
+    if mask is not None:
+        ids = ids[mask]
+    o = O.topk_order(all_s[ids], ids, k)
+    exp_i, exp_s = ids[o], all_s[ids][o]
+    assert got_c == len(exp_i)
+    gi = got_i[:got_c] - id_offset
+    gs = got_s[:got_c]
+    assert np.all(got_i[got_c:] == -1)
+    np.testing.assert_allclose(gs, all_s[gi], rtol=DENSE_RTOL, atol=1e-6)
+    if np.array_equal(gi, exp_i):
+        return
+    # every disagreement must be explained by a near-tie in the oracle's own scores
+    for pos in np.nonzero(gi != exp_i)[0]:
+        assert abs(float(all_s[gi[pos]]) - float(exp_s[pos])) <= TIE_EPS * max(1.0, abs(float(exp_s[pos]))), \
+            f"rank {pos}: got row {gi[pos]} ({all_s[gi[pos]]}) expected {exp_i[pos]} ({exp_s[pos]})"
+    missing = set(exp_i) - set(gi)
+    kth = float(exp_s[-1])
+    for r in missing:
+        assert abs(float(all_s[r]) - kth) <= TIE_EPS * max(1.0, abs(kth))
+
+
+@pytest.mark.parametrize("dtype", ["f32", "f16", "bf16"])
+@pytest.mark.parametrize("n,d", [(37, 64), (5000, 384), (4099, 768), (2500, 1024)])
+@pytest.mark.parametrize("B", [1, 3, 8])
+def test_dense_gemv(engine, dtype, n, d, B):
+    x = synth.dense_corpus(n, d, seed=11 + n)
+    q = synth.dense_queries(x, B, seed=7)
+    xs = O.round_storage(x, dtype)
+    engine.force_dense_path("gemv")
+    engine.dense_set("t", x, dtype)
+    for k in (10, 100):
+        s, i, c = engine.dense_topk("t", q, k)
+        for b in range(B):
+            check_dense(xs, O.round_storage(q[b], dtype), k, s[b], i[b], int(c[b]))
+    engine.force_dense_path(None)
+
+
+@pytest.mark.parametrize("dtype", ["f16", "bf16"])
+@pytest.mark.parametrize("n,d", [(300, 64), (20000, 768), (9000, 1024), (70000, 128)])
+@pytest.mark.parametrize("B", [16, 128, 200])
+def test_dense_tcgen05(engine, dtype, n, d, B):
+    x = synth.dense_corpus(n, d, seed=5 + n, clustered=True)
+    q = synth.dense_queries(x, B, seed=9)
+    xs = O.round_storage(x, dtype)
+    engine.dense_set("t", x, dtype)
+    engine.force_dense_path("tcgen05")
+    assert engine.dense_path("t", B) == "tcgen05"
+    k = 100
+    s, i, c = engine.dense_topk("t", q, k)
+    engine.force_dense_path(None)
+    for b in range(0, B, max(1, B // 16)):
+        check_dense(xs, O.round_storage(q[b], dtype), k, s[b], i[b], int(c[b]))
+
+
+def test_dense_paths_agree(engine):
+    """Both scan kernels feed the same re-score: final lists must be identical."""
+    x = synth.dense_corpus(30000, 256, seed=3)
+    q = synth.dense_queries(x, 24, seed=4)
+    engine.dense_set("t", x, "bf16")
+    engine.force_dense_path("gemv")
+    s0, i0, c0 = engine.dense_topk("t", q, 50)
+    engine.force_dense_path("tcgen05")
+    s1, i1, c1 = engine.dense_topk("t", q, 50)
+    engine.force_dense_path(None)
+    assert np.array_equal(i0, i1) and np.array_equal(c0, c1) and np.array_equal(s0, s1)
+
+
+@pytest.mark.parametrize("path", ["gemv", "tcgen05"])
+def test_dense_mask_and_offset(engine, path):
+    n, d, k = 6000, 128, 100
+    x = synth.dense_corpus(n, d, seed=21)
+    B = 2 if path == "gemv" else 130
+    q = synth.dense_queries(x, B, seed=22)
+    mask = synth.random_mask(n, 0.10)
+    xs = O.round_storage(x, "f16")
+    engine.dense_set("t", x, "f16")
+    engine.mask_set(1, mask)
+    engine.set_id_offset(1_000_000)
+    engine.force_dense_path(path)
+    s, i, c = engine.dense_topk("t", q, k, mask_id=1)
+    engine.force_dense_path(None)
+    engine.set_id_offset(0)
+    for b in range(0, B, max(1, B // 8)):
+        check_dense(xs, O.round_storage(q[b], "f16"), k, s[b], i[b], int(c[b]), mask=mask, id_offset=1_000_000)
+    # a mask that keeps fewer rows than k: short list, padded with -1
+    tiny = np.zeros(n, dtype=bool)
+    tiny[[5, 77, 4000]] = True
+    engine.mask_set(2, tiny)
+    s, i, c = engine.dense_topk("t", q[:1], k, mask_id=2)
+    assert int(c[0]) == 3 and set(i[0][:3]) == {5, 77, 4000} and np.all(i[0][3:] == -1)
+
+
+def test_dense_exact_ties_broken_by_id(engine):
+    """Duplicate rows score identically: the lower id must win (north_star: ties broken by id)."""
+    x = synth.dense_corpus(512, 64, seed=1)
+    x[100:110] = x[7]
+    engine.dense_set("t", x, "f32")
+    s, i, c = engine.dense_topk("t", x[7:8], 5)
+    assert list(i[0]) == [7, 100, 101, 102, 103]
+
+
+def test_dense_rescore_union_dedup_mask(engine):
+    n, d = 3000, 768
+    x = synth.dense_corpus(n, d, seed=31)
+    q = synth.dense_queries(x, 4, seed=32)
+    engine.dense_set("t", x, "f32")
+    rng = np.random.default_rng(0)
+    cand = rng.integers(0, n, size=(4, 90)).astype(np.int64)
+    cand[:, 10:20] = cand[:, 0:10]      # duplicates (union semantics)
+    cand[:, 80:] = -1                   # empty slots
+    mask = synth.random_mask(n, 0.5)
+    engine.mask_set(3, mask)
+    for mid, m in ((0, None), (3, mask)):
+        s, i, c = engine.dense_rescore("t", q, cand, 40, mask_id=mid)
+        for b in range(4):
+            es, ei = O.dense_topk(x, q[b], 40, mask=m, cand=cand[b][cand[b] >= 0])
+            assert int(c[b]) == len(ei)
+            assert np.array_equal(i[b][:len(ei)], ei)
+            np.testing.assert_allclose(s[b][:len(ei)], es, rtol=1e-6)
+
+
+# ----------------------------------------------------------------------------- sparse
+def _oracle_csr(ptr, doc, w, n_docs):
+    return O.CSR(ptr, doc, w, n_docs)
+
+
+@pytest.mark.parametrize("n_docs,V,L", [(300, 500, 20), (5000, 2000, 60), (20000, 5000, 120)])
+@pytest.mark.parametrize("regime", ["zipf", "doc"])
+def test_sparse_topk_bit_exact(engine, n_docs, V, L, regime):
+    ptr, doc, w, _ = synth.zipf_corpus(n_docs, V, L, seed=n_docs)
+    csr = _oracle_csr(ptr, doc, w, n_docs)
+    B = 33
+    q_ptr, q_terms, q_vals = synth.sparse_queries(ptr, doc, n_docs, B, 8, regime, seed=2, skip_top=8)
+    engine.sparse_set_csr("s", ptr, doc, w, n_docs)
+    for k in (10, 100):
+        s, i, c = engine.sparse_topk("s", q_ptr, q_terms, q_vals, k)
+        for b in range(B):
+            t, v = q_terms[q_ptr[b]:q_ptr[b + 1]], q_vals[q_ptr[b]:q_ptr[b + 1]]
+            es, ei = O.sparse_topk(csr, t, v, k)
+            assert int(c[b]) == len(ei)
+            assert np.array_equal(i[b][:len(ei)], ei), f"query {b}"
+            assert np.array_equal(s[b][:len(ei)].view(np.uint32), es.view(np.uint32)), "scores must be bit-exact"
+            assert np.all(i[b][len(ei):] == -1)
+
+
+def test_sparse_overlap_only_and_batch1(engine):
+    """Docs sharing no term are not candidates: rare terms give short lists."""
+    ptr, doc, w, _ = synth.zipf_corpus(4000, 3000, 40, seed=8)
+    csr = _oracle_csr(ptr, doc, w, 4000)
+    df = np.diff(ptr)
+    rare = np.nonzero((df > 0) & (df < 4))[0][:3].astype(np.int32)
+    engine.sparse_set_csr("s", ptr, doc, w, 4000)
+    q_ptr = np.array([0, len(rare)], np.int32)
+    vals = np.array([0.5, 1.25, 2.0][:len(rare)], np.float64)
+    s, i, c = engine.sparse_topk("s", q_ptr, rare, vals, 100)
+    es, ei = O.sparse_topk(csr, rare, vals, 100)
+    assert 0 < len(ei) < 100 and int(c[0]) == len(ei)
+    assert np.array_equal(i[0][:len(ei)], ei)
+    # empty query and out-of-vocabulary term: no candidates at all
+    s, i, c = engine.sparse_topk("s", np.array([0, 0, 1], np.int32), np.array([3000 + 5], np.int32), np.array([1.0]), 10)
+    assert list(c) == [0, 0] and np.all(i == -1)
+
+
+def test_sparse_idf_and_mask(engine):
+    n_docs = 6000
+    ptr, doc, w, _ = synth.zipf_corpus(n_docs, 1500, 50, seed=5)
+    csr = _oracle_csr(ptr, doc, w, n_docs)
+    engine.sparse_set_csr("s", ptr, doc, w, n_docs)
+    df = engine.sparse_df("s", 1500)
+    assert np.array_equal(df, np.diff(ptr))
+    q_ptr, q_terms, q_vals = synth.sparse_queries(ptr, doc, n_docs, 9, 6, "doc", seed=3)
+    mask = synth.random_mask(n_docs, 0.10)
+    engine.mask_set(4, mask)
+    vals_idf = np.concatenate([O.apply_idf(csr, q_terms[q_ptr[b]:q_ptr[b + 1]], q_vals[q_ptr[b]:q_ptr[b + 1]])
+                               for b in range(9)])
+    s, i, c = engine.sparse_topk("s", q_ptr, q_terms, vals_idf, 50, mask_id=4)
+    for b in range(9):
+        t = q_terms[q_ptr[b]:q_ptr[b + 1]]
+        es, ei = O.sparse_topk(csr, t, vals_idf[q_ptr[b]:q_ptr[b + 1]], 50, mask=mask)
+        assert int(c[b]) == len(ei) and np.array_equal(i[b][:len(ei)], ei)
+        assert np.array_equal(s[b][:len(ei)].view(np.uint32), es.view(np.uint32))
+
+
+def test_sparse_many_terms_per_query(engine):
+    """More than one 16-term group per query (document-sized queries)."""
+    n_docs = 3000
+    ptr, doc, w, _ = synth.zipf_corpus(n_docs, 800, 80, seed=6)
+    csr = _oracle_csr(ptr, doc, w, n_docs)
+    engine.sparse_set_csr("s", ptr, doc, w, n_docs)
+    rng = np.random.default_rng(1)
+    terms = np.sort(rng.choice(800, 45, replace=False)).astype(np.int32)
+    vals = rng.random(45) * 2 - 0.5     # includes negative weights
+    s, i, c = engine.sparse_topk("s", np.array([0, 45], np.int32), terms, vals, 64)
+    es, ei = O.sparse_topk(csr, terms, vals, 64)
+    assert np.array_equal(i[0][:len(ei)], ei)
+    assert np.array_equal(s[0][:len(ei)].view(np.uint32), es.view(np.uint32))
+
+
+# ----------------------------------------------------------------------------- fusion / merge
+@pytest.mark.parametrize("tie", ["id", "first_seen"])
+def test_rrf_ranks_exact(engine, tie):
+    rng = np.random.default_rng(5)
+    L, B, kmax = 3, 17, 60
+    ids = np.full((L, B, kmax), -1, np.int64)
+    counts = np.zeros((L, B), np.int32)
+    for l in range(L):
+        for b in range(B):
+            c = int(rng.integers(0, kmax + 1))
+            counts[l, b] = c
+            ids[l, b, :c] = rng.choice(150, size=c, replace=False)
+    for limit in (10, 100):
+        s, i, c = engine.rrf(ids, counts, limit, tie=0 if tie == "id" else 1)
+        for b in range(B):
+            es, ei = O.rrf([ids[l, b, :counts[l, b]] for l in range(L)], limit=limit, tie=tie)
+            assert int(c[b]) == len(ei)
+            assert np.array_equal(i[b][:len(ei)], ei)
+            assert np.array_equal(s[b][:len(ei)], es), "float64 RRF scores must be bit-exact"
+
+
+def test_merge_topk_matches_global_sort(engine):
+    rng = np.random.default_rng(9)
+    G, B, k = 8, 5, 100
+    scores = np.full((G, B, k), -np.inf, np.float32)
+    ids = np.full((G, B, k), -1, np.int64)
+    counts = np.zeros((G, B), np.int32)
+    for g in range(G):
+        for b in range(B):
+            c = int(rng.integers(0, k + 1))
+            sc = np.sort(rng.integers(0, 50, c).astype(np.float32))[::-1]   # many ties
+            counts[g, b] = c
+            scores[g, b, :c] = sc
+            ids[g, b, :c] = g * 1000 + np.arange(c)
+    s, i, c = engine.merge_topk(scores, ids, counts)
+    for b in range(B):
+        fs = np.concatenate([scores[g, b, :counts[g, b]] for g in range(G)])
+        fi = np.concatenate([ids[g, b, :counts[g, b]] for g in range(G)])
+        o = O.topk_order(fs, fi, k)
+        assert int(c[b]) == len(o)
+        assert np.array_equal(i[b][:len(o)], fi[o]) and np.array_equal(s[b][:len(o)], fs[o])
+
+
+def test_hybrid_three_stage(engine):
+    """north_star path in one call == oracle dense top-k + sparse top-k + RRF."""
+    n, d, k, B = 8000, 384, 100, 12
+    x = synth.dense_corpus(n, d, seed=41, clustered=True)
+    q = synth.dense_queries(x, B, seed=42)
+    ptr, doc, w, _ = synth.zipf_corpus(n, 3000, 80, seed=43)
+    q_ptr, q_terms, q_vals = synth.sparse_queries(ptr, doc, n, B, 8, "zipf", seed=44, skip_top=8)
+    col = O.OracleCollection()
+    col.add_dense("dense", x, "dot", "bf16")
+    col.add_sparse("sparse", O.CSR(ptr, doc, w, n))
+    engine.dense_set("dense", x, "bf16")
+    engine.sparse_set_csr("sparse", ptr, doc, w, n)
+    mask = synth.random_mask(n, 0.3)
+    engine.mask_set(5, mask)
+    for mid, m in ((0, None), (5, mask)):
+        s, i, c = engine.hybrid_topk("dense", "sparse", q, q_ptr, q_terms, q_vals, k, mask_id=mid)
+        for b in range(B):
+            es, ei = O.hybrid_simple(col, q[b], q_terms[q_ptr[b]:q_ptr[b + 1]], q_vals[q_ptr[b]:q_ptr[b + 1]], k, mask=m)
+            assert int(c[b]) == len(ei)
+            assert np.array_equal(i[b][:len(ei)], ei), f"query {b} mask {mid}"
+            assert np.array_equal(s[b][:len(ei)], es)
