@@ -1,0 +1,317 @@
+#!/usr/bin/env python
+"""Headline benchmark: hybrid (dense + BM25 + RRF) top-100 QPS at 10M x 1024 bf16, batch 1024
+(BASELINE.json metric / configs[3]), row-sharded over --gpus B200s of one box.
+
+One "step" = one batch of B synthetic hybrid queries through the whole hot path.
+  value : QPS with the query batch already resident in HBM (device-pointer C-ABI calls)
+  e2e   : QPS through the host-buffer C-ABI call (H2D of the batch + D2H of the results inside)
+  --impl reference : the CPU restatement (oracle/fast_cpu.py) timed on the host cores.
+Prints ONE JSON line on rank 0."""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "hybrid top-100 QPS @10Mx1024 batch 1024"
+UNIT = "queries/s"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--n", type=int, default=10_000_000, help="corpus rows / documents (whole job)")
+    ap.add_argument("--d", type=int, default=1024)
+    ap.add_argument("--batch", type=int, default=1024)
+    ap.add_argument("--k", type=int, default=100)
+    ap.add_argument("--dtype", default="bf16", choices=["bf16", "f16"])
+    ap.add_argument("--vocab", type=int, default=50_000)
+    ap.add_argument("--doc-len", type=int, default=285)
+    ap.add_argument("--q-terms", type=int, default=8)
+    ap.add_argument("--cpu-sample-rows", type=int, default=262_144)
+    ap.add_argument("--cpu-sample-queries", type=int, default=256)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            j = json.load(f)
+        return {"tflops": j.get("bf16_tflops_sustained", 1400.0), "tflops_burst": j.get("bf16_tflops"),
+                "hbm_gbs": j.get("hbm_gbs", 6650.0), "source": "measured"}
+    return {"tflops": 1400.0, "tflops_burst": 1590.0, "hbm_gbs": 6650.0, "source": "fallback"}
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled during the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+        sm = [float(r[0]) for r in self.rows if len(r) >= 6 and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) >= 6 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for j, n in enumerate(names) if any(len(r) >= 6 and r[2 + j] == "Active" for r in self.rows)]
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------ reference arm
+def run_reference(args, rank, world):
+    """CPU restatement timed on the host cores: a bounded sample (rows and queries) of the same
+    workload, scaled linearly in corpus size to the full config."""
+    if rank != 0:
+        return
+    import torch
+    from oracle import fast_cpu
+    from rag_application_b200 import synth
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    ns, bs = min(args.cpu_sample_rows, args.n), args.cpu_sample_queries
+    x = synth.dense_corpus_torch(ns, args.d, torch.bfloat16, "cpu")
+    q = synth.dense_queries_torch(x, bs).to(torch.bfloat16).float().numpy()
+    xs = x.float().numpy()
+    tp, doc, w = synth.zipf_corpus_torch(ns, args.vocab, args.doc_len, "cpu", block_docs=1 << 16)
+    qp, qt, qv = synth.sparse_queries_torch(tp, bs, args.q_terms)
+    tp, doc, w = tp.numpy(), doc.numpy().astype(np.uint32), w.numpy()
+    qp, qt, qv = qp.numpy(), qt.numpy(), qv.numpy()
+
+    def step():
+        fast_cpu.hybrid_batch(xs, q, tp, doc, w, ns, qp, qt, qv, args.k, threads=cores)
+
+    for _ in range(args.warmup):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step()
+    dt = time.perf_counter() - t0
+    scale = ns / args.n
+    val = bs * args.steps / dt * scale
+    sample = (f"{bs} queries x {ns} rows/docs per step (1/{args.n // ns if ns else 1} of the corpus); "
+              f"QPS scaled by rows ratio {scale:.5f} (cost linear in N)")
+    line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": config_dict(args, args.gpus),
+            "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+            "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+def config_dict(args, world):
+    return {"workload": f"C4 hybrid dense+BM25+RRF top-{args.k}: {args.n} chunks x {args.d}-d {args.dtype}, "
+                        f"V={args.vocab} Zipf(1.0) L={args.doc_len}, {args.q_terms}-term queries, batch {args.batch}",
+            "n": args.n, "d": args.d, "batch": args.batch, "k": args.k, "shards": world,
+            "l2": "inputs larger than L2 (corpus shard >> 126 MB)", "parallelism": f"row-shard x{world}"}
+
+
+# ------------------------------------------------------------------------------------ our arm
+def main():
+    args = parse()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+        return
+
+    import torch
+    import torch.distributed as dist
+    from rag_application_b200 import Engine, synth
+    from rag_application_b200.sharded import ShardedHybrid, shard_bounds
+
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    peaks = load_peaks()
+    tdt = torch.bfloat16 if args.dtype == "bf16" else torch.float16
+    lo, hi = shard_bounds(args.n, world, rank)
+    n_loc = hi - lo
+
+    # ---- corpus shard, built in HBM
+    eng = Engine(local)
+    x = synth.dense_corpus_torch(n_loc, args.d, tdt, dev, seed=synth.SEED_CORPUS + rank)
+    q_dev = synth.dense_queries_torch(x, args.batch)
+    if world > 1:
+        dist.broadcast(q_dev, 0)
+    cpu_x = x[: min(args.cpu_sample_rows, n_loc)].float().cpu().numpy() if rank == 0 else None
+    eng.dense_set("dense", x)
+    del x
+    torch.cuda.empty_cache()
+    tp, doc, w = synth.zipf_corpus_torch(n_loc, args.vocab, args.doc_len, dev, seed=synth.SEED_CORPUS + rank)
+    df = (tp[1:] - tp[:-1]).clone()
+    if world > 1:
+        dist.all_reduce(df)
+    gptr = torch.zeros_like(tp)
+    gptr[1:] = torch.cumsum(df, 0)
+    qp, qt, qv = synth.sparse_queries_torch(gptr, args.batch, args.q_terms)
+    eng.sparse_set_csr("sparse", tp, doc, w, n_loc)
+    # algorithmic BM25 bytes of this batch on this shard: sum_t df_t * 8 B
+    ldf = (tp[1:] - tp[:-1])
+    bm25_bytes = float(ldf[qt.to(dev).long()].sum().item()) * 8.0
+    cpu_csr = None
+    if rank == 0 and not args.no_cpu_baseline and world == 1:
+        ns = min(args.cpu_sample_rows, n_loc)
+        keep = doc < ns
+        term_of = torch.repeat_interleave(torch.arange(args.vocab, device=dev), ldf)
+        sp = torch.zeros(args.vocab + 1, dtype=torch.int64, device=dev)
+        sp[1:] = torch.cumsum(torch.bincount(term_of[keep], minlength=args.vocab), 0)
+        cpu_csr = (sp.cpu().numpy(), doc[keep].cpu().numpy().astype(np.uint32), w[keep].cpu().numpy(), ns)
+        del term_of, keep
+    del tp, doc, w
+    torch.cuda.empty_cache()
+
+    sh = ShardedHybrid(eng, rank, world, lo)
+    qp_d, qt_d, qv_d = qp.to(dev), qt.to(dev), qv.to(dev)
+    k = args.k
+
+    def step_dev():
+        if world == 1:
+            return eng.hybrid_topk("dense", "sparse", q_dev, qp_d, qt_d, qv_d, k)
+        return sh.hybrid_topk("dense", "sparse", q_dev, qp_d, qt_d, qv_d, k)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            out = fn()
+        e1.record()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item()), out
+
+    eng.profile_enable(True)
+    for _ in range(args.warmup):
+        step_dev()
+    barrier()
+    eng.profile_reset()
+    clocks = ClockSampler(local)
+    if rank == 0:
+        clocks.start()
+    ms_total, _ = timed(step_dev, args.steps)
+    stage_ms, stage_calls, launches = eng.profile_read()
+    clk = clocks.stop() if rank == 0 else None
+    ms_step = ms_total / args.steps
+    value = args.batch / (ms_step * 1e-3)
+
+    # ---- end to end: host buffers through the public call, copies inside the timed region
+    e2e = None
+    if not args.no_e2e:
+        q_host = torch.empty((args.batch, args.d), dtype=torch.float32).pin_memory()
+        q_host.copy_(q_dev)
+        qp_h, qt_h, qv_h = qp.pin_memory(), qt.pin_memory(), qv.pin_memory()
+        h2d = q_host.numel() * 4 + qp_h.numel() * 4 + qt_h.numel() * 4 + qv_h.numel() * 8
+        d2h = args.batch * k * (8 + 8) + args.batch * 4
+        if world == 1:
+            qn, qpn, qtn, qvn = q_host.numpy(), qp_h.numpy(), qt_h.numpy(), qv_h.numpy()
+
+            def step_host():
+                return eng.hybrid_topk("dense", "sparse", qn, qpn, qtn, qvn, k)
+        else:
+            def step_host():
+                s, i, c = sh.hybrid_topk("dense", "sparse", q_host.to(dev, non_blocking=True),
+                                         qp_h.to(dev, non_blocking=True), qt_h.to(dev, non_blocking=True),
+                                         qv_h.to(dev, non_blocking=True), k)
+                return s.cpu(), i.cpu(), c.cpu()
+        for _ in range(max(1, args.warmup)):
+            step_host()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            step_host()
+        barrier()
+        dt = torch.tensor([time.perf_counter() - t0], device=dev)
+        if world > 1:
+            dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+        e2e = {"value": args.batch * args.steps / float(dt.item()), "unit": UNIT, "h2d_bytes_per_step": int(h2d),
+               "d2h_bytes_per_step": int(d2h)}
+
+    # ---- CPU baseline (rank 0, N=1): bounded sample of the same workload on the host cores
+    cpu = None
+    if rank == 0 and cpu_csr is not None:
+        from oracle import fast_cpu
+        cores = os.cpu_count() or 1
+        torch.set_num_threads(cores)
+        bs = min(args.cpu_sample_queries, args.batch)
+        sp, sdoc, sw, ns = cpu_csr
+        qs = q_dev[:bs].to(tdt).float().cpu().numpy()
+        qpn, qtn, qvn = qp[: bs + 1].numpy(), qt[: int(qp[bs])].numpy(), qv[: int(qp[bs])].numpy()
+        fast_cpu.hybrid_batch(cpu_x[:ns], qs[:8], sp, sdoc, sw, ns, qpn[:9], qtn, qvn, k, threads=cores)  # warm
+        t0 = time.perf_counter()
+        fast_cpu.hybrid_batch(cpu_x[:ns], qs, sp, sdoc, sw, ns, qpn, qtn, qvn, k, threads=cores)
+        dt = time.perf_counter() - t0
+        cpu = {"value": bs / dt * (ns / args.n), "unit": UNIT, "cores": cores, "kind": "port",
+               "sample": f"{bs} queries x {ns} rows/docs ({dt:.1f} s CPU wall), QPS scaled by {ns}/{args.n} (cost linear in N)"}
+
+    if rank == 0:
+        dense_ms = stage_ms["dense_scan"] / max(1, stage_calls["dense_scan"])
+        flops = 2.0 * n_loc * args.d * args.batch
+        ach = flops / (dense_ms * 1e-3) / 1e12 if dense_ms > 0 else 0.0
+        bm_ms = stage_ms["sparse_scan"] / max(1, stage_calls["sparse_scan"])
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": args.dtype, "data": "synthetic", "config": config_dict(args, world),
+            "e2e": e2e, "gpu_launches": int(launches), "clocks": clk,
+            "roofline": {"kernel": "dense_umma_kernel (tcgen05 scan + fused top-k)", "bound": "tensor", "achieved": ach,
+                         "peak": peaks["tflops"], "unit": "TFLOP/s", "frac": ach / peaks["tflops"],
+                         "peak_kind": f"{peaks['source']} sustained cuBLAS bf16", "traffic": None,
+                         "flops_per_launch": flops, "avg_launch_ms": dense_ms},
+            "cpu_baseline": cpu,
+            "stages_ms_per_step": {s: stage_ms[s] / args.steps for s in stage_ms},
+            "bm25": {"algorithmic_bytes_per_step": bm25_bytes, "ms": bm_ms,
+                     "achieved_gbs": bm25_bytes / (bm_ms * 1e-3) / 1e9 if bm_ms > 0 else None,
+                     "peak_gbs": peaks["hbm_gbs"]},
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    eng.close()
+
+
+if __name__ == "__main__":
+    main()

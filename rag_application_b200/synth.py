@@ -145,7 +145,8 @@ def zipf_corpus_torch(n_docs: int, V: int, L: int, device, seed: int = SEED_CORP
         term = uk // n_docs
         doc = (uk - term * n_docs).to(torch.int32)
         cnt = torch.bincount(term, minlength=V)
-        blocks.append((term, doc, tf))
+        blocks.append((term.to(torch.int32), doc, tf.to(torch.int16)))
+        del uk, term, tf
         counts.append(cnt)
     counts = torch.stack(counts)                        # [nb, V]
     total = counts.sum(0)
@@ -158,12 +159,14 @@ def zipf_corpus_torch(n_docs: int, V: int, L: int, device, seed: int = SEED_CORP
     wt = torch.from_numpy(bm25_weight_table(L, max_tf)).to(device)
     base = term_ptr[:-1].clone()
     for (term, doc, tf), cnt in zip(blocks, counts):
+        term = term.long()
         start = torch.cumsum(cnt, 0) - cnt                    # first index of each term inside the block
         pos = torch.arange(term.numel(), device=device) - start[term]
         dest = base[term] + pos
         doc_out[dest] = doc
-        w_out[dest] = wt[tf]
+        w_out[dest] = wt[tf.long()]
         base += cnt
+        del term, pos, dest
     return term_ptr, doc_out, w_out
 
 
