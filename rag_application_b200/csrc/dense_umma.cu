@@ -59,16 +59,21 @@ __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
     const uint32_t addr = smem_u32(bar);
     uint32_t done = 0;
-    // bounded wait (~2 s of SM clocks): a protocol bug becomes a trap (error return), not a hung GPU
-    const long long t0 = clock64();
-    while (true) {
+    // try_wait suspends the thread in hardware (hint: up to ~1 us) instead of burning issue slots;
+    // the wait is bounded (~2 s of SM clocks) so a protocol bug becomes a trap, not a hung GPU
+    long long t0 = 0;
+    for (uint32_t spin = 0;; ++spin) {
         asm volatile(
             "{\n\t.reg .pred p;\n\t"
-            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
             "selp.u32 %0, 1, 0, p;\n\t}"
-            : "=r"(done) : "r"(addr), "r"(parity) : "memory");
+            : "=r"(done) : "r"(addr), "r"(parity), "r"(1000u) : "memory");
         if (done) return;
-        if (clock64() - t0 > 4000000000ll) __trap();
+        if ((spin & 255u) == 255u) {
+            const long long now = clock64();
+            if (t0 == 0) t0 = now;
+            else if (now - t0 > 4000000000ll) __trap();
+        }
     }
 }
 __device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* tmap, int c0, int c1, uint64_t* bar) {
@@ -88,7 +93,7 @@ __device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint64_t adesc, uint64
         "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
         ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc) : "memory");
 }
-__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
+__device__ __forceinline__ void tmem_ld32_issue(uint32_t taddr, uint32_t (&v)[32]) {
     asm volatile(
         "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
         "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
@@ -98,7 +103,16 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
           "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
           "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
         : "r"(taddr));
-    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+// wait for every outstanding tcgen05.ld of this thread; the "+r" operands tie the loaded registers
+// to the wait so no use of them can be scheduled ahead of it
+__device__ __forceinline__ void tmem_ld_wait(uint32_t (&v)[32]) {
+    asm volatile("tcgen05.wait::ld.sync.aligned;"
+        : "+r"(v[0]), "+r"(v[1]), "+r"(v[2]), "+r"(v[3]), "+r"(v[4]), "+r"(v[5]), "+r"(v[6]), "+r"(v[7]),
+          "+r"(v[8]), "+r"(v[9]), "+r"(v[10]), "+r"(v[11]), "+r"(v[12]), "+r"(v[13]), "+r"(v[14]), "+r"(v[15]),
+          "+r"(v[16]), "+r"(v[17]), "+r"(v[18]), "+r"(v[19]), "+r"(v[20]), "+r"(v[21]), "+r"(v[22]), "+r"(v[23]),
+          "+r"(v[24]), "+r"(v[25]), "+r"(v[26]), "+r"(v[27]), "+r"(v[28]), "+r"(v[29]), "+r"(v[30]), "+r"(v[31])
+        :: "memory");
 }
 
 // K-major, 128-byte swizzle: 8-row groups are 1024 B apart (SBO); LBO unused; version 1; layout 2.
@@ -142,9 +156,11 @@ __device__ __forceinline__ void um_compact(unsigned bal, uint64_t* my_list, uint
 __global__ void __launch_bounds__(UM_THREADS, 1)
 dense_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_x,
                   int64_t n, int d, int B, int n_qblocks, int64_t rows_per_chunk, const uint32_t* __restrict__ mask,
-                  int k_sel, uint32_t idesc, uint64_t* __restrict__ part, uint64_t* __restrict__ scratch) {
-    extern __shared__ uint8_t smem_raw[];
-    UmSmem& S = *reinterpret_cast<UmSmem*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+                  int k_sel, uint32_t idesc, uint64_t* __restrict__ part, uint64_t* __restrict__ scratch,
+                  uint32_t* __restrict__ gthr) {
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    UmSmem& S = *reinterpret_cast<UmSmem*>(smem_raw);   // keeps the shared address space (LDS/STS in the sort)
+    if ((smem_u32(smem_raw) & 1023u) != 0u) __trap();   // 128B-swizzle atoms need 1024-byte alignment
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int qblock = blockIdx.x % n_qblocks;
     const int chunk = blockIdx.x / n_qblocks;
@@ -219,31 +235,50 @@ dense_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
         const bool q_valid = b < B;
         uint64_t* my_list = scratch + ((size_t)blockIdx.x * UM_BM + qidx) * UM_CAP;
         uint64_t* sbuf = S.sortbuf[warp - 2];
-        float thr = q_valid ? -INFINITY : INFINITY;
+        float thr = q_valid ? -INFINITY : INFINITY;   // local k-th best (strict: later rows have larger ids)
         int cnt = 0;
+        const uint32_t lane_taddr = tmem_base + ((uint32_t)(quarter * 32) << 16);
+        auto process = [&](uint32_t (&v)[32], int64_t rbase, float eff) {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) {
+                const float s = __uint_as_float(v[i]);
+                if (s > eff) {
+                    const int64_t row = rbase + i;
+                    if (row < row_end && mask_test(mask, (uint32_t)row)) {
+                        __stcg(my_list + cnt, make_key(s, (uint32_t)row));
+                        ++cnt;
+                    }
+                }
+            }
+        };
         for (int t = 0; t < n_tiles; ++t) {
             const int as = t & 1;
             const uint32_t aphase = (uint32_t)(t >> 1) & 1;
             const int64_t row0 = row_begin + (int64_t)t * UM_BN;
+            // bound published by the CTAs scanning other chunks for the same query (non-strict: their
+            // rows may have smaller ids) -- fetched while we wait for the accumulator
+            const uint32_t g = q_valid ? __ldcg(gthr + b) : 0u;
             mbar_wait(&S.tfull[as], aphase);
             tc_fence_after();
+            float eff = thr;
+            if (g != 0u) eff = fmaxf(eff, nextafterf(ordered_f32(g), -INFINITY));
+            const uint32_t taddr = lane_taddr + (uint32_t)(as * UM_BN);
+            uint32_t va[32], vb[32];
+            tmem_ld32_issue(taddr, va);
 #pragma unroll 1
-            for (int g = 0; g < UM_BN / 32; ++g) {
-                const unsigned bal = __ballot_sync(0xFFFFFFFFu, cnt > UM_CAP - 32);
-                if (bal) um_compact(bal, my_list, my_list, cnt, thr, sbuf, k_sel, lane);
-                uint32_t v[32];
-                tmem_ld32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(as * UM_BN + g * 32), v);
-#pragma unroll
-                for (int i = 0; i < 32; ++i) {
-                    const float s = __uint_as_float(v[i]);
-                    if (s > thr) {
-                        const int64_t row = row0 + g * 32 + i;
-                        if (row < row_end && mask_test(mask, (uint32_t)row)) {
-                            __stcg(my_list + cnt, make_key(s, (uint32_t)row));
-                            ++cnt;
-                        }
-                    }
+            for (int g2 = 0; g2 < UM_BN / 64; ++g2) {
+                unsigned bal = __ballot_sync(0xFFFFFFFFu, cnt > UM_CAP - 64);
+                if (bal) {
+                    const float before = thr;
+                    um_compact(bal, my_list, my_list, cnt, thr, sbuf, k_sel, lane);
+                    if (thr > before) { atomicMax(gthr + b, f32_ordered(thr)); eff = fmaxf(eff, thr); }
                 }
+                tmem_ld_wait(va);
+                tmem_ld32_issue(taddr + (uint32_t)(g2 * 64 + 32), vb);
+                process(va, row0 + g2 * 64, eff);
+                tmem_ld_wait(vb);
+                if (g2 + 1 < UM_BN / 64) tmem_ld32_issue(taddr + (uint32_t)(g2 * 64 + 64), va);
+                process(vb, row0 + g2 * 64 + 32, eff);
             }
             tc_fence_before();
             __syncwarp();
@@ -276,7 +311,8 @@ cudaError_t dense_umma_plan(int64_t n, int d, int B, int k_sel, int num_sms, Umm
     int64_t chunks = std::max<int64_t>(1, num_sms / plan->n_qblocks);
     if (chunks > n_tiles) chunks = n_tiles;
     plan->n_chunks = (int)chunks;
-    plan->scratch_bytes = (size_t)plan->n_chunks * plan->n_qblocks * UM_BM * UM_CAP * sizeof(uint64_t);
+    plan->list_bytes = (size_t)plan->n_chunks * plan->n_qblocks * UM_BM * UM_CAP * sizeof(uint64_t);
+    plan->scratch_bytes = plan->list_bytes + (size_t)plan->n_qblocks * UM_BM * sizeof(uint32_t);
     return cudaSuccess;
 }
 
@@ -319,7 +355,7 @@ cudaError_t dense_umma_scan(const void* X16, int dtype, int64_t n, int d, const 
                             void* tmap_x, void* tmap_q, cudaStream_t st) {
     (void)X16; (void)Q16;
     static bool attr_set = false;
-    const size_t smem = sizeof(UmSmem) + 1024;
+    const size_t smem = sizeof(UmSmem);
     if (!attr_set) {
         cudaError_t e = cudaFuncSetAttribute(dense_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
@@ -333,8 +369,11 @@ cudaError_t dense_umma_scan(const void* X16, int dtype, int64_t n, int d, const 
     const uint32_t fmt = (dtype == 2) ? 1u : 0u;  // BF16 : F16
     const uint32_t idesc = (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(UM_BN >> 3) << 17) | ((uint32_t)(UM_BM >> 4) << 24);
     const int grid = plan.n_chunks * plan.n_qblocks;
+    uint32_t* gthr = reinterpret_cast<uint32_t*>(reinterpret_cast<uint8_t*>(scratch) + plan.list_bytes);
+    cudaError_t me = cudaMemsetAsync(gthr, 0, (size_t)plan.n_qblocks * UM_BM * sizeof(uint32_t), st);
+    if (me != cudaSuccess) return me;
     dense_umma_kernel<<<grid, UM_THREADS, smem, st>>>(tq, tx, n, d, B, plan.n_qblocks, rows_per_chunk, mask, k_sel,
-                                                      idesc, part, reinterpret_cast<uint64_t*>(scratch));
+                                                      idesc, part, reinterpret_cast<uint64_t*>(scratch), gthr);
     return cudaGetLastError();
 }
 

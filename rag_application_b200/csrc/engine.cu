@@ -96,7 +96,7 @@ struct brag_engine {
     std::map<std::string, SparseSpace> sparse;
     std::map<int, MaskBuf> masks;
     // scratch (grow-only)
-    DevBuf qs, q16, part, tmp_a, tmp_b, keys1, keys2, umma_scratch, work_counter;
+    DevBuf qs, q16, part, tmp_a, tmp_b, keys1, keys2, umma_scratch, work_counter, g_thr;
     DevBuf h_in[6], h_out[4];      // staging for host-pointer calls
     DevBuf hyb_ids, hyb_counts, hyb_scores;
     alignas(64) unsigned char tmap_q[128];
@@ -250,10 +250,11 @@ void sparse_topk_dev(brag_engine* e, SparseSpace& s, const int32_t* q_ptr, const
     uint64_t* part = e->part.as<uint64_t>((size_t)P * B * k);
     uint64_t* merged = e->keys1.as<uint64_t>((size_t)B * k);
     int* wc = e->work_counter.as<int>(1);
+    unsigned long long* gthr = e->g_thr.as<unsigned long long>(B);
     {
         StageTimer t(e, 2, st);
         CK(brag::bm25_scan(s.term_ptr, s.doc, s.w, s.sub_off, s.V, s.n_docs, q_ptr, q_terms, q_vals, B, mask, k,
-                           part, plan, wc, st));
+                           part, plan, wc, gthr, st));
         e->kernel_launches += 1;
     }
     {
@@ -330,7 +331,7 @@ int brag_destroy(brag_engine* e) {
         for (auto& kv : e->sparse) free_sparse(kv.second);
         for (auto& kv : e->masks) if (kv.second.bits) cudaFree(kv.second.bits);
         DevBuf* bufs[] = {&e->qs, &e->q16, &e->part, &e->tmp_a, &e->tmp_b, &e->keys1, &e->keys2, &e->umma_scratch,
-                          &e->work_counter, &e->hyb_ids, &e->hyb_counts, &e->hyb_scores};
+                          &e->work_counter, &e->g_thr, &e->hyb_ids, &e->hyb_counts, &e->hyb_scores};
         for (DevBuf* b : bufs) b->release();
         for (auto& b : e->h_in) b.release();
         for (auto& b : e->h_out) b.release();

@@ -14,7 +14,8 @@ cudaError_t dense_gemv_scan(const void* X, int dtype, int64_t n, int d, const fl
 struct UmmaPlan {
     int n_chunks;      // corpus chunks (partial lists per query) = CTAs per query block
     int n_qblocks;     // ceil(B / 128)
-    size_t scratch_bytes;  // per-(CTA, query) candidate lists in global memory
+    size_t list_bytes;     // per-(CTA, query) candidate lists in global memory
+    size_t scratch_bytes;  // lists + shared per-query thresholds
 };
 bool dense_umma_supported(int dtype, int d, int64_t n);
 cudaError_t dense_umma_plan(int64_t n, int d, int B, int k_sel, int num_sms, UmmaPlan* plan);
@@ -61,6 +62,6 @@ Bm25Plan bm25_plan(int64_t n_docs, int B, int num_sms);
 cudaError_t bm25_scan(const int64_t* term_ptr, const uint32_t* doc, const float* w, const uint32_t* sub_off,
                       int64_t V, int64_t n_docs, const int32_t* q_ptr, const int32_t* q_terms,
                       const double* q_vals, int B, const uint32_t* mask, int k_sel, uint64_t* part,
-                      const Bm25Plan& plan, int* work_counter, cudaStream_t st);
+                      const Bm25Plan& plan, int* work_counter, unsigned long long* g_thr, cudaStream_t st);
 
 }  // namespace brag
