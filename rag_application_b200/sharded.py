@@ -62,9 +62,11 @@ class ShardedHybrid:
         import torch.distributed as dist
         if self.world == 1:
             return payload[None]
-        out = torch.empty((self.world,) + tuple(payload.shape), dtype=payload.dtype, device=payload.device)
-        dist.all_gather_into_tensor(out, payload, group=self.group)
-        return out
+        # flat buffers: NCCL accepts any [world, ...] view, gloo insists on a concatenated dim 0
+        flat = payload.reshape(-1)
+        out = torch.empty((self.world * flat.numel(),), dtype=payload.dtype, device=payload.device)
+        dist.all_gather_into_tensor(out, flat, group=self.group)
+        return out.view((self.world,) + tuple(payload.shape))
 
     def hybrid_topk(self, dense_name, sparse_name, Q, q_ptr, q_terms, q_vals, k, mask_id=0):
         """Device tensors in, device tensors out: (rrf scores f64 [B,k], ids [B,k], counts [B]),

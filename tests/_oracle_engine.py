@@ -1,0 +1,135 @@
+"""TEST-ONLY stand-in for rag_application_b200.Engine backed by the CPU oracle, so the host-side
+logic above the C ABI (sharded exchange, Qdrant-shaped client, plan executor) can be exercised on
+a machine without a GPU.  Same method contract as Engine: numpy in -> numpy out, torch CPU
+tensors in -> torch CPU tensors out; lists padded with id -1 / score -inf, true length in counts.
+Never imported by the product."""
+from __future__ import annotations
+
+import numpy as np
+
+from oracle import oracle as O
+
+
+def _np(a):
+    return a.numpy() if hasattr(a, "numpy") and not isinstance(a, np.ndarray) else np.asarray(a)
+
+
+class OracleEngine:
+    def __init__(self, device: int = 0):
+        self.dense, self.dtype, self.sparse, self.masks = {}, {}, {}, {}
+        self.id_offset = 0
+        self.calls = []
+
+    def close(self):
+        pass
+
+    def set_id_offset(self, off):
+        self.id_offset = int(off)
+
+    def dense_set(self, name, rows, dtype="f32"):
+        self.dense[name] = O.round_storage(_np(rows).astype(np.float32), dtype)
+        self.dtype[name] = dtype
+
+    def dense_drop(self, name):
+        self.dense.pop(name, None)
+
+    def sparse_set_csr(self, name, term_ptr, doc, w, n_docs):
+        self.sparse[name] = O.CSR(_np(term_ptr).astype(np.int64), _np(doc).astype(np.uint32),
+                                  _np(w).astype(np.float32), int(n_docs))
+
+    def sparse_drop(self, name):
+        self.sparse.pop(name, None)
+
+    def sparse_df(self, name, n_terms):
+        return np.diff(self.sparse[name].term_ptr)
+
+    def mask_set(self, mask_id, mask):
+        m = _np(mask)
+        if m.dtype != np.bool_:
+            m = np.unpackbits(m.astype(np.uint32).view(np.uint8), bitorder="little").astype(bool)
+        self.masks[mask_id] = m
+
+    def _mask(self, mask_id, n):
+        if not mask_id:
+            return None
+        m = self.masks[mask_id]
+        return m[:n]
+
+    def _wrap(self, like, s, i, c):
+        if hasattr(like, "numpy") and not isinstance(like, np.ndarray):
+            import torch
+            return torch.from_numpy(s), torch.from_numpy(i), torch.from_numpy(c)
+        return s, i, c
+
+    def _pad(self, lists, k, sdtype=np.float32):
+        B = len(lists)
+        s = np.full((B, k), -np.inf, sdtype)
+        i = np.full((B, k), -1, np.int64)
+        c = np.zeros((B,), np.int32)
+        for b, (ls, li) in enumerate(lists):
+            n = len(li)
+            s[b, :n], i[b, :n], c[b] = ls, li, n
+        return s, i, c
+
+    def dense_topk(self, name, Q, k, mask_id=0):
+        self.calls.append(("dense_topk", name, k))
+        x = self.dense[name]
+        q = O.round_storage(_np(Q).astype(np.float32), self.dtype[name])
+        out = []
+        for b in range(q.shape[0]):
+            s, i = O.dense_topk(x, q[b], k, mask=self._mask(mask_id, x.shape[0]))
+            out.append((s, i + self.id_offset))
+        return self._wrap(Q, *self._pad(out, k))
+
+    def dense_rescore(self, name, Q, cand, k, mask_id=0):
+        self.calls.append(("dense_rescore", name, k))
+        x = self.dense[name]
+        q = O.round_storage(_np(Q).astype(np.float32), self.dtype[name])
+        cand = _np(cand)
+        out = []
+        for b in range(q.shape[0]):
+            cb = cand[b][cand[b] >= 0] - self.id_offset
+            cb = cb[(cb >= 0) & (cb < x.shape[0])]
+            s, i = O.dense_topk(x, q[b], k, mask=self._mask(mask_id, x.shape[0]), cand=cb)
+            out.append((s, i + self.id_offset))
+        return self._wrap(Q, *self._pad(out, k))
+
+    def sparse_topk(self, name, q_ptr, q_terms, q_vals, k, mask_id=0):
+        self.calls.append(("sparse_topk", name, k))
+        csr = self.sparse[name]
+        qp, qt, qv = _np(q_ptr), _np(q_terms), _np(q_vals)
+        out = []
+        for b in range(len(qp) - 1):
+            s, i = O.sparse_topk(csr, qt[qp[b]:qp[b + 1]], qv[qp[b]:qp[b + 1]], k,
+                                 mask=self._mask(mask_id, csr.n_docs))
+            out.append((s, i + self.id_offset))
+        return self._wrap(q_ptr, *self._pad(out, k))
+
+    def rrf(self, ids, counts, limit, tie=0):
+        self.calls.append(("rrf", limit))
+        I, Cn = _np(ids), _np(counts)
+        L, B, _ = I.shape
+        out = []
+        for b in range(B):
+            out.append(O.rrf([I[l, b, :Cn[l, b]] for l in range(L)], limit=limit, tie="id" if tie == 0 else "first_seen"))
+        return self._wrap(ids, *self._pad(out, limit, np.float64))
+
+    def merge_topk(self, scores, ids, counts):
+        self.calls.append(("merge_topk",))
+        S, I, Cn = _np(scores), _np(ids), _np(counts)
+        G, B, k = I.shape
+        out = []
+        for b in range(B):
+            fs = np.concatenate([S[g, b, :Cn[g, b]] for g in range(G)])
+            fi = np.concatenate([I[g, b, :Cn[g, b]] for g in range(G)])
+            o = O.topk_order(fs, fi, k)
+            out.append((fs[o], fi[o]))
+        return self._wrap(ids, *self._pad(out, k))
+
+    def hybrid_topk(self, dense_name, sparse_name, Q, q_ptr, q_terms, q_vals, k, mask_id=0):
+        d = self.dense_topk(dense_name, Q, k, mask_id)
+        s = self.sparse_topk(sparse_name, q_ptr, q_terms, q_vals, k, mask_id)
+        ids = np.stack([_np(d[1]), _np(s[1])])
+        cnt = np.stack([_np(d[2]), _np(s[2])])
+        r = self.rrf(ids, cnt, k)
+        return self._wrap(Q, *[_np(t) for t in r])
