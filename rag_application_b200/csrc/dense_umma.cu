@@ -32,6 +32,7 @@ constexpr int UM_THREADS = 192;
 constexpr int UM_A_BYTES = UM_BM * UM_BK * 2;  // 16 KB
 constexpr int UM_B_BYTES = UM_BN * UM_BK * 2;  // 32 KB
 constexpr uint32_t UM_TMEM_COLS = 512;
+constexpr int UM_MAXQB = 8;            // query blocks (x128 queries) one launch covers
 
 struct UmSmem {
     uint8_t a[UM_STAGES][UM_A_BYTES];
@@ -42,6 +43,8 @@ struct UmSmem {
     uint64_t tfull[2];
     uint64_t tempty[2];
     uint32_t tmem_base;
+    float thr[UM_MAXQB][UM_BM];   // per (query block, query) running k-th best (thread-private slots)
+    int cnt[UM_MAXQB][UM_BM];     // candidates currently in that query's list
 };
 
 // ------------------------------------------------------------------ PTX wrappers
@@ -137,13 +140,14 @@ __device__ __forceinline__ void um_compact(unsigned bal, uint64_t* my_list, uint
         uint64_t* src = reinterpret_cast<uint64_t*>(__shfl_sync(0xFFFFFFFFu, (unsigned long long)my_list, L));
         uint64_t* dst = reinterpret_cast<uint64_t*>(__shfl_sync(0xFFFFFFFFu, (unsigned long long)my_dst, L));
         const int c = __shfl_sync(0xFFFFFFFFu, cnt, L);
-        for (int i = lane; i < UM_CAP; i += 32) sbuf[i] = (i < c) ? __ldcg(src + i) : 0ull;
+        const int n2 = next_pow2(max(c, 32));           // <= UM_CAP; short lists sort cheaply
+        for (int i = lane; i < n2; i += 32) sbuf[i] = (i < c) ? __ldcg(src + i) : 0ull;
         __syncwarp();
-        bitonic_desc(sbuf, UM_CAP, lane, 32, [] { __syncwarp(); });
+        bitonic_desc(sbuf, n2, lane, 32, [] { __syncwarp(); });
         const int nc = min(c, k_sel);
         if (dst != nullptr)
-            for (int i = lane; i < k_sel; i += 32) __stcg(dst + i, sbuf[i]);
-        const uint64_t kth = sbuf[k_sel - 1];
+            for (int i = lane; i < k_sel; i += 32) __stcg(dst + i, i < n2 ? sbuf[i] : 0ull);
+        const uint64_t kth = (k_sel - 1 < n2) ? sbuf[k_sel - 1] : 0ull;
         if (lane == L) {
             cnt = nc;
             if (nc == k_sel) thr = key_score(kth);
@@ -155,17 +159,22 @@ __device__ __forceinline__ void um_compact(unsigned bal, uint64_t* my_list, uint
 // ------------------------------------------------------------------ the kernel
 __global__ void __launch_bounds__(UM_THREADS, 1)
 dense_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_x,
-                  int64_t n, int d, int B, int n_qblocks, int64_t rows_per_chunk, const uint32_t* __restrict__ mask,
+                  int64_t row_lo, int64_t row_hi, int d, int B, int qb_first, int n_qgroups, int qb_per_group,
+                  int qb_total, int64_t rows_per_chunk, const uint32_t* __restrict__ mask,
                   int k_sel, uint32_t idesc, uint64_t* __restrict__ part, uint64_t* __restrict__ scratch,
                   uint32_t* __restrict__ gthr) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     UmSmem& S = *reinterpret_cast<UmSmem*>(smem_raw);   // keeps the shared address space (LDS/STS in the sort)
     if ((smem_u32(smem_raw) & 1023u) != 0u) __trap();   // 128B-swizzle atoms need 1024-byte alignment
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int qblock = blockIdx.x % n_qblocks;
-    const int chunk = blockIdx.x / n_qblocks;
-    const int64_t row_begin = (int64_t)chunk * rows_per_chunk;
-    const int64_t row_end = min(n, row_begin + rows_per_chunk);
+    // CTA = (corpus chunk, query group).  For every X tile the CTA sweeps all query blocks of its
+    // group before moving on: with one group (the main scan) a tile is fetched from HBM once and
+    // re-read from L2 by the other query blocks.
+    const int chunk = blockIdx.x / n_qgroups;
+    const int qb_base = qb_first + (blockIdx.x % n_qgroups) * qb_per_group;
+    const int n_qblocks = max(0, min(qb_per_group, qb_total - qb_base));
+    const int64_t row_begin = row_lo + (int64_t)chunk * rows_per_chunk;
+    const int64_t row_end = min(row_hi, row_begin + rows_per_chunk);
     const int n_tiles = row_end > row_begin ? (int)((row_end - row_begin + UM_BN - 1) / UM_BN) : 0;
     const int n_kb = d / UM_BK;
 
@@ -191,12 +200,14 @@ dense_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
             uint32_t phase = 0;
             for (int t = 0; t < n_tiles; ++t) {
                 const int row0 = (int)(row_begin + (int64_t)t * UM_BN);
-                for (int kb = 0; kb < n_kb; ++kb) {
-                    mbar_wait(&S.empty[stage], phase ^ 1);
-                    mbar_expect_tx(&S.full[stage], UM_A_BYTES + UM_B_BYTES);
-                    tma_load_2d(S.a[stage], &tmap_q, kb * UM_BK, qblock * UM_BM, &S.full[stage]);
-                    tma_load_2d(S.b[stage], &tmap_x, kb * UM_BK, row0, &S.full[stage]);
-                    if (++stage == UM_STAGES) { stage = 0; phase ^= 1; }
+                for (int qb = 0; qb < n_qblocks; ++qb) {
+                    for (int kb = 0; kb < n_kb; ++kb) {
+                        mbar_wait(&S.empty[stage], phase ^ 1);
+                        mbar_expect_tx(&S.full[stage], UM_A_BYTES + UM_B_BYTES);
+                        tma_load_2d(S.a[stage], &tmap_q, kb * UM_BK, (qb_base + qb) * UM_BM, &S.full[stage]);
+                        tma_load_2d(S.b[stage], &tmap_x, kb * UM_BK, row0, &S.full[stage]);
+                        if (++stage == UM_STAGES) { stage = 0; phase ^= 1; }
+                    }
                 }
             }
         }
@@ -205,9 +216,10 @@ dense_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
         if (lane == 0) {
             int stage = 0;
             uint32_t phase = 0;
-            for (int t = 0; t < n_tiles; ++t) {
-                const int as = t & 1;
-                const uint32_t aphase = (uint32_t)(t >> 1) & 1;
+            const int n_units = n_tiles * n_qblocks;   // unit = (X tile, query block)
+            for (int u = 0; u < n_units; ++u) {
+                const int as = u & 1;
+                const uint32_t aphase = (uint32_t)(u >> 1) & 1;
                 mbar_wait(&S.tempty[as], aphase ^ 1);
                 tc_fence_after();
                 const uint32_t tmem_d = tmem_base + (uint32_t)as * UM_BN;
@@ -228,67 +240,83 @@ dense_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
             }
         }
     } else {
-        // ===== epilogue: thread <-> query
+        // ===== epilogue: thread <-> query lane; the query block changes with every unit
         const int quarter = warp & 3;                 // TMEM lane quarter this warp may access
         const int qidx = quarter * 32 + lane;         // query within the block
-        const int b = qblock * UM_BM + qidx;
-        const bool q_valid = b < B;
-        uint64_t* my_list = scratch + ((size_t)blockIdx.x * UM_BM + qidx) * UM_CAP;
         uint64_t* sbuf = S.sortbuf[warp - 2];
-        float thr = q_valid ? -INFINITY : INFINITY;   // local k-th best (strict: later rows have larger ids)
-        int cnt = 0;
         const uint32_t lane_taddr = tmem_base + ((uint32_t)(quarter * 32) << 16);
-        auto process = [&](uint32_t (&v)[32], int64_t rbase, float eff) {
-#pragma unroll
-            for (int i = 0; i < 32; ++i) {
-                const float s = __uint_as_float(v[i]);
-                if (s > eff) {
-                    const int64_t row = rbase + i;
-                    if (row < row_end && mask_test(mask, (uint32_t)row)) {
-                        __stcg(my_list + cnt, make_key(s, (uint32_t)row));
-                        ++cnt;
-                    }
-                }
-            }
-        };
+        for (int qb = 0; qb < n_qblocks; ++qb) {
+            S.thr[qb][qidx] = ((qb_base + qb) * UM_BM + qidx < B) ? -INFINITY : INFINITY;   // strict local k-th best
+            S.cnt[qb][qidx] = 0;
+        }
+        int u = 0;
         for (int t = 0; t < n_tiles; ++t) {
-            const int as = t & 1;
-            const uint32_t aphase = (uint32_t)(t >> 1) & 1;
             const int64_t row0 = row_begin + (int64_t)t * UM_BN;
-            // bound published by the CTAs scanning other chunks for the same query (non-strict: their
-            // rows may have smaller ids) -- fetched while we wait for the accumulator
-            const uint32_t g = q_valid ? __ldcg(gthr + b) : 0u;
-            mbar_wait(&S.tfull[as], aphase);
-            tc_fence_after();
-            float eff = thr;
-            if (g != 0u) eff = fmaxf(eff, nextafterf(ordered_f32(g), -INFINITY));
-            const uint32_t taddr = lane_taddr + (uint32_t)(as * UM_BN);
-            uint32_t va[32], vb[32];
-            tmem_ld32_issue(taddr, va);
+            for (int qb = 0; qb < n_qblocks; ++qb, ++u) {
+                const int as = u & 1;
+                const uint32_t aphase = (uint32_t)(u >> 1) & 1;
+                const int b = (qb_base + qb) * UM_BM + qidx;
+                const bool q_valid = b < B;
+                uint64_t* my_list = scratch + (((size_t)blockIdx.x * qb_per_group + qb) * UM_BM + qidx) * UM_CAP;
+                float thr = S.thr[qb][qidx];
+                int cnt = S.cnt[qb][qidx];
+                // bound published by the CTAs scanning other chunks for the same query (non-strict: their
+                // rows may have smaller ids) -- fetched while we wait for the accumulator
+                const uint32_t g = q_valid ? __ldcg(gthr + b) : 0u;
+                mbar_wait(&S.tfull[as], aphase);
+                tc_fence_after();
+                float eff = thr;
+                if (g != 0u) eff = fmaxf(eff, nextafterf(ordered_f32(g), -INFINITY));
+                const uint32_t taddr = lane_taddr + (uint32_t)(as * UM_BN);
+                auto process = [&](uint32_t (&v)[32], int64_t rbase) {
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) {
+                        const float s = __uint_as_float(v[i]);
+                        if (s > eff) {
+                            const int64_t row = rbase + i;
+                            if (row < row_end && mask_test(mask, (uint32_t)row)) {
+                                __stcg(my_list + cnt, make_key(s, (uint32_t)row));
+                                ++cnt;
+                            }
+                        }
+                    }
+                };
+                uint32_t va[32], vb[32];
+                tmem_ld32_issue(taddr, va);
 #pragma unroll 1
-            for (int g2 = 0; g2 < UM_BN / 64; ++g2) {
-                unsigned bal = __ballot_sync(0xFFFFFFFFu, cnt > UM_CAP - 64);
-                if (bal) {
-                    const float before = thr;
-                    um_compact(bal, my_list, my_list, cnt, thr, sbuf, k_sel, lane);
-                    if (thr > before) { atomicMax(gthr + b, f32_ordered(thr)); eff = fmaxf(eff, thr); }
+                for (int g2 = 0; g2 < UM_BN / 64; ++g2) {
+                    unsigned bal = __ballot_sync(0xFFFFFFFFu, cnt > UM_CAP - 64);
+                    if (bal) {
+                        const float before = thr;
+                        um_compact(bal, my_list, my_list, cnt, thr, sbuf, k_sel, lane);
+                        if (thr > before) { atomicMax(gthr + b, f32_ordered(thr)); eff = fmaxf(eff, thr); }
+                    }
+                    tmem_ld_wait(va);
+                    tmem_ld32_issue(taddr + (uint32_t)(g2 * 64 + 32), vb);
+                    process(va, row0 + g2 * 64);
+                    tmem_ld_wait(vb);
+                    if (g2 + 1 < UM_BN / 64) tmem_ld32_issue(taddr + (uint32_t)(g2 * 64 + 64), va);
+                    process(vb, row0 + g2 * 64 + 32);
                 }
-                tmem_ld_wait(va);
-                tmem_ld32_issue(taddr + (uint32_t)(g2 * 64 + 32), vb);
-                process(va, row0 + g2 * 64, eff);
-                tmem_ld_wait(vb);
-                if (g2 + 1 < UM_BN / 64) tmem_ld32_issue(taddr + (uint32_t)(g2 * 64 + 64), va);
-                process(vb, row0 + g2 * 64 + 32, eff);
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&S.tempty[as]);
+                S.thr[qb][qidx] = thr;
+                S.cnt[qb][qidx] = cnt;
             }
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&S.tempty[as]);
         }
         // final: every valid query emits its best k_sel keys
-        uint64_t* my_dst = q_valid ? part + ((size_t)chunk * B + b) * k_sel : nullptr;
-        const unsigned bal = __ballot_sync(0xFFFFFFFFu, q_valid);
-        __syncwarp();
-        um_compact(bal, my_list, my_dst, cnt, thr, sbuf, k_sel, lane);
+        for (int qb = 0; qb < n_qblocks; ++qb) {
+            const int b = (qb_base + qb) * UM_BM + qidx;
+            const bool q_valid = b < B;
+            uint64_t* my_list = scratch + (((size_t)blockIdx.x * qb_per_group + qb) * UM_BM + qidx) * UM_CAP;
+            uint64_t* my_dst = q_valid ? part + ((size_t)chunk * B + b) * k_sel : nullptr;
+            float thr = S.thr[qb][qidx];
+            int cnt = S.cnt[qb][qidx];
+            const unsigned bal = __ballot_sync(0xFFFFFFFFu, q_valid);
+            __syncwarp();
+            um_compact(bal, my_list, my_dst, cnt, thr, sbuf, k_sel, lane);
+        }
     }
 
     tc_fence_before();
@@ -304,16 +332,47 @@ bool dense_umma_supported(int dtype, int d, int64_t n) {
     return (dtype == 1 || dtype == 2) && d % UM_BK == 0 && d >= UM_BK && n >= 1;
 }
 
+// Scan plan.  Large corpora are scanned in two phases: a small "seeding" scan over the first
+// seed_rows rows (CTA = corpus chunk x one query block, few long lists) whose merged top-k_sel gives
+// every query a global score bound, then the main scan over the rest (CTA = corpus chunk x ALL
+// query blocks) which starts with that bound, so its per-(CTA, query) lists stay short and are
+// sorted once.  part holds n_lists lists per query: chunks_b main lists (+1 seed list).
 cudaError_t dense_umma_plan(int64_t n, int d, int B, int k_sel, int num_sms, UmmaPlan* plan) {
     if (k_sel > UM_CAP - 64) return cudaErrorInvalidValue;
+    (void)d;
     plan->n_qblocks = (B + UM_BM - 1) / UM_BM;
     const int64_t n_tiles = (n + UM_BN - 1) / UM_BN;
-    int64_t chunks = std::max<int64_t>(1, num_sms / plan->n_qblocks);
-    if (chunks > n_tiles) chunks = n_tiles;
-    plan->n_chunks = (int)chunks;
-    plan->list_bytes = (size_t)plan->n_chunks * plan->n_qblocks * UM_BM * UM_CAP * sizeof(uint64_t);
-    plan->scratch_bytes = plan->list_bytes + (size_t)plan->n_qblocks * UM_BM * sizeof(uint32_t);
+    plan->chunks_a = 0;
+    plan->seed_rows = 0;
+    plan->tiles_per_chunk_a = 0;
+    if (n_tiles >= 4 * (int64_t)num_sms) {
+        const int chunks_a = std::max(1, num_sms / plan->n_qblocks);
+        int64_t want_rows = std::min<int64_t>(131072, std::max<int64_t>(8192, n / 128));
+        int64_t tpc = std::max<int64_t>(2, (want_rows / UM_BN + chunks_a - 1) / chunks_a);
+        plan->chunks_a = chunks_a;
+        plan->tiles_per_chunk_a = (int)tpc;
+        plan->seed_rows = tpc * chunks_a * UM_BN;     // < n by the n_tiles condition
+    }
+    const int64_t tiles_b = (n - plan->seed_rows + UM_BN - 1) / UM_BN;
+    plan->chunks_b = (int)std::min<int64_t>(num_sms, std::max<int64_t>(1, tiles_b));
+    plan->n_lists = plan->chunks_b + (plan->chunks_a ? 1 : 0);
+    const int qb_launch = std::min(plan->n_qblocks, UM_MAXQB);   // lists are reused by successive query groups
+    const size_t lists_b = (size_t)plan->chunks_b * qb_launch;
+    const size_t lists_a = (size_t)plan->chunks_a * plan->n_qblocks;
+    plan->list_bytes = std::max(lists_a, lists_b) * UM_BM * UM_CAP * sizeof(uint64_t);
+    plan->gthr_bytes = ((size_t)plan->n_qblocks * UM_BM * sizeof(uint32_t) + 255) & ~(size_t)255;
+    plan->part_a_elems = (size_t)plan->chunks_a * B * k_sel;
+    plan->merge_tmp_elems = plan->chunks_a ? merge_tmp_elems(plan->chunks_a, B, k_sel) : 0;
+    plan->scratch_bytes = plan->list_bytes + plan->gthr_bytes +
+                          (plan->part_a_elems + 2 * plan->merge_tmp_elems) * sizeof(uint64_t);
     return cudaSuccess;
+}
+
+__global__ void seed_gthr_kernel(const uint64_t* __restrict__ seed, int B, int k_sel, uint32_t* __restrict__ gthr) {
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= B) return;
+    const uint64_t kth = seed[(size_t)b * k_sel + (k_sel - 1)];   // 0 = fewer than k_sel rows survived the mask
+    if (kth != 0ull) atomicMax(gthr + b, (uint32_t)(kth >> 32));
 }
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
@@ -352,7 +411,7 @@ cudaError_t make_tmap_2d(void* tmap_out, const void* base, int64_t rows, int d, 
 
 cudaError_t dense_umma_scan(const void* X16, int dtype, int64_t n, int d, const void* Q16, int B,
                             const uint32_t* mask, int k_sel, uint64_t* part, void* scratch, const UmmaPlan& plan,
-                            void* tmap_x, void* tmap_q, cudaStream_t st) {
+                            void* tmap_x, void* tmap_q, cudaStream_t st, int* launches) {
     (void)X16; (void)Q16;
     static bool attr_set = false;
     const size_t smem = sizeof(UmSmem);
@@ -364,17 +423,45 @@ cudaError_t dense_umma_scan(const void* X16, int dtype, int64_t n, int d, const 
     CUtensorMap tq, tx;
     memcpy(&tq, tmap_q, sizeof tq);
     memcpy(&tx, tmap_x, sizeof tx);
-    const int64_t n_tiles = (n + UM_BN - 1) / UM_BN;
-    const int64_t rows_per_chunk = (n_tiles + plan.n_chunks - 1) / plan.n_chunks * UM_BN;
     const uint32_t fmt = (dtype == 2) ? 1u : 0u;  // BF16 : F16
     const uint32_t idesc = (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(UM_BN >> 3) << 17) | ((uint32_t)(UM_BM >> 4) << 24);
-    const int grid = plan.n_chunks * plan.n_qblocks;
-    uint32_t* gthr = reinterpret_cast<uint32_t*>(reinterpret_cast<uint8_t*>(scratch) + plan.list_bytes);
-    cudaError_t me = cudaMemsetAsync(gthr, 0, (size_t)plan.n_qblocks * UM_BM * sizeof(uint32_t), st);
-    if (me != cudaSuccess) return me;
-    dense_umma_kernel<<<grid, UM_THREADS, smem, st>>>(tq, tx, n, d, B, plan.n_qblocks, rows_per_chunk, mask, k_sel,
-                                                      idesc, part, reinterpret_cast<uint64_t*>(scratch), gthr);
-    return cudaGetLastError();
+    uint8_t* sp = reinterpret_cast<uint8_t*>(scratch);
+    uint64_t* lists = reinterpret_cast<uint64_t*>(sp);
+    uint32_t* gthr = reinterpret_cast<uint32_t*>(sp + plan.list_bytes);
+    uint64_t* part_a = reinterpret_cast<uint64_t*>(sp + plan.list_bytes + plan.gthr_bytes);
+    uint64_t* tmp_a = part_a + plan.part_a_elems;
+    uint64_t* tmp_b = tmp_a + plan.merge_tmp_elems;
+    cudaError_t err = cudaMemsetAsync(gthr, 0, (size_t)plan.n_qblocks * UM_BM * sizeof(uint32_t), st);
+    if (err != cudaSuccess) return err;
+    int nl = 0;
+    if (plan.chunks_a) {
+        // ---- seeding scan: rows [0, seed_rows), CTA = (chunk, one query block)
+        const int64_t rpc = (int64_t)plan.tiles_per_chunk_a * UM_BN;
+        dense_umma_kernel<<<plan.chunks_a * plan.n_qblocks, UM_THREADS, smem, st>>>(
+            tq, tx, 0, plan.seed_rows, d, B, 0, plan.n_qblocks, 1, plan.n_qblocks, rpc, mask, k_sel, idesc, part_a,
+            lists, gthr);
+        if ((err = cudaGetLastError()) != cudaSuccess) return err;
+        uint64_t* seed = part + (size_t)plan.chunks_b * B * k_sel;   // list slot chunks_b of `part`
+        int ml = 0;
+        if ((err = merge_key_lists(part_a, plan.chunks_a, B, k_sel, tmp_a, tmp_b, seed, k_sel, st, &ml)) != cudaSuccess)
+            return err;
+        seed_gthr_kernel<<<(B + 255) / 256, 256, 0, st>>>(seed, B, k_sel, gthr);
+        if ((err = cudaGetLastError()) != cudaSuccess) return err;
+        nl += 2 + ml;
+    }
+    // ---- main scan: rows [seed_rows, n), CTA = (chunk, all query blocks of the group)
+    const int64_t tiles_b = (n - plan.seed_rows + UM_BN - 1) / UM_BN;
+    const int64_t rows_per_chunk = (tiles_b + plan.chunks_b - 1) / plan.chunks_b * UM_BN;
+    for (int qb0 = 0; qb0 < plan.n_qblocks; qb0 += UM_MAXQB) {
+        const int nqb = std::min(UM_MAXQB, plan.n_qblocks - qb0);
+        dense_umma_kernel<<<plan.chunks_b, UM_THREADS, smem, st>>>(tq, tx, plan.seed_rows, n, d, B, qb0, 1, nqb,
+                                                                  plan.n_qblocks, rows_per_chunk, mask, k_sel, idesc,
+                                                                  part, lists, gthr);
+        if ((err = cudaGetLastError()) != cudaSuccess) return err;
+        ++nl;
+    }
+    if (launches) *launches = nl;
+    return cudaSuccess;
 }
 
 }  // namespace brag

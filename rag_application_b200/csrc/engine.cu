@@ -198,12 +198,13 @@ void dense_topk_dev(brag_engine* e, DenseSpace& s, const float* Q, int B, int k,
             void* q16 = e->q16.ensure((size_t)Bpad * s.d * 2);
             CK(brag::round_queries(Q, B, s.d, s.dtype, qs, q16, Bpad, st));
             CK(brag::make_tmap_2d(e->tmap_q, q16, Bpad, s.d, 128));
-            P = plan.n_chunks;
+            P = plan.n_lists;
             part = e->part.as<uint64_t>((size_t)P * B * k_sel);
             void* scratch = e->umma_scratch.ensure(plan.scratch_bytes);
+            int launches = 0;
             CK(brag::dense_umma_scan(s.x, s.dtype, s.n, s.d, q16, B, mask, k_sel, part, scratch, plan, s.tmap_x,
-                                     e->tmap_q, st));
-            e->kernel_launches += 2;
+                                     e->tmap_q, st, &launches));
+            e->kernel_launches += 1 + launches;
         } else {
             CK(brag::round_queries(Q, B, s.d, s.dtype, qs, nullptr, B, st));
             const int64_t ngroups = (s.n + 31) / 32;

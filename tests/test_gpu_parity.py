@@ -74,6 +74,27 @@ def test_dense_tcgen05(engine, dtype, n, d, B):
         check_dense(xs, O.round_storage(q[b], dtype), k, s[b], i[b], int(c[b]))
 
 
+@pytest.mark.parametrize("masked", [False, True])
+def test_dense_tcgen05_seeded_two_phase(engine, masked):
+    """Corpora of >= 4*148 tiles take the two-phase scan (seeding scan -> per-query bound -> main scan)."""
+    n, d, B, k = 160_000, 64, 130, 100
+    x = synth.dense_corpus(n, d, seed=77, clustered=True)
+    q = synth.dense_queries(x, B, seed=78)
+    xs = O.round_storage(x, "bf16")
+    engine.dense_set("t", x, "bf16")
+    mask = synth.random_mask(n, 0.10) if masked else None
+    if masked:
+        engine.mask_set(7, mask)
+    engine.force_dense_path("tcgen05")
+    s, i, c = engine.dense_topk("t", q, k, mask_id=7 if masked else 0)
+    engine.force_dense_path("gemv")
+    s0, i0, c0 = engine.dense_topk("t", q[:8], k, mask_id=7 if masked else 0)
+    engine.force_dense_path(None)
+    assert np.array_equal(i[:8], i0) and np.array_equal(s[:8], s0)
+    for b in range(0, B, 13):
+        check_dense(xs, O.round_storage(q[b], "bf16"), k, s[b], i[b], int(c[b]), mask=mask)
+
+
 def test_dense_paths_agree(engine):
     """Both scan kernels feed the same re-score: final lists must be identical."""
     x = synth.dense_corpus(30000, 256, seed=3)
