@@ -4,14 +4,20 @@
 //
 // S[q, r] = sum_k Q[q, k] * X[r, k]; tile = 128 queries (UMMA M, TMEM lanes) x 256 corpus rows
 // (UMMA N, TMEM columns), K streamed 64 elements (one 128-byte swizzle atom) per pipeline stage.
+// One persistent CTA per SM owns a contiguous corpus chunk; for every X tile it sweeps ALL query
+// blocks before moving on, so a tile comes from HBM once and is re-read from L2.
 //   warp 0      : TMA producer  (cp.async.bulk.tensor -> 128B-swizzled smem, mbarrier tx)
 //   warp 1      : TMEM allocator + single-thread tcgen05.mma issuer (accumulators in TMEM, x2 buffered)
 //   warps 2..5  : epilogue.  Each thread owns ONE query (its TMEM lane): tcgen05.ld 32 columns at a
-//                 time and compare against that query's running k-th-best threshold held in a
-//                 register; the rare survivors go to the thread's candidate list in global memory.
-//                 When a list fills, the warp sorts it in shared memory and tightens the threshold.
-// A CTA is persistent over its contiguous corpus chunk for one block of 128 queries; CTAs that share
-// a chunk (different query blocks) run concurrently so the X tiles are served from L2.
+//                 time, compare against the query's global score bound; the rare survivors are
+//                 appended (unsorted) to the (CTA, query) candidate list in global memory and counted
+//                 in the query's global score histogram.
+//   warp 6      : bound manager.  Sweeps the histograms of the queries this CTA manages and
+//                 publishes, per query, the highest score edge that at least k_sel scanned rows reach.
+//                 That is the k_sel-th best score over everything ANY CTA has scanned so far, so the
+//                 pass rate decays like k/(rows scanned by the whole GPU) and no list is ever sorted
+//                 inside the scan (a full list falls back to a local sort, never seen in practice).
+// A second kernel gathers, per query, the candidates that reach the final bound and sorts them.
 // Roofline: tensor pipe; flops = 2 * N * d * B.
 #include <cuda.h>
 
@@ -27,12 +33,20 @@ constexpr int UM_BM = 128;
 constexpr int UM_BN = 256;
 constexpr int UM_BK = 64;
 constexpr int UM_STAGES = 4;
-constexpr int UM_CAP = 512;
-constexpr int UM_THREADS = 192;
+constexpr int UM_CAP = 512;            // candidate slots per (CTA, query)
+constexpr int UM_THREADS = 224;
 constexpr int UM_A_BYTES = UM_BM * UM_BK * 2;  // 16 KB
 constexpr int UM_B_BYTES = UM_BN * UM_BK * 2;  // 32 KB
 constexpr uint32_t UM_TMEM_COLS = 512;
 constexpr int UM_MAXQB = 8;            // query blocks (x128 queries) one launch covers
+// score histogram per query over the order-preserving uint32 image of the float score:
+// coarse bin = top 7 bits, fine bin = top 14 bits (sign + exponent + 5 mantissa bits, ~3 % wide)
+constexpr int UM_FINE_SHIFT = 18;
+constexpr int UM_FINE_BINS = 1 << (32 - UM_FINE_SHIFT);      // 16384
+constexpr int UM_COARSE_SHIFT = 25;
+constexpr int UM_COARSE_BINS = 1 << (32 - UM_COARSE_SHIFT);  // 128
+constexpr int UM_FINE_PER_COARSE = UM_FINE_BINS / UM_COARSE_BINS;  // 128
+constexpr int UM_SEL_CAP = 4096;       // keys per CTA sort in the final per-query selection
 
 struct UmSmem {
     uint8_t a[UM_STAGES][UM_A_BYTES];
@@ -43,7 +57,8 @@ struct UmSmem {
     uint64_t tfull[2];
     uint64_t tempty[2];
     uint32_t tmem_base;
-    float thr[UM_MAXQB][UM_BM];   // per (query block, query) running k-th best (thread-private slots)
+    int epi_done;                 // epilogue warps that have finished (stops the bound manager)
+    float thr[UM_MAXQB][UM_BM];   // per (query block, query) local k-th best after an overflow sort
     int cnt[UM_MAXQB][UM_BM];     // candidates currently in that query's list
 };
 
@@ -118,6 +133,14 @@ __device__ __forceinline__ void tmem_ld_wait(uint32_t (&v)[32]) {
         :: "memory");
 }
 
+// one column for every lane of the warp's TMEM quarter (warp-collective; used on the rare hit path)
+__device__ __forceinline__ uint32_t tmem_ld1(uint32_t taddr) {
+    uint32_t r;
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];\n\ttcgen05.wait::ld.sync.aligned;"
+                 : "=r"(r) : "r"(taddr) : "memory");
+    return r;
+}
+
 // K-major, 128-byte swizzle: 8-row groups are 1024 B apart (SBO); LBO unused; version 1; layout 2.
 __device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr) {
     uint64_t d = 0;
@@ -157,30 +180,29 @@ __device__ __forceinline__ void um_compact(unsigned bal, uint64_t* my_list, uint
 }
 
 // ------------------------------------------------------------------ the kernel
+// lists  : [grid][n_qblocks][128][UM_CAP] keys (unsorted), counts: [grid][B] entries used
+// gthr   : [B] order-preserving uint32 score bounds (0 = none yet)
+// coarse : [B][UM_COARSE_BINS], fine: [B][UM_FINE_BINS] row counts per score bin
 __global__ void __launch_bounds__(UM_THREADS, 1)
 dense_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_x,
-                  int64_t row_lo, int64_t row_hi, int d, int B, int qb_first, int n_qgroups, int qb_per_group,
-                  int qb_total, int64_t rows_per_chunk, const uint32_t* __restrict__ mask,
-                  int k_sel, uint32_t idesc, uint64_t* __restrict__ part, uint64_t* __restrict__ scratch,
-                  uint32_t* __restrict__ gthr) {
+                  int64_t n, int d, int B, int qb_base, int n_qblocks, int64_t rows_per_chunk,
+                  const uint32_t* __restrict__ mask, int k_sel, uint32_t idesc, uint64_t* __restrict__ lists,
+                  int* __restrict__ counts, uint32_t* __restrict__ gthr, uint32_t* __restrict__ coarse,
+                  uint32_t* __restrict__ fine) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     UmSmem& S = *reinterpret_cast<UmSmem*>(smem_raw);   // keeps the shared address space (LDS/STS in the sort)
     if ((smem_u32(smem_raw) & 1023u) != 0u) __trap();   // 128B-swizzle atoms need 1024-byte alignment
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    // CTA = (corpus chunk, query group).  For every X tile the CTA sweeps all query blocks of its
-    // group before moving on: with one group (the main scan) a tile is fetched from HBM once and
-    // re-read from L2 by the other query blocks.
-    const int chunk = blockIdx.x / n_qgroups;
-    const int qb_base = qb_first + (blockIdx.x % n_qgroups) * qb_per_group;
-    const int n_qblocks = max(0, min(qb_per_group, qb_total - qb_base));
-    const int64_t row_begin = row_lo + (int64_t)chunk * rows_per_chunk;
-    const int64_t row_end = min(row_hi, row_begin + rows_per_chunk);
+    const int chunk = blockIdx.x;
+    const int64_t row_begin = (int64_t)chunk * rows_per_chunk;
+    const int64_t row_end = min(n, row_begin + rows_per_chunk);
     const int n_tiles = row_end > row_begin ? (int)((row_end - row_begin + UM_BN - 1) / UM_BN) : 0;
     const int n_kb = d / UM_BK;
 
     if (warp == 0 && lane == 0) {
         for (int s = 0; s < UM_STAGES; ++s) { mbar_init(&S.full[s], 1); mbar_init(&S.empty[s], 1); }
         for (int s = 0; s < 2; ++s) { mbar_init(&S.tfull[s], 1); mbar_init(&S.tempty[s], 4); }
+        S.epi_done = 0;
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     }
@@ -239,14 +261,74 @@ dense_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
                 }
             }
         }
+    } else if (warp == 6) {
+        // ===== bound manager: queries q = blockIdx.x, blockIdx.x + gridDim.x, ... of this launch
+        const int q_lo = qb_base * UM_BM, q_hi = min(B, (qb_base + n_qblocks) * UM_BM);
+        while (true) {
+            const int done = *reinterpret_cast<volatile int*>(&S.epi_done);
+            for (int q = q_lo + (int)blockIdx.x; q < q_hi; q += (int)gridDim.x) {
+                // coarse suffix counts from the top: lane l owns coarse bins 4l..4l+3
+                const uint4 c4 = __ldcg(reinterpret_cast<const uint4*>(coarse + (size_t)q * UM_COARSE_BINS) + lane);
+                uint32_t own = c4.x + c4.y + c4.z + c4.w;
+                uint32_t suf = own;                                  // inclusive suffix over lanes >= l
+#pragma unroll
+                for (int off = 1; off < 32; off <<= 1) {
+                    const uint32_t o = __shfl_down_sync(0xFFFFFFFFu, suf, off);
+                    if (lane + off < 32) suf += o;
+                }
+                const unsigned has = __ballot_sync(0xFFFFFFFFu, suf >= (uint32_t)k_sel);
+                if (has == 0u) continue;                              // fewer than k_sel rows seen so far
+                const int L = 31 - __clz(has);                        // highest lane whose suffix reaches k_sel
+                const uint32_t above_lane = __shfl_sync(0xFFFFFFFFu, suf - own, L);   // rows in lanes > L
+                const uint32_t x = __shfl_sync(0xFFFFFFFFu, c4.x, L), y = __shfl_sync(0xFFFFFFFFu, c4.y, L),
+                               z = __shfl_sync(0xFFFFFFFFu, c4.z, L), w = __shfl_sync(0xFFFFFFFFu, c4.w, L);
+                int cb;
+                uint32_t above;                                       // rows in coarse bins > cb
+                if (above_lane + w >= (uint32_t)k_sel) { cb = 4 * L + 3; above = above_lane; }
+                else if (above_lane + w + z >= (uint32_t)k_sel) { cb = 4 * L + 2; above = above_lane + w; }
+                else if (above_lane + w + z + y >= (uint32_t)k_sel) { cb = 4 * L + 1; above = above_lane + w + z; }
+                else { cb = 4 * L; above = above_lane + w + z + y; }
+                (void)x;
+                // fine bins inside coarse bin cb
+                const uint4 f4 = __ldcg(reinterpret_cast<const uint4*>(fine + (size_t)q * UM_FINE_BINS +
+                                                                      (size_t)cb * UM_FINE_PER_COARSE) + lane);
+                const uint32_t fown = f4.x + f4.y + f4.z + f4.w;
+                uint32_t fsuf = fown;
+#pragma unroll
+                for (int off = 1; off < 32; off <<= 1) {
+                    const uint32_t o = __shfl_down_sync(0xFFFFFFFFu, fsuf, off);
+                    if (lane + off < 32) fsuf += o;
+                }
+                const unsigned fhas = __ballot_sync(0xFFFFFFFFu, above + fsuf >= (uint32_t)k_sel);
+                uint32_t bound;
+                if (fhas == 0u) {
+                    bound = (uint32_t)cb << UM_COARSE_SHIFT;          // fine counts lag: the coarse edge is still valid
+                } else {
+                    const int FL = 31 - __clz(fhas);
+                    const uint32_t fa = above + __shfl_sync(0xFFFFFFFFu, fsuf - fown, FL);
+                    const uint32_t fx = __shfl_sync(0xFFFFFFFFu, f4.x, FL), fy = __shfl_sync(0xFFFFFFFFu, f4.y, FL),
+                                   fz = __shfl_sync(0xFFFFFFFFu, f4.z, FL), fw = __shfl_sync(0xFFFFFFFFu, f4.w, FL);
+                    int fb;
+                    if (fa + fw >= (uint32_t)k_sel) fb = 3;
+                    else if (fa + fw + fz >= (uint32_t)k_sel) fb = 2;
+                    else if (fa + fw + fz + fy >= (uint32_t)k_sel) fb = 1;
+                    else fb = 0;
+                    (void)fx;
+                    bound = (uint32_t)(cb * UM_FINE_PER_COARSE + 4 * FL + fb) << UM_FINE_SHIFT;
+                }
+                if (lane == 0 && bound != 0u) atomicMax(gthr + q, bound);
+            }
+            if (done >= 4) break;
+            __nanosleep(500);
+        }
     } else {
-        // ===== epilogue: thread <-> query lane; the query block changes with every unit
+        // ===== epilogue (warps 2..5): thread <-> query lane; the query block changes with every unit
         const int quarter = warp & 3;                 // TMEM lane quarter this warp may access
         const int qidx = quarter * 32 + lane;         // query within the block
         uint64_t* sbuf = S.sortbuf[warp - 2];
         const uint32_t lane_taddr = tmem_base + ((uint32_t)(quarter * 32) << 16);
         for (int qb = 0; qb < n_qblocks; ++qb) {
-            S.thr[qb][qidx] = ((qb_base + qb) * UM_BM + qidx < B) ? -INFINITY : INFINITY;   // strict local k-th best
+            S.thr[qb][qidx] = ((qb_base + qb) * UM_BM + qidx < B) ? -INFINITY : INFINITY;
             S.cnt[qb][qidx] = 0;
         }
         int u = 0;
@@ -257,26 +339,37 @@ dense_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
                 const uint32_t aphase = (uint32_t)(u >> 1) & 1;
                 const int b = (qb_base + qb) * UM_BM + qidx;
                 const bool q_valid = b < B;
-                uint64_t* my_list = scratch + (((size_t)blockIdx.x * qb_per_group + qb) * UM_BM + qidx) * UM_CAP;
+                uint64_t* my_list = lists + (((size_t)chunk * n_qblocks + qb) * UM_BM + qidx) * UM_CAP;
+                uint32_t* my_fine = fine + (size_t)(q_valid ? b : 0) * UM_FINE_BINS;
+                uint32_t* my_coarse = coarse + (size_t)(q_valid ? b : 0) * UM_COARSE_BINS;
                 float thr = S.thr[qb][qidx];
                 int cnt = S.cnt[qb][qidx];
-                // bound published by the CTAs scanning other chunks for the same query (non-strict: their
-                // rows may have smaller ids) -- fetched while we wait for the accumulator
+                // the query's global bound (k_sel-th best score over all rows scanned so far by any CTA,
+                // rounded down to a histogram edge) -- fetched while we wait for the accumulator
                 const uint32_t g = q_valid ? __ldcg(gthr + b) : 0u;
                 mbar_wait(&S.tfull[as], aphase);
                 tc_fence_after();
                 float eff = thr;
-                if (g != 0u) eff = fmaxf(eff, nextafterf(ordered_f32(g), -INFINITY));
+                if (g != 0u) eff = fmaxf(eff, nextafterf(ordered_f32(g), -INFINITY));   // keeps score >= bound
                 const uint32_t taddr = lane_taddr + (uint32_t)(as * UM_BN);
-                auto process = [&](uint32_t (&v)[32], int64_t rbase) {
+                auto process = [&](uint32_t (&v)[32], int col0) {
+                    uint32_t m = 0u;
 #pragma unroll
-                    for (int i = 0; i < 32; ++i) {
-                        const float s = __uint_as_float(v[i]);
-                        if (s > eff) {
-                            const int64_t row = rbase + i;
+                    for (int i = 0; i < 32; ++i) m |= (__uint_as_float(v[i]) > eff) ? (1u << i) : 0u;
+                    uint32_t mw = __reduce_or_sync(0xFFFFFFFFu, m);
+                    while (mw) {                                   // rare: columns where some query has a hit
+                        const int i = __ffs(mw) - 1;
+                        mw &= mw - 1;
+                        const float s = __uint_as_float(tmem_ld1(taddr + (uint32_t)(col0 + i)));
+                        if ((m >> i) & 1u) {
+                            const int64_t row = row0 + col0 + i;
                             if (row < row_end && mask_test(mask, (uint32_t)row)) {
-                                __stcg(my_list + cnt, make_key(s, (uint32_t)row));
+                                const uint64_t key = make_key(s, (uint32_t)row);
+                                __stcg(my_list + cnt, key);
                                 ++cnt;
+                                const uint32_t o = (uint32_t)(key >> 32);
+                                atomicAdd(my_fine + (o >> UM_FINE_SHIFT), 1u);
+                                atomicAdd(my_coarse + (o >> UM_COARSE_SHIFT), 1u);
                             }
                         }
                     }
@@ -285,18 +378,17 @@ dense_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
                 tmem_ld32_issue(taddr, va);
 #pragma unroll 1
                 for (int g2 = 0; g2 < UM_BN / 64; ++g2) {
-                    unsigned bal = __ballot_sync(0xFFFFFFFFu, cnt > UM_CAP - 64);
-                    if (bal) {
-                        const float before = thr;
+                    const unsigned bal = __ballot_sync(0xFFFFFFFFu, cnt > UM_CAP - 64);
+                    if (bal) {   // list full (pathological): sort locally, keep k_sel, tighten the local bound
                         um_compact(bal, my_list, my_list, cnt, thr, sbuf, k_sel, lane);
-                        if (thr > before) { atomicMax(gthr + b, f32_ordered(thr)); eff = fmaxf(eff, thr); }
+                        eff = fmaxf(eff, thr);
                     }
                     tmem_ld_wait(va);
                     tmem_ld32_issue(taddr + (uint32_t)(g2 * 64 + 32), vb);
-                    process(va, row0 + g2 * 64);
+                    process(va, g2 * 64);
                     tmem_ld_wait(vb);
                     if (g2 + 1 < UM_BN / 64) tmem_ld32_issue(taddr + (uint32_t)(g2 * 64 + 64), va);
-                    process(vb, row0 + g2 * 64 + 32);
+                    process(vb, g2 * 64 + 32);
                 }
                 tc_fence_before();
                 __syncwarp();
@@ -305,18 +397,12 @@ dense_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
                 S.cnt[qb][qidx] = cnt;
             }
         }
-        // final: every valid query emits its best k_sel keys
         for (int qb = 0; qb < n_qblocks; ++qb) {
             const int b = (qb_base + qb) * UM_BM + qidx;
-            const bool q_valid = b < B;
-            uint64_t* my_list = scratch + (((size_t)blockIdx.x * qb_per_group + qb) * UM_BM + qidx) * UM_CAP;
-            uint64_t* my_dst = q_valid ? part + ((size_t)chunk * B + b) * k_sel : nullptr;
-            float thr = S.thr[qb][qidx];
-            int cnt = S.cnt[qb][qidx];
-            const unsigned bal = __ballot_sync(0xFFFFFFFFu, q_valid);
-            __syncwarp();
-            um_compact(bal, my_list, my_dst, cnt, thr, sbuf, k_sel, lane);
+            if (b < B) counts[(size_t)chunk * B + b] = S.cnt[qb][qidx];
         }
+        __syncwarp();
+        if (lane == 0) atomicAdd(&S.epi_done, 1);
     }
 
     tc_fence_before();
@@ -327,52 +413,75 @@ dense_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
     }
 }
 
+// ------------------------------------------------------------------ final per-query selection
+// Gathers, from the n_chunks unsorted (CTA, query) lists, the candidates that reach the query's
+// final bound (at least k_sel of them do), sorts them and writes the best k_sel keys.
+constexpr int SELK_THREADS = 256;
+constexpr int SELK_CAP = 8192;     // 64 KB of keys; 8 lists (<= 8 * UM_CAP entries) are added per round
+
+__global__ void __launch_bounds__(SELK_THREADS)
+dense_umma_select_kernel(const uint64_t* __restrict__ lists, const int* __restrict__ counts,
+                         const uint32_t* __restrict__ gthr, int n_chunks, int B, int qb_base, int n_qblocks,
+                         int k_sel, uint64_t* __restrict__ out) {
+    extern __shared__ __align__(16) uint8_t smem_raw[];
+    uint64_t* a = reinterpret_cast<uint64_t*>(smem_raw);
+    __shared__ int fill;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int b = qb_base * UM_BM + blockIdx.x;
+    if (b >= B) return;
+    const int qb = blockIdx.x / UM_BM, qidx = blockIdx.x % UM_BM;
+    const uint32_t bound = gthr[b];
+    if (tid == 0) fill = 0;
+    __syncthreads();
+    for (int c0 = 0; c0 < n_chunks; c0 += SELK_THREADS / 32) {
+        if (fill + (SELK_THREADS / 32) * UM_CAP > SELK_CAP) {       // uniform: fill is stable here
+            const int f = fill;
+            const int n2 = next_pow2(max(f, 32));
+            for (int i = f + tid; i < n2; i += SELK_THREADS) a[i] = 0ull;
+            __syncthreads();
+            bitonic_desc(a, n2, tid, SELK_THREADS, [] { __syncthreads(); });
+            if (tid == 0) fill = min(f, k_sel);
+            __syncthreads();
+        }
+        const int chunk = c0 + warp;
+        if (chunk < n_chunks) {
+            const int c = min(counts[(size_t)chunk * B + b], UM_CAP);
+            const uint64_t* src = lists + (((size_t)chunk * n_qblocks + qb) * UM_BM + qidx) * UM_CAP;
+            for (int i = lane; i < c; i += 32) {
+                const uint64_t key = __ldcg(src + i);
+                if ((uint32_t)(key >> 32) >= bound) a[atomicAdd(&fill, 1)] = key;
+            }
+        }
+        __syncthreads();
+    }
+    const int f = fill;
+    const int n2 = next_pow2(max(f, 32));
+    for (int i = f + tid; i < n2; i += SELK_THREADS) a[i] = 0ull;
+    __syncthreads();
+    bitonic_desc(a, n2, tid, SELK_THREADS, [] { __syncthreads(); });
+    for (int i = tid; i < k_sel; i += SELK_THREADS) out[(size_t)b * k_sel + i] = (i < n2) ? a[i] : 0ull;
+}
+
 // ------------------------------------------------------------------ host side
 bool dense_umma_supported(int dtype, int d, int64_t n) {
     return (dtype == 1 || dtype == 2) && d % UM_BK == 0 && d >= UM_BK && n >= 1;
 }
 
-// Scan plan.  Large corpora are scanned in two phases: a small "seeding" scan over the first
-// seed_rows rows (CTA = corpus chunk x one query block, few long lists) whose merged top-k_sel gives
-// every query a global score bound, then the main scan over the rest (CTA = corpus chunk x ALL
-// query blocks) which starts with that bound, so its per-(CTA, query) lists stay short and are
-// sorted once.  part holds n_lists lists per query: chunks_b main lists (+1 seed list).
 cudaError_t dense_umma_plan(int64_t n, int d, int B, int k_sel, int num_sms, UmmaPlan* plan) {
     if (k_sel > UM_CAP - 64) return cudaErrorInvalidValue;
     (void)d;
     plan->n_qblocks = (B + UM_BM - 1) / UM_BM;
     const int64_t n_tiles = (n + UM_BN - 1) / UM_BN;
-    plan->chunks_a = 0;
-    plan->seed_rows = 0;
-    plan->tiles_per_chunk_a = 0;
-    if (n_tiles >= 4 * (int64_t)num_sms) {
-        const int chunks_a = std::max(1, num_sms / plan->n_qblocks);
-        int64_t want_rows = std::min<int64_t>(131072, std::max<int64_t>(8192, n / 128));
-        int64_t tpc = std::max<int64_t>(2, (want_rows / UM_BN + chunks_a - 1) / chunks_a);
-        plan->chunks_a = chunks_a;
-        plan->tiles_per_chunk_a = (int)tpc;
-        plan->seed_rows = tpc * chunks_a * UM_BN;     // < n by the n_tiles condition
-    }
-    const int64_t tiles_b = (n - plan->seed_rows + UM_BN - 1) / UM_BN;
-    plan->chunks_b = (int)std::min<int64_t>(num_sms, std::max<int64_t>(1, tiles_b));
-    plan->n_lists = plan->chunks_b + (plan->chunks_a ? 1 : 0);
+    plan->n_chunks = (int)std::min<int64_t>(num_sms, std::max<int64_t>(1, n_tiles));   // one persistent CTA per SM
     const int qb_launch = std::min(plan->n_qblocks, UM_MAXQB);   // lists are reused by successive query groups
-    const size_t lists_b = (size_t)plan->chunks_b * qb_launch;
-    const size_t lists_a = (size_t)plan->chunks_a * plan->n_qblocks;
-    plan->list_bytes = std::max(lists_a, lists_b) * UM_BM * UM_CAP * sizeof(uint64_t);
-    plan->gthr_bytes = ((size_t)plan->n_qblocks * UM_BM * sizeof(uint32_t) + 255) & ~(size_t)255;
-    plan->part_a_elems = (size_t)plan->chunks_a * B * k_sel;
-    plan->merge_tmp_elems = plan->chunks_a ? merge_tmp_elems(plan->chunks_a, B, k_sel) : 0;
-    plan->scratch_bytes = plan->list_bytes + plan->gthr_bytes +
-                          (plan->part_a_elems + 2 * plan->merge_tmp_elems) * sizeof(uint64_t);
+    auto up = [](size_t x) { return (x + 255) & ~(size_t)255; };
+    plan->list_bytes = up((size_t)plan->n_chunks * qb_launch * UM_BM * UM_CAP * sizeof(uint64_t));
+    plan->count_bytes = up((size_t)plan->n_chunks * B * sizeof(int));
+    plan->gthr_bytes = up((size_t)B * sizeof(uint32_t));
+    plan->coarse_bytes = up((size_t)B * UM_COARSE_BINS * sizeof(uint32_t));
+    plan->fine_bytes = up((size_t)B * UM_FINE_BINS * sizeof(uint32_t));
+    plan->scratch_bytes = plan->list_bytes + plan->count_bytes + plan->gthr_bytes + plan->coarse_bytes + plan->fine_bytes;
     return cudaSuccess;
-}
-
-__global__ void seed_gthr_kernel(const uint64_t* __restrict__ seed, int B, int k_sel, uint32_t* __restrict__ gthr) {
-    const int b = blockIdx.x * blockDim.x + threadIdx.x;
-    if (b >= B) return;
-    const uint64_t kth = seed[(size_t)b * k_sel + (k_sel - 1)];   // 0 = fewer than k_sel rows survived the mask
-    if (kth != 0ull) atomicMax(gthr + b, (uint32_t)(kth >> 32));
 }
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
@@ -410,13 +519,15 @@ cudaError_t make_tmap_2d(void* tmap_out, const void* base, int64_t rows, int d, 
 }
 
 cudaError_t dense_umma_scan(const void* X16, int dtype, int64_t n, int d, const void* Q16, int B,
-                            const uint32_t* mask, int k_sel, uint64_t* part, void* scratch, const UmmaPlan& plan,
+                            const uint32_t* mask, int k_sel, uint64_t* cand, void* scratch, const UmmaPlan& plan,
                             void* tmap_x, void* tmap_q, cudaStream_t st, int* launches) {
     (void)X16; (void)Q16;
     static bool attr_set = false;
     const size_t smem = sizeof(UmSmem);
     if (!attr_set) {
         cudaError_t e = cudaFuncSetAttribute(dense_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        e = cudaFuncSetAttribute(dense_umma_select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SELK_CAP * 8);
         if (e != cudaSuccess) return e;
         attr_set = true;
     }
@@ -427,38 +538,26 @@ cudaError_t dense_umma_scan(const void* X16, int dtype, int64_t n, int d, const 
     const uint32_t idesc = (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(UM_BN >> 3) << 17) | ((uint32_t)(UM_BM >> 4) << 24);
     uint8_t* sp = reinterpret_cast<uint8_t*>(scratch);
     uint64_t* lists = reinterpret_cast<uint64_t*>(sp);
-    uint32_t* gthr = reinterpret_cast<uint32_t*>(sp + plan.list_bytes);
-    uint64_t* part_a = reinterpret_cast<uint64_t*>(sp + plan.list_bytes + plan.gthr_bytes);
-    uint64_t* tmp_a = part_a + plan.part_a_elems;
-    uint64_t* tmp_b = tmp_a + plan.merge_tmp_elems;
-    cudaError_t err = cudaMemsetAsync(gthr, 0, (size_t)plan.n_qblocks * UM_BM * sizeof(uint32_t), st);
+    int* counts = reinterpret_cast<int*>(sp + plan.list_bytes);
+    uint32_t* gthr = reinterpret_cast<uint32_t*>(sp + plan.list_bytes + plan.count_bytes);
+    uint32_t* coarse = reinterpret_cast<uint32_t*>(sp + plan.list_bytes + plan.count_bytes + plan.gthr_bytes);
+    uint32_t* fine = reinterpret_cast<uint32_t*>(sp + plan.list_bytes + plan.count_bytes + plan.gthr_bytes + plan.coarse_bytes);
+    cudaError_t err = cudaMemsetAsync(gthr, 0, plan.gthr_bytes + plan.coarse_bytes + plan.fine_bytes, st);
     if (err != cudaSuccess) return err;
+    const int64_t n_tiles = (n + UM_BN - 1) / UM_BN;
+    const int64_t rows_per_chunk = (n_tiles + plan.n_chunks - 1) / plan.n_chunks * UM_BN;
     int nl = 0;
-    if (plan.chunks_a) {
-        // ---- seeding scan: rows [0, seed_rows), CTA = (chunk, one query block)
-        const int64_t rpc = (int64_t)plan.tiles_per_chunk_a * UM_BN;
-        dense_umma_kernel<<<plan.chunks_a * plan.n_qblocks, UM_THREADS, smem, st>>>(
-            tq, tx, 0, plan.seed_rows, d, B, 0, plan.n_qblocks, 1, plan.n_qblocks, rpc, mask, k_sel, idesc, part_a,
-            lists, gthr);
-        if ((err = cudaGetLastError()) != cudaSuccess) return err;
-        uint64_t* seed = part + (size_t)plan.chunks_b * B * k_sel;   // list slot chunks_b of `part`
-        int ml = 0;
-        if ((err = merge_key_lists(part_a, plan.chunks_a, B, k_sel, tmp_a, tmp_b, seed, k_sel, st, &ml)) != cudaSuccess)
-            return err;
-        seed_gthr_kernel<<<(B + 255) / 256, 256, 0, st>>>(seed, B, k_sel, gthr);
-        if ((err = cudaGetLastError()) != cudaSuccess) return err;
-        nl += 2 + ml;
-    }
-    // ---- main scan: rows [seed_rows, n), CTA = (chunk, all query blocks of the group)
-    const int64_t tiles_b = (n - plan.seed_rows + UM_BN - 1) / UM_BN;
-    const int64_t rows_per_chunk = (tiles_b + plan.chunks_b - 1) / plan.chunks_b * UM_BN;
+    // query groups of <= UM_MAXQB blocks (1024 queries): each group is one pass over the corpus
     for (int qb0 = 0; qb0 < plan.n_qblocks; qb0 += UM_MAXQB) {
         const int nqb = std::min(UM_MAXQB, plan.n_qblocks - qb0);
-        dense_umma_kernel<<<plan.chunks_b, UM_THREADS, smem, st>>>(tq, tx, plan.seed_rows, n, d, B, qb0, 1, nqb,
-                                                                  plan.n_qblocks, rows_per_chunk, mask, k_sel, idesc,
-                                                                  part, lists, gthr);
+        dense_umma_kernel<<<plan.n_chunks, UM_THREADS, smem, st>>>(tq, tx, n, d, B, qb0, nqb, rows_per_chunk, mask, k_sel,
+                                                                  idesc, lists, counts, gthr, coarse, fine);
         if ((err = cudaGetLastError()) != cudaSuccess) return err;
-        ++nl;
+        const int nq = std::min(B - qb0 * UM_BM, nqb * UM_BM);
+        dense_umma_select_kernel<<<nq, SELK_THREADS, SELK_CAP * 8, st>>>(lists, counts, gthr, plan.n_chunks, B, qb0, nqb,
+                                                                        k_sel, cand);
+        if ((err = cudaGetLastError()) != cudaSuccess) return err;
+        nl += 2;
     }
     if (launches) *launches = nl;
     return cudaSuccess;

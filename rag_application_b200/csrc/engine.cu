@@ -187,45 +187,41 @@ void dense_topk_dev(brag_engine* e, DenseSpace& s, const float* Q, int B, int k,
     float* qs = e->qs.as<float>((size_t)B * s.d);
     uint64_t* cand = e->keys1.as<uint64_t>((size_t)B * k_sel);
     uint64_t* cand2 = e->keys2.as<uint64_t>((size_t)B * k_sel);
-    int P = 0;
-    uint64_t* part = nullptr;
     {
         StageTimer t(e, 0, st);
         if (path == 1) {
+            // tcgen05 scan; the per-query selection is part of the scan (no partial lists to merge)
             brag::UmmaPlan plan;
             CK(brag::dense_umma_plan(s.n, s.d, B, k_sel, e->num_sms, &plan));
             const int Bpad = plan.n_qblocks * 128;
             void* q16 = e->q16.ensure((size_t)Bpad * s.d * 2);
             CK(brag::round_queries(Q, B, s.d, s.dtype, qs, q16, Bpad, st));
             CK(brag::make_tmap_2d(e->tmap_q, q16, Bpad, s.d, 128));
-            P = plan.n_lists;
-            part = e->part.as<uint64_t>((size_t)P * B * k_sel);
             void* scratch = e->umma_scratch.ensure(plan.scratch_bytes);
             int launches = 0;
-            CK(brag::dense_umma_scan(s.x, s.dtype, s.n, s.d, q16, B, mask, k_sel, part, scratch, plan, s.tmap_x,
+            CK(brag::dense_umma_scan(s.x, s.dtype, s.n, s.d, q16, B, mask, k_sel, cand, scratch, plan, s.tmap_x,
                                      e->tmap_q, st, &launches));
             e->kernel_launches += 1 + launches;
         } else {
             CK(brag::round_queries(Q, B, s.d, s.dtype, qs, nullptr, B, st));
             const int64_t ngroups = (s.n + 31) / 32;
             int grid = (int)std::min<int64_t>((int64_t)e->num_sms * 2, std::max<int64_t>(1, (ngroups + 15) / 16));
-            P = grid;
-            part = e->part.as<uint64_t>((size_t)P * B * k_sel);
+            const int P = grid;
+            uint64_t* part = e->part.as<uint64_t>((size_t)P * B * k_sel);
             int launches = 0;
             CK(brag::dense_gemv_scan(s.x, s.dtype, s.n, s.d, qs, B, mask, k_sel, part, grid, st, &launches));
+            size_t tmp = brag::merge_tmp_elems(P, B, k_sel);
+            uint64_t* ta = e->tmp_a.as<uint64_t>(tmp);
+            uint64_t* tb = e->tmp_b.as<uint64_t>(tmp);
+            CK(brag::merge_key_lists(part, P, B, k_sel, ta, tb, cand, k_sel, st, &launches));
             e->kernel_launches += 1 + launches;
         }
     }
     {
         StageTimer t(e, 1, st);
-        size_t tmp = brag::merge_tmp_elems(P, B, k_sel);
-        uint64_t* ta = e->tmp_a.as<uint64_t>(tmp);
-        uint64_t* tb = e->tmp_b.as<uint64_t>(tmp);
-        int launches = 0;
-        CK(brag::merge_key_lists(part, P, B, k_sel, ta, tb, cand, k_sel, st, &launches));
         CK(brag::rescore_keys(s.x, s.dtype, s.n, s.d, qs, B, cand, k_sel, cand2, st));
         CK(brag::finalize_keys(cand2, B, k_sel, k, false, e->id_offset, out_scores, out_ids, out_counts, st));
-        e->kernel_launches += launches + 2;
+        e->kernel_launches += 2;
     }
 }
 

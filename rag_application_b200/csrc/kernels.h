@@ -13,20 +13,16 @@ cudaError_t dense_gemv_scan(const void* X, int dtype, int64_t n, int d, const fl
 // ---- dense_umma.cu
 struct UmmaPlan {
     int n_qblocks;          // ceil(B / 128)
-    int n_lists;            // partial lists per query written to `part` (main chunks + optional seed list)
-    int chunks_b;           // CTAs (corpus chunks) of the main scan
-    int chunks_a;           // corpus chunks of the seeding scan (0 = no seeding)
-    int tiles_per_chunk_a;
-    int64_t seed_rows;      // rows [0, seed_rows) are covered by the seeding scan
-    size_t list_bytes, gthr_bytes, part_a_elems, merge_tmp_elems;
-    size_t scratch_bytes;   // lists | per-query bounds | seeding partials | merge temporaries
+    int n_chunks;           // persistent CTAs = corpus chunks = candidate lists per query
+    size_t list_bytes, count_bytes, gthr_bytes, coarse_bytes, fine_bytes;
+    size_t scratch_bytes;   // lists | counts | per-query bounds | coarse + fine score histograms
 };
 bool dense_umma_supported(int dtype, int d, int64_t n);
 cudaError_t dense_umma_plan(int64_t n, int d, int B, int k_sel, int num_sms, UmmaPlan* plan);
 // X16: [n, d] f16/bf16; Q16: [Bpad, d] same dtype (Bpad = n_qblocks*128, zero padded).
-// part: [plan.n_lists][B][k_sel] keys.
+// cand: [B][k_sel] keys, best first (0 = empty slot).
 cudaError_t dense_umma_scan(const void* X16, int dtype, int64_t n, int d, const void* Q16, int B,
-                            const uint32_t* mask, int k_sel, uint64_t* part, void* scratch,
+                            const uint32_t* mask, int k_sel, uint64_t* cand, void* scratch,
                             const UmmaPlan& plan, void* tmap_x, void* tmap_q, cudaStream_t st, int* launches);
 // builds a CUtensorMap (128 bytes) for a [rows, d] 16-bit row-major matrix, box = [box_rows, 64]
 cudaError_t make_tmap_2d(void* tmap_out, const void* base, int64_t rows, int d, int box_rows);
