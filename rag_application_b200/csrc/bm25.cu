@@ -6,18 +6,21 @@
 // term are not candidates.
 //
 // Roofline: HBM.  Algorithmic bytes per query = sum_t df_t * 8 B (u32 doc + f32 weight).
-// Design: warp-autonomous.  A warp owns a 2048-document sub-tile whose f64 accumulators live in
-// its private shared-memory slab (initialised to the sentinel -0.0 = "not touched"; -0.0 + p == p
+// Design: warp-autonomous.  A worker warp owns a 2048-document sub-tile whose f64 accumulators live
+// in its private shared-memory slab (initialised to the sentinel -0.0 = "not touched"; -0.0 + p == p
 // bit-for-bit, so the first add equals the oracle's 0.0 + p).  A term's postings hit unique docs,
 // so they update the slab without atomics, and terms are applied in ascending order with only
 // __syncwarp between them -- bit-reproducible.  A per-(term, sub-tile) offset table makes every
 // segment lookup O(1); the first 128 postings of term t+1 are in flight while term t is applied.
-// After the terms, the warp sweeps its slab once (LDS.128, conflict-free): a double-precision
-// prefilter against the running k-th-best threshold rejects almost everything with one compare;
-// survivors go to the warp's candidate list (bitonic compaction in shared memory when it fills).
-// Thresholds are shared between the warps of a CTA and, through global memory, between CTAs
-// working on the same query.  Work items (doc split, query) are claimed split-major so CTAs that
-// run together read the same doc range and share posting segments in L2.
+// Selection is fused into the update: every update compares the new partial sum with the query's
+// global score bound (common.cuh: per-query score histograms + a bound-manager warp per CTA), and
+// the rare documents that exceed it are recorded; since the LAST update of a document produces its
+// final score, re-reading the recorded slots after the last term finds every candidate without
+// sweeping the slab.  The slab is then reset blindly (32 STS.128 per lane).  If the record buffer
+// overflows (no bound yet) the warp falls back to a full sweep of its slab.  Candidates go to the
+// warp's shared-memory list (bitonic compaction if it ever fills) and are emitted per work item.
+// Work items (doc split, query) are claimed split-major so CTAs that run together read the same
+// doc range and share posting segments in L2.
 // Known edge: a document whose every matching product is exactly -0.0 (zero weight times a
 // negative query value) is indistinguishable from "not touched" and is not returned.
 #include "common.cuh"
@@ -25,15 +28,18 @@
 
 namespace brag {
 
-constexpr int BM_WARPS = 5;
-constexpr int BM_THREADS = BM_WARPS * 32;
+constexpr int BM_WARPS = 12;                     // worker warps (one CTA per SM); one more warp manages the bounds
+constexpr int BM_THREADS = (BM_WARPS + 1) * 32;
 constexpr int BM_HEAD = 4;       // posting chunks (x32) prefetched per term
 constexpr int BM_TG = 16;        // query terms per group
+constexpr int BM_REC = 96;       // recorded over-the-bound slots per sub-tile visit before falling back
 constexpr uint32_t BM_INVALID = 0xFFFFFFFFu;
 constexpr unsigned long long BM_SENTINEL = 0x8000000000000000ull;  // -0.0: "document not touched"
 
-// per-warp shared-memory slab: acc[BM25_SUB] f64 | list[lcap] u64 | cnt
-__host__ __device__ inline size_t bm_warp_bytes(int lcap) { return (size_t)BM25_SUB * 8 + (size_t)lcap * 8 + 16; }
+// per-warp shared-memory slab: acc[BM25_SUB] f64 | list[lcap] u64 | rec[BM_REC] u32 | cnt, nrec
+__host__ __device__ inline size_t bm_warp_bytes(int lcap) {
+    return (size_t)BM25_SUB * 8 + (size_t)lcap * 8 + (size_t)BM_REC * 4 + 16;
+}
 
 __global__ void bm25_suboff_kernel(const int64_t* __restrict__ term_ptr, const uint32_t* __restrict__ doc,
                                    int64_t V, int ns1, uint32_t* __restrict__ sub_off) {
@@ -73,59 +79,75 @@ __device__ __forceinline__ void warp_compact(uint64_t* list, int* cnt, int lcap,
     __syncwarp();
 }
 
-// float threshold -> double prefilter: any acc whose float rounding is >= thr_score is > pre
-__device__ __forceinline__ double prefilter_of(uint64_t thr) {
-    if (thr == 0ull) return -INFINITY;
-    const float t = key_score(thr);
-    return (double)nextafterf(t, -INFINITY);
-}
+// double prefilter for "float32(acc) can reach score t": any acc whose float rounding is >= t is > pre
+__device__ __forceinline__ double prefilter_of_score(float t) { return (double)nextafterf(t, -INFINITY); }
 
-__global__ void __launch_bounds__(BM_THREADS, 2)
+__device__ __forceinline__ void worker_bar() { asm volatile("bar.sync 1, %0;" ::"n"(BM_WARPS * 32) : "memory"); }
+
+__global__ void __launch_bounds__(BM_THREADS, 1)
 bm25_scan_kernel(const int64_t* __restrict__ term_ptr, const uint32_t* __restrict__ doc,
                  const float* __restrict__ w, const uint32_t* __restrict__ sub_off, int64_t V,
                  int64_t n_docs, const int32_t* __restrict__ q_ptr, const int32_t* __restrict__ q_terms,
                  const double* __restrict__ q_vals, int B, const uint32_t* __restrict__ mask, int k_sel,
                  int lcap, uint64_t* __restrict__ part, int splits, int* __restrict__ work_counter,
-                 unsigned long long* __restrict__ g_thr) {
+                 uint32_t* __restrict__ gthr, uint32_t* __restrict__ coarse, uint32_t* __restrict__ fine) {
     extern __shared__ __align__(16) uint8_t smem_raw[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    __shared__ int s_item;
+    __shared__ int s_done;
+    if (threadIdx.x == 0) s_done = 0;
+    __syncthreads();
+
+    if (warp == BM_WARPS) {
+        // ===== bound manager: queries blockIdx.x, blockIdx.x + gridDim.x, ...
+        while (true) {
+            const int done = *reinterpret_cast<volatile int*>(&s_done);
+            for (int q = (int)blockIdx.x; q < B; q += (int)gridDim.x) {
+                const uint32_t bound = hist_bound(coarse, fine, q, (uint32_t)k_sel, lane);
+                if (lane == 0 && bound != 0u) atomicMax(gthr + q, bound);
+            }
+            if (done) break;
+            __nanosleep(20000);
+        }
+        return;
+    }
+
     uint8_t* slab = smem_raw + (size_t)warp * bm_warp_bytes(lcap);
     double* acc = reinterpret_cast<double*>(slab);
     uint64_t* list = reinterpret_cast<uint64_t*>(slab + (size_t)BM25_SUB * 8);
-    int* cntp = reinterpret_cast<int*>(slab + (size_t)BM25_SUB * 8 + (size_t)lcap * 8);
-    __shared__ int s_item;
-    __shared__ unsigned long long s_cta_thr;
+    uint32_t* rec = reinterpret_cast<uint32_t*>(slab + (size_t)BM25_SUB * 8 + (size_t)lcap * 8);
+    int* cntp = reinterpret_cast<int*>(slab + (size_t)BM25_SUB * 8 + (size_t)lcap * 8 + (size_t)BM_REC * 4);
+    int* nrecp = cntp + 1;
     const int ns = (int)((n_docs + BM25_SUB - 1) / BM25_SUB);
     const int ns1 = ns + 1;
     const int ns_per_split = (ns + splits - 1) / splits;
     const int n_items = splits * B;
     const double sentinel = __longlong_as_double((long long)BM_SENTINEL);
+    const double2 sent2 = make_double2(sentinel, sentinel);
 
     for (int i = lane; i < BM25_SUB; i += 32) acc[i] = sentinel;
+    if (lane == 0) *nrecp = 0;
     __syncwarp();
 
     while (true) {
-        __syncthreads();
-        if (threadIdx.x == 0) { s_item = atomicAdd(work_counter, 1); s_cta_thr = 0ull; }
-        __syncthreads();
+        worker_bar();
+        if (threadIdx.x == 0) s_item = atomicAdd(work_counter, 1);
+        worker_bar();
         const int item = s_item;
         if (item >= n_items) break;
         const int split = item / B, q = item - split * B;
         const int qb = q_ptr[q], qe = q_ptr[q + 1];
         const int j_begin = split * ns_per_split, j_end = min(ns, j_begin + ns_per_split);
-        uint64_t thr = __ldcg(g_thr + q);
-        double pre = prefilter_of(thr);
+        uint64_t thr = 0ull;              // local: k_sel-th best key of this warp's list after a compaction
+        double pre_local = -INFINITY;
         if (lane == 0) *cntp = 0;
         __syncwarp();
 
-        int iter = 0;
-        for (int j = j_begin + warp; j < j_end; j += BM_WARPS, ++iter) {
+        for (int j = j_begin + warp; j < j_end; j += BM_WARPS) {
             const uint32_t sub_base = (uint32_t)j * BM25_SUB;
-            {   // adopt a tighter bound found by sibling warps (same query) or other CTAs
-                uint64_t t = s_cta_thr;
-                if ((iter & 15) == 15) t = max(t, (uint64_t)__ldcg(g_thr + q));
-                if (t > thr) { thr = t; pre = prefilter_of(thr); }
-            }
+            // the query's global bound: k_sel-th best score over everything any warp has pushed so far
+            const uint32_t g = __ldcg(gthr + q);
+            const double pre = (g != 0u) ? fmax(pre_local, prefilter_of_score(ordered_f32(g))) : pre_local;
             bool any = false;
             for (int tg = qb; tg < qe; tg += BM_TG) {
                 const int nq = min(BM_TG, qe - tg);
@@ -146,96 +168,132 @@ bm25_scan_kernel(const int64_t* __restrict__ term_ptr, const uint32_t* __restric
                 if (!__any_sync(0xFFFFFFFFu, n != 0)) continue;
                 any = true;
 
-                // ---- terms in ascending order; head of term t+1 is in flight while term t is applied
-                uint32_t hd[BM_HEAD], nd[BM_HEAD];
-                float hw[BM_HEAD], nw[BM_HEAD];
-                auto load_head = [&](int64_t b_t, uint32_t n_t, uint32_t (&d)[BM_HEAD], float (&ww)[BM_HEAD]) {
+                // ---- the group's postings as one stream of 128-posting pieces, terms in ascending order;
+                //      two pieces are always in flight ahead of the one being applied
+                struct Piece { uint32_t d[BM_HEAD]; float w[BM_HEAD]; double qv; bool last; };
+                int ft = 0;            // fetch cursor: term index inside the group, posting offset in its segment
+                uint32_t fi = 0;
+                auto fetch = [&](Piece& P) -> bool {
+                    uint32_t n_t = 0;
+                    while (ft < nq) {                       // warp-uniform
+                        n_t = __shfl_sync(0xFFFFFFFFu, n, ft);
+                        if (fi < n_t) break;
+                        ++ft;
+                        fi = 0;
+                    }
+                    if (ft >= nq) return false;
+                    const int64_t b_t = __shfl_sync(0xFFFFFFFFu, base, ft);
+                    P.qv = __shfl_sync(0xFFFFFFFFu, qv, ft);
 #pragma unroll
                     for (int u = 0; u < BM_HEAD; ++u) {
-                        const uint32_t idx = (uint32_t)u * 32u + lane;
-                        d[u] = BM_INVALID;
-                        ww[u] = 0.0f;
-                        if (idx < n_t) { d[u] = __ldg(doc + b_t + idx); ww[u] = __ldg(w + b_t + idx); }
+                        const uint32_t idx = fi + (uint32_t)u * 32u + lane;
+                        P.d[u] = BM_INVALID;
+                        P.w[u] = 0.0f;
+                        if (idx < n_t) { P.d[u] = __ldg(doc + b_t + idx); P.w[u] = __ldg(w + b_t + idx); }
                     }
+                    fi += BM_HEAD * 32u;
+                    P.last = fi >= n_t;                     // next piece belongs to another term
+                    if (P.last) { ++ft; fi = 0; }
+                    return true;
                 };
                 auto apply = [&](uint32_t d, float ww, double qv_t) {
                     if (d != BM_INVALID) {
                         const uint32_t dl = d - sub_base;
-                        acc[dl] = __dadd_rn(acc[dl], __dmul_rn(qv_t, (double)ww));   // -0.0 + p == p
+                        const double nv = __dadd_rn(acc[dl], __dmul_rn(qv_t, (double)ww));   // -0.0 + p == p
+                        acc[dl] = nv;
+                        if (nv > pre) {                       // rare once the bound is warm
+                            const int pos = atomicAdd(nrecp, 1);
+                            if (pos < BM_REC) rec[pos] = dl;
+                        }
                     }
                 };
-                int64_t b_t = __shfl_sync(0xFFFFFFFFu, base, 0);
-                uint32_t n_t = __shfl_sync(0xFFFFFFFFu, n, 0);
-                load_head(b_t, n_t, hd, hw);
+                Piece p0, p1, p2;
+                bool v0 = fetch(p0);
+                bool v1 = v0 && fetch(p1);
+                bool v2 = v1 && fetch(p2);
 #pragma unroll 1
-                for (int t = 0; t < nq; ++t) {
-                    const double qv_t = __shfl_sync(0xFFFFFFFFu, qv, t);
-                    const int64_t b_n = __shfl_sync(0xFFFFFFFFu, base, (t + 1) & 31);
-                    const uint32_t n_n = (t + 1 < nq) ? __shfl_sync(0xFFFFFFFFu, n, (t + 1) & 31) : 0u;
-                    load_head(b_n, n_n, nd, nw);
+                while (v0) {
 #pragma unroll
-                    for (int u = 0; u < BM_HEAD; ++u) apply(hd[u], hw[u], qv_t);
-                    // tail of a long segment: BM_HEAD chunks per trip, loads batched ahead of the updates
-                    for (uint32_t i0 = BM_HEAD * 32u; i0 < n_t; i0 += BM_HEAD * 32u) {
-                        uint32_t td[BM_HEAD];
-                        float tw[BM_HEAD];
-#pragma unroll
-                        for (int u = 0; u < BM_HEAD; ++u) {
-                            const uint32_t idx = i0 + (uint32_t)u * 32u + lane;
-                            td[u] = BM_INVALID;
-                            tw[u] = 0.0f;
-                            if (idx < n_t) { td[u] = __ldg(doc + b_t + idx); tw[u] = __ldg(w + b_t + idx); }
-                        }
-#pragma unroll
-                        for (int u = 0; u < BM_HEAD; ++u) apply(td[u], tw[u], qv_t);
-                    }
-                    __syncwarp();   // this term's updates are visible before the next term's
-#pragma unroll
-                    for (int u = 0; u < BM_HEAD; ++u) { hd[u] = nd[u]; hw[u] = nw[u]; }
-                    b_t = b_n;
-                    n_t = n_n;
+                    for (int u = 0; u < BM_HEAD; ++u) apply(p0.d[u], p0.w[u], p0.qv);
+                    if (p0.last) __syncwarp();   // a term's updates are visible before the next term's
+                    p0 = p1; v0 = v1;
+                    p1 = p2; v1 = v2;
+                    v2 = v1 && fetch(p2);
                 }
             }
             if (!any) continue;
-
-            // ---- scan the sub-tile: prefilter against the running threshold, push survivors, reset
-#pragma unroll 1
-            for (int it = 0; it < BM25_SUB / 64; ++it) {
-                if (*cntp > lcap - 64) { warp_compact(list, cntp, lcap, k_sel, thr, lane); pre = prefilter_of(thr);
-                                         if (lane == 0) atomicMax(&s_cta_thr, (unsigned long long)thr); }
-                const int d0 = it * 64 + lane * 2;
-                const double2 v = *reinterpret_cast<const double2*>(acc + d0);
-                *reinterpret_cast<double2*>(acc + d0) = make_double2(sentinel, sentinel);
-                if (v.x > pre || v.y > pre) {
-#pragma unroll
-                    for (int h = 0; h < 2; ++h) {
-                        const double a = h ? v.y : v.x;
-                        if (a > pre && (unsigned long long)__double_as_longlong(a) != BM_SENTINEL) {
-                            const uint32_t dg = sub_base + d0 + h;
-                            if (mask_test(mask, dg)) {
-                                const uint64_t key = make_key((float)a, dg);
-                                if (key > thr) list[atomicAdd(cntp, 1)] = key;
-                            }
-                        }
+            // ---- selection: re-read the recorded slots (their last update left the final score there)
+            const int nrec = *nrecp;
+            double pre_eff = pre;
+            auto push = [&](double a, uint32_t dl) {
+                const uint32_t dg = sub_base + dl;
+                if (mask_test(mask, dg)) {
+                    const uint64_t key = make_key((float)a, dg);
+                    if (key > thr && (uint32_t)(key >> 32) >= g) {
+                        list[atomicAdd(cntp, 1)] = key;
+                        hist_count(coarse, fine, q, (uint32_t)(key >> 32));
                     }
                 }
-                __syncwarp();
+            };
+            if (nrec > BM_REC) {
+                // no useful bound yet (or a flood of ties): sweep the whole slab once, resetting as we go
+#pragma unroll 1
+                for (int it = 0; it < BM25_SUB / 64; ++it) {
+                    if (*cntp > lcap - 64) {
+                        warp_compact(list, cntp, lcap, k_sel, thr, lane);
+                        if (thr != 0ull) { pre_local = prefilter_of_score(key_score(thr)); pre_eff = fmax(pre_eff, pre_local); }
+                    }
+                    const int d0 = it * 64 + lane * 2;
+                    const double2 v = *reinterpret_cast<const double2*>(acc + d0);
+                    *reinterpret_cast<double2*>(acc + d0) = sent2;
+                    if (v.x > pre_eff || v.y > pre_eff) {
+#pragma unroll
+                        for (int h = 0; h < 2; ++h) {
+                            const double a = h ? v.y : v.x;
+                            if (a > pre_eff && (unsigned long long)__double_as_longlong(a) != BM_SENTINEL) push(a, d0 + h);
+                        }
+                    }
+                    __syncwarp();
+                }
+            } else {
+                if (nrec > 0) {
+                    if (*cntp > lcap - BM_REC) {
+                        warp_compact(list, cntp, lcap, k_sel, thr, lane);
+                        if (thr != 0ull) { pre_local = prefilter_of_score(key_score(thr)); pre_eff = fmax(pre_eff, pre_local); }
+                    }
+                    for (int i = lane; i < nrec; i += 32) {
+                        const uint32_t dl = rec[i];
+                        // a slot may be recorded several times: whoever swaps the sentinel in owns it
+                        const unsigned long long old =
+                            atomicExch(reinterpret_cast<unsigned long long*>(acc + dl), BM_SENTINEL);
+                        if (old != BM_SENTINEL) {
+                            const double a = __longlong_as_double((long long)old);
+                            if (a > pre_eff) push(a, dl);
+                        }
+                    }
+                    __syncwarp();
+                }
+                double2* acc2 = reinterpret_cast<double2*>(acc);
+#pragma unroll 8
+                for (int i = lane; i < BM25_SUB / 2; i += 32) acc2[i] = sent2;
             }
+            if (lane == 0) *nrecp = 0;
+            __syncwarp();
         }
         // ---- emit this warp's list for (split, warp, q)
         warp_compact(list, cntp, lcap, k_sel, thr, lane);
-        if (lane == 0 && thr != 0ull) atomicMax(g_thr + q, (unsigned long long)thr);
         uint64_t* out = part + ((size_t)(split * BM_WARPS + warp) * B + q) * k_sel;
         for (int i = lane; i < k_sel; i += 32) out[i] = list[i];
         __syncwarp();
     }
+    if (threadIdx.x == 0) *reinterpret_cast<volatile int*>(&s_done) = 1;
 }
 
 Bm25Plan bm25_plan(int64_t n_docs, int B, int num_sms) {
     Bm25Plan p;
     const int ns = (int)((n_docs + BM25_SUB - 1) / BM25_SUB);
-    const int resident = num_sms * 2;
-    // enough items for ~8 claims per resident CTA, but never more splits than sub-tile quads
+    const int resident = num_sms;
+    // enough items for ~8 claims per resident CTA, but never more splits than sub-tile groups
     int splits = (resident * 8 + B - 1) / B;
     int max_splits = (ns + BM_WARPS - 1) / BM_WARPS;
     if (splits > max_splits) splits = max_splits;
@@ -245,31 +303,43 @@ Bm25Plan bm25_plan(int64_t n_docs, int B, int num_sms) {
     p.lists_per_query = splits * BM_WARPS;
     int64_t items = (int64_t)splits * B;
     p.grid = (int)(items < resident ? items : resident);
+    auto up = [](size_t x) { return (x + 255) & ~(size_t)255; };
+    p.gthr_bytes = up((size_t)B * sizeof(uint32_t));
+    p.coarse_bytes = up((size_t)B * HIST_COARSE_BINS * sizeof(uint32_t));
+    p.fine_bytes = up((size_t)B * HIST_FINE_BINS * sizeof(uint32_t));
+    p.scratch_bytes = 256 + p.gthr_bytes + p.coarse_bytes + p.fine_bytes;   // work counter | bounds | histograms
     return p;
 }
 
 cudaError_t bm25_scan(const int64_t* term_ptr, const uint32_t* doc, const float* w, const uint32_t* sub_off,
                       int64_t V, int64_t n_docs, const int32_t* q_ptr, const int32_t* q_terms,
                       const double* q_vals, int B, const uint32_t* mask, int k_sel, uint64_t* part,
-                      const Bm25Plan& plan, int* work_counter, unsigned long long* g_thr, cudaStream_t st) {
+                      const Bm25Plan& plan, void* scratch, cudaStream_t st) {
     if (k_sel > 512) return cudaErrorInvalidValue;
     int lcap = 256;
-    while (lcap < 2 * k_sel || lcap - 64 < k_sel + 64) lcap <<= 1;   // room for k_sel kept + 64 pushes per scan trip
+    while (lcap < k_sel + BM_REC) lcap <<= 1;   // k_sel kept after a compaction + one visit's pushes (<= BM_REC)
     const size_t smem = bm_warp_bytes(lcap) * BM_WARPS;
     static size_t attr_smem = 0;
     if (smem > attr_smem) {
         cudaError_t e = cudaFuncSetAttribute(bm25_scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              (int)smem);
         if (e != cudaSuccess) return e;
+        // two CTAs per SM need the largest shared-memory carve-out; the default heuristic sizes it for one
+        e = cudaFuncSetAttribute(bm25_scan_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                 cudaSharedmemCarveoutMaxShared);
+        if (e != cudaSuccess) return e;
         attr_smem = smem;
     }
-    cudaError_t e = cudaMemsetAsync(work_counter, 0, sizeof(int), st);
-    if (e != cudaSuccess) return e;
-    e = cudaMemsetAsync(g_thr, 0, (size_t)B * sizeof(unsigned long long), st);
+    uint8_t* sp = reinterpret_cast<uint8_t*>(scratch);
+    int* work_counter = reinterpret_cast<int*>(sp);
+    uint32_t* gthr = reinterpret_cast<uint32_t*>(sp + 256);
+    uint32_t* coarse = reinterpret_cast<uint32_t*>(sp + 256 + plan.gthr_bytes);
+    uint32_t* fine = reinterpret_cast<uint32_t*>(sp + 256 + plan.gthr_bytes + plan.coarse_bytes);
+    cudaError_t e = cudaMemsetAsync(scratch, 0, plan.scratch_bytes, st);
     if (e != cudaSuccess) return e;
     bm25_scan_kernel<<<plan.grid, BM_THREADS, smem, st>>>(term_ptr, doc, w, sub_off, V, n_docs, q_ptr, q_terms,
                                                           q_vals, B, mask, k_sel, lcap, part, plan.splits,
-                                                          work_counter, g_thr);
+                                                          work_counter, gthr, coarse, fine);
     return cudaGetLastError();
 }
 

@@ -25,6 +25,73 @@ __device__ __forceinline__ uint64_t make_key(float s, uint32_t row) {
 __device__ __forceinline__ float key_score(uint64_t k) { return ordered_f32((uint32_t)(k >> 32)); }
 __device__ __forceinline__ uint32_t key_row(uint64_t k) { return 0xFFFFFFFFu - (uint32_t)k; }
 
+// ---------------------------------------------------------------- global score bounds
+// Every scan keeps, per query, a histogram of the scores it has pushed as candidates, over the
+// order-preserving uint32 image of the float score: coarse bin = top 7 bits, fine bin = top 14
+// bits (sign + exponent + 5 mantissa bits, ~3 % wide).  Each counted entry is a distinct corpus
+// row, so "at least k rows counted in bins >= e" proves that the k-th best score is >= edge(e):
+// that edge is published as the query's bound (f32_ordered units, 0 = none) and candidates
+// below it are dropped by every CTA.  The bound only ever rises.
+constexpr int HIST_FINE_SHIFT = 18;
+constexpr int HIST_FINE_BINS = 1 << (32 - HIST_FINE_SHIFT);        // 16384
+constexpr int HIST_COARSE_SHIFT = 25;
+constexpr int HIST_COARSE_BINS = 1 << (32 - HIST_COARSE_SHIFT);    // 128
+constexpr int HIST_FINE_PER_COARSE = HIST_FINE_BINS / HIST_COARSE_BINS;  // 128
+
+__device__ __forceinline__ void hist_count(uint32_t* __restrict__ coarse, uint32_t* __restrict__ fine, int q,
+                                           uint32_t ord) {
+    atomicAdd(fine + (size_t)q * HIST_FINE_BINS + (ord >> HIST_FINE_SHIFT), 1u);
+    atomicAdd(coarse + (size_t)q * HIST_COARSE_BINS + (ord >> HIST_COARSE_SHIFT), 1u);
+}
+
+// inclusive suffix sum over lanes >= lane
+__device__ __forceinline__ uint32_t warp_suffix_sum(uint32_t v, int lane) {
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+        const uint32_t o = __shfl_down_sync(0xFFFFFFFFu, v, off);
+        if (lane + off < 32) v += o;
+    }
+    return v;
+}
+
+// Whole warp: highest histogram edge that at least k counted rows reach (0 = fewer than k counted).
+// Counts are read with ld.cg while other CTAs keep adding, so the result is a valid, possibly
+// slightly stale bound.
+__device__ __forceinline__ uint32_t hist_bound(const uint32_t* __restrict__ coarse, const uint32_t* __restrict__ fine,
+                                               int q, uint32_t k, int lane) {
+    const uint4 c4 = __ldcg(reinterpret_cast<const uint4*>(coarse + (size_t)q * HIST_COARSE_BINS) + lane);
+    const uint32_t own = c4.x + c4.y + c4.z + c4.w;     // lane l owns coarse bins 4l .. 4l+3
+    const uint32_t suf = warp_suffix_sum(own, lane);
+    const unsigned has = __ballot_sync(0xFFFFFFFFu, suf >= k);
+    if (has == 0u) return 0u;
+    const int L = 31 - __clz(has);
+    const uint32_t al = __shfl_sync(0xFFFFFFFFu, suf - own, L);     // rows in lanes above L
+    const uint32_t y = __shfl_sync(0xFFFFFFFFu, c4.y, L), z = __shfl_sync(0xFFFFFFFFu, c4.z, L),
+                   w = __shfl_sync(0xFFFFFFFFu, c4.w, L);
+    int cb;
+    uint32_t above;                                                  // rows in coarse bins above cb
+    if (al + w >= k) { cb = 4 * L + 3; above = al; }
+    else if (al + w + z >= k) { cb = 4 * L + 2; above = al + w; }
+    else if (al + w + z + y >= k) { cb = 4 * L + 1; above = al + w + z; }
+    else { cb = 4 * L; above = al + w + z + y; }
+    const uint4 f4 = __ldcg(reinterpret_cast<const uint4*>(fine + (size_t)q * HIST_FINE_BINS +
+                                                          (size_t)cb * HIST_FINE_PER_COARSE) + lane);
+    const uint32_t fown = f4.x + f4.y + f4.z + f4.w;
+    const uint32_t fsuf = warp_suffix_sum(fown, lane);
+    const unsigned fhas = __ballot_sync(0xFFFFFFFFu, above + fsuf >= k);
+    if (fhas == 0u) return (uint32_t)cb << HIST_COARSE_SHIFT;        // fine counts lag: the coarse edge holds
+    const int FL = 31 - __clz(fhas);
+    const uint32_t fa = above + __shfl_sync(0xFFFFFFFFu, fsuf - fown, FL);
+    const uint32_t fy = __shfl_sync(0xFFFFFFFFu, f4.y, FL), fz = __shfl_sync(0xFFFFFFFFu, f4.z, FL),
+                   fw = __shfl_sync(0xFFFFFFFFu, f4.w, FL);
+    int fb;
+    if (fa + fw >= k) fb = 3;
+    else if (fa + fw + fz >= k) fb = 2;
+    else if (fa + fw + fz + fy >= k) fb = 1;
+    else fb = 0;
+    return (uint32_t)(cb * HIST_FINE_PER_COARSE + 4 * FL + fb) << HIST_FINE_SHIFT;
+}
+
 // ---------------------------------------------------------------- bitonic sort (descending)
 // n must be a power of two; all `nthreads` threads of the group call it; `sync` is
 // __syncthreads for a CTA-wide sort or __syncwarp for a warp-private one.

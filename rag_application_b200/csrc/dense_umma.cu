@@ -39,13 +39,6 @@ constexpr int UM_A_BYTES = UM_BM * UM_BK * 2;  // 16 KB
 constexpr int UM_B_BYTES = UM_BN * UM_BK * 2;  // 32 KB
 constexpr uint32_t UM_TMEM_COLS = 512;
 constexpr int UM_MAXQB = 8;            // query blocks (x128 queries) one launch covers
-// score histogram per query over the order-preserving uint32 image of the float score:
-// coarse bin = top 7 bits, fine bin = top 14 bits (sign + exponent + 5 mantissa bits, ~3 % wide)
-constexpr int UM_FINE_SHIFT = 18;
-constexpr int UM_FINE_BINS = 1 << (32 - UM_FINE_SHIFT);      // 16384
-constexpr int UM_COARSE_SHIFT = 25;
-constexpr int UM_COARSE_BINS = 1 << (32 - UM_COARSE_SHIFT);  // 128
-constexpr int UM_FINE_PER_COARSE = UM_FINE_BINS / UM_COARSE_BINS;  // 128
 constexpr int UM_SEL_CAP = 4096;       // keys per CTA sort in the final per-query selection
 
 struct UmSmem {
@@ -182,7 +175,7 @@ __device__ __forceinline__ void um_compact(unsigned bal, uint64_t* my_list, uint
 // ------------------------------------------------------------------ the kernel
 // lists  : [grid][n_qblocks][128][UM_CAP] keys (unsorted), counts: [grid][B] entries used
 // gthr   : [B] order-preserving uint32 score bounds (0 = none yet)
-// coarse : [B][UM_COARSE_BINS], fine: [B][UM_FINE_BINS] row counts per score bin
+// coarse : [B][HIST_COARSE_BINS], fine: [B][HIST_FINE_BINS] row counts per score bin
 __global__ void __launch_bounds__(UM_THREADS, 1)
 dense_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_x,
                   int64_t n, int d, int B, int qb_base, int n_qblocks, int64_t rows_per_chunk,
@@ -267,55 +260,7 @@ dense_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
         while (true) {
             const int done = *reinterpret_cast<volatile int*>(&S.epi_done);
             for (int q = q_lo + (int)blockIdx.x; q < q_hi; q += (int)gridDim.x) {
-                // coarse suffix counts from the top: lane l owns coarse bins 4l..4l+3
-                const uint4 c4 = __ldcg(reinterpret_cast<const uint4*>(coarse + (size_t)q * UM_COARSE_BINS) + lane);
-                uint32_t own = c4.x + c4.y + c4.z + c4.w;
-                uint32_t suf = own;                                  // inclusive suffix over lanes >= l
-#pragma unroll
-                for (int off = 1; off < 32; off <<= 1) {
-                    const uint32_t o = __shfl_down_sync(0xFFFFFFFFu, suf, off);
-                    if (lane + off < 32) suf += o;
-                }
-                const unsigned has = __ballot_sync(0xFFFFFFFFu, suf >= (uint32_t)k_sel);
-                if (has == 0u) continue;                              // fewer than k_sel rows seen so far
-                const int L = 31 - __clz(has);                        // highest lane whose suffix reaches k_sel
-                const uint32_t above_lane = __shfl_sync(0xFFFFFFFFu, suf - own, L);   // rows in lanes > L
-                const uint32_t x = __shfl_sync(0xFFFFFFFFu, c4.x, L), y = __shfl_sync(0xFFFFFFFFu, c4.y, L),
-                               z = __shfl_sync(0xFFFFFFFFu, c4.z, L), w = __shfl_sync(0xFFFFFFFFu, c4.w, L);
-                int cb;
-                uint32_t above;                                       // rows in coarse bins > cb
-                if (above_lane + w >= (uint32_t)k_sel) { cb = 4 * L + 3; above = above_lane; }
-                else if (above_lane + w + z >= (uint32_t)k_sel) { cb = 4 * L + 2; above = above_lane + w; }
-                else if (above_lane + w + z + y >= (uint32_t)k_sel) { cb = 4 * L + 1; above = above_lane + w + z; }
-                else { cb = 4 * L; above = above_lane + w + z + y; }
-                (void)x;
-                // fine bins inside coarse bin cb
-                const uint4 f4 = __ldcg(reinterpret_cast<const uint4*>(fine + (size_t)q * UM_FINE_BINS +
-                                                                      (size_t)cb * UM_FINE_PER_COARSE) + lane);
-                const uint32_t fown = f4.x + f4.y + f4.z + f4.w;
-                uint32_t fsuf = fown;
-#pragma unroll
-                for (int off = 1; off < 32; off <<= 1) {
-                    const uint32_t o = __shfl_down_sync(0xFFFFFFFFu, fsuf, off);
-                    if (lane + off < 32) fsuf += o;
-                }
-                const unsigned fhas = __ballot_sync(0xFFFFFFFFu, above + fsuf >= (uint32_t)k_sel);
-                uint32_t bound;
-                if (fhas == 0u) {
-                    bound = (uint32_t)cb << UM_COARSE_SHIFT;          // fine counts lag: the coarse edge is still valid
-                } else {
-                    const int FL = 31 - __clz(fhas);
-                    const uint32_t fa = above + __shfl_sync(0xFFFFFFFFu, fsuf - fown, FL);
-                    const uint32_t fx = __shfl_sync(0xFFFFFFFFu, f4.x, FL), fy = __shfl_sync(0xFFFFFFFFu, f4.y, FL),
-                                   fz = __shfl_sync(0xFFFFFFFFu, f4.z, FL), fw = __shfl_sync(0xFFFFFFFFu, f4.w, FL);
-                    int fb;
-                    if (fa + fw >= (uint32_t)k_sel) fb = 3;
-                    else if (fa + fw + fz >= (uint32_t)k_sel) fb = 2;
-                    else if (fa + fw + fz + fy >= (uint32_t)k_sel) fb = 1;
-                    else fb = 0;
-                    (void)fx;
-                    bound = (uint32_t)(cb * UM_FINE_PER_COARSE + 4 * FL + fb) << UM_FINE_SHIFT;
-                }
+                const uint32_t bound = hist_bound(coarse, fine, q, (uint32_t)k_sel, lane);
                 if (lane == 0 && bound != 0u) atomicMax(gthr + q, bound);
             }
             if (done >= 4) break;
@@ -340,8 +285,6 @@ dense_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
                 const int b = (qb_base + qb) * UM_BM + qidx;
                 const bool q_valid = b < B;
                 uint64_t* my_list = lists + (((size_t)chunk * n_qblocks + qb) * UM_BM + qidx) * UM_CAP;
-                uint32_t* my_fine = fine + (size_t)(q_valid ? b : 0) * UM_FINE_BINS;
-                uint32_t* my_coarse = coarse + (size_t)(q_valid ? b : 0) * UM_COARSE_BINS;
                 float thr = S.thr[qb][qidx];
                 int cnt = S.cnt[qb][qidx];
                 // the query's global bound (k_sel-th best score over all rows scanned so far by any CTA,
@@ -367,9 +310,7 @@ dense_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
                                 const uint64_t key = make_key(s, (uint32_t)row);
                                 __stcg(my_list + cnt, key);
                                 ++cnt;
-                                const uint32_t o = (uint32_t)(key >> 32);
-                                atomicAdd(my_fine + (o >> UM_FINE_SHIFT), 1u);
-                                atomicAdd(my_coarse + (o >> UM_COARSE_SHIFT), 1u);
+                                hist_count(coarse, fine, b, (uint32_t)(key >> 32));
                             }
                         }
                     }
@@ -478,8 +419,8 @@ cudaError_t dense_umma_plan(int64_t n, int d, int B, int k_sel, int num_sms, Umm
     plan->list_bytes = up((size_t)plan->n_chunks * qb_launch * UM_BM * UM_CAP * sizeof(uint64_t));
     plan->count_bytes = up((size_t)plan->n_chunks * B * sizeof(int));
     plan->gthr_bytes = up((size_t)B * sizeof(uint32_t));
-    plan->coarse_bytes = up((size_t)B * UM_COARSE_BINS * sizeof(uint32_t));
-    plan->fine_bytes = up((size_t)B * UM_FINE_BINS * sizeof(uint32_t));
+    plan->coarse_bytes = up((size_t)B * HIST_COARSE_BINS * sizeof(uint32_t));
+    plan->fine_bytes = up((size_t)B * HIST_FINE_BINS * sizeof(uint32_t));
     plan->scratch_bytes = plan->list_bytes + plan->count_bytes + plan->gthr_bytes + plan->coarse_bytes + plan->fine_bytes;
     return cudaSuccess;
 }

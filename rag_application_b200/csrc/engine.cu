@@ -246,12 +246,11 @@ void sparse_topk_dev(brag_engine* e, SparseSpace& s, const int32_t* q_ptr, const
     const int P = plan.lists_per_query;
     uint64_t* part = e->part.as<uint64_t>((size_t)P * B * k);
     uint64_t* merged = e->keys1.as<uint64_t>((size_t)B * k);
-    int* wc = e->work_counter.as<int>(1);
-    unsigned long long* gthr = e->g_thr.as<unsigned long long>(B);
+    void* scratch = e->g_thr.ensure(plan.scratch_bytes);
     {
         StageTimer t(e, 2, st);
         CK(brag::bm25_scan(s.term_ptr, s.doc, s.w, s.sub_off, s.V, s.n_docs, q_ptr, q_terms, q_vals, B, mask, k,
-                           part, plan, wc, gthr, st));
+                           part, plan, scratch, st));
         e->kernel_launches += 1;
     }
     {
