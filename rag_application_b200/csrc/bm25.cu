@@ -23,25 +23,41 @@
 // doc range and share posting segments in L2.
 // Known edge: a document whose every matching product is exactly -0.0 (zero weight times a
 // negative query value) is indistinguishable from "not touched" and is not returned.
+#include <algorithm>
+
 #include "common.cuh"
 #include "kernels.h"
 
 namespace brag {
 
-constexpr int BM_WARPS = 12;                     // worker warps (one CTA per SM); one more warp manages the bounds
+constexpr int BM_WARPS = 12;                     // max worker warps (one CTA per SM); one more warp manages the bounds
 constexpr int BM_THREADS = (BM_WARPS + 1) * 32;
+constexpr size_t BM_SMEM_MAX = 232448 - 64;      // opt-in shared memory per CTA on sm_100
 constexpr int BM_HEAD = 4;       // posting chunks (x32) prefetched per term
 constexpr int BM_TG = 16;        // query terms per group
 constexpr int BM_REC = 96;       // recorded over-the-bound slots per sub-tile visit before falling back
 constexpr uint32_t BM_INVALID = 0xFFFFFFFFu;
 constexpr unsigned long long BM_SENTINEL = 0x8000000000000000ull;  // -0.0: "document not touched"
 
-// per-warp shared-memory slab: acc[BM25_SUB] f64 | list[lcap] u64 | rec[BM_REC] u32 | cnt, nrec
+constexpr int BM_ACC = BM25_SUB + 32;   // + one dummy slot per lane: padding lanes of a chunk update it
+// per-warp shared-memory slab: acc[BM_ACC] f64 | list[lcap] u64 | rec[BM_REC] u32 | cnt, nrec
 __host__ __device__ inline size_t bm_warp_bytes(int lcap) {
-    return (size_t)BM25_SUB * 8 + (size_t)lcap * 8 + (size_t)BM_REC * 4 + 16;
+    return (size_t)BM_ACC * 8 + (size_t)lcap * 8 + (size_t)BM_REC * 4 + 16;
 }
 
-__global__ void bm25_suboff_kernel(const int64_t* __restrict__ term_ptr, const uint32_t* __restrict__ doc,
+__global__ void bm25_interleave_kernel(const uint32_t* __restrict__ doc, const float* __restrict__ w, int64_t nnz,
+                                       uint2* __restrict__ post) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < nnz) post[i] = make_uint2(doc[i], __float_as_uint(w[i]));
+}
+
+cudaError_t bm25_interleave(const uint32_t* doc, const float* w, int64_t nnz, uint2* post, cudaStream_t st) {
+    if (nnz == 0) return cudaSuccess;
+    bm25_interleave_kernel<<<(unsigned)((nnz + 255) / 256), 256, 0, st>>>(doc, w, nnz, post);
+    return cudaGetLastError();
+}
+
+__global__ void bm25_suboff_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict__ post,
                                    int64_t V, int ns1, uint32_t* __restrict__ sub_off) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= V * ns1) return;
@@ -52,18 +68,18 @@ __global__ void bm25_suboff_kernel(const int64_t* __restrict__ term_ptr, const u
     int64_t lo = lo0, hi = hi0;
     while (lo < hi) {
         int64_t mid = (lo + hi) >> 1;
-        if ((uint64_t)doc[mid] < target) lo = mid + 1; else hi = mid;
+        if ((uint64_t)post[mid].x < target) lo = mid + 1; else hi = mid;
     }
     sub_off[i] = (uint32_t)(lo - lo0);
 }
 
-cudaError_t bm25_build_suboffsets(const int64_t* term_ptr, const uint32_t* doc, int64_t V, int64_t n_docs,
+cudaError_t bm25_build_suboffsets(const int64_t* term_ptr, const uint2* post, int64_t V, int64_t n_docs,
                                   uint32_t* sub_off, cudaStream_t st) {
     const int ns1 = (int)((n_docs + BM25_SUB - 1) / BM25_SUB) + 1;
     const int64_t total = V * ns1;
     if (total == 0) return cudaSuccess;
     const int64_t blocks = (total + 255) / 256;
-    bm25_suboff_kernel<<<(unsigned)blocks, 256, 0, st>>>(term_ptr, doc, V, ns1, sub_off);
+    bm25_suboff_kernel<<<(unsigned)blocks, 256, 0, st>>>(term_ptr, post, V, ns1, sub_off);
     return cudaGetLastError();
 }
 
@@ -82,14 +98,14 @@ __device__ __forceinline__ void warp_compact(uint64_t* list, int* cnt, int lcap,
 // double prefilter for "float32(acc) can reach score t": any acc whose float rounding is >= t is > pre
 __device__ __forceinline__ double prefilter_of_score(float t) { return (double)nextafterf(t, -INFINITY); }
 
-__device__ __forceinline__ void worker_bar() { asm volatile("bar.sync 1, %0;" ::"n"(BM_WARPS * 32) : "memory"); }
+__device__ __forceinline__ void worker_bar(int nthreads) { asm volatile("bar.sync 1, %0;" ::"r"(nthreads) : "memory"); }
 
 __global__ void __launch_bounds__(BM_THREADS, 1)
-bm25_scan_kernel(const int64_t* __restrict__ term_ptr, const uint32_t* __restrict__ doc,
-                 const float* __restrict__ w, const uint32_t* __restrict__ sub_off, int64_t V,
+bm25_scan_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict__ post,
+                 const uint32_t* __restrict__ sub_off, int64_t V,
                  int64_t n_docs, const int32_t* __restrict__ q_ptr, const int32_t* __restrict__ q_terms,
                  const double* __restrict__ q_vals, int B, const uint32_t* __restrict__ mask, int k_sel,
-                 int lcap, uint64_t* __restrict__ part, int splits, int* __restrict__ work_counter,
+                 int lcap, int nw, uint64_t* __restrict__ part, int splits, int* __restrict__ work_counter,
                  uint32_t* __restrict__ gthr, uint32_t* __restrict__ coarse, uint32_t* __restrict__ fine) {
     extern __shared__ __align__(16) uint8_t smem_raw[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -98,8 +114,8 @@ bm25_scan_kernel(const int64_t* __restrict__ term_ptr, const uint32_t* __restric
     if (threadIdx.x == 0) s_done = 0;
     __syncthreads();
 
-    if (warp == BM_WARPS) {
-        // ===== bound manager: queries blockIdx.x, blockIdx.x + gridDim.x, ...
+    if (warp == nw) {
+        // ===== bound manager (last warp): queries blockIdx.x, blockIdx.x + gridDim.x, ...
         while (true) {
             const int done = *reinterpret_cast<volatile int*>(&s_done);
             for (int q = (int)blockIdx.x; q < B; q += (int)gridDim.x) {
@@ -114,9 +130,9 @@ bm25_scan_kernel(const int64_t* __restrict__ term_ptr, const uint32_t* __restric
 
     uint8_t* slab = smem_raw + (size_t)warp * bm_warp_bytes(lcap);
     double* acc = reinterpret_cast<double*>(slab);
-    uint64_t* list = reinterpret_cast<uint64_t*>(slab + (size_t)BM25_SUB * 8);
-    uint32_t* rec = reinterpret_cast<uint32_t*>(slab + (size_t)BM25_SUB * 8 + (size_t)lcap * 8);
-    int* cntp = reinterpret_cast<int*>(slab + (size_t)BM25_SUB * 8 + (size_t)lcap * 8 + (size_t)BM_REC * 4);
+    uint64_t* list = reinterpret_cast<uint64_t*>(slab + (size_t)BM_ACC * 8);
+    uint32_t* rec = reinterpret_cast<uint32_t*>(slab + (size_t)BM_ACC * 8 + (size_t)lcap * 8);
+    int* cntp = reinterpret_cast<int*>(slab + (size_t)BM_ACC * 8 + (size_t)lcap * 8 + (size_t)BM_REC * 4);
     int* nrecp = cntp + 1;
     const int ns = (int)((n_docs + BM25_SUB - 1) / BM25_SUB);
     const int ns1 = ns + 1;
@@ -130,9 +146,9 @@ bm25_scan_kernel(const int64_t* __restrict__ term_ptr, const uint32_t* __restric
     __syncwarp();
 
     while (true) {
-        worker_bar();
+        worker_bar(nw * 32);
         if (threadIdx.x == 0) s_item = atomicAdd(work_counter, 1);
-        worker_bar();
+        worker_bar(nw * 32);
         const int item = s_item;
         if (item >= n_items) break;
         const int split = item / B, q = item - split * B;
@@ -143,7 +159,7 @@ bm25_scan_kernel(const int64_t* __restrict__ term_ptr, const uint32_t* __restric
         if (lane == 0) *cntp = 0;
         __syncwarp();
 
-        for (int j = j_begin + warp; j < j_end; j += BM_WARPS) {
+        for (int j = j_begin + warp; j < j_end; j += nw) {
             const uint32_t sub_base = (uint32_t)j * BM25_SUB;
             // the query's global bound: k_sel-th best score over everything any warp has pushed so far
             const uint32_t g = __ldcg(gthr + q);
@@ -161,64 +177,80 @@ bm25_scan_kernel(const int64_t* __restrict__ term_ptr, const uint32_t* __restric
                         const uint32_t lo = __ldg(sub_off + (size_t)t * ns1 + j);
                         const uint32_t hi = __ldg(sub_off + (size_t)t * ns1 + j + 1);
                         n = hi - lo;
-                        base = term_ptr[t] + lo;
+                        base = __ldg(term_ptr + t) + lo;
                         qv = q_vals[tg + lane];
                     }
                 }
-                if (!__any_sync(0xFFFFFFFFu, n != 0)) continue;
+                unsigned active = __ballot_sync(0xFFFFFFFFu, n != 0);   // terms with postings in this sub-tile
+                if (active == 0u) continue;
                 any = true;
 
-                // ---- the group's postings as one stream of 128-posting pieces, terms in ascending order;
+                // ---- the group's postings as one stream of <=128-posting pieces, terms in ascending order;
                 //      two pieces are always in flight ahead of the one being applied
-                struct Piece { uint32_t d[BM_HEAD]; float w[BM_HEAD]; double qv; bool last; };
-                int ft = 0;            // fetch cursor: term index inside the group, posting offset in its segment
-                uint32_t fi = 0;
+                struct Piece { uint2 v[BM_HEAD]; double qv; uint32_t cnt; bool last; };
+                uint32_t c_n = 0, c_i = 0;       // current term's segment length / fetch offset
+                int64_t c_base = 0;
+                double c_qv = 0.0;
+                bool more = true;
                 auto fetch = [&](Piece& P) -> bool {
-                    uint32_t n_t = 0;
-                    while (ft < nq) {                       // warp-uniform
-                        n_t = __shfl_sync(0xFFFFFFFFu, n, ft);
-                        if (fi < n_t) break;
-                        ++ft;
-                        fi = 0;
+                    if (c_i >= c_n) {                       // next term with postings (warp-uniform)
+                        if (active == 0u) { more = false; return false; }
+                        const int t = __ffs(active) - 1;
+                        active &= active - 1;
+                        c_n = __shfl_sync(0xFFFFFFFFu, n, t);
+                        c_base = __shfl_sync(0xFFFFFFFFu, base, t);
+                        c_qv = __shfl_sync(0xFFFFFFFFu, qv, t);
+                        c_i = 0;
                     }
-                    if (ft >= nq) return false;
-                    const int64_t b_t = __shfl_sync(0xFFFFFFFFu, base, ft);
-                    P.qv = __shfl_sync(0xFFFFFFFFu, qv, ft);
+                    const uint32_t rem = c_n - c_i;
+                    const uint2* src = post + c_base + c_i;
+                    P.qv = c_qv;
+                    P.cnt = rem;
 #pragma unroll
                     for (int u = 0; u < BM_HEAD; ++u) {
-                        const uint32_t idx = fi + (uint32_t)u * 32u + lane;
-                        P.d[u] = BM_INVALID;
-                        P.w[u] = 0.0f;
-                        if (idx < n_t) { P.d[u] = __ldg(doc + b_t + idx); P.w[u] = __ldg(w + b_t + idx); }
+                        const uint32_t idx = (uint32_t)u * 32u + lane;
+                        P.v[u] = make_uint2(BM_INVALID, 0u);
+                        if (idx < rem) P.v[u] = __ldg(src + idx);
                     }
-                    fi += BM_HEAD * 32u;
-                    P.last = fi >= n_t;                     // next piece belongs to another term
-                    if (P.last) { ++ft; fi = 0; }
+                    c_i += BM_HEAD * 32u;
+                    P.last = c_i >= c_n;                    // the next piece belongs to another term
                     return true;
                 };
-                auto apply = [&](uint32_t d, float ww, double qv_t) {
-                    if (d != BM_INVALID) {
-                        const uint32_t dl = d - sub_base;
-                        const double nv = __dadd_rn(acc[dl], __dmul_rn(qv_t, (double)ww));   // -0.0 + p == p
-                        acc[dl] = nv;
-                        if (nv > pre) {                       // rare once the bound is warm
-                            const int pos = atomicAdd(nrecp, 1);
-                            if (pos < BM_REC) rec[pos] = dl;
-                        }
+                // two chunks at a time: the documents of one term are distinct, so the accumulator reads
+                // of a pair are issued together, then the adds, then the writes
+                auto apply2 = [&](const uint2& x0, const uint2& x1, double qv_t) {
+                    const uint32_t dl0 = (x0.x != BM_INVALID) ? x0.x - sub_base : (uint32_t)BM25_SUB + lane;
+                    const uint32_t dl1 = (x1.x != BM_INVALID) ? x1.x - sub_base : (uint32_t)BM25_SUB + lane;
+                    const double a0 = acc[dl0], a1 = acc[dl1];
+                    const double n0 = __dadd_rn(a0, __dmul_rn(qv_t, (double)__uint_as_float(x0.y)));   // -0.0 + p == p
+                    const double n1 = __dadd_rn(a1, __dmul_rn(qv_t, (double)__uint_as_float(x1.y)));
+                    acc[dl0] = n0;
+                    acc[dl1] = n1;
+                    if (n0 > pre || n1 > pre) {               // rare once the bound is warm
+                        if (n0 > pre && x0.x != BM_INVALID) { const int pos = atomicAdd(nrecp, 1); if (pos < BM_REC) rec[pos] = dl0; }
+                        if (n1 > pre && x1.x != BM_INVALID) { const int pos = atomicAdd(nrecp, 1); if (pos < BM_REC) rec[pos] = dl1; }
                     }
                 };
-                Piece p0, p1, p2;
-                bool v0 = fetch(p0);
-                bool v1 = v0 && fetch(p1);
-                bool v2 = v1 && fetch(p2);
+                auto apply = [&](const Piece& P) {
+                    apply2(P.v[0], P.v[1], P.qv);
+                    if (P.cnt > 64u) apply2(P.v[2], P.v[3], P.qv);   // warp-uniform
+                    if (P.last) __syncwarp();     // a term's updates are visible before the next term's
+                };
+                Piece pa, pb, pc;
+                bool va = fetch(pa);
+                bool vb = va && fetch(pb);
+                bool vc = vb && fetch(pc);
 #pragma unroll 1
-                while (v0) {
-#pragma unroll
-                    for (int u = 0; u < BM_HEAD; ++u) apply(p0.d[u], p0.w[u], p0.qv);
-                    if (p0.last) __syncwarp();   // a term's updates are visible before the next term's
-                    p0 = p1; v0 = v1;
-                    p1 = p2; v1 = v2;
-                    v2 = v1 && fetch(p2);
+                while (true) {
+                    if (!va) break;
+                    apply(pa);
+                    va = more && fetch(pa);
+                    if (!vb) break;
+                    apply(pb);
+                    vb = more && fetch(pb);
+                    if (!vc) break;
+                    apply(pc);
+                    vc = more && fetch(pc);
                 }
             }
             if (!any) continue;
@@ -282,25 +314,32 @@ bm25_scan_kernel(const int64_t* __restrict__ term_ptr, const uint32_t* __restric
         }
         // ---- emit this warp's list for (split, warp, q)
         warp_compact(list, cntp, lcap, k_sel, thr, lane);
-        uint64_t* out = part + ((size_t)(split * BM_WARPS + warp) * B + q) * k_sel;
+        uint64_t* out = part + ((size_t)(split * nw + warp) * B + q) * k_sel;
         for (int i = lane; i < k_sel; i += 32) out[i] = list[i];
         __syncwarp();
     }
     if (threadIdx.x == 0) *reinterpret_cast<volatile int*>(&s_done) = 1;
 }
 
-Bm25Plan bm25_plan(int64_t n_docs, int B, int num_sms) {
+static int bm25_lcap(int k_sel) {
+    int lcap = 256;
+    while (lcap < k_sel + BM_REC) lcap <<= 1;   // k_sel kept after a compaction + one visit's pushes (<= BM_REC)
+    return lcap;
+}
+
+Bm25Plan bm25_plan(int64_t n_docs, int B, int k_sel, int num_sms) {
     Bm25Plan p;
     const int ns = (int)((n_docs + BM25_SUB - 1) / BM25_SUB);
+    p.workers = (int)std::min<size_t>(BM_WARPS, BM_SMEM_MAX / bm_warp_bytes(bm25_lcap(k_sel)));
     const int resident = num_sms;
     // enough items for ~8 claims per resident CTA, but never more splits than sub-tile groups
     int splits = (resident * 8 + B - 1) / B;
-    int max_splits = (ns + BM_WARPS - 1) / BM_WARPS;
+    int max_splits = (ns + p.workers - 1) / p.workers;
     if (splits > max_splits) splits = max_splits;
     if (splits < 1) splits = 1;
     if (splits > 64) splits = 64;
     p.splits = splits;
-    p.lists_per_query = splits * BM_WARPS;
+    p.lists_per_query = splits * p.workers;
     int64_t items = (int64_t)splits * B;
     p.grid = (int)(items < resident ? items : resident);
     auto up = [](size_t x) { return (x + 255) & ~(size_t)255; };
@@ -311,14 +350,13 @@ Bm25Plan bm25_plan(int64_t n_docs, int B, int num_sms) {
     return p;
 }
 
-cudaError_t bm25_scan(const int64_t* term_ptr, const uint32_t* doc, const float* w, const uint32_t* sub_off,
+cudaError_t bm25_scan(const int64_t* term_ptr, const uint2* post, const uint32_t* sub_off,
                       int64_t V, int64_t n_docs, const int32_t* q_ptr, const int32_t* q_terms,
                       const double* q_vals, int B, const uint32_t* mask, int k_sel, uint64_t* part,
                       const Bm25Plan& plan, void* scratch, cudaStream_t st) {
     if (k_sel > 512) return cudaErrorInvalidValue;
-    int lcap = 256;
-    while (lcap < k_sel + BM_REC) lcap <<= 1;   // k_sel kept after a compaction + one visit's pushes (<= BM_REC)
-    const size_t smem = bm_warp_bytes(lcap) * BM_WARPS;
+    const int lcap = bm25_lcap(k_sel);
+    const size_t smem = bm_warp_bytes(lcap) * plan.workers;
     static size_t attr_smem = 0;
     if (smem > attr_smem) {
         cudaError_t e = cudaFuncSetAttribute(bm25_scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -337,8 +375,8 @@ cudaError_t bm25_scan(const int64_t* term_ptr, const uint32_t* doc, const float*
     uint32_t* fine = reinterpret_cast<uint32_t*>(sp + 256 + plan.gthr_bytes + plan.coarse_bytes);
     cudaError_t e = cudaMemsetAsync(scratch, 0, plan.scratch_bytes, st);
     if (e != cudaSuccess) return e;
-    bm25_scan_kernel<<<plan.grid, BM_THREADS, smem, st>>>(term_ptr, doc, w, sub_off, V, n_docs, q_ptr, q_terms,
-                                                          q_vals, B, mask, k_sel, lcap, part, plan.splits,
+    bm25_scan_kernel<<<plan.grid, (plan.workers + 1) * 32, smem, st>>>(term_ptr, post, sub_off, V, n_docs, q_ptr, q_terms,
+                                                          q_vals, B, mask, k_sel, lcap, plan.workers, part, plan.splits,
                                                           work_counter, gthr, coarse, fine);
     return cudaGetLastError();
 }

@@ -68,8 +68,7 @@ struct DenseSpace {
 
 struct SparseSpace {
     int64_t* term_ptr = nullptr;
-    uint32_t* doc = nullptr;
-    float* w = nullptr;
+    uint2* post = nullptr;      // interleaved (doc id, weight bits)
     uint32_t* sub_off = nullptr;
     int64_t V = 0, n_docs = 0, nnz = 0;
     std::vector<int64_t> term_ptr_host;
@@ -165,8 +164,7 @@ void free_dense(DenseSpace& s) {
 }
 void free_sparse(SparseSpace& s) {
     if (s.term_ptr) cudaFree(s.term_ptr);
-    if (s.doc) cudaFree(s.doc);
-    if (s.w) cudaFree(s.w);
+    if (s.post) cudaFree(s.post);
     if (s.sub_off) cudaFree(s.sub_off);
     s = SparseSpace();
 }
@@ -242,14 +240,14 @@ void sparse_topk_dev(brag_engine* e, SparseSpace& s, const int32_t* q_ptr, const
                      const double* q_vals, int B, int k, const uint32_t* mask, float* out_scores,
                      int64_t* out_ids, int32_t* out_counts, cudaStream_t st) {
     REQUIRE(B >= 1 && k >= 1 && k <= 512, "sparse_topk: need B >= 1 and 1 <= k <= 512");
-    brag::Bm25Plan plan = brag::bm25_plan(s.n_docs, B, e->num_sms);
+    brag::Bm25Plan plan = brag::bm25_plan(s.n_docs, B, k, e->num_sms);
     const int P = plan.lists_per_query;
     uint64_t* part = e->part.as<uint64_t>((size_t)P * B * k);
     uint64_t* merged = e->keys1.as<uint64_t>((size_t)B * k);
     void* scratch = e->g_thr.ensure(plan.scratch_bytes);
     {
         StageTimer t(e, 2, st);
-        CK(brag::bm25_scan(s.term_ptr, s.doc, s.w, s.sub_off, s.V, s.n_docs, q_ptr, q_terms, q_vals, B, mask, k,
+        CK(brag::bm25_scan(s.term_ptr, s.post, s.sub_off, s.V, s.n_docs, q_ptr, q_terms, q_vals, B, mask, k,
                            part, plan, scratch, st));
         e->kernel_launches += 1;
     }
@@ -405,15 +403,27 @@ int brag_sparse_set_csr(brag_engine* e, const char* name, const int64_t* term_pt
         try {
             CK(cudaMalloc(&s.term_ptr, (n_terms + 1) * sizeof(int64_t)));
             CK(cudaMemcpy(s.term_ptr, term_ptr, (n_terms + 1) * sizeof(int64_t), kind));
-            CK(cudaMalloc(&s.doc, std::max<size_t>(s.nnz, 1) * sizeof(uint32_t)));
-            CK(cudaMalloc(&s.w, std::max<size_t>(s.nnz, 1) * sizeof(float)));
+            CK(cudaMalloc(&s.post, std::max<size_t>(s.nnz, 1) * sizeof(uint2)));
             if (s.nnz) {
-                CK(cudaMemcpy(s.doc, doc_ids, s.nnz * sizeof(uint32_t), kind));
-                CK(cudaMemcpy(s.w, weights, s.nnz * sizeof(float), kind));
+                if (on_device) {
+                    CK(brag::bm25_interleave(doc_ids, weights, s.nnz, s.post, 0));
+                } else {
+                    uint32_t* td = nullptr;
+                    float* tw = nullptr;
+                    cudaError_t ce = cudaMalloc(&td, s.nnz * sizeof(uint32_t));
+                    if (ce == cudaSuccess) ce = cudaMalloc(&tw, s.nnz * sizeof(float));
+                    if (ce == cudaSuccess) ce = cudaMemcpy(td, doc_ids, s.nnz * sizeof(uint32_t), kind);
+                    if (ce == cudaSuccess) ce = cudaMemcpy(tw, weights, s.nnz * sizeof(float), kind);
+                    if (ce == cudaSuccess) ce = brag::bm25_interleave(td, tw, s.nnz, s.post, 0);
+                    if (ce == cudaSuccess) ce = cudaDeviceSynchronize();
+                    if (td) cudaFree(td);
+                    if (tw) cudaFree(tw);
+                    CK(ce);
+                }
             }
             const int64_t ns1 = (n_docs + brag::BM25_SUB - 1) / brag::BM25_SUB + 1;
             CK(cudaMalloc(&s.sub_off, (size_t)n_terms * ns1 * sizeof(uint32_t)));
-            CK(brag::bm25_build_suboffsets(s.term_ptr, s.doc, n_terms, n_docs, s.sub_off, 0));
+            CK(brag::bm25_build_suboffsets(s.term_ptr, s.post, n_terms, n_docs, s.sub_off, 0));
             CK(cudaDeviceSynchronize());
         } catch (...) {
             free_sparse(s);

@@ -54,15 +54,17 @@ cudaError_t merge_scored_lists(const float* scores, const int64_t* ids, const in
 
 // ---- bm25.cu
 constexpr int BM25_SUB = 2048;  // documents per warp sub-tile
-cudaError_t bm25_build_suboffsets(const int64_t* term_ptr, const uint32_t* doc, int64_t V, int64_t n_docs,
+// postings are stored interleaved: post[i] = (doc id, float32 weight bits)
+cudaError_t bm25_interleave(const uint32_t* doc, const float* w, int64_t nnz, uint2* post, cudaStream_t st);
+cudaError_t bm25_build_suboffsets(const int64_t* term_ptr, const uint2* post, int64_t V, int64_t n_docs,
                                   uint32_t* sub_off, cudaStream_t st);
 struct Bm25Plan {
-    int splits; int lists_per_query; int grid;
+    int splits; int lists_per_query; int grid; int workers;
     size_t gthr_bytes, coarse_bytes, fine_bytes, scratch_bytes;
 };
-Bm25Plan bm25_plan(int64_t n_docs, int B, int num_sms);
+Bm25Plan bm25_plan(int64_t n_docs, int B, int k_sel, int num_sms);
 // part: [lists_per_query][B][k_sel]; scratch: plan.scratch_bytes (work counter | bounds | histograms)
-cudaError_t bm25_scan(const int64_t* term_ptr, const uint32_t* doc, const float* w, const uint32_t* sub_off,
+cudaError_t bm25_scan(const int64_t* term_ptr, const uint2* post, const uint32_t* sub_off,
                       int64_t V, int64_t n_docs, const int32_t* q_ptr, const int32_t* q_terms,
                       const double* q_vals, int B, const uint32_t* mask, int k_sel, uint64_t* part,
                       const Bm25Plan& plan, void* scratch, cudaStream_t st);

@@ -224,6 +224,21 @@ def test_sparse_idf_and_mask(engine):
         assert np.array_equal(s[b][:len(ei)].view(np.uint32), es.view(np.uint32))
 
 
+def test_sparse_large_k(engine):
+    """k up to 512 (fewer worker warps per CTA: the per-warp candidate list grows)."""
+    n_docs = 30000
+    ptr, doc, w, _ = synth.zipf_corpus(n_docs, 3000, 60, seed=17)
+    csr = _oracle_csr(ptr, doc, w, n_docs)
+    engine.sparse_set_csr("s", ptr, doc, w, n_docs)
+    q_ptr, q_terms, q_vals = synth.sparse_queries(ptr, doc, n_docs, 5, 8, "zipf", seed=18, skip_top=8)
+    for k in (200, 512):
+        s, i, c = engine.sparse_topk("s", q_ptr, q_terms, q_vals, k)
+        for b in range(5):
+            es, ei = O.sparse_topk(csr, q_terms[q_ptr[b]:q_ptr[b + 1]], q_vals[q_ptr[b]:q_ptr[b + 1]], k)
+            assert int(c[b]) == len(ei) and np.array_equal(i[b][:len(ei)], ei)
+            assert np.array_equal(s[b][:len(ei)].view(np.uint32), es.view(np.uint32))
+
+
 def test_sparse_many_terms_per_query(engine):
     """More than one 16-term group per query (document-sized queries)."""
     n_docs = 3000
