@@ -159,19 +159,40 @@ bm25_scan_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict__
         if (lane == 0) *cntp = 0;
         __syncwarp();
 
+        // first term group of the query: term row, query value and posting base are the same for every
+        // sub-tile, and the (lo, hi) offsets of the NEXT sub-tile are fetched while this one is processed
+        int t0 = -1;
+        double qv0 = 0.0;
+        int64_t tp0 = 0;
+        if (lane < min(BM_TG, qe - qb)) {
+            const int t = q_terms[qb + lane];
+            if (t >= 0 && t < V) { t0 = t; qv0 = q_vals[qb + lane]; tp0 = __ldg(term_ptr + t); }
+        }
+        uint32_t lo_nx = 0, hi_nx = 0;
+        if (t0 >= 0 && j_begin + warp < j_end) {
+            lo_nx = __ldg(sub_off + (size_t)t0 * ns1 + (j_begin + warp));
+            hi_nx = __ldg(sub_off + (size_t)t0 * ns1 + (j_begin + warp) + 1);
+        }
         for (int j = j_begin + warp; j < j_end; j += nw) {
             const uint32_t sub_base = (uint32_t)j * BM25_SUB;
             // the query's global bound: k_sel-th best score over everything any warp has pushed so far
             const uint32_t g = __ldcg(gthr + q);
             const double pre = (g != 0u) ? fmax(pre_local, prefilter_of_score(ordered_f32(g))) : pre_local;
             bool any = false;
+            const uint32_t lo_cur = lo_nx, hi_cur = hi_nx;
+            if (t0 >= 0 && j + nw < j_end) {
+                lo_nx = __ldg(sub_off + (size_t)t0 * ns1 + (j + nw));
+                hi_nx = __ldg(sub_off + (size_t)t0 * ns1 + (j + nw) + 1);
+            }
             for (int tg = qb; tg < qe; tg += BM_TG) {
                 const int nq = min(BM_TG, qe - tg);
                 // ---- segment setup: lane l < nq owns term tg + l
                 uint32_t n = 0;
                 int64_t base = 0;
                 double qv = 0.0;
-                if (lane < nq) {
+                if (tg == qb) {
+                    if (t0 >= 0) { n = hi_cur - lo_cur; base = tp0 + lo_cur; qv = qv0; }
+                } else if (lane < nq) {
                     const int t = q_terms[tg + lane];
                     if (t >= 0 && t < V) {
                         const uint32_t lo = __ldg(sub_off + (size_t)t * ns1 + j);
@@ -236,21 +257,29 @@ bm25_scan_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict__
                     if (P.cnt > 64u) apply2(P.v[2], P.v[3], P.qv);   // warp-uniform
                     if (P.last) __syncwarp();     // a term's updates are visible before the next term's
                 };
-                Piece pa, pb, pc;
-                bool va = fetch(pa);
-                bool vb = va && fetch(pb);
-                bool vc = vb && fetch(pc);
+                Piece p0, p1, p2, p3, p4;           // four pieces in flight ahead of the one being applied
+                bool v0 = fetch(p0);
+                bool v1 = v0 && fetch(p1);
+                bool v2 = v1 && fetch(p2);
+                bool v3 = v2 && fetch(p3);
+                bool v4 = v3 && fetch(p4);
 #pragma unroll 1
                 while (true) {
-                    if (!va) break;
-                    apply(pa);
-                    va = more && fetch(pa);
-                    if (!vb) break;
-                    apply(pb);
-                    vb = more && fetch(pb);
-                    if (!vc) break;
-                    apply(pc);
-                    vc = more && fetch(pc);
+                    if (!v0) break;
+                    apply(p0);
+                    v0 = more && fetch(p0);
+                    if (!v1) break;
+                    apply(p1);
+                    v1 = more && fetch(p1);
+                    if (!v2) break;
+                    apply(p2);
+                    v2 = more && fetch(p2);
+                    if (!v3) break;
+                    apply(p3);
+                    v3 = more && fetch(p3);
+                    if (!v4) break;
+                    apply(p4);
+                    v4 = more && fetch(p4);
                 }
             }
             if (!any) continue;
