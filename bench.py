@@ -40,8 +40,9 @@ def parse():
     ap.add_argument("--vocab", type=int, default=50_000)
     ap.add_argument("--doc-len", type=int, default=285)
     ap.add_argument("--q-terms", type=int, default=8)
-    ap.add_argument("--cpu-sample-rows", type=int, default=262_144)
-    ap.add_argument("--cpu-sample-queries", type=int, default=256)
+    ap.add_argument("--cpu-sample-rows", type=int, default=1 << 21, help="rows/docs of the CPU-baseline sample")
+    ap.add_argument("--cpu-sample-queries", type=int, default=1024)
+    ap.add_argument("--b1-iters", type=int, default=30, help="batch-1 latency iterations (0 = skip)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     return ap.parse_args()
@@ -55,6 +56,16 @@ def load_peaks():
         return {"tflops": j.get("bf16_tflops_sustained", 1400.0), "tflops_burst": j.get("bf16_tflops"),
                 "hbm_gbs": j.get("hbm_gbs", 6650.0), "source": "measured"}
     return {"tflops": 1400.0, "tflops_burst": 1590.0, "hbm_gbs": 6650.0, "source": "fallback"}
+
+
+def ncu_traffic(kernel, world):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel` from the committed
+    `ncu --set full` capture of this same command at N=1 (profiles/ncu_traffic.json); None otherwise."""
+    p = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+    if world != 1 or not os.path.exists(p):
+        return None
+    with open(p) as f:
+        return json.load(f).get(kernel)
 
 
 class ClockSampler:
@@ -100,7 +111,8 @@ def run_reference(args, rank, world):
     from rag_application_b200 import synth
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
-    ns, bs = min(args.cpu_sample_rows, args.n), args.cpu_sample_queries
+    # the sample corpus is generated on the host here, so it is kept smaller than the in-run baseline's
+    ns, bs = min(args.cpu_sample_rows, args.n, 1 << 18), min(args.cpu_sample_queries, 256)
     x = synth.dense_corpus_torch(ns, args.d, torch.bfloat16, "cpu")
     q = synth.dense_queries_torch(x, bs).to(torch.bfloat16).float().numpy()
     xs = x.float().numpy()
@@ -269,6 +281,26 @@ def main():
         e2e = {"value": args.batch * args.steps / float(dt.item()), "unit": UNIT, "h2d_bytes_per_step": int(h2d),
                "d2h_bytes_per_step": int(d2h)}
 
+    # ---- batch-1 latency (the metric's second half): p50 over single-query hybrid calls
+    b1 = None
+    if args.b1_iters > 0:
+        q1, qp1 = q_dev[:1].contiguous(), qp_d[:2].contiguous()
+        nt1 = int(qp[1])
+        qt1, qv1 = qt_d[:nt1].contiguous(), qv_d[:nt1].contiguous()
+
+        def step_b1():
+            if world == 1:
+                return eng.hybrid_topk("dense", "sparse", q1, qp1, qt1, qv1, k)
+            return sh.hybrid_topk("dense", "sparse", q1, qp1, qt1, qv1, k)
+        for _ in range(3):
+            step_b1()
+        lat = []
+        for _ in range(args.b1_iters):
+            ms1, _ = timed(step_b1, 1)
+            lat.append(ms1)
+        b1 = {"p50_ms": float(np.median(lat)), "p95_ms": float(np.percentile(lat, 95)), "iters": args.b1_iters,
+              "hbm_floor_ms": n_loc * args.d * 2 / (peaks["hbm_gbs"] * 1e9) * 1e3}
+
     # ---- CPU baseline (rank 0, N=1): bounded sample of the same workload on the host cores
     cpu = None
     if rank == 0 and cpu_csr is not None:
@@ -298,9 +330,9 @@ def main():
             "e2e": e2e, "gpu_launches": int(launches), "clocks": clk,
             "roofline": {"kernel": "dense_umma_kernel (tcgen05 scan + fused top-k)", "bound": "tensor", "achieved": ach,
                          "peak": peaks["tflops"], "unit": "TFLOP/s", "frac": ach / peaks["tflops"],
-                         "peak_kind": f"{peaks['source']} sustained cuBLAS bf16", "traffic": None,
+                         "peak_kind": f"{peaks['source']} sustained cuBLAS bf16", "traffic": ncu_traffic("dense_umma_kernel", world),
                          "flops_per_launch": flops, "avg_launch_ms": dense_ms},
-            "cpu_baseline": cpu,
+            "cpu_baseline": cpu, "batch1": b1,
             "stages_ms_per_step": {s: stage_ms[s] / args.steps for s in stage_ms},
             "bm25": {"algorithmic_bytes_per_step": bm25_bytes, "ms": bm_ms,
                      "achieved_gbs": bm25_bytes / (bm_ms * 1e-3) / 1e9 if bm_ms > 0 else None,

@@ -1,0 +1,560 @@
+"""`AsyncQdrantClient`-shaped front end over the B200 engine: the seven methods the reference's
+vector-store adapter calls on `qdrant_session.client` (qdrant_handler.py:44,55,94,190,363,467,474),
+with the same keyword names and result shapes, so `QdrantHandler` runs unmodified on top of it
+(INTEGRATION.md shows the one-line change in qdrant_session.py:21).
+
+Semantics follow qdrant-client local mode as restated in SURVEY.md 8c: COSINE spaces store
+L2-normalised float32 rows and normalise the query; sparse scoring is an overlap-only dot product
+with optional Modifier.IDF; a Prefetch with children re-scores the union of its children's ids; a
+FusionQuery(RRF) fuses them with constant 2 and default limit 10; ranking is (score desc, insertion
+row asc).  Points live on the host until the first query after a mutation, then every named vector
+space of the collection is (re)uploaded to HBM in one go.
+
+All numeric work goes through rag_application_b200.Engine (the C ABI); there is no CPU path here.
+`engine_factory` exists so the host logic can be unit-tested against the oracle-backed stand-in in
+tests/_oracle_engine.py."""
+from __future__ import annotations
+
+import asyncio
+import math
+import threading
+from typing import Any, Callable, Dict, Iterable, List, Optional, Sequence, Tuple
+
+import numpy as np
+
+from . import models as M
+
+EPS32 = float(np.finfo(np.float32).eps)
+DEFAULT_LIMIT = 10          # qdrant's default `limit` (also used by a fusion prefetch that omits it)
+_STORAGE = {None: "f32", "float32": "f32", "float16": "f16", "bfloat16": "bf16", "f32": "f32", "f16": "f16", "bf16": "bf16"}
+
+
+def _get(obj, name, default=None):
+    """Attribute or mapping access: accepts our dataclasses, real qdrant models and plain dicts."""
+    if obj is None:
+        return default
+    if isinstance(obj, dict):
+        return obj.get(name, default)
+    return getattr(obj, name, default)
+
+
+def _enum_value(x):
+    return getattr(x, "value", x)
+
+
+def _normalize_rows(x: np.ndarray) -> np.ndarray:
+    x = np.array(x, dtype=np.float32, copy=True)
+    n = np.linalg.norm(x, axis=-1, keepdims=True).astype(np.float32)
+    return (x / np.where(n != 0.0, n, np.float32(EPS32))).astype(np.float32)
+
+
+# ------------------------------------------------------------------------------ payload filters
+def _match_column(col: List[Any], cond) -> np.ndarray:
+    match, rng = _get(cond, "match"), _get(cond, "range")
+    out = np.ones(len(col), dtype=bool)
+    if match is not None:
+        if _get(match, "any") is not None:
+            allowed = set(_get(match, "any"))
+            out &= np.fromiter((_contains(v, allowed) for v in col), bool, len(col))
+        else:
+            val = _get(match, "value")
+            out &= np.fromiter((_equals(v, val) for v in col), bool, len(col))
+    if rng is not None:
+        lo, loe, hi, hie = _get(rng, "gt"), _get(rng, "gte"), _get(rng, "lt"), _get(rng, "lte")
+
+        def ok(v):
+            if not isinstance(v, (int, float)) or isinstance(v, bool):
+                return False
+            return ((lo is None or v > lo) and (loe is None or v >= loe) and
+                    (hi is None or v < hi) and (hie is None or v <= hie))
+        out &= np.fromiter((ok(v) for v in col), bool, len(col))
+    return out
+
+
+def _equals(v, val) -> bool:
+    if isinstance(v, (list, tuple)):
+        return any(e == val for e in v)      # qdrant: array payloads match if any element matches
+    return v == val
+
+
+def _contains(v, allowed) -> bool:
+    if isinstance(v, (list, tuple)):
+        return any(e in allowed for e in v)
+    try:
+        return v in allowed
+    except TypeError:
+        return False
+
+
+def _payload_column(payloads: List[Optional[dict]], key: str) -> List[Any]:
+    parts = key.split(".")
+    col = []
+    for p in payloads:
+        v: Any = p
+        for k in parts:
+            v = v.get(k) if isinstance(v, dict) else None
+        col.append(v)
+    return col
+
+
+def compile_filter(flt, payloads: List[Optional[dict]], ids: List[Any]) -> np.ndarray:
+    """Filter(must / must_not / should) -> bool[n].  Conditions: FieldCondition(match value / any,
+    range), HasIdCondition, nested Filter; dict spellings of the same are accepted."""
+    n = len(payloads)
+    if flt is None:
+        return np.ones(n, dtype=bool)
+
+    def cond_mask(c) -> np.ndarray:
+        if _get(c, "must") is not None or _get(c, "must_not") is not None or _get(c, "should") is not None:
+            return compile_filter(c, payloads, ids)
+        if _get(c, "has_id") is not None:
+            want = set(_get(c, "has_id"))
+            return np.fromiter((i in want for i in ids), bool, n)
+        key = _get(c, "key")
+        if key is None:
+            raise ValueError(f"unsupported filter condition: {c!r}")
+        return _match_column(_payload_column(payloads, key), c)
+
+    def as_list(x):
+        if x is None:
+            return []
+        return list(x) if isinstance(x, (list, tuple)) else [x]
+
+    out = np.ones(n, dtype=bool)
+    for c in as_list(_get(flt, "must")):
+        out &= cond_mask(c)
+    for c in as_list(_get(flt, "must_not")):
+        out &= ~cond_mask(c)
+    should = as_list(_get(flt, "should"))
+    if should:
+        any_ = np.zeros(n, dtype=bool)
+        for c in should:
+            any_ |= cond_mask(c)
+        out &= any_
+    return out
+
+
+# ------------------------------------------------------------------------------ collection (host side)
+class _Collection:
+    def __init__(self, name: str, vectors_config: Dict[str, Any], sparse_config: Optional[Dict[str, Any]],
+                 default_storage: Optional[str]):
+        self.name = name
+        self.dense_cfg: Dict[str, Tuple[int, str, str]] = {}     # vector name -> (size, distance, storage)
+        for vname, vp in (vectors_config or {}).items():
+            dist = str(_enum_value(_get(vp, "distance", M.Distance.COSINE))).lower()
+            if dist not in ("cosine", "dot"):
+                raise ValueError(f"distance {dist!r} of vector {vname!r} is not supported (Cosine / Dot only)")
+            storage = _STORAGE[_enum_value(_get(vp, "datatype"))] if _get(vp, "datatype") else (default_storage or "f32")
+            self.dense_cfg[vname] = (int(_get(vp, "size")), dist, _STORAGE[storage])
+        self.sparse_cfg: Dict[str, str] = {}                      # vector name -> "none" | "idf"
+        for vname, sp in (sparse_config or {}).items():
+            self.sparse_cfg[vname] = str(_enum_value(_get(sp, "modifier") or "none")).lower()
+        self.ids: List[Any] = []
+        self.id2row: Dict[Any, int] = {}
+        self.payloads: List[Optional[dict]] = []
+        self.dense_rows: Dict[str, List[Optional[np.ndarray]]] = {v: [] for v in self.dense_cfg}
+        self.sparse_rows: Dict[str, List[Optional[Tuple[np.ndarray, np.ndarray]]]] = {v: [] for v in self.sparse_cfg}
+        self.version = 0            # bumped by every mutation
+        self.committed = -1         # version present in HBM
+        # filled by commit()
+        self.term_ids: Dict[str, np.ndarray] = {}     # sparse space -> sorted external indices (row = position)
+        self.df: Dict[str, np.ndarray] = {}
+        self.n_sparse: Dict[str, int] = {}            # points that have that sparse vector (IDF's N)
+        self.present: Dict[str, Optional[np.ndarray]] = {}   # dense space -> bool[n] when some points lack it
+        self.mask_cache: Dict[Any, int] = {}
+
+    def __len__(self):
+        return len(self.ids)
+
+    def upsert(self, points: Iterable[Any]):
+        parsed = []                                   # validate everything before touching the collection
+        for p in points:
+            pid = _get(p, "id")
+            vec = _get(p, "vector") or {}
+            if not isinstance(vec, dict):
+                if list(self.dense_cfg) == [""]:
+                    vec = {"": vec}
+                else:
+                    raise ValueError("collection has named vectors: pass vector={name: ...}")
+            dense, sparse = {}, {}
+            for vname, v in vec.items():
+                if vname in self.dense_cfg:
+                    a = np.asarray(v, dtype=np.float32)
+                    if a.shape != (self.dense_cfg[vname][0],):
+                        raise ValueError(f"vector {vname!r}: expected dim {self.dense_cfg[vname][0]}, got {a.shape}")
+                    dense[vname] = a
+                elif vname in self.sparse_cfg:
+                    idx = np.asarray(_get(v, "indices"), dtype=np.int64)
+                    val = np.asarray(_get(v, "values"), dtype=np.float32)
+                    if idx.shape != val.shape or idx.ndim != 1:
+                        raise ValueError(f"sparse vector {vname!r}: indices/values length mismatch")
+                    if len(np.unique(idx)) != len(idx):
+                        raise ValueError(f"sparse vector {vname!r}: indices must be unique")
+                    sparse[vname] = (idx, val)
+                else:
+                    raise ValueError(f"Not existing vector name error: {vname}")
+            payload = _get(p, "payload")
+            parsed.append((pid, dense, sparse, dict(payload) if payload is not None else None))
+        for pid, dense, sparse, payload in parsed:
+            row = self.id2row.get(pid)
+            if row is None:
+                row = len(self.ids)
+                self.id2row[pid] = row
+                self.ids.append(pid)
+                self.payloads.append(None)
+                for lst in self.dense_rows.values():
+                    lst.append(None)
+                for lst in self.sparse_rows.values():
+                    lst.append(None)
+            self.payloads[row] = payload
+            for vname, a in dense.items():
+                self.dense_rows[vname][row] = a
+            for vname, sv in sparse.items():
+                self.sparse_rows[vname][row] = sv
+        self.version += 1
+
+    # -------------------------------------------------------------- upload to HBM
+    def space(self, vname: str) -> str:
+        return f"{self.name}\x1f{vname}"
+
+    def commit(self, engine):
+        if self.committed == self.version:
+            return
+        n = len(self.ids)
+        self.mask_cache.clear()
+        for vname, (size, dist, storage) in self.dense_cfg.items():
+            rows = self.dense_rows[vname]
+            have = np.fromiter((r is not None for r in rows), bool, n)
+            if n == 0 or not have.any():
+                engine.dense_drop(self.space(vname))
+                self.present[vname] = np.zeros(n, dtype=bool)
+                continue
+            x = np.zeros((n, size), dtype=np.float32)
+            for i, r in enumerate(rows):
+                if r is not None:
+                    x[i] = r
+            if dist == "cosine":
+                x = _normalize_rows(x)
+            engine.dense_set(self.space(vname), x, storage)
+            self.present[vname] = None if have.all() else have
+        for vname in self.sparse_cfg:
+            rows = self.sparse_rows[vname]
+            have = [i for i, r in enumerate(rows) if r is not None]
+            self.n_sparse[vname] = len(have)
+            if not have:
+                engine.sparse_drop(self.space(vname))
+                self.term_ids[vname] = np.zeros(0, np.int64)
+                self.df[vname] = np.zeros(0, np.int64)
+                continue
+            idx = np.concatenate([rows[i][0] for i in have])
+            val = np.concatenate([rows[i][1] for i in have])
+            doc = np.concatenate([np.full(len(rows[i][0]), i, dtype=np.int64) for i in have])
+            terms, trow = np.unique(idx, return_inverse=True)     # ascending external index == ascending term row
+            o = np.lexsort((doc, trow))
+            trow, doc, val = trow[o], doc[o], val[o]
+            ptr = np.zeros(len(terms) + 1, dtype=np.int64)
+            np.add.at(ptr, trow + 1, 1)
+            ptr = np.cumsum(ptr)
+            engine.sparse_set_csr(self.space(vname), ptr, doc.astype(np.uint32), val.astype(np.float32), n)
+            self.term_ids[vname] = terms
+            self.df[vname] = np.diff(ptr)
+        self.committed = self.version
+
+
+# ------------------------------------------------------------------------------ synchronous core
+class B200QdrantCore:
+    """Synchronous implementation; `B200QdrantClient` below wraps it in the async surface the
+    reference awaits.  One engine (one GPU) per client; spaces are named '<collection>\\x1f<vector>'."""
+
+    MAX_MASKS = 64
+
+    def __init__(self, device: int = 0, storage: Optional[str] = None, engine_factory: Optional[Callable] = None,
+                 rrf_tie: str = "id"):
+        if engine_factory is None:
+            from .engine import Engine      # fails loudly if libbrag.so / a B200 is missing
+            engine_factory = Engine
+        self.engine = engine_factory(device)
+        self.default_storage = storage
+        self.rrf_tie = 0 if rrf_tie == "id" else 1
+        self.collections: Dict[str, _Collection] = {}
+        self._lock = threading.RLock()
+        self._next_mask = 1
+        self._mask_owner: Dict[int, Tuple[str, Any]] = {}
+
+    def close(self):
+        self.engine.close()
+
+    # ---------------------------------------------------------------- collection management
+    def get_collections(self) -> M.CollectionsResponse:
+        with self._lock:
+            return M.CollectionsResponse([M.CollectionDescription(n) for n in self.collections])
+
+    def collection_exists(self, collection_name: str) -> bool:
+        return collection_name in self.collections
+
+    def create_collection(self, collection_name: str, vectors_config=None, sparse_vectors_config=None,
+                          optimizers_config=None, on_disk_payload=None, **_ignored) -> bool:
+        with self._lock:
+            if collection_name in self.collections:
+                raise ValueError(f"Collection {collection_name} already exists")
+            if vectors_config is not None and not isinstance(vectors_config, dict):
+                vectors_config = {"": vectors_config}
+            self.collections[collection_name] = _Collection(collection_name, vectors_config or {},
+                                                            sparse_vectors_config, self.default_storage)
+            return True
+
+    def delete_collection(self, collection_name: str, **_ignored) -> bool:
+        with self._lock:
+            col = self.collections.pop(collection_name, None)
+            if col is None:
+                return False
+            for v in col.dense_cfg:
+                self.engine.dense_drop(col.space(v))
+            for v in col.sparse_cfg:
+                self.engine.sparse_drop(col.space(v))
+            return True
+
+    def _col(self, name: str) -> _Collection:
+        col = self.collections.get(name)
+        if col is None:
+            raise ValueError(f"Collection {name} not found")
+        return col
+
+    def upsert(self, collection_name: str, points, wait: bool = True, **_ignored) -> M.UpdateResult:
+        with self._lock:
+            self._col(collection_name).upsert(points)
+            return M.UpdateResult()
+
+    def get_collection(self, collection_name: str) -> M.CollectionInfo:
+        with self._lock:
+            col = self._col(collection_name)
+            return M.CollectionInfo(points_count=len(col), vectors_count=len(col) * (len(col.dense_cfg) + len(col.sparse_cfg)))
+
+    def count(self, collection_name: str, count_filter=None, exact: bool = True, **_ignored) -> M.CountResult:
+        with self._lock:
+            col = self._col(collection_name)
+            if count_filter is None:
+                return M.CountResult(len(col))
+            return M.CountResult(int(compile_filter(count_filter, col.payloads, col.ids).sum()))
+
+    # ---------------------------------------------------------------- masks
+    def _mask_id(self, col: _Collection, mask: Optional[np.ndarray], key) -> int:
+        """Upload a bool[n] mask (cached per collection version under `key`); None -> 0 (no filter)."""
+        if mask is None:
+            return 0
+        if key is not None and key in col.mask_cache:
+            return col.mask_cache[key]
+        mid = self._next_mask
+        self._next_mask = self._next_mask % self.MAX_MASKS + 1
+        old = self._mask_owner.pop(mid, None)
+        if old is not None:
+            oc = self.collections.get(old[0])
+            if oc is not None:
+                oc.mask_cache.pop(old[1], None)
+        self.engine.mask_set(mid, mask)
+        if key is not None:
+            col.mask_cache[key] = mid
+            self._mask_owner[mid] = (col.name, key)
+        return mid
+
+    @staticmethod
+    def _filter_key(flt):
+        return None if flt is None else repr(flt)
+
+    # ---------------------------------------------------------------- plan executor (one query)
+    def _sparse_query(self, col: _Collection, using: str, q) -> Tuple[np.ndarray, np.ndarray]:
+        """External (hashed) indices -> ascending term rows + float64 values (IDF applied if configured)."""
+        idx = np.asarray(_get(q, "indices"), dtype=np.int64)
+        val = np.asarray(_get(q, "values"), dtype=np.float64)
+        terms = col.term_ids.get(using, np.zeros(0, np.int64))
+        if len(terms) == 0 or len(idx) == 0:
+            return np.zeros(0, np.int32), np.zeros(0, np.float64)
+        pos = np.searchsorted(terms, idx)
+        ok = (pos < len(terms)) & (terms[np.minimum(pos, len(terms) - 1)] == idx)
+        pos, val = pos[ok], val[ok]
+        o = np.argsort(pos, kind="stable")
+        pos, val = pos[o], val[o]
+        if col.sparse_cfg[using] == "idf":
+            n = col.n_sparse[using]
+            df = col.df[using][pos].astype(np.float64)
+            val = np.array([float(v) * math.log(1.0 + (n - d + 0.5) / (d + 0.5)) for v, d in zip(val, df)], np.float64)
+        return pos.astype(np.int32), val
+
+    def _run(self, col: _Collection, query, using, limit, prefetch, flt) -> Tuple[np.ndarray, np.ndarray]:
+        """Bottom-up evaluation of one Prefetch / top-level request -> (scores, rows), best first."""
+        n = len(col)
+        limit = DEFAULT_LIMIT if limit is None else int(limit)
+        empty = (np.zeros(0, np.float64), np.zeros(0, np.int64))
+        if prefetch is None:
+            kids = []
+        else:
+            plist = prefetch if isinstance(prefetch, (list, tuple)) else [prefetch]
+            kids = [self._run(col, _get(p, "query"), _get(p, "using"), _get(p, "limit"), _get(p, "prefetch"),
+                              _get(p, "filter")) for p in plist]
+        fmask = None if flt is None else compile_filter(flt, col.payloads, col.ids)
+
+        fusion = _get(query, "fusion")
+        if fusion is not None:
+            if str(_enum_value(fusion)).lower() != "rrf":
+                raise NotImplementedError("only Fusion.RRF is implemented")
+            if not kids:
+                raise ValueError("a fusion query needs prefetches")
+            kmax = max(1, max(len(r) for _, r in kids))
+            ids = np.full((len(kids), 1, kmax), -1, np.int64)
+            cnt = np.zeros((len(kids), 1), np.int32)
+            for l, (_, r) in enumerate(kids):
+                ids[l, 0, :len(r)] = r
+                cnt[l, 0] = len(r)
+            s, i, c = self.engine.rrf(ids, cnt, limit, self.rrf_tie)
+            s, i = np.asarray(s)[0, :int(c[0])], np.asarray(i)[0, :int(c[0])]
+            if fmask is not None and len(i):
+                keep = fmask[i]
+                s, i = s[keep], i[keep]
+            return s.astype(np.float64), i.astype(np.int64)
+
+        if query is None:
+            raise NotImplementedError("query=None (scroll-like requests) is not part of the hot path")
+        if n == 0 or limit <= 0:
+            return empty
+        cand = None
+        if kids:
+            cand = np.unique(np.concatenate([r for _, r in kids])) if any(len(r) for _, r in kids) else np.zeros(0, np.int64)
+            if len(cand) == 0:
+                return empty
+
+        if _get(query, "indices") is not None:                       # sparse query
+            if using not in col.sparse_cfg:
+                raise ValueError(f"Not existing vector name error: {using}")
+            terms, vals = self._sparse_query(col, using, query)
+            if len(terms) == 0 or col.n_sparse.get(using, 0) == 0:
+                return empty
+            mask, key = fmask, self._filter_key(flt)
+            if cand is not None:
+                cm = np.zeros(n, dtype=bool)
+                cm[cand] = True
+                mask, key = (cm if mask is None else (cm & mask)), None
+            mid = self._mask_id(col, mask, key)
+            q_ptr = np.array([0, len(terms)], np.int32)
+            s, i, c = self.engine.sparse_topk(col.space(using), q_ptr, terms, vals, min(limit, n), mid)
+        else:                                                        # dense query
+            using = "" if using is None else using
+            if using not in col.dense_cfg:
+                raise ValueError(f"Not existing vector name error: {using}")
+            size, dist, _ = col.dense_cfg[using]
+            q = np.asarray(query, dtype=np.float32).reshape(1, -1)
+            if q.shape[1] != size:
+                raise ValueError(f"query for {using!r}: expected dim {size}, got {q.shape[1]}")
+            if dist == "cosine":
+                q = _normalize_rows(q)
+            present = col.present.get(using)
+            if present is not None and not present.any():
+                return empty
+            mask, key = fmask, self._filter_key(flt)
+            if present is not None:
+                mask, key = (present if mask is None else (present & mask)), (("present", using, key))
+            mid = self._mask_id(col, mask, key)
+            if cand is not None:
+                s, i, c = self.engine.dense_rescore(col.space(using), q, cand.reshape(1, -1), min(limit, len(cand)), mid)
+            else:
+                s, i, c = self.engine.dense_topk(col.space(using), q, min(limit, n), mid)
+        c0 = int(np.asarray(c)[0])
+        return np.asarray(s)[0, :c0].astype(np.float64), np.asarray(i)[0, :c0].astype(np.int64)
+
+    def _points(self, col: _Collection, scores, rows, with_payload) -> List[M.ScoredPoint]:
+        out = []
+        for s, r in zip(scores, rows):
+            p = col.payloads[int(r)] if with_payload else None
+            out.append(M.ScoredPoint(id=col.ids[int(r)], score=float(s), payload=dict(p) if p is not None else None))
+        return out
+
+    def query_points(self, collection_name: str, query=None, using: Optional[str] = None, prefetch=None,
+                     query_filter=None, search_params=None, limit: int = DEFAULT_LIMIT, offset: Optional[int] = None,
+                     with_payload=True, with_vectors=False, score_threshold: Optional[float] = None,
+                     **_ignored) -> M.QueryResponse:
+        """search_params (hnsw_ef / exact) are accepted and ignored: every scan here is exact."""
+        with self._lock:
+            col = self._col(collection_name)
+            col.commit(self.engine)
+            off = int(offset or 0)
+            s, r = self._run(col, query, using, int(limit) + off, prefetch, query_filter)
+            if score_threshold is not None:
+                keep = s >= score_threshold
+                s, r = s[keep], r[keep]
+            return M.QueryResponse(points=self._points(col, s[off:], r[off:], bool(with_payload)))
+
+    # ---------------------------------------------------------------- batched north_star shape
+    def hybrid_search_batch(self, collection_name: str, dense_queries, sparse_queries: Sequence[Any], limit: int = 10,
+                            using_dense: str = "dense", using_sparse: str = "sparse", query_filter=None,
+                            with_payload: bool = False) -> List[List[M.ScoredPoint]]:
+        """dense top-`limit` + sparse top-`limit` + RRF(limit) for a whole batch of queries in one engine
+        call (brag_hybrid_topk): the throughput path benchmarked in bench.py."""
+        with self._lock:
+            col = self._col(collection_name)
+            col.commit(self.engine)
+            size, dist, _ = col.dense_cfg[using_dense]
+            Q = np.asarray(dense_queries, dtype=np.float32).reshape(len(sparse_queries), size)
+            if dist == "cosine":
+                Q = _normalize_rows(Q)
+            terms, vals, ptr = [], [], [0]
+            for sq in sparse_queries:
+                t, v = self._sparse_query(col, using_sparse, sq)
+                terms.append(t)
+                vals.append(v)
+                ptr.append(ptr[-1] + len(t))
+            fmask = None if query_filter is None else compile_filter(query_filter, col.payloads, col.ids)
+            mid = self._mask_id(col, fmask, self._filter_key(query_filter))
+            k = min(int(limit), len(col))
+            s, i, c = self.engine.hybrid_topk(col.space(using_dense), col.space(using_sparse), Q,
+                                              np.asarray(ptr, np.int32),
+                                              np.concatenate(terms) if terms else np.zeros(0, np.int32),
+                                              np.concatenate(vals) if vals else np.zeros(0, np.float64), k, mid)
+            s, i, c = np.asarray(s), np.asarray(i), np.asarray(c)
+            return [self._points(col, s[b, :int(c[b])], i[b, :int(c[b])], with_payload) for b in range(len(sparse_queries))]
+
+
+# ------------------------------------------------------------------------------ async surface
+class B200QdrantClient:
+    """Drop-in for `AsyncQdrantClient(url=...)` at qdrant_session.py:21.  Every method is a coroutine;
+    GPU work runs in a worker thread so the single uvicorn event loop is never blocked, and
+    mutations / queries of one client are serialised (interleaved awaits are safe)."""
+
+    def __init__(self, device: int = 0, storage: Optional[str] = None, engine_factory: Optional[Callable] = None,
+                 rrf_tie: str = "id", **_ignored):
+        self._core = B200QdrantCore(device=device, storage=storage, engine_factory=engine_factory, rrf_tie=rrf_tie)
+
+    @property
+    def core(self) -> B200QdrantCore:
+        return self._core
+
+    async def _call(self, fn, *a, **kw):
+        return await asyncio.to_thread(fn, *a, **kw)
+
+    async def get_collections(self):
+        return await self._call(self._core.get_collections)
+
+    async def collection_exists(self, collection_name: str):
+        return await self._call(self._core.collection_exists, collection_name)
+
+    async def create_collection(self, collection_name: str, **kw):
+        return await self._call(self._core.create_collection, collection_name, **kw)
+
+    async def delete_collection(self, collection_name: str, **kw):
+        return await self._call(self._core.delete_collection, collection_name, **kw)
+
+    async def upsert(self, collection_name: str, points, **kw):
+        return await self._call(self._core.upsert, collection_name, points, **kw)
+
+    async def query_points(self, collection_name: str, **kw):
+        return await self._call(self._core.query_points, collection_name, **kw)
+
+    async def count(self, collection_name: str, **kw):
+        return await self._call(self._core.count, collection_name, **kw)
+
+    async def get_collection(self, collection_name: str):
+        return await self._call(self._core.get_collection, collection_name)
+
+    async def hybrid_search_batch(self, collection_name: str, *a, **kw):
+        return await self._call(self._core.hybrid_search_batch, collection_name, *a, **kw)
+
+    async def close(self):
+        await self._call(self._core.close)

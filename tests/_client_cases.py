@@ -1,0 +1,140 @@
+"""Shared bodies of the client tests: the same requests the reference's QdrantHandler issues
+(qdrant_handler.py:57-100 create_collection, :155-193 upsert, :305-372 hybrid_search), run against a
+B200QdrantClient built either on the real engine (GPU tests) or on the oracle stand-in (CPU tests),
+and compared with the committed known-answer vectors."""
+import asyncio
+import json
+import os
+
+import numpy as np
+
+from rag_application_b200 import models as M
+from rag_application_b200.client import B200QdrantClient
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "kat.json")
+
+
+def load_tree_case():
+    with open(GOLD) as f:
+        c = json.load(f)["tree"]
+    rng = np.random.Generator(np.random.PCG64(c["seed"]))
+    n, d = c["n"], c["d"]
+    x = rng.standard_normal((n, d)).astype(np.float32)
+    x /= np.linalg.norm(x, axis=1, keepdims=True)
+    q = (x[17] + 0.2 * rng.standard_normal(d)).astype(np.float32)
+    q /= np.linalg.norm(q)
+    return c, x, q
+
+
+async def reference_create_collection(client, user_id, dense=768, sizes=(64, 128, 256)):
+    """qdrant_handler.py:57-100."""
+    vectors_config = {
+        "dense": M.VectorParams(size=dense, distance=M.Distance.COSINE, on_disk=True),
+        "quantized": M.VectorParams(size=dense, distance=M.Distance.COSINE, on_disk=True),
+    }
+    for dim in sizes:
+        vectors_config[f"matryoshka_{dim}"] = M.VectorParams(size=dim, distance=M.Distance.COSINE, on_disk=False)
+    await client.create_collection(
+        collection_name=user_id, vectors_config=vectors_config,
+        sparse_vectors_config={"sparse": M.SparseVectorParams(index=M.SparseIndexParams(on_disk=False))},
+        optimizers_config=M.OptimizersConfigDiff(memmap_threshold=20000), on_disk_payload=True)
+
+
+def reference_points(x, docs, id_of=lambda i: f"chunk-{i:04d}"):
+    """qdrant_handler.py:134-187: derived vectors exactly as the reference computes them."""
+    pts = []
+    for i, row in enumerate(x):
+        emb = row.tolist()
+        quant = np.clip((np.array(emb) * 127).astype(np.int8), -128, 127).tolist()
+        e = np.array(emb)
+        pts.append(M.PointStruct(
+            id=id_of(i),
+            vector={"dense": emb, "matryoshka_64": e[:64].tolist(), "matryoshka_128": e[:128].tolist(),
+                    "matryoshka_256": e[:256].tolist(), "quantized": quant,
+                    "sparse": {"indices": docs[i][0], "values": docs[i][1]}},
+            payload={"document_id": f"doc-{i % 7}", "content": f"text {i}", "page_number": i % 5, "row": i}))
+    return pts
+
+
+async def reference_hybrid_search(client, user_id, dense_vector, sparse_vector, sp, query_filter=None):
+    """qdrant_handler.py:296-372, request construction only (no reranker)."""
+    quantized_query = np.clip((np.array(dense_vector) * 127).astype(np.int8), -128, 127).tolist()
+    matryoshka_prefetch = M.Prefetch(
+        prefetch=[M.Prefetch(
+            prefetch=[M.Prefetch(
+                prefetch=[M.Prefetch(query=dense_vector[:64], using="matryoshka_64", limit=sp["matryoshka_64_limit"])],
+                query=dense_vector[:128], using="matryoshka_128", limit=sp["matryoshka_128_limit"])],
+            query=dense_vector[:256], using="matryoshka_256", limit=sp["matryoshka_256_limit"])],
+        query=dense_vector, using="dense", limit=sp["dense_limit"])
+    quantized_dense_prefetch = M.Prefetch(
+        prefetch=[M.Prefetch(query=quantized_query, using="quantized", limit=sp["quantized_limit"])],
+        query=dense_vector, using="dense", limit=sp["dense_limit"])
+    sparse_search_prefetch = M.Prefetch(
+        query=M.SparseVector(indices=sparse_vector["indices"], values=sparse_vector["values"]),
+        using="sparse", limit=sp["sparse_limit"])
+    sparse_dense_rrf = M.Prefetch(prefetch=[quantized_dense_prefetch, sparse_search_prefetch],
+                                  query=M.models.FusionQuery(fusion=M.models.Fusion.RRF))
+    res = await client.query_points(
+        collection_name=str(user_id), prefetch=[matryoshka_prefetch, sparse_dense_rrf], query=dense_vector,
+        using="dense", limit=sp["final_limit"], search_params={"hnsw_ef": 128, "exact": True},
+        with_payload=True, query_filter=query_filter)
+    return res.points
+
+
+def run_reference_flow(engine_factory=None, rtol=1e-5):
+    c, x, q = load_tree_case()
+
+    async def flow():
+        client = B200QdrantClient(engine_factory=engine_factory)
+        user = "user-42"
+        assert [col.name for col in (await client.get_collections()).collections] == []
+        await reference_create_collection(client, user)
+        assert user in [col.name for col in (await client.get_collections()).collections]
+        pts = reference_points(x, c["docs"])
+        await client.upsert(collection_name=user, points=pts[:120])
+        await client.upsert(collection_name=user, points=pts[120:])
+        assert (await client.get_collection(collection_name=user)).points_count == c["n"]
+        sp = dict(c["search_params"], hnsw_ef=128)
+        sv = {"indices": c["q_idx"], "values": c["q_val"]}
+        got = await reference_hybrid_search(client, user, q.tolist(), sv, sp)
+        exp = c["final"]
+        assert [p.payload["row"] for p in got] == [r for _, r in exp]
+        assert [p.id for p in got] == [f"chunk-{r:04d}" for _, r in exp]
+        np.testing.assert_allclose([p.score for p in got], [s for s, _ in exp], rtol=rtol, atol=1e-6)
+        assert got[0].payload["content"] == f"text {exp[0][1]}"
+        # top-level payload filter (query_filter applies only at the top level)
+        mask = np.array(c["mask"], bool)
+        keep_rows = [int(i) for i in np.nonzero(mask)[0]]
+        flt = M.Filter(must=[M.FieldCondition(key="row", match=M.MatchAny(any=keep_rows))])
+        got = await reference_hybrid_search(client, user, q.tolist(), sv, sp, query_filter=flt)
+        assert [p.payload["row"] for p in got] == [r for _, r in c["final_masked"]]
+        assert (await client.count(collection_name=user, count_filter=flt)).count == int(mask.sum())
+        # Filter(**dict) spelling the reference uses (qdrant_handler.py:297)
+        flt2 = M.Filter(**{"must": [{"key": "page_number", "match": {"value": 3}}]})
+        cnt = (await client.count(collection_name=user, count_filter=flt2)).count
+        assert cnt == sum(1 for i in range(c["n"]) if i % 5 == 3)
+        res = await client.query_points(collection_name=user, query=q.tolist(), using="dense", limit=5, query_filter=flt2)
+        assert len(res.points) == 5 and all(p.payload["page_number"] == 3 for p in res.points)
+        # sparse-only leaf == golden S1, default fusion limit is 10
+        res = await client.query_points(collection_name=user, query=M.SparseVector(indices=c["q_idx"], values=c["q_val"]),
+                                        using="sparse", limit=sp["sparse_limit"])
+        s1 = c["stages"]["S1"]
+        assert [p.payload["row"] for p in res.points] == [r for _, r in s1]
+        assert [np.float32(p.score) for p in res.points] == [np.float32(s) for s, _ in s1]
+        # batched three-stage shape agrees with the per-query tree of the same shape
+        batch = await client.hybrid_search_batch(user, np.stack([q, x[5]]), [sv, {"indices": c["docs"][5][0], "values": c["docs"][5][1]}],
+                                                 limit=10, with_payload=True)
+        one = await client.query_points(
+            collection_name=user, query=M.FusionQuery(fusion=M.Fusion.RRF), limit=10,
+            prefetch=[M.Prefetch(query=q.tolist(), using="dense", limit=10),
+                      M.Prefetch(query=M.SparseVector(indices=c["q_idx"], values=c["q_val"]), using="sparse", limit=10)])
+        assert [p.id for p in batch[0]] == [p.id for p in one.points]
+        assert [p.score for p in batch[0]] == [p.score for p in one.points]
+        # upsert of an existing id overwrites in place; delete drops the collection
+        await client.upsert(collection_name=user, points=[pts[17]])
+        assert (await client.get_collection(collection_name=user)).points_count == c["n"]
+        await client.delete_collection(collection_name=user)
+        assert [col.name for col in (await client.get_collections()).collections] == []
+        await client.close()
+
+    asyncio.run(flow())

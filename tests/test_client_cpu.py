@@ -1,0 +1,67 @@
+"""CPU: the Qdrant-shaped client (plan executor, filter compiler, id/payload mapping, lazy upload)
+on the oracle-backed stand-in engine, against the committed known-answer vectors."""
+import numpy as np
+import pytest
+
+from _oracle_engine import OracleEngine
+from _client_cases import run_reference_flow
+from rag_application_b200 import models as M
+from rag_application_b200.client import B200QdrantCore, compile_filter
+
+
+def test_reference_flow_on_oracle_engine():
+    run_reference_flow(engine_factory=OracleEngine)
+
+
+def test_filter_compiler():
+    payloads = [{"a": 1, "t": ["x", "y"], "n": {"k": 5}}, {"a": 2, "t": "x"}, None, {"a": 1, "n": {"k": 9}}]
+    ids = ["p0", "p1", "p2", "p3"]
+    f = M.Filter(must=[M.FieldCondition(key="a", match=M.MatchValue(value=1))])
+    assert compile_filter(f, payloads, ids).tolist() == [True, False, False, True]
+    f = M.Filter(must_not=[{"key": "t", "match": {"value": "x"}}])
+    assert compile_filter(f, payloads, ids).tolist() == [False, False, True, True]
+    f = M.Filter(should=[M.FieldCondition(key="n.k", range=M.Range(gte=6)), M.HasIdCondition(has_id=["p1"])])
+    assert compile_filter(f, payloads, ids).tolist() == [False, True, False, True]
+    f = M.Filter(must=[M.Filter(should=[{"key": "a", "match": {"any": [2, 3]}}]), {"key": "t", "match": {"value": "x"}}])
+    assert compile_filter(f, payloads, ids).tolist() == [False, True, False, False]
+    assert compile_filter(None, payloads, ids).all()
+    with pytest.raises(ValueError):
+        compile_filter(M.Filter(must=[{"nonsense": 1}]), payloads, ids)
+
+
+def test_errors_and_edge_cases():
+    core = B200QdrantCore(engine_factory=OracleEngine)
+    core.create_collection("c", vectors_config={"v": M.VectorParams(size=4, distance=M.Distance.DOT)},
+                           sparse_vectors_config={"s": M.SparseVectorParams(modifier=M.Modifier.IDF)})
+    with pytest.raises(ValueError):
+        core.create_collection("c", vectors_config={})
+    with pytest.raises(ValueError):
+        core.query_points("nope", query=[0, 0, 0, 0], using="v")
+    # empty collection answers with no points
+    assert core.query_points("c", query=[1, 0, 0, 0], using="v", limit=3).points == []
+    with pytest.raises(ValueError):
+        core.upsert("c", [M.PointStruct(id=1, vector={"v": [1, 2, 3]})])          # wrong dim
+    with pytest.raises(ValueError):
+        core.upsert("c", [M.PointStruct(id=1, vector={"zzz": [1, 2, 3, 4]})])     # unknown vector name
+    with pytest.raises(ValueError):
+        core.upsert("c", [M.PointStruct(id=1, vector={"s": {"indices": [3, 3], "values": [1.0, 2.0]}})])
+    core.upsert("c", [M.PointStruct(id=7, vector={"v": [1, 0, 0, 0], "s": M.SparseVector([10, 2**31 - 5], [1.0, 2.0])}, payload={"k": 1}),
+                      M.PointStruct(id=8, vector={"v": [0, 2, 0, 0]}, payload={"k": 2}),
+                      M.PointStruct(id="u-9", vector={"s": {"indices": [10], "values": [3.0]}})])
+    r = core.query_points("c", query=[1, 1, 0, 0], using="v", limit=10).points
+    assert [(p.id, p.score) for p in r] == [(8, 2.0), (7, 1.0)]                    # point u-9 has no dense vector
+    r = core.query_points("c", query=M.SparseVector([10, 999], [1.0, 1.0]), using="s", limit=10).points
+    # IDF: N = 2 points carry the sparse vector, df(10) = 2 -> ln(1 + 0.5/2.5)
+    import math
+    w = math.log(1 + 0.5 / 2.5)
+    assert [p.id for p in r] == ["u-9", 7]
+    np.testing.assert_allclose([p.score for p in r], [3.0 * w, 1.0 * w], rtol=1e-6)
+    assert core.query_points("c", query=M.SparseVector([999], [1.0]), using="s").points == []   # unknown term only
+    # offset / score_threshold / with_payload
+    r = core.query_points("c", query=[1, 1, 0, 0], using="v", limit=1, offset=1, with_payload=False).points
+    assert [(p.id, p.payload) for p in r] == [(7, None)]
+    assert core.query_points("c", query=[1, 1, 0, 0], using="v", score_threshold=1.5).points[0].id == 8
+    assert core.count("c").count == 3 and core.get_collection("c").points_count == 3
+    with pytest.raises(NotImplementedError):
+        core.query_points("c", query=M.FusionQuery(fusion=M.Fusion.DBSF), prefetch=[M.Prefetch(query=[1, 0, 0, 0], using="v")])
+    assert core.delete_collection("c") and not core.delete_collection("c")
