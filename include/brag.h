@@ -120,7 +120,8 @@ int brag_hybrid_topk(brag_engine* e, const char* dense_name, const char* sparse_
 int brag_profile_enable(brag_engine* e, int32_t on);
 int brag_profile_read(brag_engine* e, double* ms, int64_t* launches, int64_t* kernel_launches_total);
 int brag_profile_reset(brag_engine* e);
-/* Which dense scan kernel brag_dense_topk would pick for batch B: 0 = GEMV stream, 1 = tcgen05. */
+/* Which dense scan kernel brag_dense_topk would pick for batch B: 0 = GEMV stream (float32 storage, or
+ * d not a multiple of 64), 1 = TMA + tcgen05 (16-bit storage, any batch size). */
 int brag_dense_path(brag_engine* e, const char* name, int32_t B);
 /* Force a path (-1 auto, 0 GEMV, 1 tcgen05) -- used by the parity tests. */
 int brag_force_dense_path(brag_engine* e, int32_t path);

@@ -289,29 +289,32 @@ dense_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
                 int cnt = S.cnt[qb][qidx];
                 // the query's global bound (k_sel-th best score over all rows scanned so far by any CTA,
                 // rounded down to a histogram edge) -- fetched while we wait for the accumulator
-                const uint32_t g = q_valid ? __ldcg(gthr + b) : 0u;
+                uint32_t g = q_valid ? __ldcg(gthr + b) : 0u;
                 mbar_wait(&S.tfull[as], aphase);
                 tc_fence_after();
                 float eff = thr;
                 if (g != 0u) eff = fmaxf(eff, nextafterf(ordered_f32(g), -INFINITY));   // keeps score >= bound
                 const uint32_t taddr = lane_taddr + (uint32_t)(as * UM_BN);
                 auto process = [&](uint32_t (&v)[32], int col0) {
+                    // rows of this 32-column group that exist and pass the payload filter (tiles start on
+                    // multiples of 256 rows, so a group is exactly one filter word): warp-uniform
+                    const int64_t r0 = row0 + col0;
+                    uint32_t cm = (row_end - r0 >= 32) ? 0xFFFFFFFFu : (row_end > r0 ? (1u << (int)(row_end - r0)) - 1u : 0u);
+                    if (mask != nullptr) cm &= __ldg(mask + (r0 >> 5));
                     uint32_t m = 0u;
 #pragma unroll
                     for (int i = 0; i < 32; ++i) m |= (__uint_as_float(v[i]) > eff) ? (1u << i) : 0u;
+                    m &= cm;
                     uint32_t mw = __reduce_or_sync(0xFFFFFFFFu, m);
                     while (mw) {                                   // rare: columns where some query has a hit
                         const int i = __ffs(mw) - 1;
                         mw &= mw - 1;
                         const float s = __uint_as_float(tmem_ld1(taddr + (uint32_t)(col0 + i)));
                         if ((m >> i) & 1u) {
-                            const int64_t row = row0 + col0 + i;
-                            if (row < row_end && mask_test(mask, (uint32_t)row)) {
-                                const uint64_t key = make_key(s, (uint32_t)row);
-                                __stcg(my_list + cnt, key);
-                                ++cnt;
-                                hist_count(coarse, fine, b, (uint32_t)(key >> 32));
-                            }
+                            const uint64_t key = make_key(s, (uint32_t)(r0 + i));
+                            __stcg(my_list + cnt, key);
+                            ++cnt;
+                            hist_count(coarse, fine, b, (uint32_t)(key >> 32));
                         }
                     }
                 };
@@ -323,6 +326,14 @@ dense_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
                     if (bal) {   // list full (pathological): sort locally, keep k_sel, tighten the local bound
                         um_compact(bal, my_list, my_list, cnt, thr, sbuf, k_sel, lane);
                         eff = fmaxf(eff, thr);
+                    }
+                    if (__any_sync(0xFFFFFFFFu, q_valid && g == 0u)) {
+                        // warm-up: no bound yet -- pick it up as soon as the manager publishes one, so the
+                        // initial flood of candidates stops after a few dozen rows per query
+                        if (q_valid && g == 0u) {
+                            g = __ldcg(gthr + b);
+                            if (g != 0u) eff = fmaxf(eff, nextafterf(ordered_f32(g), -INFINITY));
+                        }
                     }
                     tmem_ld_wait(va);
                     tmem_ld32_issue(taddr + (uint32_t)(g2 * 64 + 32), vb);

@@ -173,7 +173,11 @@ int pick_path(brag_engine* e, const DenseSpace& s, int B) {
     if (!s.umma_ok) return 0;
     if (e->force_path == 0) return 0;
     if (e->force_path == 1) return 1;
-    return B > 8 ? 1 : 0;
+    // measured on B200 (tools/_probe_paths.py): the TMA + tcgen05 scan streams 16-bit corpora faster than the
+    // GEMV at EVERY batch size (B=1: 7.3 vs 7.1 TB/s at 10M x 1024, 5.5 vs 3.7 TB/s at 1M x 768), so the GEMV
+    // is only the path of float32 storage and of row lengths the 64-element K slices cannot tile
+    (void)B;
+    return 1;
 }
 
 // ---- device-pointer implementations -------------------------------------------------------

@@ -318,3 +318,44 @@ def test_hybrid_three_stage(engine):
             assert int(c[b]) == len(ei)
             assert np.array_equal(i[b][:len(ei)], ei), f"query {b} mask {mid}"
             assert np.array_equal(s[b][:len(ei)], es)
+
+
+def test_two_shards_on_one_gpu_match_unsharded(engine):
+    """Row sharding emulated on one device: two engines own disjoint row ranges and answer with
+    global ids; gathered lists -> brag_merge_topk x2 -> brag_rrf must equal the unsharded hybrid call."""
+    from rag_application_b200 import Engine
+    from rag_application_b200.sharded import shard_bounds
+    n, d, k, B, V = 9001, 128, 50, 20, 2000
+    x = synth.dense_corpus(n, d, seed=51, clustered=True)
+    q = synth.dense_queries(x, B, seed=52)
+    ptr, doc, w, _ = synth.zipf_corpus(n, V, 50, seed=53)
+    q_ptr, q_terms, q_vals = synth.sparse_queries(ptr, doc, n, B, 8, "zipf", seed=54, skip_top=8)
+    engine.dense_set("dense", x, "bf16")
+    engine.sparse_set_csr("sparse", ptr, doc, w, n)
+    es, ei, ec = engine.hybrid_topk("dense", "sparse", q, q_ptr, q_terms, q_vals, k)
+    term_of = np.repeat(np.arange(V), np.diff(ptr))
+    lists = []
+    shards = []
+    for r in range(2):
+        lo, hi = shard_bounds(n, 2, r)
+        e = Engine(0)
+        shards.append(e)
+        e.set_id_offset(lo)
+        e.dense_set("dense", x[lo:hi], "bf16")
+        keep = (doc >= lo) & (doc < hi)
+        p = np.zeros(V + 1, np.int64)
+        np.add.at(p, term_of[keep] + 1, 1)
+        e.sparse_set_csr("sparse", np.cumsum(p), (doc[keep] - lo).astype(np.uint32), w[keep], hi - lo)
+        lists.append((e.dense_topk("dense", q, k), e.sparse_topk("sparse", q_ptr, q_terms, q_vals, k)))
+    merged = []
+    for which in range(2):
+        s = np.stack([lists[r][which][0] for r in range(2)])
+        i = np.stack([lists[r][which][1] for r in range(2)])
+        c = np.stack([lists[r][which][2] for r in range(2)])
+        merged.append(engine.merge_topk(s, i, c))
+    ids = np.stack([merged[0][1], merged[1][1]])
+    cnt = np.stack([merged[0][2], merged[1][2]])
+    s, i, c = engine.rrf(ids, cnt, k)
+    for e in shards:
+        e.close()
+    assert np.array_equal(c, ec) and np.array_equal(i, ei) and np.array_equal(s, es)
