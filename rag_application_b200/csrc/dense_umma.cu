@@ -87,10 +87,15 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
         }
     }
 }
-__device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* tmap, int c0, int c1, uint64_t* bar) {
+// L2 eviction-priority policies (the encodings CUTLASS uses for TMA cache hints)
+constexpr uint64_t L2_EVICT_NORMAL = 0x1000000000000000ull;
+constexpr uint64_t L2_EVICT_FIRST = 0x12F0000000000000ull;
+constexpr uint64_t L2_EVICT_LAST = 0x14F0000000000000ull;
+__device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* tmap, int c0, int c1, uint64_t* bar,
+                                            uint64_t policy) {
     asm volatile(
-        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
-        ::"r"(smem_u32(smem_dst)), "l"(tmap), "r"(smem_u32(bar)), "r"(c0), "r"(c1) : "memory");
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1, {%3, %4}], [%2], %5;"
+        ::"r"(smem_u32(smem_dst)), "l"(tmap), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "l"(policy) : "memory");
 }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
@@ -219,8 +224,11 @@ dense_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
                     for (int kb = 0; kb < n_kb; ++kb) {
                         mbar_wait(&S.empty[stage], phase ^ 1);
                         mbar_expect_tx(&S.full[stage], UM_A_BYTES + UM_B_BYTES);
-                        tma_load_2d(S.a[stage], &tmap_q, kb * UM_BK, (qb_base + qb) * UM_BM, &S.full[stage]);
-                        tma_load_2d(S.b[stage], &tmap_x, kb * UM_BK, row0, &S.full[stage]);
+                        // queries stay hot in L2 for the whole scan; an X tile is wanted until its last
+                        // query block has used it, then it should leave first
+                        tma_load_2d(S.a[stage], &tmap_q, kb * UM_BK, (qb_base + qb) * UM_BM, &S.full[stage], L2_EVICT_LAST);
+                        tma_load_2d(S.b[stage], &tmap_x, kb * UM_BK, row0, &S.full[stage],
+                                    qb + 1 < n_qblocks ? L2_EVICT_NORMAL : L2_EVICT_FIRST);
                         if (++stage == UM_STAGES) { stage = 0; phase ^= 1; }
                     }
                 }
