@@ -125,6 +125,9 @@ int brag_profile_reset(brag_engine* e);
 int brag_dense_path(brag_engine* e, const char* name, int32_t B);
 /* Force a path (-1 auto, 0 GEMV, 1 tcgen05) -- used by the parity tests. */
 int brag_force_dense_path(brag_engine* e, int32_t path);
+/* Sparse scan kernel (-1 auto, 0 scatter-accumulate, 1 bitmap filter).  Auto = bitmap filter unless a query of
+ * the batch has more than 32 terms or the space holds non-finite weights; both give identical results. */
+int brag_force_sparse_path(brag_engine* e, int32_t path);
 
 #ifdef __cplusplus
 }

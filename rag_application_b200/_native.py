@@ -37,6 +37,7 @@ PROTOTYPES = {
     "brag_profile_reset": (C.c_int, [c_p]),
     "brag_dense_path": (C.c_int, [c_p, C.c_char_p, i32]),
     "brag_force_dense_path": (C.c_int, [c_p, i32]),
+    "brag_force_sparse_path": (C.c_int, [c_p, i32]),
 }
 
 _lib = None

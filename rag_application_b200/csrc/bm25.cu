@@ -27,6 +27,7 @@
 
 #include "common.cuh"
 #include "kernels.h"
+#include "bm25_common.cuh"
 
 namespace brag {
 
@@ -82,23 +83,6 @@ cudaError_t bm25_build_suboffsets(const int64_t* term_ptr, const uint2* post, in
     bm25_suboff_kernel<<<(unsigned)blocks, 256, 0, st>>>(term_ptr, post, V, ns1, sub_off);
     return cudaGetLastError();
 }
-
-__device__ __forceinline__ void warp_compact(uint64_t* list, int* cnt, int lcap, int k_sel, uint64_t& thr, int lane) {
-    const int c = min(*cnt, lcap);
-    for (int i = c + lane; i < lcap; i += 32) list[i] = 0ull;
-    __syncwarp();
-    bitonic_desc(list, lcap, lane, 32, [] { __syncwarp(); });
-    const int nc = min(c, k_sel);
-    if (nc == k_sel) thr = max(thr, list[k_sel - 1]);
-    __syncwarp();
-    if (lane == 0) *cnt = nc;
-    __syncwarp();
-}
-
-// double prefilter for "float32(acc) can reach score t": any acc whose float rounding is >= t is > pre
-__device__ __forceinline__ double prefilter_of_score(float t) { return (double)nextafterf(t, -INFINITY); }
-
-__device__ __forceinline__ void worker_bar(int nthreads) { asm volatile("bar.sync 1, %0;" ::"r"(nthreads) : "memory"); }
 
 __global__ void __launch_bounds__(BM_THREADS, 1)
 bm25_scan_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict__ post,

@@ -70,6 +70,12 @@ struct SparseSpace {
     int64_t* term_ptr = nullptr;
     uint2* post = nullptr;      // interleaved (doc id, weight bits)
     uint32_t* sub_off = nullptr;
+    // bitmap-filter scan (bm25x.cu): per-term weight range, document maps of the dense terms
+    float2* wrange = nullptr;
+    int32_t* bm_row = nullptr;
+    uint32_t* bits = nullptr;
+    int n_dense = 0;
+    bool bitmap_ok = false;
     int64_t V = 0, n_docs = 0, nnz = 0;
     std::vector<int64_t> term_ptr_host;
 };
@@ -91,6 +97,7 @@ struct brag_engine {
     int num_sms = 148;
     int64_t id_offset = 0;
     int force_path = -1;
+    int force_sparse_path = -1;    // -1 auto, 0 scatter-accumulate (bm25.cu), 1 bitmap filter (bm25x.cu)
     std::map<std::string, DenseSpace> dense;
     std::map<std::string, SparseSpace> sparse;
     std::map<int, MaskBuf> masks;
@@ -98,6 +105,7 @@ struct brag_engine {
     DevBuf qs, q16, part, tmp_a, tmp_b, keys1, keys2, umma_scratch, work_counter, g_thr;
     DevBuf h_in[6], h_out[4];      // staging for host-pointer calls
     DevBuf hyb_ids, hyb_counts, hyb_scores;
+    std::vector<int32_t> qptr_host;
     alignas(64) unsigned char tmap_q[128];
     // profiling
     bool prof = false;
@@ -166,7 +174,52 @@ void free_sparse(SparseSpace& s) {
     if (s.term_ptr) cudaFree(s.term_ptr);
     if (s.post) cudaFree(s.post);
     if (s.sub_off) cudaFree(s.sub_off);
+    if (s.wrange) cudaFree(s.wrange);
+    if (s.bm_row) cudaFree(s.bm_row);
+    if (s.bits) cudaFree(s.bits);
     s = SparseSpace();
+}
+
+// Index of the bitmap-filter scan: weight range per term, and a document map for every term whose map is
+// smaller than its postings (df >= N/64), densest first, within a quarter of the posting bytes.
+void build_bitmap_index(SparseSpace& s) {
+    CK(cudaMalloc(&s.wrange, (size_t)s.V * sizeof(float2)));
+    int* flag = nullptr;
+    CK(cudaMalloc(&flag, sizeof(int)));
+    cudaError_t ce = brag::bm25x_build_wrange(s.term_ptr, s.post, s.V, s.nnz, s.wrange, flag, 0);
+    int nonfinite = 0;
+    if (ce == cudaSuccess) ce = cudaMemcpy(&nonfinite, flag, sizeof(int), cudaMemcpyDeviceToHost);
+    cudaFree(flag);
+    CK(ce);
+    const int64_t ns = (s.n_docs + brag::BM25_SUB - 1) / brag::BM25_SUB;
+    const size_t row_bytes = (size_t)ns * (brag::BM25_SUB / 8);
+    const int64_t min_df = std::max<int64_t>(32, s.n_docs / 64);
+    std::vector<std::pair<int64_t, int32_t>> dense;     // (df, term)
+    for (int64_t t = 0; t < s.V; ++t) {
+        const int64_t df = s.term_ptr_host[t + 1] - s.term_ptr_host[t];
+        if (df >= min_df) dense.push_back({df, (int32_t)t});
+    }
+    std::sort(dense.begin(), dense.end(), [](const std::pair<int64_t, int32_t>& a, const std::pair<int64_t, int32_t>& b) {
+        return a.first != b.first ? a.first > b.first : a.second < b.second;
+    });
+    const size_t budget = std::max<size_t>((size_t)64 << 20, (size_t)s.nnz * 2);
+    while (!dense.empty() && dense.size() * row_bytes > budget) dense.pop_back();
+    std::vector<int32_t> rows((size_t)s.V, -1), terms(dense.size());
+    for (size_t r = 0; r < dense.size(); ++r) { rows[(size_t)dense[r].second] = (int32_t)r; terms[r] = dense[r].second; }
+    s.n_dense = (int)dense.size();
+    CK(cudaMalloc(&s.bm_row, (size_t)s.V * sizeof(int32_t)));
+    CK(cudaMemcpy(s.bm_row, rows.data(), (size_t)s.V * sizeof(int32_t), cudaMemcpyHostToDevice));
+    CK(cudaMalloc(&s.bits, std::max<size_t>(256, (size_t)s.n_dense * row_bytes)));
+    if (s.n_dense) {
+        int32_t* dterms = nullptr;
+        CK(cudaMalloc(&dterms, terms.size() * sizeof(int32_t)));
+        ce = cudaMemcpy(dterms, terms.data(), terms.size() * sizeof(int32_t), cudaMemcpyHostToDevice);
+        if (ce == cudaSuccess) ce = brag::bm25x_build_bitmaps(s.term_ptr, s.post, dterms, s.n_dense, s.n_docs, s.bits, 0);
+        if (ce == cudaSuccess) ce = cudaDeviceSynchronize();
+        cudaFree(dterms);
+        CK(ce);
+    }
+    s.bitmap_ok = !nonfinite;
 }
 
 int pick_path(brag_engine* e, const DenseSpace& s, int B) {
@@ -240,19 +293,47 @@ void dense_rescore_dev(brag_engine* e, DenseSpace& s, const float* Q, int B, con
     e->kernel_launches += 3;
 }
 
+// longest query of a batch whose q_ptr lives on the device (one small D2H copy + stream sync)
+int max_terms_dev(brag_engine* e, const int32_t* q_ptr, int B, cudaStream_t st) {
+    e->qptr_host.resize((size_t)B + 1);
+    CK(cudaMemcpyAsync(e->qptr_host.data(), q_ptr, ((size_t)B + 1) * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    int mx = 0;
+    for (int b = 0; b < B; ++b) mx = std::max(mx, e->qptr_host[b + 1] - e->qptr_host[b]);
+    return mx;
+}
+int max_terms_host(const int32_t* q_ptr, int B) {
+    int mx = 0;
+    for (int b = 0; b < B; ++b) mx = std::max(mx, q_ptr[b + 1] - q_ptr[b]);
+    return mx;
+}
+
+// max_terms: longest query of the batch, or -1 when only the device copy of q_ptr is at hand
 void sparse_topk_dev(brag_engine* e, SparseSpace& s, const int32_t* q_ptr, const int32_t* q_terms,
                      const double* q_vals, int B, int k, const uint32_t* mask, float* out_scores,
-                     int64_t* out_ids, int32_t* out_counts, cudaStream_t st) {
+                     int64_t* out_ids, int32_t* out_counts, int max_terms, cudaStream_t st) {
     REQUIRE(B >= 1 && k >= 1 && k <= 512, "sparse_topk: need B >= 1 and 1 <= k <= 512");
-    brag::Bm25Plan plan = brag::bm25_plan(s.n_docs, B, k, e->num_sms);
+    // bitmap-filter scan unless the space has non-finite weights or a query is longer than 32 terms
+    bool bitmap = s.bitmap_ok && e->force_sparse_path != 0;
+    if (bitmap) {
+        if (max_terms < 0) max_terms = max_terms_dev(e, q_ptr, B, st);
+        bitmap = brag::bm25x_supported(max_terms, k);
+    }
+    REQUIRE(bitmap || e->force_sparse_path != 1, "sparse_topk: the bitmap scan was forced but cannot run this batch");
+    brag::Bm25Plan plan = bitmap ? brag::bm25x_plan(s.n_docs, B, k, max_terms, e->num_sms)
+                                 : brag::bm25_plan(s.n_docs, B, k, e->num_sms);
     const int P = plan.lists_per_query;
     uint64_t* part = e->part.as<uint64_t>((size_t)P * B * k);
     uint64_t* merged = e->keys1.as<uint64_t>((size_t)B * k);
     void* scratch = e->g_thr.ensure(plan.scratch_bytes);
     {
         StageTimer t(e, 2, st);
-        CK(brag::bm25_scan(s.term_ptr, s.post, s.sub_off, s.V, s.n_docs, q_ptr, q_terms, q_vals, B, mask, k,
-                           part, plan, scratch, st));
+        if (bitmap)
+            CK(brag::bm25x_scan(s.term_ptr, s.post, s.sub_off, s.bm_row, s.bits, s.wrange, s.V, s.n_docs, q_ptr, q_terms,
+                                q_vals, B, max_terms, mask, k, part, plan, scratch, st));
+        else
+            CK(brag::bm25_scan(s.term_ptr, s.post, s.sub_off, s.V, s.n_docs, q_ptr, q_terms, q_vals, B, mask, k,
+                               part, plan, scratch, st));
         e->kernel_launches += 1;
     }
     {
@@ -428,6 +509,7 @@ int brag_sparse_set_csr(brag_engine* e, const char* name, const int64_t* term_pt
             const int64_t ns1 = (n_docs + brag::BM25_SUB - 1) / brag::BM25_SUB + 1;
             CK(cudaMalloc(&s.sub_off, (size_t)n_terms * ns1 * sizeof(uint32_t)));
             CK(brag::bm25_build_suboffsets(s.term_ptr, s.post, n_terms, n_docs, s.sub_off, 0));
+            build_bitmap_index(s);
             CK(cudaDeviceSynchronize());
         } catch (...) {
             free_sparse(s);
@@ -533,7 +615,7 @@ int brag_sparse_topk(brag_engine* e, const char* name, const int32_t* q_ptr, con
         SparseSpace& s = sparse_space(e, name);
         const uint32_t* mask = mask_ptr(e, mask_id, s.n_docs);
         if (on_device) {
-            sparse_topk_dev(e, s, q_ptr, q_terms, q_vals, B, k, mask, out_scores, out_ids, out_counts, st);
+            sparse_topk_dev(e, s, q_ptr, q_terms, q_vals, B, k, mask, out_scores, out_ids, out_counts, -1, st);
         } else {
             const size_t nt = (size_t)q_ptr[B];
             for (int b = 0; b < B; ++b) {
@@ -547,7 +629,7 @@ int brag_sparse_topk(brag_engine* e, const char* name, const int32_t* q_ptr, con
             float* ds = e->h_out[0].as<float>((size_t)B * k);
             int64_t* di = e->h_out[1].as<int64_t>((size_t)B * k);
             int32_t* dc = e->h_out[2].as<int32_t>(B);
-            sparse_topk_dev(e, s, dp, dt, dv, B, k, mask, ds, di, dc, st);
+            sparse_topk_dev(e, s, dp, dt, dv, B, k, mask, ds, di, dc, max_terms_host(q_ptr, B), st);
             to_host(out_scores, ds, (size_t)B * k, st);
             to_host(out_ids, di, (size_t)B * k, st);
             to_host(out_counts, dc, (size_t)B, st);
@@ -646,7 +728,8 @@ int brag_hybrid_topk(brag_engine* e, const char* dense_name, const char* sparse_
             oc = e->h_out[2].as<int32_t>(B);
         }
         dense_topk_dev(e, ds, dq, B, k, mask, scs, ids, cnts, st);
-        sparse_topk_dev(e, ss, dp, dt, dv, B, k, mask, scs + (size_t)B * k, ids + (size_t)B * k, cnts + B, st);
+        sparse_topk_dev(e, ss, dp, dt, dv, B, k, mask, scs + (size_t)B * k, ids + (size_t)B * k, cnts + B,
+                        on_device ? -1 : max_terms_host(q_ptr, B), st);
         {
             StageTimer t(e, 4, st);
             CK(brag::rrf_fuse(ids, cnts, 2, B, k, k, BRAG_TIE_ID, os, oi, oc, st));
@@ -708,6 +791,13 @@ int brag_dense_path(brag_engine* e, const char* name, int32_t B) {
         path = pick_path(e, dense_space(e, name), B);
     });
     return rc == 0 ? path : -1;
+}
+
+int brag_force_sparse_path(brag_engine* e, int32_t path) {
+    return guarded([&] {
+        REQUIRE(e && path >= -1 && path <= 1, "brag_force_sparse_path: path must be -1, 0 or 1");
+        e->force_sparse_path = path;
+    });
 }
 
 int brag_force_dense_path(brag_engine* e, int32_t path) {

@@ -69,4 +69,20 @@ cudaError_t bm25_scan(const int64_t* term_ptr, const uint2* post, const uint32_t
                       const double* q_vals, int B, const uint32_t* mask, int k_sel, uint64_t* part,
                       const Bm25Plan& plan, void* scratch, cudaStream_t st);
 
+
+// ---- bm25x.cu: bitmap-filter variant of the sparse scan (same results, prunes on per-term weight bounds)
+// wrange[t] = (min, max) weight of term t; *nonfinite_flag is set when any weight is NaN/Inf
+cudaError_t bm25x_build_wrange(const int64_t* term_ptr, const uint2* post, int64_t V, int64_t nnz, float2* wrange,
+                               int* nonfinite_flag, cudaStream_t st);
+// bits: [n_dense][ceil(n_docs / BM25_SUB) * 64] words, bit d of row r = term dense_terms[r] occurs in document d
+cudaError_t bm25x_build_bitmaps(const int64_t* term_ptr, const uint2* post, const int32_t* dense_terms, int n_dense,
+                                int64_t n_docs, uint32_t* bits, cudaStream_t st);
+bool bm25x_supported(int max_terms, int k_sel);
+Bm25Plan bm25x_plan(int64_t n_docs, int B, int k_sel, int max_terms, int num_sms);
+// bm_row[t] = bitmap row of term t or -1; max_terms = longest query of the batch (<= 32)
+cudaError_t bm25x_scan(const int64_t* term_ptr, const uint2* post, const uint32_t* sub_off, const int32_t* bm_row,
+                       const uint32_t* bits, const float2* wrange, int64_t V, int64_t n_docs, const int32_t* q_ptr,
+                       const int32_t* q_terms, const double* q_vals, int B, int max_terms, const uint32_t* mask,
+                       int k_sel, uint64_t* part, const Bm25Plan& plan, void* scratch, cudaStream_t st);
+
 }  // namespace brag

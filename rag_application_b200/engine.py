@@ -238,5 +238,8 @@ class Engine:
         p = self._lib.brag_dense_path(self._h, name.encode(), B)
         return {0: "gemv", 1: "tcgen05"}.get(p, "?")
 
+    def force_sparse_path(self, path: Optional[str]):
+        _native.check(self._lib.brag_force_sparse_path(self._h, {None: -1, "scatter": 0, "bitmap": 1}[path]))
+
     def force_dense_path(self, path: Optional[str]):
         _native.check(self._lib.brag_force_dense_path(self._h, {None: -1, "gemv": 0, "tcgen05": 1}[path]))

@@ -167,9 +167,17 @@ def _oracle_csr(ptr, doc, w, n_docs):
     return O.CSR(ptr, doc, w, n_docs)
 
 
+@pytest.fixture(params=["scatter", "bitmap"])
+def sparse_path(request, engine):
+    """Both sparse scan kernels (bm25.cu scatter-accumulate, bm25x.cu bitmap filter) must give the oracle's bits."""
+    engine.force_sparse_path(request.param)
+    yield request.param
+    engine.force_sparse_path(None)
+
+
 @pytest.mark.parametrize("n_docs,V,L", [(300, 500, 20), (5000, 2000, 60), (20000, 5000, 120)])
 @pytest.mark.parametrize("regime", ["zipf", "doc"])
-def test_sparse_topk_bit_exact(engine, n_docs, V, L, regime):
+def test_sparse_topk_bit_exact(engine, sparse_path, n_docs, V, L, regime):
     ptr, doc, w, _ = synth.zipf_corpus(n_docs, V, L, seed=n_docs)
     csr = _oracle_csr(ptr, doc, w, n_docs)
     B = 33
@@ -186,7 +194,7 @@ def test_sparse_topk_bit_exact(engine, n_docs, V, L, regime):
             assert np.all(i[b][len(ei):] == -1)
 
 
-def test_sparse_overlap_only_and_batch1(engine):
+def test_sparse_overlap_only_and_batch1(engine, sparse_path):
     """Docs sharing no term are not candidates: rare terms give short lists."""
     ptr, doc, w, _ = synth.zipf_corpus(4000, 3000, 40, seed=8)
     csr = _oracle_csr(ptr, doc, w, 4000)
@@ -204,7 +212,7 @@ def test_sparse_overlap_only_and_batch1(engine):
     assert list(c) == [0, 0] and np.all(i == -1)
 
 
-def test_sparse_idf_and_mask(engine):
+def test_sparse_idf_and_mask(engine, sparse_path):
     n_docs = 6000
     ptr, doc, w, _ = synth.zipf_corpus(n_docs, 1500, 50, seed=5)
     csr = _oracle_csr(ptr, doc, w, n_docs)
@@ -224,7 +232,7 @@ def test_sparse_idf_and_mask(engine):
         assert np.array_equal(s[b][:len(ei)].view(np.uint32), es.view(np.uint32))
 
 
-def test_sparse_large_k(engine):
+def test_sparse_large_k(engine, sparse_path):
     """k up to 512 (fewer worker warps per CTA: the per-warp candidate list grows)."""
     n_docs = 30000
     ptr, doc, w, _ = synth.zipf_corpus(n_docs, 3000, 60, seed=17)
@@ -252,6 +260,78 @@ def test_sparse_many_terms_per_query(engine):
     es, ei = O.sparse_topk(csr, terms, vals, 64)
     assert np.array_equal(i[0][:len(ei)], ei)
     assert np.array_equal(s[0][:len(ei)].view(np.uint32), es.view(np.uint32))
+
+
+@pytest.mark.parametrize("n_terms", [12, 16, 17, 32])
+def test_sparse_bitmap_term_groups_and_signs(engine, n_terms):
+    """The bitmap scan's 16- and 32-term variants, with negative and zero query values (a term's contribution
+    is bounded by max(0, qv*maxw, qv*minw), so pruning stays rank-safe for any sign)."""
+    n_docs = 9000
+    ptr, doc, w, _ = synth.zipf_corpus(n_docs, 900, 70, seed=16)
+    w = (w * np.where(np.arange(len(w)) % 7 == 0, -1.0, 1.0)).astype(np.float32)    # some negative weights too
+    csr = _oracle_csr(ptr, doc, w, n_docs)
+    engine.sparse_set_csr("s", ptr, doc, w, n_docs)
+    rng = np.random.default_rng(n_terms)
+    B = 7
+    q_ptr = np.arange(0, (B + 1) * n_terms, n_terms, dtype=np.int32)
+    q_terms = np.concatenate([np.sort(rng.choice(900, n_terms, replace=False)) for _ in range(B)]).astype(np.int32)
+    q_vals = rng.random(B * n_terms) * 2 - 0.6
+    q_vals[::5] = 0.0
+    engine.force_sparse_path("bitmap")
+    try:
+        s, i, c = engine.sparse_topk("s", q_ptr, q_terms, q_vals, 40)
+    finally:
+        engine.force_sparse_path(None)
+    for b in range(B):
+        es, ei = O.sparse_topk(csr, q_terms[q_ptr[b]:q_ptr[b + 1]], q_vals[q_ptr[b]:q_ptr[b + 1]], 40)
+        assert int(c[b]) == len(ei) and np.array_equal(i[b][:len(ei)], ei), f"query {b}"
+        assert np.array_equal(s[b][:len(ei)].view(np.uint32), es.view(np.uint32))
+
+
+@pytest.mark.parametrize("masked", [False, True])
+def test_sparse_bitmap_warm_bound_large(engine, masked):
+    """Enough documents for the global bound to warm up and the count filter to prune (dense-term maps, many
+    sub-tiles, several splits); both kernels must agree with the oracle and with each other."""
+    n_docs = 150000
+    ptr, doc, w, _ = synth.zipf_corpus(n_docs, 3000, 100, seed=21)
+    csr = _oracle_csr(ptr, doc, w, n_docs)
+    engine.sparse_set_csr("s", ptr, doc, w, n_docs)
+    B = 48
+    q_ptr, q_terms, q_vals = synth.sparse_queries(ptr, doc, n_docs, B, 8, "zipf", seed=22, skip_top=16)
+    mask = synth.random_mask(n_docs, 0.10) if masked else None
+    if masked:
+        engine.mask_set(6, mask)
+    out = {}
+    for path in ("scatter", "bitmap"):
+        engine.force_sparse_path(path)
+        try:
+            out[path] = [engine.sparse_topk("s", q_ptr, q_terms, q_vals, k, mask_id=6 if masked else 0) for k in (10, 100)]
+        finally:
+            engine.force_sparse_path(None)
+    for kk, k in enumerate((10, 100)):
+        s, i, c = out["bitmap"][kk]
+        s0, i0, c0 = out["scatter"][kk]
+        assert np.array_equal(i, i0) and np.array_equal(c, c0) and np.array_equal(s.view(np.uint32), s0.view(np.uint32))
+        for b in range(B):
+            es, ei = O.sparse_topk(csr, q_terms[q_ptr[b]:q_ptr[b + 1]], q_vals[q_ptr[b]:q_ptr[b + 1]], k, mask=mask)
+            assert int(c[b]) == len(ei) and np.array_equal(i[b][:len(ei)], ei), f"query {b}"
+            assert np.array_equal(s[b][:len(ei)].view(np.uint32), es.view(np.uint32))
+
+
+def test_sparse_nonfinite_weights_use_the_scatter_scan(engine):
+    """A NaN/Inf weight makes per-term bounds meaningless: the space falls back to the exhaustive kernel."""
+    ptr, doc, w, _ = synth.zipf_corpus(2000, 300, 30, seed=3)
+    w = w.copy()
+    w[5] = np.inf
+    engine.sparse_set_csr("s", ptr, doc, w, 2000)
+    q_ptr, q_terms, q_vals = synth.sparse_queries(ptr, doc, 2000, 3, 4, "zipf", seed=4, skip_top=2)
+    s, i, c = engine.sparse_topk("s", q_ptr, q_terms, q_vals, 10)      # auto: must not raise
+    engine.force_sparse_path("bitmap")
+    try:
+        with pytest.raises(Exception):
+            engine.sparse_topk("s", q_ptr, q_terms, q_vals, 10)
+    finally:
+        engine.force_sparse_path(None)
 
 
 # ----------------------------------------------------------------------------- fusion / merge
