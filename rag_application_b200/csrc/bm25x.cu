@@ -33,13 +33,27 @@ constexpr size_t BX_SMEM_MAX = 232448 - 64;
 constexpr int BX_WORDS = BM25_SUB / 32;             // 64 map words per sub-tile, 2 per lane
 constexpr unsigned long long BX_SENTINEL = 0x8000000000000000ull;   // -0.0 + p == p: first add equals 0.0 + p
 
-constexpr int BX_STAGE = 64;                        // postings of a map-less term staged in shared memory per sub-tile
+// One visit of a worker warp covers SUBS consecutive 2048-document sub-tiles (the granularity of sub_off): more
+// documents per visit amortise the per-visit and per-term overheads, fewer leave room for more resident warps.
+template <int MAXT, int SUBS>
+struct BxCfg {
+    static constexpr int WPL = 2 * SUBS;          // map words per lane
+    static constexpr int WORDS = 64 * SUBS;       // map words per tile
+    static constexpr int TILE = BM25_SUB * SUBS;  // documents per tile
+    static constexpr int POOL = 128 * SUBS;       // postings of map-less terms staged in shared memory per tile
+    static constexpr int PLANES = (MAXT == 8) ? 4 : (MAXT == 16 ? 5 : 6);     // bit planes of the counts 0..MAXT
+};
 
-// per-warp shared memory: bm[MAXT][64] u32 | pre[MAXT][64] u16 | stage[MAXT][64] (doc, weight) | list[lcap] u64 |
-//                         sbase[MAXT] i64 | sqv[MAXT] f64 | clist[32] u16 | cnt
-__host__ __device__ inline size_t bx_warp_bytes(int maxt, int lcap) {
-    return (size_t)maxt * BX_WORDS * 4 + (size_t)maxt * BX_WORDS * 2 + (size_t)maxt * BX_STAGE * 8 + (size_t)lcap * 8 +
-           (size_t)maxt * 16 + 64 + 16;
+// per-warp shared memory: bm[MAXT][WORDS] u32 | pre[MAXT][WORDS] u16 | pool[POOL] (doc, weight) | list[lcap] u64 |
+//                         sbase[MAXT] i64 | sqv[MAXT] f64 | spoff[MAXT] i32 | spcnt[MAXT] i32 | clist[32] u16 | cnt
+__host__ __device__ inline size_t bx_warp_bytes(int maxt, int subs, int lcap) {
+    return (size_t)maxt * 64 * subs * 6 + (size_t)128 * subs * 8 + (size_t)lcap * 8 + (size_t)maxt * 24 + 64 + 16;
+}
+
+// words of one stored document map: the sub-tile count is rounded up to 4 so a tile of any SUBS stays inside its row
+int64_t bm25x_row_words(int64_t n_docs) {
+    const int64_t ns = (n_docs + BM25_SUB - 1) / BM25_SUB;
+    return (ns + 3) / 4 * 4 * BX_WORDS;
 }
 
 // ------------------------------------------------------------------------------------ index build
@@ -107,8 +121,7 @@ cudaError_t bm25x_build_wrange(const int64_t* term_ptr, const uint2* post, int64
 cudaError_t bm25x_build_bitmaps(const int64_t* term_ptr, const uint2* post, const int32_t* dense_terms, int n_dense,
                                 int64_t n_docs, uint32_t* bits, cudaStream_t st) {
     if (n_dense == 0) return cudaSuccess;
-    const int64_t ns = (n_docs + BM25_SUB - 1) / BM25_SUB;
-    const int64_t words_per_row = ns * BX_WORDS;
+    const int64_t words_per_row = bm25x_row_words(n_docs);
     cudaError_t e = cudaMemsetAsync(bits, 0, (size_t)n_dense * words_per_row * 4, st);
     if (e != cudaSuccess) return e;
     for (int r0 = 0; r0 < n_dense; r0 += 32768) {
@@ -122,13 +135,14 @@ cudaError_t bm25x_build_bitmaps(const int64_t* term_ptr, const uint2* post, cons
 }
 
 // ------------------------------------------------------------------------------------ scan
-__device__ __forceinline__ void cp_async8(void* smem_dst, const void* gsrc) {
+template <int BYTES>
+__device__ __forceinline__ void cp_async(void* smem_dst, const void* gsrc) {
     const uint32_t d = (uint32_t)__cvta_generic_to_shared(smem_dst);
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(d), "l"(gsrc) : "memory");
+    asm volatile("cp.async.ca.shared.global [%0], [%1], %2;" ::"r"(d), "l"(gsrc), "n"(BYTES) : "memory");
 }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
-template <int MAXT>
+template <int MAXT, int SUBS>
 __global__ void __launch_bounds__(BX_THREADS, 1)
 bm25x_scan_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict__ post,
                   const uint32_t* __restrict__ sub_off, const int32_t* __restrict__ bm_row,
@@ -137,7 +151,8 @@ bm25x_scan_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict_
                   const double* __restrict__ q_vals, int B, const uint32_t* __restrict__ mask, int k_sel, int lcap,
                   int nw, uint64_t* __restrict__ part, int splits, int* __restrict__ work_counter,
                   uint32_t* __restrict__ gthr, uint32_t* __restrict__ coarse, uint32_t* __restrict__ fine) {
-    constexpr int PLANES = (MAXT == 8) ? 4 : (MAXT == 16 ? 5 : 6);     // counts 0..MAXT
+    using C = BxCfg<MAXT, SUBS>;
+    constexpr int WPL = C::WPL, WORDS = C::WORDS, POOL = C::POOL, PLANES = C::PLANES;
     extern __shared__ __align__(16) uint8_t smem_raw[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     __shared__ int s_item;
@@ -159,18 +174,22 @@ bm25x_scan_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict_
         return;
     }
 
-    uint8_t* slab = smem_raw + (size_t)warp * bx_warp_bytes(MAXT, lcap);
-    uint32_t* bm = reinterpret_cast<uint32_t*>(slab);                                   // [MAXT][64]
-    uint16_t* pre = reinterpret_cast<uint16_t*>(slab + (size_t)MAXT * BX_WORDS * 4);    // [MAXT][64]
-    uint2* stage = reinterpret_cast<uint2*>(slab + (size_t)MAXT * BX_WORDS * 6);        // [MAXT][BX_STAGE]
-    uint64_t* list = reinterpret_cast<uint64_t*>(stage + MAXT * BX_STAGE);
+    uint8_t* slab = smem_raw + (size_t)warp * bx_warp_bytes(MAXT, SUBS, lcap);
+    uint32_t* bm = reinterpret_cast<uint32_t*>(slab);                                 // [MAXT][WORDS]
+    uint16_t* pre = reinterpret_cast<uint16_t*>(slab + (size_t)MAXT * WORDS * 4);     // [MAXT][WORDS]
+    uint2* pool = reinterpret_cast<uint2*>(slab + (size_t)MAXT * WORDS * 6);          // [POOL]
+    uint64_t* list = reinterpret_cast<uint64_t*>(pool + POOL);
     int64_t* sbase = reinterpret_cast<int64_t*>(list + lcap);
     double* sqv = reinterpret_cast<double*>(sbase + MAXT);
-    uint16_t* clist = reinterpret_cast<uint16_t*>(sqv + MAXT);
+    int* spoff = reinterpret_cast<int*>(sqv + MAXT);
+    int* spcnt = spoff + MAXT;
+    uint16_t* clist = reinterpret_cast<uint16_t*>(spcnt + MAXT);
     int* cntp = reinterpret_cast<int*>(clist + 32);
     const int ns = (int)((n_docs + BM25_SUB - 1) / BM25_SUB);
     const int ns1 = ns + 1;
-    const int ns_per_split = (ns + splits - 1) / splits;
+    const int nt = (ns + SUBS - 1) / SUBS;                    // tiles of SUBS sub-tiles
+    const int nt_per_split = (nt + splits - 1) / splits;
+    const size_t row_words = (size_t)((ns + 3) / 4 * 4) * BX_WORDS;
     const int n_items = splits * B;
     const double sentinel = __longlong_as_double((long long)BX_SENTINEL);
 
@@ -183,7 +202,7 @@ bm25x_scan_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict_
         const int split = item / B, q = item - split * B;
         const int qb = q_ptr[q];
         const int nq = min(q_ptr[q + 1] - qb, MAXT);      // the launcher guarantees nq <= MAXT
-        const int j_begin = split * ns_per_split, j_end = min(ns, j_begin + ns_per_split);
+        const int j_begin = split * nt_per_split, j_end = min(nt, j_begin + nt_per_split);
         uint64_t thr = 0ull;
         double pre_local = -INFINITY;
         if (lane == 0) *cntp = 0;
@@ -215,22 +234,28 @@ bm25x_scan_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict_
         }
         su *= 1.0 + 1e-12;
         const unsigned sparse_terms = __ballot_sync(0xFFFFFFFFu, t0 >= 0 && row0 < 0);
+        const uint32_t* so = sub_off + (size_t)max(t0, 0) * ns1;     // this lane's row of the offset table
         __syncwarp();
 
         uint32_t lo_nx = 0, hi_nx = 0;
         if (t0 >= 0 && j_begin + warp < j_end) {
-            lo_nx = __ldg(sub_off + (size_t)t0 * ns1 + (j_begin + warp));
-            hi_nx = __ldg(sub_off + (size_t)t0 * ns1 + (j_begin + warp) + 1);
+            const int s_lo = (j_begin + warp) * SUBS;
+            lo_nx = __ldg(so + s_lo);
+            hi_nx = __ldg(so + min(ns, s_lo + SUBS));
         }
+        uint32_t g_seen = 0u;
+        double pre_g = -INFINITY;
 #pragma unroll 1
         for (int j = j_begin + warp; j < j_end; j += nw) {
-            const uint32_t sub_base = (uint32_t)j * BM25_SUB;
+            const uint32_t tile_base = (uint32_t)j * C::TILE;
             const uint32_t g = __ldcg(gthr + q);
-            double pre_eff = (g != 0u) ? fmax(pre_local, prefilter_of_score(ordered_f32(g))) : pre_local;
+            if (g != g_seen) { g_seen = g; pre_g = prefilter_of_score(ordered_f32(g)); }
+            double pre_eff = fmax(pre_local, pre_g);
             const uint32_t lo_cur = lo_nx, hi_cur = hi_nx;
             if (t0 >= 0 && j + nw < j_end) {
-                lo_nx = __ldg(sub_off + (size_t)t0 * ns1 + (j + nw));
-                hi_nx = __ldg(sub_off + (size_t)t0 * ns1 + (j + nw) + 1);
+                const int s_lo = (j + nw) * SUBS;
+                lo_nx = __ldg(so + s_lo);
+                hi_nx = __ldg(so + min(ns, s_lo + SUBS));
             }
             const uint32_t n = (t0 >= 0) ? hi_cur - lo_cur : 0u;
             const unsigned active = __ballot_sync(0xFFFFFFFFu, n != 0u);
@@ -238,59 +263,88 @@ bm25x_scan_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict_
             const int m = 1 + __popc(__ballot_sync(0xFFFFFFFFu, lane < nq && su <= pre_eff));
             if (__popc(active) < m) continue;
 
-            // ---- phase 1: the (term, sub-tile) document maps into shared memory.  Stored maps and the postings of
+            // ---- phase 1: the (term, tile) document maps into shared memory.  Stored maps and the postings of
             //      map-less terms are all fetched with cp.async before anything waits: one memory round trip
             const int64_t base_cur = tp0 + lo_cur;
-            if (n != 0u) sbase[lane] = base_cur;
+            const bool is_sp = n != 0u && row0 < 0;
+            int poff = is_sp ? (int)n : 0;                       // -> exclusive prefix: slot of this term in the pool
+#pragma unroll
+            for (int off = 1; off < MAXT; off <<= 1) {
+                const int o = __shfl_up_sync(0xFFFFFFFFu, poff, off);
+                if (lane >= off) poff += o;
+            }
+            poff -= is_sp ? (int)n : 0;
+            const int pcnt = is_sp ? max(0, min((int)n, POOL - poff)) : 0;
+            if (n != 0u) { sbase[lane] = base_cur; spoff[lane] = poff; spcnt[lane] = pcnt; }
             for (unsigned a = active; a; a &= a - 1) {
                 const int l = __ffs(a) - 1;
                 const int row = __shfl_sync(0xFFFFFFFFu, row0, l);
-                uint32_t* dst = bm + l * BX_WORDS + 2 * lane;
+                uint32_t* dst = bm + l * WORDS + WPL * lane;
                 if (row >= 0) {
-                    cp_async8(dst, bits + ((size_t)row * ns + j) * BX_WORDS + 2 * lane);
+                    const uint32_t* src = bits + (size_t)row * row_words + (size_t)j * WORDS + WPL * lane;
+                    if (SUBS == 1) cp_async<8>(dst, src);
+                    else {
+#pragma unroll
+                        for (int w = 0; w < WPL; w += 4) cp_async<16>(dst + w, src + w);
+                    }
                 } else {
-                    *reinterpret_cast<uint2*>(dst) = make_uint2(0u, 0u);
-                    const uint32_t n_l = __shfl_sync(0xFFFFFFFFu, n, l);
+#pragma unroll
+                    for (int w = 0; w < WPL; w += 2) *reinterpret_cast<uint2*>(dst + w) = make_uint2(0u, 0u);
+                    const int c_l = __shfl_sync(0xFFFFFFFFu, pcnt, l);
+                    uint2* pd = pool + __shfl_sync(0xFFFFFFFFu, poff, l);
                     const uint2* src = post + __shfl_sync(0xFFFFFFFFu, base_cur, l);
-                    if ((uint32_t)lane < n_l) cp_async8(stage + l * BX_STAGE + lane, src + lane);
-                    if ((uint32_t)lane + 32u < n_l) cp_async8(stage + l * BX_STAGE + lane + 32, src + lane + 32);
+                    for (int i = lane; i < c_l; i += 32) cp_async<8>(pd + i, src + i);
                 }
             }
             cp_async_wait_all();
             __syncwarp();
             for (unsigned a = active & sparse_terms; a; a &= a - 1) {
                 const int l = __ffs(a) - 1;
-                const uint32_t n_l = __shfl_sync(0xFFFFFFFFu, n, l);
-                for (uint32_t i = lane; i < min(n_l, (uint32_t)BX_STAGE); i += 32) {
-                    const uint32_t dl = stage[l * BX_STAGE + i].x - sub_base;
-                    atomicOr(bm + l * BX_WORDS + (dl >> 5), 1u << (dl & 31));
+                const int n_l = (int)__shfl_sync(0xFFFFFFFFu, n, l);
+                const int c_l = __shfl_sync(0xFFFFFFFFu, pcnt, l);
+                const uint2* pd = pool + __shfl_sync(0xFFFFFFFFu, poff, l);
+                for (int i = lane; i < c_l; i += 32) {
+                    const uint32_t dl = pd[i].x - tile_base;
+                    atomicOr(bm + l * WORDS + (dl >> 5), 1u << (dl & 31));
                 }
-                if (n_l > (uint32_t)BX_STAGE) {            // rare: a locally dense stretch of a map-less term
+                if (n_l > c_l) {                              // rare: the pool is full, read the rest from global
                     const uint2* src = post + __shfl_sync(0xFFFFFFFFu, base_cur, l);
-                    for (uint32_t i = BX_STAGE + lane; i < n_l; i += 32) {
-                        const uint32_t dl = __ldg(&src[i].x) - sub_base;
-                        atomicOr(bm + l * BX_WORDS + (dl >> 5), 1u << (dl & 31));
+                    for (int i = c_l + lane; i < n_l; i += 32) {
+                        const uint32_t dl = __ldg(&src[i].x) - tile_base;
+                        atomicOr(bm + l * WORDS + (dl >> 5), 1u << (dl & 31));
                     }
                 }
             }
             __syncwarp();
 
-            // ---- phase 2: per-word ranks + bit-sliced count of the maps (lane owns words 2*lane, 2*lane+1);
-            //      two terms share one warp scan (12-bit counts packed in the halves of a register)
-            uint32_t c0[PLANES], c1[PLANES];
+            // ---- phase 2: per-word ranks + bit-sliced count of the maps (lane owns words WPL*lane ..);
+            //      two terms share one warp scan (13-bit counts packed in the halves of a register)
+            uint32_t cn[PLANES][WPL];
 #pragma unroll
-            for (int p = 0; p < PLANES; ++p) { c0[p] = 0u; c1[p] = 0u; }
+            for (int p = 0; p < PLANES; ++p)
+#pragma unroll
+                for (int w = 0; w < WPL; ++w) cn[p][w] = 0u;
             for (unsigned a = active; a;) {
                 const int la = __ffs(a) - 1;
                 a &= a - 1;
                 const bool two = a != 0u;
                 const int lb = two ? __ffs(a) - 1 : la;
                 a &= a - 1;
-                const uint2 wa = *reinterpret_cast<const uint2*>(bm + la * BX_WORDS + 2 * lane);
-                uint2 wb = *reinterpret_cast<const uint2*>(bm + lb * BX_WORDS + 2 * lane);
-                if (!two) wb = make_uint2(0u, 0u);
-                const uint32_t pa0 = __popc(wa.x), pb0 = __popc(wb.x);
-                const uint32_t own = (pa0 + __popc(wa.y)) | ((pb0 + __popc(wb.y)) << 16);
+                uint32_t wa[WPL], wb[WPL];
+#pragma unroll
+                for (int w = 0; w < WPL; w += 2) {
+                    const uint2 va = *reinterpret_cast<const uint2*>(bm + la * WORDS + WPL * lane + w);
+                    const uint2 vb = *reinterpret_cast<const uint2*>(bm + lb * WORDS + WPL * lane + w);
+                    wa[w] = va.x; wa[w + 1] = va.y;
+                    wb[w] = two ? vb.x : 0u; wb[w + 1] = two ? vb.y : 0u;
+                }
+                uint32_t loc[WPL];                       // packed exclusive prefix inside the lane
+                uint32_t own = 0u;
+#pragma unroll
+                for (int w = 0; w < WPL; ++w) {
+                    loc[w] = own;
+                    own += (uint32_t)__popc(wa[w]) | ((uint32_t)__popc(wb[w]) << 16);
+                }
                 uint32_t inc = own;
 #pragma unroll
                 for (int off = 1; off < 32; off <<= 1) {
@@ -298,40 +352,46 @@ bm25x_scan_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict_
                     if (lane >= off) inc += o;
                 }
                 const uint32_t ex = inc - own;
-                const uint32_t exa = ex & 0xFFFFu, exb = ex >> 16;
-                *reinterpret_cast<uint32_t*>(pre + la * BX_WORDS + 2 * lane) = exa | ((exa + pa0) << 16);
-                if (two) *reinterpret_cast<uint32_t*>(pre + lb * BX_WORDS + 2 * lane) = exb | ((exb + pb0) << 16);
-                uint32_t k0 = wa.x, k1 = wa.y;
 #pragma unroll
-                for (int p = 0; p < PLANES; ++p) {
-                    const uint32_t t0_ = c0[p] & k0, t1_ = c1[p] & k1;
-                    c0[p] ^= k0; c1[p] ^= k1;
-                    k0 = t0_; k1 = t1_;
+                for (int w = 0; w < WPL; w += 2) {
+                    const uint32_t r0 = ex + loc[w], r1 = ex + loc[w + 1];
+                    *reinterpret_cast<uint32_t*>(pre + la * WORDS + WPL * lane + w) = (r0 & 0xFFFFu) | (r1 << 16);
+                    if (two) *reinterpret_cast<uint32_t*>(pre + lb * WORDS + WPL * lane + w) = (r0 >> 16) | (r1 & 0xFFFF0000u);
                 }
-                k0 = wb.x; k1 = wb.y;
 #pragma unroll
-                for (int p = 0; p < PLANES; ++p) {
-                    const uint32_t t0_ = c0[p] & k0, t1_ = c1[p] & k1;
-                    c0[p] ^= k0; c1[p] ^= k1;
-                    k0 = t0_; k1 = t1_;
+                for (int w = 0; w < WPL; ++w) {
+                    uint32_t k = wa[w];
+#pragma unroll
+                    for (int p = 0; p < PLANES; ++p) { const uint32_t t_ = cn[p][w] & k; cn[p][w] ^= k; k = t_; }
+                    k = wb[w];
+#pragma unroll
+                    for (int p = 0; p < PLANES; ++p) { const uint32_t t_ = cn[p][w] & k; cn[p][w] ^= k; k = t_; }
                 }
             }
-            // count >= m, bit-slice compare from the top plane down
-            uint32_t gt0 = 0u, gt1 = 0u, eq0 = 0xFFFFFFFFu, eq1 = 0xFFFFFFFFu;
+            // count >= m, bit-slice compare from the top plane down; then the payload filter
+            uint32_t cand[WPL];
+            int own_c = 0;
 #pragma unroll
-            for (int p = PLANES - 1; p >= 0; --p) {
-                if ((m >> p) & 1) { eq0 &= c0[p]; eq1 &= c1[p]; }
-                else { gt0 |= eq0 & c0[p]; gt1 |= eq1 & c1[p]; eq0 &= ~c0[p]; eq1 &= ~c1[p]; }
+            for (int w = 0; w < WPL; ++w) {
+                uint32_t gt = 0u, eq = 0xFFFFFFFFu;
+#pragma unroll
+                for (int p = PLANES - 1; p >= 0; --p) {
+                    if ((m >> p) & 1) eq &= cn[p][w];
+                    else { gt |= eq & cn[p][w]; eq &= ~cn[p][w]; }
+                }
+                cand[w] = (m >> PLANES) ? 0u : (gt | eq);
             }
-            uint32_t cand0 = gt0 | eq0, cand1 = gt1 | eq1;
-            if (m >> PLANES) { cand0 = 0u; cand1 = 0u; }
             if (mask != nullptr) {
-                const uint2 mw = __ldg(reinterpret_cast<const uint2*>(mask + (sub_base >> 5)) + lane);
-                cand0 &= mw.x; cand1 &= mw.y;
+#pragma unroll
+                for (int w = 0; w < WPL; w += 2) {
+                    const uint2 mw = __ldg(reinterpret_cast<const uint2*>(mask + (tile_base >> 5) + WPL * lane + w));
+                    cand[w] &= mw.x; cand[w + 1] &= mw.y;
+                }
             }
+#pragma unroll
+            for (int w = 0; w < WPL; ++w) own_c += __popc(cand[w]);
 
             // ---- phase 3: score the survivors, 32 at a time (compacted through clist so every lane has one)
-            const int own_c = __popc(cand0) + __popc(cand1);
             int pos = own_c;                                  // -> exclusive prefix of own_c
 #pragma unroll
             for (int off = 1; off < 32; off <<= 1) {
@@ -346,12 +406,14 @@ bm25x_scan_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict_
                     warp_compact(list, cntp, lcap, k_sel, thr, lane);
                     if (thr != 0ull) { pre_local = prefilter_of_score(key_score(thr)); pre_eff = fmax(pre_eff, pre_local); }
                 }
-                while ((cand0 | cand1) != 0u && pos < r0 + 32) {      // this lane's candidates that fall in the window
-                    int dl;
-                    if (cand0) { dl = __ffs(cand0) - 1 + 64 * lane; cand0 &= cand0 - 1; }
-                    else { dl = __ffs(cand1) - 1 + 64 * lane + 32; cand1 &= cand1 - 1; }
-                    clist[pos - r0] = (uint16_t)dl;
-                    ++pos;
+                // this lane's candidates that fall in the window [r0, r0 + 32), in document order
+#pragma unroll
+                for (int w = 0; w < WPL; ++w) {
+                    while (cand[w] != 0u && pos < r0 + 32) {
+                        clist[pos - r0] = (uint16_t)(__ffs(cand[w]) - 1 + 32 * (WPL * lane + w));
+                        cand[w] &= cand[w] - 1;
+                        ++pos;
+                    }
                 }
                 __syncwarp();
                 const bool mine = r0 + lane < total;
@@ -359,31 +421,31 @@ bm25x_scan_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict_
                 const int word = dl >> 5, bit = dl & 31;
                 const uint32_t below = (1u << bit) - 1u;
                 float wt[MAXT];
-                unsigned hit = 0u, from_stage = 0u;
                 uint32_t rk[MAXT];
+                unsigned hit = 0u, from_pool = 0u;
 #pragma unroll
                 for (int l = 0; l < MAXT; ++l) {
-                    const uint32_t wv = bm[l * BX_WORDS + word];
+                    const uint32_t wv = bm[l * WORDS + word];
                     const bool h = mine && ((active >> l) & 1u) && ((wv >> bit) & 1u);
-                    rk[l] = (uint32_t)pre[l * BX_WORDS + word] + __popc(wv & below);
-                    const bool st = h && ((sparse_terms >> l) & 1u) && rk[l] < (uint32_t)BX_STAGE;
+                    rk[l] = (uint32_t)pre[l * WORDS + word] + __popc(wv & below);
+                    const bool st = h && ((sparse_terms >> l) & 1u) && (int)rk[l] < spcnt[l];
                     const bool gl = h && !st;
                     // unconditional load (a dummy, L1-resident address when this term misses): the MAXT loads issue
                     // back to back instead of one dependent branch per term
                     const uint2* ap = gl ? post + sbase[l] + rk[l] : post;
                     wt[l] = __uint_as_float(__ldg(&ap->y));
                     hit |= (h ? 1u : 0u) << l;
-                    from_stage |= (st ? 1u : 0u) << l;
+                    from_pool |= (st ? 1u : 0u) << l;
                 }
 #pragma unroll
                 for (int l = 0; l < MAXT; ++l)
-                    if ((from_stage >> l) & 1u) wt[l] = __uint_as_float(stage[l * BX_STAGE + rk[l]].y);
+                    if ((from_pool >> l) & 1u) wt[l] = __uint_as_float(pool[spoff[l] + rk[l]].y);
                 double acc = sentinel;
 #pragma unroll
                 for (int l = 0; l < MAXT; ++l)
                     if ((hit >> l) & 1u) acc = __dadd_rn(acc, __dmul_rn(sqv[l], (double)wt[l]));
                 if (mine && acc > pre_eff) {
-                    const uint32_t dg = sub_base + (uint32_t)dl;
+                    const uint32_t dg = tile_base + (uint32_t)dl;
                     const uint64_t key = make_key((float)acc, dg);
                     if (key > thr && (uint32_t)(key >> 32) >= g) {
                         list[atomicAdd(cntp, 1)] = key;
@@ -410,16 +472,28 @@ static int bx_lcap(int k_sel) {
 
 static int bx_maxt(int max_terms) { return max_terms <= 8 ? 8 : (max_terms <= 16 ? 16 : 32); }
 
+// sub-tiles per visit: 2 unless BRAG_BX_SUBS says otherwise (tuning knob, read once)
+static int bx_subs() {
+    static int subs = [] {
+        const char* e = getenv("BRAG_BX_SUBS");
+        const int v = e ? atoi(e) : 2;
+        return (v == 1 || v == 2 || v == 4) ? v : 2;
+    }();
+    return subs;
+}
+
 bool bm25x_supported(int max_terms, int k_sel) { return max_terms >= 0 && max_terms <= 32 && k_sel <= 512; }
 
 Bm25Plan bm25x_plan(int64_t n_docs, int B, int k_sel, int max_terms, int num_sms) {
     Bm25Plan p;
+    const int subs = bx_subs();
     const int ns = (int)((n_docs + BM25_SUB - 1) / BM25_SUB);
-    p.workers = (int)std::min<size_t>(BX_MAX_WORKERS, BX_SMEM_MAX / bx_warp_bytes(bx_maxt(max_terms), bx_lcap(k_sel)));
-    p.workers = std::max(1, std::min(p.workers, ns));
+    const int nt = (ns + subs - 1) / subs;
+    p.workers = (int)std::min<size_t>(BX_MAX_WORKERS, BX_SMEM_MAX / bx_warp_bytes(bx_maxt(max_terms), subs, bx_lcap(k_sel)));
+    p.workers = std::max(1, std::min(p.workers, nt));
     const int resident = num_sms;
     int splits = (resident * 8 + B - 1) / B;
-    int max_splits = (ns + p.workers - 1) / p.workers;
+    int max_splits = (nt + p.workers - 1) / p.workers;
     if (splits > max_splits) splits = max_splits;
     if (splits < 1) splits = 1;
     if (splits > 64) splits = 64;
@@ -435,32 +509,44 @@ Bm25Plan bm25x_plan(int64_t n_docs, int B, int k_sel, int max_terms, int num_sms
     return p;
 }
 
-template <int MAXT>
-static cudaError_t bx_launch(const int64_t* term_ptr, const uint2* post, const uint32_t* sub_off, const int32_t* bm_row,
-                             const uint32_t* bits, const float2* wrange, int64_t V, int64_t n_docs,
-                             const int32_t* q_ptr, const int32_t* q_terms, const double* q_vals, int B,
-                             const uint32_t* mask, int k_sel, uint64_t* part, const Bm25Plan& plan, void* scratch,
-                             cudaStream_t st) {
-    const int lcap = bx_lcap(k_sel);
-    const size_t smem = bx_warp_bytes(MAXT, lcap) * plan.workers;
+struct BxArgs {
+    const int64_t* term_ptr; const uint2* post; const uint32_t* sub_off; const int32_t* bm_row; const uint32_t* bits;
+    const float2* wrange; int64_t V, n_docs; const int32_t *q_ptr, *q_terms; const double* q_vals; int B;
+    const uint32_t* mask; int k_sel; uint64_t* part; const Bm25Plan* plan; void* scratch; cudaStream_t st;
+};
+
+template <int MAXT, int SUBS>
+static cudaError_t bx_launch(const BxArgs& a) {
+    const Bm25Plan& plan = *a.plan;
+    const int lcap = bx_lcap(a.k_sel);
+    const size_t smem = bx_warp_bytes(MAXT, SUBS, lcap) * plan.workers;
     static size_t attr_smem = 0;
     if (smem > attr_smem) {
-        cudaError_t e = cudaFuncSetAttribute(bm25x_scan_kernel<MAXT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        cudaError_t e = cudaFuncSetAttribute(bm25x_scan_kernel<MAXT, SUBS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              (int)smem);
         if (e != cudaSuccess) return e;
         attr_smem = smem;
     }
-    uint8_t* sp = reinterpret_cast<uint8_t*>(scratch);
+    uint8_t* sp = reinterpret_cast<uint8_t*>(a.scratch);
     int* work_counter = reinterpret_cast<int*>(sp);
     uint32_t* gthr = reinterpret_cast<uint32_t*>(sp + 256);
     uint32_t* coarse = reinterpret_cast<uint32_t*>(sp + 256 + plan.gthr_bytes);
     uint32_t* fine = reinterpret_cast<uint32_t*>(sp + 256 + plan.gthr_bytes + plan.coarse_bytes);
-    cudaError_t e = cudaMemsetAsync(scratch, 0, plan.scratch_bytes, st);
+    cudaError_t e = cudaMemsetAsync(a.scratch, 0, plan.scratch_bytes, a.st);
     if (e != cudaSuccess) return e;
-    bm25x_scan_kernel<MAXT><<<plan.grid, (plan.workers + 1) * 32, smem, st>>>(
-        term_ptr, post, sub_off, bm_row, bits, wrange, V, n_docs, q_ptr, q_terms, q_vals, B, mask, k_sel, lcap,
-        plan.workers, part, plan.splits, work_counter, gthr, coarse, fine);
+    bm25x_scan_kernel<MAXT, SUBS><<<plan.grid, (plan.workers + 1) * 32, smem, a.st>>>(
+        a.term_ptr, a.post, a.sub_off, a.bm_row, a.bits, a.wrange, a.V, a.n_docs, a.q_ptr, a.q_terms, a.q_vals, a.B,
+        a.mask, a.k_sel, lcap, plan.workers, a.part, plan.splits, work_counter, gthr, coarse, fine);
     return cudaGetLastError();
+}
+
+template <int MAXT>
+static cudaError_t bx_launch_subs(const BxArgs& a) {
+    switch (bx_subs()) {
+        case 1: return bx_launch<MAXT, 1>(a);
+        case 4: return bx_launch<MAXT, 4>(a);
+        default: return bx_launch<MAXT, 2>(a);
+    }
 }
 
 cudaError_t bm25x_scan(const int64_t* term_ptr, const uint2* post, const uint32_t* sub_off, const int32_t* bm_row,
@@ -468,16 +554,12 @@ cudaError_t bm25x_scan(const int64_t* term_ptr, const uint2* post, const uint32_
                        const int32_t* q_terms, const double* q_vals, int B, int max_terms, const uint32_t* mask,
                        int k_sel, uint64_t* part, const Bm25Plan& plan, void* scratch, cudaStream_t st) {
     if (!bm25x_supported(max_terms, k_sel)) return cudaErrorInvalidValue;
+    const BxArgs a{term_ptr, post, sub_off, bm_row, bits, wrange, V, n_docs, q_ptr, q_terms, q_vals, B,
+                   mask, k_sel, part, &plan, scratch, st};
     switch (bx_maxt(max_terms)) {
-        case 8:
-            return bx_launch<8>(term_ptr, post, sub_off, bm_row, bits, wrange, V, n_docs, q_ptr, q_terms, q_vals, B, mask,
-                                k_sel, part, plan, scratch, st);
-        case 16:
-            return bx_launch<16>(term_ptr, post, sub_off, bm_row, bits, wrange, V, n_docs, q_ptr, q_terms, q_vals, B, mask,
-                                 k_sel, part, plan, scratch, st);
-        default:
-            return bx_launch<32>(term_ptr, post, sub_off, bm_row, bits, wrange, V, n_docs, q_ptr, q_terms, q_vals, B, mask,
-                                 k_sel, part, plan, scratch, st);
+        case 8: return bx_launch_subs<8>(a);
+        case 16: return bx_launch_subs<16>(a);
+        default: return bx_launch_subs<32>(a);
     }
 }
 

@@ -191,8 +191,7 @@ void build_bitmap_index(SparseSpace& s) {
     if (ce == cudaSuccess) ce = cudaMemcpy(&nonfinite, flag, sizeof(int), cudaMemcpyDeviceToHost);
     cudaFree(flag);
     CK(ce);
-    const int64_t ns = (s.n_docs + brag::BM25_SUB - 1) / brag::BM25_SUB;
-    const size_t row_bytes = (size_t)ns * (brag::BM25_SUB / 8);
+    const size_t row_bytes = (size_t)brag::bm25x_row_words(s.n_docs) * 4;
     const int64_t min_df = std::max<int64_t>(32, s.n_docs / 64);
     std::vector<std::pair<int64_t, int32_t>> dense;     // (df, term)
     for (int64_t t = 0; t < s.V; ++t) {
@@ -548,8 +547,8 @@ int brag_mask_set(brag_engine* e, int32_t mask_id, const uint32_t* bits, int64_t
         const size_t words = (size_t)((nbits + 31) / 32);
         if (m.bits) { CK(cudaDeviceSynchronize()); CK(cudaFree(m.bits)); m.bits = nullptr; }
         // padded so a warp's mask-word read past the last group stays in bounds
-        CK(cudaMalloc(&m.bits, (words + 64) * sizeof(uint32_t)));
-        CK(cudaMemset(m.bits, 0, (words + 64) * sizeof(uint32_t)));
+        CK(cudaMalloc(&m.bits, (words + 512) * sizeof(uint32_t)));
+        CK(cudaMemset(m.bits, 0, (words + 512) * sizeof(uint32_t)));
         CK(cudaMemcpy(m.bits, bits, words * sizeof(uint32_t), on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice));
         m.nbits = nbits;
     });

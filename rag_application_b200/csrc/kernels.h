@@ -74,9 +74,10 @@ cudaError_t bm25_scan(const int64_t* term_ptr, const uint2* post, const uint32_t
 // wrange[t] = (min, max) weight of term t; *nonfinite_flag is set when any weight is NaN/Inf
 cudaError_t bm25x_build_wrange(const int64_t* term_ptr, const uint2* post, int64_t V, int64_t nnz, float2* wrange,
                                int* nonfinite_flag, cudaStream_t st);
-// bits: [n_dense][ceil(n_docs / BM25_SUB) * 64] words, bit d of row r = term dense_terms[r] occurs in document d
+// bits: [n_dense][bm25x_row_words(n_docs)] words, bit d of row r = term dense_terms[r] occurs in document d
 cudaError_t bm25x_build_bitmaps(const int64_t* term_ptr, const uint2* post, const int32_t* dense_terms, int n_dense,
                                 int64_t n_docs, uint32_t* bits, cudaStream_t st);
+int64_t bm25x_row_words(int64_t n_docs);     // words per stored map row (sub-tile count rounded up to 4)
 bool bm25x_supported(int max_terms, int k_sel);
 Bm25Plan bm25x_plan(int64_t n_docs, int B, int k_sel, int max_terms, int num_sms);
 // bm_row[t] = bitmap row of term t or -1; max_terms = longest query of the batch (<= 32)
