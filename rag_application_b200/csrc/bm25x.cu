@@ -41,13 +41,14 @@ struct BxCfg {
     static constexpr int WORDS = 64 * SUBS;       // map words per tile
     static constexpr int TILE = BM25_SUB * SUBS;  // documents per tile
     static constexpr int POOL = 128 * SUBS;       // postings of map-less terms staged in shared memory per tile
-    static constexpr int PLANES = (MAXT == 8) ? 4 : (MAXT == 16 ? 5 : 6);     // bit planes of the counts 0..MAXT
+    static constexpr int PLANES = (MAXT == 8) ? 5 : (MAXT == 16 ? 6 : 7);     // bit planes of the counts 0..2*MAXT
 };
 
-// per-warp shared memory: bm[MAXT][WORDS] u32 | pre[MAXT][WORDS] u16 | pool[POOL] (doc, weight) | list[lcap] u64 |
-//                         sbase[MAXT] i64 | sqv[MAXT] f64 | spoff[MAXT] i32 | spcnt[MAXT] i32 | clist[32] u16 | cnt
+// per-warp shared memory: bm[MAXT][WORDS] u32 | bmh[MAXT][WORDS] u32 | pre[MAXT][WORDS] u16 | pool[POOL] (doc, weight) |
+//                         list[lcap] u64 | sbase[MAXT] i64 | sqv[MAXT] f64 | spoff[MAXT] i32 | spcnt[MAXT] i32 |
+//                         clist[32] u16 | cnt
 __host__ __device__ inline size_t bx_warp_bytes(int maxt, int subs, int lcap) {
-    return (size_t)maxt * 64 * subs * 6 + (size_t)128 * subs * 8 + (size_t)lcap * 8 + (size_t)maxt * 24 + 64 + 16;
+    return (size_t)maxt * 64 * subs * 10 + (size_t)128 * subs * 8 + (size_t)lcap * 8 + (size_t)maxt * 24 + 64 + 16;
 }
 
 // words of one stored document map: the sub-tile count is rounded up to 4 so a tile of any SUBS stays inside its row
@@ -93,24 +94,73 @@ __global__ void bm25x_nan_kernel(const uint2* __restrict__ post, int64_t nnz, in
     }
 }
 
+// tau[t]: weight threshold that splits the postings of term t into a "low" class (w <= tau, at least ~70 % of them)
+// and a "high" class: 64-bin histogram over [min, max], tau = upper edge of the first bin whose cumulative count
+// reaches 70 % (tau = max when the term has a single weight).  For BM25 the low class is the tf = 1 postings.
+__global__ void bm25x_tau_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict__ post, int64_t V,
+                                 const float2* __restrict__ wrange, float* __restrict__ tau) {
+    __shared__ unsigned int hist[64];
+    for (int64_t t = blockIdx.x; t < V; t += gridDim.x) {
+        const int64_t lo = term_ptr[t], hi = term_ptr[t + 1];
+        const float2 wr = wrange[t];
+        const float span = wr.y - wr.x;
+        if (threadIdx.x < 64) hist[threadIdx.x] = 0u;
+        __syncthreads();
+        if (span > 0.f && span < 3.0e38f) {
+            const float inv = 64.f / span;
+            for (int64_t i = lo + threadIdx.x; i < hi; i += blockDim.x) {
+                const float w = __uint_as_float(__ldg(&post[i].y));
+                int b = (int)((w - wr.x) * inv);
+                b = min(63, max(0, b));
+                atomicAdd(&hist[b], 1u);
+            }
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            float tv = wr.y;
+            if (span > 0.f && span < 3.0e38f) {
+                const unsigned long long need = (unsigned long long)((hi - lo) * 7 / 10);
+                unsigned long long cum = 0;
+                for (int b = 0; b < 64; ++b) {
+                    cum += hist[b];
+                    if (cum >= need) {
+                        // upper edge of the bin; the class test is w > tau everywhere, so rounding here is harmless
+                        tv = (b >= 63) ? wr.y : wr.x + span * (float)(b + 1) / 64.f;
+                        break;
+                    }
+                }
+            }
+            tau[t] = fminf(tv, wr.y);
+        }
+        __syncthreads();
+    }
+}
+
+// present map (every posting) and high map (postings with w > tau) of the dense terms
 __global__ void bm25x_bitmap_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict__ post,
-                                    const int32_t* __restrict__ dense_terms, int64_t words_per_row,
-                                    uint32_t* __restrict__ bits) {
+                                    const int32_t* __restrict__ dense_terms, const float* __restrict__ tau,
+                                    int64_t words_per_row, uint32_t* __restrict__ bits, uint32_t* __restrict__ bits_hi) {
     const int row = blockIdx.y;
     const int64_t t = dense_terms[row];
     const int64_t lo = term_ptr[t], hi = term_ptr[t + 1];
+    const float tv = tau[t];
     uint32_t* out = bits + (size_t)row * words_per_row;
+    uint32_t* out_hi = bits_hi + (size_t)row * words_per_row;
     for (int64_t i = lo + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += (int64_t)gridDim.x * blockDim.x) {
-        const uint32_t d = __ldg(&post[i].x);
-        atomicOr(out + (d >> 5), 1u << (d & 31));
+        const uint2 p = __ldg(&post[i]);
+        atomicOr(out + (p.x >> 5), 1u << (p.x & 31));
+        if (__uint_as_float(p.y) > tv) atomicOr(out_hi + (p.x >> 5), 1u << (p.x & 31));
     }
 }
 
 cudaError_t bm25x_build_wrange(const int64_t* term_ptr, const uint2* post, int64_t V, int64_t nnz, float2* wrange,
-                               int* nonfinite_flag, cudaStream_t st) {
+                               float* tau, int* nonfinite_flag, cudaStream_t st) {
     if (V == 0) return cudaSuccess;
     bm25x_wrange_kernel<<<(unsigned)std::min<int64_t>(V, 148 * 16), 256, 0, st>>>(term_ptr, post, V, wrange);
     cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+    bm25x_tau_kernel<<<(unsigned)std::min<int64_t>(V, 148 * 16), 256, 0, st>>>(term_ptr, post, V, wrange, tau);
+    e = cudaGetLastError();
     if (e != cudaSuccess) return e;
     e = cudaMemsetAsync(nonfinite_flag, 0, sizeof(int), st);
     if (e != cudaSuccess || nnz == 0) return e;
@@ -119,15 +169,18 @@ cudaError_t bm25x_build_wrange(const int64_t* term_ptr, const uint2* post, int64
 }
 
 cudaError_t bm25x_build_bitmaps(const int64_t* term_ptr, const uint2* post, const int32_t* dense_terms, int n_dense,
-                                int64_t n_docs, uint32_t* bits, cudaStream_t st) {
+                                const float* tau, int64_t n_docs, uint32_t* bits, uint32_t* bits_hi, cudaStream_t st) {
     if (n_dense == 0) return cudaSuccess;
     const int64_t words_per_row = bm25x_row_words(n_docs);
     cudaError_t e = cudaMemsetAsync(bits, 0, (size_t)n_dense * words_per_row * 4, st);
     if (e != cudaSuccess) return e;
+    e = cudaMemsetAsync(bits_hi, 0, (size_t)n_dense * words_per_row * 4, st);
+    if (e != cudaSuccess) return e;
     for (int r0 = 0; r0 < n_dense; r0 += 32768) {
         const int rows = std::min(32768, n_dense - r0);
-        bm25x_bitmap_kernel<<<dim3(64, rows), 256, 0, st>>>(term_ptr, post, dense_terms + r0, words_per_row,
-                                                           bits + (size_t)r0 * words_per_row);
+        bm25x_bitmap_kernel<<<dim3(64, rows), 256, 0, st>>>(term_ptr, post, dense_terms + r0, tau, words_per_row,
+                                                           bits + (size_t)r0 * words_per_row,
+                                                           bits_hi + (size_t)r0 * words_per_row);
         e = cudaGetLastError();
         if (e != cudaSuccess) return e;
     }
@@ -146,7 +199,8 @@ template <int MAXT, int SUBS>
 __global__ void __launch_bounds__(BX_THREADS, 1)
 bm25x_scan_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict__ post,
                   const uint32_t* __restrict__ sub_off, const int32_t* __restrict__ bm_row,
-                  const uint32_t* __restrict__ bits, const float2* __restrict__ wrange, int64_t V, int64_t n_docs,
+                  const uint32_t* __restrict__ bits, const uint32_t* __restrict__ bits_hi,
+                  const float2* __restrict__ wrange, const float* __restrict__ tau, int64_t V, int64_t n_docs,
                   const int32_t* __restrict__ q_ptr, const int32_t* __restrict__ q_terms,
                   const double* __restrict__ q_vals, int B, const uint32_t* __restrict__ mask, int k_sel, int lcap,
                   int nw, uint64_t* __restrict__ part, int splits, int* __restrict__ work_counter,
@@ -175,9 +229,10 @@ bm25x_scan_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict_
     }
 
     uint8_t* slab = smem_raw + (size_t)warp * bx_warp_bytes(MAXT, SUBS, lcap);
-    uint32_t* bm = reinterpret_cast<uint32_t*>(slab);                                 // [MAXT][WORDS]
-    uint16_t* pre = reinterpret_cast<uint16_t*>(slab + (size_t)MAXT * WORDS * 4);     // [MAXT][WORDS]
-    uint2* pool = reinterpret_cast<uint2*>(slab + (size_t)MAXT * WORDS * 6);          // [POOL]
+    uint32_t* bm = reinterpret_cast<uint32_t*>(slab);                                 // [MAXT][WORDS] present maps
+    uint32_t* bmh = bm + MAXT * WORDS;                                                // [MAXT][WORDS] high maps
+    uint16_t* pre = reinterpret_cast<uint16_t*>(slab + (size_t)MAXT * WORDS * 8);     // [MAXT][WORDS]
+    uint2* pool = reinterpret_cast<uint2*>(slab + (size_t)MAXT * WORDS * 10);         // [POOL]
     uint64_t* list = reinterpret_cast<uint64_t*>(pool + POOL);
     int64_t* sbase = reinterpret_cast<int64_t*>(list + lcap);
     double* sqv = reinterpret_cast<double*>(sbase + MAXT);
@@ -209,7 +264,8 @@ bm25x_scan_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict_
 
         // ---- per-query term setup: lane l < nq owns term l
         int t0 = -1, row0 = -1;
-        double qv0 = 0.0, ub = 0.0;
+        double qv0 = 0.0, ua = 0.0, ue = 0.0;     // bound of a low-class posting; extra of a high-class one
+        float tau0 = 0.f;
         int64_t tp0 = 0;
         if (lane < nq) {
             const int t = q_terms[qb + lane];
@@ -218,21 +274,33 @@ bm25x_scan_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict_
                 qv0 = q_vals[qb + lane];
                 tp0 = __ldg(term_ptr + t);
                 row0 = __ldg(bm_row + t);
+                tau0 = __ldg(tau + t);
                 const float2 wr = __ldg(wrange + t);
-                ub = fmax(0.0, fmax(qv0 * (double)wr.x, qv0 * (double)wr.y));
-                if (!(ub == ub)) ub = INFINITY;           // NaN query value: never prune on this term
-                ub *= 1.0 + 1e-12;                         // slack for the rounding of the float64 sums
+                // low class: w in [min, tau]; high class: w in (tau, max]
+                ua = fmax(0.0, fmax(qv0 * (double)wr.x, qv0 * (double)tau0));
+                const double uh = fmax(ua, qv0 * (double)wr.y);
+                ue = uh - ua;
+                if (!(ua == ua) || !(ue == ue)) { ua = INFINITY; ue = 0.0; }   // NaN query value: never prune on this term
+                ua *= 1.0 + 1e-12;                         // slack for the rounding of the float64 sums
+                ue *= 1.0 + 1e-12;
             }
         }
         if (lane < MAXT) sqv[lane] = qv0;
-        // S_c for c = rank + 1: sum of the bounds that sort at or before this lane's (descending, ties by lane)
-        double su = 0.0;
+        // The 2*nq bounds {ua_l} U {ue_l} sorted descending and prefix-summed give S_c; a document with c1 terms
+        // present, c2 of them high, scores at most S_(c1+c2).  sa / se = S at the rank of this lane's ua / ue
+        // (ties broken by kind, then lane).
+        double sa = 0.0, se = 0.0;
 #pragma unroll 1
         for (int o = 0; o < nq; ++o) {
-            const double uo = __shfl_sync(0xFFFFFFFFu, ub, o);
-            if (uo > ub || (uo == ub && o <= lane)) su += uo;
+            const double ao = __shfl_sync(0xFFFFFFFFu, ua, o);
+            const double eo = __shfl_sync(0xFFFFFFFFu, ue, o);
+            if (ao > ua || (ao == ua && o <= lane)) sa += ao;
+            if (eo > ua) sa += eo;
+            if (ao >= ue) se += ao;
+            if (eo > ue || (eo == ue && o <= lane)) se += eo;
         }
-        su *= 1.0 + 1e-12;
+        sa *= 1.0 + 1e-12;
+        se *= 1.0 + 1e-12;
         const unsigned sparse_terms = __ballot_sync(0xFFFFFFFFu, t0 >= 0 && row0 < 0);
         const uint32_t* so = sub_off + (size_t)max(t0, 0) * ns1;     // this lane's row of the offset table
         __syncwarp();
@@ -259,9 +327,10 @@ bm25x_scan_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict_
             }
             const uint32_t n = (t0 >= 0) ? hi_cur - lo_cur : 0u;
             const unsigned active = __ballot_sync(0xFFFFFFFFu, n != 0u);
-            // a document needs at least m of the query's terms to beat the bound
-            const int m = 1 + __popc(__ballot_sync(0xFFFFFFFFu, lane < nq && su <= pre_eff));
-            if (__popc(active) < m) continue;
+            // a document needs (terms present) + (terms in their high class) >= m to beat the bound
+            const int m = 1 + __popc(__ballot_sync(0xFFFFFFFFu, lane < nq && sa <= pre_eff)) +
+                          __popc(__ballot_sync(0xFFFFFFFFu, lane < nq && se <= pre_eff));
+            if (2 * __popc(active) < m) continue;
 
             // ---- phase 1: the (term, tile) document maps into shared memory.  Stored maps and the postings of
             //      map-less terms are all fetched with cp.async before anything waits: one memory round trip
@@ -280,16 +349,20 @@ bm25x_scan_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict_
                 const int l = __ffs(a) - 1;
                 const int row = __shfl_sync(0xFFFFFFFFu, row0, l);
                 uint32_t* dst = bm + l * WORDS + WPL * lane;
+                uint32_t* dsth = bmh + l * WORDS + WPL * lane;
                 if (row >= 0) {
-                    const uint32_t* src = bits + (size_t)row * row_words + (size_t)j * WORDS + WPL * lane;
-                    if (SUBS == 1) cp_async<8>(dst, src);
+                    const size_t at = (size_t)row * row_words + (size_t)j * WORDS + WPL * lane;
+                    if (SUBS == 1) { cp_async<8>(dst, bits + at); cp_async<8>(dsth, bits_hi + at); }
                     else {
 #pragma unroll
-                        for (int w = 0; w < WPL; w += 4) cp_async<16>(dst + w, src + w);
+                        for (int w = 0; w < WPL; w += 4) { cp_async<16>(dst + w, bits + at + w); cp_async<16>(dsth + w, bits_hi + at + w); }
                     }
                 } else {
 #pragma unroll
-                    for (int w = 0; w < WPL; w += 2) *reinterpret_cast<uint2*>(dst + w) = make_uint2(0u, 0u);
+                    for (int w = 0; w < WPL; w += 2) {
+                        *reinterpret_cast<uint2*>(dst + w) = make_uint2(0u, 0u);
+                        *reinterpret_cast<uint2*>(dsth + w) = make_uint2(0u, 0u);
+                    }
                     const int c_l = __shfl_sync(0xFFFFFFFFu, pcnt, l);
                     uint2* pd = pool + __shfl_sync(0xFFFFFFFFu, poff, l);
                     const uint2* src = post + __shfl_sync(0xFFFFFFFFu, base_cur, l);
@@ -303,15 +376,20 @@ bm25x_scan_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict_
                 const int n_l = (int)__shfl_sync(0xFFFFFFFFu, n, l);
                 const int c_l = __shfl_sync(0xFFFFFFFFu, pcnt, l);
                 const uint2* pd = pool + __shfl_sync(0xFFFFFFFFu, poff, l);
+                const float tau_l = __shfl_sync(0xFFFFFFFFu, tau0, l);
                 for (int i = lane; i < c_l; i += 32) {
-                    const uint32_t dl = pd[i].x - tile_base;
+                    const uint2 pp = pd[i];
+                    const uint32_t dl = pp.x - tile_base;
                     atomicOr(bm + l * WORDS + (dl >> 5), 1u << (dl & 31));
+                    if (__uint_as_float(pp.y) > tau_l) atomicOr(bmh + l * WORDS + (dl >> 5), 1u << (dl & 31));
                 }
                 if (n_l > c_l) {                              // rare: the pool is full, read the rest from global
                     const uint2* src = post + __shfl_sync(0xFFFFFFFFu, base_cur, l);
                     for (int i = c_l + lane; i < n_l; i += 32) {
-                        const uint32_t dl = __ldg(&src[i].x) - tile_base;
+                        const uint2 pp = __ldg(&src[i]);
+                        const uint32_t dl = pp.x - tile_base;
                         atomicOr(bm + l * WORDS + (dl >> 5), 1u << (dl & 31));
+                        if (__uint_as_float(pp.y) > tau_l) atomicOr(bmh + l * WORDS + (dl >> 5), 1u << (dl & 31));
                     }
                 }
             }
@@ -330,13 +408,17 @@ bm25x_scan_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict_
                 const bool two = a != 0u;
                 const int lb = two ? __ffs(a) - 1 : la;
                 a &= a - 1;
-                uint32_t wa[WPL], wb[WPL];
+                uint32_t wa[WPL], wb[WPL], ha[WPL], hb[WPL];
 #pragma unroll
                 for (int w = 0; w < WPL; w += 2) {
                     const uint2 va = *reinterpret_cast<const uint2*>(bm + la * WORDS + WPL * lane + w);
                     const uint2 vb = *reinterpret_cast<const uint2*>(bm + lb * WORDS + WPL * lane + w);
+                    const uint2 xa = *reinterpret_cast<const uint2*>(bmh + la * WORDS + WPL * lane + w);
+                    const uint2 xb = *reinterpret_cast<const uint2*>(bmh + lb * WORDS + WPL * lane + w);
                     wa[w] = va.x; wa[w + 1] = va.y;
+                    ha[w] = xa.x; ha[w + 1] = xa.y;
                     wb[w] = two ? vb.x : 0u; wb[w + 1] = two ? vb.y : 0u;
+                    hb[w] = two ? xb.x : 0u; hb[w + 1] = two ? xb.y : 0u;
                 }
                 uint32_t loc[WPL];                       // packed exclusive prefix inside the lane
                 uint32_t own = 0u;
@@ -358,14 +440,18 @@ bm25x_scan_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict_
                     *reinterpret_cast<uint32_t*>(pre + la * WORDS + WPL * lane + w) = (r0 & 0xFFFFu) | (r1 << 16);
                     if (two) *reinterpret_cast<uint32_t*>(pre + lb * WORDS + WPL * lane + w) = (r0 >> 16) | (r1 & 0xFFFF0000u);
                 }
+                // count += present + high, two maps at a time through a 3:2 compressor on plane 0
 #pragma unroll
                 for (int w = 0; w < WPL; ++w) {
-                    uint32_t k = wa[w];
 #pragma unroll
-                    for (int p = 0; p < PLANES; ++p) { const uint32_t t_ = cn[p][w] & k; cn[p][w] ^= k; k = t_; }
-                    k = wb[w];
+                    for (int h = 0; h < 2; ++h) {
+                        const uint32_t x = h ? wb[w] : wa[w], y = h ? hb[w] : ha[w];
+                        const uint32_t c = cn[0][w];
+                        cn[0][w] = c ^ x ^ y;
+                        uint32_t k = (c & x) | (c & y) | (x & y);
 #pragma unroll
-                    for (int p = 0; p < PLANES; ++p) { const uint32_t t_ = cn[p][w] & k; cn[p][w] ^= k; k = t_; }
+                        for (int p = 1; p < PLANES; ++p) { const uint32_t t_ = cn[p][w] & k; cn[p][w] ^= k; k = t_; }
+                    }
                 }
             }
             // count >= m, bit-slice compare from the top plane down; then the payload filter
@@ -511,7 +597,7 @@ Bm25Plan bm25x_plan(int64_t n_docs, int B, int k_sel, int max_terms, int num_sms
 
 struct BxArgs {
     const int64_t* term_ptr; const uint2* post; const uint32_t* sub_off; const int32_t* bm_row; const uint32_t* bits;
-    const float2* wrange; int64_t V, n_docs; const int32_t *q_ptr, *q_terms; const double* q_vals; int B;
+    const uint32_t* bits_hi; const float2* wrange; const float* tau; int64_t V, n_docs; const int32_t *q_ptr, *q_terms; const double* q_vals; int B;
     const uint32_t* mask; int k_sel; uint64_t* part; const Bm25Plan* plan; void* scratch; cudaStream_t st;
 };
 
@@ -535,7 +621,7 @@ static cudaError_t bx_launch(const BxArgs& a) {
     cudaError_t e = cudaMemsetAsync(a.scratch, 0, plan.scratch_bytes, a.st);
     if (e != cudaSuccess) return e;
     bm25x_scan_kernel<MAXT, SUBS><<<plan.grid, (plan.workers + 1) * 32, smem, a.st>>>(
-        a.term_ptr, a.post, a.sub_off, a.bm_row, a.bits, a.wrange, a.V, a.n_docs, a.q_ptr, a.q_terms, a.q_vals, a.B,
+        a.term_ptr, a.post, a.sub_off, a.bm_row, a.bits, a.bits_hi, a.wrange, a.tau, a.V, a.n_docs, a.q_ptr, a.q_terms, a.q_vals, a.B,
         a.mask, a.k_sel, lcap, plan.workers, a.part, plan.splits, work_counter, gthr, coarse, fine);
     return cudaGetLastError();
 }
@@ -550,11 +636,12 @@ static cudaError_t bx_launch_subs(const BxArgs& a) {
 }
 
 cudaError_t bm25x_scan(const int64_t* term_ptr, const uint2* post, const uint32_t* sub_off, const int32_t* bm_row,
-                       const uint32_t* bits, const float2* wrange, int64_t V, int64_t n_docs, const int32_t* q_ptr,
+                       const uint32_t* bits, const uint32_t* bits_hi, const float2* wrange, const float* tau, int64_t V,
+                       int64_t n_docs, const int32_t* q_ptr,
                        const int32_t* q_terms, const double* q_vals, int B, int max_terms, const uint32_t* mask,
                        int k_sel, uint64_t* part, const Bm25Plan& plan, void* scratch, cudaStream_t st) {
     if (!bm25x_supported(max_terms, k_sel)) return cudaErrorInvalidValue;
-    const BxArgs a{term_ptr, post, sub_off, bm_row, bits, wrange, V, n_docs, q_ptr, q_terms, q_vals, B,
+    const BxArgs a{term_ptr, post, sub_off, bm_row, bits, bits_hi, wrange, tau, V, n_docs, q_ptr, q_terms, q_vals, B,
                    mask, k_sel, part, &plan, scratch, st};
     switch (bx_maxt(max_terms)) {
         case 8: return bx_launch_subs<8>(a);

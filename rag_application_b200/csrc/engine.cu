@@ -72,6 +72,8 @@ struct SparseSpace {
     uint32_t* sub_off = nullptr;
     // bitmap-filter scan (bm25x.cu): per-term weight range, document maps of the dense terms
     float2* wrange = nullptr;
+    float* tau = nullptr;
+    uint32_t* bits_hi = nullptr;
     int32_t* bm_row = nullptr;
     uint32_t* bits = nullptr;
     int n_dense = 0;
@@ -175,6 +177,8 @@ void free_sparse(SparseSpace& s) {
     if (s.post) cudaFree(s.post);
     if (s.sub_off) cudaFree(s.sub_off);
     if (s.wrange) cudaFree(s.wrange);
+    if (s.tau) cudaFree(s.tau);
+    if (s.bits_hi) cudaFree(s.bits_hi);
     if (s.bm_row) cudaFree(s.bm_row);
     if (s.bits) cudaFree(s.bits);
     s = SparseSpace();
@@ -184,9 +188,10 @@ void free_sparse(SparseSpace& s) {
 // smaller than its postings (df >= N/64), densest first, within a quarter of the posting bytes.
 void build_bitmap_index(SparseSpace& s) {
     CK(cudaMalloc(&s.wrange, (size_t)s.V * sizeof(float2)));
+    CK(cudaMalloc(&s.tau, (size_t)s.V * sizeof(float)));
     int* flag = nullptr;
     CK(cudaMalloc(&flag, sizeof(int)));
-    cudaError_t ce = brag::bm25x_build_wrange(s.term_ptr, s.post, s.V, s.nnz, s.wrange, flag, 0);
+    cudaError_t ce = brag::bm25x_build_wrange(s.term_ptr, s.post, s.V, s.nnz, s.wrange, s.tau, flag, 0);
     int nonfinite = 0;
     if (ce == cudaSuccess) ce = cudaMemcpy(&nonfinite, flag, sizeof(int), cudaMemcpyDeviceToHost);
     cudaFree(flag);
@@ -201,19 +206,21 @@ void build_bitmap_index(SparseSpace& s) {
     std::sort(dense.begin(), dense.end(), [](const std::pair<int64_t, int32_t>& a, const std::pair<int64_t, int32_t>& b) {
         return a.first != b.first ? a.first > b.first : a.second < b.second;
     });
+    // two maps per dense term (present, high class) within a quarter of the posting bytes
     const size_t budget = std::max<size_t>((size_t)64 << 20, (size_t)s.nnz * 2);
-    while (!dense.empty() && dense.size() * row_bytes > budget) dense.pop_back();
+    while (!dense.empty() && dense.size() * row_bytes * 2 > budget) dense.pop_back();
     std::vector<int32_t> rows((size_t)s.V, -1), terms(dense.size());
     for (size_t r = 0; r < dense.size(); ++r) { rows[(size_t)dense[r].second] = (int32_t)r; terms[r] = dense[r].second; }
     s.n_dense = (int)dense.size();
     CK(cudaMalloc(&s.bm_row, (size_t)s.V * sizeof(int32_t)));
     CK(cudaMemcpy(s.bm_row, rows.data(), (size_t)s.V * sizeof(int32_t), cudaMemcpyHostToDevice));
     CK(cudaMalloc(&s.bits, std::max<size_t>(256, (size_t)s.n_dense * row_bytes)));
+    CK(cudaMalloc(&s.bits_hi, std::max<size_t>(256, (size_t)s.n_dense * row_bytes)));
     if (s.n_dense) {
         int32_t* dterms = nullptr;
         CK(cudaMalloc(&dterms, terms.size() * sizeof(int32_t)));
         ce = cudaMemcpy(dterms, terms.data(), terms.size() * sizeof(int32_t), cudaMemcpyHostToDevice);
-        if (ce == cudaSuccess) ce = brag::bm25x_build_bitmaps(s.term_ptr, s.post, dterms, s.n_dense, s.n_docs, s.bits, 0);
+        if (ce == cudaSuccess) ce = brag::bm25x_build_bitmaps(s.term_ptr, s.post, dterms, s.n_dense, s.tau, s.n_docs, s.bits, s.bits_hi, 0);
         if (ce == cudaSuccess) ce = cudaDeviceSynchronize();
         cudaFree(dterms);
         CK(ce);
@@ -328,7 +335,7 @@ void sparse_topk_dev(brag_engine* e, SparseSpace& s, const int32_t* q_ptr, const
     {
         StageTimer t(e, 2, st);
         if (bitmap)
-            CK(brag::bm25x_scan(s.term_ptr, s.post, s.sub_off, s.bm_row, s.bits, s.wrange, s.V, s.n_docs, q_ptr, q_terms,
+            CK(brag::bm25x_scan(s.term_ptr, s.post, s.sub_off, s.bm_row, s.bits, s.bits_hi, s.wrange, s.tau, s.V, s.n_docs, q_ptr, q_terms,
                                 q_vals, B, max_terms, mask, k, part, plan, scratch, st));
         else
             CK(brag::bm25_scan(s.term_ptr, s.post, s.sub_off, s.V, s.n_docs, q_ptr, q_terms, q_vals, B, mask, k,

@@ -71,19 +71,22 @@ cudaError_t bm25_scan(const int64_t* term_ptr, const uint2* post, const uint32_t
 
 
 // ---- bm25x.cu: bitmap-filter variant of the sparse scan (same results, prunes on per-term weight bounds)
-// wrange[t] = (min, max) weight of term t; *nonfinite_flag is set when any weight is NaN/Inf
+// wrange[t] = (min, max) weight of term t; tau[t] = low/high class threshold (>= ~70 % of the postings have
+// w <= tau); *nonfinite_flag is set when any weight is NaN/Inf
 cudaError_t bm25x_build_wrange(const int64_t* term_ptr, const uint2* post, int64_t V, int64_t nnz, float2* wrange,
-                               int* nonfinite_flag, cudaStream_t st);
-// bits: [n_dense][bm25x_row_words(n_docs)] words, bit d of row r = term dense_terms[r] occurs in document d
+                               float* tau, int* nonfinite_flag, cudaStream_t st);
+// bits / bits_hi: [n_dense][bm25x_row_words(n_docs)] words; bit d of row r = term dense_terms[r] occurs in
+// document d (bits) with a weight above tau (bits_hi)
 cudaError_t bm25x_build_bitmaps(const int64_t* term_ptr, const uint2* post, const int32_t* dense_terms, int n_dense,
-                                int64_t n_docs, uint32_t* bits, cudaStream_t st);
+                                const float* tau, int64_t n_docs, uint32_t* bits, uint32_t* bits_hi, cudaStream_t st);
 int64_t bm25x_row_words(int64_t n_docs);     // words per stored map row (sub-tile count rounded up to 4)
 bool bm25x_supported(int max_terms, int k_sel);
 Bm25Plan bm25x_plan(int64_t n_docs, int B, int k_sel, int max_terms, int num_sms);
 // bm_row[t] = bitmap row of term t or -1; max_terms = longest query of the batch (<= 32)
 cudaError_t bm25x_scan(const int64_t* term_ptr, const uint2* post, const uint32_t* sub_off, const int32_t* bm_row,
-                       const uint32_t* bits, const float2* wrange, int64_t V, int64_t n_docs, const int32_t* q_ptr,
-                       const int32_t* q_terms, const double* q_vals, int B, int max_terms, const uint32_t* mask,
-                       int k_sel, uint64_t* part, const Bm25Plan& plan, void* scratch, cudaStream_t st);
+                       const uint32_t* bits, const uint32_t* bits_hi, const float2* wrange, const float* tau, int64_t V,
+                       int64_t n_docs, const int32_t* q_ptr, const int32_t* q_terms, const double* q_vals, int B,
+                       int max_terms, const uint32_t* mask, int k_sel, uint64_t* part, const Bm25Plan& plan,
+                       void* scratch, cudaStream_t st);
 
 }  // namespace brag
