@@ -44,11 +44,11 @@ struct BxCfg {
     static constexpr int PLANES = (MAXT == 8) ? 5 : (MAXT == 16 ? 6 : 7);     // bit planes of the counts 0..2*MAXT
 };
 
-// per-warp shared memory: bm[MAXT][WORDS] u32 | bmh[MAXT][WORDS] u32 | pre[MAXT][WORDS] u16 | pool[POOL] (doc, weight) |
-//                         list[lcap] u64 | sbase[MAXT] i64 | sqv[MAXT] f64 | spoff[MAXT] i32 | spcnt[MAXT] i32 |
-//                         clist[32] u16 | cnt
+// per-warp shared memory: bm[MAXT][WORDS] u32 | bmh[MAXT][WORDS] u32 (the rank table pre[MAXT][WORDS] u16 overwrites
+//                         each term's high map once it has been counted) | pool[POOL] (doc, weight) | list[lcap] u64 |
+//                         sbase[MAXT] i64 | sqv[MAXT] f64 | spoff[MAXT] i32 | spcnt[MAXT] i32 | clist[32] u16 | cnt
 __host__ __device__ inline size_t bx_warp_bytes(int maxt, int subs, int lcap) {
-    return (size_t)maxt * 64 * subs * 10 + (size_t)128 * subs * 8 + (size_t)lcap * 8 + (size_t)maxt * 24 + 64 + 16;
+    return (size_t)maxt * 64 * subs * 8 + (size_t)128 * subs * 8 + (size_t)lcap * 8 + (size_t)maxt * 24 + 64 + 16;
 }
 
 // words of one stored document map: the sub-tile count is rounded up to 4 so a tile of any SUBS stays inside its row
@@ -231,8 +231,9 @@ bm25x_scan_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict_
     uint8_t* slab = smem_raw + (size_t)warp * bx_warp_bytes(MAXT, SUBS, lcap);
     uint32_t* bm = reinterpret_cast<uint32_t*>(slab);                                 // [MAXT][WORDS] present maps
     uint32_t* bmh = bm + MAXT * WORDS;                                                // [MAXT][WORDS] high maps
-    uint16_t* pre = reinterpret_cast<uint16_t*>(slab + (size_t)MAXT * WORDS * 8);     // [MAXT][WORDS]
-    uint2* pool = reinterpret_cast<uint2*>(slab + (size_t)MAXT * WORDS * 10);         // [POOL]
+    // rank table: term l's ranks (u16) live in the first half of bmh[l], written after bmh[l] has been counted
+    uint16_t* pre = reinterpret_cast<uint16_t*>(bmh);                                 // stride 2 * WORDS u16 per term
+    uint2* pool = reinterpret_cast<uint2*>(slab + (size_t)MAXT * WORDS * 8);          // [POOL]
     uint64_t* list = reinterpret_cast<uint64_t*>(pool + POOL);
     int64_t* sbase = reinterpret_cast<int64_t*>(list + lcap);
     double* sqv = reinterpret_cast<double*>(sbase + MAXT);
@@ -434,11 +435,12 @@ bm25x_scan_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict_
                     if (lane >= off) inc += o;
                 }
                 const uint32_t ex = inc - own;
+                __syncwarp();       // every lane has read its words of bmh[la], bmh[lb] before the ranks overwrite them
 #pragma unroll
                 for (int w = 0; w < WPL; w += 2) {
                     const uint32_t r0 = ex + loc[w], r1 = ex + loc[w + 1];
-                    *reinterpret_cast<uint32_t*>(pre + la * WORDS + WPL * lane + w) = (r0 & 0xFFFFu) | (r1 << 16);
-                    if (two) *reinterpret_cast<uint32_t*>(pre + lb * WORDS + WPL * lane + w) = (r0 >> 16) | (r1 & 0xFFFF0000u);
+                    *reinterpret_cast<uint32_t*>(pre + la * 2 * WORDS + WPL * lane + w) = (r0 & 0xFFFFu) | (r1 << 16);
+                    if (two) *reinterpret_cast<uint32_t*>(pre + lb * 2 * WORDS + WPL * lane + w) = (r0 >> 16) | (r1 & 0xFFFF0000u);
                 }
                 // count += present + high, two maps at a time through a 3:2 compressor on plane 0
 #pragma unroll
@@ -513,7 +515,7 @@ bm25x_scan_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict_
                 for (int l = 0; l < MAXT; ++l) {
                     const uint32_t wv = bm[l * WORDS + word];
                     const bool h = mine && ((active >> l) & 1u) && ((wv >> bit) & 1u);
-                    rk[l] = (uint32_t)pre[l * WORDS + word] + __popc(wv & below);
+                    rk[l] = (uint32_t)pre[l * 2 * WORDS + word] + __popc(wv & below);
                     const bool st = h && ((sparse_terms >> l) & 1u) && (int)rk[l] < spcnt[l];
                     const bool gl = h && !st;
                     // unconditional load (a dummy, L1-resident address when this term misses): the MAXT loads issue
