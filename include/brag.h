@@ -123,7 +123,8 @@ int brag_profile_reset(brag_engine* e);
 /* Which dense scan kernel brag_dense_topk would pick for batch B: 0 = GEMV stream (float32 storage, or
  * d not a multiple of 64), 1 = TMA + tcgen05 (16-bit storage, any batch size). */
 int brag_dense_path(brag_engine* e, const char* name, int32_t B);
-/* Force a path (-1 auto, 0 GEMV, 1 tcgen05) -- used by the parity tests. */
+/* Force a path (-1 auto, 0 GEMV, 1 tcgen05, 2 tcgen05 scanning the full space under a filter instead of its
+ * filter-compacted copy) -- used by the parity tests. */
 int brag_force_dense_path(brag_engine* e, int32_t path);
 /* Sparse scan kernel (-1 auto, 0 scatter-accumulate, 1 bitmap filter).  Auto = bitmap filter unless a query of
  * the batch has more than 32 terms or the space holds non-finite weights; both give identical results. */

@@ -4,18 +4,22 @@
 //
 // Idea: the scatter kernel spends its time adding postings of documents that cannot reach the top k.
 // Here a document's score is only evaluated when it CAN exceed the query's running global bound:
-//   * every term has an upper bound of its contribution, ub_t = max(0, qv_t*maxw_t, qv_t*minw_t); with
-//     the bounds sorted descending and prefix-summed (S_c), a document that contains c of the query's
-//     terms scores at most S_c, so it needs c >= m where m = 1 + #{c : S_c <= bound};
-//   * per (term, 2048-document sub-tile) the set of documents containing the term is a 2048-bit map:
-//     stored at upload for dense terms (df >= N/64: the map is smaller than the postings it stands for),
-//     built in shared memory from the few postings otherwise;
-//   * the per-document term count is a bit-sliced carry-save sum of the <= MAXT maps (each lane owns
-//     64 documents = 2 words per map), compared with m bit-slice-wise, and-ed with the payload filter;
+//   * every term t splits its postings at a weight threshold tau_t into a low class (w <= tau_t, >= ~70 % of
+//     them; for BM25: tf = 1) and a high class.  A low posting contributes at most ua_t = max(0, qv*min_t,
+//     qv*tau_t), a high one at most ua_t + ue_t with ue_t = max(ua_t, qv*max_t) - ua_t.  With the 2*nq values
+//     {ua_t} U {ue_t} sorted descending and prefix-summed (S_c), a document that contains c1 of the query's
+//     terms, c2 of them in their high class, scores at most S_(c1+c2): it needs c1 + c2 >= m, where
+//     m = 1 + #{c : S_c <= bound}.  Valid for any sign of weights and query values;
+//   * per (term, 2048-document sub-tile) the documents containing the term (and those in its high class) are
+//     2048-bit maps: stored at upload for dense terms (df >= N/64: a map is smaller than the postings it stands
+//     for), built in shared memory from the few postings (staged with cp.async) otherwise;
+//   * c1 + c2 per document is a bit-sliced carry-save sum of the <= 2*MAXT maps (each lane owns 64*SUBS
+//     documents), compared with m bit-slice-wise, and-ed with the payload filter;
 //   * only the surviving documents are scored: weight of term t for document d = posting number
-//     sub_off[t][tile] + rank_t(d), rank = prefix popcount of the map (one 8-byte load, no search).
-// With a warm bound <1 % of the documents survive, so the kernel reads 1 bit instead of 8 bytes for
-// most postings.  Selection (global histograms, bound-manager warp, per-warp lists) is bm25.cu's.
+//     sub_off[t][tile] + rank_t(d), rank = prefix popcount of the map (one 8-byte load, no search); survivors
+//     are compacted so that every lane of a scoring round holds one; the float64 sum runs in ascending term order.
+// With a warm bound ~0.3 % of the documents survive, so the kernel reads 2 bits instead of 8 bytes for most
+// postings.  Selection (global histograms, bound-manager warp, per-warp lists) is bm25.cu's.
 // Roofline: HBM against the ALGORITHMIC bytes sum_t df_t * 8 B (what an exhaustive scan must read);
 // the bytes this kernel really moves are reported separately from ncu (profiles/).
 #include <algorithm>

@@ -64,6 +64,15 @@ struct DenseSpace {
     int dtype = 0;
     bool umma_ok = false;
     alignas(64) unsigned char tmap_x[128];
+    // filter-compacted copy (compact.cu) of the rows passing the filter (mask_id, version) last scanned with
+    int cp_mask_id = 0;
+    uint64_t cp_version = 0;
+    bool cp_use = false;           // false: the filter keeps too many / too few rows, scan the full space
+    int64_t cp_n = 0;
+    void* cp_x = nullptr;
+    uint32_t* cp_rowmap = nullptr;
+    size_t cp_x_cap = 0, cp_rowmap_cap = 0;
+    alignas(64) unsigned char cp_tmap[128];
 };
 
 struct SparseSpace {
@@ -85,6 +94,7 @@ struct SparseSpace {
 struct MaskBuf {
     uint32_t* bits = nullptr;
     int64_t nbits = 0;
+    uint64_t version = 0;          // bumped by every brag_mask_set: invalidates compacted copies
 };
 
 struct StageEvent {
@@ -99,6 +109,8 @@ struct brag_engine {
     int num_sms = 148;
     int64_t id_offset = 0;
     int force_path = -1;
+    bool no_compact = false;       // parity tests: scan the full space under a filter
+    uint64_t mask_epoch = 0;
     int force_sparse_path = -1;    // -1 auto, 0 scatter-accumulate (bm25.cu), 1 bitmap filter (bm25x.cu)
     std::map<std::string, DenseSpace> dense;
     std::map<std::string, SparseSpace> sparse;
@@ -106,7 +118,7 @@ struct brag_engine {
     // scratch (grow-only)
     DevBuf qs, q16, part, tmp_a, tmp_b, keys1, keys2, umma_scratch, work_counter, g_thr;
     DevBuf h_in[6], h_out[4];      // staging for host-pointer calls
-    DevBuf hyb_ids, hyb_counts, hyb_scores;
+    DevBuf hyb_ids, hyb_counts, hyb_scores, cp_prefix, cp_tmp;
     std::vector<int32_t> qptr_host;
     alignas(64) unsigned char tmap_q[128];
     // profiling
@@ -170,7 +182,11 @@ SparseSpace& sparse_space(brag_engine* e, const char* name) {
 
 void free_dense(DenseSpace& s) {
     if (s.x) cudaFree(s.x);
+    if (s.cp_x) cudaFree(s.cp_x);
+    if (s.cp_rowmap) cudaFree(s.cp_rowmap);
     s.x = nullptr;
+    s.cp_x = nullptr;
+    s.cp_rowmap = nullptr;
 }
 void free_sparse(SparseSpace& s) {
     if (s.term_ptr) cudaFree(s.term_ptr);
@@ -240,7 +256,50 @@ int pick_path(brag_engine* e, const DenseSpace& s, int B) {
 }
 
 // ---- device-pointer implementations -------------------------------------------------------
-void dense_topk_dev(brag_engine* e, DenseSpace& s, const float* Q, int B, int k, const uint32_t* mask,
+// Compacted copy of the rows of `s` that pass filter `mask_id` (compact.cu), built on first use and kept until the
+// filter changes.  Returns false when the filter is not worth compacting (keeps more than half of the rows, or so
+// few that the masked scan is already cheap) or the copy does not fit; the caller then scans the full space.
+bool ensure_compact(brag_engine* e, DenseSpace& s, int mask_id, const uint32_t* mask, cudaStream_t st) {
+    const uint64_t version = e->masks[mask_id].version;
+    if (s.cp_mask_id == mask_id && s.cp_version == version) return s.cp_use;
+    s.cp_mask_id = mask_id;
+    s.cp_version = version;
+    s.cp_use = false;
+    const int64_t nwords = (s.n + 31) / 32;
+    uint32_t* prefix = e->cp_prefix.as<uint32_t>((size_t)nwords + 1);
+    const size_t tmp_bytes = brag::compact_tmp_bytes(nwords);
+    void* tmp = e->cp_tmp.ensure(tmp_bytes);
+    CK(brag::compact_prefix(mask, s.n, prefix, tmp, tmp_bytes, st));
+    uint32_t nc = 0;
+    CK(cudaMemcpyAsync(&nc, prefix + nwords, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    e->kernel_launches += 2;
+    if ((int64_t)nc * 2 > s.n || nc < 4096 || !brag::dense_umma_supported(s.dtype, s.d, nc)) return false;
+    const size_t row_bytes = (size_t)s.d * 2;
+    const size_t need_x = (size_t)nc * row_bytes, need_map = (size_t)nc * sizeof(uint32_t);
+    if (need_x > s.cp_x_cap) {
+        if (s.cp_x) CK(cudaFree(s.cp_x));
+        s.cp_x = nullptr;
+        s.cp_x_cap = 0;
+        if (cudaMalloc(&s.cp_x, need_x) != cudaSuccess) { cudaGetLastError(); s.cp_x = nullptr; return false; }
+        s.cp_x_cap = need_x;
+    }
+    if (need_map > s.cp_rowmap_cap) {
+        if (s.cp_rowmap) CK(cudaFree(s.cp_rowmap));
+        s.cp_rowmap = nullptr;
+        s.cp_rowmap_cap = 0;
+        if (cudaMalloc(&s.cp_rowmap, need_map) != cudaSuccess) { cudaGetLastError(); s.cp_rowmap = nullptr; return false; }
+        s.cp_rowmap_cap = need_map;
+    }
+    CK(brag::compact_rows(s.x, (int)row_bytes, mask, s.n, prefix, nc, s.cp_rowmap, s.cp_x, st));
+    if (brag::make_tmap_2d(s.cp_tmap, s.cp_x, nc, s.d, 256) != cudaSuccess) return false;
+    e->kernel_launches += 2;
+    s.cp_n = nc;
+    s.cp_use = true;
+    return true;
+}
+
+void dense_topk_dev(brag_engine* e, DenseSpace& s, const float* Q, int B, int k, int mask_id, const uint32_t* mask,
                     float* out_scores, int64_t* out_ids, int32_t* out_counts, cudaStream_t st) {
     REQUIRE(B >= 1 && k >= 1 && k <= 512, "dense_topk: need B >= 1 and 1 <= k <= 512");
     const int k_sel = k_select(k);
@@ -248,19 +307,29 @@ void dense_topk_dev(brag_engine* e, DenseSpace& s, const float* Q, int B, int k,
     float* qs = e->qs.as<float>((size_t)B * s.d);
     uint64_t* cand = e->keys1.as<uint64_t>((size_t)B * k_sel);
     uint64_t* cand2 = e->keys2.as<uint64_t>((size_t)B * k_sel);
+    // rows actually scanned: the whole space, or its filter-compacted copy
+    const void* X = s.x;
+    int64_t n = s.n;
+    void* tmap_x = s.tmap_x;
+    const uint32_t* scan_mask = mask;
+    bool compact = false;
     {
         StageTimer t(e, 0, st);
+        if (path == 1 && mask != nullptr && !e->no_compact && ensure_compact(e, s, mask_id, mask, st)) {
+            compact = true;
+            X = s.cp_x; n = s.cp_n; tmap_x = s.cp_tmap; scan_mask = nullptr;
+        }
         if (path == 1) {
             // tcgen05 scan; the per-query selection is part of the scan (no partial lists to merge)
             brag::UmmaPlan plan;
-            CK(brag::dense_umma_plan(s.n, s.d, B, k_sel, e->num_sms, &plan));
+            CK(brag::dense_umma_plan(n, s.d, B, k_sel, e->num_sms, &plan));
             const int Bpad = plan.n_qblocks * 128;
             void* q16 = e->q16.ensure((size_t)Bpad * s.d * 2);
             CK(brag::round_queries(Q, B, s.d, s.dtype, qs, q16, Bpad, st));
             CK(brag::make_tmap_2d(e->tmap_q, q16, Bpad, s.d, 128));
             void* scratch = e->umma_scratch.ensure(plan.scratch_bytes);
             int launches = 0;
-            CK(brag::dense_umma_scan(s.x, s.dtype, s.n, s.d, q16, B, mask, k_sel, cand, scratch, plan, s.tmap_x,
+            CK(brag::dense_umma_scan(X, s.dtype, n, s.d, q16, B, scan_mask, k_sel, cand, scratch, plan, tmap_x,
                                      e->tmap_q, st, &launches));
             e->kernel_launches += 1 + launches;
         } else {
@@ -280,7 +349,11 @@ void dense_topk_dev(brag_engine* e, DenseSpace& s, const float* Q, int B, int k,
     }
     {
         StageTimer t(e, 1, st);
-        CK(brag::rescore_keys(s.x, s.dtype, s.n, s.d, qs, B, cand, k_sel, cand2, st));
+        CK(brag::rescore_keys(X, s.dtype, n, s.d, qs, B, cand, k_sel, cand2, st));
+        if (compact) {
+            CK(brag::remap_keys(cand2, (int64_t)B * k_sel, s.cp_rowmap, st));
+            e->kernel_launches += 1;
+        }
         CK(brag::finalize_keys(cand2, B, k_sel, k, false, e->id_offset, out_scores, out_ids, out_counts, st));
         e->kernel_launches += 2;
     }
@@ -558,6 +631,7 @@ int brag_mask_set(brag_engine* e, int32_t mask_id, const uint32_t* bits, int64_t
         CK(cudaMemset(m.bits, 0, (words + 512) * sizeof(uint32_t)));
         CK(cudaMemcpy(m.bits, bits, words * sizeof(uint32_t), on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice));
         m.nbits = nbits;
+        m.version = ++e->mask_epoch;
     });
 }
 
@@ -570,13 +644,13 @@ int brag_dense_topk(brag_engine* e, const char* name, const float* Q, int32_t B,
         DenseSpace& s = dense_space(e, name);
         const uint32_t* mask = mask_ptr(e, mask_id, s.n);
         if (on_device) {
-            dense_topk_dev(e, s, Q, B, k, mask, out_scores, out_ids, out_counts, st);
+            dense_topk_dev(e, s, Q, B, k, mask_id, mask, out_scores, out_ids, out_counts, st);
         } else {
             const float* dq = to_dev(e->h_in[0], Q, (size_t)B * s.d, st);
             float* ds = e->h_out[0].as<float>((size_t)B * k);
             int64_t* di = e->h_out[1].as<int64_t>((size_t)B * k);
             int32_t* dc = e->h_out[2].as<int32_t>(B);
-            dense_topk_dev(e, s, dq, B, k, mask, ds, di, dc, st);
+            dense_topk_dev(e, s, dq, B, k, mask_id, mask, ds, di, dc, st);
             to_host(out_scores, ds, (size_t)B * k, st);
             to_host(out_ids, di, (size_t)B * k, st);
             to_host(out_counts, dc, (size_t)B, st);
@@ -733,7 +807,7 @@ int brag_hybrid_topk(brag_engine* e, const char* dense_name, const char* sparse_
             oi = e->h_out[1].as<int64_t>((size_t)B * k);
             oc = e->h_out[2].as<int32_t>(B);
         }
-        dense_topk_dev(e, ds, dq, B, k, mask, scs, ids, cnts, st);
+        dense_topk_dev(e, ds, dq, B, k, mask_id, mask, scs, ids, cnts, st);
         sparse_topk_dev(e, ss, dp, dt, dv, B, k, mask, scs + (size_t)B * k, ids + (size_t)B * k, cnts + B,
                         on_device ? -1 : max_terms_host(q_ptr, B), st);
         {
@@ -808,8 +882,9 @@ int brag_force_sparse_path(brag_engine* e, int32_t path) {
 
 int brag_force_dense_path(brag_engine* e, int32_t path) {
     return guarded([&] {
-        REQUIRE(e && path >= -1 && path <= 1, "brag_force_dense_path: path must be -1, 0 or 1");
-        e->force_path = path;
+        REQUIRE(e && path >= -1 && path <= 2, "brag_force_dense_path: path must be -1, 0, 1 or 2");
+        e->force_path = path == 2 ? 1 : path;
+        e->no_compact = path == 2;
     });
 }
 

@@ -52,6 +52,17 @@ cudaError_t merge_scored_lists(const float* scores, const int64_t* ids, const in
                                int B, int k, float* out_scores, int64_t* out_ids, int32_t* out_counts,
                                cudaStream_t st);
 
+// ---- compact.cu: filter-compacted copy of a dense space (rows that pass a filter, gathered contiguously)
+size_t compact_tmp_bytes(int64_t nwords);
+// prefix: [ceil(n/32) + 1] passing rows before each filter word; the last entry is the number of passing rows
+cudaError_t compact_prefix(const uint32_t* mask, int64_t n, uint32_t* prefix, void* tmp, size_t tmp_bytes,
+                           cudaStream_t st);
+// rowmap: [nc] original row of every compact row (increasing); out: [nc, row_bytes]
+cudaError_t compact_rows(const void* X, int row_bytes, const uint32_t* mask, int64_t n, const uint32_t* prefix,
+                         int64_t nc, uint32_t* rowmap, void* out, cudaStream_t st);
+// keys of compact rows -> keys of original rows (same order: rowmap is increasing)
+cudaError_t remap_keys(uint64_t* keys, int64_t count, const uint32_t* rowmap, cudaStream_t st);
+
 // ---- bm25.cu
 constexpr int BM25_SUB = 2048;  // documents per warp sub-tile
 // postings are stored interleaved: post[i] = (doc id, float32 weight bits)

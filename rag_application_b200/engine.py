@@ -242,4 +242,4 @@ class Engine:
         _native.check(self._lib.brag_force_sparse_path(self._h, {None: -1, "scatter": 0, "bitmap": 1}[path]))
 
     def force_dense_path(self, path: Optional[str]):
-        _native.check(self._lib.brag_force_dense_path(self._h, {None: -1, "gemv": 0, "tcgen05": 1}[path]))
+        _native.check(self._lib.brag_force_dense_path(self._h, {None: -1, "gemv": 0, "tcgen05": 1, "tcgen05_full": 2}[path]))

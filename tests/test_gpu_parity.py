@@ -133,6 +133,34 @@ def test_dense_mask_and_offset(engine, path):
     assert int(c[0]) == 3 and set(i[0][:3]) == {5, 77, 4000} and np.all(i[0][3:] == -1)
 
 
+@pytest.mark.parametrize("B", [1, 40])
+def test_dense_filter_compacted_copy(engine, B):
+    """A filter that keeps <= half of the rows (and >= 4096 of them) is scanned through a gathered copy of the
+    passing rows (compact.cu): same ids and scores as the oracle and as the full-space masked scan; a new filter
+    under the same mask_id rebuilds the copy."""
+    n, d, k = 60000, 128, 50
+    x = synth.dense_corpus(n, d, seed=31, clustered=True)
+    q = synth.dense_queries(x, B, seed=32)
+    engine.dense_set("x", x, "bf16")
+    xs = O.round_storage(x, "bf16")
+    for seed, sel in ((41, 0.10), (42, 0.30)):
+        mask = synth.random_mask(n, sel, seed=seed)
+        engine.mask_set(5, mask)
+        engine.force_dense_path("tcgen05")
+        try:
+            s, i, c = engine.dense_topk("x", q, k, mask_id=5)
+            s2, i2, c2 = engine.dense_topk("x", q, k, mask_id=5)       # second call: cached copy
+            engine.force_dense_path("tcgen05_full")
+            s3, i3, c3 = engine.dense_topk("x", q, k, mask_id=5)
+        finally:
+            engine.force_dense_path(None)
+        assert np.array_equal(i, i2) and np.array_equal(s.view(np.uint32), s2.view(np.uint32))
+        assert np.array_equal(i, i3) and np.array_equal(s.view(np.uint32), s3.view(np.uint32)) and np.array_equal(c, c3)
+        assert mask[i[np.arange(k)[None, :] < c[:, None]]].all()
+        for b in range(0, B, max(1, B // 8)):
+            check_dense(xs, O.round_storage(q[b], "bf16"), k, s[b], i[b], int(c[b]), mask=mask)
+
+
 def test_dense_exact_ties_broken_by_id(engine):
     """Duplicate rows score identically: the lower id must win (north_star: ties broken by id)."""
     x = synth.dense_corpus(512, 64, seed=1)
