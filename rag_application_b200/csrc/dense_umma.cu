@@ -183,7 +183,8 @@ __device__ __forceinline__ void um_compact(unsigned bal, uint64_t* my_list, uint
 // coarse : [B][HIST_COARSE_BINS], fine: [B][HIST_FINE_BINS] row counts per score bin
 __global__ void __launch_bounds__(UM_THREADS, 1)
 dense_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_x,
-                  int64_t n, int d, int B, int qb_base, int n_qblocks, int64_t rows_per_chunk,
+                  int64_t n, int d, int B, int qb_base, int n_qblocks, int qb_split, int64_t row_base, int chunk_base,
+                  int64_t rows_per_chunk,
                   const uint32_t* __restrict__ mask, int k_sel, uint32_t idesc, uint64_t* __restrict__ lists,
                   int* __restrict__ counts, uint32_t* __restrict__ gthr, uint32_t* __restrict__ coarse,
                   uint32_t* __restrict__ fine) {
@@ -191,8 +192,14 @@ dense_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
     UmSmem& S = *reinterpret_cast<UmSmem*>(smem_raw);   // keeps the shared address space (LDS/STS in the sort)
     if ((smem_u32(smem_raw) & 1023u) != 0u) __trap();   // 128B-swizzle atoms need 1024-byte alignment
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int chunk = blockIdx.x;
-    const int64_t row_begin = (int64_t)chunk * rows_per_chunk;
+    // qb_split (seed launch): blockIdx.y picks the ONE query block this CTA scores, so the unbounded first pushes of
+    // all query blocks run side by side instead of one after the other
+    const int qb_stride = n_qblocks;
+    const int qb_off = qb_split ? (int)blockIdx.y : 0;
+    if (qb_split) { qb_base += qb_off; n_qblocks = 1; }
+    // this launch scans rows [row_base, n) in chunks of rows_per_chunk; its lists are chunk_base + blockIdx.x
+    const int chunk = chunk_base + (int)blockIdx.x;
+    const int64_t row_begin = row_base + (int64_t)blockIdx.x * rows_per_chunk;
     const int64_t row_end = min(n, row_begin + rows_per_chunk);
     const int n_tiles = row_end > row_begin ? (int)((row_end - row_begin + UM_BN - 1) / UM_BN) : 0;
     const int n_kb = d / UM_BK;
@@ -292,7 +299,7 @@ dense_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
                 const uint32_t aphase = (uint32_t)(u >> 1) & 1;
                 const int b = (qb_base + qb) * UM_BM + qidx;
                 const bool q_valid = b < B;
-                uint64_t* my_list = lists + (((size_t)chunk * n_qblocks + qb) * UM_BM + qidx) * UM_CAP;
+                uint64_t* my_list = lists + (((size_t)chunk * qb_stride + qb_off + qb) * UM_BM + qidx) * UM_CAP;
                 float thr = S.thr[qb][qidx];
                 int cnt = S.cnt[qb][qidx];
                 // the query's global bound (k_sel-th best score over all rows scanned so far by any CTA,
@@ -373,6 +380,16 @@ dense_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
     }
 }
 
+// Publishes every query's bound from its histograms (one warp per query): run after the seed launch so that the
+// main launch starts with the seed rows' k_sel-th best score instead of flooding its first tile into the lists.
+__global__ void um_bound_kernel(const uint32_t* __restrict__ coarse, const uint32_t* __restrict__ fine,
+                                uint32_t* __restrict__ gthr, int q_lo, int q_hi, int k_sel) {
+    const int q = q_lo + (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5);
+    if (q >= q_hi) return;
+    const uint32_t bound = hist_bound(coarse, fine, q, (uint32_t)k_sel, (int)(threadIdx.x & 31));
+    if ((threadIdx.x & 31) == 0 && bound != 0u) atomicMax(gthr + q, bound);
+}
+
 // ------------------------------------------------------------------ final per-query selection
 // Gathers, from the n_chunks unsorted (CTA, query) lists, the candidates that reach the query's
 // final bound (at least k_sel of them do), sorts them and writes the best k_sel keys.
@@ -432,7 +449,12 @@ cudaError_t dense_umma_plan(int64_t n, int d, int B, int k_sel, int num_sms, Umm
     (void)d;
     plan->n_qblocks = (B + UM_BM - 1) / UM_BM;
     const int64_t n_tiles = (n + UM_BN - 1) / UM_BN;
-    plan->n_chunks = (int)std::min<int64_t>(num_sms, std::max<int64_t>(1, n_tiles));   // one persistent CTA per SM
+    // Seed launch: for batches of more than 64 queries over a corpus of >= 64 tiles, a few single-tile CTAs scan the
+    // first rows and their k_sel-th best score becomes every query's starting bound.  Without it every CTA of the
+    // main launch pushes its whole first tile (min(n, 148 * 256) candidates per query) before a bound exists.
+    plan->n_seed = (B > 64 && n_tiles >= 64) ? (int)std::min<int64_t>(8, n_tiles / 8) : 0;
+    const int n_main = (int)std::min<int64_t>(num_sms, std::max<int64_t>(1, n_tiles - plan->n_seed));   // one persistent CTA per SM
+    plan->n_chunks = n_main + plan->n_seed;
     const int qb_launch = std::min(plan->n_qblocks, UM_MAXQB);   // lists are reused by successive query groups
     auto up = [](size_t x) { return (x + 255) & ~(size_t)255; };
     plan->list_bytes = up((size_t)plan->n_chunks * qb_launch * UM_BM * UM_CAP * sizeof(uint64_t));
@@ -505,15 +527,31 @@ cudaError_t dense_umma_scan(const void* X16, int dtype, int64_t n, int d, const 
     cudaError_t err = cudaMemsetAsync(gthr, 0, plan.gthr_bytes + plan.coarse_bytes + plan.fine_bytes, st);
     if (err != cudaSuccess) return err;
     const int64_t n_tiles = (n + UM_BN - 1) / UM_BN;
-    const int64_t rows_per_chunk = (n_tiles + plan.n_chunks - 1) / plan.n_chunks * UM_BN;
+    const int n_seed = plan.n_seed, n_main = plan.n_chunks - plan.n_seed;
+    const int64_t seed_rows = (int64_t)n_seed * UM_BN;
+    const int64_t rows_per_chunk = (n_tiles - n_seed + n_main - 1) / n_main * UM_BN;
     int nl = 0;
     // query groups of <= UM_MAXQB blocks (1024 queries): each group is one pass over the corpus
     for (int qb0 = 0; qb0 < plan.n_qblocks; qb0 += UM_MAXQB) {
         const int nqb = std::min(UM_MAXQB, plan.n_qblocks - qb0);
-        dense_umma_kernel<<<plan.n_chunks, UM_THREADS, smem, st>>>(tq, tx, n, d, B, qb0, nqb, rows_per_chunk, mask, k_sel,
-                                                                  idesc, lists, counts, gthr, coarse, fine);
-        if ((err = cudaGetLastError()) != cudaSuccess) return err;
         const int nq = std::min(B - qb0 * UM_BM, nqb * UM_BM);
+        if (n_seed > 0) {
+            dense_umma_kernel<<<dim3(n_seed, nqb), UM_THREADS, smem, st>>>(tq, tx, seed_rows, d, B, qb0, nqb, 1, 0, n_main,
+                                                                          UM_BN, mask, k_sel, idesc, lists, counts, gthr,
+                                                                          coarse, fine);
+            if ((err = cudaGetLastError()) != cudaSuccess) return err;
+            um_bound_kernel<<<(nq + 7) / 8, 256, 0, st>>>(coarse, fine, gthr, qb0 * UM_BM, qb0 * UM_BM + nq, k_sel);
+            if ((err = cudaGetLastError()) != cudaSuccess) return err;
+            nl += 2;
+        }
+        dense_umma_kernel<<<n_main, UM_THREADS, smem, st>>>(tq, tx, n, d, B, qb0, nqb, 0, seed_rows, 0, rows_per_chunk, mask,
+                                                           k_sel, idesc, lists, counts, gthr, coarse, fine);
+        if ((err = cudaGetLastError()) != cudaSuccess) return err;
+        // final bounds from the complete histograms (a CTA's manager stops with its own CTA, so the bounds it left
+        // may predate the last pushes of the others): the selection then gathers ~k_sel keys per query, not more
+        um_bound_kernel<<<(nq + 7) / 8, 256, 0, st>>>(coarse, fine, gthr, qb0 * UM_BM, qb0 * UM_BM + nq, k_sel);
+        if ((err = cudaGetLastError()) != cudaSuccess) return err;
+        ++nl;
         dense_umma_select_kernel<<<nq, SELK_THREADS, SELK_CAP * 8, st>>>(lists, counts, gthr, plan.n_chunks, B, qb0, nqb,
                                                                         k_sel, cand);
         if ((err = cudaGetLastError()) != cudaSuccess) return err;

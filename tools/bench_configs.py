@@ -75,10 +75,65 @@ words.scatter_add_(0, idx // 32, (1 << (idx % 32)).to(torch.int64))
 eng.mask_set(1, words.to(torch.int32))
 for B in (1, 1024):
     qb = q[:B].contiguous()
-    scan = stage_ms(lambda: eng.dense_topk("c2", qb, k, mask_id=1), "dense_scan")
-    out[f"C5like_dense_1Mx768_f16_mask10pct_B{B}"] = {"scan_kernel_ms": scan, "rows_kept": int(mask.sum().item())}
+    rec = {"rows_kept": int(mask.sum().item())}
+    for label, path in (("full_space_masked", "tcgen05_full"), ("compacted_copy", "tcgen05")):
+        eng.force_dense_path(path)
+        rec[label + "_scan_ms"] = stage_ms(lambda: eng.dense_topk("c2", qb, k, mask_id=1), "dense_scan")
+    eng.force_dense_path(None)
+    out[f"C5like_dense_1Mx768_f16_mask10pct_B{B}"] = rec
 eng.dense_drop("c2")
 torch.cuda.empty_cache()
+
+
+def pack_mask(m):
+    w = torch.zeros((m.numel() + 31) // 32, dtype=torch.int64, device=dev)
+    ix = torch.nonzero(m).squeeze(1)
+    w.scatter_add_(0, ix // 32, (1 << (ix % 32)).to(torch.int64))
+    return w.to(torch.int32)
+
+
+# ---- C5 shard (1 of 8 GPUs): 12.5M x 384 fp16 + BM25 over the same 12.5M docs, 10 % payload filter
+if "--c5" in sys.argv:
+    n5, d5 = 12_500_000, 384
+    x = synth.dense_corpus_torch(n5, d5, torch.float16, dev)
+    q5 = synth.dense_queries_torch(x, 4096)
+    eng.dense_set("c5", x)
+    del x
+    torch.cuda.empty_cache()
+    tp, doc, w = synth.zipf_corpus_torch(n5, 50000, 285, dev)
+    qp, qt, qv = synth.sparse_queries_torch(tp, 4096, 8)
+    eng.sparse_set_csr("c5s", tp, doc, w, n5)
+    del doc, w
+    torch.cuda.empty_cache()
+    g = torch.Generator(device=dev)
+    g.manual_seed(synth.SEED_MASK)
+    m5 = torch.rand(n5, generator=g, device=dev) < 0.10
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    eng.mask_set(2, pack_mask(m5))
+    a.record()
+    eng.dense_topk("c5", q5[:1].contiguous(), k, mask_id=2)       # first call under this filter: builds the copy
+    b.record()
+    torch.cuda.synchronize()
+    rec = {"rows_kept": int(m5.sum().item()), "first_call_with_copy_build_ms": a.elapsed_time(b)}
+    qp_d, qt_d, qv_d = qp.to(dev), qt.to(dev), qv.to(dev)
+    for B in (1, 4096):
+        qb = q5[:B].contiguous()
+        qpb, qtb, qvb = qp_d[:B + 1].contiguous(), qt_d[:8 * B].contiguous(), qv_d[:8 * B].contiguous()
+        for mid, label in ((2, "filtered"), (0, "unfiltered")):
+            p50, best = timeit(lambda: eng.hybrid_topk("c5", "c5s", qb, qpb, qtb, qvb, k, mask_id=mid), iters=10)
+            fn = lambda: eng.hybrid_topk("c5", "c5s", qb, qpb, qtb, qvb, k, mask_id=mid)
+            fn(); eng.profile_reset()
+            for _ in range(5):
+                fn()
+            ms, calls, _ = eng.profile_read()
+            rec[f"hybrid_B{B}_{label}"] = {"call_p50_ms": p50, "qps_per_gpu": B / (p50 * 1e-3),
+                                           "dense_scan_ms": ms["dense_scan"] / 5, "sparse_scan_ms": ms["sparse_scan"] / 5}
+    rec["hbm_floor_ms_B1_filtered"] = (n5 / 8 + 0.10 * n5 * (d5 * 2 + 4)) / (peaks["hbm_gbs"] * 1e9) * 1e3
+    rec["tensor_floor_ms_B4096_filtered"] = 2.0 * 0.10 * n5 * d5 * 4096 / (peaks["bf16_tflops_sustained"] * 1e12) * 1e3
+    out["C5_shard_12.5Mx384_f16_mask10pct"] = rec
+    eng.dense_drop("c5")
+    eng.sparse_drop("c5s")
+    torch.cuda.empty_cache()
 
 # ---- C3: BM25 top-100 over 1M docs, 50k-term Zipf vocab, 8-term queries, batch 1024
 nd, V = 1 << 20, 50000
