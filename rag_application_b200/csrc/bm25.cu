@@ -353,6 +353,7 @@ Bm25Plan bm25_plan(int64_t n_docs, int B, int k_sel, int num_sms) {
     if (splits > 64) splits = 64;
     p.splits = splits;
     p.lists_per_query = splits * p.workers;
+    p.visits_per_list = ns / p.lists_per_query;
     int64_t items = (int64_t)splits * B;
     p.grid = (int)(items < resident ? items : resident);
     auto up = [](size_t x) { return (x + 255) & ~(size_t)255; };

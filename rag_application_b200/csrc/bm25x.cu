@@ -588,9 +588,10 @@ Bm25Plan bm25x_plan(int64_t n_docs, int B, int k_sel, int max_terms, int num_sms
     int max_splits = (nt + p.workers - 1) / p.workers;
     if (splits > max_splits) splits = max_splits;
     if (splits < 1) splits = 1;
-    if (splits > 64) splits = 64;
+    if (splits > resident) splits = resident;     // batch 1: one split per SM
     p.splits = splits;
     p.lists_per_query = splits * p.workers;
+    p.visits_per_list = nt / p.lists_per_query;
     int64_t items = (int64_t)splits * B;
     p.grid = (int)(items < resident ? items : resident);
     auto up = [](size_t x) { return (x + 255) & ~(size_t)255; };

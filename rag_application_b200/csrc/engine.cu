@@ -394,6 +394,10 @@ void sparse_topk_dev(brag_engine* e, SparseSpace& s, const int32_t* q_ptr, const
     REQUIRE(B >= 1 && k >= 1 && k <= 512, "sparse_topk: need B >= 1 and 1 <= k <= 512");
     // bitmap-filter scan unless the space has non-finite weights or a query is longer than 32 terms
     bool bitmap = s.bitmap_ok && e->force_sparse_path != 0;
+    // (checked first with the 32-term variant, which has the fewest lists: batch-1 calls on device pointers then
+    // skip the copy of q_ptr that finding the longest query needs)
+    if (bitmap && e->force_sparse_path < 0 && brag::bm25x_plan(s.n_docs, B, k, 32, e->num_sms).visits_per_list < 4)
+        bitmap = false;
     if (bitmap) {
         if (max_terms < 0) max_terms = max_terms_dev(e, q_ptr, B, st);
         bitmap = brag::bm25x_supported(max_terms, k);
@@ -401,6 +405,13 @@ void sparse_topk_dev(brag_engine* e, SparseSpace& s, const int32_t* q_ptr, const
     REQUIRE(bitmap || e->force_sparse_path != 1, "sparse_topk: the bitmap scan was forced but cannot run this batch");
     brag::Bm25Plan plan = bitmap ? brag::bm25x_plan(s.n_docs, B, k, max_terms, e->num_sms)
                                  : brag::bm25_plan(s.n_docs, B, k, e->num_sms);
+    // A worker warp's first visit of a work item has no bound yet and scores every document that shares a term, so
+    // the filter only pays when a list covers several tiles: small batches (one split per SM) and small corpora go
+    // to the exhaustive kernel (measured crossover at C4: batch ~32, tools/bm25_probe.py)
+    if (bitmap && e->force_sparse_path < 0 && plan.visits_per_list < 4) {
+        bitmap = false;
+        plan = brag::bm25_plan(s.n_docs, B, k, e->num_sms);
+    }
     const int P = plan.lists_per_query;
     uint64_t* part = e->part.as<uint64_t>((size_t)P * B * k);
     uint64_t* merged = e->keys1.as<uint64_t>((size_t)B * k);

@@ -72,6 +72,7 @@ cudaError_t bm25_build_suboffsets(const int64_t* term_ptr, const uint2* post, in
                                   uint32_t* sub_off, cudaStream_t st);
 struct Bm25Plan {
     int splits; int lists_per_query; int grid; int workers;
+    int visits_per_list;    // tiles a worker warp visits per work item (bm25x: the first one runs without a bound)
     size_t gthr_bytes, coarse_bytes, fine_bytes, scratch_bytes;
 };
 Bm25Plan bm25_plan(int64_t n_docs, int B, int k_sel, int num_sms);
