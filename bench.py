@@ -334,9 +334,14 @@ def main():
                          "flops_per_launch": flops, "avg_launch_ms": dense_ms},
             "cpu_baseline": cpu, "batch1": b1,
             "stages_ms_per_step": {s: stage_ms[s] / args.steps for s in stage_ms},
-            "bm25": {"algorithmic_bytes_per_step": bm25_bytes, "ms": bm_ms,
+            # second kernel of the step: the sparse scan against the HBM roofline, on the ALGORITHMIC bytes an
+            # exhaustive posting scan reads (sum_t df_t * 8 B); `traffic` = DRAM bytes the pruning kernel really moves
+            "bm25": {"kernel": "bm25x_scan_kernel (bitmap-filter BM25 scan + fused top-k)", "bound": "hbm",
+                     "algorithmic_bytes_per_step": bm25_bytes, "ms": bm_ms,
                      "achieved_gbs": bm25_bytes / (bm_ms * 1e-3) / 1e9 if bm_ms > 0 else None,
-                     "peak_gbs": peaks["hbm_gbs"]},
+                     "peak_gbs": peaks["hbm_gbs"],
+                     "frac": bm25_bytes / (bm_ms * 1e-3) / 1e9 / peaks["hbm_gbs"] if bm_ms > 0 else None,
+                     "traffic": ncu_traffic("bm25x_scan_kernel", world)},
         }
         print(json.dumps(line), flush=True)
     if world > 1:

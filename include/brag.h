@@ -130,6 +130,20 @@ int brag_force_dense_path(brag_engine* e, int32_t path);
  * the batch has more than 32 terms or the space holds non-finite weights; both give identical results. */
 int brag_force_sparse_path(brag_engine* e, int32_t path);
 
+/* ---- the sparse encoder the reference runs before it calls the vector store
+ * (fastembed SparseTextEmbedding("Qdrant/bm25").embed, embedding_handler.py:41,123-138).  Host-only code.
+ * tokens: the document after fastembed's normalisation (non-word characters -> space, lower-case, whitespace split),
+ * concatenated; token i = tokens[tok_off[i] .. tok_off[i+1]).  Drops punctuation tokens, English stop words and
+ * tokens longer than max_token_len characters, stems (Snowball English), id = |murmur3_x86_32(stem, seed 0)|,
+ * value = tf*(k1+1)/(tf + k1*(1-b+b*len/avgdl)) (query_mode != 0: value = 1, fastembed's query_embed).
+ * out_ids / out_vals need n_tokens slots; ids come in first-occurrence order. */
+int brag_bm25_encode(const char* tokens, const int32_t* tok_off, int32_t n_tokens, double k1, double b,
+                     double avgdl, int32_t max_token_len, int32_t query_mode, int64_t* out_ids,
+                     double* out_vals, int32_t* out_n);
+/* Snowball English (Porter2) stem of one lower-case word; MurmurHash3 x86_32 -- exposed for the known-answer tests. */
+int brag_bm25_stem(const char* word, char* out, int32_t cap);
+uint32_t brag_murmur3_32(const void* data, int32_t len, uint32_t seed);
+
 #ifdef __cplusplus
 }
 #endif
