@@ -169,6 +169,8 @@ def main():
     dev = torch.device("cuda", local)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
+            os.environ.pop("NCCL_DEBUG")        # its banner goes to stdout, which carries the one JSON line
         dist.init_process_group("nccl", device_id=dev)
     peaks = load_peaks()
     tdt = torch.bfloat16 if args.dtype == "bf16" else torch.float16

@@ -207,7 +207,8 @@ bm25x_scan_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict_
                   const float2* __restrict__ wrange, const float* __restrict__ tau, int64_t V, int64_t n_docs,
                   const int32_t* __restrict__ q_ptr, const int32_t* __restrict__ q_terms,
                   const double* __restrict__ q_vals, int B, const uint32_t* __restrict__ mask, int k_sel, int lcap,
-                  int nw, uint64_t* __restrict__ part, int splits, int* __restrict__ work_counter,
+                  int nw, uint64_t* __restrict__ part, int splits, int seed_tiles, int seed_qpi, int seed_mode,
+                  int* __restrict__ work_counter,
                   uint32_t* __restrict__ gthr, uint32_t* __restrict__ coarse, uint32_t* __restrict__ fine) {
     using C = BxCfg<MAXT, SUBS>;
     constexpr int WPL = C::WPL, WORDS = C::WORDS, POOL = C::POOL, PLANES = C::PLANES;
@@ -248,9 +249,13 @@ bm25x_scan_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict_
     const int ns = (int)((n_docs + BM25_SUB - 1) / BM25_SUB);
     const int ns1 = ns + 1;
     const int nt = (ns + SUBS - 1) / SUBS;                    // tiles of SUBS sub-tiles
-    const int nt_per_split = (nt + splits - 1) / splits;
+    // Seed launch (seed_mode): work item = seed_qpi queries, warp w scans the first seed_tiles tiles for query
+    // item * seed_qpi + w and writes list number splits * nw.  Main launch: tiles [seed_tiles, nt) in `splits` ranges,
+    // work item = (range, query), warp w takes every nw-th tile and writes list range * nw + w.  The seed's bound
+    // (k-th best of its few thousand documents) keeps the main launch's first visits from scoring every document.
+    const int nt_per_split = (nt - seed_tiles + splits - 1) / splits;
     const size_t row_words = (size_t)((ns + 3) / 4 * 4) * BX_WORDS;
-    const int n_items = splits * B;
+    const int n_items = seed_mode ? (B + seed_qpi - 1) / seed_qpi : splits * B;
     const double sentinel = __longlong_as_double((long long)BX_SENTINEL);
 
     while (true) {
@@ -259,10 +264,21 @@ bm25x_scan_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict_
         worker_bar(nw * 32);
         const int item = s_item;
         if (item >= n_items) break;
-        const int split = item / B, q = item - split * B;
+        int q, j_first, j_end, j_stride, slot;
+        if (seed_mode) {
+            q = item * seed_qpi + warp;
+            j_first = 0; j_stride = 1; slot = splits * nw;
+            j_end = (warp < seed_qpi && q < B) ? min(seed_tiles, nt) : 0;
+            if (j_end == 0) continue;                      // idle warp of a seed item (no CTA-wide sync below)
+        } else {
+            const int split = item / B;
+            q = item - split * B;
+            const int j_begin = seed_tiles + split * nt_per_split;
+            j_first = j_begin + warp; j_stride = nw; slot = split * nw + warp;
+            j_end = min(nt, j_begin + nt_per_split);
+        }
         const int qb = q_ptr[q];
         const int nq = min(q_ptr[q + 1] - qb, MAXT);      // the launcher guarantees nq <= MAXT
-        const int j_begin = split * nt_per_split, j_end = min(nt, j_begin + nt_per_split);
         uint64_t thr = 0ull;
         double pre_local = -INFINITY;
         if (lane == 0) *cntp = 0;
@@ -311,22 +327,22 @@ bm25x_scan_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict_
         __syncwarp();
 
         uint32_t lo_nx = 0, hi_nx = 0;
-        if (t0 >= 0 && j_begin + warp < j_end) {
-            const int s_lo = (j_begin + warp) * SUBS;
+        if (t0 >= 0 && j_first < j_end) {
+            const int s_lo = j_first * SUBS;
             lo_nx = __ldg(so + s_lo);
             hi_nx = __ldg(so + min(ns, s_lo + SUBS));
         }
         uint32_t g_seen = 0u;
         double pre_g = -INFINITY;
 #pragma unroll 1
-        for (int j = j_begin + warp; j < j_end; j += nw) {
+        for (int j = j_first; j < j_end; j += j_stride) {
             const uint32_t tile_base = (uint32_t)j * C::TILE;
             const uint32_t g = __ldcg(gthr + q);
             if (g != g_seen) { g_seen = g; pre_g = prefilter_of_score(ordered_f32(g)); }
             double pre_eff = fmax(pre_local, pre_g);
             const uint32_t lo_cur = lo_nx, hi_cur = hi_nx;
-            if (t0 >= 0 && j + nw < j_end) {
-                const int s_lo = (j + nw) * SUBS;
+            if (t0 >= 0 && j + j_stride < j_end) {
+                const int s_lo = (j + j_stride) * SUBS;
                 lo_nx = __ldg(so + s_lo);
                 hi_nx = __ldg(so + min(ns, s_lo + SUBS));
             }
@@ -549,7 +565,7 @@ bm25x_scan_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict_
         }
         // ---- emit this warp's list for (split, warp, q)
         warp_compact(list, cntp, lcap, k_sel, thr, lane);
-        uint64_t* out = part + ((size_t)(split * nw + warp) * B + q) * k_sel;
+        uint64_t* out = part + ((size_t)slot * B + q) * k_sel;
         for (int i = lane; i < k_sel; i += 32) out[i] = list[i];
         __syncwarp();
     }
@@ -584,14 +600,20 @@ Bm25Plan bm25x_plan(int64_t n_docs, int B, int k_sel, int max_terms, int num_sms
     p.workers = (int)std::min<size_t>(BX_MAX_WORKERS, BX_SMEM_MAX / bx_warp_bytes(bx_maxt(max_terms), subs, bx_lcap(k_sel)));
     p.workers = std::max(1, std::min(p.workers, nt));
     const int resident = num_sms;
+    // seed launch: BRAG_BX_SEED tiles per query (default 2; measured at C4 / a 1.25 M-document shard: 8.6 / 2.48 ms
+    // without, 8.0 / 1.88 ms with), when the corpus has tiles to spare
+    static const int seed_cfg = [] { const char* e = getenv("BRAG_BX_SEED"); const int v = e ? atoi(e) : 2; return v < 0 ? 0 : (v > 4 ? 4 : v); }();
+    p.seed_tiles = (nt >= 32) ? seed_cfg : 0;
+    p.seed_qpi = std::max(1, std::min(p.workers, (B + resident - 1) / resident));
+    const int nt_main = nt - p.seed_tiles;
     int splits = (resident * 8 + B - 1) / B;
-    int max_splits = (nt + p.workers - 1) / p.workers;
+    int max_splits = (nt_main + p.workers - 1) / p.workers;
     if (splits > max_splits) splits = max_splits;
     if (splits < 1) splits = 1;
     if (splits > resident) splits = resident;     // batch 1: one split per SM
     p.splits = splits;
-    p.lists_per_query = splits * p.workers;
-    p.visits_per_list = nt / p.lists_per_query;
+    p.visits_per_list = nt_main / (splits * p.workers);
+    p.lists_per_query = splits * p.workers + (p.seed_tiles ? 1 : 0);
     int64_t items = (int64_t)splits * B;
     p.grid = (int)(items < resident ? items : resident);
     auto up = [](size_t x) { return (x + 255) & ~(size_t)255; };
@@ -627,9 +649,18 @@ static cudaError_t bx_launch(const BxArgs& a) {
     uint32_t* fine = reinterpret_cast<uint32_t*>(sp + 256 + plan.gthr_bytes + plan.coarse_bytes);
     cudaError_t e = cudaMemsetAsync(a.scratch, 0, plan.scratch_bytes, a.st);
     if (e != cudaSuccess) return e;
+    if (plan.seed_tiles > 0) {
+        const int seed_items = (a.B + plan.seed_qpi - 1) / plan.seed_qpi;
+        bm25x_scan_kernel<MAXT, SUBS><<<std::min(seed_items, plan.grid), (plan.workers + 1) * 32, smem, a.st>>>(
+            a.term_ptr, a.post, a.sub_off, a.bm_row, a.bits, a.bits_hi, a.wrange, a.tau, a.V, a.n_docs, a.q_ptr, a.q_terms,
+            a.q_vals, a.B, a.mask, a.k_sel, lcap, plan.workers, a.part, plan.splits, plan.seed_tiles, plan.seed_qpi, 1,
+            work_counter + 1, gthr, coarse, fine);
+        if ((e = cudaGetLastError()) != cudaSuccess) return e;
+    }
     bm25x_scan_kernel<MAXT, SUBS><<<plan.grid, (plan.workers + 1) * 32, smem, a.st>>>(
-        a.term_ptr, a.post, a.sub_off, a.bm_row, a.bits, a.bits_hi, a.wrange, a.tau, a.V, a.n_docs, a.q_ptr, a.q_terms, a.q_vals, a.B,
-        a.mask, a.k_sel, lcap, plan.workers, a.part, plan.splits, work_counter, gthr, coarse, fine);
+        a.term_ptr, a.post, a.sub_off, a.bm_row, a.bits, a.bits_hi, a.wrange, a.tau, a.V, a.n_docs, a.q_ptr, a.q_terms,
+        a.q_vals, a.B, a.mask, a.k_sel, lcap, plan.workers, a.part, plan.splits, plan.seed_tiles, plan.seed_qpi, 0,
+        work_counter, gthr, coarse, fine);
     return cudaGetLastError();
 }
 

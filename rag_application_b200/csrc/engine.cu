@@ -424,7 +424,7 @@ void sparse_topk_dev(brag_engine* e, SparseSpace& s, const int32_t* q_ptr, const
         else
             CK(brag::bm25_scan(s.term_ptr, s.post, s.sub_off, s.V, s.n_docs, q_ptr, q_terms, q_vals, B, mask, k,
                                part, plan, scratch, st));
-        e->kernel_launches += 1;
+        e->kernel_launches += 1 + ((bitmap && plan.seed_tiles > 0) ? 1 : 0);
     }
     {
         StageTimer t(e, 3, st);

@@ -73,6 +73,8 @@ cudaError_t bm25_build_suboffsets(const int64_t* term_ptr, const uint2* post, in
 struct Bm25Plan {
     int splits; int lists_per_query; int grid; int workers;
     int visits_per_list;    // tiles a worker warp visits per work item (bm25x: the first one runs without a bound)
+    int seed_tiles = 0;     // bm25x: tiles scanned per query by the seed launch (one warp per query, extra list)
+    int seed_qpi = 0;       // bm25x: queries per seed work item
     size_t gthr_bytes, coarse_bytes, fine_bytes, scratch_bytes;
 };
 Bm25Plan bm25_plan(int64_t n_docs, int B, int k_sel, int num_sms);
