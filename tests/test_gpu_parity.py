@@ -428,9 +428,10 @@ def test_hybrid_three_stage(engine):
             assert np.array_equal(s[b][:len(ei)], es)
 
 
-def test_two_shards_on_one_gpu_match_unsharded(engine):
-    """Row sharding emulated on one device: two engines own disjoint row ranges and answer with
-    global ids; gathered lists -> brag_merge_topk x2 -> brag_rrf must equal the unsharded hybrid call."""
+@pytest.mark.parametrize("G", [2, 4, 8])
+def test_logical_shards_on_one_gpu_match_unsharded(engine, G):
+    """Row sharding emulated on one device: G engines own disjoint row ranges and answer
+    with global ids; gathered lists -> brag_merge_topk x2 -> brag_rrf must equal the unsharded hybrid call."""
     from rag_application_b200 import Engine
     from rag_application_b200.sharded import shard_bounds
     n, d, k, B, V = 9001, 128, 50, 20, 2000
@@ -444,8 +445,8 @@ def test_two_shards_on_one_gpu_match_unsharded(engine):
     term_of = np.repeat(np.arange(V), np.diff(ptr))
     lists = []
     shards = []
-    for r in range(2):
-        lo, hi = shard_bounds(n, 2, r)
+    for r in range(G):
+        lo, hi = shard_bounds(n, G, r)
         e = Engine(0)
         shards.append(e)
         e.set_id_offset(lo)
@@ -457,9 +458,9 @@ def test_two_shards_on_one_gpu_match_unsharded(engine):
         lists.append((e.dense_topk("dense", q, k), e.sparse_topk("sparse", q_ptr, q_terms, q_vals, k)))
     merged = []
     for which in range(2):
-        s = np.stack([lists[r][which][0] for r in range(2)])
-        i = np.stack([lists[r][which][1] for r in range(2)])
-        c = np.stack([lists[r][which][2] for r in range(2)])
+        s = np.stack([lists[r][which][0] for r in range(G)])
+        i = np.stack([lists[r][which][1] for r in range(G)])
+        c = np.stack([lists[r][which][2] for r in range(G)])
         merged.append(engine.merge_topk(s, i, c))
     ids = np.stack([merged[0][1], merged[1][1]])
     cnt = np.stack([merged[0][2], merged[1][2]])
