@@ -13,9 +13,9 @@ cudaError_t dense_gemv_scan(const void* X, int dtype, int64_t n, int d, const fl
 // ---- dense_umma.cu
 struct UmmaPlan {
     int n_qblocks;          // ceil(B / 128)
-    int n_chunks;           // corpus chunks = candidate lists per query: persistent CTAs of the main launch + n_seed
+    int n_chunks;           // persistent CTAs = corpus chunks = candidate lists per query
     int n_seed;             // single-tile CTAs of the seed launch (0 = no seeding)
-    size_t list_bytes, count_bytes, gthr_bytes, coarse_bytes, fine_bytes;
+    size_t list_bytes, count_bytes, gthr_bytes, coarse_bytes, fine_bytes, seed_bytes;
     size_t scratch_bytes;   // lists | counts | per-query bounds | coarse + fine score histograms
 };
 bool dense_umma_supported(int dtype, int d, int64_t n);
