@@ -432,9 +432,16 @@ void sparse_topk_dev(brag_engine* e, SparseSpace& s, const int32_t* q_ptr, const
         uint64_t* ta = e->tmp_a.as<uint64_t>(tmp);
         uint64_t* tb = e->tmp_b.as<uint64_t>(tmp);
         int launches = 0;
-        CK(brag::merge_key_lists(part, P, B, k, ta, tb, merged, k, st, &launches));
+        // both sparse kernels keep [work counters | bounds | coarse | fine histograms] in `scratch`: the bound of the
+        // complete histograms lets the merge drop all but a few hundred of the P * k keys before it sorts
+        uint8_t* sp = reinterpret_cast<uint8_t*>(scratch);
+        uint32_t* gthr = reinterpret_cast<uint32_t*>(sp + 256);
+        const uint32_t* coarse = reinterpret_cast<const uint32_t*>(sp + 256 + plan.gthr_bytes);
+        const uint32_t* fine = reinterpret_cast<const uint32_t*>(sp + 256 + plan.gthr_bytes + plan.coarse_bytes);
+        CK(brag::publish_bounds(coarse, fine, gthr, B, k, st));
+        CK(brag::merge_key_lists(part, P, B, k, ta, tb, merged, k, st, &launches, gthr));
         CK(brag::finalize_keys(merged, B, k, k, false, e->id_offset, out_scores, out_ids, out_counts, st));
-        e->kernel_launches += launches + 1;
+        e->kernel_launches += launches + 2;
     }
 }
 

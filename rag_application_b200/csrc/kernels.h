@@ -30,8 +30,11 @@ cudaError_t make_tmap_2d(void* tmap_out, const void* base, int64_t rows, int d, 
 
 // ---- select.cu
 // multi-level merge of P key lists per query: in [P][B][kk] -> out [B][kout] sorted desc
+// bound (optional, [B], f32_ordered units): keys whose score image is below it are dropped before sorting
 cudaError_t merge_key_lists(const uint64_t* in, int P, int B, int kk, uint64_t* tmp_a, uint64_t* tmp_b,
-                            uint64_t* out, int kout, cudaStream_t st, int* launches);
+                            uint64_t* out, int kout, cudaStream_t st, int* launches, const uint32_t* bound = nullptr);
+// gthr[q] = max(gthr[q], bound of query q's complete score histograms) -- see common.cuh
+cudaError_t publish_bounds(const uint32_t* coarse, const uint32_t* fine, uint32_t* gthr, int B, int k, cudaStream_t st);
 size_t merge_tmp_elems(int P, int B, int kk);
 // round queries to the storage dtype: Qs f32 (rounded values) and optional 16-bit copy (padded rows zero)
 cudaError_t round_queries(const float* Q, int B, int d, int dtype, float* Qs, void* Q16, int Bpad,

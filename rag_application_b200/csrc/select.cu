@@ -11,27 +11,62 @@ constexpr int SEL_THREADS = 512;
 constexpr int SEL_MAX = 8192;  // keys per CTA sort (64 KB of shared memory)
 
 // ------------------------------------------------------------------ merge of key lists
+// bound (optional): per-query lower bound of the kout-th best key's score image (f32_ordered units, 0 = none); keys
+// below it cannot be in the result, so they are dropped while loading and the sort runs over a few hundred keys
+// instead of P * kk.
 __global__ void __launch_bounds__(SEL_THREADS)
 merge_keys_kernel(const uint64_t* __restrict__ in, int P, int B, int kk, int GP,
-                  uint64_t* __restrict__ out, int kout) {
+                  uint64_t* __restrict__ out, int kout, const uint32_t* __restrict__ bound) {
     extern __shared__ __align__(16) uint8_t smem_raw[];
     uint64_t* a = reinterpret_cast<uint64_t*>(smem_raw);
+    __shared__ int fill;
     const int b = blockIdx.x, pg = blockIdx.y, tid = threadIdx.x;
     const int p0 = pg * GP, np = min(GP, P - p0);
     const int n_in = np * kk;
-    const int n2 = next_pow2(max(n_in, kout));
-    for (int i = tid; i < n2; i += SEL_THREADS) {
-        uint64_t v = 0ull;
-        if (i < n_in) {
-            int p = p0 + i / kk, j = i % kk;
-            v = in[((size_t)p * B + b) * kk + j];
+    int n2;
+    if (bound != nullptr) {
+        const uint32_t bnd = bound[b];
+        if (tid == 0) fill = 0;
+        __syncthreads();
+        for (int i = tid; i < n_in; i += SEL_THREADS) {
+            const int p = p0 + i / kk, j = i % kk;
+            const uint64_t v = in[((size_t)p * B + b) * kk + j];
+            if (v != 0ull && (uint32_t)(v >> 32) >= bnd) a[atomicAdd(&fill, 1)] = v;
         }
-        a[i] = v;
+        __syncthreads();
+        const int f = fill;
+        n2 = next_pow2(max(f, kout));
+        for (int i = f + tid; i < n2; i += SEL_THREADS) a[i] = 0ull;
+    } else {
+        n2 = next_pow2(max(n_in, kout));
+        for (int i = tid; i < n2; i += SEL_THREADS) {
+            uint64_t v = 0ull;
+            if (i < n_in) {
+                int p = p0 + i / kk, j = i % kk;
+                v = in[((size_t)p * B + b) * kk + j];
+            }
+            a[i] = v;
+        }
     }
     __syncthreads();
     bitonic_desc(a, n2, tid, SEL_THREADS, [] { __syncthreads(); });
     uint64_t* o = out + ((size_t)pg * B + b) * kout;
     for (int i = tid; i < kout; i += SEL_THREADS) o[i] = a[i];
+}
+
+// One warp per query: bound = highest histogram edge that at least k counted rows reach (common.cuh), published
+// with atomicMax.  Run after a scan so that the selection sees the bound of the COMPLETE histograms.
+__global__ void publish_bounds_kernel(const uint32_t* __restrict__ coarse, const uint32_t* __restrict__ fine,
+                                      uint32_t* __restrict__ gthr, int B, int k) {
+    const int q = (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5);
+    if (q >= B) return;
+    const uint32_t bound = hist_bound(coarse, fine, q, (uint32_t)k, (int)(threadIdx.x & 31));
+    if ((threadIdx.x & 31) == 0 && bound != 0u) atomicMax(gthr + q, bound);
+}
+
+cudaError_t publish_bounds(const uint32_t* coarse, const uint32_t* fine, uint32_t* gthr, int B, int k, cudaStream_t st) {
+    publish_bounds_kernel<<<(B + 7) / 8, 256, 0, st>>>(coarse, fine, gthr, B, k);
+    return cudaGetLastError();
 }
 
 size_t merge_tmp_elems(int P, int B, int kk) {
@@ -41,7 +76,7 @@ size_t merge_tmp_elems(int P, int B, int kk) {
 }
 
 cudaError_t merge_key_lists(const uint64_t* in, int P, int B, int kk, uint64_t* tmp_a, uint64_t* tmp_b,
-                            uint64_t* out, int kout, cudaStream_t st, int* launches) {
+                            uint64_t* out, int kout, cudaStream_t st, int* launches, const uint32_t* bound) {
     static bool attr_set = false;
     if (!attr_set) {
         cudaError_t e = cudaFuncSetAttribute(merge_keys_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -62,7 +97,7 @@ cudaError_t merge_key_lists(const uint64_t* in, int P, int B, int kk, uint64_t* 
         int n_in = min(GP, P) * kk;
         int n2 = 1;
         while (n2 < max(n_in, ko)) n2 <<= 1;
-        merge_keys_kernel<<<dim3(B, PG), SEL_THREADS, (size_t)n2 * 8, st>>>(cur, P, B, kk, GP, dst, ko);
+        merge_keys_kernel<<<dim3(B, PG), SEL_THREADS, (size_t)n2 * 8, st>>>(cur, P, B, kk, GP, dst, ko, bound);
         cudaError_t e = cudaGetLastError();
         if (e != cudaSuccess) return e;
         if (launches) ++*launches;
