@@ -49,6 +49,13 @@ int brag_set_id_offset(brag_engine* e, int64_t offset);
  * already L2-normalised by the caller when the space is COSINE.  The engine copies. */
 int brag_dense_set(brag_engine* e, const char* name, const void* rows, int64_t n, int32_t d,
                    int32_t dtype, int32_t on_device);
+/* SURVEY 8 row f2 (incremental upsert, qdrant_handler.py:190,259): append n_new rows to an existing dense space
+ * without re-uploading it (capacity doubles when full; rows in the space's storage dtype, prepared like
+ * brag_dense_set's), and overwrite existing rows in place (row_ids: host int64 [m] local rows; rows: host [m, d]).
+ * Both synchronise the device and drop any filter-compacted copy of the space. */
+int brag_dense_append(brag_engine* e, const char* name, const void* rows, int64_t n_new, int32_t d,
+                      int32_t dtype, int32_t on_device);
+int brag_dense_update(brag_engine* e, const char* name, const int64_t* row_ids, const void* rows, int64_t m);
 int brag_dense_drop(brag_engine* e, const char* name);
 
 /* Sparse corpus upload: term-major CSR of the sparse named vector (qdrant_handler.py:80-86,

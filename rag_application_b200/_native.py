@@ -21,6 +21,8 @@ PROTOTYPES = {
     "brag_version": (C.c_int, []),
     "brag_set_id_offset": (C.c_int, [c_p, i64]),
     "brag_dense_set": (C.c_int, [c_p, C.c_char_p, c_p, i64, i32, i32, i32]),
+    "brag_dense_append": (C.c_int, [c_p, C.c_char_p, c_p, i64, i32, i32, i32]),
+    "brag_dense_update": (C.c_int, [c_p, C.c_char_p, c_p, c_p, i64]),
     "brag_dense_drop": (C.c_int, [c_p, C.c_char_p]),
     "brag_sparse_set_csr": (C.c_int, [c_p, C.c_char_p, c_p, c_p, c_p, i64, i64, i32]),
     "brag_sparse_drop": (C.c_int, [c_p, C.c_char_p]),

@@ -156,6 +156,9 @@ class _Collection:
         self.sparse_rows: Dict[str, List[Optional[Tuple[np.ndarray, np.ndarray]]]] = {v: [] for v in self.sparse_cfg}
         self.version = 0            # bumped by every mutation
         self.committed = -1         # version present in HBM
+        # incremental upload: rows already in HBM per dense space, and which of them were overwritten
+        self.dense_in_hbm: Dict[str, int] = {}
+        self.dense_dirty: Dict[str, set] = {v: set() for v in self.dense_cfg}
         # filled by commit()
         self.term_ids: Dict[str, np.ndarray] = {}     # sparse space -> sorted external indices (row = position)
         self.df: Dict[str, np.ndarray] = {}
@@ -209,6 +212,8 @@ class _Collection:
             self.payloads[row] = payload
             for vname, a in dense.items():
                 self.dense_rows[vname][row] = a
+                if row < self.dense_in_hbm.get(vname, 0):
+                    self.dense_dirty[vname].add(row)
             for vname, sv in sparse.items():
                 self.sparse_rows[vname][row] = sv
         self.version += 1
@@ -228,15 +233,31 @@ class _Collection:
             if n == 0 or not have.any():
                 engine.dense_drop(self.space(vname))
                 self.present[vname] = np.zeros(n, dtype=bool)
+                self.dense_in_hbm[vname] = 0
+                self.dense_dirty[vname].clear()
                 continue
-            x = np.zeros((n, size), dtype=np.float32)
-            for i, r in enumerate(rows):
-                if r is not None:
-                    x[i] = r
-            if dist == "cosine":
-                x = _normalize_rows(x)
-            engine.dense_set(self.space(vname), x, storage)
+            n_old = self.dense_in_hbm.get(vname, 0)
+            if 0 < n_old <= n and have.all() and self.present.get(vname, False) is None:
+                # every row has the vector, before and now: append the new rows and overwrite the changed ones in
+                # place (brag_dense_append / brag_dense_update) instead of re-uploading the space
+                if n > n_old:
+                    xa = np.stack(rows[n_old:]).astype(np.float32)
+                    engine.dense_append(self.space(vname), _normalize_rows(xa) if dist == "cosine" else xa)
+                dirty = sorted(self.dense_dirty[vname])
+                if dirty:
+                    xu = np.stack([rows[i] for i in dirty]).astype(np.float32)
+                    engine.dense_update(self.space(vname), dirty, _normalize_rows(xu) if dist == "cosine" else xu)
+            else:
+                x = np.zeros((n, size), dtype=np.float32)
+                for i, r in enumerate(rows):
+                    if r is not None:
+                        x[i] = r
+                if dist == "cosine":
+                    x = _normalize_rows(x)
+                engine.dense_set(self.space(vname), x, storage)
             self.present[vname] = None if have.all() else have
+            self.dense_in_hbm[vname] = n
+            self.dense_dirty[vname].clear()
         for vname in self.sparse_cfg:
             rows = self.sparse_rows[vname]
             have = [i for i, r in enumerate(rows) if r is not None]

@@ -60,6 +60,7 @@ struct DevBuf {
 struct DenseSpace {
     void* x = nullptr;
     int64_t n = 0;
+    int64_t cap = 0;               // rows allocated (brag_dense_append grows by doubling)
     int d = 0;
     int dtype = 0;
     bool umma_ok = false;
@@ -537,7 +538,7 @@ int brag_dense_set(brag_engine* e, const char* name, const void* rows, int64_t n
         auto it = e->dense.find(name);
         if (it != e->dense.end()) { CK(cudaDeviceSynchronize()); free_dense(it->second); e->dense.erase(it); }
         DenseSpace s;
-        s.n = n; s.d = d; s.dtype = dtype;
+        s.n = n; s.cap = n; s.d = d; s.dtype = dtype;
         const size_t bytes = (size_t)n * d * esz;
         CK(cudaMalloc(&s.x, bytes));
         cudaError_t ce = cudaMemcpy(s.x, rows, bytes, on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice);
@@ -548,6 +549,56 @@ int brag_dense_set(brag_engine* e, const char* name, const void* rows, int64_t n
             if (te != cudaSuccess) s.umma_ok = false;
         }
         e->dense[name] = s;
+    });
+}
+
+int brag_dense_append(brag_engine* e, const char* name, const void* rows, int64_t n_new, int32_t d, int32_t dtype,
+                      int32_t on_device) {
+    return guarded([&] {
+        REQUIRE(e && name && rows && n_new >= 1, "brag_dense_append: bad arguments");
+        use_device(e);
+        auto it = e->dense.find(name);
+        REQUIRE(it != e->dense.end(), std::string("brag_dense_append: unknown dense space: ") + name);
+        DenseSpace& s = it->second;
+        REQUIRE(s.d == d && s.dtype == dtype, "brag_dense_append: dimension / storage type differ from the space");
+        REQUIRE(s.n + n_new < (int64_t)0xFFFFFFFFll, "brag_dense_append: too many rows");
+        const size_t row_bytes = (size_t)d * (dtype == 0 ? 4 : 2);
+        CK(cudaDeviceSynchronize());                      // no scan may still read the buffer that is about to move
+        if (s.n + n_new > s.cap) {
+            const int64_t cap = std::max<int64_t>(s.n + n_new, s.cap * 2);
+            void* nx = nullptr;
+            CK(cudaMalloc(&nx, (size_t)cap * row_bytes));
+            cudaError_t ce = cudaMemcpy(nx, s.x, (size_t)s.n * row_bytes, cudaMemcpyDeviceToDevice);
+            if (ce != cudaSuccess) { cudaFree(nx); CK(ce); }
+            cudaFree(s.x);
+            s.x = nx;
+            s.cap = cap;
+        }
+        CK(cudaMemcpy(static_cast<char*>(s.x) + (size_t)s.n * row_bytes, rows, (size_t)n_new * row_bytes,
+                      on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice));
+        s.n += n_new;
+        s.umma_ok = brag::dense_umma_supported(s.dtype, s.d, s.n) &&
+                    brag::make_tmap_2d(s.tmap_x, s.x, s.n, s.d, 256) == cudaSuccess;
+        s.cp_mask_id = 0;                                 // any filter-compacted copy is stale
+        s.cp_use = false;
+    });
+}
+
+int brag_dense_update(brag_engine* e, const char* name, const int64_t* row_ids, const void* rows, int64_t m) {
+    return guarded([&] {
+        REQUIRE(e && name && row_ids && rows && m >= 1, "brag_dense_update: bad arguments");
+        use_device(e);
+        DenseSpace& s = dense_space(e, name);
+        const size_t row_bytes = (size_t)s.d * (s.dtype == 0 ? 4 : 2);
+        for (int64_t i = 0; i < m; ++i)
+            REQUIRE(row_ids[i] >= 0 && row_ids[i] < s.n, "brag_dense_update: row id out of range");
+        CK(cudaDeviceSynchronize());
+        for (int64_t i = 0; i < m; ++i)
+            CK(cudaMemcpyAsync(static_cast<char*>(s.x) + (size_t)row_ids[i] * row_bytes,
+                               static_cast<const char*>(rows) + (size_t)i * row_bytes, row_bytes, cudaMemcpyHostToDevice, 0));
+        CK(cudaDeviceSynchronize());
+        s.cp_mask_id = 0;
+        s.cp_use = false;
     });
 }
 

@@ -92,6 +92,24 @@ class Engine:
             _native.check(self._lib.brag_dense_set(self._h, name.encode(), st.ctypes.data, n, d, DTYPES[dtype], 0))
         self._spaces[name] = (n, d, dtype)
 
+    def dense_append(self, name: str, rows):
+        """Append float32 [m,d] rows (host) to an existing space, converted to its storage dtype."""
+        n, d, dtype = self._spaces[name]
+        rows = np.asarray(rows)
+        assert rows.ndim == 2 and rows.shape[1] == d
+        st = to_storage(rows, dtype)
+        _native.check(self._lib.brag_dense_append(self._h, name.encode(), st.ctypes.data, rows.shape[0], d, DTYPES[dtype], 0))
+        self._spaces[name] = (n + rows.shape[0], d, dtype)
+
+    def dense_update(self, name: str, row_ids, rows):
+        """Overwrite rows `row_ids` (local) with float32 [m,d] rows (host)."""
+        n, d, dtype = self._spaces[name]
+        ids = np.ascontiguousarray(row_ids, dtype=np.int64)
+        rows = np.asarray(rows)
+        assert rows.shape == (len(ids), d)
+        st = to_storage(rows, dtype)
+        _native.check(self._lib.brag_dense_update(self._h, name.encode(), ids.ctypes.data, st.ctypes.data, len(ids)))
+
     def dense_drop(self, name: str):
         _native.check(self._lib.brag_dense_drop(self._h, name.encode()))
         self._spaces.pop(name, None)

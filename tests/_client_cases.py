@@ -138,3 +138,53 @@ def run_reference_flow(engine_factory=None, rtol=1e-5):
         await client.close()
 
     asyncio.run(flow())
+
+
+def run_incremental_upsert(engine_factory=None, storage=None):
+    """points upserted after the first query are appended / overwritten in HBM
+    (brag_dense_append / brag_dense_update) and must answer exactly like a collection uploaded in one go."""
+    from rag_application_b200.client import B200QdrantCore
+    rng = np.random.Generator(np.random.PCG64(99))
+    n, d = 900, 64
+    x = rng.standard_normal((n + 50, d)).astype(np.float32)
+    sp = [(np.sort(rng.choice(500, 6, replace=False)), rng.random(6).astype(np.float32) + 0.1) for _ in range(n + 50)]
+
+    def point(i, vec=None):
+        return M.PointStruct(id=i, vector={"dense": (x[i] if vec is None else vec).tolist(),
+                                           "sparse": M.SparseVector(indices=sp[i][0].tolist(), values=sp[i][1].tolist())},
+                             payload={"i": int(i)})
+
+    def make():
+        kw = {"engine_factory": engine_factory} if engine_factory else {}
+        core = B200QdrantCore(storage=storage, **kw)
+        core.create_collection("c", vectors_config={"dense": M.VectorParams(size=d, distance=M.Distance.COSINE)},
+                               sparse_vectors_config={"sparse": M.SparseVectorParams()})
+        return core
+
+    def ask(core, q):
+        r = core.query_points("c", prefetch=[M.Prefetch(query=q.tolist(), using="dense", limit=40),
+                                             M.Prefetch(query=M.SparseVector(indices=sp[3][0].tolist(), values=sp[3][1].tolist()),
+                                                        using="sparse", limit=40)],
+                              query=M.FusionQuery(fusion=M.Fusion.RRF), limit=20).points
+        return [(p.id, p.score) for p in r]
+
+    q = x[5] + 0.05 * rng.standard_normal(d).astype(np.float32)
+    inc = make()
+    inc.upsert("c", [point(i) for i in range(n)])
+    first = ask(inc, q)                                           # commits n rows
+    calls = []
+    eng = inc.engine
+    for name in ("dense_set", "dense_append", "dense_update"):
+        orig = getattr(eng, name)
+        setattr(eng, name, (lambda o, nm: (lambda *a, **k: (calls.append(nm), o(*a, **k))[1]))(orig, name))
+    changed = -x[7]
+    inc.upsert("c", [point(i) for i in range(n, n + 50)] + [point(7, changed)])
+    second = ask(inc, q)
+    assert "dense_append" in calls and "dense_update" in calls and "dense_set" not in calls
+    x2 = x.copy()
+    x2[7] = changed
+    full = make()
+    full.upsert("c", [point(i, x2[i]) for i in range(n + 50)])
+    assert ask(full, q) == second
+    inc.close()
+    full.close()

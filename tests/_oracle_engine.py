@@ -30,6 +30,13 @@ class OracleEngine:
         self.dense[name] = O.round_storage(_np(rows).astype(np.float32), dtype)
         self.dtype[name] = dtype
 
+    def dense_append(self, name, rows):
+        new = O.round_storage(_np(rows).astype(np.float32), self.dtype[name])
+        self.dense[name] = np.concatenate([self.dense[name], new])
+
+    def dense_update(self, name, row_ids, rows):
+        self.dense[name][np.asarray(row_ids, dtype=np.int64)] = O.round_storage(_np(rows).astype(np.float32), self.dtype[name])
+
     def dense_drop(self, name):
         self.dense.pop(name, None)
 

@@ -4,13 +4,17 @@ import numpy as np
 import pytest
 
 from _oracle_engine import OracleEngine
-from _client_cases import run_reference_flow
+from _client_cases import run_incremental_upsert, run_reference_flow
 from rag_application_b200 import models as M
 from rag_application_b200.client import B200QdrantCore, compile_filter
 
 
 def test_reference_flow_on_oracle_engine():
     run_reference_flow(engine_factory=OracleEngine)
+
+
+def test_incremental_upsert_on_oracle_engine():
+    run_incremental_upsert(engine_factory=OracleEngine)
 
 
 def test_filter_compiler():
