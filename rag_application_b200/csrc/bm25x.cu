@@ -462,18 +462,20 @@ bm25x_scan_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict_
                     *reinterpret_cast<uint32_t*>(pre + la * 2 * WORDS + WPL * lane + w) = (r0 & 0xFFFFu) | (r1 << 16);
                     if (two) *reinterpret_cast<uint32_t*>(pre + lb * 2 * WORDS + WPL * lane + w) = (r0 >> 16) | (r1 & 0xFFFF0000u);
                 }
-                // count += present + high, two maps at a time through a 3:2 compressor on plane 0
+                // count += present_a + high_a + present_b + high_b: two full adders on the ones plane, one on the
+                // twos plane, then the single carry ripples up through half adders
 #pragma unroll
                 for (int w = 0; w < WPL; ++w) {
+                    uint32_t c = cn[0][w];
+                    const uint32_t ta = (c & wa[w]) | (c & ha[w]) | (wa[w] & ha[w]);
+                    c = c ^ wa[w] ^ ha[w];
+                    const uint32_t tb = (c & wb[w]) | (c & hb[w]) | (wb[w] & hb[w]);
+                    cn[0][w] = c ^ wb[w] ^ hb[w];
+                    const uint32_t d = cn[1][w];
+                    uint32_t k = (d & ta) | (d & tb) | (ta & tb);
+                    cn[1][w] = d ^ ta ^ tb;
 #pragma unroll
-                    for (int h = 0; h < 2; ++h) {
-                        const uint32_t x = h ? wb[w] : wa[w], y = h ? hb[w] : ha[w];
-                        const uint32_t c = cn[0][w];
-                        cn[0][w] = c ^ x ^ y;
-                        uint32_t k = (c & x) | (c & y) | (x & y);
-#pragma unroll
-                        for (int p = 1; p < PLANES; ++p) { const uint32_t t_ = cn[p][w] & k; cn[p][w] ^= k; k = t_; }
-                    }
+                    for (int p = 2; p < PLANES; ++p) { const uint32_t t_ = cn[p][w] & k; cn[p][w] ^= k; k = t_; }
                 }
             }
             // count >= m, bit-slice compare from the top plane down; then the payload filter
