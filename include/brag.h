@@ -136,6 +136,11 @@ int brag_force_dense_path(brag_engine* e, int32_t path);
 /* Sparse scan kernel (-1 auto, 0 scatter-accumulate, 1 bitmap filter).  Auto = bitmap filter unless a query of
  * the batch has more than 32 terms or the space holds non-finite weights; both give identical results. */
 int brag_force_sparse_path(brag_engine* e, int32_t path);
+/* Filtered sparse scans: once one filter (mask_id, contents) has served `queries` queries of a sparse space and keeps
+ * at most half of its documents, an index of just the passing documents is built on the device and used for that
+ * filter from then on (results identical).  Only calls with B >= 32 count towards `queries` (single queries are
+ * latency-bound either way).  Default 256; 0 = build on first use; < 0 = never (an index already built is bypassed). */
+int brag_sparse_compact_after(brag_engine* e, int64_t queries);
 
 /* ---- the sparse encoder the reference runs before it calls the vector store
  * (fastembed SparseTextEmbedding("Qdrant/bm25").embed, embedding_handler.py:41,123-138).  Host-only code.

@@ -7,6 +7,7 @@
 #include <algorithm>
 
 #include <cub/device/device_scan.cuh>
+#include <cub/device/device_select.cuh>
 
 #include "common.cuh"
 #include "kernels.h"
@@ -60,6 +61,131 @@ __global__ void remap_keys_kernel(uint64_t* __restrict__ keys, int64_t count, co
     const uint64_t k = keys[i];
     if (k == 0ull) return;
     keys[i] = (k & 0xFFFFFFFF00000000ull) | (uint64_t)(0xFFFFFFFFu - rowmap[key_row(k)]);
+}
+
+// ---- filter-compacted copy of a sparse space ------------------------------------------------------------------
+// The BM25 scans cost time proportional to the postings they walk, filtered out or not.  Under a filter that keeps
+// at most half of the documents, the postings of the passing documents are selected once (stable, so every term's
+// list stays sorted by document), renumbered to compact document ids, and indexed like any other space; scores are
+// sums of the same weights in the same term order, so the results are bit-identical after the id remap.
+
+__device__ __forceinline__ int64_t term_of_posting(const int64_t* __restrict__ term_ptr, int64_t V, int64_t i) {
+    int64_t lo = 0, hi = V;              // last t with term_ptr[t] <= i
+    while (hi - lo > 1) {
+        const int64_t mid = (lo + hi) >> 1;
+        if (__ldg(term_ptr + mid) <= i) lo = mid; else hi = mid;
+    }
+    return lo;
+}
+
+// cnt[t] = postings of term t whose document passes the mask.  A warp walks chunks of KEEP_CHUNK consecutive
+// postings, four coalesced loads per lane in flight; the term is searched once per chunk and followed from there, the
+// count lives in registers and reaches cnt[] once per (chunk, term).  Only a 128-posting block that straddles a term
+// boundary takes the per-posting search.
+constexpr int KEEP_CHUNK = 8192;
+
+__global__ void sparse_keep_count_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict__ post,
+                                         int64_t V, int64_t nnz, const uint32_t* __restrict__ mask,
+                                         unsigned long long* __restrict__ cnt) {
+    const int lane = threadIdx.x & 31;
+    const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    const int64_t nchunks = (nnz + KEEP_CHUNK - 1) / KEEP_CHUNK;
+    for (int64_t c = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; c < nchunks; c += nwarps) {
+        const int64_t i0 = c * KEEP_CHUNK, i1 = min(nnz, i0 + (int64_t)KEEP_CHUNK);
+        int64_t t = term_of_posting(term_ptr, V, i0);
+        int64_t end = __ldg(term_ptr + t + 1);
+        uint32_t local = 0u;
+        for (int64_t base = i0; base < i1; base += 128) {
+            uint32_t doc[4];
+            bool keep[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int64_t i = base + u * 32 + lane;
+                doc[u] = i < i1 ? __ldcs(post + i).x : 0xFFFFFFFFu;
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+                keep[u] = doc[u] != 0xFFFFFFFFu && ((__ldg(mask + (doc[u] >> 5)) >> (doc[u] & 31)) & 1u);
+            if (base + 128 <= end) {
+                local += (uint32_t)keep[0] + (uint32_t)keep[1] + (uint32_t)keep[2] + (uint32_t)keep[3];
+                continue;
+            }
+            // a term ends inside this block: flush the running count, then one search per kept posting
+            uint32_t tot = local;
+#pragma unroll
+            for (int o = 16; o; o >>= 1) tot += __shfl_xor_sync(0xFFFFFFFFu, tot, o);
+            if (lane == 0 && tot) atomicAdd(cnt + t, (unsigned long long)tot);
+            local = 0u;
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+                if (keep[u]) atomicAdd(cnt + term_of_posting(term_ptr, V, base + u * 32 + lane), 1ull);
+            if (base + 128 < i1) {
+                t = term_of_posting(term_ptr, V, base + 128);
+                end = __ldg(term_ptr + t + 1);
+            }
+        }
+        uint32_t tot = local;
+#pragma unroll
+        for (int o = 16; o; o >>= 1) tot += __shfl_xor_sync(0xFFFFFFFFu, tot, o);
+        if (lane == 0 && tot) atomicAdd(cnt + t, (unsigned long long)tot);
+    }
+}
+
+struct KeepPosting {
+    const uint32_t* mask;
+    __device__ __forceinline__ bool operator()(const uint2& p) const { return (mask[p.x >> 5] >> (p.x & 31)) & 1u; }
+};
+
+__global__ void sparse_renumber_kernel(uint2* __restrict__ post, int64_t nnz, const uint32_t* __restrict__ mask,
+                                       const uint32_t* __restrict__ prefix) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nnz) return;
+    const uint32_t doc = post[i].x;
+    const uint32_t w = __ldg(mask + (doc >> 5));
+    post[i].x = __ldg(prefix + (doc >> 5)) + __popc(w & ((1u << (doc & 31)) - 1u));
+}
+
+size_t sparse_compact_tmp_bytes(int64_t V, int64_t nnz) {
+    size_t a = 0, b = 0;
+    cub::DeviceScan::ExclusiveSum(nullptr, a, (const int64_t*)nullptr, (int64_t*)nullptr, (int)(V + 1));
+    KeepPosting keep{nullptr};
+    cub::DeviceSelect::If(nullptr, b, (const uint2*)nullptr, (uint2*)nullptr, (int64_t*)nullptr, (int64_t)nnz, keep);
+    return std::max(a, b) + 256;
+}
+
+// new_term_ptr: [V + 1] (term_ptr of the passing postings)
+cudaError_t sparse_compact_count(const int64_t* term_ptr, const uint2* post, int64_t V, int64_t nnz,
+                                 const uint32_t* mask, int64_t* new_term_ptr, void* tmp, size_t tmp_bytes,
+                                 cudaStream_t st) {
+    cudaError_t e = cudaMemsetAsync(new_term_ptr, 0, (size_t)(V + 1) * sizeof(int64_t), st);
+    if (e != cudaSuccess) return e;
+    if (nnz) {
+        const int64_t blocks = std::min<int64_t>((nnz + KEEP_CHUNK * 8 - 1) / (KEEP_CHUNK * 8), 148 * 8);
+        sparse_keep_count_kernel<<<(unsigned)blocks, 256, 0, st>>>(term_ptr, post, V, nnz, mask,
+                                                                  reinterpret_cast<unsigned long long*>(new_term_ptr));
+        e = cudaGetLastError();
+        if (e != cudaSuccess) return e;
+    }
+    return cub::DeviceScan::ExclusiveSum(tmp, tmp_bytes, new_term_ptr, new_term_ptr, (int)(V + 1), st);
+}
+
+// out: [nnz_c] passing postings with compact document ids; n_selected: device scratch (one int64)
+cudaError_t sparse_compact_select(const uint2* post, int64_t nnz, const uint32_t* mask, const uint32_t* prefix,
+                                  uint2* out, int64_t nnz_c, int64_t* n_selected, void* tmp, size_t tmp_bytes,
+                                  cudaStream_t st) {
+    if (nnz == 0 || nnz_c == 0) return cudaSuccess;
+    KeepPosting keep{mask};
+    cudaError_t e = cub::DeviceSelect::If(tmp, tmp_bytes, post, out, n_selected, (int64_t)nnz, keep, st);
+    if (e != cudaSuccess) return e;
+    sparse_renumber_kernel<<<(unsigned)((nnz_c + 255) / 256), 256, 0, st>>>(out, nnz_c, mask, prefix);
+    return cudaGetLastError();
+}
+
+// rowmap only (the dense gather builds its own inside compact_rows)
+cudaError_t compact_rowmap(const uint32_t* mask, int64_t n, const uint32_t* prefix, uint32_t* rowmap, cudaStream_t st) {
+    const int64_t nwords = (n + 31) / 32;
+    mask_rowmap_kernel<<<(unsigned)((nwords + 255) / 256), 256, 0, st>>>(mask, n, nwords, prefix, rowmap);
+    return cudaGetLastError();
 }
 
 size_t compact_tmp_bytes(int64_t nwords) {

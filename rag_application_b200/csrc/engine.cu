@@ -20,12 +20,17 @@ struct BragError : std::runtime_error {
     using std::runtime_error::runtime_error;
 };
 
+struct CudaOom : BragError {
+    using BragError::BragError;
+};
+
 #define CK(expr)                                                                                   \
     do {                                                                                           \
         cudaError_t _e = (expr);                                                                   \
         if (_e != cudaSuccess) {                                                                   \
             char _b[512];                                                                          \
             snprintf(_b, sizeof _b, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__); \
+            if (_e == cudaErrorMemoryAllocation) { cudaGetLastError(); throw CudaOom(_b); }         \
             throw BragError(_b);                                                                   \
         }                                                                                          \
     } while (0)
@@ -90,6 +95,14 @@ struct SparseSpace {
     bool bitmap_ok = false;
     int64_t V = 0, n_docs = 0, nnz = 0;
     std::vector<int64_t> term_ptr_host;
+    // filter-compacted copy (compact.cu): an index of the documents passing filter (cp_mask_id, cp_version), built
+    // once that filter has served cp_queries queries of this space
+    SparseSpace* cp = nullptr;
+    int cp_mask_id = 0;
+    uint64_t cp_version = 0;
+    int64_t cp_queries = 0;
+    int cp_state = 0;              // 0 counting queries, 1 built and in use, 2 not worth it / did not fit
+    uint32_t* cp_rowmap = nullptr;
 };
 
 struct MaskBuf {
@@ -111,6 +124,7 @@ struct brag_engine {
     int64_t id_offset = 0;
     int force_path = -1;
     bool no_compact = false;       // parity tests: scan the full space under a filter
+    int64_t sparse_compact_after = 256;   // queries under one filter before its sparse copy is built; < 0 never
     uint64_t mask_epoch = 0;
     int force_sparse_path = -1;    // -1 auto, 0 scatter-accumulate (bm25.cu), 1 bitmap filter (bm25x.cu)
     std::map<std::string, DenseSpace> dense;
@@ -190,6 +204,8 @@ void free_dense(DenseSpace& s) {
     s.cp_rowmap = nullptr;
 }
 void free_sparse(SparseSpace& s) {
+    if (s.cp) { free_sparse(*s.cp); delete s.cp; }
+    if (s.cp_rowmap) cudaFree(s.cp_rowmap);
     if (s.term_ptr) cudaFree(s.term_ptr);
     if (s.post) cudaFree(s.post);
     if (s.sub_off) cudaFree(s.sub_off);
@@ -245,6 +261,15 @@ void build_bitmap_index(SparseSpace& s) {
     s.bitmap_ok = !nonfinite;
 }
 
+// everything the scans need beside term_ptr / post (both already on the device)
+void build_sparse_index(SparseSpace& s) {
+    const int64_t ns1 = (s.n_docs + brag::BM25_SUB - 1) / brag::BM25_SUB + 1;
+    CK(cudaMalloc(&s.sub_off, (size_t)s.V * ns1 * sizeof(uint32_t)));
+    CK(brag::bm25_build_suboffsets(s.term_ptr, s.post, s.V, s.n_docs, s.sub_off, 0));
+    build_bitmap_index(s);
+    CK(cudaDeviceSynchronize());
+}
+
 int pick_path(brag_engine* e, const DenseSpace& s, int B) {
     if (!s.umma_ok) return 0;
     if (e->force_path == 0) return 0;
@@ -297,6 +322,68 @@ bool ensure_compact(brag_engine* e, DenseSpace& s, int mask_id, const uint32_t* 
     e->kernel_launches += 2;
     s.cp_n = nc;
     s.cp_use = true;
+    return true;
+}
+
+// Sparse counterpart: an index over the documents passing filter `mask_id`, built once the filter has served
+// `sparse_compact_after` queries of this space (the build reads every posting once, about what a few hundred queries
+// cost) and kept until the filter or the space changes.
+bool ensure_sparse_compact(brag_engine* e, SparseSpace& s, int mask_id, const uint32_t* mask, int B, cudaStream_t st) {
+    const uint64_t version = e->masks[mask_id].version;
+    if (s.cp_mask_id != mask_id || s.cp_version != version) {
+        if (s.cp) { CK(cudaDeviceSynchronize()); free_sparse(*s.cp); delete s.cp; s.cp = nullptr; }
+        s.cp_mask_id = mask_id;
+        s.cp_version = version;
+        s.cp_queries = 0;
+        s.cp_state = 0;
+    }
+    if (e->sparse_compact_after < 0) return false;
+    if (s.cp_state == 1) return true;
+    if (s.cp_state == 2) return false;
+    // single queries are latency-bound, not posting-bound (C5 shard: 0.13 ms either way): only batches count
+    if (s.cp_queries < e->sparse_compact_after) { if (B >= 32) s.cp_queries += B; return false; }
+    s.cp_state = 2;
+    const int64_t nwords = (s.n_docs + 31) / 32;
+    uint32_t* prefix = e->cp_prefix.as<uint32_t>((size_t)nwords + 1);
+    const size_t tmp_bytes = std::max(brag::compact_tmp_bytes(nwords), brag::sparse_compact_tmp_bytes(s.V, s.nnz));
+    void* tmp = e->cp_tmp.ensure(tmp_bytes + 64);
+    CK(brag::compact_prefix(mask, s.n_docs, prefix, tmp, tmp_bytes, st));
+    uint32_t nc = 0;
+    CK(cudaMemcpyAsync(&nc, prefix + nwords, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    e->kernel_launches += 2;
+    if ((int64_t)nc * 2 > s.n_docs || nc < 1024) return false;
+    SparseSpace* c = new SparseSpace();
+    try {
+        c->V = s.V;
+        c->n_docs = nc;
+        CK(cudaMalloc(&c->term_ptr, (size_t)(s.V + 1) * sizeof(int64_t)));
+        CK(brag::sparse_compact_count(s.term_ptr, s.post, s.V, s.nnz, mask, c->term_ptr, tmp, tmp_bytes, st));
+        c->term_ptr_host.resize((size_t)s.V + 1);
+        CK(cudaMemcpyAsync(c->term_ptr_host.data(), c->term_ptr, (size_t)(s.V + 1) * sizeof(int64_t),
+                           cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+        c->nnz = c->term_ptr_host[(size_t)s.V];
+        CK(cudaMalloc(&c->post, std::max<size_t>((size_t)c->nnz, 1) * sizeof(uint2)));
+        int64_t* n_sel = reinterpret_cast<int64_t*>(reinterpret_cast<uint8_t*>(tmp) + ((tmp_bytes + 7) / 8) * 8);
+        CK(brag::sparse_compact_select(s.post, s.nnz, mask, prefix, c->post, c->nnz, n_sel, tmp, tmp_bytes, st));
+        if (s.cp_rowmap) { CK(cudaFree(s.cp_rowmap)); s.cp_rowmap = nullptr; }
+        CK(cudaMalloc(&s.cp_rowmap, (size_t)nc * sizeof(uint32_t)));
+        CK(brag::compact_rowmap(mask, s.n_docs, prefix, s.cp_rowmap, st));
+        CK(cudaStreamSynchronize(st));
+        build_sparse_index(*c);
+        e->kernel_launches += 8;
+    } catch (const CudaOom&) {
+        free_sparse(*c);
+        delete c;
+        return false;
+    } catch (...) {
+        free_sparse(*c);
+        delete c;
+        throw;
+    }
+    s.cp = c;
+    s.cp_state = 1;
     return true;
 }
 
@@ -389,10 +476,14 @@ int max_terms_host(const int32_t* q_ptr, int B) {
 }
 
 // max_terms: longest query of the batch, or -1 when only the device copy of q_ptr is at hand
-void sparse_topk_dev(brag_engine* e, SparseSpace& s, const int32_t* q_ptr, const int32_t* q_terms,
-                     const double* q_vals, int B, int k, const uint32_t* mask, float* out_scores,
+void sparse_topk_dev(brag_engine* e, SparseSpace& full, const int32_t* q_ptr, const int32_t* q_terms,
+                     const double* q_vals, int B, int k, int mask_id, const uint32_t* mask, float* out_scores,
                      int64_t* out_ids, int32_t* out_counts, int max_terms, cudaStream_t st) {
     REQUIRE(B >= 1 && k >= 1 && k <= 512, "sparse_topk: need B >= 1 and 1 <= k <= 512");
+    // documents actually scanned: the whole space, or the index of the documents passing the filter
+    const bool compact = mask != nullptr && !e->no_compact && ensure_sparse_compact(e, full, mask_id, mask, B, st);
+    SparseSpace& s = compact ? *full.cp : full;
+    if (compact) mask = nullptr;
     // bitmap-filter scan unless the space has non-finite weights or a query is longer than 32 terms
     bool bitmap = s.bitmap_ok && e->force_sparse_path != 0;
     // (checked first with the 32-term variant, which has the fewest lists: batch-1 calls on device pointers then
@@ -441,6 +532,10 @@ void sparse_topk_dev(brag_engine* e, SparseSpace& s, const int32_t* q_ptr, const
         const uint32_t* fine = reinterpret_cast<const uint32_t*>(sp + 256 + plan.gthr_bytes + plan.coarse_bytes);
         CK(brag::publish_bounds(coarse, fine, gthr, B, k, st));
         CK(brag::merge_key_lists(part, P, B, k, ta, tb, merged, k, st, &launches, gthr));
+        if (compact) {
+            CK(brag::remap_keys(merged, (int64_t)B * k, full.cp_rowmap, st));
+            launches += 1;
+        }
         CK(brag::finalize_keys(merged, B, k, k, false, e->id_offset, out_scores, out_ids, out_counts, st));
         e->kernel_launches += launches + 2;
     }
@@ -654,11 +749,7 @@ int brag_sparse_set_csr(brag_engine* e, const char* name, const int64_t* term_pt
                     CK(ce);
                 }
             }
-            const int64_t ns1 = (n_docs + brag::BM25_SUB - 1) / brag::BM25_SUB + 1;
-            CK(cudaMalloc(&s.sub_off, (size_t)n_terms * ns1 * sizeof(uint32_t)));
-            CK(brag::bm25_build_suboffsets(s.term_ptr, s.post, n_terms, n_docs, s.sub_off, 0));
-            build_bitmap_index(s);
-            CK(cudaDeviceSynchronize());
+            build_sparse_index(s);
         } catch (...) {
             free_sparse(s);
             throw;
@@ -764,7 +855,7 @@ int brag_sparse_topk(brag_engine* e, const char* name, const int32_t* q_ptr, con
         SparseSpace& s = sparse_space(e, name);
         const uint32_t* mask = mask_ptr(e, mask_id, s.n_docs);
         if (on_device) {
-            sparse_topk_dev(e, s, q_ptr, q_terms, q_vals, B, k, mask, out_scores, out_ids, out_counts, -1, st);
+            sparse_topk_dev(e, s, q_ptr, q_terms, q_vals, B, k, mask_id, mask, out_scores, out_ids, out_counts, -1, st);
         } else {
             const size_t nt = (size_t)q_ptr[B];
             for (int b = 0; b < B; ++b) {
@@ -778,7 +869,7 @@ int brag_sparse_topk(brag_engine* e, const char* name, const int32_t* q_ptr, con
             float* ds = e->h_out[0].as<float>((size_t)B * k);
             int64_t* di = e->h_out[1].as<int64_t>((size_t)B * k);
             int32_t* dc = e->h_out[2].as<int32_t>(B);
-            sparse_topk_dev(e, s, dp, dt, dv, B, k, mask, ds, di, dc, max_terms_host(q_ptr, B), st);
+            sparse_topk_dev(e, s, dp, dt, dv, B, k, mask_id, mask, ds, di, dc, max_terms_host(q_ptr, B), st);
             to_host(out_scores, ds, (size_t)B * k, st);
             to_host(out_ids, di, (size_t)B * k, st);
             to_host(out_counts, dc, (size_t)B, st);
@@ -877,7 +968,7 @@ int brag_hybrid_topk(brag_engine* e, const char* dense_name, const char* sparse_
             oc = e->h_out[2].as<int32_t>(B);
         }
         dense_topk_dev(e, ds, dq, B, k, mask_id, mask, scs, ids, cnts, st);
-        sparse_topk_dev(e, ss, dp, dt, dv, B, k, mask, scs + (size_t)B * k, ids + (size_t)B * k, cnts + B,
+        sparse_topk_dev(e, ss, dp, dt, dv, B, k, mask_id, mask, scs + (size_t)B * k, ids + (size_t)B * k, cnts + B,
                         on_device ? -1 : max_terms_host(q_ptr, B), st);
         {
             StageTimer t(e, 4, st);
@@ -946,6 +1037,13 @@ int brag_force_sparse_path(brag_engine* e, int32_t path) {
     return guarded([&] {
         REQUIRE(e && path >= -1 && path <= 1, "brag_force_sparse_path: path must be -1, 0 or 1");
         e->force_sparse_path = path;
+    });
+}
+
+int brag_sparse_compact_after(brag_engine* e, int64_t queries) {
+    return guarded([&] {
+        REQUIRE(e, "brag_sparse_compact_after: NULL engine");
+        e->sparse_compact_after = queries;
     });
 }
 

@@ -66,6 +66,15 @@ cudaError_t compact_rows(const void* X, int row_bytes, const uint32_t* mask, int
                          int64_t nc, uint32_t* rowmap, void* out, cudaStream_t st);
 // keys of compact rows -> keys of original rows (same order: rowmap is increasing)
 cudaError_t remap_keys(uint64_t* keys, int64_t count, const uint32_t* rowmap, cudaStream_t st);
+cudaError_t compact_rowmap(const uint32_t* mask, int64_t n, const uint32_t* prefix, uint32_t* rowmap, cudaStream_t st);
+// filter-compacted copy of a sparse space: postings of the passing documents, renumbered (see compact.cu)
+size_t sparse_compact_tmp_bytes(int64_t V, int64_t nnz);
+cudaError_t sparse_compact_count(const int64_t* term_ptr, const uint2* post, int64_t V, int64_t nnz,
+                                 const uint32_t* mask, int64_t* new_term_ptr, void* tmp, size_t tmp_bytes,
+                                 cudaStream_t st);
+cudaError_t sparse_compact_select(const uint2* post, int64_t nnz, const uint32_t* mask, const uint32_t* prefix,
+                                  uint2* out, int64_t nnz_c, int64_t* n_selected, void* tmp, size_t tmp_bytes,
+                                  cudaStream_t st);
 
 // ---- bm25.cu
 constexpr int BM25_SUB = 2048;  // documents per warp sub-tile

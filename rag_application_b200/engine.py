@@ -259,5 +259,9 @@ class Engine:
     def force_sparse_path(self, path: Optional[str]):
         _native.check(self._lib.brag_force_sparse_path(self._h, {None: -1, "scatter": 0, "bitmap": 1}[path]))
 
+    def sparse_compact_after(self, queries: int):
+        """Queries one filter serves before the index of its passing documents is built (0: first use, < 0: never)."""
+        _native.check(self._lib.brag_sparse_compact_after(self._h, int(queries)))
+
     def force_dense_path(self, path: Optional[str]):
         _native.check(self._lib.brag_force_dense_path(self._h, {None: -1, "gemv": 0, "tcgen05": 1, "tcgen05_full": 2}[path]))

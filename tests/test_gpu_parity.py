@@ -346,6 +346,49 @@ def test_sparse_bitmap_warm_bound_large(engine, masked):
             assert np.array_equal(s[b][:len(ei)].view(np.uint32), es.view(np.uint32))
 
 
+@pytest.mark.parametrize("B", [1, 40])
+def test_sparse_filter_compacted_index(engine, B):
+    """A filter that keeps <= half of the documents gets, once it has served enough queries, an index of just the
+    passing documents (compact.cu): ids, scores and counts equal the masked scan of the full space and the oracle,
+    through both scan kernels and through the fused hybrid call; a new filter under the same mask_id rebuilds it."""
+    n_docs, k, d = 120000, 40, 64
+    ptr, doc, w, _ = synth.zipf_corpus(n_docs, 3000, 60, seed=51)
+    csr = _oracle_csr(ptr, doc, w, n_docs)
+    engine.sparse_set_csr("s", ptr, doc, w, n_docs)
+    x = synth.dense_corpus(n_docs, d, seed=53)
+    q = synth.dense_queries(x, B, seed=54)
+    engine.dense_set("x", x, "bf16")
+    q_ptr, q_terms, q_vals = synth.sparse_queries(ptr, doc, n_docs, B, 8, "zipf", seed=52, skip_top=8)
+    for seed, sel in ((61, 0.10), (62, 0.35)):
+        mask = synth.random_mask(n_docs, sel, seed=seed)
+        engine.mask_set(7, mask)
+        got = {}
+        try:
+            engine.sparse_compact_after(-1)
+            full = engine.sparse_topk("s", q_ptr, q_terms, q_vals, k, mask_id=7)
+            hyb_full = engine.hybrid_topk("x", "s", q, q_ptr, q_terms, q_vals, k, mask_id=7)
+            engine.sparse_compact_after(0)
+            for path in (None, "scatter", "bitmap"):
+                engine.force_sparse_path(path)
+                got[path] = engine.sparse_topk("s", q_ptr, q_terms, q_vals, k, mask_id=7)
+            engine.force_sparse_path(None)
+            hyb = engine.hybrid_topk("x", "s", q, q_ptr, q_terms, q_vals, k, mask_id=7)
+        finally:
+            engine.force_sparse_path(None)
+            engine.sparse_compact_after(256)
+        s0, i0, c0 = full
+        for path, (s, i, c) in got.items():
+            assert np.array_equal(i, i0) and np.array_equal(c, c0), path
+            assert np.array_equal(s.view(np.uint32), s0.view(np.uint32)), path
+        for a, b in zip(hyb, hyb_full):
+            assert np.array_equal(np.asarray(a), np.asarray(b), equal_nan=np.asarray(a).dtype.kind == "f")
+        assert mask[i0[np.arange(k)[None, :] < c0[:, None]]].all()
+        for b in range(0, B, max(1, B // 8)):
+            es, ei = O.sparse_topk(csr, q_terms[q_ptr[b]:q_ptr[b + 1]], q_vals[q_ptr[b]:q_ptr[b + 1]], k, mask=mask)
+            assert int(c0[b]) == len(ei) and np.array_equal(i0[b][:len(ei)], ei), f"query {b}"
+            assert np.array_equal(s0[b][:len(ei)].view(np.uint32), es.view(np.uint32))
+
+
 def test_sparse_nonfinite_weights_use_the_scatter_scan(engine):
     """A NaN/Inf weight makes per-term bounds meaningless: the space falls back to the exhaustive kernel."""
     ptr, doc, w, _ = synth.zipf_corpus(2000, 300, 30, seed=3)

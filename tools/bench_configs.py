@@ -116,10 +116,17 @@ if "--c5" in sys.argv:
     torch.cuda.synchronize()
     rec = {"rows_kept": int(m5.sum().item()), "first_call_with_copy_build_ms": a.elapsed_time(b)}
     qp_d, qt_d, qv_d = qp.to(dev), qt.to(dev), qv.to(dev)
+    eng.sparse_compact_after(0)
+    a.record()
+    eng.sparse_topk("c5s", qp_d[:2].contiguous(), qt_d[:8].contiguous(), qv_d[:8].contiguous(), k, mask_id=2)
+    b.record()
+    torch.cuda.synchronize()
+    rec["sparse_first_call_with_index_build_ms"] = a.elapsed_time(b)
     for B in (1, 4096):
         qb = q5[:B].contiguous()
         qpb, qtb, qvb = qp_d[:B + 1].contiguous(), qt_d[:8 * B].contiguous(), qv_d[:8 * B].contiguous()
-        for mid, label in ((2, "filtered"), (0, "unfiltered")):
+        for mid, label in ((2, "filtered"), (2, "filtered_sparse_full_index"), (0, "unfiltered")):
+            eng.sparse_compact_after(-1 if label == "filtered_sparse_full_index" else 0)
             p50, best = timeit(lambda: eng.hybrid_topk("c5", "c5s", qb, qpb, qtb, qvb, k, mask_id=mid), iters=10)
             fn = lambda: eng.hybrid_topk("c5", "c5s", qb, qpb, qtb, qvb, k, mask_id=mid)
             fn(); eng.profile_reset()
@@ -134,6 +141,9 @@ if "--c5" in sys.argv:
     eng.dense_drop("c5")
     eng.sparse_drop("c5s")
     torch.cuda.empty_cache()
+    if "--c5-only" in sys.argv:
+        print(json.dumps(out, indent=1))
+        sys.exit(0)
 
 # ---- C3: BM25 top-100 over 1M docs, 50k-term Zipf vocab, 8-term queries, batch 1024
 nd, V = 1 << 20, 50000
