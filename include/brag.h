@@ -64,6 +64,16 @@ int brag_dense_drop(brag_engine* e, const char* name);
 int brag_sparse_set_csr(brag_engine* e, const char* name, const int64_t* term_ptr,
                         const uint32_t* doc_ids, const float* weights, int64_t n_terms,
                         int64_t n_docs, int32_t on_device);
+/* Append documents to a sparse space on the device (replaces the re-upload the reference's
+ * client.upsert(points) of new points would otherwise cost: qdrant_handler.py:190,259).  The delta is a term-major CSR
+ * over the GROWN vocabulary of n_terms_new rows: delta_term_ptr[n_terms_new + 1], doc_ids / weights per posting, every
+ * document id in [current n_docs, n_docs_new) and strictly ascending within a term.  row_map[t] is the new row of the
+ * space's current row t (strictly increasing), so a vocabulary kept in ascending external-index order stays in that
+ * order and scores keep the summation order of a fresh upload.  Old posting lists are moved inside HBM, the delta
+ * is spliced in after them and the scan indexes are rebuilt.  Host pointers only (the delta is small).  On failure
+ * after the old index was released the space is dropped and must be uploaded again. */
+int brag_sparse_append(brag_engine* e, const char* name, const int64_t* delta_term_ptr, const uint32_t* doc_ids,
+                       const float* weights, const int32_t* row_map, int64_t n_terms_new, int64_t n_docs_new);
 int brag_sparse_drop(brag_engine* e, const char* name);
 
 /* Payload-filter bitmask (bit r set = row r passes).  Replaces query_filter=Filter(...)

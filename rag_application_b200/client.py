@@ -159,6 +159,9 @@ class _Collection:
         # incremental upload: rows already in HBM per dense space, and which of them were overwritten
         self.dense_in_hbm: Dict[str, int] = {}
         self.dense_dirty: Dict[str, set] = {v: set() for v in self.dense_cfg}
+        # sparse spaces: rows in HBM as of the last commit; True once a row below that count changed its vector
+        self.sparse_in_hbm: Dict[str, int] = {}
+        self.sparse_dirty: Dict[str, bool] = {v: False for v in self.sparse_cfg}
         # filled by commit()
         self.term_ids: Dict[str, np.ndarray] = {}     # sparse space -> sorted external indices (row = position)
         self.df: Dict[str, np.ndarray] = {}
@@ -215,12 +218,31 @@ class _Collection:
                 if row < self.dense_in_hbm.get(vname, 0):
                     self.dense_dirty[vname].add(row)
             for vname, sv in sparse.items():
+                old = self.sparse_rows[vname][row]
+                if row < self.sparse_in_hbm.get(vname, 0) and not (
+                        old is not None and np.array_equal(old[0], sv[0]) and np.array_equal(old[1], sv[1])):
+                    self.sparse_dirty[vname] = True
                 self.sparse_rows[vname][row] = sv
         self.version += 1
 
     # -------------------------------------------------------------- upload to HBM
     def space(self, vname: str) -> str:
         return f"{self.name}\x1f{vname}"
+
+    @staticmethod
+    def _coo(rows, which):
+        idx = np.concatenate([rows[i][0] for i in which])
+        val = np.concatenate([rows[i][1] for i in which])
+        doc = np.concatenate([np.full(len(rows[i][0]), i, dtype=np.int64) for i in which])
+        return idx, val, doc
+
+    @staticmethod
+    def _term_major(trow, doc, val, n_terms):
+        o = np.lexsort((doc, trow))
+        trow, doc, val = trow[o], doc[o], val[o]
+        ptr = np.zeros(n_terms + 1, dtype=np.int64)
+        np.add.at(ptr, trow + 1, 1)
+        return np.cumsum(ptr), doc, val
 
     def commit(self, engine):
         if self.committed == self.version:
@@ -262,20 +284,34 @@ class _Collection:
             rows = self.sparse_rows[vname]
             have = [i for i, r in enumerate(rows) if r is not None]
             self.n_sparse[vname] = len(have)
+            n_old = self.sparse_in_hbm.get(vname, 0)
+            dirty, self.sparse_dirty[vname] = self.sparse_dirty[vname], False
+            self.sparse_in_hbm[vname] = n if have else 0
             if not have:
                 engine.sparse_drop(self.space(vname))
                 self.term_ids[vname] = np.zeros(0, np.int64)
                 self.df[vname] = np.zeros(0, np.int64)
                 continue
-            idx = np.concatenate([rows[i][0] for i in have])
-            val = np.concatenate([rows[i][1] for i in have])
-            doc = np.concatenate([np.full(len(rows[i][0]), i, dtype=np.int64) for i in have])
+            if 0 < n_old <= n and not dirty and len(self.term_ids.get(vname, ())) > 0:
+                # only new rows since the last commit: splice their postings into the index in HBM
+                # (brag_sparse_append) instead of rebuilding and re-uploading the whole CSR
+                new = [i for i in have if i >= n_old]
+                if not new:
+                    continue
+                idx, val, doc = self._coo(rows, new)
+                old_terms = self.term_ids[vname]
+                terms = np.union1d(old_terms, idx)                 # ascending external index == ascending term row
+                row_map = np.searchsorted(terms, old_terms)
+                ptr, doc, val = self._term_major(np.searchsorted(terms, idx), doc, val, len(terms))
+                engine.sparse_append(self.space(vname), ptr, doc.astype(np.uint32), val.astype(np.float32),
+                                     row_map.astype(np.int32), n)
+                df = np.diff(ptr)
+                df[row_map] += self.df[vname]
+                self.term_ids[vname], self.df[vname] = terms, df
+                continue
+            idx, val, doc = self._coo(rows, have)
             terms, trow = np.unique(idx, return_inverse=True)     # ascending external index == ascending term row
-            o = np.lexsort((doc, trow))
-            trow, doc, val = trow[o], doc[o], val[o]
-            ptr = np.zeros(len(terms) + 1, dtype=np.int64)
-            np.add.at(ptr, trow + 1, 1)
-            ptr = np.cumsum(ptr)
+            ptr, doc, val = self._term_major(trow, doc, val, len(terms))
             engine.sparse_set_csr(self.space(vname), ptr, doc.astype(np.uint32), val.astype(np.float32), n)
             self.term_ids[vname] = terms
             self.df[vname] = np.diff(ptr)

@@ -131,6 +131,72 @@ __global__ void sparse_keep_count_kernel(const int64_t* __restrict__ term_ptr, c
     }
 }
 
+// ---- append to a sparse space (brag_sparse_append): every old posting list moves to its place in the grown index --
+// out[dst_start[t] + (i - term_ptr[t])] = post[i] for posting i of old term t; same chunked walk as the count above.
+__global__ void sparse_move_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict__ post, int64_t V,
+                                   int64_t nnz, const int64_t* __restrict__ dst_start, uint2* __restrict__ out) {
+    const int lane = threadIdx.x & 31;
+    const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    const int64_t nchunks = (nnz + KEEP_CHUNK - 1) / KEEP_CHUNK;
+    for (int64_t c = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; c < nchunks; c += nwarps) {
+        const int64_t i0 = c * KEEP_CHUNK, i1 = min(nnz, i0 + (int64_t)KEEP_CHUNK);
+        int64_t t = term_of_posting(term_ptr, V, i0);
+        int64_t end = __ldg(term_ptr + t + 1);
+        int64_t shift = __ldg(dst_start + t) - __ldg(term_ptr + t);
+        for (int64_t base = i0; base < i1; base += 128) {
+            uint2 p[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int64_t i = base + u * 32 + lane;
+                p[u] = i < i1 ? __ldcs(post + i) : make_uint2(0u, 0u);
+            }
+            if (base + 128 <= end) {
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const int64_t i = base + u * 32 + lane;
+                    if (i < i1) out[i + shift] = p[u];
+                }
+                continue;
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int64_t i = base + u * 32 + lane;
+                if (i < i1) {
+                    const int64_t tt = term_of_posting(term_ptr, V, i);
+                    out[i + __ldg(dst_start + tt) - __ldg(term_ptr + tt)] = p[u];
+                }
+            }
+            if (base + 128 < i1) {
+                t = term_of_posting(term_ptr, V, base + 128);
+                end = __ldg(term_ptr + t + 1);
+                shift = __ldg(dst_start + t) - __ldg(term_ptr + t);
+            }
+        }
+    }
+}
+
+__global__ void sparse_place_kernel(const uint2* __restrict__ dpost, const int64_t* __restrict__ dst, int64_t n,
+                                    uint2* __restrict__ out) {
+    const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j < n) out[dst[j]] = dpost[j];
+}
+
+cudaError_t sparse_append_move(const int64_t* term_ptr, const uint2* post, int64_t V, int64_t nnz,
+                               const int64_t* dst_start, const uint2* dpost, const int64_t* ddst, int64_t dnnz,
+                               uint2* out, cudaStream_t st) {
+    if (nnz) {
+        const int64_t blocks = std::min<int64_t>((nnz + KEEP_CHUNK * 8 - 1) / (KEEP_CHUNK * 8), 148 * 8);
+        sparse_move_kernel<<<(unsigned)blocks, 256, 0, st>>>(term_ptr, post, V, nnz, dst_start, out);
+        cudaError_t e = cudaGetLastError();
+        if (e != cudaSuccess) return e;
+    }
+    if (dnnz) {
+        sparse_place_kernel<<<(unsigned)((dnnz + 255) / 256), 256, 0, st>>>(dpost, ddst, dnnz, out);
+        return cudaGetLastError();
+    }
+    return cudaSuccess;
+}
+
 struct KeepPosting {
     const uint32_t* mask;
     __device__ __forceinline__ bool operator()(const uint2& p) const { return (mask[p.x >> 5] >> (p.x & 31)) & 1u; }

@@ -758,6 +758,88 @@ int brag_sparse_set_csr(brag_engine* e, const char* name, const int64_t* term_pt
     });
 }
 
+int brag_sparse_append(brag_engine* e, const char* name, const int64_t* delta_term_ptr, const uint32_t* doc_ids,
+                       const float* weights, const int32_t* row_map, int64_t n_terms_new, int64_t n_docs_new) {
+    return guarded([&] {
+        REQUIRE(e && name && delta_term_ptr && row_map, "brag_sparse_append: NULL argument");
+        use_device(e);
+        SparseSpace& s = sparse_space(e, name);
+        REQUIRE(n_terms_new >= s.V && n_docs_new >= s.n_docs && n_docs_new < (int64_t)0xFFFFFFFFll,
+                "brag_sparse_append: the space can only grow");
+        REQUIRE(delta_term_ptr[0] == 0, "brag_sparse_append: delta_term_ptr[0] must be 0");
+        const int64_t dnnz = delta_term_ptr[n_terms_new];
+        REQUIRE(dnnz == 0 || (doc_ids && weights), "brag_sparse_append: NULL postings");
+        for (int64_t t = 0; t < n_terms_new; ++t) {
+            REQUIRE(delta_term_ptr[t + 1] >= delta_term_ptr[t], "brag_sparse_append: delta_term_ptr must be non-decreasing");
+            for (int64_t j = delta_term_ptr[t]; j < delta_term_ptr[t + 1]; ++j) {
+                REQUIRE((int64_t)doc_ids[j] >= s.n_docs && (int64_t)doc_ids[j] < n_docs_new,
+                        "brag_sparse_append: delta documents must be new rows (>= the current document count)");
+                REQUIRE(j == delta_term_ptr[t] || doc_ids[j] > doc_ids[j - 1],
+                        "brag_sparse_append: documents must be strictly ascending within a term");
+            }
+        }
+        for (int64_t t = 0; t < s.V; ++t)
+            REQUIRE(row_map[t] >= 0 && row_map[t] < n_terms_new && (t == 0 || row_map[t] > row_map[t - 1]),
+                    "brag_sparse_append: row_map must be strictly increasing inside the new vocabulary");
+        // new term_ptr; where each old list and each delta posting lands
+        std::vector<int64_t> new_ptr((size_t)n_terms_new + 1, 0), dst_start((size_t)std::max<int64_t>(s.V, 1), 0);
+        for (int64_t t = 0; t < n_terms_new; ++t) new_ptr[(size_t)t + 1] = delta_term_ptr[t + 1] - delta_term_ptr[t];
+        for (int64_t t = 0; t < s.V; ++t) new_ptr[(size_t)row_map[t] + 1] += s.term_ptr_host[t + 1] - s.term_ptr_host[t];
+        for (int64_t t = 0; t < n_terms_new; ++t) new_ptr[(size_t)t + 1] += new_ptr[(size_t)t];
+        for (int64_t t = 0; t < s.V; ++t) dst_start[(size_t)t] = new_ptr[(size_t)row_map[t]];
+        std::vector<int64_t> ddst((size_t)std::max<int64_t>(dnnz, 1));
+        std::vector<uint2> dpost((size_t)std::max<int64_t>(dnnz, 1));
+        for (int64_t t = 0; t < n_terms_new; ++t) {
+            const int64_t dcount = delta_term_ptr[t + 1] - delta_term_ptr[t];
+            const int64_t at = new_ptr[(size_t)t + 1] - dcount;       // after the old postings of the term
+            for (int64_t j = 0; j < dcount; ++j) {
+                const int64_t src = delta_term_ptr[t] + j;
+                ddst[(size_t)src] = at + j;
+                uint32_t wb;
+                std::memcpy(&wb, &weights[src], 4);
+                dpost[(size_t)src] = make_uint2(doc_ids[src], wb);
+            }
+        }
+        const int64_t nnz_new = new_ptr[(size_t)n_terms_new];
+        CK(cudaDeviceSynchronize());
+        SparseSpace g;
+        g.V = n_terms_new; g.n_docs = n_docs_new; g.nnz = nnz_new;
+        int64_t *d_dst_start = nullptr, *d_ddst = nullptr;
+        uint2* d_dpost = nullptr;
+        bool old_freed = false;
+        try {
+            CK(cudaMalloc(&g.term_ptr, (size_t)(n_terms_new + 1) * sizeof(int64_t)));
+            CK(cudaMemcpy(g.term_ptr, new_ptr.data(), (size_t)(n_terms_new + 1) * sizeof(int64_t), cudaMemcpyHostToDevice));
+            CK(cudaMalloc(&g.post, std::max<size_t>((size_t)nnz_new, 1) * sizeof(uint2)));
+            CK(cudaMalloc(&d_dst_start, dst_start.size() * sizeof(int64_t)));
+            CK(cudaMemcpy(d_dst_start, dst_start.data(), dst_start.size() * sizeof(int64_t), cudaMemcpyHostToDevice));
+            CK(cudaMalloc(&d_ddst, ddst.size() * sizeof(int64_t)));
+            CK(cudaMemcpy(d_ddst, ddst.data(), ddst.size() * sizeof(int64_t), cudaMemcpyHostToDevice));
+            CK(cudaMalloc(&d_dpost, dpost.size() * sizeof(uint2)));
+            CK(cudaMemcpy(d_dpost, dpost.data(), dpost.size() * sizeof(uint2), cudaMemcpyHostToDevice));
+            CK(brag::sparse_append_move(s.term_ptr, s.post, s.V, s.nnz, d_dst_start, d_dpost, d_ddst, dnnz, g.post, 0));
+            CK(cudaDeviceSynchronize());
+            // the old postings are no longer needed: release them before the index of the grown space is built
+            free_sparse(s);
+            old_freed = true;
+            g.term_ptr_host = std::move(new_ptr);
+            build_sparse_index(g);
+        } catch (...) {
+            if (d_dst_start) cudaFree(d_dst_start);
+            if (d_ddst) cudaFree(d_ddst);
+            if (d_dpost) cudaFree(d_dpost);
+            free_sparse(g);
+            if (old_freed) e->sparse.erase(name);      // nothing left to serve: the caller must upload the space again
+            throw;
+        }
+        cudaFree(d_dst_start);
+        cudaFree(d_ddst);
+        cudaFree(d_dpost);
+        e->kernel_launches += 8;
+        s = std::move(g);
+    });
+}
+
 int brag_sparse_drop(brag_engine* e, const char* name) {
     return guarded([&] {
         REQUIRE(e && name, "brag_sparse_drop: NULL argument");

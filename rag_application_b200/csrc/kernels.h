@@ -67,6 +67,10 @@ cudaError_t compact_rows(const void* X, int row_bytes, const uint32_t* mask, int
 // keys of compact rows -> keys of original rows (same order: rowmap is increasing)
 cudaError_t remap_keys(uint64_t* keys, int64_t count, const uint32_t* rowmap, cudaStream_t st);
 cudaError_t compact_rowmap(const uint32_t* mask, int64_t n, const uint32_t* prefix, uint32_t* rowmap, cudaStream_t st);
+// brag_sparse_append: old posting i of term t -> out[dst_start[t] + i - term_ptr[t]]; delta posting j -> out[ddst[j]]
+cudaError_t sparse_append_move(const int64_t* term_ptr, const uint2* post, int64_t V, int64_t nnz,
+                               const int64_t* dst_start, const uint2* dpost, const int64_t* ddst, int64_t dnnz,
+                               uint2* out, cudaStream_t st);
 // filter-compacted copy of a sparse space: postings of the passing documents, renumbered (see compact.cu)
 size_t sparse_compact_tmp_bytes(int64_t V, int64_t nnz);
 cudaError_t sparse_compact_count(const int64_t* term_ptr, const uint2* post, int64_t V, int64_t nnz,

@@ -129,6 +129,16 @@ class Engine:
             _native.check(self._lib.brag_sparse_set_csr(self._h, name.encode(), term_ptr.ctypes.data, doc.ctypes.data,
                                                         w.ctypes.data, len(term_ptr) - 1, int(n_docs), 0))
 
+    def sparse_append(self, name: str, delta_term_ptr, doc, w, row_map, n_docs: int):
+        """Splice the postings of new documents (a CSR over the grown vocabulary) into a space already in HBM."""
+        delta_term_ptr = np.ascontiguousarray(delta_term_ptr, dtype=np.int64)
+        doc = np.ascontiguousarray(doc, dtype=np.uint32)
+        w = np.ascontiguousarray(w, dtype=np.float32)
+        row_map = np.ascontiguousarray(row_map, dtype=np.int32)
+        _native.check(self._lib.brag_sparse_append(self._h, name.encode(), delta_term_ptr.ctypes.data, doc.ctypes.data,
+                                                   w.ctypes.data, row_map.ctypes.data, len(delta_term_ptr) - 1,
+                                                   int(n_docs)))
+
     def sparse_drop(self, name: str):
         _native.check(self._lib.brag_sparse_drop(self._h, name.encode()))
 

@@ -142,7 +142,8 @@ def run_reference_flow(engine_factory=None, rtol=1e-5):
 
 def run_incremental_upsert(engine_factory=None, storage=None):
     """points upserted after the first query are appended / overwritten in HBM
-    (brag_dense_append / brag_dense_update) and must answer exactly like a collection uploaded in one go."""
+    (brag_dense_append / brag_dense_update / brag_sparse_append) and must answer exactly like a collection uploaded
+    in one go; overwriting a stored sparse vector falls back to a rebuild of that space."""
     from rag_application_b200.client import B200QdrantCore
     rng = np.random.Generator(np.random.PCG64(99))
     n, d = 900, 64
@@ -174,17 +175,35 @@ def run_incremental_upsert(engine_factory=None, storage=None):
     first = ask(inc, q)                                           # commits n rows
     calls = []
     eng = inc.engine
-    for name in ("dense_set", "dense_append", "dense_update"):
+    for name in ("dense_set", "dense_append", "dense_update", "sparse_set_csr", "sparse_append"):
         orig = getattr(eng, name)
         setattr(eng, name, (lambda o, nm: (lambda *a, **k: (calls.append(nm), o(*a, **k))[1]))(orig, name))
     changed = -x[7]
     inc.upsert("c", [point(i) for i in range(n, n + 50)] + [point(7, changed)])
     second = ask(inc, q)
     assert "dense_append" in calls and "dense_update" in calls and "dense_set" not in calls
+    assert "sparse_append" in calls and "sparse_set_csr" not in calls
     x2 = x.copy()
     x2[7] = changed
     full = make()
     full.upsert("c", [point(i, x2[i]) for i in range(n + 50)])
     assert ask(full, q) == second
+    # new vocabulary rows in the middle of the term order, then an overwritten sparse vector (rebuild)
+    del calls[:]
+    sp.append((np.array([3, 250, 777, 900]), np.array([0.9, 0.8, 0.7, 0.6], np.float32)))
+    x = np.concatenate([x, x[5:6] * 0.9 + 0.1 * x[6:7]])
+    x2 = np.concatenate([x2, x[-1:]])
+    inc.upsert("c", [point(n + 50)])
+    third = ask(inc, q)
+    assert "sparse_append" in calls and "sparse_set_csr" not in calls
+    full.upsert("c", [point(n + 50, x2[n + 50])])
+    assert ask(full, q) == third
+    del calls[:]
+    sp[11] = (sp[3][0].copy(), (sp[3][1] * 2).astype(np.float32))
+    inc.upsert("c", [point(11, x2[11])])
+    fourth = ask(inc, q)
+    assert "sparse_set_csr" in calls and fourth != third
+    full.upsert("c", [point(11, x2[11])])
+    assert ask(full, q) == fourth
     inc.close()
     full.close()

@@ -44,6 +44,28 @@ class OracleEngine:
         self.sparse[name] = O.CSR(_np(term_ptr).astype(np.int64), _np(doc).astype(np.uint32),
                                   _np(w).astype(np.float32), int(n_docs))
 
+    def sparse_append(self, name, delta_term_ptr, doc, w, row_map, n_docs):
+        """CPU mirror of brag_sparse_append: old lists keep their order, the delta follows them inside each term."""
+        old = self.sparse[name]
+        dptr = _np(delta_term_ptr).astype(np.int64)
+        ddoc, dw, rm = _np(doc).astype(np.uint32), _np(w).astype(np.float32), _np(row_map).astype(np.int64)
+        v_new = len(dptr) - 1
+        assert len(rm) == len(old.term_ptr) - 1 and (np.diff(rm) > 0).all() and n_docs >= old.n_docs
+        assert len(ddoc) == 0 or ddoc.min() >= old.n_docs
+        inv = np.full(v_new, -1, np.int64)
+        inv[rm] = np.arange(len(rm))
+        docs, ws, ptr = [], [], [0]
+        for t in range(v_new):
+            n = int(dptr[t + 1] - dptr[t])
+            if inv[t] >= 0:
+                a, b = old.term_ptr[inv[t]], old.term_ptr[inv[t] + 1]
+                docs.append(old.doc[a:b]); ws.append(old.w[a:b])
+                n += int(b - a)
+            docs.append(ddoc[dptr[t]:dptr[t + 1]]); ws.append(dw[dptr[t]:dptr[t + 1]])
+            ptr.append(ptr[-1] + n)
+        self.sparse[name] = O.CSR(np.asarray(ptr, np.int64), np.concatenate(docs).astype(np.uint32) if docs else np.zeros(0, np.uint32),
+                                  np.concatenate(ws).astype(np.float32) if ws else np.zeros(0, np.float32), int(n_docs))
+
     def sparse_drop(self, name):
         self.sparse.pop(name, None)
 

@@ -389,6 +389,55 @@ def test_sparse_filter_compacted_index(engine, B):
             assert np.array_equal(s0[b][:len(ei)].view(np.uint32), es.view(np.uint32))
 
 
+def test_sparse_append_equals_a_fresh_upload(engine):
+    """brag_sparse_append splices the postings of new documents into the index in HBM (old lists moved on
+    the device, vocabulary rows inserted in the middle of the term order, scan indexes rebuilt); every answer must be
+    bit-identical to a fresh upload of the grown corpus, through both scan kernels."""
+    n0, n1, V, k = 90000, 100000, 3000, 100
+    ptr, doc, w, _ = synth.zipf_corpus(n1, V, 60, seed=71)
+    term = np.repeat(np.arange(V), np.diff(ptr))
+    late = (term % 7) == 3                         # terms that only the appended documents use
+    keep = ~(late & (doc < n0))
+    term, doc, w = term[keep], doc[keep], w[keep]
+
+    def csr(sel, rows, n_rows):
+        p = np.zeros(n_rows + 1, np.int64)
+        np.add.at(p, rows[sel] + 1, 1)
+        return np.cumsum(p), doc[sel].astype(np.uint32), w[sel].astype(np.float32)
+
+    full_ptr, full_doc, full_w = csr(np.ones(len(term), bool), term, V)
+    old_terms = np.flatnonzero((np.arange(V) % 7) != 3)
+    old_row = np.full(V, -1, np.int64)
+    old_row[old_terms] = np.arange(len(old_terms))
+    is_old = doc < n0
+    o_ptr, o_doc, o_w = csr(is_old, old_row[term], len(old_terms))
+    d_ptr, d_doc, d_w = csr(~is_old, term, V)
+    engine.sparse_set_csr("f", full_ptr, full_doc, full_w, n1)
+    engine.sparse_set_csr("a", o_ptr, o_doc, o_w, n0)
+    engine.sparse_append("a", d_ptr, d_doc, d_w, old_terms.astype(np.int32), n1)
+    assert np.array_equal(engine.sparse_df("a", V), engine.sparse_df("f", V))
+    B = 48
+    q_ptr, q_terms, q_vals = synth.sparse_queries(full_ptr, full_doc, n1, B, 8, "zipf", seed=72, skip_top=16)
+    csr_o = _oracle_csr(full_ptr, full_doc, full_w, n1)
+    for path in ("scatter", "bitmap"):
+        engine.force_sparse_path(path)
+        try:
+            sa, ia, ca = engine.sparse_topk("a", q_ptr, q_terms, q_vals, k)
+            sf, if_, cf = engine.sparse_topk("f", q_ptr, q_terms, q_vals, k)
+        finally:
+            engine.force_sparse_path(None)
+        assert np.array_equal(ia, if_) and np.array_equal(ca, cf) and np.array_equal(sa.view(np.uint32), sf.view(np.uint32))
+        assert (ia[:, 0] >= 0).all() and (ia >= n0).any()
+    for b in range(0, B, 6):
+        es, ei = O.sparse_topk(csr_o, q_terms[q_ptr[b]:q_ptr[b + 1]], q_vals[q_ptr[b]:q_ptr[b + 1]], k)
+        assert int(ca[b]) == len(ei) and np.array_equal(ia[b][:len(ei)], ei)
+        assert np.array_equal(sa[b][:len(ei)].view(np.uint32), es.view(np.uint32))
+    with pytest.raises(Exception):                 # documents below the current count cannot be appended
+        engine.sparse_append("a", d_ptr, d_doc, d_w, np.arange(V, dtype=np.int32), n1 + 10)
+    engine.sparse_drop("a")
+    engine.sparse_drop("f")
+
+
 def test_sparse_nonfinite_weights_use_the_scatter_scan(engine):
     """A NaN/Inf weight makes per-term bounds meaningless: the space falls back to the exhaustive kernel."""
     ptr, doc, w, _ = synth.zipf_corpus(2000, 300, 30, seed=3)
