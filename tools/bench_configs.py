@@ -161,4 +161,33 @@ out["C3_bm25_1Mdocs_B1024"] = {"call_p50_ms": p50, "scan_kernel_ms": scan, "algo
 qp1, qt1, qv1 = qp_d[:2].contiguous(), qt_d[:8].contiguous(), qv_d[:8].contiguous()
 p50, best = timeit(lambda: eng.sparse_topk("c3", qp1, qt1, qv1, k), iters=20)
 out["C3_bm25_1Mdocs_B1"] = {"call_p50_ms": p50, "call_min_ms": best}
+
+# ---- f2: 8192 new documents appended to the C3 index in HBM vs re-uploading the grown CSR from host memory
+import time
+n_new = 8192
+d_ptr, d_doc, d_w, _ = synth.zipf_corpus(n_new, V, 285, seed=777)
+d_doc = (d_doc.astype(np.int64) + nd).astype(np.uint32)
+h_tp, h_doc, h_w = tp.cpu().numpy(), doc.cpu().numpy().astype(np.uint32), w.cpu().numpy()
+torch.cuda.synchronize()
+t0 = time.perf_counter()
+eng.sparse_append("c3", d_ptr, d_doc, d_w, np.arange(V, dtype=np.int32), nd + n_new)
+torch.cuda.synchronize()
+t_app = (time.perf_counter() - t0) * 1e3
+after = eng.sparse_topk("c3", qp_d, qt_d, qv_d, k)
+# the same grown corpus built on the host (what a commit did before brag_sparse_append) and uploaded
+t0 = time.perf_counter()
+term_h = np.repeat(np.arange(V), np.diff(h_tp))
+term_d = np.repeat(np.arange(V), np.diff(d_ptr))
+o = np.argsort(np.concatenate([term_h, term_d]), kind="stable")
+g_doc, g_w = np.concatenate([h_doc, d_doc])[o], np.concatenate([h_w, d_w])[o]
+g_ptr = h_tp + d_ptr
+t_host = (time.perf_counter() - t0) * 1e3
+t0 = time.perf_counter()
+eng.sparse_set_csr("c3f", g_ptr, g_doc, g_w, nd + n_new)
+torch.cuda.synchronize()
+t_up = (time.perf_counter() - t0) * 1e3
+fresh = eng.sparse_topk("c3f", qp_d, qt_d, qv_d, k)
+same = all(bool((a == b).all().item()) for a, b in zip(after, fresh))
+out["C3_append_8192_docs"] = {"sparse_append_ms": t_app, "host_merge_ms": t_host, "fresh_upload_ms": t_up,
+                              "delta_postings": int(d_ptr[-1]), "answers_identical": same}
 print(json.dumps(out, indent=1))
