@@ -115,6 +115,14 @@ int brag_rrf(brag_engine* e, const int64_t* ids, const int32_t* counts, int32_t 
              int32_t kmax, int32_t limit, int32_t tie_mode, double* out_scores,
              int64_t* out_ids, int32_t* out_counts, int32_t on_device, void* stream);
 
+/* Rerank of the fused hits, everything after the encoder (replaces the tensor code of
+ * rerank_documents, app/core/models/huggingface/huggingface.py:183-189, reached from qdrant_handler.py:401):
+ * query_hidden [Tq, d] and doc_hidden [n, T, d] are the encoder's last hidden states (float32, padding positions
+ * included, as the reference pools them); scores[i] = <mean_t query_hidden, mean_t doc_hidden[i]> and out_order is
+ * np.argsort(scores)[::-1] with equal scores ordered higher index first.  1 <= n <= 4096. */
+int brag_rerank_meanpool(brag_engine* e, const float* query_hidden, int32_t Tq, const float* doc_hidden, int32_t n,
+                         int32_t T, int32_t d, int32_t* out_order, float* out_scores, int32_t on_device, void* stream);
+
 /* k-way merge of per-shard top-k lists after the all-gather:
  * scores/ids = [G, B, k], counts = [G, B] -> [B, k]. */
 int brag_merge_topk(brag_engine* e, const float* scores, const int64_t* ids,

@@ -205,6 +205,18 @@ def apply_idf(csr: CSR, q_terms: Sequence[int], q_vals: Sequence[float]) -> List
     return out
 
 
+# ----------------------------------------------------------------------------- rerank (row f4)
+def rerank_meanpool(query_hidden: np.ndarray, doc_hidden: np.ndarray) -> Tuple[np.ndarray, np.ndarray]:
+    """The tensor code of rerank_documents (app/core/models/huggingface/huggingface.py:183-189): hidden states
+    mean-pooled over every position (padding included), dot products, `np.argsort(scores)[::-1]`.  The reference's
+    argsort is numpy's default (unstable); ties are pinned here as the reversed STABLE ascending order, i.e. equal
+    scores put the higher index first.  Returns (order, scores)."""
+    q = np.asarray(query_hidden, dtype=np.float32).mean(axis=0, dtype=np.float32)
+    dm = np.asarray(doc_hidden, dtype=np.float32).mean(axis=1, dtype=np.float32)
+    scores = (dm @ q).astype(np.float32)
+    return np.argsort(scores, kind="stable")[::-1].astype(np.int32), scores
+
+
 # ----------------------------------------------------------------------------- fusion
 def rrf(lists: Sequence[Sequence[int]], limit: int = DEFAULT_FUSION_LIMIT, tie: str = "id"
         ) -> Tuple[np.ndarray, np.ndarray]:

@@ -988,6 +988,30 @@ int brag_rrf(brag_engine* e, const int64_t* ids, const int32_t* counts, int32_t 
     });
 }
 
+int brag_rerank_meanpool(brag_engine* e, const float* query_hidden, int32_t Tq, const float* doc_hidden, int32_t n,
+                         int32_t T, int32_t d, int32_t* out_order, float* out_scores, int32_t on_device, void* stream) {
+    return guarded([&] {
+        REQUIRE(e && query_hidden && doc_hidden && out_order && out_scores, "brag_rerank_meanpool: NULL argument");
+        REQUIRE(Tq >= 1 && T >= 1 && d >= 1 && n >= 1 && n <= 4096, "brag_rerank_meanpool: need Tq, T, d >= 1 and 1 <= n <= 4096");
+        use_device(e);
+        cudaStream_t st = (cudaStream_t)stream;
+        StageTimer t(e, 1, st);
+        e->kernel_launches += 2;
+        if (on_device) {
+            CK(brag::rerank_meanpool(query_hidden, Tq, doc_hidden, n, T, d, out_scores, out_order, st));
+        } else {
+            const float* dq = to_dev(e->h_in[0], query_hidden, (size_t)Tq * d, st);
+            const float* dd = to_dev(e->h_in[1], doc_hidden, (size_t)n * T * d, st);
+            float* ds = e->h_out[0].as<float>((size_t)n);
+            int32_t* dord = e->h_out[2].as<int32_t>((size_t)n);
+            CK(brag::rerank_meanpool(dq, Tq, dd, n, T, d, ds, dord, st));
+            to_host(out_scores, ds, (size_t)n, st);
+            to_host(out_order, dord, (size_t)n, st);
+            CK(cudaStreamSynchronize(st));
+        }
+    });
+}
+
 int brag_merge_topk(brag_engine* e, const float* scores, const int64_t* ids, const int32_t* counts, int32_t G,
                     int32_t B, int32_t k, float* out_scores, int64_t* out_ids, int32_t* out_counts,
                     int32_t on_device, void* stream) {

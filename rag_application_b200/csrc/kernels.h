@@ -56,6 +56,10 @@ cudaError_t merge_scored_lists(const float* scores, const int64_t* ids, const in
                                int B, int k, float* out_scores, int64_t* out_ids, int32_t* out_counts,
                                cudaStream_t st);
 
+// ---- rerank.cu: mean-pooled hidden states -> scores [n] and the document order (score desc, higher index first)
+cudaError_t rerank_meanpool(const float* qh, int Tq, const float* dh, int n, int T, int d, float* scores,
+                            int32_t* order, cudaStream_t st);
+
 // ---- compact.cu: filter-compacted copy of a dense space (rows that pass a filter, gathered contiguously)
 size_t compact_tmp_bytes(int64_t nwords);
 // prefix: [ceil(n/32) + 1] passing rows before each filter word; the last entry is the number of passing rows

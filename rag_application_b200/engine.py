@@ -221,6 +221,27 @@ class Engine:
                                          int(dev), _stream() if dev else None))
         return s, i, c
 
+    def rerank_meanpool(self, query_hidden, doc_hidden):
+        """query_hidden [Tq, d], doc_hidden [n, T, d] float32 -> (order int32 [n], scores float32 [n])."""
+        dev = _is_torch_cuda(doc_hidden)
+        if dev:
+            import torch
+            query_hidden = query_hidden.to(torch.float32).contiguous()
+            doc_hidden = doc_hidden.to(torch.float32).contiguous()
+            n, T, d = doc_hidden.shape
+            order = torch.empty(n, dtype=torch.int32, device=doc_hidden.device)
+            scores = torch.empty(n, dtype=torch.float32, device=doc_hidden.device)
+        else:
+            query_hidden = np.ascontiguousarray(query_hidden, dtype=np.float32)
+            doc_hidden = np.ascontiguousarray(doc_hidden, dtype=np.float32)
+            n, T, d = doc_hidden.shape
+            order, scores = np.empty(n, np.int32), np.empty(n, np.float32)
+        assert query_hidden.ndim == 2 and query_hidden.shape[1] == d
+        _native.check(self._lib.brag_rerank_meanpool(self._h, _ptr(query_hidden), query_hidden.shape[0], _ptr(doc_hidden),
+                                                     n, T, d, _ptr(order), _ptr(scores), int(dev),
+                                                     _stream() if dev else None))
+        return order, scores
+
     def merge_topk(self, scores, ids, counts):
         """[G,B,k] per-shard lists -> [B,k]."""
         dev = _is_torch_cuda(ids)

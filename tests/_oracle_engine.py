@@ -143,6 +143,9 @@ class OracleEngine:
             out.append(O.rrf([I[l, b, :Cn[l, b]] for l in range(L)], limit=limit, tie="id" if tie == 0 else "first_seen"))
         return self._wrap(ids, *self._pad(out, limit, np.float64))
 
+    def rerank_meanpool(self, query_hidden, doc_hidden):
+        return O.rerank_meanpool(_np(query_hidden), _np(doc_hidden))
+
     def merge_topk(self, scores, ids, counts):
         self.calls.append(("merge_topk",))
         S, I, Cn = _np(scores), _np(ids), _np(counts)
