@@ -62,45 +62,96 @@ int64_t bm25x_row_words(int64_t n_docs) {
 }
 
 // ------------------------------------------------------------------------------------ index build
-__global__ void bm25x_wrange_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict__ post, int64_t V,
-                                    float2* __restrict__ wrange) {
-    __shared__ float s_mn[8], s_mx[8];
-    for (int64_t t = blockIdx.x; t < V; t += gridDim.x) {
-        const int64_t lo = term_ptr[t], hi = term_ptr[t + 1];
-        float mn = INFINITY, mx = -INFINITY;
-        for (int64_t i = lo + threadIdx.x; i < hi; i += blockDim.x) {
-            const float w = __uint_as_float(__ldg(&post[i].y));
-            mn = fminf(mn, w);
-            mx = fmaxf(mx, w);
-        }
-#pragma unroll
-        for (int off = 16; off > 0; off >>= 1) {
-            mn = fminf(mn, __shfl_xor_sync(0xFFFFFFFFu, mn, off));
-            mx = fmaxf(mx, __shfl_xor_sync(0xFFFFFFFFu, mx, off));
-        }
-        if ((threadIdx.x & 31) == 0) { s_mn[threadIdx.x >> 5] = mn; s_mx[threadIdx.x >> 5] = mx; }
-        __syncthreads();
-        if (threadIdx.x == 0) {
-            for (int i = 1; i < (int)(blockDim.x >> 5); ++i) { mn = fminf(mn, s_mn[i]); mx = fmaxf(mx, s_mx[i]); }
-            if (hi == lo) { mn = 0.f; mx = 0.f; }
-            // NaN weights: fminf/fmaxf drop them; such a term gets an infinite bound (never pruned on)
-            wrange[t] = make_float2(mn, mx);
-        }
-        __syncthreads();
+// Weight range of every term, and whether any weight is NaN / Inf, in one pass over the postings: a warp walks chunks of
+// WR_CHUNK consecutive postings (four coalesced loads per lane in flight), follows the term boundaries from one search
+// per chunk, keeps min / max in registers and folds them into the term's slot (order-preserving uint32 images, so
+// atomicMin / atomicMax work) once per (chunk, term).  `slots` aliases wrange: {min image, max image} per term,
+// converted in place by bm25x_wrange_fin_kernel.
+constexpr int WR_CHUNK = 8192;
+
+__global__ void bm25x_wrange_init_kernel(uint2* __restrict__ slots, int64_t V) {
+    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t < V) slots[t] = make_uint2(0xFFFFFFFFu, 0u);
+}
+
+__device__ __forceinline__ void wr_fold(uint2* __restrict__ slots, int64_t t, float mn, float mx) {
+    if (mn <= mx) {          // false when nothing finite-or-infinite was seen (empty segment, or only NaNs)
+        atomicMin(&slots[t].x, f32_ordered(mn));
+        atomicMax(&slots[t].y, f32_ordered(mx));
     }
 }
 
-__global__ void bm25x_nan_kernel(const uint2* __restrict__ post, int64_t nnz, int* __restrict__ flag) {
-    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < nnz) {
-        const float w = __uint_as_float(post[i].y);
-        if (!(fabsf(w) <= 3.0e38f)) *flag = 1;      // NaN or Inf weight: pruning bounds are meaningless
+__global__ void bm25x_wrange_walk_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict__ post, int64_t V,
+                                         int64_t nnz, uint2* __restrict__ slots, int* __restrict__ flag) {
+    const int lane = threadIdx.x & 31;
+    const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    const int64_t nchunks = (nnz + WR_CHUNK - 1) / WR_CHUNK;
+    bool bad = false;
+    for (int64_t c = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; c < nchunks; c += nwarps) {
+        const int64_t i0 = c * WR_CHUNK, i1 = min(nnz, i0 + (int64_t)WR_CHUNK);
+        int64_t t = term_of_posting(term_ptr, V, i0);
+        int64_t end = __ldg(term_ptr + t + 1);
+        float mn = INFINITY, mx = -INFINITY;
+        for (int64_t base = i0; base < i1; base += 128) {
+            float w[4];
+            bool have[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int64_t i = base + u * 32 + lane;
+                have[u] = i < i1;
+                w[u] = have[u] ? __uint_as_float(__ldcs(post + i).y) : 0.f;
+                bad |= !(fabsf(w[u]) <= 3.0e38f);      // NaN or Inf weight: pruning bounds are meaningless
+            }
+            if (base + 128 <= end) {
+#pragma unroll
+                for (int u = 0; u < 4; ++u)
+                    if (have[u]) { mn = fminf(mn, w[u]); mx = fmaxf(mx, w[u]); }
+                continue;
+            }
+            // a term ends inside this block: fold what the warp holds, then one search per posting
+#pragma unroll
+            for (int o = 16; o; o >>= 1) {
+                mn = fminf(mn, __shfl_xor_sync(0xFFFFFFFFu, mn, o));
+                mx = fmaxf(mx, __shfl_xor_sync(0xFFFFFFFFu, mx, o));
+            }
+            if (lane == 0) wr_fold(slots, t, mn, mx);
+            mn = INFINITY;
+            mx = -INFINITY;
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+                if (have[u] && w[u] == w[u])
+                    wr_fold(slots, term_of_posting(term_ptr, V, base + u * 32 + lane), w[u], w[u]);
+            if (base + 128 < i1) {
+                t = term_of_posting(term_ptr, V, base + 128);
+                end = __ldg(term_ptr + t + 1);
+            }
+        }
+#pragma unroll
+        for (int o = 16; o; o >>= 1) {
+            mn = fminf(mn, __shfl_xor_sync(0xFFFFFFFFu, mn, o));
+            mx = fmaxf(mx, __shfl_xor_sync(0xFFFFFFFFu, mx, o));
+        }
+        if (lane == 0) wr_fold(slots, t, mn, mx);
     }
+    if (bad) *flag = 1;
+}
+
+__global__ void bm25x_wrange_fin_kernel(const int64_t* __restrict__ term_ptr, float2* __restrict__ wrange, int64_t V) {
+    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= V) return;
+    const uint2 s = reinterpret_cast<const uint2*>(wrange)[t];
+    float2 r;
+    if (term_ptr[t + 1] == term_ptr[t]) r = make_float2(0.f, 0.f);
+    else if (s.x > s.y) r = make_float2(INFINITY, -INFINITY);      // only NaN weights: never pruned on
+    else r = make_float2(ordered_f32(s.x), ordered_f32(s.y));
+    wrange[t] = r;
 }
 
 // tau[t]: weight threshold that splits the postings of term t into a "low" class (w <= tau, at least ~70 % of them)
 // and a "high" class: 64-bin histogram over [min, max], tau = upper edge of the first bin whose cumulative count
 // reaches 70 % (tau = max when the term has a single weight).  For BM25 the low class is the tf = 1 postings.
+constexpr int TAU_SAMPLES = 4096;
+
 __global__ void bm25x_tau_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict__ post, int64_t V,
                                  const float2* __restrict__ wrange, float* __restrict__ tau) {
     __shared__ unsigned int hist[64];
@@ -108,12 +159,16 @@ __global__ void bm25x_tau_kernel(const int64_t* __restrict__ term_ptr, const uin
         const int64_t lo = term_ptr[t], hi = term_ptr[t + 1];
         const float2 wr = wrange[t];
         const float span = wr.y - wr.x;
+        // tau only steers how well the two classes prune (the scan and the maps use the same value, any value is
+        // safe), so long lists are sampled: TAU_SAMPLES postings at an even stride
+        const int64_t stride = max((int64_t)1, (hi - lo) / TAU_SAMPLES);
+        const int64_t ns = (hi - lo + stride - 1) / stride;
         if (threadIdx.x < 64) hist[threadIdx.x] = 0u;
         __syncthreads();
         if (span > 0.f && span < 3.0e38f) {
             const float inv = 64.f / span;
-            for (int64_t i = lo + threadIdx.x; i < hi; i += blockDim.x) {
-                const float w = __uint_as_float(__ldg(&post[i].y));
+            for (int64_t j = threadIdx.x; j < ns; j += blockDim.x) {
+                const float w = __uint_as_float(__ldg(&post[lo + j * stride].y));
                 int b = (int)((w - wr.x) * inv);
                 b = min(63, max(0, b));
                 atomicAdd(&hist[b], 1u);
@@ -123,7 +178,7 @@ __global__ void bm25x_tau_kernel(const int64_t* __restrict__ term_ptr, const uin
         if (threadIdx.x == 0) {
             float tv = wr.y;
             if (span > 0.f && span < 3.0e38f) {
-                const unsigned long long need = (unsigned long long)((hi - lo) * 7 / 10);
+                const unsigned long long need = (unsigned long long)(ns * 7 / 10);
                 unsigned long long cum = 0;
                 for (int b = 0; b < 64; ++b) {
                     cum += hist[b];
@@ -160,15 +215,17 @@ __global__ void bm25x_bitmap_kernel(const int64_t* __restrict__ term_ptr, const 
 cudaError_t bm25x_build_wrange(const int64_t* term_ptr, const uint2* post, int64_t V, int64_t nnz, float2* wrange,
                                float* tau, int* nonfinite_flag, cudaStream_t st) {
     if (V == 0) return cudaSuccess;
-    bm25x_wrange_kernel<<<(unsigned)std::min<int64_t>(V, 148 * 16), 256, 0, st>>>(term_ptr, post, V, wrange);
-    cudaError_t e = cudaGetLastError();
+    cudaError_t e = cudaMemsetAsync(nonfinite_flag, 0, sizeof(int), st);
     if (e != cudaSuccess) return e;
+    bm25x_wrange_init_kernel<<<(unsigned)((V + 255) / 256), 256, 0, st>>>(reinterpret_cast<uint2*>(wrange), V);
+    if (nnz) {
+        const int64_t blocks = std::min<int64_t>((nnz + WR_CHUNK * 8 - 1) / (WR_CHUNK * 8), 148 * 8);
+        bm25x_wrange_walk_kernel<<<(unsigned)blocks, 256, 0, st>>>(term_ptr, post, V, nnz,
+                                                                  reinterpret_cast<uint2*>(wrange), nonfinite_flag);
+    }
+    bm25x_wrange_fin_kernel<<<(unsigned)((V + 255) / 256), 256, 0, st>>>(term_ptr, wrange, V);
+    if ((e = cudaGetLastError()) != cudaSuccess) return e;
     bm25x_tau_kernel<<<(unsigned)std::min<int64_t>(V, 148 * 16), 256, 0, st>>>(term_ptr, post, V, wrange, tau);
-    e = cudaGetLastError();
-    if (e != cudaSuccess) return e;
-    e = cudaMemsetAsync(nonfinite_flag, 0, sizeof(int), st);
-    if (e != cudaSuccess || nnz == 0) return e;
-    bm25x_nan_kernel<<<(unsigned)((nnz + 255) / 256), 256, 0, st>>>(post, nnz, nonfinite_flag);
     return cudaGetLastError();
 }
 

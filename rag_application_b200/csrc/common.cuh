@@ -92,6 +92,17 @@ __device__ __forceinline__ uint32_t hist_bound(const uint32_t* __restrict__ coar
     return (uint32_t)(cb * HIST_FINE_PER_COARSE + 4 * FL + fb) << HIST_FINE_SHIFT;
 }
 
+// ---------------------------------------------------------------- term-major CSR walks
+// term owning posting i of a term-major CSR: the last t with term_ptr[t] <= i (empty terms are skipped)
+__device__ __forceinline__ int64_t term_of_posting(const int64_t* __restrict__ term_ptr, int64_t V, int64_t i) {
+    int64_t lo = 0, hi = V;              // last t with term_ptr[t] <= i
+    while (hi - lo > 1) {
+        const int64_t mid = (lo + hi) >> 1;
+        if (__ldg(term_ptr + mid) <= i) lo = mid; else hi = mid;
+    }
+    return lo;
+}
+
 // ---------------------------------------------------------------- bitonic sort (descending)
 // n must be a power of two; all `nthreads` threads of the group call it; `sync` is
 // __syncthreads for a CTA-wide sort or __syncwarp for a warp-private one.

@@ -69,15 +69,6 @@ __global__ void remap_keys_kernel(uint64_t* __restrict__ keys, int64_t count, co
 // list stays sorted by document), renumbered to compact document ids, and indexed like any other space; scores are
 // sums of the same weights in the same term order, so the results are bit-identical after the id remap.
 
-__device__ __forceinline__ int64_t term_of_posting(const int64_t* __restrict__ term_ptr, int64_t V, int64_t i) {
-    int64_t lo = 0, hi = V;              // last t with term_ptr[t] <= i
-    while (hi - lo > 1) {
-        const int64_t mid = (lo + hi) >> 1;
-        if (__ldg(term_ptr + mid) <= i) lo = mid; else hi = mid;
-    }
-    return lo;
-}
-
 // cnt[t] = postings of term t whose document passes the mask.  A warp walks chunks of KEEP_CHUNK consecutive
 // postings, four coalesced loads per lane in flight; the term is searched once per chunk and followed from there, the
 // count lives in registers and reaches cnt[] once per (chunk, term).  Only a 128-posting block that straddles a term

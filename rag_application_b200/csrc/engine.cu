@@ -603,7 +603,8 @@ int brag_destroy(brag_engine* e) {
         for (auto& kv : e->sparse) free_sparse(kv.second);
         for (auto& kv : e->masks) if (kv.second.bits) cudaFree(kv.second.bits);
         DevBuf* bufs[] = {&e->qs, &e->q16, &e->part, &e->tmp_a, &e->tmp_b, &e->keys1, &e->keys2, &e->umma_scratch,
-                          &e->work_counter, &e->g_thr, &e->hyb_ids, &e->hyb_counts, &e->hyb_scores};
+                          &e->work_counter, &e->g_thr, &e->hyb_ids, &e->hyb_counts, &e->hyb_scores, &e->cp_prefix,
+                          &e->cp_tmp};
         for (DevBuf* b : bufs) b->release();
         for (auto& b : e->h_in) b.release();
         for (auto& b : e->h_out) b.release();

@@ -32,7 +32,12 @@ tp, doc, w = synth.zipf_corpus_torch(a.n, a.vocab, a.doc_len, dev)
 qp, qt, qv = synth.sparse_queries_torch(tp, a.batch, a.q_terms)
 ldf = tp[1:] - tp[:-1]
 alg_bytes = float(ldf[qt.to(dev).long()].sum().item()) * 8.0
+import time
+torch.cuda.synchronize()
+_t0 = time.perf_counter()
 eng.sparse_set_csr("s", tp, doc, w, a.n)
+torch.cuda.synchronize()
+index_build_ms = (time.perf_counter() - _t0) * 1e3      # device-resident CSR -> interleave + every scan index
 del doc, w
 torch.cuda.empty_cache()
 mask_id = 0
@@ -43,7 +48,8 @@ if a.mask > 0:
     mask_id = 1
 qp_d, qt_d, qv_d = qp.to(dev), qt.to(dev), qv.to(dev)
 eng.profile_enable(True)
-out = {"n": a.n, "batch": a.batch, "k": a.k, "algorithmic_bytes": alg_bytes, "mask": a.mask}
+out = {"n": a.n, "batch": a.batch, "k": a.k, "algorithmic_bytes": alg_bytes, "mask": a.mask,
+       "index_build_ms": index_build_ms}
 res = {}
 for path in a.paths.split(","):
     eng.force_sparse_path(path)
