@@ -706,8 +706,15 @@ static cudaError_t bx_launch(const BxArgs& a) {
     uint32_t* gthr = reinterpret_cast<uint32_t*>(sp + 256);
     uint32_t* coarse = reinterpret_cast<uint32_t*>(sp + 256 + plan.gthr_bytes);
     uint32_t* fine = reinterpret_cast<uint32_t*>(sp + 256 + plan.gthr_bytes + plan.coarse_bytes);
-    cudaError_t e = cudaMemsetAsync(a.scratch, 0, plan.scratch_bytes, a.st);
+    // BRAG_BX_WARM=1 (experiment only, tools/bm25_probe.py): keep the previous call's per-query bounds, to measure
+    // what a perfect starting bound would be worth when the same batch is repeated
+    static const bool warm = [] { const char* w = getenv("BRAG_BX_WARM"); return w && atoi(w) == 1; }();
+    cudaError_t e = cudaMemsetAsync(a.scratch, 0, warm ? 256 : plan.scratch_bytes, a.st);
     if (e != cudaSuccess) return e;
+    if (warm) {
+        e = cudaMemsetAsync(sp + 256 + plan.gthr_bytes, 0, plan.coarse_bytes + plan.fine_bytes, a.st);
+        if (e != cudaSuccess) return e;
+    }
     if (plan.seed_tiles > 0) {
         const int seed_items = (a.B + plan.seed_qpi - 1) / plan.seed_qpi;
         bm25x_scan_kernel<MAXT, SUBS><<<std::min(seed_items, plan.grid), (plan.workers + 1) * 32, smem, a.st>>>(

@@ -520,6 +520,47 @@ def test_hybrid_three_stage(engine):
             assert np.array_equal(s[b][:len(ei)], es)
 
 
+def test_hybrid_call_replays_from_a_cuda_graph(engine):
+    """The device-pointer hybrid call is stream-ordered and, once warmed up, allocation- and sync-free, so a serving loop
+    can capture it once and replay it per query (bench.py batch1.graph_replay_p50_ms): the replay must answer like the
+    eager call, also after new query contents were copied into the captured buffers."""
+    import torch
+    n, d, k = 20000, 256, 50
+    x = synth.dense_corpus(n, d, seed=61, clustered=True)
+    q = synth.dense_queries(x, 2, seed=62)
+    ptr, doc, w, _ = synth.zipf_corpus(n, 3000, 80, seed=63)
+    q_ptr, q_terms, q_vals = synth.sparse_queries(ptr, doc, n, 2, 8, "zipf", seed=64, skip_top=8)
+    engine.dense_set("dense", x, "bf16")
+    engine.sparse_set_csr("sparse", ptr, doc, w, n)
+    dev = torch.device("cuda", 0)
+    tq = torch.from_numpy(q).to(dev)
+    tt, tv = torch.from_numpy(q_terms).to(dev), torch.from_numpy(q_vals).to(dev)
+    q1, qp1 = tq[:1].clone(), torch.tensor([0, 8], dtype=torch.int32, device=dev)
+    qt1, qv1 = tt[:8].clone(), tv[:8].clone()
+
+    def call():
+        return engine.hybrid_topk("dense", "sparse", q1, qp1, qt1, qv1, k)
+
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        for _ in range(3):
+            call()
+    torch.cuda.current_stream().wait_stream(side)
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph):
+        captured = call()
+    for b in range(2):
+        q1.copy_(tq[b:b + 1]); qt1.copy_(tt[8 * b:8 * b + 8]); qv1.copy_(tv[8 * b:8 * b + 8])
+        graph.replay()
+        torch.cuda.synchronize()
+        got = [t.clone() for t in captured]
+        want = call()
+        torch.cuda.synchronize()
+        assert all(torch.equal(a, b_) for a, b_ in zip(got, want)), f"query {b}"
+        assert int(got[2][0]) > 0
+
+
 @pytest.mark.parametrize("G", [2, 4, 8])
 def test_logical_shards_on_one_gpu_match_unsharded(engine, G):
     """Row sharding emulated on one device: G engines own disjoint row ranges and answer
