@@ -8,7 +8,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "csrc", "libbrag.so")
+# BRAG_LIB: load another build of the same ABI (A/B timing of kernel variants in tools/); default = the in-tree build
+LIB_PATH = os.environ.get("BRAG_LIB") or os.path.join(_HERE, "csrc", "libbrag.so")
 
 c_p = C.c_void_p
 i32, i64 = C.c_int32, C.c_int64

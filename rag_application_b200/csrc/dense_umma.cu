@@ -29,6 +29,13 @@
 
 namespace brag {
 
+// max of three floats in one instruction (PTX ISA 8.6, sm_100: FMNMX3); NaN operands are ignored like fmaxf
+__device__ __forceinline__ float fmax3(float a, float b, float c) {
+    float d;
+    asm("max.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
+    return d;
+}
+
 constexpr int UM_BM = 128;
 constexpr int UM_BN = 256;
 constexpr int UM_BK = 64;
@@ -340,6 +347,23 @@ dense_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
                 auto process = [&](uint32_t (&v)[32], int col0) {
                     // rows of this 32-column group that exist and pass the payload filter (tiles start on
                     // multiples of 256 rows, so a group is exactly one filter word): warp-uniform
+                    // most groups hold no candidate for any of the warp's 32 queries: the group's maximum (three-input
+                    // max, 18 instructions for 32 scores) against the bound settles those with one vote
+                    float c0 = fmax3(__uint_as_float(v[0]), __uint_as_float(v[1]), __uint_as_float(v[2]));
+                    float c1 = fmax3(__uint_as_float(v[8]), __uint_as_float(v[9]), __uint_as_float(v[10]));
+                    float c2 = fmax3(__uint_as_float(v[16]), __uint_as_float(v[17]), __uint_as_float(v[18]));
+                    float c3 = fmax3(__uint_as_float(v[24]), __uint_as_float(v[25]), __uint_as_float(v[26]));
+                    c0 = fmax3(c0, __uint_as_float(v[3]), __uint_as_float(v[4]));
+                    c1 = fmax3(c1, __uint_as_float(v[11]), __uint_as_float(v[12]));
+                    c2 = fmax3(c2, __uint_as_float(v[19]), __uint_as_float(v[20]));
+                    c3 = fmax3(c3, __uint_as_float(v[27]), __uint_as_float(v[28]));
+                    c0 = fmax3(c0, __uint_as_float(v[5]), __uint_as_float(v[6]));
+                    c1 = fmax3(c1, __uint_as_float(v[13]), __uint_as_float(v[14]));
+                    c2 = fmax3(c2, __uint_as_float(v[21]), __uint_as_float(v[22]));
+                    c3 = fmax3(c3, __uint_as_float(v[29]), __uint_as_float(v[30]));
+                    c0 = fmax3(c0, __uint_as_float(v[7]), __uint_as_float(v[15]));
+                    c2 = fmax3(c2, __uint_as_float(v[23]), __uint_as_float(v[31]));
+                    if (!__any_sync(0xFFFFFFFFu, fmax3(c0, c1, fmaxf(c2, c3)) > eff)) return;
                     const int64_t r0 = row0 + col0;
                     uint32_t cm = (row_end - r0 >= 32) ? 0xFFFFFFFFu : (row_end > r0 ? (1u << (int)(row_end - r0)) - 1u : 0u);
                     if (mask != nullptr) cm &= __ldg(mask + (r0 >> 5));
