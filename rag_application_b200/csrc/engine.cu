@@ -338,7 +338,8 @@ bool ensure_sparse_compact(brag_engine* e, SparseSpace& s, int mask_id, const ui
         s.cp_state = 0;
     }
     if (e->sparse_compact_after < 0) return false;
-    if (s.cp_state == 1) return true;
+    // (a single query is as fast through the masked scan of the full index: C5 shard 0.105 vs 0.142 ms)
+    if (s.cp_state == 1) return B >= 32 || e->sparse_compact_after == 0;
     if (s.cp_state == 2) return false;
     // single queries are latency-bound, not posting-bound (C5 shard: 0.13 ms either way): only batches count
     if (s.cp_queries < e->sparse_compact_after) { if (B >= 32) s.cp_queries += B; return false; }
