@@ -303,6 +303,8 @@ def main():
         b1 = {"p50_ms": float(np.median(lat)), "p95_ms": float(np.percentile(lat, 95)), "iters": args.b1_iters,
               "hbm_floor_ms": n_loc * args.d * 2 / (peaks["hbm_gbs"] * 1e9) * 1e3}
         if world == 1:
+            # (N > 1 was tried with the all-gather inside the graph: 1.90 -> 1.76 ms at 2 GPUs, but the process group
+            # then hangs at teardown, so the sharded path stays eager)
             # the same call captured once in a CUDA graph and replayed (the call is stream-ordered and allocation-free
             # after warm-up): what a serving loop with fixed query buffers pays per query, launch overhead removed
             try:
