@@ -264,7 +264,7 @@ bm25x_scan_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict_
                   const float2* __restrict__ wrange, const float* __restrict__ tau, int64_t V, int64_t n_docs,
                   const int32_t* __restrict__ q_ptr, const int32_t* __restrict__ q_terms,
                   const double* __restrict__ q_vals, int B, const uint32_t* __restrict__ mask, int k_sel, int lcap,
-                  int nw, uint64_t* __restrict__ part, int splits, int seed_tiles, int seed_qpi, int seed_mode,
+                  int nw, uint64_t* __restrict__ part, int splits, int seed_tiles, int seed_qpi, int seed_mode, unsigned mgr_sleep_ns,
                   int* __restrict__ work_counter,
                   uint32_t* __restrict__ gthr, uint32_t* __restrict__ coarse, uint32_t* __restrict__ fine) {
     using C = BxCfg<MAXT, SUBS>;
@@ -285,7 +285,7 @@ bm25x_scan_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict_
                 if (lane == 0 && bound != 0u) atomicMax(gthr + q, bound);
             }
             if (done) break;
-            __nanosleep(10000);
+            __nanosleep(mgr_sleep_ns);
         }
         return;
     }
@@ -639,6 +639,12 @@ static int bx_lcap(int k_sel) {
 
 static int bx_maxt(int max_terms) { return max_terms <= 8 ? 8 : (max_terms <= 16 ? 16 : 32); }
 
+// pause of a CTA's bound-manager warp between sweeps of its queries' histograms (BRAG_BX_MGR_NS, tuning knob)
+static unsigned bx_mgr_sleep() {
+    static const unsigned ns = [] { const char* e = getenv("BRAG_BX_MGR_NS"); const int v = e ? atoi(e) : 4000; return (unsigned)(v < 0 ? 0 : v); }();
+    return ns;
+}
+
 // sub-tiles per visit: 2 unless BRAG_BX_SUBS says otherwise (tuning knob, read once)
 static int bx_subs() {
     static int subs = [] {
@@ -719,13 +725,13 @@ static cudaError_t bx_launch(const BxArgs& a) {
         const int seed_items = (a.B + plan.seed_qpi - 1) / plan.seed_qpi;
         bm25x_scan_kernel<MAXT, SUBS><<<std::min(seed_items, plan.grid), (plan.workers + 1) * 32, smem, a.st>>>(
             a.term_ptr, a.post, a.sub_off, a.bm_row, a.bits, a.bits_hi, a.wrange, a.tau, a.V, a.n_docs, a.q_ptr, a.q_terms,
-            a.q_vals, a.B, a.mask, a.k_sel, lcap, plan.workers, a.part, plan.splits, plan.seed_tiles, plan.seed_qpi, 1,
+            a.q_vals, a.B, a.mask, a.k_sel, lcap, plan.workers, a.part, plan.splits, plan.seed_tiles, plan.seed_qpi, 1, bx_mgr_sleep(),
             work_counter + 1, gthr, coarse, fine);
         if ((e = cudaGetLastError()) != cudaSuccess) return e;
     }
     bm25x_scan_kernel<MAXT, SUBS><<<plan.grid, (plan.workers + 1) * 32, smem, a.st>>>(
         a.term_ptr, a.post, a.sub_off, a.bm_row, a.bits, a.bits_hi, a.wrange, a.tau, a.V, a.n_docs, a.q_ptr, a.q_terms,
-        a.q_vals, a.B, a.mask, a.k_sel, lcap, plan.workers, a.part, plan.splits, plan.seed_tiles, plan.seed_qpi, 0,
+        a.q_vals, a.B, a.mask, a.k_sel, lcap, plan.workers, a.part, plan.splits, plan.seed_tiles, plan.seed_qpi, 0, bx_mgr_sleep(),
         work_counter, gthr, coarse, fine);
     return cudaGetLastError();
 }
