@@ -68,6 +68,84 @@ def test_sparse_random_shapes_bit_exact(engine, n_docs, V, L, k, B, nt, path, se
         assert np.all(i[b][len(ei):] == -1)
 
 
+@settings(max_examples=15, **COMMON)
+@given(n_docs=st.integers(2100, 30000), V=st.integers(1, 3000), L=st.integers(1, 80), k=st.integers(1, 128),
+       B=st.sampled_from([1, 5, 40]), nt=st.integers(1, 12), path=st.sampled_from(["scatter", "bitmap", None]),
+       sel=st.sampled_from([0.5, 0.3, 0.06]), seed=st.integers(0, 2 ** 16))
+def test_sparse_compacted_index_random_shapes_bit_exact(engine, n_docs, V, L, k, B, nt, path, sel, seed):
+    """Filter-compacted sparse index (compact.cu) on random shapes: built on first use, oracle-exact.  (Filters keeping
+    fewer than 1024 documents or more than half of them fall back to the masked scan: also exercised here.)"""
+    ptr, doc, w, _ = synth.zipf_corpus(n_docs, V, L, seed=seed)
+    rng = np.random.default_rng(seed)
+    csr = O.CSR(ptr, doc, w, n_docs)
+    nt = min(nt, V)
+    q_ptr = np.arange(0, (B + 1) * nt, nt, dtype=np.int32)
+    q_terms = np.concatenate([np.sort(rng.choice(V, nt, replace=False)) for _ in range(B)]).astype(np.int32)
+    q_vals = rng.random(B * nt)
+    engine.sparse_set_csr("h", ptr, doc, w, n_docs)
+    mask = synth.random_mask(n_docs, sel, seed=seed + 2)
+    engine.mask_set(9, mask)
+    engine.sparse_compact_after(0)
+    engine.force_sparse_path(path)
+    try:
+        s, i, c = engine.sparse_topk("h", q_ptr, q_terms, q_vals, k, mask_id=9)
+        s2, i2, c2 = engine.sparse_topk("h", q_ptr, q_terms, q_vals, k, mask_id=9)       # cached index
+    finally:
+        engine.force_sparse_path(None)
+        engine.sparse_compact_after(256)
+    assert np.array_equal(i, i2) and np.array_equal(c, c2) and np.array_equal(s.view(np.uint32), s2.view(np.uint32))
+    for b in range(B):
+        es, ei = O.sparse_topk(csr, q_terms[q_ptr[b]:q_ptr[b + 1]], q_vals[q_ptr[b]:q_ptr[b + 1]], k, mask=mask)
+        assert int(c[b]) == len(ei) and np.array_equal(i[b][:len(ei)], ei), (b, path)
+        assert np.array_equal(s[b][:len(ei)].view(np.uint32), es.view(np.uint32))
+
+
+@settings(max_examples=15, **COMMON)
+@given(n0=st.integers(1, 8000), extra=st.integers(0, 3000), V=st.integers(2, 2000), L=st.integers(1, 60),
+       drop=st.sampled_from([0, 2, 5]), k=st.integers(1, 100), seed=st.integers(0, 2 ** 16))
+def test_sparse_append_random_shapes_equal_fresh_upload(engine, n0, extra, V, L, drop, k, seed):
+    """brag_sparse_append on random shapes: documents [n0, n0 + extra) spliced into an index of the first n0, with
+    every `drop`-th vocabulary row unknown to the old index (inserted in the middle of the term order); answers and
+    document frequencies must equal a fresh upload, and the oracle."""
+    n1 = n0 + extra
+    ptr, doc, w, _ = synth.zipf_corpus(n1, V, L, seed=seed)
+    term = np.repeat(np.arange(V), np.diff(ptr))
+    late = ((term % drop) == 1) if drop else np.zeros(len(term), bool)
+    keep = ~(late & (doc < n0))
+    term, doc, w = term[keep], doc[keep], w[keep]
+
+    def csr(sel, rows, n_rows):
+        p = np.zeros(n_rows + 1, np.int64)
+        np.add.at(p, rows[sel] + 1, 1)
+        return np.cumsum(p), doc[sel].astype(np.uint32), w[sel].astype(np.float32)
+
+    full = csr(np.ones(len(term), bool), term, V)
+    old_terms = np.flatnonzero((np.arange(V) % drop) != 1) if drop else np.arange(V)
+    old_row = np.full(V, -1, np.int64)
+    old_row[old_terms] = np.arange(len(old_terms))
+    is_old = doc < n0
+    o = csr(is_old, old_row[term], len(old_terms))
+    d = csr(~is_old, term, V)
+    engine.sparse_set_csr("f", full[0], full[1], full[2], n1)
+    engine.sparse_set_csr("a", o[0], o[1], o[2], n0)
+    engine.sparse_append("a", d[0], d[1], d[2], old_terms.astype(np.int32), n1)
+    assert np.array_equal(engine.sparse_df("a", V), engine.sparse_df("f", V))
+    rng = np.random.default_rng(seed)
+    B, nt = 6, min(6, V)
+    q_ptr = np.arange(0, (B + 1) * nt, nt, dtype=np.int32)
+    q_terms = np.concatenate([np.sort(rng.choice(V, nt, replace=False)) for _ in range(B)]).astype(np.int32)
+    q_vals = rng.random(B * nt)
+    sa, ia, ca = engine.sparse_topk("a", q_ptr, q_terms, q_vals, k)
+    sf, if_, cf = engine.sparse_topk("f", q_ptr, q_terms, q_vals, k)
+    assert np.array_equal(ia, if_) and np.array_equal(ca, cf) and np.array_equal(sa.view(np.uint32), sf.view(np.uint32))
+    oc = O.CSR(full[0], full[1], full[2], n1)
+    for b in range(B):
+        es, ei = O.sparse_topk(oc, q_terms[q_ptr[b]:q_ptr[b + 1]], q_vals[q_ptr[b]:q_ptr[b + 1]], k)
+        assert int(ca[b]) == len(ei) and np.array_equal(ia[b][:len(ei)], ei)
+    engine.sparse_drop("a")
+    engine.sparse_drop("f")
+
+
 def test_full_size_sparse_kernels_agree():
     """C4 sparse stage at full size: 10 M documents, 50 k-term Zipf vocabulary, batch 1024, top-100."""
     import torch
