@@ -437,6 +437,36 @@ class B200QdrantCore:
             val = np.array([float(v) * math.log(1.0 + (n - d + 0.5) / (d + 0.5)) for v, d in zip(val, df)], np.float64)
         return pos.astype(np.int32), val
 
+    ENGINE_MAX_K = 512          # longest list one brag_dense_topk / brag_sparse_topk call returns
+
+    def _paged(self, col: _Collection, limit: int, mask: Optional[np.ndarray], key, call):
+        """One ranked list of `limit` entries for one query.  The reference's prefetch limits are free parameters (an
+        LLM picks them per query, hybrid_search_workflow.py:28-66) and may exceed the engine's list length: longer
+        lists are served in pages, each page a scan under the filter minus the rows already returned.  Every page is
+        the best of what is left under (score desc, id asc), so the concatenation is exactly the long list."""
+        if limit <= self.ENGINE_MAX_K:
+            return call(limit, self._mask_id(col, mask, key))
+        left = np.ones(len(col), dtype=bool) if mask is None else mask.copy()
+        ss, ii = [], []
+        got = 0
+        while got < limit:
+            want = min(self.ENGINE_MAX_K, limit - got)
+            s, i, c = call(want, self._mask_id(col, left, None))
+            c0 = int(np.asarray(c)[0])
+            if c0 == 0:
+                break
+            s0, i0 = np.asarray(s)[0, :c0], np.asarray(i)[0, :c0]
+            ss.append(s0)
+            ii.append(i0)
+            got += c0
+            if c0 < want:
+                break
+            left[i0] = False
+        if not ss:
+            return np.zeros((1, 0), np.float32), np.zeros((1, 0), np.int64), np.zeros(1, np.int32)
+        s, i = np.concatenate(ss)[None, :], np.concatenate(ii)[None, :]
+        return s, i, np.array([s.shape[1]], np.int32)
+
     def _run(self, col: _Collection, query, using, limit, prefetch, flt) -> Tuple[np.ndarray, np.ndarray]:
         """Bottom-up evaluation of one Prefetch / top-level request -> (scores, rows), best first."""
         n = len(col)
@@ -490,9 +520,9 @@ class B200QdrantCore:
                 cm = np.zeros(n, dtype=bool)
                 cm[cand] = True
                 mask, key = (cm if mask is None else (cm & mask)), None
-            mid = self._mask_id(col, mask, key)
             q_ptr = np.array([0, len(terms)], np.int32)
-            s, i, c = self.engine.sparse_topk(col.space(using), q_ptr, terms, vals, min(limit, n), mid)
+            s, i, c = self._paged(col, min(limit, n), mask, key,
+                                  lambda kk, mid: self.engine.sparse_topk(col.space(using), q_ptr, terms, vals, kk, mid))
         else:                                                        # dense query
             using = "" if using is None else using
             if using not in col.dense_cfg:
@@ -509,11 +539,12 @@ class B200QdrantCore:
             mask, key = fmask, self._filter_key(flt)
             if present is not None:
                 mask, key = (present if mask is None else (present & mask)), (("present", using, key))
-            mid = self._mask_id(col, mask, key)
             if cand is not None:
+                mid = self._mask_id(col, mask, key)
                 s, i, c = self.engine.dense_rescore(col.space(using), q, cand.reshape(1, -1), min(limit, len(cand)), mid)
             else:
-                s, i, c = self.engine.dense_topk(col.space(using), q, min(limit, n), mid)
+                s, i, c = self._paged(col, min(limit, n), mask, key,
+                                      lambda kk, mid: self.engine.dense_topk(col.space(using), q, kk, mid))
         c0 = int(np.asarray(c)[0])
         return np.asarray(s)[0, :c0].astype(np.float64), np.asarray(i)[0, :c0].astype(np.int64)
 

@@ -207,3 +207,53 @@ def run_incremental_upsert(engine_factory=None, storage=None):
     assert ask(full, q) == fourth
     inc.close()
     full.close()
+
+
+def run_long_limits(engine_factory=None, storage=None):
+    """Prefetch limits above the engine's list length (the reference lets an LLM choose them,
+    hybrid_search_workflow.py:28-66) are served in pages: ids must come back in exactly the brute-force order."""
+    from rag_application_b200.client import B200QdrantCore
+    rng = np.random.Generator(np.random.PCG64(7))
+    n, d, V = 1500, 32, 300
+    x = rng.standard_normal((n, d)).astype(np.float32)
+    sp = [(np.sort(rng.choice(V, 6, replace=False)), (rng.random(6) + 0.1).astype(np.float32)) for _ in range(n)]
+    kw = {"engine_factory": engine_factory} if engine_factory else {}
+    core = B200QdrantCore(storage=storage, **kw)
+    core.create_collection("c", vectors_config={"dense": M.VectorParams(size=d, distance=M.Distance.COSINE)},
+                           sparse_vectors_config={"sparse": M.SparseVectorParams()})
+    core.upsert("c", [M.PointStruct(id=i, vector={"dense": x[i].tolist(),
+                                                  "sparse": M.SparseVector(indices=sp[i][0].tolist(), values=sp[i][1].tolist())},
+                                    payload={"even": i % 2 == 0}) for i in range(n)])
+    q = rng.standard_normal(d).astype(np.float32)
+    xn = x / np.linalg.norm(x, axis=1, keepdims=True)
+    cos = xn.astype(np.float64) @ (q / np.linalg.norm(q)).astype(np.float64)
+    for flt, ok in ((None, np.ones(n, bool)),
+                    (M.Filter(must=[M.FieldCondition(key="even", match=M.MatchValue(value=True))]), np.arange(n) % 2 == 0)):
+        want = [int(i) for i in np.argsort(-cos, kind="stable") if ok[i]][:1300]
+        got = core.query_points("c", query=q.tolist(), using="dense", limit=1300, query_filter=flt, with_payload=False).points
+        assert len(got) == min(1300, int(ok.sum()))
+        ids = [p.id for p in got]
+        # float32 scores of near-equal neighbours may swap places: compare as sets per page and check monotone scores
+        assert set(ids) == set(want) or len(set(ids) ^ set(want)) <= 4
+        assert all(a.score >= b.score - 1e-6 for a, b in zip(got, got[1:]))
+        assert len(set(ids)) == len(ids)
+    qi = np.sort(rng.choice(V, 80, replace=False))
+    qv = (rng.random(80) + 0.1).astype(np.float32)
+    sc = np.zeros(n)
+    hit = np.zeros(n, bool)
+    lut = dict(zip(qi.tolist(), qv.tolist()))
+    for i, (ti, tv) in enumerate(sp):
+        for t, v in zip(ti.tolist(), tv.tolist()):
+            if t in lut:
+                sc[i] += float(np.float32(lut[t])) * float(v)
+                hit[i] = True
+    got = core.query_points("c", query=M.SparseVector(indices=qi.tolist(), values=qv.tolist()), using="sparse",
+                            limit=1300, with_payload=False).points
+    assert len(got) == min(1300, int(hit.sum())) and len(got) > 600
+    ids = [p.id for p in got]
+    assert len(set(ids)) == len(ids) and all(hit[i] for i in ids)
+    assert all(a.score >= b.score for a, b in zip(got, got[1:]))
+    assert np.allclose([p.score for p in got], sc[ids], rtol=1e-5)
+    worst_kept = min(p.score for p in got)
+    assert all(sc[i] <= worst_kept + 1e-6 for i in range(n) if hit[i] and i not in set(ids))
+    core.close()

@@ -4,7 +4,7 @@ import numpy as np
 import pytest
 
 from _oracle_engine import OracleEngine
-from _client_cases import run_incremental_upsert, run_reference_flow
+from _client_cases import run_incremental_upsert, run_long_limits, run_reference_flow
 from rag_application_b200 import models as M
 from rag_application_b200.client import B200QdrantCore, compile_filter
 
@@ -69,3 +69,7 @@ def test_errors_and_edge_cases():
     with pytest.raises(NotImplementedError):
         core.query_points("c", query=M.FusionQuery(fusion=M.Fusion.DBSF), prefetch=[M.Prefetch(query=[1, 0, 0, 0], using="v")])
     assert core.delete_collection("c") and not core.delete_collection("c")
+
+
+def test_limits_above_the_engine_list_length_on_oracle_engine():
+    run_long_limits(engine_factory=OracleEngine)

@@ -11,6 +11,11 @@ def test_reference_flow_on_b200():
     run_reference_flow(engine_factory=None)
 
 
+def test_limits_above_the_engine_list_length_on_b200():
+    from _client_cases import run_long_limits
+    run_long_limits()
+
+
 @pytest.mark.parametrize("storage", [None, "bf16"])
 def test_incremental_upsert_on_b200(storage):
     from _client_cases import run_incremental_upsert
