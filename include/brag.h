@@ -110,7 +110,7 @@ int brag_sparse_df(brag_engine* e, const char* name, int64_t* df_host, int64_t n
 
 /* Reciprocal rank fusion: Prefetch(prefetch=[...], query=FusionQuery(RRF))
  * (qdrant_handler.py:357-360).  ids = [L, B, kmax], counts = [L, B]; score = sum 1/(2+rank)
- * in float64; out_scores float64 [B, limit]. */
+ * in float64; out_scores float64 [B, limit].  L <= 16, L * kmax <= 8192, limit <= 8192. */
 int brag_rrf(brag_engine* e, const int64_t* ids, const int32_t* counts, int32_t L, int32_t B,
              int32_t kmax, int32_t limit, int32_t tie_mode, double* out_scores,
              int64_t* out_ids, int32_t* out_counts, int32_t on_device, void* stream);

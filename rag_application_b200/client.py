@@ -438,6 +438,7 @@ class B200QdrantCore:
         return pos.astype(np.int32), val
 
     ENGINE_MAX_K = 512          # longest list one brag_dense_topk / brag_sparse_topk call returns
+    ENGINE_MAX_CAND = 8192      # candidates (and results) of one brag_dense_rescore call
 
     def _paged(self, col: _Collection, limit: int, mask: Optional[np.ndarray], key, call):
         """One ranked list of `limit` entries for one query.  The reference's prefetch limits are free parameters (an
@@ -541,7 +542,21 @@ class B200QdrantCore:
                 mask, key = (present if mask is None else (present & mask)), (("present", using, key))
             if cand is not None:
                 mid = self._mask_id(col, mask, key)
-                s, i, c = self.engine.dense_rescore(col.space(using), q, cand.reshape(1, -1), min(limit, len(cand)), mid)
+                if len(cand) <= self.ENGINE_MAX_CAND:
+                    s, i, c = self.engine.dense_rescore(col.space(using), q, cand.reshape(1, -1), min(limit, len(cand)), mid)
+                else:
+                    # more candidates than one brag_dense_rescore call takes: score them in slices (every slice
+                    # returns all of its passing candidates with exact scores) and order the union by (score desc, id)
+                    ss, ii = [], []
+                    for a in range(0, len(cand), self.ENGINE_MAX_CAND):
+                        part = cand[a:a + self.ENGINE_MAX_CAND]
+                        s, i, c = self.engine.dense_rescore(col.space(using), q, part.reshape(1, -1), len(part), mid)
+                        c0 = int(np.asarray(c)[0])
+                        ss.append(np.asarray(s)[0, :c0])
+                        ii.append(np.asarray(i)[0, :c0])
+                    s, i = np.concatenate(ss), np.concatenate(ii)
+                    o = np.lexsort((i, -s.astype(np.float64)))[:limit]
+                    s, i, c = s[o][None, :], i[o][None, :], np.array([len(o)], np.int32)
             else:
                 s, i, c = self._paged(col, min(limit, n), mask, key,
                                       lambda kk, mid: self.engine.dense_topk(col.space(using), q, kk, mid))

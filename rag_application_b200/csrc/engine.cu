@@ -967,8 +967,8 @@ int brag_rrf(brag_engine* e, const int64_t* ids, const int32_t* counts, int32_t 
              int32_t on_device, void* stream) {
     return guarded([&] {
         REQUIRE(e && ids && counts && out_scores && out_ids && out_counts, "brag_rrf: NULL argument");
-        REQUIRE(L >= 1 && L <= 16 && B >= 1 && kmax >= 1 && limit >= 1 && (int64_t)L * kmax <= 4096 && limit <= 4096,
-                "brag_rrf: need 1 <= L <= 16, L*kmax <= 4096, limit <= 4096");
+        REQUIRE(L >= 1 && L <= 16 && B >= 1 && kmax >= 1 && limit >= 1 && (int64_t)L * kmax <= 8192 && limit <= 8192,
+                "brag_rrf: need 1 <= L <= 16, L*kmax <= 8192, limit <= 8192");
         use_device(e);
         cudaStream_t st = (cudaStream_t)stream;
         StageTimer t(e, 4, st);

@@ -278,7 +278,7 @@ struct RrfEntry {
 };
 
 constexpr int RRF_THREADS = 256;
-constexpr int RRF_MAX = 4096;
+constexpr int RRF_MAX = 8192;          // 8192 * (16 + 12) bytes = 224 KB of the 227 KB a CTA may use
 
 __global__ void __launch_bounds__(RRF_THREADS)
 rrf_kernel(const int64_t* __restrict__ ids, const int32_t* __restrict__ counts, int L, int B, int kmax,

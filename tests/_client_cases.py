@@ -237,8 +237,25 @@ def run_long_limits(engine_factory=None, storage=None):
         assert set(ids) == set(want) or len(set(ids) ^ set(want)) <= 4
         assert all(a.score >= b.score - 1e-6 for a, b in zip(got, got[1:]))
         assert len(set(ids)) == len(ids)
+    # nested prefetch whose inner list is longer than one page, fused with a long sparse list (RRF over 2 x 700 entries)
+    inner = M.Prefetch(query=q.tolist(), using="dense", limit=700)
+    nested = core.query_points("c", prefetch=[inner], query=(-q).tolist(), using="dense", limit=650, with_payload=False).points
+    top700 = [int(i) for i in np.argsort(-cos, kind="stable")][:700]
+    assert len(nested) == 650 and set(p.id for p in nested) <= set(top700)
+    assert all(a.score >= b.score - 1e-6 for a, b in zip(nested, nested[1:]))
+    worst = sorted(top700, key=lambda i: cos[i])[:600]          # re-ranked by -q: the worst of the 700 come first
+    assert len(set(p.id for p in nested[:600]) ^ set(worst)) <= 4
+    core.ENGINE_MAX_CAND = 256                                   # force the sliced re-score of the 700 candidates
+    sliced = core.query_points("c", prefetch=[inner], query=(-q).tolist(), using="dense", limit=650, with_payload=False).points
+    del core.ENGINE_MAX_CAND
+    assert [p.id for p in sliced] == [p.id for p in nested] and [p.score for p in sliced] == [p.score for p in nested]
     qi = np.sort(rng.choice(V, 80, replace=False))
     qv = (rng.random(80) + 0.1).astype(np.float32)
+    fused = core.query_points("c", prefetch=[inner, M.Prefetch(query=M.SparseVector(indices=qi.tolist(), values=qv.tolist()),
+                                                               using="sparse", limit=700)],
+                              query=M.FusionQuery(fusion=M.Fusion.RRF), limit=900, with_payload=False).points
+    assert len(fused) == 900 and len(set(p.id for p in fused)) == 900
+    assert all(a.score >= b.score for a, b in zip(fused, fused[1:]))
     sc = np.zeros(n)
     hit = np.zeros(n, bool)
     lut = dict(zip(qi.tolist(), qv.tolist()))
