@@ -607,6 +607,9 @@ class B200QdrantCore:
             fmask = None if query_filter is None else compile_filter(query_filter, col.payloads, col.ids)
             mid = self._mask_id(col, fmask, self._filter_key(query_filter))
             k = min(int(limit), len(col))
+            if k > self.ENGINE_MAX_K:
+                raise ValueError(f"hybrid_search_batch: limit {k} exceeds the engine's {self.ENGINE_MAX_K}-entry lists; "
+                                 "use query_points (paged) for longer lists")
             s, i, c = self.engine.hybrid_topk(col.space(using_dense), col.space(using_sparse), Q,
                                               np.asarray(ptr, np.int32),
                                               np.concatenate(terms) if terms else np.zeros(0, np.int32),
