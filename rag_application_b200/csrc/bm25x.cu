@@ -664,6 +664,9 @@ Bm25Plan bm25x_plan(int64_t n_docs, int B, int k_sel, int max_terms, int num_sms
     const int nt = (ns + subs - 1) / subs;
     p.workers = (int)std::min<size_t>(BX_MAX_WORKERS, BX_SMEM_MAX / bx_warp_bytes(bx_maxt(max_terms), subs, bx_lcap(k_sel)));
     p.workers = std::max(1, std::min(p.workers, nt));
+    // BRAG_BX_WORKERS (experiments): fewer worker warps per CTA, e.g. to run beside another resident kernel
+    static const int wcap = [] { const char* e = getenv("BRAG_BX_WORKERS"); return e ? atoi(e) : 0; }();
+    if (wcap > 0) p.workers = std::min(p.workers, wcap);
     const int resident = num_sms;
     // seed launch: BRAG_BX_SEED tiles per query (default 2; measured at C4 / a 1.25 M-document shard: 8.6 / 2.48 ms
     // without, 8.0 / 1.88 ms with), when the corpus has tiles to spare
