@@ -515,6 +515,8 @@ bool dense_umma_supported(int dtype, int d, int64_t n) {
     return (dtype == 1 || dtype == 2) && d % UM_BK == 0 && d >= UM_BK && n >= 1;
 }
 
+int dense_umma_max_ksel() { return UM_CAP - 64; }
+
 cudaError_t dense_umma_plan(int64_t n, int d, int B, int k_sel, int num_sms, UmmaPlan* plan) {
     if (k_sel > UM_CAP - 64) return cudaErrorInvalidValue;
     (void)d;

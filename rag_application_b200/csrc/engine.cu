@@ -392,7 +392,8 @@ void dense_topk_dev(brag_engine* e, DenseSpace& s, const float* Q, int B, int k,
                     float* out_scores, int64_t* out_ids, int32_t* out_counts, cudaStream_t st) {
     REQUIRE(B >= 1 && k >= 1 && k <= 512, "dense_topk: need B >= 1 and 1 <= k <= 512");
     const int k_sel = k_select(k);
-    const int path = pick_path(e, s, B);
+    int path = pick_path(e, s, B);
+    if (path == 1 && k_sel > brag::dense_umma_max_ksel()) path = 0;     // k > 416: the GEMV scan holds longer lists
     float* qs = e->qs.as<float>((size_t)B * s.d);
     uint64_t* cand = e->keys1.as<uint64_t>((size_t)B * k_sel);
     uint64_t* cand2 = e->keys2.as<uint64_t>((size_t)B * k_sel);

@@ -19,6 +19,8 @@ struct UmmaPlan {
     size_t scratch_bytes;   // lists | counts | per-query bounds | coarse + fine score histograms
 };
 bool dense_umma_supported(int dtype, int d, int64_t n);
+// longest candidate list (k + selection margin) the tcgen05 scan keeps per (CTA, query); longer ones take the GEMV scan
+int dense_umma_max_ksel();
 cudaError_t dense_umma_plan(int64_t n, int d, int B, int k_sel, int num_sms, UmmaPlan* plan);
 // X16: [n, d] f16/bf16; Q16: [Bpad, d] same dtype (Bpad = n_qblocks*128, zero padded).
 // cand: [B][k_sel] keys, best first (0 = empty slot).

@@ -161,6 +161,49 @@ def test_dense_filter_compacted_copy(engine, B):
             check_dense(xs, O.round_storage(q[b], "bf16"), k, s[b], i[b], int(c[b]), mask=mask)
 
 
+@pytest.mark.parametrize("k", [416, 417, 512])
+@pytest.mark.parametrize("dtype,d", [("bf16", 64), ("f16", 768)])
+def test_dense_longest_lists_on_16bit_storage(engine, k, dtype, d):
+    """k up to 512 on 16-bit spaces: lists longer than the tcgen05 scan's per-CTA candidate slots (k > 416) are
+    scanned by the GEMV kernel; same oracle either way (the paged long limits of client.py ask for k = 512)."""
+    n = 5000
+    x = synth.dense_corpus(n, d, seed=81, clustered=True)
+    q = synth.dense_queries(x, 3, seed=82)
+    engine.dense_set("x", x, dtype)
+    xs = O.round_storage(x, dtype)
+    mask = synth.random_mask(n, 0.5, seed=83)
+    engine.mask_set(4, mask)
+    for mid, m in ((0, None), (4, mask)):
+        s, i, c = engine.dense_topk("x", q, k, mask_id=mid)
+        for b in range(3):
+            check_dense(xs, O.round_storage(q[b], dtype), k, s[b], i[b], int(c[b]), mask=m)
+
+
+@pytest.mark.parametrize("k", [300, 512])
+def test_sparse_and_hybrid_longest_lists(engine, k):
+    """k up to 512 through the sparse scan (auto path) and the fused hybrid call, against the oracle."""
+    n, d, B = 30000, 128, 5
+    ptr, doc, w, _ = synth.zipf_corpus(n, 2000, 60, seed=91)
+    csr = _oracle_csr(ptr, doc, w, n)
+    engine.sparse_set_csr("s", ptr, doc, w, n)
+    q_ptr, q_terms, q_vals = synth.sparse_queries(ptr, doc, n, B, 8, "zipf", seed=92, skip_top=8)
+    s, i, c = engine.sparse_topk("s", q_ptr, q_terms, q_vals, k)
+    for b in range(B):
+        es, ei = O.sparse_topk(csr, q_terms[q_ptr[b]:q_ptr[b + 1]], q_vals[q_ptr[b]:q_ptr[b + 1]], k)
+        assert int(c[b]) == len(ei) and np.array_equal(i[b][:len(ei)], ei)
+        assert np.array_equal(s[b][:len(ei)].view(np.uint32), es.view(np.uint32))
+    x = synth.dense_corpus(n, d, seed=93, clustered=True)
+    q = synth.dense_queries(x, B, seed=94)
+    engine.dense_set("x", x, "bf16")
+    col = O.OracleCollection()
+    col.add_dense("dense", x, "dot", "bf16")
+    col.add_sparse("sparse", csr)
+    hs, hi, hc = engine.hybrid_topk("x", "s", q, q_ptr, q_terms, q_vals, k)
+    for b in range(B):
+        es, ei = O.hybrid_simple(col, q[b], q_terms[q_ptr[b]:q_ptr[b + 1]], q_vals[q_ptr[b]:q_ptr[b + 1]], k)
+        assert int(hc[b]) == len(ei) and set(hi[b][:len(ei)].tolist()) == set(ei.tolist())
+
+
 def test_dense_exact_ties_broken_by_id(engine):
     """Duplicate rows score identically: the lower id must win (north_star: ties broken by id)."""
     x = synth.dense_corpus(512, 64, seed=1)
