@@ -108,6 +108,7 @@ struct SparseSpace {
 struct MaskBuf {
     uint32_t* bits = nullptr;
     int64_t nbits = 0;
+    size_t cap = 0;                // words allocated (the buffer is reused by later brag_mask_set calls that fit)
     uint64_t version = 0;          // bumped by every brag_mask_set: invalidates compacted copies
 };
 
@@ -870,11 +871,16 @@ int brag_mask_set(brag_engine* e, int32_t mask_id, const uint32_t* bits, int64_t
         use_device(e);
         MaskBuf& m = e->masks[mask_id];
         const size_t words = (size_t)((nbits + 31) / 32);
-        if (m.bits) { CK(cudaDeviceSynchronize()); CK(cudaFree(m.bits)); m.bits = nullptr; }
-        // padded so a warp's mask-word read past the last group stays in bounds
-        CK(cudaMalloc(&m.bits, (words + 512) * sizeof(uint32_t)));
-        CK(cudaMemset(m.bits, 0, (words + 512) * sizeof(uint32_t)));
+        // padded (zeros) so a warp's mask-word read past the last group stays in bounds; a buffer that fits is reused:
+        // the plan executor of client.py sets several candidate / page masks per query
+        if (m.bits) CK(cudaDeviceSynchronize());
+        if (m.cap < words + 512) {
+            if (m.bits) { CK(cudaFree(m.bits)); m.bits = nullptr; m.cap = 0; }
+            CK(cudaMalloc(&m.bits, (words + 512) * sizeof(uint32_t)));
+            m.cap = words + 512;
+        }
         CK(cudaMemcpy(m.bits, bits, words * sizeof(uint32_t), on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice));
+        CK(cudaMemset(m.bits + words, 0, (m.cap - words) * sizeof(uint32_t)));
         m.nbits = nbits;
         m.version = ++e->mask_epoch;
     });
