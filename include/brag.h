@@ -159,6 +159,8 @@ int brag_force_sparse_path(brag_engine* e, int32_t path);
  * filter from then on (results identical).  Only calls with B >= 32 count towards `queries` (single queries are
  * latency-bound either way).  Default 256; 0 = build on first use; < 0 = never (an index already built is bypassed). */
 int brag_sparse_compact_after(brag_engine* e, int64_t queries);
+/* Which filter the space's compacted index was built for (0 = none built) and how many documents it holds. */
+int brag_sparse_compact_info(brag_engine* e, const char* name, int32_t* mask_id, int64_t* n_docs);
 
 /* ---- the sparse encoder the reference runs before it calls the vector store
  * (fastembed SparseTextEmbedding("Qdrant/bm25").embed, embedding_handler.py:41,123-138).  Host-only code.

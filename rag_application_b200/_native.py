@@ -42,6 +42,7 @@ PROTOTYPES = {
     "brag_force_dense_path": (C.c_int, [c_p, i32]),
     "brag_force_sparse_path": (C.c_int, [c_p, i32]),
     "brag_sparse_compact_after": (C.c_int, [c_p, i64]),
+    "brag_sparse_compact_info": (C.c_int, [c_p, C.c_char_p, c_p, c_p]),
     "brag_rerank_meanpool": (C.c_int, [c_p, c_p, i32, c_p, i32, i32, i32, c_p, c_p, i32, c_p]),
     "brag_sparse_append": (C.c_int, [c_p, C.c_char_p, c_p, c_p, c_p, c_p, i64, i64]),
     "brag_bm25_encode": (C.c_int, [C.c_char_p, c_p, i32, C.c_double, C.c_double, C.c_double, i32, i32, c_p, c_p, c_p]),

@@ -331,6 +331,8 @@ bool ensure_compact(brag_engine* e, DenseSpace& s, int mask_id, const uint32_t* 
 // cost) and kept until the filter or the space changes.
 bool ensure_sparse_compact(brag_engine* e, SparseSpace& s, int mask_id, const uint32_t* mask, int B, cudaStream_t st) {
     const uint64_t version = e->masks[mask_id].version;
+    // single queries under other filters (candidate and page masks of the plan executor) neither count nor evict
+    if ((s.cp_mask_id != mask_id || s.cp_version != version) && B < 32 && e->sparse_compact_after != 0) return false;
     if (s.cp_mask_id != mask_id || s.cp_version != version) {
         if (s.cp) { CK(cudaDeviceSynchronize()); free_sparse(*s.cp); delete s.cp; s.cp = nullptr; }
         s.cp_mask_id = mask_id;
@@ -1159,6 +1161,16 @@ int brag_sparse_compact_after(brag_engine* e, int64_t queries) {
     return guarded([&] {
         REQUIRE(e, "brag_sparse_compact_after: NULL engine");
         e->sparse_compact_after = queries;
+    });
+}
+
+int brag_sparse_compact_info(brag_engine* e, const char* name, int32_t* mask_id, int64_t* n_docs) {
+    return guarded([&] {
+        REQUIRE(e && name && mask_id && n_docs, "brag_sparse_compact_info: NULL argument");
+        SparseSpace& s = sparse_space(e, name);
+        const bool built = s.cp != nullptr && s.cp_state == 1;
+        *mask_id = built ? s.cp_mask_id : 0;
+        *n_docs = built ? s.cp->n_docs : 0;
     });
 }
 

@@ -294,5 +294,11 @@ class Engine:
         """Queries one filter serves before the index of its passing documents is built (0: first use, < 0: never)."""
         _native.check(self._lib.brag_sparse_compact_after(self._h, int(queries)))
 
+    def sparse_compact_info(self, name: str):
+        """(mask_id the compacted index of this space was built for or 0, documents it holds)."""
+        mid, nd = C.c_int32(0), C.c_int64(0)
+        _native.check(self._lib.brag_sparse_compact_info(self._h, name.encode(), C.byref(mid), C.byref(nd)))
+        return int(mid.value), int(nd.value)
+
     def force_dense_path(self, path: Optional[str]):
         _native.check(self._lib.brag_force_dense_path(self._h, {None: -1, "gemv": 0, "tcgen05": 1, "tcgen05_full": 2}[path]))

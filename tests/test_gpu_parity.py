@@ -481,6 +481,41 @@ def test_sparse_append_equals_a_fresh_upload(engine):
     engine.sparse_drop("f")
 
 
+def test_sparse_compacted_index_lifecycle(engine):
+    """Default policy: the index of a filter's passing documents appears once that filter has served 256 batched
+    queries; single queries under other filters (the plan executor's candidate / page masks) neither count nor evict
+    it; a batch under another filter, or new contents under the same mask_id, start over.  Answers stay exact."""
+    n_docs, k, B = 60000, 20, 40
+    ptr, doc, w, _ = synth.zipf_corpus(n_docs, 2000, 50, seed=101)
+    csr = _oracle_csr(ptr, doc, w, n_docs)
+    engine.sparse_set_csr("s", ptr, doc, w, n_docs)
+    q_ptr, q_terms, q_vals = synth.sparse_queries(ptr, doc, n_docs, B, 8, "zipf", seed=102, skip_top=8)
+    m7, m8 = synth.random_mask(n_docs, 0.2, seed=103), synth.random_mask(n_docs, 0.3, seed=104)
+    engine.mask_set(7, m7)
+    engine.mask_set(8, m8)
+
+    def exact(out, mask, nq):
+        s, i, c = out
+        for b in range(nq):
+            es, ei = O.sparse_topk(csr, q_terms[q_ptr[b]:q_ptr[b + 1]], q_vals[q_ptr[b]:q_ptr[b + 1]], k, mask=mask)
+            assert int(c[b]) == len(ei) and np.array_equal(i[b][:len(ei)], ei)
+            assert np.array_equal(s[b][:len(ei)].view(np.uint32), es.view(np.uint32))
+
+    for call in range(8):
+        assert engine.sparse_compact_info("s")[0] == 0, call           # 7 x 40 queries counted, none built yet
+        out = engine.sparse_topk("s", q_ptr, q_terms, q_vals, k, mask_id=7)
+    assert engine.sparse_compact_info("s") == (7, int(m7.sum()))
+    exact(out, m7, 6)
+    one = engine.sparse_topk("s", q_ptr[:2], q_terms[:q_ptr[1]], q_vals[:q_ptr[1]], k, mask_id=8)
+    exact(one, m8, 1)
+    assert engine.sparse_compact_info("s")[0] == 7                      # a single query under another filter: kept
+    exact(engine.sparse_topk("s", q_ptr, q_terms, q_vals, k, mask_id=7), m7, 6)
+    exact(engine.sparse_topk("s", q_ptr, q_terms, q_vals, k, mask_id=8), m8, 6)
+    assert engine.sparse_compact_info("s")[0] == 0                      # a batch under another filter starts over
+    engine.mask_set(7, m8)                                              # same id, new contents
+    exact(engine.sparse_topk("s", q_ptr, q_terms, q_vals, k, mask_id=7), m8, 6)
+
+
 def test_sparse_nonfinite_weights_use_the_scatter_scan(engine):
     """A NaN/Inf weight makes per-term bounds meaningless: the space falls back to the exhaustive kernel."""
     ptr, doc, w, _ = synth.zipf_corpus(2000, 300, 30, seed=3)
