@@ -473,8 +473,9 @@ bm25x_scan_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict_
             }
             __syncwarp();
 
-            // ---- phase 2: per-word ranks + bit-sliced count of the maps (lane owns words WPL*lane ..);
-            //      two terms share one warp scan (13-bit counts packed in the halves of a register)
+            // ---- phase 2: bit-sliced count of the maps (lane owns words WPL*lane ..), two terms per step:
+            //      count += present_a + high_a + present_b + high_b -- two full adders on the ones plane, one on the
+            //      twos plane, then the single carry ripples up through half adders
             uint32_t cn[PLANES][WPL];
 #pragma unroll
             for (int p = 0; p < PLANES; ++p)
@@ -486,53 +487,27 @@ bm25x_scan_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict_
                 const bool two = a != 0u;
                 const int lb = two ? __ffs(a) - 1 : la;
                 a &= a - 1;
-                uint32_t wa[WPL], wb[WPL], ha[WPL], hb[WPL];
 #pragma unroll
                 for (int w = 0; w < WPL; w += 2) {
                     const uint2 va = *reinterpret_cast<const uint2*>(bm + la * WORDS + WPL * lane + w);
                     const uint2 vb = *reinterpret_cast<const uint2*>(bm + lb * WORDS + WPL * lane + w);
                     const uint2 xa = *reinterpret_cast<const uint2*>(bmh + la * WORDS + WPL * lane + w);
                     const uint2 xb = *reinterpret_cast<const uint2*>(bmh + lb * WORDS + WPL * lane + w);
-                    wa[w] = va.x; wa[w + 1] = va.y;
-                    ha[w] = xa.x; ha[w + 1] = xa.y;
-                    wb[w] = two ? vb.x : 0u; wb[w + 1] = two ? vb.y : 0u;
-                    hb[w] = two ? xb.x : 0u; hb[w + 1] = two ? xb.y : 0u;
-                }
-                uint32_t loc[WPL];                       // packed exclusive prefix inside the lane
-                uint32_t own = 0u;
+                    const uint32_t wa[2] = {va.x, va.y}, ha[2] = {xa.x, xa.y};
+                    const uint32_t wb[2] = {two ? vb.x : 0u, two ? vb.y : 0u}, hb[2] = {two ? xb.x : 0u, two ? xb.y : 0u};
 #pragma unroll
-                for (int w = 0; w < WPL; ++w) {
-                    loc[w] = own;
-                    own += (uint32_t)__popc(wa[w]) | ((uint32_t)__popc(wb[w]) << 16);
-                }
-                uint32_t inc = own;
+                    for (int h = 0; h < 2; ++h) {
+                        uint32_t c = cn[0][w + h];
+                        const uint32_t ta = (c & wa[h]) | (c & ha[h]) | (wa[h] & ha[h]);
+                        c = c ^ wa[h] ^ ha[h];
+                        const uint32_t tb = (c & wb[h]) | (c & hb[h]) | (wb[h] & hb[h]);
+                        cn[0][w + h] = c ^ wb[h] ^ hb[h];
+                        const uint32_t d = cn[1][w + h];
+                        uint32_t k = (d & ta) | (d & tb) | (ta & tb);
+                        cn[1][w + h] = d ^ ta ^ tb;
 #pragma unroll
-                for (int off = 1; off < 32; off <<= 1) {
-                    const uint32_t o = __shfl_up_sync(0xFFFFFFFFu, inc, off);
-                    if (lane >= off) inc += o;
-                }
-                const uint32_t ex = inc - own;
-                __syncwarp();       // every lane has read its words of bmh[la], bmh[lb] before the ranks overwrite them
-#pragma unroll
-                for (int w = 0; w < WPL; w += 2) {
-                    const uint32_t r0 = ex + loc[w], r1 = ex + loc[w + 1];
-                    *reinterpret_cast<uint32_t*>(pre + la * 2 * WORDS + WPL * lane + w) = (r0 & 0xFFFFu) | (r1 << 16);
-                    if (two) *reinterpret_cast<uint32_t*>(pre + lb * 2 * WORDS + WPL * lane + w) = (r0 >> 16) | (r1 & 0xFFFF0000u);
-                }
-                // count += present_a + high_a + present_b + high_b: two full adders on the ones plane, one on the
-                // twos plane, then the single carry ripples up through half adders
-#pragma unroll
-                for (int w = 0; w < WPL; ++w) {
-                    uint32_t c = cn[0][w];
-                    const uint32_t ta = (c & wa[w]) | (c & ha[w]) | (wa[w] & ha[w]);
-                    c = c ^ wa[w] ^ ha[w];
-                    const uint32_t tb = (c & wb[w]) | (c & hb[w]) | (wb[w] & hb[w]);
-                    cn[0][w] = c ^ wb[w] ^ hb[w];
-                    const uint32_t d = cn[1][w];
-                    uint32_t k = (d & ta) | (d & tb) | (ta & tb);
-                    cn[1][w] = d ^ ta ^ tb;
-#pragma unroll
-                    for (int p = 2; p < PLANES; ++p) { const uint32_t t_ = cn[p][w] & k; cn[p][w] ^= k; k = t_; }
+                        for (int p = 2; p < PLANES; ++p) { const uint32_t t_ = cn[p][w + h] & k; cn[p][w + h] ^= k; k = t_; }
+                    }
                 }
             }
             // count >= m, bit-slice compare from the top plane down; then the payload filter
@@ -567,6 +542,42 @@ bm25x_scan_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict_
             }
             const int total = __shfl_sync(0xFFFFFFFFu, pos, 31);
             pos -= own_c;
+            if (total == 0) continue;                          // nothing of this tile can reach the bound
+            // per-word ranks of the present maps (a posting's slot in its term's list = sub-tile offset + rank), only
+            // for tiles with survivors; two terms share one warp scan (13-bit counts packed in the halves of a register).
+            // The rank table overwrites the high maps, which every lane has finished reading.
+            __syncwarp();
+            for (unsigned a = active; a;) {
+                const int la = __ffs(a) - 1;
+                a &= a - 1;
+                const bool two = a != 0u;
+                const int lb = two ? __ffs(a) - 1 : la;
+                a &= a - 1;
+                uint32_t loc[WPL];                       // packed exclusive prefix inside the lane
+                uint32_t own = 0u;
+#pragma unroll
+                for (int w = 0; w < WPL; w += 2) {
+                    const uint2 va = *reinterpret_cast<const uint2*>(bm + la * WORDS + WPL * lane + w);
+                    const uint2 vb = *reinterpret_cast<const uint2*>(bm + lb * WORDS + WPL * lane + w);
+                    loc[w] = own;
+                    own += (uint32_t)__popc(va.x) | (two ? (uint32_t)__popc(vb.x) << 16 : 0u);
+                    loc[w + 1] = own;
+                    own += (uint32_t)__popc(va.y) | (two ? (uint32_t)__popc(vb.y) << 16 : 0u);
+                }
+                uint32_t inc = own;
+#pragma unroll
+                for (int off = 1; off < 32; off <<= 1) {
+                    const uint32_t o = __shfl_up_sync(0xFFFFFFFFu, inc, off);
+                    if (lane >= off) inc += o;
+                }
+                const uint32_t ex = inc - own;
+#pragma unroll
+                for (int w = 0; w < WPL; w += 2) {
+                    const uint32_t r0 = ex + loc[w], r1 = ex + loc[w + 1];
+                    *reinterpret_cast<uint32_t*>(pre + la * 2 * WORDS + WPL * lane + w) = (r0 & 0xFFFFu) | (r1 << 16);
+                    if (two) *reinterpret_cast<uint32_t*>(pre + lb * 2 * WORDS + WPL * lane + w) = (r0 >> 16) | (r1 & 0xFFFF0000u);
+                }
+            }
 #pragma unroll 1
             for (int r0 = 0; r0 < total; r0 += 32) {
                 if (*cntp > lcap - 32) {
