@@ -7,7 +7,6 @@
 #include <algorithm>
 
 #include <cub/device/device_scan.cuh>
-#include <cub/device/device_select.cuh>
 
 #include "common.cuh"
 #include "kernels.h"
@@ -77,7 +76,7 @@ constexpr int KEEP_CHUNK = 8192;
 
 __global__ void sparse_keep_count_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict__ post,
                                          int64_t V, int64_t nnz, const uint32_t* __restrict__ mask,
-                                         unsigned long long* __restrict__ cnt) {
+                                         unsigned long long* __restrict__ cnt, int64_t* __restrict__ chunk_cnt) {
     const int lane = threadIdx.x & 31;
     const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
     const int64_t nchunks = (nnz + KEEP_CHUNK - 1) / KEEP_CHUNK;
@@ -85,7 +84,7 @@ __global__ void sparse_keep_count_kernel(const int64_t* __restrict__ term_ptr, c
         const int64_t i0 = c * KEEP_CHUNK, i1 = min(nnz, i0 + (int64_t)KEEP_CHUNK);
         int64_t t = term_of_posting(term_ptr, V, i0);
         int64_t end = __ldg(term_ptr + t + 1);
-        uint32_t local = 0u;
+        uint32_t local = 0u, ctot = 0u;
         for (int64_t base = i0; base < i1; base += 128) {
             uint32_t doc[4];
             bool keep[4];
@@ -97,6 +96,7 @@ __global__ void sparse_keep_count_kernel(const int64_t* __restrict__ term_ptr, c
 #pragma unroll
             for (int u = 0; u < 4; ++u)
                 keep[u] = doc[u] != 0xFFFFFFFFu && ((__ldg(mask + (doc[u] >> 5)) >> (doc[u] & 31)) & 1u);
+            ctot += (uint32_t)keep[0] + (uint32_t)keep[1] + (uint32_t)keep[2] + (uint32_t)keep[3];
             if (base + 128 <= end) {
                 local += (uint32_t)keep[0] + (uint32_t)keep[1] + (uint32_t)keep[2] + (uint32_t)keep[3];
                 continue;
@@ -117,8 +117,49 @@ __global__ void sparse_keep_count_kernel(const int64_t* __restrict__ term_ptr, c
         }
         uint32_t tot = local;
 #pragma unroll
-        for (int o = 16; o; o >>= 1) tot += __shfl_xor_sync(0xFFFFFFFFu, tot, o);
+        for (int o = 16; o; o >>= 1) {
+            tot += __shfl_xor_sync(0xFFFFFFFFu, tot, o);
+            ctot += __shfl_xor_sync(0xFFFFFFFFu, ctot, o);
+        }
         if (lane == 0 && tot) atomicAdd(cnt + t, (unsigned long long)tot);
+        if (lane == 0) chunk_cnt[c] = (int64_t)ctot;      // kept postings of this chunk: the write pass's offsets
+    }
+}
+
+// Second pass of the selection: chunk c's kept postings go to out[chunk_off[c] ...] in their original order (a ballot
+// and a popcount per 32 postings), with the document id renumbered to its rank among the passing documents.
+__global__ void sparse_keep_write_kernel(const uint2* __restrict__ post, int64_t nnz, const uint32_t* __restrict__ mask,
+                                         const uint32_t* __restrict__ prefix, const int64_t* __restrict__ chunk_off,
+                                         uint2* __restrict__ out) {
+    const int lane = threadIdx.x & 31;
+    const unsigned below = (1u << lane) - 1u;
+    const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    const int64_t nchunks = (nnz + KEEP_CHUNK - 1) / KEEP_CHUNK;
+    for (int64_t c = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; c < nchunks; c += nwarps) {
+        const int64_t i0 = c * KEEP_CHUNK, i1 = min(nnz, i0 + (int64_t)KEEP_CHUNK);
+        int64_t at = __ldg(chunk_off + c);
+        if (__ldg(chunk_off + c + 1) == at) continue;     // nothing kept in this chunk
+        for (int64_t base = i0; base < i1; base += 128) {
+            uint2 p[4];
+            uint32_t mw[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int64_t i = base + u * 32 + lane;
+                p[u] = i < i1 ? __ldcs(post + i) : make_uint2(0xFFFFFFFFu, 0u);
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) mw[u] = p[u].x != 0xFFFFFFFFu ? __ldg(mask + (p[u].x >> 5)) : 0u;
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const bool keep = (mw[u] >> (p[u].x & 31)) & 1u;
+                const unsigned bal = __ballot_sync(0xFFFFFFFFu, keep);
+                if (keep) {
+                    const uint32_t nd = __ldg(prefix + (p[u].x >> 5)) + __popc(mw[u] & ((1u << (p[u].x & 31)) - 1u));
+                    out[at + __popc(bal & below)] = make_uint2(nd, p[u].y);
+                }
+                at += __popc(bal);
+            }
+        }
     }
 }
 
@@ -188,53 +229,44 @@ cudaError_t sparse_append_move(const int64_t* term_ptr, const uint2* post, int64
     return cudaSuccess;
 }
 
-struct KeepPosting {
-    const uint32_t* mask;
-    __device__ __forceinline__ bool operator()(const uint2& p) const { return (mask[p.x >> 5] >> (p.x & 31)) & 1u; }
-};
-
-__global__ void sparse_renumber_kernel(uint2* __restrict__ post, int64_t nnz, const uint32_t* __restrict__ mask,
-                                       const uint32_t* __restrict__ prefix) {
-    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= nnz) return;
-    const uint32_t doc = post[i].x;
-    const uint32_t w = __ldg(mask + (doc >> 5));
-    post[i].x = __ldg(prefix + (doc >> 5)) + __popc(w & ((1u << (doc & 31)) - 1u));
-}
+int64_t sparse_compact_chunks(int64_t nnz) { return (nnz + KEEP_CHUNK - 1) / KEEP_CHUNK; }
 
 size_t sparse_compact_tmp_bytes(int64_t V, int64_t nnz) {
     size_t a = 0, b = 0;
     cub::DeviceScan::ExclusiveSum(nullptr, a, (const int64_t*)nullptr, (int64_t*)nullptr, (int)(V + 1));
-    KeepPosting keep{nullptr};
-    cub::DeviceSelect::If(nullptr, b, (const uint2*)nullptr, (uint2*)nullptr, (int64_t*)nullptr, (int64_t)nnz, keep);
+    cub::DeviceScan::ExclusiveSum(nullptr, b, (const int64_t*)nullptr, (int64_t*)nullptr,
+                                  (int)(sparse_compact_chunks(nnz) + 1));
     return std::max(a, b) + 256;
 }
 
-// new_term_ptr: [V + 1] (term_ptr of the passing postings)
+// new_term_ptr: [V + 1] (term_ptr of the passing postings); chunk_off: [chunks + 1] (where each chunk of the old
+// posting array starts in the new one)
 cudaError_t sparse_compact_count(const int64_t* term_ptr, const uint2* post, int64_t V, int64_t nnz,
-                                 const uint32_t* mask, int64_t* new_term_ptr, void* tmp, size_t tmp_bytes,
-                                 cudaStream_t st) {
+                                 const uint32_t* mask, int64_t* new_term_ptr, int64_t* chunk_off, void* tmp,
+                                 size_t tmp_bytes, cudaStream_t st) {
+    const int64_t nchunks = sparse_compact_chunks(nnz);
     cudaError_t e = cudaMemsetAsync(new_term_ptr, 0, (size_t)(V + 1) * sizeof(int64_t), st);
+    if (e != cudaSuccess) return e;
+    e = cudaMemsetAsync(chunk_off, 0, (size_t)(nchunks + 1) * sizeof(int64_t), st);
     if (e != cudaSuccess) return e;
     if (nnz) {
         const int64_t blocks = std::min<int64_t>((nnz + KEEP_CHUNK * 8 - 1) / (KEEP_CHUNK * 8), 148 * 8);
         sparse_keep_count_kernel<<<(unsigned)blocks, 256, 0, st>>>(term_ptr, post, V, nnz, mask,
-                                                                  reinterpret_cast<unsigned long long*>(new_term_ptr));
+                                                                  reinterpret_cast<unsigned long long*>(new_term_ptr), chunk_off);
         e = cudaGetLastError();
         if (e != cudaSuccess) return e;
     }
-    return cub::DeviceScan::ExclusiveSum(tmp, tmp_bytes, new_term_ptr, new_term_ptr, (int)(V + 1), st);
+    e = cub::DeviceScan::ExclusiveSum(tmp, tmp_bytes, new_term_ptr, new_term_ptr, (int)(V + 1), st);
+    if (e != cudaSuccess) return e;
+    return cub::DeviceScan::ExclusiveSum(tmp, tmp_bytes, chunk_off, chunk_off, (int)(nchunks + 1), st);
 }
 
-// out: [nnz_c] passing postings with compact document ids; n_selected: device scratch (one int64)
+// out: [nnz_c] passing postings in their original order, with compact document ids
 cudaError_t sparse_compact_select(const uint2* post, int64_t nnz, const uint32_t* mask, const uint32_t* prefix,
-                                  uint2* out, int64_t nnz_c, int64_t* n_selected, void* tmp, size_t tmp_bytes,
-                                  cudaStream_t st) {
+                                  const int64_t* chunk_off, uint2* out, int64_t nnz_c, cudaStream_t st) {
     if (nnz == 0 || nnz_c == 0) return cudaSuccess;
-    KeepPosting keep{mask};
-    cudaError_t e = cub::DeviceSelect::If(tmp, tmp_bytes, post, out, n_selected, (int64_t)nnz, keep, st);
-    if (e != cudaSuccess) return e;
-    sparse_renumber_kernel<<<(unsigned)((nnz_c + 255) / 256), 256, 0, st>>>(out, nnz_c, mask, prefix);
+    const int64_t blocks = std::min<int64_t>((nnz + KEEP_CHUNK * 8 - 1) / (KEEP_CHUNK * 8), 148 * 8);
+    sparse_keep_write_kernel<<<(unsigned)blocks, 256, 0, st>>>(post, nnz, mask, prefix, chunk_off, out);
     return cudaGetLastError();
 }
 

@@ -134,7 +134,7 @@ struct brag_engine {
     // scratch (grow-only)
     DevBuf qs, q16, part, tmp_a, tmp_b, keys1, keys2, umma_scratch, work_counter, g_thr;
     DevBuf h_in[6], h_out[4];      // staging for host-pointer calls
-    DevBuf hyb_ids, hyb_counts, hyb_scores, cp_prefix, cp_tmp;
+    DevBuf hyb_ids, hyb_counts, hyb_scores, cp_prefix, cp_tmp, cp_chunks;
     std::vector<int32_t> qptr_host;
     alignas(64) unsigned char tmap_q[128];
     // profiling
@@ -362,15 +362,15 @@ bool ensure_sparse_compact(brag_engine* e, SparseSpace& s, int mask_id, const ui
         c->V = s.V;
         c->n_docs = nc;
         CK(cudaMalloc(&c->term_ptr, (size_t)(s.V + 1) * sizeof(int64_t)));
-        CK(brag::sparse_compact_count(s.term_ptr, s.post, s.V, s.nnz, mask, c->term_ptr, tmp, tmp_bytes, st));
+        int64_t* chunk_off = e->cp_chunks.as<int64_t>((size_t)brag::sparse_compact_chunks(s.nnz) + 1);
+        CK(brag::sparse_compact_count(s.term_ptr, s.post, s.V, s.nnz, mask, c->term_ptr, chunk_off, tmp, tmp_bytes, st));
         c->term_ptr_host.resize((size_t)s.V + 1);
         CK(cudaMemcpyAsync(c->term_ptr_host.data(), c->term_ptr, (size_t)(s.V + 1) * sizeof(int64_t),
                            cudaMemcpyDeviceToHost, st));
         CK(cudaStreamSynchronize(st));
         c->nnz = c->term_ptr_host[(size_t)s.V];
         CK(cudaMalloc(&c->post, std::max<size_t>((size_t)c->nnz, 1) * sizeof(uint2)));
-        int64_t* n_sel = reinterpret_cast<int64_t*>(reinterpret_cast<uint8_t*>(tmp) + ((tmp_bytes + 7) / 8) * 8);
-        CK(brag::sparse_compact_select(s.post, s.nnz, mask, prefix, c->post, c->nnz, n_sel, tmp, tmp_bytes, st));
+        CK(brag::sparse_compact_select(s.post, s.nnz, mask, prefix, chunk_off, c->post, c->nnz, st));
         if (s.cp_rowmap) { CK(cudaFree(s.cp_rowmap)); s.cp_rowmap = nullptr; }
         CK(cudaMalloc(&s.cp_rowmap, (size_t)nc * sizeof(uint32_t)));
         CK(brag::compact_rowmap(mask, s.n_docs, prefix, s.cp_rowmap, st));
@@ -609,7 +609,7 @@ int brag_destroy(brag_engine* e) {
         for (auto& kv : e->masks) if (kv.second.bits) cudaFree(kv.second.bits);
         DevBuf* bufs[] = {&e->qs, &e->q16, &e->part, &e->tmp_a, &e->tmp_b, &e->keys1, &e->keys2, &e->umma_scratch,
                           &e->work_counter, &e->g_thr, &e->hyb_ids, &e->hyb_counts, &e->hyb_scores, &e->cp_prefix,
-                          &e->cp_tmp};
+                          &e->cp_tmp, &e->cp_chunks};
         for (DevBuf* b : bufs) b->release();
         for (auto& b : e->h_in) b.release();
         for (auto& b : e->h_out) b.release();

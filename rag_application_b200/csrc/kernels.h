@@ -79,12 +79,12 @@ cudaError_t sparse_append_move(const int64_t* term_ptr, const uint2* post, int64
                                uint2* out, cudaStream_t st);
 // filter-compacted copy of a sparse space: postings of the passing documents, renumbered (see compact.cu)
 size_t sparse_compact_tmp_bytes(int64_t V, int64_t nnz);
+int64_t sparse_compact_chunks(int64_t nnz);
 cudaError_t sparse_compact_count(const int64_t* term_ptr, const uint2* post, int64_t V, int64_t nnz,
-                                 const uint32_t* mask, int64_t* new_term_ptr, void* tmp, size_t tmp_bytes,
-                                 cudaStream_t st);
+                                 const uint32_t* mask, int64_t* new_term_ptr, int64_t* chunk_off, void* tmp,
+                                 size_t tmp_bytes, cudaStream_t st);
 cudaError_t sparse_compact_select(const uint2* post, int64_t nnz, const uint32_t* mask, const uint32_t* prefix,
-                                  uint2* out, int64_t nnz_c, int64_t* n_selected, void* tmp, size_t tmp_bytes,
-                                  cudaStream_t st);
+                                  const int64_t* chunk_off, uint2* out, int64_t nnz_c, cudaStream_t st);
 
 // ---- bm25.cu
 constexpr int BM25_SUB = 2048;  // documents per warp sub-tile
