@@ -256,6 +256,36 @@ __device__ __forceinline__ void cp_async(void* smem_dst, const void* gsrc) {
 }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
+// A lane's WPL consecutive map words (16-byte aligned when WPL is a multiple of 4): one 128-bit shared access per
+// four words.  Two 64-bit accesses at a 16-byte lane stride are 2-way bank-conflicted (ncu: 4 wavefronts each
+// instead of 2), so the wide form halves the shared-memory wavefronts of the map reads.
+template <int WPL>
+__device__ __forceinline__ void lds_words(const uint32_t* p, uint32_t (&v)[WPL]) {
+    if constexpr (WPL % 4 == 0) {
+#pragma unroll
+        for (int w = 0; w < WPL; w += 4) {
+            const uint4 t = *reinterpret_cast<const uint4*>(p + w);
+            v[w] = t.x; v[w + 1] = t.y; v[w + 2] = t.z; v[w + 3] = t.w;
+        }
+    } else {
+#pragma unroll
+        for (int w = 0; w < WPL; w += 2) {
+            const uint2 t = *reinterpret_cast<const uint2*>(p + w);
+            v[w] = t.x; v[w + 1] = t.y;
+        }
+    }
+}
+template <int WPL>
+__device__ __forceinline__ void sts_zero_words(uint32_t* p) {
+    if constexpr (WPL % 4 == 0) {
+#pragma unroll
+        for (int w = 0; w < WPL; w += 4) *reinterpret_cast<uint4*>(p + w) = make_uint4(0u, 0u, 0u, 0u);
+    } else {
+#pragma unroll
+        for (int w = 0; w < WPL; w += 2) *reinterpret_cast<uint2*>(p + w) = make_uint2(0u, 0u);
+    }
+}
+
 template <int MAXT, int SUBS>
 __global__ void __launch_bounds__(BX_THREADS, 1)
 bm25x_scan_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict__ post,
@@ -436,11 +466,8 @@ bm25x_scan_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict_
                         for (int w = 0; w < WPL; w += 4) { cp_async<16>(dst + w, bits + at + w); cp_async<16>(dsth + w, bits_hi + at + w); }
                     }
                 } else {
-#pragma unroll
-                    for (int w = 0; w < WPL; w += 2) {
-                        *reinterpret_cast<uint2*>(dst + w) = make_uint2(0u, 0u);
-                        *reinterpret_cast<uint2*>(dsth + w) = make_uint2(0u, 0u);
-                    }
+                    sts_zero_words<WPL>(dst);
+                    sts_zero_words<WPL>(dsth);
                     const int c_l = __shfl_sync(0xFFFFFFFFu, pcnt, l);
                     uint2* pd = pool + __shfl_sync(0xFFFFFFFFu, poff, l);
                     const uint2* src = post + __shfl_sync(0xFFFFFFFFu, base_cur, l);
@@ -487,27 +514,24 @@ bm25x_scan_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict_
                 const bool two = a != 0u;
                 const int lb = two ? __ffs(a) - 1 : la;
                 a &= a - 1;
+                uint32_t wa[WPL], ha[WPL], wb[WPL], hb[WPL];
+                lds_words<WPL>(bm + la * WORDS + WPL * lane, wa);
+                lds_words<WPL>(bm + lb * WORDS + WPL * lane, wb);
+                lds_words<WPL>(bmh + la * WORDS + WPL * lane, ha);
+                lds_words<WPL>(bmh + lb * WORDS + WPL * lane, hb);
 #pragma unroll
-                for (int w = 0; w < WPL; w += 2) {
-                    const uint2 va = *reinterpret_cast<const uint2*>(bm + la * WORDS + WPL * lane + w);
-                    const uint2 vb = *reinterpret_cast<const uint2*>(bm + lb * WORDS + WPL * lane + w);
-                    const uint2 xa = *reinterpret_cast<const uint2*>(bmh + la * WORDS + WPL * lane + w);
-                    const uint2 xb = *reinterpret_cast<const uint2*>(bmh + lb * WORDS + WPL * lane + w);
-                    const uint32_t wa[2] = {va.x, va.y}, ha[2] = {xa.x, xa.y};
-                    const uint32_t wb[2] = {two ? vb.x : 0u, two ? vb.y : 0u}, hb[2] = {two ? xb.x : 0u, two ? xb.y : 0u};
+                for (int w = 0; w < WPL; ++w) {
+                    const uint32_t wbw = two ? wb[w] : 0u, hbw = two ? hb[w] : 0u;
+                    uint32_t c = cn[0][w];
+                    const uint32_t ta = (c & wa[w]) | (c & ha[w]) | (wa[w] & ha[w]);
+                    c = c ^ wa[w] ^ ha[w];
+                    const uint32_t tb = (c & wbw) | (c & hbw) | (wbw & hbw);
+                    cn[0][w] = c ^ wbw ^ hbw;
+                    const uint32_t d = cn[1][w];
+                    uint32_t k = (d & ta) | (d & tb) | (ta & tb);
+                    cn[1][w] = d ^ ta ^ tb;
 #pragma unroll
-                    for (int h = 0; h < 2; ++h) {
-                        uint32_t c = cn[0][w + h];
-                        const uint32_t ta = (c & wa[h]) | (c & ha[h]) | (wa[h] & ha[h]);
-                        c = c ^ wa[h] ^ ha[h];
-                        const uint32_t tb = (c & wb[h]) | (c & hb[h]) | (wb[h] & hb[h]);
-                        cn[0][w + h] = c ^ wb[h] ^ hb[h];
-                        const uint32_t d = cn[1][w + h];
-                        uint32_t k = (d & ta) | (d & tb) | (ta & tb);
-                        cn[1][w + h] = d ^ ta ^ tb;
-#pragma unroll
-                        for (int p = 2; p < PLANES; ++p) { const uint32_t t_ = cn[p][w + h] & k; cn[p][w + h] ^= k; k = t_; }
-                    }
+                    for (int p = 2; p < PLANES; ++p) { const uint32_t t_ = cn[p][w] & k; cn[p][w] ^= k; k = t_; }
                 }
             }
             // count >= m, bit-slice compare from the top plane down; then the payload filter
@@ -555,14 +579,13 @@ bm25x_scan_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict_
                 a &= a - 1;
                 uint32_t loc[WPL];                       // packed exclusive prefix inside the lane
                 uint32_t own = 0u;
+                uint32_t va[WPL], vb[WPL];
+                lds_words<WPL>(bm + la * WORDS + WPL * lane, va);
+                lds_words<WPL>(bm + lb * WORDS + WPL * lane, vb);
 #pragma unroll
-                for (int w = 0; w < WPL; w += 2) {
-                    const uint2 va = *reinterpret_cast<const uint2*>(bm + la * WORDS + WPL * lane + w);
-                    const uint2 vb = *reinterpret_cast<const uint2*>(bm + lb * WORDS + WPL * lane + w);
+                for (int w = 0; w < WPL; ++w) {
                     loc[w] = own;
-                    own += (uint32_t)__popc(va.x) | (two ? (uint32_t)__popc(vb.x) << 16 : 0u);
-                    loc[w + 1] = own;
-                    own += (uint32_t)__popc(va.y) | (two ? (uint32_t)__popc(vb.y) << 16 : 0u);
+                    own += (uint32_t)__popc(va[w]) | (two ? (uint32_t)__popc(vb[w]) << 16 : 0u);
                 }
                 uint32_t inc = own;
 #pragma unroll
@@ -571,11 +594,25 @@ bm25x_scan_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict_
                     if (lane >= off) inc += o;
                 }
                 const uint32_t ex = inc - own;
+                uint32_t pa[WPL / 2], pb[WPL / 2];
 #pragma unroll
                 for (int w = 0; w < WPL; w += 2) {
                     const uint32_t r0 = ex + loc[w], r1 = ex + loc[w + 1];
-                    *reinterpret_cast<uint32_t*>(pre + la * 2 * WORDS + WPL * lane + w) = (r0 & 0xFFFFu) | (r1 << 16);
-                    if (two) *reinterpret_cast<uint32_t*>(pre + lb * 2 * WORDS + WPL * lane + w) = (r0 >> 16) | (r1 & 0xFFFF0000u);
+                    pa[w / 2] = (r0 & 0xFFFFu) | (r1 << 16);
+                    pb[w / 2] = (r0 >> 16) | (r1 & 0xFFFF0000u);
+                }
+                if constexpr (WPL % 4 == 0) {           // a lane's packed ranks are 8-byte aligned: one 64-bit store per 4 words
+#pragma unroll
+                    for (int w = 0; w < WPL; w += 4) {
+                        *reinterpret_cast<uint2*>(pre + la * 2 * WORDS + WPL * lane + w) = make_uint2(pa[w / 2], pa[w / 2 + 1]);
+                        if (two) *reinterpret_cast<uint2*>(pre + lb * 2 * WORDS + WPL * lane + w) = make_uint2(pb[w / 2], pb[w / 2 + 1]);
+                    }
+                } else {
+#pragma unroll
+                    for (int w = 0; w < WPL; w += 2) {
+                        *reinterpret_cast<uint32_t*>(pre + la * 2 * WORDS + WPL * lane + w) = pa[w / 2];
+                        if (two) *reinterpret_cast<uint32_t*>(pre + lb * 2 * WORDS + WPL * lane + w) = pb[w / 2];
+                    }
                 }
             }
 #pragma unroll 1
