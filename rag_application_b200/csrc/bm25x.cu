@@ -314,7 +314,7 @@ bm25x_scan_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict_
                 const uint32_t bound = hist_bound(coarse, fine, q, (uint32_t)k_sel, lane);
                 if (lane == 0 && bound != 0u) atomicMax(gthr + q, bound);
             }
-            if (done) break;
+            if (done >= nw) break;
             __nanosleep(mgr_sleep_ns);
         }
         return;
@@ -346,11 +346,25 @@ bm25x_scan_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict_
     const double sentinel = __longlong_as_double((long long)BX_SENTINEL);
 
     while (true) {
-        worker_bar(nw * 32);
-        if (threadIdx.x == 0) s_item = atomicAdd(work_counter, 1);
-        worker_bar(nw * 32);
-        const int item = s_item;
-        if (item >= n_items) break;
+        // Seed launch: the CTA's warps share one item (seed_qpi queries).  Main launch: every warp claims its own
+        // (range, query, warp slot) -- the same decomposition as a CTA-wide (range, query) item, without the two
+        // barriers per item and without the warps of an item waiting for its slowest one.
+        int item, wslot;
+        if (seed_mode) {
+            worker_bar(nw * 32);
+            if (threadIdx.x == 0) s_item = atomicAdd(work_counter, 1);
+            worker_bar(nw * 32);
+            item = s_item;
+            wslot = warp;
+            if (item >= n_items) break;
+        } else {
+            int wi = 0;
+            if (lane == 0) wi = atomicAdd(work_counter, 1);
+            wi = __shfl_sync(0xFFFFFFFFu, wi, 0);
+            item = wi / nw;
+            wslot = wi - item * nw;
+            if (item >= n_items) break;
+        }
         int q, j_first, j_end, j_stride, slot;
         if (seed_mode) {
             q = item * seed_qpi + warp;
@@ -361,7 +375,7 @@ bm25x_scan_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict_
             const int split = item / B;
             q = item - split * B;
             const int j_begin = seed_tiles + split * nt_per_split;
-            j_first = j_begin + warp; j_stride = nw; slot = split * nw + warp;
+            j_first = j_begin + wslot; j_stride = nw; slot = split * nw + wslot;
             j_end = min(nt, j_begin + nt_per_split);
         }
         const int qb = q_ptr[q];
@@ -676,7 +690,7 @@ bm25x_scan_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict_
         for (int i = lane; i < k_sel; i += 32) out[i] = list[i];
         __syncwarp();
     }
-    if (threadIdx.x == 0) *reinterpret_cast<volatile int*>(&s_done) = 1;
+    if (lane == 0) atomicAdd(&s_done, 1);             // the manager leaves once all nw worker warps are done
 }
 
 static int bx_lcap(int k_sel) {
