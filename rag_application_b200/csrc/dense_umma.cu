@@ -22,6 +22,7 @@
 #include <cuda.h>
 
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 
 #include "common.cuh"
@@ -191,7 +192,7 @@ __device__ __forceinline__ void um_compact(unsigned bal, uint64_t* my_list, uint
 __global__ void __launch_bounds__(UM_THREADS, 1)
 dense_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_x,
                   int64_t n, int d, int B, int qb_base, int n_qblocks, float4* __restrict__ seedv, int seed_tiles,
-                  int64_t rows_per_chunk,
+                  int64_t rows_per_chunk, int share,
                   const uint32_t* __restrict__ mask, int k_sel, uint32_t idesc, uint64_t* __restrict__ lists,
                   int* __restrict__ counts, uint32_t* __restrict__ gthr, uint32_t* __restrict__ coarse,
                   uint32_t* __restrict__ fine) {
@@ -204,7 +205,13 @@ dense_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
     // histograms.  Main launch: CTA i owns rows [i * rows_per_chunk, (i + 1) * rows_per_chunk) and list `chunk`.
     const bool seeding = seedv != nullptr;
     const int chunk = (int)blockIdx.x;
-    const int64_t row_begin = (int64_t)blockIdx.x * rows_per_chunk;
+    // share > 1 (main launch only): `share` neighbouring CTAs scan the SAME rows, each against its own 1/share of the
+    // query blocks, so the X tiles in flight at any moment are 148/share instead of 148 (they fit L2 and are read from
+    // HBM once).  Lists / counts stay per CTA; the query blocks a CTA never sees keep count 0.
+    const int sh = seeding ? 1 : share;
+    const int part = (int)blockIdx.x % sh;
+    const int qb_lo = part * n_qblocks / sh, qb_hi = (part + 1) * n_qblocks / sh;
+    const int64_t row_begin = (int64_t)((int)blockIdx.x / sh) * rows_per_chunk;
     const int64_t row_end = min(n, row_begin + (seeding ? (int64_t)UM_BN : rows_per_chunk));
     const int n_tiles = row_end > row_begin ? (int)((row_end - row_begin + UM_BN - 1) / UM_BN) : 0;
     const int n_kb = d / UM_BK;
@@ -232,7 +239,7 @@ dense_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
             uint32_t phase = 0;
             for (int t = 0; t < n_tiles; ++t) {
                 const int row0 = (int)(row_begin + (int64_t)t * UM_BN);
-                for (int qb = 0; qb < n_qblocks; ++qb) {
+                for (int qb = qb_lo; qb < qb_hi; ++qb) {
                     for (int kb = 0; kb < n_kb; ++kb) {
                         mbar_wait(&S.empty[stage], phase ^ 1);
                         mbar_expect_tx(&S.full[stage], UM_A_BYTES + UM_B_BYTES);
@@ -240,7 +247,7 @@ dense_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
                         // query block has used it, then it should leave first
                         tma_load_2d(S.a[stage], &tmap_q, kb * UM_BK, (qb_base + qb) * UM_BM, &S.full[stage], L2_EVICT_LAST);
                         tma_load_2d(S.b[stage], &tmap_x, kb * UM_BK, row0, &S.full[stage],
-                                    qb + 1 < n_qblocks ? L2_EVICT_NORMAL : L2_EVICT_FIRST);
+                                    (qb + 1 < qb_hi || sh > 1) ? L2_EVICT_NORMAL : L2_EVICT_FIRST);
                         if (++stage == UM_STAGES) { stage = 0; phase ^= 1; }
                     }
                 }
@@ -251,7 +258,7 @@ dense_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
         if (lane == 0) {
             int stage = 0;
             uint32_t phase = 0;
-            const int n_units = n_tiles * n_qblocks;   // unit = (X tile, query block)
+            const int n_units = n_tiles * (qb_hi - qb_lo);   // unit = (X tile, query block)
             for (int u = 0; u < n_units; ++u) {
                 const int as = u & 1;
                 const uint32_t aphase = (uint32_t)(u >> 1) & 1;
@@ -299,7 +306,7 @@ dense_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
         int u = 0;
         for (int t = 0; t < n_tiles; ++t) {
             const int64_t row0 = row_begin + (int64_t)t * UM_BN;
-            for (int qb = 0; qb < n_qblocks; ++qb, ++u) {
+            for (int qb = qb_lo; qb < qb_hi; ++qb, ++u) {
                 const int as = u & 1;
                 const uint32_t aphase = (uint32_t)(u >> 1) & 1;
                 const int b = (qb_base + qb) * UM_BM + qidx;
@@ -517,6 +524,18 @@ bool dense_umma_supported(int dtype, int d, int64_t n) {
 
 int dense_umma_max_ksel() { return UM_CAP - 64; }
 
+// CTAs per shared row range in the main launch: 2 (BRAG_UM_SHARE = 1, 2 or 4 overrides; tuning knob, read once).
+// Measured at 10 M x 1024 bf16, batch 1024, inside the hybrid step (the scan is power-capped, so HBM traffic saved
+// is clock gained): 1 -> 16.65 ms, 2 -> 13.79 ms, 4 -> 13.95 ms (profiles/r1_dense_share_v30.txt).
+static int um_share() {
+    static const int v = [] {
+        const char* e = getenv("BRAG_UM_SHARE");
+        const int x = e ? atoi(e) : 2;
+        return (x == 1 || x == 2 || x == 4) ? x : 2;
+    }();
+    return v;
+}
+
 cudaError_t dense_umma_plan(int64_t n, int d, int B, int k_sel, int num_sms, UmmaPlan* plan) {
     if (k_sel > UM_CAP - 64) return cudaErrorInvalidValue;
     (void)d;
@@ -610,21 +629,23 @@ cudaError_t dense_umma_scan(const void* X16, int dtype, int64_t n, int d, const 
     const int64_t n_tiles = (n + UM_BN - 1) / UM_BN;
     const int n_seed = plan.n_seed, n_main = plan.n_chunks;
     const int64_t seed_stride = n_seed > 0 ? (n_tiles / n_seed) * UM_BN : 0;      // rows between seed tiles
-    const int64_t rows_per_chunk = (n_tiles + n_main - 1) / n_main * UM_BN;
     int nl = 0;
     // query groups of <= UM_MAXQB blocks (1024 queries): each group is one pass over the corpus
     for (int qb0 = 0; qb0 < plan.n_qblocks; qb0 += UM_MAXQB) {
         const int nqb = std::min(UM_MAXQB, plan.n_qblocks - qb0);
         const int nq = std::min(B - qb0 * UM_BM, nqb * UM_BM);
         if (n_seed > 0) {
-            dense_umma_kernel<<<n_seed, UM_THREADS, smem, st>>>(tq, tx, n, d, B, qb0, nqb, seedv, n_seed, seed_stride, mask,
+            dense_umma_kernel<<<n_seed, UM_THREADS, smem, st>>>(tq, tx, n, d, B, qb0, nqb, seedv, n_seed, seed_stride, 1, mask,
                                                                k_sel, idesc, lists, counts, gthr, coarse, fine);
             if ((err = cudaGetLastError()) != cudaSuccess) return err;
             um_seed_bound_kernel<<<nq, 256, 0, st>>>(seedv, n_seed, qb0 * UM_BM, qb0 * UM_BM + nq, k_sel, gthr);
             if ((err = cudaGetLastError()) != cudaSuccess) return err;
             nl += 2;
         }
-        dense_umma_kernel<<<n_main, UM_THREADS, smem, st>>>(tq, tx, n, d, B, qb0, nqb, nullptr, 0, rows_per_chunk, mask,
+        // CTAs sharing a row range (see the kernel): only when the query blocks and the grid split evenly
+        const int share = (um_share() > 1 && nqb % um_share() == 0 && n_main % um_share() == 0 && n_tiles >= n_main) ? um_share() : 1;
+        const int64_t rows_per_chunk = (n_tiles + n_main / share - 1) / (n_main / share) * UM_BN;
+        dense_umma_kernel<<<n_main, UM_THREADS, smem, st>>>(tq, tx, n, d, B, qb0, nqb, nullptr, 0, rows_per_chunk, share, mask,
                                                            k_sel, idesc, lists, counts, gthr, coarse, fine);
         if ((err = cudaGetLastError()) != cudaSuccess) return err;
         // final bounds from the complete histograms (a CTA's manager stops with its own CTA, so the bounds it left

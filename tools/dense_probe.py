@@ -20,6 +20,7 @@ ap.add_argument("--dtype", default="f16")
 ap.add_argument("--k", type=int, default=100)
 ap.add_argument("--iters", type=int, default=5)
 ap.add_argument("--mask", type=float, default=0.0)
+ap.add_argument("--dump", default="", help="write the last batch's (scores, ids) to this .npz (to compare runs under different knobs)")
 a = ap.parse_args()
 dev = torch.device("cuda", 0)
 eng = Engine(0)
@@ -42,9 +43,12 @@ for B in batches:
         eng.dense_topk("x", qb, a.k, mask_id=mask_id)
     eng.profile_reset()
     for _ in range(a.iters):
-        eng.dense_topk("x", qb, a.k, mask_id=mask_id)
+        r = eng.dense_topk("x", qb, a.k, mask_id=mask_id)
     ms, calls, _ = eng.profile_read()
     scan = ms["dense_scan"] / a.iters
     out[f"B{B}"] = {"scan_ms": scan, "select_ms": ms["dense_select"] / a.iters,
                     "tflops": 2.0 * a.n * a.d * B / (scan * 1e-3) / 1e12, "gbs": a.n * a.d * 2 / (scan * 1e-3) / 1e9}
+if a.dump:
+    import numpy as np
+    np.savez(a.dump, **{f"r{i}": t.cpu().numpy() for i, t in enumerate(r)})
 print(json.dumps(out))
