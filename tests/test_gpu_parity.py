@@ -95,6 +95,28 @@ def test_dense_tcgen05_seeded_two_phase(engine, masked):
         check_dense(xs, O.round_storage(q[b], "bf16"), k, s[b], i[b], int(c[b]), mask=mask)
 
 
+@pytest.mark.parametrize("n,B", [(50_001, 512), (38_000, 256), (160_000, 1024)])
+def test_dense_tcgen05_shared_row_ranges(engine, n, B):
+    """Even numbers of query blocks on corpora of >= 148 tiles: pairs of CTAs scan the same rows, each against half of
+    the query blocks (dense_umma.cu: share).  Ragged last chunk, payload filter, every query block checked."""
+    d, k = 64, 100
+    x = synth.dense_corpus(n, d, seed=81, clustered=True)
+    q = synth.dense_queries(x, B, seed=82)
+    xs = O.round_storage(x, "f16")
+    engine.dense_set("t", x, "f16")
+    mask = synth.random_mask(n, 0.5)
+    engine.mask_set(9, mask)
+    engine.force_dense_path("tcgen05")
+    s, i, c = engine.dense_topk("t", q, k, mask_id=9)
+    engine.force_dense_path("gemv")
+    rows = np.arange(0, B, 37)
+    s0, i0, c0 = engine.dense_topk("t", q[rows], k, mask_id=9)
+    engine.force_dense_path(None)
+    assert np.array_equal(i[rows], i0) and np.array_equal(s[rows], s0)
+    for b in range(5, B, 61):
+        check_dense(xs, O.round_storage(q[b], "f16"), k, s[b], i[b], int(c[b]), mask=mask)
+
+
 def test_dense_paths_agree(engine):
     """Both scan kernels feed the same re-score: final lists must be identical."""
     x = synth.dense_corpus(30000, 256, seed=3)
