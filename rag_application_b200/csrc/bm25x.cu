@@ -435,6 +435,29 @@ bm25x_scan_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict_
         }
         uint32_t g_seen = 0u;
         double pre_g = -INFINITY;
+        // one scored-but-not-yet-summed candidate per lane, carried from a scoring round to the next one
+        float pwt[MAXT];
+        unsigned phit = 0u;
+        uint32_t pdg = 0u;
+#pragma unroll
+        for (int l = 0; l < MAXT; ++l) pwt[l] = 0.f;
+        auto flush_pending = [&](double pre_now, uint32_t g_now) {
+            if (phit != 0u) {
+                double acc = sentinel;
+#pragma unroll
+                for (int l = 0; l < MAXT; ++l)
+                    if ((phit >> l) & 1u) acc = __dadd_rn(acc, __dmul_rn(sqv[l], (double)pwt[l]));
+                if (acc > pre_now) {
+                    const uint64_t key = make_key((float)acc, pdg);
+                    if (key > thr && (uint32_t)(key >> 32) >= g_now) {
+                        list[atomicAdd(cntp, 1)] = key;
+                        hist_count(coarse, fine, q, (uint32_t)(key >> 32));
+                    }
+                }
+                phit = 0u;
+            }
+            __syncwarp();
+        };
 #pragma unroll 1
         for (int j = j_first; j < j_end; j += j_stride) {
             const uint32_t tile_base = (uint32_t)j * C::TILE;
@@ -649,9 +672,11 @@ bm25x_scan_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict_
                 const int dl = mine ? (int)clist[lane] : 0;
                 const int word = dl >> 5, bit = dl & 31;
                 const uint32_t below = (1u << bit) - 1u;
-                float wt[MAXT];
+                // the previous round's candidate (usually the previous visit's): its weight loads have had a whole
+                // visit to land; sum and push it now, then start this round's loads into the same registers
+                flush_pending(pre_eff, g);
                 uint32_t rk[MAXT];
-                unsigned hit = 0u, from_pool = 0u;
+                unsigned hit = 0u;
 #pragma unroll
                 for (int l = 0; l < MAXT; ++l) {
                     const uint32_t wv = bm[l * WORDS + word];
@@ -660,31 +685,20 @@ bm25x_scan_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict_
                     const bool st = h && ((sparse_terms >> l) & 1u) && (int)rk[l] < spcnt[l];
                     const bool gl = h && !st;
                     // unconditional load (a dummy, L1-resident address when this term misses): the MAXT loads issue
-                    // back to back instead of one dependent branch per term
-                    const uint2* ap = gl ? post + sbase[l] + rk[l] : post;
-                    wt[l] = __uint_as_float(__ldg(&ap->y));
+                    // back to back instead of one dependent branch per term.  Generic loads: the posting is either in
+                    // the global array or in this visit's shared-memory pool (read now, before the pool is refilled).
+                    const uint2* ap = st ? pool + spoff[l] + rk[l] : (gl ? post + sbase[l] + rk[l] : post);
+                    pwt[l] = __uint_as_float(ap->y);
                     hit |= (h ? 1u : 0u) << l;
-                    from_pool |= (st ? 1u : 0u) << l;
                 }
-#pragma unroll
-                for (int l = 0; l < MAXT; ++l)
-                    if ((from_pool >> l) & 1u) wt[l] = __uint_as_float(pool[spoff[l] + rk[l]].y);
-                double acc = sentinel;
-#pragma unroll
-                for (int l = 0; l < MAXT; ++l)
-                    if ((hit >> l) & 1u) acc = __dadd_rn(acc, __dmul_rn(sqv[l], (double)wt[l]));
-                if (mine && acc > pre_eff) {
-                    const uint32_t dg = tile_base + (uint32_t)dl;
-                    const uint64_t key = make_key((float)acc, dg);
-                    if (key > thr && (uint32_t)(key >> 32) >= g) {
-                        list[atomicAdd(cntp, 1)] = key;
-                        hist_count(coarse, fine, q, (uint32_t)(key >> 32));
-                    }
-                }
+                phit = hit;
+                pdg = tile_base + (uint32_t)dl;
                 __syncwarp();
             }
         }
-        // ---- emit this warp's list for (split, warp, q)
+        // ---- the last round's candidates, then emit this warp's list for (split, warp, q)
+        if (*cntp > lcap - 32) warp_compact(list, cntp, lcap, k_sel, thr, lane);
+        flush_pending(fmax(pre_local, pre_g), g_seen);
         warp_compact(list, cntp, lcap, k_sel, thr, lane);
         uint64_t* out = part + ((size_t)slot * B + q) * k_sel;
         for (int i = lane; i < k_sel; i += 32) out[i] = list[i];
@@ -736,7 +750,9 @@ Bm25Plan bm25x_plan(int64_t n_docs, int B, int k_sel, int max_terms, int num_sms
     p.seed_tiles = (nt >= 32) ? seed_cfg : 0;
     p.seed_qpi = std::max(1, std::min(p.workers, (B + resident - 1) / resident));
     const int nt_main = nt - p.seed_tiles;
-    int splits = (resident * 8 + B - 1) / B;
+    // ranges per query: enough items to keep every SM busy ~8 times over (BRAG_BX_ITEMS_PER_SM overrides; tuning knob)
+    static const int items_per_sm = [] { const char* e = getenv("BRAG_BX_ITEMS_PER_SM"); const int v = e ? atoi(e) : 8; return v < 1 ? 1 : (v > 64 ? 64 : v); }();
+    int splits = (resident * items_per_sm + B - 1) / B;
     int max_splits = (nt_main + p.workers - 1) / p.workers;
     if (splits > max_splits) splits = max_splits;
     if (splits < 1) splits = 1;
