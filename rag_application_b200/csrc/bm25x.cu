@@ -51,9 +51,18 @@ struct BxCfg {
 // per-warp shared memory: bm[MAXT][WORDS] u32 | bmh[MAXT][WORDS] u32 (the rank table pre[MAXT][WORDS] u16 overwrites
 //                         each term's high map once it has been counted) | pool[POOL] (doc, weight) | list[lcap] u64 |
 //                         sbase[MAXT] i64 | sqv[MAXT] f64 | spoff[MAXT] i32 | spcnt[MAXT] i32 | clist[32] u16 | cnt
-__host__ __device__ inline size_t bx_warp_bytes(int maxt, int subs, int lcap) {
+__host__ __device__ constexpr size_t bx_warp_bytes(int maxt, int subs, int lcap) {
     return (size_t)maxt * 64 * subs * 8 + (size_t)128 * subs * 8 + (size_t)lcap * 8 + (size_t)maxt * 24 + 64 + 16;
 }
+// Worker warps per CTA of an instantiation: what shared memory allows with the shortest list (lcap = 128), at most
+// BX_MAX_WORKERS; registers are allocated per 4 warps, so a count of 16 or more is rounded down to 4k - 1 (+ the manager
+// warp = 4k warps): <8, 2> gets 19 workers = 640 threads -> 96 registers instead of the 80 that 21+ warps allow.
+constexpr int bx_worker_cap(int maxt, int subs) {
+    const size_t f = BX_SMEM_MAX / bx_warp_bytes(maxt, subs, 128);
+    const int w = (int)(f < (size_t)BX_MAX_WORKERS ? f : (size_t)BX_MAX_WORKERS);
+    return w >= 16 ? (w + 1) / 4 * 4 - 1 : w;
+}
+constexpr int bx_max_threads(int maxt, int subs) { return (bx_worker_cap(maxt, subs) + 1) * 32; }
 
 // words of one stored document map: the sub-tile count is rounded up to 4 so a tile of any SUBS stays inside its row
 int64_t bm25x_row_words(int64_t n_docs) {
@@ -287,7 +296,7 @@ __device__ __forceinline__ void sts_zero_words(uint32_t* p) {
 }
 
 template <int MAXT, int SUBS>
-__global__ void __launch_bounds__(BX_THREADS, 1)
+__global__ void __launch_bounds__(bx_max_threads(MAXT, SUBS), 1)
 bm25x_scan_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict__ post,
                   const uint32_t* __restrict__ sub_off, const int32_t* __restrict__ bm_row,
                   const uint32_t* __restrict__ bits, const uint32_t* __restrict__ bits_hi,
@@ -738,7 +747,7 @@ Bm25Plan bm25x_plan(int64_t n_docs, int B, int k_sel, int max_terms, int num_sms
     const int subs = bx_subs();
     const int ns = (int)((n_docs + BM25_SUB - 1) / BM25_SUB);
     const int nt = (ns + subs - 1) / subs;
-    p.workers = (int)std::min<size_t>(BX_MAX_WORKERS, BX_SMEM_MAX / bx_warp_bytes(bx_maxt(max_terms), subs, bx_lcap(k_sel)));
+    p.workers = (int)std::min<size_t>(bx_worker_cap(bx_maxt(max_terms), subs), BX_SMEM_MAX / bx_warp_bytes(bx_maxt(max_terms), subs, bx_lcap(k_sel)));
     p.workers = std::max(1, std::min(p.workers, nt));
     // BRAG_BX_WORKERS (experiments): fewer worker warps per CTA, e.g. to run beside another resident kernel
     static const int wcap = [] { const char* e = getenv("BRAG_BX_WORKERS"); return e ? atoi(e) : 0; }();
