@@ -347,7 +347,8 @@ bm25x_scan_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict_
     const int nt = (ns + SUBS - 1) / SUBS;                    // tiles of SUBS sub-tiles
     // Seed launch (seed_mode): work item = seed_qpi queries, warp w scans the first seed_tiles tiles for query
     // item * seed_qpi + w and writes list number splits * nw.  Main launch: tiles [seed_tiles, nt) in `splits` ranges,
-    // work item = (range, query), warp w takes every nw-th tile and writes list range * nw + w.  The seed's bound
+    // work item = (range, query, slot w) claimed by one warp, which takes every nw-th tile of the range starting at the
+    // w-th and writes list range * nw + w.  The seed's bound
     // (k-th best of its few thousand documents) keeps the main launch's first visits from scoring every document.
     const int nt_per_split = (nt - seed_tiles + splits - 1) / splits;
     const size_t row_words = (size_t)((ns + 3) / 4 * 4) * BX_WORDS;
