@@ -31,8 +31,7 @@
 
 namespace brag {
 
-constexpr int BX_MAX_WORKERS = 23;                  // + the bound-manager warp = 24 warps (<= 80 registers/thread)
-constexpr int BX_THREADS = (BX_MAX_WORKERS + 1) * 32;
+constexpr int BX_MAX_WORKERS = 23;                  // + the bound-manager warp = 24 warps; bx_worker_cap() per instantiation
 constexpr size_t BX_SMEM_MAX = 232448 - 64;
 constexpr int BX_WORDS = BM25_SUB / 32;             // 64 map words per sub-tile, 2 per lane
 constexpr unsigned long long BX_SENTINEL = 0x8000000000000000ull;   // -0.0 + p == p: first add equals 0.0 + p
