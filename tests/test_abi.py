@@ -80,3 +80,20 @@ def test_product_never_imports_the_oracle():
                 txt = open(os.path.join(dp, f), errors="ignore").read()
                 assert not re.search(r"^\s*(from|import)\s+oracle\b", txt, flags=re.M), f
                 assert "libbm25_cpu" not in txt, f
+
+
+def test_every_tuning_knob_is_documented():
+    """Every environment knob the library or the host code reads (getenv / os.environ) is listed in DESIGN.md."""
+    import re
+    pkg = os.path.join(ROOT, "rag_application_b200")
+    knobs = set()
+    for dp, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h")):
+                txt = open(os.path.join(dp, f), errors="ignore").read()
+                knobs |= set(re.findall(r'getenv\("(BRAG_[A-Z0-9_]+)"\)', txt))
+                knobs |= set(re.findall(r'environ(?:\.get)?[\[(]\s*"(BRAG_[A-Z0-9_]+)"', txt))
+    assert knobs, "no knobs found: the patterns above no longer match the code"
+    design = open(os.path.join(ROOT, "DESIGN.md")).read()
+    missing = sorted(k for k in knobs if k not in design)
+    assert not missing, f"undocumented knobs: {missing}"
