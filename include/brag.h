@@ -100,11 +100,15 @@ int brag_dense_rescore(brag_engine* e, const char* name, const float* Q, int32_t
 /* Sparse (BM25) top-k: Prefetch(query=SparseVector, using=name, limit=k)
  * (qdrant_handler.py:347-354).  Query b owns q_terms/q_vals[q_ptr[b]:q_ptr[b+1]], term rows
  * strictly ascending; q_vals are float64 (Python floats; IDF already applied by the host).
- * Only documents sharing >=1 term are candidates. */
+ * Only documents sharing >=1 term are candidates.
+ * max_terms: an upper bound of the longest query of the batch, in terms (it selects the kernel variant); -1 = let the
+ * engine find it.  With host pointers that is a loop over q_ptr; with device pointers it costs a device->host copy of
+ * q_ptr and a stream synchronisation in the middle of the call, so stream-ordered callers pass the bound (ABI 2).
+ * With device pointers the bound is the caller's promise: terms of a query beyond it are ignored. */
 int brag_sparse_topk(brag_engine* e, const char* name, const int32_t* q_ptr,
                      const int32_t* q_terms, const double* q_vals, int32_t B, int32_t k,
-                     int32_t mask_id, float* out_scores, int64_t* out_ids, int32_t* out_counts,
-                     int32_t on_device, void* stream);
+                     int32_t mask_id, int32_t max_terms, float* out_scores, int64_t* out_ids,
+                     int32_t* out_counts, int32_t on_device, void* stream);
 /* Document frequency of each term row (for Modifier.IDF on the host): df[V] int64, host. */
 int brag_sparse_df(brag_engine* e, const char* name, int64_t* df_host, int64_t n_terms);
 
@@ -130,15 +134,52 @@ int brag_merge_topk(brag_engine* e, const float* scores, const int64_t* ids,
                     int64_t* out_ids, int32_t* out_counts, int32_t on_device, void* stream);
 
 /* The north_star three-stage path in one call: dense top-k, sparse top-k, RRF(limit=k).
- * Optional outputs (may be NULL): the two per-stage lists. */
+ * max_terms as in brag_sparse_topk. */
 int brag_hybrid_topk(brag_engine* e, const char* dense_name, const char* sparse_name,
                      const float* Q, const int32_t* q_ptr, const int32_t* q_terms,
-                     const double* q_vals, int32_t B, int32_t k, int32_t mask_id,
+                     const double* q_vals, int32_t B, int32_t k, int32_t mask_id, int32_t max_terms,
                      double* out_scores, int64_t* out_ids, int32_t* out_counts,
                      int32_t on_device, void* stream);
 
+/* ---- Row sharding across the GPUs of one box (the `brag_allgather_merge` of SURVEY 8b).
+ * One engine per GPU, each holding the rows [id_offset, id_offset + n) of every space; a query batch is answered by
+ * all of them.  A stage's per-shard list travels as sorted 64-bit keys, ordered(score) << 32 | (0xFFFFFFFF - global
+ * row), 0 = empty slot: [2 lists (dense, sparse)][B][k].
+ *
+ * Collective variant (any transport): brag_shard_local_lists on every rank -> all-gather of the key arrays ->
+ * brag_shard_fuse on every rank (merge of the G dense lists, merge of the G sparse lists, RRF of the two; one kernel).
+ * stage_* (all three or none): the two merged lists, [2][B][k] scores / ids and [2][B] counts. */
+int brag_shard_local_lists(brag_engine* e, const char* dense_name, const char* sparse_name, const float* Q,
+                           const int32_t* q_ptr, const int32_t* q_terms, const double* q_vals, int32_t B, int32_t k,
+                           int32_t mask_id, int32_t max_terms, uint64_t* out_keys, int32_t on_device, void* stream);
+int brag_shard_fuse(brag_engine* e, const uint64_t* keys /* [G][2][B][k] */, int32_t G, int32_t B, int32_t k,
+                    int32_t limit, int32_t tie_mode, double* out_scores, int64_t* out_ids, int32_t* out_counts,
+                    float* stage_scores, int64_t* stage_ids, int32_t* stage_counts, int32_t on_device, void* stream);
+/* Peer variant: the exchange is fused into the tail kernels over NVLink peer memory -- no collective call.
+ * brag_shard_window_create allocates this engine's exchange window (for batches <= max_batch, lists <= max_k;
+ * world * max_k <= 8192) and returns its 64-byte CUDA IPC handle; the caller carries the handles of all ranks to every
+ * rank (any host transport) and calls brag_shard_connect(rank, world, handles [world][64]).  Engines living in ONE
+ * process pass local_peers (the world's engine handles, in rank order) instead and handles = NULL.
+ * brag_shard_hybrid_topk must then be called by every rank with the same batch, in the same order (it counts epochs):
+ * each rank pushes its two lists straight into every peer's window while it scans, tells its score bounds to the peers
+ * (any shard's k-th best is a lower bound of the global k-th best), and one kernel per rank waits for the world's
+ * lists, merges and fuses them.  The result is identical on every rank.  The wait is bounded (a peer that never
+ * arrives becomes a CUDA error after 8 s).  With on_device = 0 the call synchronises: engines of one process must
+ * then be driven from one thread each, or with device pointers. */
+#define BRAG_SHARD_HANDLE_BYTES 64
+int brag_shard_window_create(brag_engine* e, int32_t world, int32_t max_batch, int32_t max_k, void* handle_out);
+int brag_shard_connect(brag_engine* e, int32_t rank, int32_t world, const void* handles,
+                       brag_engine* const* local_peers);
+int brag_shard_hybrid_topk(brag_engine* e, const char* dense_name, const char* sparse_name, const float* Q,
+                           const int32_t* q_ptr, const int32_t* q_terms, const double* q_vals, int32_t B, int32_t k,
+                           int32_t mask_id, int32_t max_terms, double* out_scores, int64_t* out_ids,
+                           int32_t* out_counts, float* stage_scores, int64_t* stage_ids, int32_t* stage_counts,
+                           int32_t on_device, void* stream);
+int brag_shard_close(brag_engine* e);
+
 /* Per-stage device timing (CUDA events on the call's stream).  Stages: 0 dense scan,
- * 1 dense select+rescore, 2 sparse scan, 3 sparse select, 4 rrf, 5 merge.
+ * 1 dense select+rescore, 2 sparse scan, 3 sparse select, 4 rrf, 5 merge / sharded signal + fuse (includes the wait
+ * for the slowest peer).
  * brag_profile_read returns accumulated ms and launch counts since the last reset and
  * synchronises the device. */
 #define BRAG_N_STAGES 6

@@ -31,10 +31,17 @@ PROTOTYPES = {
     "brag_mask_set": (C.c_int, [c_p, i32, c_p, i64, i32]),
     "brag_dense_topk": (C.c_int, [c_p, C.c_char_p, c_p, i32, i32, i32, c_p, c_p, c_p, i32, c_p]),
     "brag_dense_rescore": (C.c_int, [c_p, C.c_char_p, c_p, i32, c_p, i32, i32, i32, c_p, c_p, c_p, i32, c_p]),
-    "brag_sparse_topk": (C.c_int, [c_p, C.c_char_p, c_p, c_p, c_p, i32, i32, i32, c_p, c_p, c_p, i32, c_p]),
+    "brag_sparse_topk": (C.c_int, [c_p, C.c_char_p, c_p, c_p, c_p, i32, i32, i32, i32, c_p, c_p, c_p, i32, c_p]),
     "brag_rrf": (C.c_int, [c_p, c_p, c_p, i32, i32, i32, i32, i32, c_p, c_p, c_p, i32, c_p]),
     "brag_merge_topk": (C.c_int, [c_p, c_p, c_p, c_p, i32, i32, i32, c_p, c_p, c_p, i32, c_p]),
-    "brag_hybrid_topk": (C.c_int, [c_p, C.c_char_p, C.c_char_p, c_p, c_p, c_p, c_p, i32, i32, i32, c_p, c_p, c_p, i32, c_p]),
+    "brag_hybrid_topk": (C.c_int, [c_p, C.c_char_p, C.c_char_p, c_p, c_p, c_p, c_p, i32, i32, i32, i32, c_p, c_p, c_p, i32, c_p]),
+    "brag_shard_local_lists": (C.c_int, [c_p, C.c_char_p, C.c_char_p, c_p, c_p, c_p, c_p, i32, i32, i32, i32, c_p, i32, c_p]),
+    "brag_shard_fuse": (C.c_int, [c_p, c_p, i32, i32, i32, i32, i32, c_p, c_p, c_p, c_p, c_p, c_p, i32, c_p]),
+    "brag_shard_window_create": (C.c_int, [c_p, i32, i32, i32, c_p]),
+    "brag_shard_connect": (C.c_int, [c_p, i32, i32, c_p, c_p]),
+    "brag_shard_hybrid_topk": (C.c_int, [c_p, C.c_char_p, C.c_char_p, c_p, c_p, c_p, c_p, i32, i32, i32, i32, c_p, c_p, c_p,
+                                         c_p, c_p, c_p, i32, c_p]),
+    "brag_shard_close": (C.c_int, [c_p]),
     "brag_profile_enable": (C.c_int, [c_p, i32]),
     "brag_profile_read": (C.c_int, [c_p, c_p, c_p, c_p]),
     "brag_profile_reset": (C.c_int, [c_p]),

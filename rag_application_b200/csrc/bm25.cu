@@ -90,7 +90,8 @@ bm25_scan_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict__
                  int64_t n_docs, const int32_t* __restrict__ q_ptr, const int32_t* __restrict__ q_terms,
                  const double* __restrict__ q_vals, int B, const uint32_t* __restrict__ mask, int k_sel,
                  int lcap, int nw, uint64_t* __restrict__ part, int splits, int* __restrict__ work_counter,
-                 uint32_t* __restrict__ gthr, uint32_t* __restrict__ coarse, uint32_t* __restrict__ fine) {
+                 uint32_t* __restrict__ gthr, uint32_t* __restrict__ coarse, uint32_t* __restrict__ fine,
+                 const ShardBounds xb) {
     extern __shared__ __align__(16) uint8_t smem_raw[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     __shared__ int s_item;
@@ -103,8 +104,7 @@ bm25_scan_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict__
         while (true) {
             const int done = *reinterpret_cast<volatile int*>(&s_done);
             for (int q = (int)blockIdx.x; q < B; q += (int)gridDim.x) {
-                const uint32_t bound = hist_bound(coarse, fine, q, (uint32_t)k_sel, lane);
-                if (lane == 0 && bound != 0u) atomicMax(gthr + q, bound);
+                publish_bound(gthr, q, hist_bound(coarse, fine, q, (uint32_t)k_sel, lane), xb, lane);
             }
             if (done) break;
             __nanosleep(20000);
@@ -364,24 +364,23 @@ Bm25Plan bm25_plan(int64_t n_docs, int B, int k_sel, int num_sms) {
     return p;
 }
 
+// kernel attributes are per device: brag_create calls this with the engine's device current
+cudaError_t bm25_init_device() {
+    cudaError_t e = cudaFuncSetAttribute(bm25_scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BM_SMEM_MAX);
+    if (e != cudaSuccess) return e;
+    // the largest shared-memory carve-out; the default heuristic sizes it from the first launch
+    return cudaFuncSetAttribute(bm25_scan_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                cudaSharedmemCarveoutMaxShared);
+}
+
 cudaError_t bm25_scan(const int64_t* term_ptr, const uint2* post, const uint32_t* sub_off,
                       int64_t V, int64_t n_docs, const int32_t* q_ptr, const int32_t* q_terms,
                       const double* q_vals, int B, const uint32_t* mask, int k_sel, uint64_t* part,
-                      const Bm25Plan& plan, void* scratch, cudaStream_t st) {
+                      const Bm25Plan& plan, void* scratch, cudaStream_t st, const ShardBounds& xb) {
     if (k_sel > 512) return cudaErrorInvalidValue;
     const int lcap = bm25_lcap(k_sel);
     const size_t smem = bm_warp_bytes(lcap) * plan.workers;
-    static size_t attr_smem = 0;
-    if (smem > attr_smem) {
-        cudaError_t e = cudaFuncSetAttribute(bm25_scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             (int)smem);
-        if (e != cudaSuccess) return e;
-        // two CTAs per SM need the largest shared-memory carve-out; the default heuristic sizes it for one
-        e = cudaFuncSetAttribute(bm25_scan_kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
-                                 cudaSharedmemCarveoutMaxShared);
-        if (e != cudaSuccess) return e;
-        attr_smem = smem;
-    }
+    if (smem > BM_SMEM_MAX) return cudaErrorInvalidValue;
     uint8_t* sp = reinterpret_cast<uint8_t*>(scratch);
     int* work_counter = reinterpret_cast<int*>(sp);
     uint32_t* gthr = reinterpret_cast<uint32_t*>(sp + 256);
@@ -391,7 +390,7 @@ cudaError_t bm25_scan(const int64_t* term_ptr, const uint2* post, const uint32_t
     if (e != cudaSuccess) return e;
     bm25_scan_kernel<<<plan.grid, (plan.workers + 1) * 32, smem, st>>>(term_ptr, post, sub_off, V, n_docs, q_ptr, q_terms,
                                                           q_vals, B, mask, k_sel, lcap, plan.workers, part, plan.splits,
-                                                          work_counter, gthr, coarse, fine);
+                                                          work_counter, gthr, coarse, fine, xb);
     return cudaGetLastError();
 }
 

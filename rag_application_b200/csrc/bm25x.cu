@@ -304,7 +304,8 @@ bm25x_scan_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict_
                   const double* __restrict__ q_vals, int B, const uint32_t* __restrict__ mask, int k_sel, int lcap,
                   int nw, uint64_t* __restrict__ part, int splits, int seed_tiles, int seed_qpi, int seed_mode, unsigned mgr_sleep_ns,
                   int* __restrict__ work_counter,
-                  uint32_t* __restrict__ gthr, uint32_t* __restrict__ coarse, uint32_t* __restrict__ fine) {
+                  uint32_t* __restrict__ gthr, uint32_t* __restrict__ coarse, uint32_t* __restrict__ fine,
+                  const ShardBounds xb) {
     using C = BxCfg<MAXT, SUBS>;
     constexpr int WPL = C::WPL, WORDS = C::WORDS, POOL = C::POOL, PLANES = C::PLANES;
     extern __shared__ __align__(16) uint8_t smem_raw[];
@@ -319,8 +320,7 @@ bm25x_scan_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict_
         while (true) {
             const int done = *reinterpret_cast<volatile int*>(&s_done);
             for (int q = (int)blockIdx.x; q < B; q += (int)gridDim.x) {
-                const uint32_t bound = hist_bound(coarse, fine, q, (uint32_t)k_sel, lane);
-                if (lane == 0 && bound != 0u) atomicMax(gthr + q, bound);
+                publish_bound(gthr, q, hist_bound(coarse, fine, q, (uint32_t)k_sel, lane), xb, lane);
             }
             if (done >= nw) break;
             __nanosleep(mgr_sleep_ns);
@@ -783,6 +783,7 @@ struct BxArgs {
     const int64_t* term_ptr; const uint2* post; const uint32_t* sub_off; const int32_t* bm_row; const uint32_t* bits;
     const uint32_t* bits_hi; const float2* wrange; const float* tau; int64_t V, n_docs; const int32_t *q_ptr, *q_terms; const double* q_vals; int B;
     const uint32_t* mask; int k_sel; uint64_t* part; const Bm25Plan* plan; void* scratch; cudaStream_t st;
+    ShardBounds xb;
 };
 
 template <int MAXT, int SUBS>
@@ -790,39 +791,26 @@ static cudaError_t bx_launch(const BxArgs& a) {
     const Bm25Plan& plan = *a.plan;
     const int lcap = bx_lcap(a.k_sel);
     const size_t smem = bx_warp_bytes(MAXT, SUBS, lcap) * plan.workers;
-    static size_t attr_smem = 0;
-    if (smem > attr_smem) {
-        cudaError_t e = cudaFuncSetAttribute(bm25x_scan_kernel<MAXT, SUBS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             (int)smem);
-        if (e != cudaSuccess) return e;
-        attr_smem = smem;
-    }
+    if (smem > BX_SMEM_MAX) return cudaErrorInvalidValue;
     uint8_t* sp = reinterpret_cast<uint8_t*>(a.scratch);
     int* work_counter = reinterpret_cast<int*>(sp);
     uint32_t* gthr = reinterpret_cast<uint32_t*>(sp + 256);
     uint32_t* coarse = reinterpret_cast<uint32_t*>(sp + 256 + plan.gthr_bytes);
     uint32_t* fine = reinterpret_cast<uint32_t*>(sp + 256 + plan.gthr_bytes + plan.coarse_bytes);
-    // BRAG_BX_WARM=1 (experiment only, tools/bm25_probe.py): keep the previous call's per-query bounds, to measure
-    // what a perfect starting bound would be worth when the same batch is repeated
-    static const bool warm = [] { const char* w = getenv("BRAG_BX_WARM"); return w && atoi(w) == 1; }();
-    cudaError_t e = cudaMemsetAsync(a.scratch, 0, warm ? 256 : plan.scratch_bytes, a.st);
+    cudaError_t e = cudaMemsetAsync(a.scratch, 0, plan.scratch_bytes, a.st);
     if (e != cudaSuccess) return e;
-    if (warm) {
-        e = cudaMemsetAsync(sp + 256 + plan.gthr_bytes, 0, plan.coarse_bytes + plan.fine_bytes, a.st);
-        if (e != cudaSuccess) return e;
-    }
     if (plan.seed_tiles > 0) {
         const int seed_items = (a.B + plan.seed_qpi - 1) / plan.seed_qpi;
         bm25x_scan_kernel<MAXT, SUBS><<<std::min(seed_items, plan.grid), (plan.workers + 1) * 32, smem, a.st>>>(
             a.term_ptr, a.post, a.sub_off, a.bm_row, a.bits, a.bits_hi, a.wrange, a.tau, a.V, a.n_docs, a.q_ptr, a.q_terms,
             a.q_vals, a.B, a.mask, a.k_sel, lcap, plan.workers, a.part, plan.splits, plan.seed_tiles, plan.seed_qpi, 1, bx_mgr_sleep(),
-            work_counter + 1, gthr, coarse, fine);
+            work_counter + 1, gthr, coarse, fine, ShardBounds());
         if ((e = cudaGetLastError()) != cudaSuccess) return e;
     }
     bm25x_scan_kernel<MAXT, SUBS><<<plan.grid, (plan.workers + 1) * 32, smem, a.st>>>(
         a.term_ptr, a.post, a.sub_off, a.bm_row, a.bits, a.bits_hi, a.wrange, a.tau, a.V, a.n_docs, a.q_ptr, a.q_terms,
         a.q_vals, a.B, a.mask, a.k_sel, lcap, plan.workers, a.part, plan.splits, plan.seed_tiles, plan.seed_qpi, 0, bx_mgr_sleep(),
-        work_counter, gthr, coarse, fine);
+        work_counter, gthr, coarse, fine, a.xb);
     return cudaGetLastError();
 }
 
@@ -835,14 +823,33 @@ static cudaError_t bx_launch_subs(const BxArgs& a) {
     }
 }
 
+// kernel attributes are per device: brag_create calls this with the engine's device current
+template <int MAXT, int SUBS>
+static cudaError_t bx_init_one() {
+    return cudaFuncSetAttribute(bm25x_scan_kernel<MAXT, SUBS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BX_SMEM_MAX);
+}
+cudaError_t bm25x_init_device() {
+    cudaError_t e = bx_init_one<8, 1>();
+    if (e == cudaSuccess) e = bx_init_one<8, 2>();
+    if (e == cudaSuccess) e = bx_init_one<8, 4>();
+    if (e == cudaSuccess) e = bx_init_one<16, 1>();
+    if (e == cudaSuccess) e = bx_init_one<16, 2>();
+    if (e == cudaSuccess) e = bx_init_one<16, 4>();
+    if (e == cudaSuccess) e = bx_init_one<32, 1>();
+    if (e == cudaSuccess) e = bx_init_one<32, 2>();
+    if (e == cudaSuccess) e = bx_init_one<32, 4>();
+    return e;
+}
+
 cudaError_t bm25x_scan(const int64_t* term_ptr, const uint2* post, const uint32_t* sub_off, const int32_t* bm_row,
                        const uint32_t* bits, const uint32_t* bits_hi, const float2* wrange, const float* tau, int64_t V,
                        int64_t n_docs, const int32_t* q_ptr,
                        const int32_t* q_terms, const double* q_vals, int B, int max_terms, const uint32_t* mask,
-                       int k_sel, uint64_t* part, const Bm25Plan& plan, void* scratch, cudaStream_t st) {
+                       int k_sel, uint64_t* part, const Bm25Plan& plan, void* scratch, cudaStream_t st,
+                       const ShardBounds& xb) {
     if (!bm25x_supported(max_terms, k_sel)) return cudaErrorInvalidValue;
     const BxArgs a{term_ptr, post, sub_off, bm_row, bits, bits_hi, wrange, tau, V, n_docs, q_ptr, q_terms, q_vals, B,
-                   mask, k_sel, part, &plan, scratch, st};
+                   mask, k_sel, part, &plan, scratch, st, xb};
     switch (bx_maxt(max_terms)) {
         case 8: return bx_launch_subs<8>(a);
         case 16: return bx_launch_subs<16>(a);

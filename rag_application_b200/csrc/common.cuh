@@ -92,6 +92,42 @@ __device__ __forceinline__ uint32_t hist_bound(const uint32_t* __restrict__ coar
     return (uint32_t)(cb * HIST_FINE_PER_COARSE + 4 * FL + fb) << HIST_FINE_SHIFT;
 }
 
+// ---------------------------------------------------------------- cross-shard bounds (row sharding, shard.cu)
+// Any shard's k-th best score is a lower bound of the global k-th best, so the shards of one box tell each other
+// their bounds while they scan: rank g owns one word per (list, query) inside its peer-mapped window,
+// (epoch << 32 | bound); a bound manager that raises its query's bound above everything it knew pushes it into every
+// peer's word with a system-scope atomicMax over NVLink, and folds what the peers pushed into its own gthr.  The epoch
+// (one per sharded call, the same on every rank) keeps a word written for another batch from being used: a newer
+// epoch replaces an older one under max, an older one never survives, and a reader ignores any epoch but its own.
+struct ShardBounds {
+    unsigned long long* const* peers = nullptr;   // device table [world]: rank g's words of this list (peers[rank] = own)
+    const unsigned* epoch = nullptr;              // device word holding the current sharded call's epoch
+    int world = 0, rank = 0;
+};
+
+// Whole warp, `bound` warp-uniform: publish a query's bound locally and, when sharded, to the peers.
+__device__ __forceinline__ void publish_bound(uint32_t* __restrict__ gthr, int q, uint32_t bound, const ShardBounds& xb,
+                                              int lane) {
+    if (xb.world <= 1) {
+        if (lane == 0 && bound != 0u) atomicMax(gthr + q, bound);
+        return;
+    }
+    const uint32_t ep = *reinterpret_cast<const volatile unsigned*>(xb.epoch);
+    uint32_t old = 0u, remote = 0u;
+    if (lane == 0) {
+        unsigned long long x;
+        asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(x) : "l"(xb.peers[xb.rank] + q) : "memory");
+        if ((uint32_t)(x >> 32) == ep) remote = (uint32_t)x;
+        const uint32_t best = max(bound, remote);
+        if (best != 0u) old = atomicMax(gthr + q, best);
+    }
+    old = __shfl_sync(0xFFFFFFFFu, old, 0);
+    remote = __shfl_sync(0xFFFFFFFFu, remote, 0);
+    // only a bound that beats everything this rank knew is news to a peer
+    if (bound > old && bound > remote && lane < xb.world && lane != xb.rank)
+        atomicMax_system(xb.peers[lane] + q, ((unsigned long long)ep << 32) | (unsigned long long)bound);
+}
+
 // ---------------------------------------------------------------- term-major CSR walks
 // term owning posting i of a term-major CSR: the last t with term_ptr[t] <= i (empty terms are skipped)
 __device__ __forceinline__ int64_t term_of_posting(const int64_t* __restrict__ term_ptr, int64_t V, int64_t i) {

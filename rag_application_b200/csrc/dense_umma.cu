@@ -195,7 +195,7 @@ dense_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
                   int64_t rows_per_chunk, int share,
                   const uint32_t* __restrict__ mask, int k_sel, uint32_t idesc, uint64_t* __restrict__ lists,
                   int* __restrict__ counts, uint32_t* __restrict__ gthr, uint32_t* __restrict__ coarse,
-                  uint32_t* __restrict__ fine) {
+                  uint32_t* __restrict__ fine, const ShardBounds xb) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     UmSmem& S = *reinterpret_cast<UmSmem*>(smem_raw);   // keeps the shared address space (LDS/STS in the sort)
     if ((smem_u32(smem_raw) & 1023u) != 0u) __trap();   // 128B-swizzle atoms need 1024-byte alignment
@@ -287,8 +287,7 @@ dense_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
         while (true) {
             const int done = *reinterpret_cast<volatile int*>(&S.epi_done);
             for (int q = q_lo + (int)blockIdx.x; q < q_hi; q += (int)gridDim.x) {
-                const uint32_t bound = hist_bound(coarse, fine, q, (uint32_t)k_sel, lane);
-                if (lane == 0 && bound != 0u) atomicMax(gthr + q, bound);
+                publish_bound(gthr, q, hist_bound(coarse, fine, q, (uint32_t)k_sel, lane), xb, lane);
             }
             if (done >= 4) break;
             __nanosleep(500);
@@ -441,11 +440,10 @@ dense_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
 // Publishes every query's bound from its histograms (one warp per query): run after the seed launch so that the
 // main launch starts with the seed rows' k_sel-th best score instead of flooding its first tile into the lists.
 __global__ void um_bound_kernel(const uint32_t* __restrict__ coarse, const uint32_t* __restrict__ fine,
-                                uint32_t* __restrict__ gthr, int q_lo, int q_hi, int k_sel) {
+                                uint32_t* __restrict__ gthr, int q_lo, int q_hi, int k_sel, const ShardBounds xb) {
     const int q = q_lo + (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5);
     if (q >= q_hi) return;
-    const uint32_t bound = hist_bound(coarse, fine, q, (uint32_t)k_sel, (int)(threadIdx.x & 31));
-    if ((threadIdx.x & 31) == 0 && bound != 0u) atomicMax(gthr + q, bound);
+    publish_bound(gthr, q, hist_bound(coarse, fine, q, (uint32_t)k_sel, (int)(threadIdx.x & 31)), xb, (int)(threadIdx.x & 31));
 }
 
 // Seed bound: per query, the k_sel-th largest of the seed_tiles * 4 per-tile best scores.  They are scores of
@@ -598,19 +596,18 @@ cudaError_t make_tmap_2d(void* tmap_out, const void* base, int64_t rows, int d, 
     return cudaSuccess;
 }
 
+// kernel attributes are per device: brag_create calls this with the engine's device current
+cudaError_t dense_umma_init_device() {
+    cudaError_t e = cudaFuncSetAttribute(dense_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(UmSmem));
+    if (e != cudaSuccess) return e;
+    return cudaFuncSetAttribute(dense_umma_select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SELK_CAP * 8);
+}
+
 cudaError_t dense_umma_scan(const void* X16, int dtype, int64_t n, int d, const void* Q16, int B,
                             const uint32_t* mask, int k_sel, uint64_t* cand, void* scratch, const UmmaPlan& plan,
-                            void* tmap_x, void* tmap_q, cudaStream_t st, int* launches) {
+                            void* tmap_x, void* tmap_q, cudaStream_t st, int* launches, const ShardBounds& xb) {
     (void)X16; (void)Q16;
-    static bool attr_set = false;
     const size_t smem = sizeof(UmSmem);
-    if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(dense_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) return e;
-        e = cudaFuncSetAttribute(dense_umma_select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SELK_CAP * 8);
-        if (e != cudaSuccess) return e;
-        attr_set = true;
-    }
     CUtensorMap tq, tx;
     memcpy(&tq, tmap_q, sizeof tq);
     memcpy(&tx, tmap_x, sizeof tx);
@@ -636,7 +633,7 @@ cudaError_t dense_umma_scan(const void* X16, int dtype, int64_t n, int d, const 
         const int nq = std::min(B - qb0 * UM_BM, nqb * UM_BM);
         if (n_seed > 0) {
             dense_umma_kernel<<<n_seed, UM_THREADS, smem, st>>>(tq, tx, n, d, B, qb0, nqb, seedv, n_seed, seed_stride, 1, mask,
-                                                               k_sel, idesc, lists, counts, gthr, coarse, fine);
+                                                               k_sel, idesc, lists, counts, gthr, coarse, fine, ShardBounds());
             if ((err = cudaGetLastError()) != cudaSuccess) return err;
             um_seed_bound_kernel<<<nq, 256, 0, st>>>(seedv, n_seed, qb0 * UM_BM, qb0 * UM_BM + nq, k_sel, gthr);
             if ((err = cudaGetLastError()) != cudaSuccess) return err;
@@ -646,11 +643,11 @@ cudaError_t dense_umma_scan(const void* X16, int dtype, int64_t n, int d, const 
         const int share = (um_share() > 1 && nqb % um_share() == 0 && n_main % um_share() == 0 && n_tiles >= n_main) ? um_share() : 1;
         const int64_t rows_per_chunk = (n_tiles + n_main / share - 1) / (n_main / share) * UM_BN;
         dense_umma_kernel<<<n_main, UM_THREADS, smem, st>>>(tq, tx, n, d, B, qb0, nqb, nullptr, 0, rows_per_chunk, share, mask,
-                                                           k_sel, idesc, lists, counts, gthr, coarse, fine);
+                                                           k_sel, idesc, lists, counts, gthr, coarse, fine, xb);
         if ((err = cudaGetLastError()) != cudaSuccess) return err;
         // final bounds from the complete histograms (a CTA's manager stops with its own CTA, so the bounds it left
         // may predate the last pushes of the others): the selection then gathers ~k_sel keys per query, not more
-        um_bound_kernel<<<(nq + 7) / 8, 256, 0, st>>>(coarse, fine, gthr, qb0 * UM_BM, qb0 * UM_BM + nq, k_sel);
+        um_bound_kernel<<<(nq + 7) / 8, 256, 0, st>>>(coarse, fine, gthr, qb0 * UM_BM, qb0 * UM_BM + nq, k_sel, xb);
         if ((err = cudaGetLastError()) != cudaSuccess) return err;
         ++nl;
         dense_umma_select_kernel<<<nq, SELK_THREADS, SELK_CAP * 8, st>>>(lists, counts, gthr, plan.n_chunks, B, qb0, nqb,

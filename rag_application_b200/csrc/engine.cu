@@ -3,6 +3,7 @@
 
 #include <algorithm>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include <stdexcept>
@@ -10,6 +11,7 @@
 #include <vector>
 
 #include "../../include/brag.h"
+#include "common.cuh"
 #include "kernels.h"
 
 namespace {
@@ -117,6 +119,26 @@ struct StageEvent {
     cudaEvent_t a, b;
 };
 
+// Row sharding (shard.cu): this rank's window, the peers' mappings of theirs, and the device tables the kernels read.
+struct ShardState {
+    bool connected = false;
+    int rank = 0, world = 1;
+    bool bounds = true;                    // exchange score bounds across the shards while scanning
+    brag::ShardWindowLayout lay{};
+    uint8_t* window = nullptr;             // own (cudaMalloc)
+    uint8_t* peer[16] = {nullptr};         // every rank's window as seen from this device (peer[rank] = window)
+    bool ipc_open[16] = {false};
+};
+
+// Where a stage's final list goes in a sharded call: packed keys with global rows, to a local buffer or into the
+// world's windows -- and which cross-shard bound words its scan exchanges.
+struct ListSink {
+    int list = 0;                          // 0 dense, 1 sparse
+    uint64_t* local_out = nullptr;         // [2][B][k] keys (collective variant); NULL = push into the windows
+    brag::ShardPush push{};
+    brag::ShardBounds xb{};
+};
+
 }  // namespace
 
 struct brag_engine {
@@ -133,8 +155,9 @@ struct brag_engine {
     std::map<int, MaskBuf> masks;
     // scratch (grow-only)
     DevBuf qs, q16, part, tmp_a, tmp_b, keys1, keys2, umma_scratch, work_counter, g_thr;
-    DevBuf h_in[6], h_out[4];      // staging for host-pointer calls
-    DevBuf hyb_ids, hyb_counts, hyb_scores, cp_prefix, cp_tmp, cp_chunks;
+    DevBuf h_in[6], h_out[6];      // staging for host-pointer calls
+    DevBuf hyb_ids, hyb_counts, hyb_scores, cp_prefix, cp_tmp, cp_chunks, shard_keys;
+    ShardState shard;
     std::vector<int32_t> qptr_host;
     alignas(64) unsigned char tmap_q[128];
     // profiling
@@ -392,7 +415,9 @@ bool ensure_sparse_compact(brag_engine* e, SparseSpace& s, int mask_id, const ui
 }
 
 void dense_topk_dev(brag_engine* e, DenseSpace& s, const float* Q, int B, int k, int mask_id, const uint32_t* mask,
-                    float* out_scores, int64_t* out_ids, int32_t* out_counts, cudaStream_t st) {
+                    float* out_scores, int64_t* out_ids, int32_t* out_counts, cudaStream_t st,
+                    const ListSink* sink = nullptr) {
+    const brag::ShardBounds xb = sink ? sink->xb : brag::ShardBounds();
     REQUIRE(B >= 1 && k >= 1 && k <= 512, "dense_topk: need B >= 1 and 1 <= k <= 512");
     const int k_sel = k_select(k);
     int path = pick_path(e, s, B);
@@ -423,7 +448,7 @@ void dense_topk_dev(brag_engine* e, DenseSpace& s, const float* Q, int B, int k,
             void* scratch = e->umma_scratch.ensure(plan.scratch_bytes);
             int launches = 0;
             CK(brag::dense_umma_scan(X, s.dtype, n, s.d, q16, B, scan_mask, k_sel, cand, scratch, plan, tmap_x,
-                                     e->tmap_q, st, &launches));
+                                     e->tmap_q, st, &launches, xb));
             e->kernel_launches += 1 + launches;
         } else {
             CK(brag::round_queries(Q, B, s.d, s.dtype, qs, nullptr, B, st));
@@ -447,7 +472,10 @@ void dense_topk_dev(brag_engine* e, DenseSpace& s, const float* Q, int B, int k,
             CK(brag::remap_keys(cand2, (int64_t)B * k_sel, s.cp_rowmap, st));
             e->kernel_launches += 1;
         }
-        CK(brag::finalize_keys(cand2, B, k_sel, k, false, e->id_offset, out_scores, out_ids, out_counts, st));
+        if (sink)
+            CK(brag::shard_finalize_push(cand2, B, k_sel, k, e->id_offset, sink->list, sink->local_out, sink->push, st));
+        else
+            CK(brag::finalize_keys(cand2, B, k_sel, k, false, e->id_offset, out_scores, out_ids, out_counts, st));
         e->kernel_launches += 2;
     }
 }
@@ -479,12 +507,23 @@ int max_terms_host(const int32_t* q_ptr, int B) {
     for (int b = 0; b < B; ++b) mx = std::max(mx, q_ptr[b + 1] - q_ptr[b]);
     return mx;
 }
+// host-pointer calls: the sparse queries are validated here (the device-pointer contract is the caller's)
+void check_host_queries(const int32_t* q_ptr, const int32_t* q_terms, int B, int max_terms, const char* who) {
+    for (int b = 0; b < B; ++b) {
+        REQUIRE(q_ptr[b + 1] >= q_ptr[b], std::string(who) + ": q_ptr must be non-decreasing");
+        REQUIRE(max_terms < 0 || q_ptr[b + 1] - q_ptr[b] <= max_terms, std::string(who) + ": a query is longer than max_terms");
+        for (int i = q_ptr[b] + 1; i < q_ptr[b + 1]; ++i)
+            REQUIRE(q_terms[i] > q_terms[i - 1], std::string(who) + ": query term rows must be strictly ascending");
+    }
+}
 
 // max_terms: longest query of the batch, or -1 when only the device copy of q_ptr is at hand
 void sparse_topk_dev(brag_engine* e, SparseSpace& full, const int32_t* q_ptr, const int32_t* q_terms,
                      const double* q_vals, int B, int k, int mask_id, const uint32_t* mask, float* out_scores,
-                     int64_t* out_ids, int32_t* out_counts, int max_terms, cudaStream_t st) {
+                     int64_t* out_ids, int32_t* out_counts, int max_terms, cudaStream_t st,
+                     const ListSink* sink = nullptr) {
     REQUIRE(B >= 1 && k >= 1 && k <= 512, "sparse_topk: need B >= 1 and 1 <= k <= 512");
+    const brag::ShardBounds xb = sink ? sink->xb : brag::ShardBounds();
     // documents actually scanned: the whole space, or the index of the documents passing the filter
     const bool compact = mask != nullptr && !e->no_compact && ensure_sparse_compact(e, full, mask_id, mask, B, st);
     SparseSpace& s = compact ? *full.cp : full;
@@ -517,10 +556,10 @@ void sparse_topk_dev(brag_engine* e, SparseSpace& full, const int32_t* q_ptr, co
         StageTimer t(e, 2, st);
         if (bitmap)
             CK(brag::bm25x_scan(s.term_ptr, s.post, s.sub_off, s.bm_row, s.bits, s.bits_hi, s.wrange, s.tau, s.V, s.n_docs, q_ptr, q_terms,
-                                q_vals, B, max_terms, mask, k, part, plan, scratch, st));
+                                q_vals, B, max_terms, mask, k, part, plan, scratch, st, xb));
         else
             CK(brag::bm25_scan(s.term_ptr, s.post, s.sub_off, s.V, s.n_docs, q_ptr, q_terms, q_vals, B, mask, k,
-                               part, plan, scratch, st));
+                               part, plan, scratch, st, xb));
         e->kernel_launches += 1 + ((bitmap && plan.seed_tiles > 0) ? 1 : 0);
     }
     {
@@ -535,13 +574,16 @@ void sparse_topk_dev(brag_engine* e, SparseSpace& full, const int32_t* q_ptr, co
         uint32_t* gthr = reinterpret_cast<uint32_t*>(sp + 256);
         const uint32_t* coarse = reinterpret_cast<const uint32_t*>(sp + 256 + plan.gthr_bytes);
         const uint32_t* fine = reinterpret_cast<const uint32_t*>(sp + 256 + plan.gthr_bytes + plan.coarse_bytes);
-        CK(brag::publish_bounds(coarse, fine, gthr, B, k, st));
+        CK(brag::publish_bounds(coarse, fine, gthr, B, k, st, xb));
         CK(brag::merge_key_lists(part, P, B, k, ta, tb, merged, k, st, &launches, gthr));
         if (compact) {
             CK(brag::remap_keys(merged, (int64_t)B * k, full.cp_rowmap, st));
             launches += 1;
         }
-        CK(brag::finalize_keys(merged, B, k, k, false, e->id_offset, out_scores, out_ids, out_counts, st));
+        if (sink)
+            CK(brag::shard_finalize_push(merged, B, k, k, e->id_offset, sink->list, sink->local_out, sink->push, st));
+        else
+            CK(brag::finalize_keys(merged, B, k, k, false, e->id_offset, out_scores, out_ids, out_counts, st));
         e->kernel_launches += launches + 2;
     }
 }
@@ -556,6 +598,36 @@ const T* to_dev(DevBuf& buf, const T* host, size_t n, cudaStream_t st) {
 template <typename T>
 void to_host(T* host, const T* dev, size_t n, cudaStream_t st) {
     if (n && host) CK(cudaMemcpyAsync(host, dev, n * sizeof(T), cudaMemcpyDeviceToHost, st));
+}
+
+// ---- row sharding: window lifetime and the per-call kernel arguments ---------------------------
+void shard_release(brag_engine* e) {
+    ShardState& sh = e->shard;
+    for (int g = 0; g < 16; ++g) {
+        if (sh.ipc_open[g] && sh.peer[g]) cudaIpcCloseMemHandle(sh.peer[g]);
+        sh.peer[g] = nullptr;
+        sh.ipc_open[g] = false;
+    }
+    if (sh.window) cudaFree(sh.window);
+    sh = ShardState();
+}
+
+brag::ShardPush shard_push_args(const ShardState& sh) {
+    brag::ShardPush p;
+    p.windows = reinterpret_cast<uint8_t* const*>(sh.window + sh.lay.tables_off);
+    p.epoch = reinterpret_cast<const unsigned*>(sh.window + sh.lay.epoch_off);
+    p.world = sh.world; p.rank = sh.rank;
+    p.slots_off = sh.lay.slots_off; p.slot_bytes = sh.lay.slot_bytes; p.flags_off = sh.lay.flags_off;
+    return p;
+}
+
+brag::ShardBounds shard_bound_args(const ShardState& sh, int list) {
+    brag::ShardBounds xb;
+    if (!sh.bounds || sh.world <= 1) return xb;
+    xb.peers = reinterpret_cast<unsigned long long* const*>(sh.window + sh.lay.tables_off) + (size_t)(1 + list) * sh.world;
+    xb.epoch = reinterpret_cast<const unsigned*>(sh.window + sh.lay.epoch_off);
+    xb.world = sh.world; xb.rank = sh.rank;
+    return xb;
 }
 
 template <typename F>
@@ -578,7 +650,7 @@ int guarded(F&& f) {
 extern "C" {
 
 const char* brag_last_error(void) { return g_err.c_str(); }
-int brag_version(void) { return 1; }
+int brag_version(void) { return 2; }
 
 int brag_create(int device, brag_engine** out) {
     return guarded([&] {
@@ -592,6 +664,11 @@ int brag_create(int device, brag_engine** out) {
         cudaDeviceProp prop;
         CK(cudaGetDeviceProperties(&prop, device));
         REQUIRE(prop.major >= 10, "brag_create: this library is built for sm_100a (B200) only");
+        CK(brag::dense_umma_init_device());
+        CK(brag::select_init_device());
+        CK(brag::bm25_init_device());
+        CK(brag::bm25x_init_device());
+        CK(brag::shard_init_device());
         auto* e = new brag_engine();
         e->device = device;
         e->num_sms = prop.multiProcessorCount;
@@ -613,6 +690,8 @@ int brag_destroy(brag_engine* e) {
         for (DevBuf* b : bufs) b->release();
         for (auto& b : e->h_in) b.release();
         for (auto& b : e->h_out) b.release();
+        e->shard_keys.release();
+        shard_release(e);
         for (auto& ev : e->events) { cudaEventDestroy(ev.a); cudaEventDestroy(ev.b); }
         for (auto ev : e->pool) cudaEventDestroy(ev);
         delete e;
@@ -939,7 +1018,7 @@ int brag_dense_rescore(brag_engine* e, const char* name, const float* Q, int32_t
 }
 
 int brag_sparse_topk(brag_engine* e, const char* name, const int32_t* q_ptr, const int32_t* q_terms,
-                     const double* q_vals, int32_t B, int32_t k, int32_t mask_id, float* out_scores,
+                     const double* q_vals, int32_t B, int32_t k, int32_t mask_id, int32_t max_terms, float* out_scores,
                      int64_t* out_ids, int32_t* out_counts, int32_t on_device, void* stream) {
     return guarded([&] {
         REQUIRE(e && name && q_ptr && out_scores && out_ids && out_counts, "brag_sparse_topk: NULL argument");
@@ -948,21 +1027,19 @@ int brag_sparse_topk(brag_engine* e, const char* name, const int32_t* q_ptr, con
         SparseSpace& s = sparse_space(e, name);
         const uint32_t* mask = mask_ptr(e, mask_id, s.n_docs);
         if (on_device) {
-            sparse_topk_dev(e, s, q_ptr, q_terms, q_vals, B, k, mask_id, mask, out_scores, out_ids, out_counts, -1, st);
+            sparse_topk_dev(e, s, q_ptr, q_terms, q_vals, B, k, mask_id, mask, out_scores, out_ids, out_counts,
+                            max_terms, st);
         } else {
             const size_t nt = (size_t)q_ptr[B];
-            for (int b = 0; b < B; ++b) {
-                REQUIRE(q_ptr[b + 1] >= q_ptr[b], "brag_sparse_topk: q_ptr must be non-decreasing");
-                for (int i = q_ptr[b] + 1; i < q_ptr[b + 1]; ++i)
-                    REQUIRE(q_terms[i] > q_terms[i - 1], "brag_sparse_topk: query term rows must be strictly ascending");
-            }
+            check_host_queries(q_ptr, q_terms, B, max_terms, "brag_sparse_topk");
             const int32_t* dp = to_dev(e->h_in[0], q_ptr, (size_t)B + 1, st);
             const int32_t* dt = to_dev(e->h_in[1], q_terms, nt, st);
             const double* dv = to_dev(e->h_in[2], q_vals, nt, st);
             float* ds = e->h_out[0].as<float>((size_t)B * k);
             int64_t* di = e->h_out[1].as<int64_t>((size_t)B * k);
             int32_t* dc = e->h_out[2].as<int32_t>(B);
-            sparse_topk_dev(e, s, dp, dt, dv, B, k, mask_id, mask, ds, di, dc, max_terms_host(q_ptr, B), st);
+            sparse_topk_dev(e, s, dp, dt, dv, B, k, mask_id, mask, ds, di, dc,
+                            max_terms < 0 ? max_terms_host(q_ptr, B) : max_terms, st);
             to_host(out_scores, ds, (size_t)B * k, st);
             to_host(out_ids, di, (size_t)B * k, st);
             to_host(out_counts, dc, (size_t)B, st);
@@ -1053,8 +1130,8 @@ int brag_merge_topk(brag_engine* e, const float* scores, const int64_t* ids, con
 
 int brag_hybrid_topk(brag_engine* e, const char* dense_name, const char* sparse_name, const float* Q,
                      const int32_t* q_ptr, const int32_t* q_terms, const double* q_vals, int32_t B, int32_t k,
-                     int32_t mask_id, double* out_scores, int64_t* out_ids, int32_t* out_counts, int32_t on_device,
-                     void* stream) {
+                     int32_t mask_id, int32_t max_terms, double* out_scores, int64_t* out_ids, int32_t* out_counts,
+                     int32_t on_device, void* stream) {
     return guarded([&] {
         REQUIRE(e && dense_name && sparse_name && Q && q_ptr && out_scores && out_ids && out_counts,
                 "brag_hybrid_topk: NULL argument");
@@ -1076,6 +1153,8 @@ int brag_hybrid_topk(brag_engine* e, const char* dense_name, const char* sparse_
         int32_t* oc = out_counts;
         if (!on_device) {
             const size_t nt = (size_t)q_ptr[B];
+            check_host_queries(q_ptr, q_terms, B, max_terms, "brag_hybrid_topk");
+            if (max_terms < 0) max_terms = max_terms_host(q_ptr, B);
             dq = to_dev(e->h_in[0], Q, (size_t)B * ds.d, st);
             dp = to_dev(e->h_in[1], q_ptr, (size_t)B + 1, st);
             dt = to_dev(e->h_in[2], q_terms, nt, st);
@@ -1086,7 +1165,7 @@ int brag_hybrid_topk(brag_engine* e, const char* dense_name, const char* sparse_
         }
         dense_topk_dev(e, ds, dq, B, k, mask_id, mask, scs, ids, cnts, st);
         sparse_topk_dev(e, ss, dp, dt, dv, B, k, mask_id, mask, scs + (size_t)B * k, ids + (size_t)B * k, cnts + B,
-                        on_device ? -1 : max_terms_host(q_ptr, B), st);
+                        max_terms, st);
         {
             StageTimer t(e, 4, st);
             CK(brag::rrf_fuse(ids, cnts, 2, B, k, k, BRAG_TIE_ID, os, oi, oc, st));
@@ -1096,6 +1175,236 @@ int brag_hybrid_topk(brag_engine* e, const char* dense_name, const char* sparse_
             to_host(out_scores, os, (size_t)B * k, st);
             to_host(out_ids, oi, (size_t)B * k, st);
             to_host(out_counts, oc, (size_t)B, st);
+            CK(cudaStreamSynchronize(st));
+        }
+    });
+}
+
+// ---- row sharding across the GPUs of one box (include/brag.h; kernels in shard.cu) ---------------
+int brag_shard_window_create(brag_engine* e, int32_t world, int32_t max_batch, int32_t max_k, void* handle_out) {
+    return guarded([&] {
+        REQUIRE(e && handle_out, "brag_shard_window_create: NULL argument");
+        REQUIRE(world >= 1 && world <= 16 && max_batch >= 1 && max_k >= 1 && max_k <= 512 && (int64_t)world * max_k <= 8192,
+                "brag_shard_window_create: need 1 <= world <= 16, 1 <= max_k <= 512, world * max_k <= 8192");
+        use_device(e);
+        CK(cudaDeviceSynchronize());
+        shard_release(e);
+        ShardState& sh = e->shard;
+        sh.lay = brag::shard_window_layout(world, max_batch, max_k);
+        sh.world = world;
+        CK(cudaMalloc(&sh.window, sh.lay.total));
+        CK(cudaMemset(sh.window, 0, sh.lay.total));
+        cudaIpcMemHandle_t h;
+        static_assert(sizeof(h) == BRAG_SHARD_HANDLE_BYTES, "cudaIpcMemHandle_t is 64 bytes");
+        CK(cudaIpcGetMemHandle(&h, sh.window));
+        std::memcpy(handle_out, &h, sizeof h);
+        const char* nb = getenv("BRAG_SHARD_BOUNDS");      // A/B knob: 0 = no cross-shard bound exchange
+        sh.bounds = !(nb && atoi(nb) == 0);
+    });
+}
+
+int brag_shard_connect(brag_engine* e, int32_t rank, int32_t world, const void* handles, brag_engine* const* local_peers) {
+    return guarded([&] {
+        REQUIRE(e && (handles || local_peers), "brag_shard_connect: need the world's window handles or its engines");
+        ShardState& sh = e->shard;
+        REQUIRE(sh.window && !sh.connected, "brag_shard_connect: call brag_shard_window_create first (once per connect)");
+        REQUIRE(world == sh.world && rank >= 0 && rank < world, "brag_shard_connect: rank / world do not match the window");
+        use_device(e);
+        sh.rank = rank;
+        for (int g = 0; g < world; ++g) {
+            if (g == rank) { sh.peer[g] = sh.window; continue; }
+            if (local_peers) {
+                // engines of this process: enable peer access and use the peer's pointer as it is
+                brag_engine* pe = local_peers[g];
+                REQUIRE(pe && pe->shard.window && pe->shard.lay.total == sh.lay.total,
+                        "brag_shard_connect: a local peer has no window of the same shape");
+                if (pe->device != e->device) {
+                    int can = 0;
+                    CK(cudaDeviceCanAccessPeer(&can, e->device, pe->device));
+                    REQUIRE(can, "brag_shard_connect: no peer access between the devices");
+                    cudaError_t pe_rc = cudaDeviceEnablePeerAccess(pe->device, 0);
+                    if (pe_rc == cudaErrorPeerAccessAlreadyEnabled) cudaGetLastError();
+                    else CK(pe_rc);
+                }
+                sh.peer[g] = pe->shard.window;
+            } else {
+                cudaIpcMemHandle_t h;
+                std::memcpy(&h, static_cast<const uint8_t*>(handles) + (size_t)g * BRAG_SHARD_HANDLE_BYTES, sizeof h);
+                void* p = nullptr;
+                CK(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+                sh.peer[g] = static_cast<uint8_t*>(p);
+                sh.ipc_open[g] = true;
+            }
+        }
+        // device tables: [0] window bases, [1] dense bound words, [2] sparse bound words of every rank
+        std::vector<void*> tab((size_t)3 * world);
+        for (int g = 0; g < world; ++g) {
+            tab[(size_t)g] = sh.peer[g];
+            tab[(size_t)world + g] = sh.peer[g] + sh.lay.xb_off;
+            tab[(size_t)2 * world + g] = sh.peer[g] + sh.lay.xb_off + (size_t)sh.lay.max_batch * sizeof(uint64_t);
+        }
+        CK(cudaMemcpy(sh.window + sh.lay.tables_off, tab.data(), tab.size() * sizeof(void*), cudaMemcpyHostToDevice));
+        sh.connected = true;
+    });
+}
+
+int brag_shard_close(brag_engine* e) {
+    return guarded([&] {
+        REQUIRE(e, "brag_shard_close: NULL engine");
+        use_device(e);
+        CK(cudaDeviceSynchronize());
+        shard_release(e);
+    });
+}
+
+// the two per-shard lists of a batch as packed keys: into `local_out` [2][B][k], or (NULL) into the world's windows
+static void shard_lists_dev(brag_engine* e, DenseSpace& ds, SparseSpace& ss, const float* dq, const int32_t* dp,
+                            const int32_t* dt, const double* dv, int B, int k, int mask_id, const uint32_t* mask,
+                            int max_terms, uint64_t* local_out, cudaStream_t st) {
+    ListSink sink;
+    sink.local_out = local_out;
+    if (local_out == nullptr) sink.push = shard_push_args(e->shard);
+    sink.list = 0;
+    if (local_out == nullptr) sink.xb = shard_bound_args(e->shard, 0);
+    dense_topk_dev(e, ds, dq, B, k, mask_id, mask, nullptr, nullptr, nullptr, st, &sink);
+    sink.list = 1;
+    if (local_out == nullptr) sink.xb = shard_bound_args(e->shard, 1);
+    sparse_topk_dev(e, ss, dp, dt, dv, B, k, mask_id, mask, nullptr, nullptr, nullptr, max_terms, st, &sink);
+}
+
+int brag_shard_local_lists(brag_engine* e, const char* dense_name, const char* sparse_name, const float* Q,
+                           const int32_t* q_ptr, const int32_t* q_terms, const double* q_vals, int32_t B, int32_t k,
+                           int32_t mask_id, int32_t max_terms, uint64_t* out_keys, int32_t on_device, void* stream) {
+    return guarded([&] {
+        REQUIRE(e && dense_name && sparse_name && Q && q_ptr && out_keys, "brag_shard_local_lists: NULL argument");
+        REQUIRE(k >= 1 && k <= 512, "brag_shard_local_lists: need 1 <= k <= 512");
+        use_device(e);
+        cudaStream_t st = (cudaStream_t)stream;
+        DenseSpace& ds = dense_space(e, dense_name);
+        SparseSpace& ss = sparse_space(e, sparse_name);
+        REQUIRE(e->id_offset + std::max(ds.n, ss.n_docs) <= (int64_t)0xFFFFFFFFll, "brag_shard_local_lists: global ids must stay below 2^32");
+        const uint32_t* mask = mask_ptr(e, mask_id, std::max(ds.n, ss.n_docs));
+        if (on_device) {
+            shard_lists_dev(e, ds, ss, Q, q_ptr, q_terms, q_vals, B, k, mask_id, mask, max_terms, out_keys, st);
+        } else {
+            const size_t nt = (size_t)q_ptr[B];
+            check_host_queries(q_ptr, q_terms, B, max_terms, "brag_shard_local_lists");
+            if (max_terms < 0) max_terms = max_terms_host(q_ptr, B);
+            const float* dq = to_dev(e->h_in[0], Q, (size_t)B * ds.d, st);
+            const int32_t* dp = to_dev(e->h_in[1], q_ptr, (size_t)B + 1, st);
+            const int32_t* dt = to_dev(e->h_in[2], q_terms, nt, st);
+            const double* dv = to_dev(e->h_in[3], q_vals, nt, st);
+            uint64_t* dk = e->h_out[0].as<uint64_t>((size_t)2 * B * k);
+            shard_lists_dev(e, ds, ss, dq, dp, dt, dv, B, k, mask_id, mask, max_terms, dk, st);
+            to_host(out_keys, dk, (size_t)2 * B * k, st);
+            CK(cudaStreamSynchronize(st));
+        }
+    });
+}
+
+int brag_shard_fuse(brag_engine* e, const uint64_t* keys, int32_t G, int32_t B, int32_t k, int32_t limit,
+                    int32_t tie_mode, double* out_scores, int64_t* out_ids, int32_t* out_counts, float* stage_scores,
+                    int64_t* stage_ids, int32_t* stage_counts, int32_t on_device, void* stream) {
+    return guarded([&] {
+        REQUIRE(e && keys && out_scores && out_ids && out_counts, "brag_shard_fuse: NULL argument");
+        REQUIRE((stage_scores != nullptr) == (stage_ids != nullptr) && (stage_ids != nullptr) == (stage_counts != nullptr),
+                "brag_shard_fuse: pass all three stage outputs or none");
+        REQUIRE(G >= 1 && B >= 1 && k >= 1 && k <= 512 && (int64_t)G * k <= 8192 && limit >= 1 && limit <= 1024,
+                "brag_shard_fuse: need G * k <= 8192, k <= 512, limit <= 1024");
+        use_device(e);
+        cudaStream_t st = (cudaStream_t)stream;
+        StageTimer t(e, 5, st);
+        e->kernel_launches += 1;
+        if (on_device) {
+            CK(brag::shard_fuse(keys, brag::ShardPush(), G, B, k, limit, tie_mode, out_scores, out_ids, out_counts,
+                                stage_scores, stage_ids, stage_counts, st));
+        } else {
+            const uint64_t* dk = to_dev(e->h_in[0], keys, (size_t)G * 2 * B * k, st);
+            double* os = e->h_out[0].as<double>((size_t)B * limit);
+            int64_t* oi = e->h_out[1].as<int64_t>((size_t)B * limit);
+            int32_t* oc = e->h_out[2].as<int32_t>(B);
+            float* ts = stage_scores ? e->h_out[3].as<float>((size_t)2 * B * k) : nullptr;
+            int64_t* ti = stage_scores ? e->h_out[4].as<int64_t>((size_t)2 * B * k) : nullptr;
+            int32_t* tc = stage_scores ? e->h_out[5].as<int32_t>((size_t)2 * B) : nullptr;
+            CK(brag::shard_fuse(dk, brag::ShardPush(), G, B, k, limit, tie_mode, os, oi, oc, ts, ti, tc, st));
+            to_host(out_scores, os, (size_t)B * limit, st);
+            to_host(out_ids, oi, (size_t)B * limit, st);
+            to_host(out_counts, oc, (size_t)B, st);
+            if (stage_scores) {
+                to_host(stage_scores, ts, (size_t)2 * B * k, st);
+                to_host(stage_ids, ti, (size_t)2 * B * k, st);
+                to_host(stage_counts, tc, (size_t)2 * B, st);
+            }
+            CK(cudaStreamSynchronize(st));
+        }
+    });
+}
+
+int brag_shard_hybrid_topk(brag_engine* e, const char* dense_name, const char* sparse_name, const float* Q,
+                           const int32_t* q_ptr, const int32_t* q_terms, const double* q_vals, int32_t B, int32_t k,
+                           int32_t mask_id, int32_t max_terms, double* out_scores, int64_t* out_ids,
+                           int32_t* out_counts, float* stage_scores, int64_t* stage_ids, int32_t* stage_counts,
+                           int32_t on_device, void* stream) {
+    return guarded([&] {
+        REQUIRE(e && dense_name && sparse_name && Q && q_ptr && out_scores && out_ids && out_counts,
+                "brag_shard_hybrid_topk: NULL argument");
+        REQUIRE((stage_scores != nullptr) == (stage_ids != nullptr) && (stage_ids != nullptr) == (stage_counts != nullptr),
+                "brag_shard_hybrid_topk: pass all three stage outputs or none");
+        ShardState& sh = e->shard;
+        REQUIRE(sh.connected, "brag_shard_hybrid_topk: the engine is not connected to its peers (brag_shard_connect)");
+        REQUIRE(B >= 1 && B <= sh.lay.max_batch && k >= 1 && k <= sh.lay.max_k,
+                "brag_shard_hybrid_topk: batch or k exceed what the window was created for");
+        use_device(e);
+        cudaStream_t st = (cudaStream_t)stream;
+        DenseSpace& ds = dense_space(e, dense_name);
+        SparseSpace& ss = sparse_space(e, sparse_name);
+        REQUIRE(e->id_offset + std::max(ds.n, ss.n_docs) <= (int64_t)0xFFFFFFFFll, "brag_shard_hybrid_topk: global ids must stay below 2^32");
+        const uint32_t* mask = mask_ptr(e, mask_id, std::max(ds.n, ss.n_docs));
+        const float* dq = Q;
+        const int32_t *dp = q_ptr, *dt = q_terms;
+        const double* dv = q_vals;
+        double* os = out_scores;
+        int64_t* oi = out_ids;
+        int32_t* oc = out_counts;
+        float* ts = stage_scores;
+        int64_t* ti = stage_ids;
+        int32_t* tc = stage_counts;
+        if (!on_device) {
+            const size_t nt = (size_t)q_ptr[B];
+            check_host_queries(q_ptr, q_terms, B, max_terms, "brag_shard_hybrid_topk");
+            if (max_terms < 0) max_terms = max_terms_host(q_ptr, B);
+            dq = to_dev(e->h_in[0], Q, (size_t)B * ds.d, st);
+            dp = to_dev(e->h_in[1], q_ptr, (size_t)B + 1, st);
+            dt = to_dev(e->h_in[2], q_terms, nt, st);
+            dv = to_dev(e->h_in[3], q_vals, nt, st);
+            os = e->h_out[0].as<double>((size_t)B * k);
+            oi = e->h_out[1].as<int64_t>((size_t)B * k);
+            oc = e->h_out[2].as<int32_t>(B);
+            if (stage_scores) {
+                ts = e->h_out[3].as<float>((size_t)2 * B * k);
+                ti = e->h_out[4].as<int64_t>((size_t)2 * B * k);
+                tc = e->h_out[5].as<int32_t>((size_t)2 * B);
+            }
+        }
+        // one epoch per call, bumped on the device so that a CUDA-graph replay of this call stays in step with its peers
+        CK(brag::shard_next_epoch(reinterpret_cast<unsigned*>(sh.window + sh.lay.epoch_off), st));
+        shard_lists_dev(e, ds, ss, dq, dp, dt, dv, B, k, mask_id, mask, max_terms, nullptr, st);
+        const brag::ShardPush push = shard_push_args(sh);
+        {
+            StageTimer t(e, 5, st);
+            CK(brag::shard_signal(push, st));
+            CK(brag::shard_fuse(nullptr, push, sh.world, B, k, k, BRAG_TIE_ID, os, oi, oc, ts, ti, tc, st));
+            e->kernel_launches += 3;
+        }
+        if (!on_device) {
+            to_host(out_scores, os, (size_t)B * k, st);
+            to_host(out_ids, oi, (size_t)B * k, st);
+            to_host(out_counts, oc, (size_t)B, st);
+            if (stage_scores) {
+                to_host(stage_scores, ts, (size_t)2 * B * k, st);
+                to_host(stage_ids, ti, (size_t)2 * B * k, st);
+                to_host(stage_counts, tc, (size_t)2 * B, st);
+            }
             CK(cudaStreamSynchronize(st));
         }
     });

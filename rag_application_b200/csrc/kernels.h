@@ -5,6 +5,16 @@
 
 namespace brag {
 
+struct ShardBounds;     // common.cuh: cross-shard bound exchange of a sharded call (default = none)
+
+// Per-device kernel attributes (opt-in shared memory): brag_create calls these with the engine's device current, so a
+// second engine on another GPU of the same process gets them too.
+cudaError_t dense_umma_init_device();
+cudaError_t select_init_device();
+cudaError_t bm25_init_device();
+cudaError_t bm25x_init_device();
+cudaError_t shard_init_device();
+
 // ---- dense_gemv.cu
 cudaError_t dense_gemv_scan(const void* X, int dtype, int64_t n, int d, const float* Q, int B,
                             const uint32_t* mask, int k_sel, uint64_t* part, int grid, cudaStream_t st,
@@ -26,7 +36,8 @@ cudaError_t dense_umma_plan(int64_t n, int d, int B, int k_sel, int num_sms, Umm
 // cand: [B][k_sel] keys, best first (0 = empty slot).
 cudaError_t dense_umma_scan(const void* X16, int dtype, int64_t n, int d, const void* Q16, int B,
                             const uint32_t* mask, int k_sel, uint64_t* cand, void* scratch,
-                            const UmmaPlan& plan, void* tmap_x, void* tmap_q, cudaStream_t st, int* launches);
+                            const UmmaPlan& plan, void* tmap_x, void* tmap_q, cudaStream_t st, int* launches,
+                            const ShardBounds& xb);
 // builds a CUtensorMap (128 bytes) for a [rows, d] 16-bit row-major matrix, box = [box_rows, 64]
 cudaError_t make_tmap_2d(void* tmap_out, const void* base, int64_t rows, int d, int box_rows);
 
@@ -36,7 +47,8 @@ cudaError_t make_tmap_2d(void* tmap_out, const void* base, int64_t rows, int d, 
 cudaError_t merge_key_lists(const uint64_t* in, int P, int B, int kk, uint64_t* tmp_a, uint64_t* tmp_b,
                             uint64_t* out, int kout, cudaStream_t st, int* launches, const uint32_t* bound = nullptr);
 // gthr[q] = max(gthr[q], bound of query q's complete score histograms) -- see common.cuh
-cudaError_t publish_bounds(const uint32_t* coarse, const uint32_t* fine, uint32_t* gthr, int B, int k, cudaStream_t st);
+cudaError_t publish_bounds(const uint32_t* coarse, const uint32_t* fine, uint32_t* gthr, int B, int k, cudaStream_t st,
+                           const ShardBounds& xb);
 size_t merge_tmp_elems(int P, int B, int kk);
 // round queries to the storage dtype: Qs f32 (rounded values) and optional 16-bit copy (padded rows zero)
 cudaError_t round_queries(const float* Q, int B, int d, int dtype, float* Qs, void* Q16, int Bpad,
@@ -57,6 +69,37 @@ cudaError_t rrf_fuse(const int64_t* ids, const int32_t* counts, int L, int B, in
 cudaError_t merge_scored_lists(const float* scores, const int64_t* ids, const int32_t* counts, int G,
                                int B, int k, float* out_scores, int64_t* out_ids, int32_t* out_counts,
                                cudaStream_t st);
+
+// ---- shard.cu: row sharding across the GPUs of one box (exchange fused into the tail kernels)
+// One window per engine (a single cudaMalloc, peer-mapped by every other rank), same layout on every rank.
+struct ShardWindowLayout {
+    int world, max_batch, max_k;
+    size_t slot_bytes;      // one rank's lists of one call: [2 lists][max_batch][max_k] keys
+    size_t slots_off;       // [2 epoch parities][world] slots
+    size_t flags_off;       // [2 epoch parities][world] u64: epoch whose lists of that rank have arrived
+    size_t xb_off;          // [2 lists][max_batch] u64 cross-shard bound words (common.cuh: ShardBounds)
+    size_t epoch_off;       // u32: the current epoch of this rank (bumped on the device: graph replays stay in step)
+    size_t tables_off;      // [3][world] device pointers: window bases, dense bound words, sparse bound words
+    size_t total;
+};
+ShardWindowLayout shard_window_layout(int world, int max_batch, int max_k);
+struct ShardPush {
+    uint8_t* const* windows = nullptr;    // device table [world] of window bases (windows[rank] = own)
+    const unsigned* epoch = nullptr;
+    int world = 0, rank = 0;
+    size_t slots_off = 0, slot_bytes = 0, flags_off = 0;
+};
+cudaError_t shard_next_epoch(unsigned* epoch, cudaStream_t st);
+// keys [B][m] (local rows) -> best k per query as keys with global rows, into local_out [2][B][k] (list `list`) or,
+// when local_out is NULL, into slot (epoch parity, rank) of every rank's window
+cudaError_t shard_finalize_push(const uint64_t* keys, int B, int m, int k, int64_t id_offset, int list,
+                                uint64_t* local_out, const ShardPush& dst, cudaStream_t st);
+cudaError_t shard_signal(const ShardPush& dst, cudaStream_t st);
+// gathered [G][2][B][k] keys, or NULL = read this rank's window after waiting for the world's flags;
+// merged lists (optional stage_* outputs, [2][B][k] / [2][B]) and their RRF fusion
+cudaError_t shard_fuse(const uint64_t* gathered, const ShardPush& win, int G, int B, int k, int limit, int tie_mode,
+                       double* out_scores, int64_t* out_ids, int32_t* out_counts, float* stage_scores,
+                       int64_t* stage_ids, int32_t* stage_counts, cudaStream_t st);
 
 // ---- rerank.cu: mean-pooled hidden states -> scores [n] and the document order (score desc, higher index first)
 cudaError_t rerank_meanpool(const float* qh, int Tq, const float* dh, int n, int T, int d, float* scores,
@@ -104,7 +147,7 @@ Bm25Plan bm25_plan(int64_t n_docs, int B, int k_sel, int num_sms);
 cudaError_t bm25_scan(const int64_t* term_ptr, const uint2* post, const uint32_t* sub_off,
                       int64_t V, int64_t n_docs, const int32_t* q_ptr, const int32_t* q_terms,
                       const double* q_vals, int B, const uint32_t* mask, int k_sel, uint64_t* part,
-                      const Bm25Plan& plan, void* scratch, cudaStream_t st);
+                      const Bm25Plan& plan, void* scratch, cudaStream_t st, const ShardBounds& xb);
 
 
 // ---- bm25x.cu: bitmap-filter variant of the sparse scan (same results, prunes on per-term weight bounds)
@@ -124,6 +167,6 @@ cudaError_t bm25x_scan(const int64_t* term_ptr, const uint2* post, const uint32_
                        const uint32_t* bits, const uint32_t* bits_hi, const float2* wrange, const float* tau, int64_t V,
                        int64_t n_docs, const int32_t* q_ptr, const int32_t* q_terms, const double* q_vals, int B,
                        int max_terms, const uint32_t* mask, int k_sel, uint64_t* part, const Bm25Plan& plan,
-                       void* scratch, cudaStream_t st);
+                       void* scratch, cudaStream_t st, const ShardBounds& xb);
 
 }  // namespace brag

@@ -4,6 +4,7 @@
 // All of these touch <= a few thousand entries per query: latency-bound, not roofed.
 #include "common.cuh"
 #include "kernels.h"
+#include "rrf.cuh"
 
 namespace brag {
 
@@ -57,15 +58,15 @@ merge_keys_kernel(const uint64_t* __restrict__ in, int P, int B, int kk, int GP,
 // One warp per query: bound = highest histogram edge that at least k counted rows reach (common.cuh), published
 // with atomicMax.  Run after a scan so that the selection sees the bound of the COMPLETE histograms.
 __global__ void publish_bounds_kernel(const uint32_t* __restrict__ coarse, const uint32_t* __restrict__ fine,
-                                      uint32_t* __restrict__ gthr, int B, int k) {
+                                      uint32_t* __restrict__ gthr, int B, int k, const ShardBounds xb) {
     const int q = (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5);
     if (q >= B) return;
-    const uint32_t bound = hist_bound(coarse, fine, q, (uint32_t)k, (int)(threadIdx.x & 31));
-    if ((threadIdx.x & 31) == 0 && bound != 0u) atomicMax(gthr + q, bound);
+    publish_bound(gthr, q, hist_bound(coarse, fine, q, (uint32_t)k, (int)(threadIdx.x & 31)), xb, (int)(threadIdx.x & 31));
 }
 
-cudaError_t publish_bounds(const uint32_t* coarse, const uint32_t* fine, uint32_t* gthr, int B, int k, cudaStream_t st) {
-    publish_bounds_kernel<<<(B + 7) / 8, 256, 0, st>>>(coarse, fine, gthr, B, k);
+cudaError_t publish_bounds(const uint32_t* coarse, const uint32_t* fine, uint32_t* gthr, int B, int k, cudaStream_t st,
+                           const ShardBounds& xb) {
+    publish_bounds_kernel<<<(B + 7) / 8, 256, 0, st>>>(coarse, fine, gthr, B, k, xb);
     return cudaGetLastError();
 }
 
@@ -77,13 +78,6 @@ size_t merge_tmp_elems(int P, int B, int kk) {
 
 cudaError_t merge_key_lists(const uint64_t* in, int P, int B, int kk, uint64_t* tmp_a, uint64_t* tmp_b,
                             uint64_t* out, int kout, cudaStream_t st, int* launches, const uint32_t* bound) {
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(merge_keys_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             SEL_MAX * 8);
-        if (e != cudaSuccess) return e;
-        attr_set = true;
-    }
     if (kk > SEL_MAX / 2 || kout > SEL_MAX) return cudaErrorInvalidValue;
     const int GP = max(2, SEL_MAX / kk);
     const uint64_t* cur = in;
@@ -254,13 +248,6 @@ finalize_keys_kernel(const uint64_t* __restrict__ keys, int m, int k, int dedup,
 
 cudaError_t finalize_keys(const uint64_t* keys, int B, int m, int k, bool dedup, int64_t id_offset,
                           float* out_scores, int64_t* out_ids, int32_t* out_counts, cudaStream_t st) {
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(finalize_keys_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             SEL_MAX * 8);
-        if (e != cudaSuccess) return e;
-        attr_set = true;
-    }
     int n2 = 1;
     while (n2 < (m > k ? m : k)) n2 <<= 1;
     if (n2 > SEL_MAX) return cudaErrorInvalidValue;
@@ -270,16 +257,7 @@ cudaError_t finalize_keys(const uint64_t* keys, int B, int m, int k, bool dedup,
 }
 
 // ------------------------------------------------------------------ reciprocal rank fusion
-struct RrfEntry {
-    double s;
-    uint32_t tb;   // tie-break, ascending
-    int32_t src;   // flattened source index
-    __device__ bool operator<(const RrfEntry& o) const { return s < o.s || (s == o.s && tb > o.tb); }
-};
-
-constexpr int RRF_THREADS = 256;
-constexpr int RRF_MAX = 8192;          // 8192 * (16 + 12) bytes = 224 KB of the 227 KB a CTA may use
-
+// (the fusion itself is rrf_cta in rrf.cuh, shared with the sharded fuse kernel of shard.cu)
 __global__ void __launch_bounds__(RRF_THREADS)
 rrf_kernel(const int64_t* __restrict__ ids, const int32_t* __restrict__ counts, int L, int B, int kmax,
            int limit, int tie_mode, double* __restrict__ out_scores, int64_t* __restrict__ out_ids,
@@ -309,50 +287,14 @@ rrf_kernel(const int64_t* __restrict__ ids, const int32_t* __restrict__ counts, 
         }
     }
     __syncthreads();
-    for (int e = tid; e < n2; e += RRF_THREADS) {
-        RrfEntry r;
-        r.s = -1.0; r.tb = 0xFFFFFFFFu; r.src = -1;
-        if (e < E) {
-            const int64_t id = fid[e];
-            double s = 0.0;
-            bool first = true;
-            for (int f = 0; f < E; ++f) {
-                if (fid[f] == id) {
-                    if (f < e) first = false;
-                    s += 1.0 / (double)(2 + fpos[f]);   // list order == upstream accumulation order
-                }
-            }
-            if (first) {
-                r.s = s;
-                r.tb = (tie_mode == 0) ? (uint32_t)id : (uint32_t)e;
-                r.src = e;
-                atomicAdd(&n_unique, 1);
-            }
-        }
-        ent[e] = r;
-    }
-    __syncthreads();
-    bitonic_desc(ent, n2, tid, RRF_THREADS, [] { __syncthreads(); });
-    const int nu = min(n_unique, limit);
-    for (int i = tid; i < limit; i += RRF_THREADS) {
-        const bool ok = i < nu;
-        out_scores[(size_t)b * limit + i] = ok ? ent[i].s : -INFINITY;
-        out_ids[(size_t)b * limit + i] = ok ? fid[ent[i].src] : -1;
-    }
-    if (tid == 0) out_counts[b] = nu;
+    rrf_cta(ent, fid, fpos, E, n2, limit, tie_mode, &n_unique, out_scores + (size_t)b * limit,
+            out_ids + (size_t)b * limit, out_counts + b, tid, RRF_THREADS);
 }
 
 cudaError_t rrf_fuse(const int64_t* ids, const int32_t* counts, int L, int B, int kmax, int limit,
                      int tie_mode, double* out_scores, int64_t* out_ids, int32_t* out_counts,
                      cudaStream_t st) {
     if (L < 1 || L > 16 || (int64_t)L * kmax > RRF_MAX || limit > RRF_MAX) return cudaErrorInvalidValue;
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(rrf_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             RRF_MAX * (int)sizeof(RrfEntry) + RRF_MAX * 12);
-        if (e != cudaSuccess) return e;
-        attr_set = true;
-    }
     int E = L * kmax;
     int n2 = 1;
     while (n2 < (E > limit ? E : limit)) n2 <<= 1;
@@ -401,19 +343,23 @@ merge_scored_kernel(const float* __restrict__ scores, const int64_t* __restrict_
 cudaError_t merge_scored_lists(const float* scores, const int64_t* ids, const int32_t* counts, int G,
                                int B, int k, float* out_scores, int64_t* out_ids, int32_t* out_counts,
                                cudaStream_t st) {
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaError_t e = cudaFuncSetAttribute(merge_scored_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             SEL_MAX * 8);
-        if (e != cudaSuccess) return e;
-        attr_set = true;
-    }
     int n2 = 1;
     while (n2 < G * k) n2 <<= 1;
     if (n2 > SEL_MAX) return cudaErrorInvalidValue;
     merge_scored_kernel<<<B, SEL_THREADS, (size_t)n2 * 8, st>>>(scores, ids, counts, G, B, k, out_scores,
                                                              out_ids, out_counts);
     return cudaGetLastError();
+}
+
+// kernel attributes are per device: brag_create calls this with the engine's device current
+cudaError_t select_init_device() {
+    cudaError_t e = cudaFuncSetAttribute(merge_keys_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SEL_MAX * 8);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(finalize_keys_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SEL_MAX * 8);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(merge_scored_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SEL_MAX * 8);
+    if (e == cudaSuccess)
+        e = cudaFuncSetAttribute(rrf_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 RRF_MAX * (int)sizeof(RrfEntry) + RRF_MAX * 12);
+    return e;
 }
 
 }  // namespace brag

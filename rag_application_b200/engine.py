@@ -197,7 +197,9 @@ class Engine:
                                                    _ptr(i), _ptr(c), int(dev), _stream() if dev else None))
         return s, i, c
 
-    def sparse_topk(self, name: str, q_ptr, q_terms, q_vals, k: int, mask_id: int = 0):
+    def sparse_topk(self, name: str, q_ptr, q_terms, q_vals, k: int, mask_id: int = 0, max_terms: int = -1):
+        """max_terms: upper bound of the longest query (terms).  Device callers should pass it: without it the engine
+        copies q_ptr back and synchronises the stream in the middle of the call."""
         dev = _is_torch_cuda(q_ptr)
         if not dev:
             q_ptr = np.ascontiguousarray(q_ptr, dtype=np.int32)
@@ -206,7 +208,8 @@ class Engine:
         B = q_ptr.shape[0] - 1
         s, i, c = self._outs(B, k, dev)
         _native.check(self._lib.brag_sparse_topk(self._h, name.encode(), _ptr(q_ptr), _ptr(q_terms), _ptr(q_vals), B, k,
-                                                 mask_id, _ptr(s), _ptr(i), _ptr(c), int(dev), _stream() if dev else None))
+                                                 mask_id, int(max_terms), _ptr(s), _ptr(i), _ptr(c), int(dev),
+                                                 _stream() if dev else None))
         return s, i, c
 
     def rrf(self, ids, counts, limit: int, tie: int = TIE_ID):
@@ -255,19 +258,95 @@ class Engine:
                                                 _ptr(c), int(dev), _stream() if dev else None))
         return s, i, c
 
-    def hybrid_topk(self, dense_name: str, sparse_name: str, Q, q_ptr, q_terms, q_vals, k: int, mask_id: int = 0):
+    def _hybrid_inputs(self, Q, q_ptr, q_terms, q_vals):
         dev = _is_torch_cuda(Q)
-        if not dev:
-            Q = np.ascontiguousarray(Q, dtype=np.float32)
-            q_ptr = np.ascontiguousarray(q_ptr, dtype=np.int32)
-            q_terms = np.ascontiguousarray(q_terms, dtype=np.int32)
-            q_vals = np.ascontiguousarray(q_vals, dtype=np.float64)
+        if dev:
+            return dev, Q.contiguous(), q_ptr, q_terms, q_vals
+        return (dev, np.ascontiguousarray(Q, dtype=np.float32), np.ascontiguousarray(q_ptr, dtype=np.int32),
+                np.ascontiguousarray(q_terms, dtype=np.int32), np.ascontiguousarray(q_vals, dtype=np.float64))
+
+    def hybrid_topk(self, dense_name: str, sparse_name: str, Q, q_ptr, q_terms, q_vals, k: int, mask_id: int = 0,
+                    max_terms: int = -1):
+        dev, Q, q_ptr, q_terms, q_vals = self._hybrid_inputs(Q, q_ptr, q_terms, q_vals)
         B = Q.shape[0]
         s, i, c = self._outs(B, k, dev, "f64")
         _native.check(self._lib.brag_hybrid_topk(self._h, dense_name.encode(), sparse_name.encode(), _ptr(Q), _ptr(q_ptr),
-                                                 _ptr(q_terms), _ptr(q_vals), B, k, mask_id, _ptr(s), _ptr(i), _ptr(c),
-                                                 int(dev), _stream() if dev else None))
+                                                 _ptr(q_terms), _ptr(q_vals), B, k, mask_id, int(max_terms), _ptr(s),
+                                                 _ptr(i), _ptr(c), int(dev), _stream() if dev else None))
         return s, i, c
+
+    # ------------------------------------------------------------------ row sharding (include/brag.h, shard.cu)
+    def _stage_outs(self, B, k, dev, want):
+        if not want:
+            return None, None, None
+        if dev:
+            import torch
+            d = torch.device("cuda", self.device)
+            return (torch.empty((2, B, k), dtype=torch.float32, device=d), torch.empty((2, B, k), dtype=torch.int64, device=d),
+                    torch.empty((2, B), dtype=torch.int32, device=d))
+        return np.empty((2, B, k), np.float32), np.empty((2, B, k), np.int64), np.empty((2, B), np.int32)
+
+    def shard_local_lists(self, dense_name: str, sparse_name: str, Q, q_ptr, q_terms, q_vals, k: int, mask_id: int = 0,
+                          max_terms: int = -1):
+        """This shard's dense and sparse top-k as packed keys [2, B, k] (uint64 bits carried as int64)."""
+        dev, Q, q_ptr, q_terms, q_vals = self._hybrid_inputs(Q, q_ptr, q_terms, q_vals)
+        B = Q.shape[0]
+        if dev:
+            import torch
+            keys = torch.empty((2, B, k), dtype=torch.int64, device=Q.device)
+        else:
+            keys = np.empty((2, B, k), np.int64)
+        _native.check(self._lib.brag_shard_local_lists(self._h, dense_name.encode(), sparse_name.encode(), _ptr(Q),
+                                                       _ptr(q_ptr), _ptr(q_terms), _ptr(q_vals), B, k, mask_id,
+                                                       int(max_terms), _ptr(keys), int(dev), _stream() if dev else None))
+        return keys
+
+    def shard_fuse(self, keys, limit: int, tie: int = TIE_ID, stages: bool = False):
+        """keys [G, 2, B, k] gathered from every shard -> (rrf scores f64 [B, limit], ids, counts)
+        (+ the two merged lists (scores [2,B,k], ids [2,B,k], counts [2,B]) when `stages`)."""
+        dev = _is_torch_cuda(keys)
+        keys = keys.contiguous() if dev else np.ascontiguousarray(keys, dtype=np.int64)
+        G, two, B, k = keys.shape
+        assert two == 2
+        s, i, c = self._outs(B, limit, dev, "f64")
+        ts, ti, tc = self._stage_outs(B, k, dev, stages)
+        _native.check(self._lib.brag_shard_fuse(self._h, _ptr(keys), G, B, k, limit, tie, _ptr(s), _ptr(i), _ptr(c),
+                                                _ptr(ts), _ptr(ti), _ptr(tc), int(dev), _stream() if dev else None))
+        return (s, i, c, (ts, ti, tc)) if stages else (s, i, c)
+
+    def shard_window_create(self, world: int, max_batch: int, max_k: int) -> bytes:
+        """Allocate this engine's exchange window; returns its 64-byte CUDA IPC handle."""
+        buf = (C.c_uint8 * 64)()
+        _native.check(self._lib.brag_shard_window_create(self._h, world, max_batch, max_k, buf))
+        return bytes(buf)
+
+    def shard_connect(self, rank: int, world: int, handles: Optional[Sequence[bytes]] = None,
+                      local_peers: Optional[Sequence["Engine"]] = None):
+        """handles: every rank's window handle (one process per GPU); local_peers: the world's engines, in rank order,
+        when they all live in this process."""
+        if local_peers is not None:
+            arr = (C.c_void_p * world)(*[p._h for p in local_peers])
+            _native.check(self._lib.brag_shard_connect(self._h, rank, world, None, arr))
+        else:
+            blob = b"".join(handles)
+            assert len(blob) == 64 * world
+            _native.check(self._lib.brag_shard_connect(self._h, rank, world, blob, None))
+
+    def shard_hybrid_topk(self, dense_name: str, sparse_name: str, Q, q_ptr, q_terms, q_vals, k: int, mask_id: int = 0,
+                          max_terms: int = -1, stages: bool = False):
+        """Every rank calls this with the same batch, in the same order; identical result on every rank."""
+        dev, Q, q_ptr, q_terms, q_vals = self._hybrid_inputs(Q, q_ptr, q_terms, q_vals)
+        B = Q.shape[0]
+        s, i, c = self._outs(B, k, dev, "f64")
+        ts, ti, tc = self._stage_outs(B, k, dev, stages)
+        _native.check(self._lib.brag_shard_hybrid_topk(self._h, dense_name.encode(), sparse_name.encode(), _ptr(Q),
+                                                       _ptr(q_ptr), _ptr(q_terms), _ptr(q_vals), B, k, mask_id,
+                                                       int(max_terms), _ptr(s), _ptr(i), _ptr(c), _ptr(ts), _ptr(ti),
+                                                       _ptr(tc), int(dev), _stream() if dev else None))
+        return (s, i, c, (ts, ti, tc)) if stages else (s, i, c)
+
+    def shard_close(self):
+        _native.check(self._lib.brag_shard_close(self._h))
 
     # ------------------------------------------------------------------ introspection
     def profile_enable(self, on: bool = True):

@@ -1,16 +1,22 @@
 """Row-sharded hybrid search across the GPUs of one box.
 
-One process per GPU.  Rank r owns corpus rows / documents [offset_r, offset_r + n_r) and answers
-with GLOBAL ids.  Per query batch there is exactly one exchange step: an all-gather of the two
-per-shard ranked lists (dense and sparse are merged separately, because RRF needs global ranks),
-followed on every rank by the k-way merge kernel and the RRF kernel.  Queries are replicated.
+One engine per GPU.  Rank r owns corpus rows / documents [offset_r, offset_r + n_r) and answers with
+GLOBAL ids.  A stage's per-shard ranked list travels as sorted 64-bit keys (ordered score << 32 |
+0xFFFFFFFF - global row): dense and sparse lists are merged separately (RRF needs global ranks) and
+then fused, all in ONE kernel per rank (brag_shard_fuse / brag_shard_hybrid_topk).  Queries are replicated.
 
-`merge_lists` / `fuse` are pure functions of gathered tensors so the same code path is exercised
-by the world_size-2 gloo tests on CPU (tests/test_sharded_cpu.py) with a numpy stand-in for the
-two kernels' contracts."""
+Two exchanges, same kernels, same results:
+  "peer"        the product path on a box: every rank pushes its lists straight into every peer's window over
+                NVLink while it scans (brag_shard_hybrid_topk; no collective call, CUDA-graph capturable), and the
+                shards tell each other their running score bounds;
+  "collective"  brag_shard_local_lists -> torch.distributed all-gather of the keys -> brag_shard_fuse; any
+                backend (the world_size-2 gloo tests on CPU run it with the oracle-backed stand-in engine), and
+                the checker of the peer path in bench.py."""
 from __future__ import annotations
 
-from typing import Callable, Optional, Tuple
+from typing import Tuple
+
+import numpy as np
 
 
 def shard_bounds(n: int, world: int, rank: int) -> Tuple[int, int]:
@@ -20,63 +26,72 @@ def shard_bounds(n: int, world: int, rank: int) -> Tuple[int, int]:
     return lo, lo + base + (1 if rank < rem else 0)
 
 
-def pack_lists(dense, sparse):
-    """(scores [B,k] f32, ids [B,k] i64, counts [B] i32) x 2 -> one contiguous int64 payload
-    [2, B, 2k+1] so the exchange is a single collective.  Scores travel as raw bits."""
-    import torch
-    out = []
-    for s, i, c in (dense, sparse):
-        sb = s.contiguous().view(torch.int32).to(torch.int64)
-        out.append(torch.cat([sb, i, c.to(torch.int64)[:, None]], dim=1))
-    return torch.stack(out).contiguous()
+def keys_to_lists(keys) -> Tuple[np.ndarray, np.ndarray]:
+    """Packed keys (any shape, int64 / uint64 bits) -> (float32 scores, int64 global ids); empty slots -> (-inf, -1).
+    The inverse of the engine's key format (csrc/common.cuh: make_key), for checkers."""
+    u = np.ascontiguousarray(keys).view(np.uint64)
+    o = (u >> np.uint64(32)).astype(np.uint32)
+    bits = np.where(o & np.uint32(0x80000000), o & np.uint32(0x7FFFFFFF), ~o).astype(np.uint32)
+    s = bits.view(np.float32).copy()
+    i = (np.uint64(0xFFFFFFFF) - (u & np.uint64(0xFFFFFFFF))).astype(np.int64)
+    empty = u == 0
+    s[empty] = -np.inf
+    i[empty] = -1
+    return s, i
 
 
-def unpack_lists(payload, k: int):
-    """[G, 2, B, 2k+1] -> per list: (scores [G,B,k] f32, ids [G,B,k] i64, counts [G,B] i32)."""
-    import torch
-    res = []
-    for l in range(2):
-        p = payload[:, l]
-        s = p[:, :, :k].to(torch.int32).view(torch.float32).contiguous()
-        i = p[:, :, k:2 * k].contiguous()
-        c = p[:, :, 2 * k].to(torch.int32).contiguous()
-        res.append((s, i, c))
-    return res
+def lists_to_keys(scores, ids) -> np.ndarray:
+    """(float32 scores, int64 global ids, -1 = empty) -> packed keys as int64 bits (csrc/common.cuh: make_key)."""
+    s = np.ascontiguousarray(scores, dtype=np.float32) + np.float32(0.0)        # -0 -> +0
+    u = s.view(np.uint32)
+    o = np.where(u & np.uint32(0x80000000), ~u, u | np.uint32(0x80000000)).astype(np.uint64)
+    i = np.asarray(ids, dtype=np.int64)
+    k = (o << np.uint64(32)) | (np.uint64(0xFFFFFFFF) - np.where(i >= 0, i, 0).astype(np.uint64))
+    k[i < 0] = 0
+    return k.view(np.int64)
 
 
 class ShardedHybrid:
-    """Hybrid top-k over a row-sharded corpus.  `engine` is this rank's rag_application_b200.Engine
-    (or any object with dense_topk / sparse_topk / merge_topk / rrf of the same contract)."""
+    """Hybrid top-k over a row-sharded corpus, one process per GPU.  `engine` is this rank's
+    rag_application_b200.Engine (or any object with shard_local_lists / shard_fuse of the same contract)."""
 
-    def __init__(self, engine, rank: int, world: int, id_offset: int, group=None):
+    def __init__(self, engine, rank: int, world: int, id_offset: int, group=None, exchange: str = "auto",
+                 max_batch: int = 4096, max_k: int = 128):
         self.engine, self.rank, self.world, self.group = engine, rank, world, group
         engine.set_id_offset(id_offset)
+        if exchange == "auto":
+            exchange = "peer" if world > 1 and hasattr(engine, "shard_window_create") else "collective"
+        self.exchange = exchange
+        if exchange == "peer":
+            import torch.distributed as dist
+            handle = engine.shard_window_create(world, max_batch, max_k)
+            handles = [None] * world
+            if world > 1:
+                dist.all_gather_object(handles, handle, group=group)
+            else:
+                handles = [handle]
+            engine.shard_connect(rank, world, handles=handles)
+            if world > 1:
+                dist.barrier(group=group)          # nobody pushes before everybody has mapped everybody
 
-    def local_lists(self, dense_name, sparse_name, Q, q_ptr, q_terms, q_vals, k, mask_id=0):
-        d = self.engine.dense_topk(dense_name, Q, k, mask_id)
-        s = self.engine.sparse_topk(sparse_name, q_ptr, q_terms, q_vals, k, mask_id)
-        return d, s
-
-    def exchange(self, payload):
+    def gather_keys(self, keys):
+        """[2, B, k] keys of this rank -> [world, 2, B, k] (one all-gather)."""
         import torch
         import torch.distributed as dist
         if self.world == 1:
-            return payload[None]
-        # flat buffers: NCCL accepts any [world, ...] view, gloo insists on a concatenated dim 0
-        flat = payload.reshape(-1)
-        out = torch.empty((self.world * flat.numel(),), dtype=payload.dtype, device=payload.device)
+            return keys[None]
+        flat = keys.reshape(-1)          # NCCL accepts any [world, ...] view, gloo insists on a concatenated dim 0
+        out = torch.empty((self.world * flat.numel(),), dtype=keys.dtype, device=keys.device)
         dist.all_gather_into_tensor(out, flat, group=self.group)
-        return out.view((self.world,) + tuple(payload.shape))
+        return out.view((self.world,) + tuple(keys.shape))
 
-    def hybrid_topk(self, dense_name, sparse_name, Q, q_ptr, q_terms, q_vals, k, mask_id=0):
-        """Device tensors in, device tensors out: (rrf scores f64 [B,k], ids [B,k], counts [B]),
-        identical on every rank."""
-        import torch
-        d, s = self.local_lists(dense_name, sparse_name, Q, q_ptr, q_terms, q_vals, k, mask_id)
-        gathered = self.exchange(pack_lists(d, s))
-        (ds, di, dc), (ss, si, sc) = unpack_lists(gathered, k)
-        md = self.engine.merge_topk(ds, di, dc)
-        ms = self.engine.merge_topk(ss, si, sc)
-        ids = torch.stack([md[1], ms[1]]).contiguous()
-        cnt = torch.stack([md[2], ms[2]]).contiguous()
-        return self.engine.rrf(ids, cnt, k)
+    def hybrid_topk(self, dense_name, sparse_name, Q, q_ptr, q_terms, q_vals, k, mask_id=0, max_terms=-1,
+                    stages=False, exchange=None):
+        """Device tensors in, device tensors out: (rrf scores f64 [B,k], ids [B,k], counts [B]) -- identical on every
+        rank -- plus the merged dense / sparse lists when `stages`."""
+        if (exchange or self.exchange) == "peer":
+            return self.engine.shard_hybrid_topk(dense_name, sparse_name, Q, q_ptr, q_terms, q_vals, k, mask_id,
+                                                 max_terms=max_terms, stages=stages)
+        keys = self.engine.shard_local_lists(dense_name, sparse_name, Q, q_ptr, q_terms, q_vals, k, mask_id,
+                                             max_terms=max_terms)
+        return self.engine.shard_fuse(self.gather_keys(keys), k, stages=stages)

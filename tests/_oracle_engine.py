@@ -123,7 +123,7 @@ class OracleEngine:
             out.append((s, i + self.id_offset))
         return self._wrap(Q, *self._pad(out, k))
 
-    def sparse_topk(self, name, q_ptr, q_terms, q_vals, k, mask_id=0):
+    def sparse_topk(self, name, q_ptr, q_terms, q_vals, k, mask_id=0, max_terms=-1):
         self.calls.append(("sparse_topk", name, k))
         csr = self.sparse[name]
         qp, qt, qv = _np(q_ptr), _np(q_terms), _np(q_vals)
@@ -158,7 +158,35 @@ class OracleEngine:
             out.append((fs[o], fi[o]))
         return self._wrap(ids, *self._pad(out, k))
 
-    def hybrid_topk(self, dense_name, sparse_name, Q, q_ptr, q_terms, q_vals, k, mask_id=0):
+    def shard_local_lists(self, dense_name, sparse_name, Q, q_ptr, q_terms, q_vals, k, mask_id=0, max_terms=-1):
+        """CPU mirror of brag_shard_local_lists: [2, B, k] packed keys with global ids."""
+        from rag_application_b200.sharded import lists_to_keys
+        d = self.dense_topk(dense_name, Q, k, mask_id)
+        s = self.sparse_topk(sparse_name, q_ptr, q_terms, q_vals, k, mask_id)
+        keys = np.stack([lists_to_keys(_np(d[0]), _np(d[1])), lists_to_keys(_np(s[0]), _np(s[1]))])
+        if hasattr(Q, "numpy") and not isinstance(Q, np.ndarray):
+            import torch
+            return torch.from_numpy(keys)
+        return keys
+
+    def shard_fuse(self, keys, limit, tie=0, stages=False):
+        """CPU mirror of brag_shard_fuse: merge the G dense lists, the G sparse lists, RRF of the two."""
+        from rag_application_b200.sharded import keys_to_lists
+        K = _np(keys)
+        G, _, B, k = K.shape
+        S, I = keys_to_lists(K)
+        merged = []
+        for l in range(2):
+            C = (I[:, l] >= 0).sum(axis=2).astype(np.int32)
+            merged.append([_np(t) for t in self.merge_topk(S[:, l], I[:, l], C)])
+        ids = np.stack([merged[0][1], merged[1][1]])
+        cnt = np.stack([merged[0][2], merged[1][2]])
+        r = self._wrap(keys, *[_np(t) for t in self.rrf(ids, cnt, limit, tie)])
+        if stages:
+            return r + ((np.stack([merged[0][0], merged[1][0]]), ids, cnt),)
+        return r
+
+    def hybrid_topk(self, dense_name, sparse_name, Q, q_ptr, q_terms, q_vals, k, mask_id=0, max_terms=-1):
         d = self.dense_topk(dense_name, Q, k, mask_id)
         s = self.sparse_topk(sparse_name, q_ptr, q_terms, q_vals, k, mask_id)
         ids = np.stack([_np(d[1]), _np(s[1])])

@@ -71,19 +71,22 @@ def test_shard_bounds_cover():
             assert max(sizes) - min(sizes) <= 1
 
 
-def test_pack_unpack_roundtrip():
-    import torch
-    from rag_application_b200.sharded import pack_lists, unpack_lists
-    B, k = 3, 5
-    g = torch.Generator().manual_seed(0)
-    mk = lambda: (torch.randn(B, k, generator=g), torch.randint(0, 1 << 31, (B, k), generator=g),
-                  torch.randint(0, k + 1, (B,), generator=g, dtype=torch.int32))
-    d, s = mk(), mk()
-    d[0][0, 0] = float("-inf")
-    p = pack_lists(d, s)
-    (ds, di, dc), (ss, si, sc) = unpack_lists(p[None], k)
-    for a, b in ((ds[0], d[0]), (di[0], d[1]), (dc[0], d[2]), (ss[0], s[0]), (si[0], s[1]), (sc[0], s[2])):
-        assert torch.equal(a, b)
+def test_key_format_roundtrip():
+    """keys_to_lists / lists_to_keys mirror csrc/common.cuh make_key: order-preserving, ids in the low word."""
+    from rag_application_b200.sharded import keys_to_lists, lists_to_keys
+    rng = np.random.default_rng(0)
+    s = rng.standard_normal((3, 7)).astype(np.float32)
+    s[0, 0], s[0, 1], s[1, 2] = 0.0, -0.0, np.float32(-1e-30)
+    i = rng.integers(0, 1 << 32, (3, 7)).astype(np.int64)
+    i[2, 3:] = -1
+    k = lists_to_keys(s, i)
+    s2, i2 = keys_to_lists(k)
+    assert np.array_equal(i2, i)
+    assert np.array_equal(s2[i >= 0], (s + np.float32(0))[i >= 0]) and np.all(np.isneginf(s2[i < 0]))
+    # a bigger key is a better entry under (score desc, id asc)
+    flat_s, flat_i, flat_k = s[i >= 0], i[i >= 0], k.view(np.uint64)[i >= 0]
+    order = np.lexsort((flat_i, -flat_s.astype(np.float64)))
+    assert np.array_equal(np.sort(flat_k)[::-1], flat_k[order])
 
 
 @pytest.mark.timeout(180)
