@@ -3,8 +3,11 @@
 (BASELINE.json metric / configs[3]), row-sharded over --gpus B200s of one box.
 
 One "step" = one batch of B synthetic hybrid queries through the whole hot path.
-  value : QPS with the query batch already resident in HBM (device-pointer C-ABI calls)
-  e2e   : QPS through the host-buffer C-ABI call (H2D of the batch + D2H of the results inside)
+  value  : QPS with the query batch already resident in HBM (device-pointer C-ABI calls)
+  e2e    : QPS through the host-buffer C-ABI call (H2D of the batch + D2H of the results inside)
+  parity : the timed step's answers on sampled queries against tools/torch_checker.py (torch on the device, no code
+           shared with libbrag.so), outside the timed region; at N > 1 also "every rank holds the same lists"
+  --workload c5 : configs[4] (100 M x 384 f16 + 10 % payload filter, batch 4096) sharded over N >= 4 GPUs
   --impl reference : the CPU restatement (oracle/fast_cpu.py) timed on the host cores.
 Prints ONE JSON line on rank 0."""
 from __future__ import annotations
@@ -32,20 +35,33 @@ def parse():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--n", type=int, default=10_000_000, help="corpus rows / documents (whole job)")
-    ap.add_argument("--d", type=int, default=1024)
-    ap.add_argument("--batch", type=int, default=1024)
+    ap.add_argument("--workload", default="c4", choices=["c4", "c5"],
+                    help="c4 = BASELINE configs[3] (the metric's config, default); c5 = configs[4]: 100M x 384 f16 + 10%% filter")
+    ap.add_argument("--n", type=int, default=None, help="corpus rows / documents (whole job)")
+    ap.add_argument("--d", type=int, default=None)
+    ap.add_argument("--batch", type=int, default=None)
     ap.add_argument("--k", type=int, default=100)
-    ap.add_argument("--dtype", default="bf16", choices=["bf16", "f16"])
+    ap.add_argument("--dtype", default=None, choices=["bf16", "f16"])
+    ap.add_argument("--selectivity", type=float, default=None, help="payload-filter pass rate (c5: 0.10; c4: none)")
+    ap.add_argument("--exchange", default="peer", choices=["peer", "collective"],
+                    help="N > 1: lists pushed over NVLink peer memory by the tail kernels, or an NCCL all-gather")
+    ap.add_argument("--parity-queries", type=int, default=8, help="sampled queries checked after the timed loop (0 = skip)")
     ap.add_argument("--vocab", type=int, default=50_000)
     ap.add_argument("--doc-len", type=int, default=285)
     ap.add_argument("--q-terms", type=int, default=8)
-    ap.add_argument("--cpu-sample-rows", type=int, default=1 << 21, help="rows/docs of the CPU-baseline sample")
-    ap.add_argument("--cpu-sample-queries", type=int, default=1024)
+    ap.add_argument("--cpu-sample-rows", type=int, default=1 << 19, help="rows/docs of the CPU-baseline sample")
+    ap.add_argument("--cpu-sample-queries", type=int, default=256)
     ap.add_argument("--b1-iters", type=int, default=30, help="batch-1 latency iterations (0 = skip)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
-    return ap.parse_args()
+    a = ap.parse_args()
+    c5 = a.workload == "c5"
+    a.n = a.n if a.n is not None else (100_000_000 if c5 else 10_000_000)
+    a.d = a.d if a.d is not None else (384 if c5 else 1024)
+    a.batch = a.batch if a.batch is not None else (4096 if c5 else 1024)
+    a.dtype = a.dtype or ("f16" if c5 else "bf16")
+    a.selectivity = a.selectivity if a.selectivity is not None else (0.10 if c5 else None)
+    return a
 
 
 def load_peaks():
@@ -106,15 +122,19 @@ def run_reference(args, rank, world):
     workload, scaled linearly in corpus size to the full config."""
     if rank != 0:
         return
+    cores = os.cpu_count() or 1
+    # torchrun exports OMP_NUM_THREADS=1, which throttled this arm 3x at N > 1 in round 1: the CPU baseline always gets
+    # every host core (BLAS reads these when it is first loaded, i.e. below)
+    for var in ("OMP_NUM_THREADS", "OPENBLAS_NUM_THREADS", "MKL_NUM_THREADS"):
+        os.environ[var] = str(cores)
     import torch
     from oracle import fast_cpu
     from rag_application_b200 import synth
-    cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
-    # the sample corpus is generated on the host here, so it is kept smaller than the in-run baseline's
-    ns, bs = min(args.cpu_sample_rows, args.n, 1 << 18), min(args.cpu_sample_queries, 256)
-    x = synth.dense_corpus_torch(ns, args.d, torch.bfloat16, "cpu")
-    q = synth.dense_queries_torch(x, bs).to(torch.bfloat16).float().numpy()
+    # same sample as the in-run cpu_baseline leg of the GPU arm (CPU_SAMPLE_ROWS x CPU_SAMPLE_QUERIES)
+    ns, bs = min(args.cpu_sample_rows, args.n), min(args.cpu_sample_queries, args.batch)
+    x = synth.dense_corpus_torch(ns, args.d, torch.bfloat16 if args.dtype == "bf16" else torch.float16, "cpu")
+    q = synth.dense_queries_torch(x, bs).numpy()
     xs = x.float().numpy()
     tp, doc, w = synth.zipf_corpus_torch(ns, args.vocab, args.doc_len, "cpu", block_docs=1 << 16)
     qp, qt, qv = synth.sparse_queries_torch(tp, bs, args.q_terms)
@@ -144,10 +164,85 @@ def run_reference(args, rank, world):
 
 
 def config_dict(args, world):
-    return {"workload": f"C4 hybrid dense+BM25+RRF top-{args.k}: {args.n} chunks x {args.d}-d {args.dtype}, "
-                        f"V={args.vocab} Zipf(1.0) L={args.doc_len}, {args.q_terms}-term queries, batch {args.batch}",
+    flt = f", payload filter Bernoulli({args.selectivity}) seed 4242" if args.selectivity else ""
+    return {"workload": f"{args.workload.upper()} hybrid dense+BM25+RRF top-{args.k}: {args.n} chunks x {args.d}-d {args.dtype}, "
+                        f"V={args.vocab} Zipf(1.0) L={args.doc_len}, {args.q_terms}-term queries, batch {args.batch}{flt}"
+                        + (" (strong scaling over N >= 4: the postings of 100 M documents do not fit fewer GPUs)"
+                           if args.workload == "c5" else ""),
             "n": args.n, "d": args.d, "batch": args.batch, "k": args.k, "shards": world,
             "l2": "inputs larger than L2 (corpus shard >> 126 MB)", "parallelism": f"row-shard x{world}"}
+
+
+
+
+# ------------------------------------------------------------------------------------ parity of the timed step
+def parity_check(args, rank, world, dev, raw, queries, answer, lo, mask_t):
+    """The step's answers on sampled queries against the torch checker (tools/torch_checker.py: float64 on the raw
+    corpus tensors, no code shared with libbrag.so).  answer = (rrf scores, ids, counts, (stage scores, ids, counts))
+    of one extra, untimed call with the stage lists exposed.  At N > 1 every rank ranks its own shard with the checker,
+    the (score, id) lists are all-gathered and globally sorted on every rank -- a torch global sort of the gathered
+    payload -- and the ranks' fused lists are compared with each other."""
+    import torch
+    import torch.distributed as dist
+    from tools import torch_checker as T
+    x, tp, doc, w = raw
+    q_dev, qp, qt, qv = queries
+    fs, fi, fc = [t.cpu().numpy() for t in answer[:3]]
+    ts, ti, tc = [t.cpu().numpy() for t in answer[3]]
+    k, n_loc = args.k, x.shape[0]
+    rows = sorted(set(np.linspace(0, args.batch - 1, args.parity_queries).astype(int).tolist()))
+    res = {"queries": len(rows), "checker": "tools/torch_checker.py (torch float64 on device)", "dense_ids_equal": 0,
+           "dense_explained_by_near_ties": 0, "sparse_ids_equal": 0, "sparse_scores_bit_equal": 0, "fused_ids_equal": 0,
+           "max_rel_score_err": 0.0}
+    for b in rows:
+        ds, di, all_s = T.dense_topk(x, q_dev[b], k, mask=mask_t, id_offset=lo)
+        ss, si = T.sparse_topk(tp, doc, w, n_loc, qt[qp[b]:qp[b + 1]], qv[qp[b]:qp[b + 1]], k, mask=mask_t, id_offset=lo)
+        if world > 1:
+            def gather(s, i):
+                pad_s = torch.full((k,), -float("inf"), device=dev)
+                pad_i = torch.full((k,), -1, dtype=torch.int64, device=dev)
+                pad_s[:len(s)] = torch.from_numpy(s).to(dev)
+                pad_i[:len(i)] = torch.from_numpy(i).to(dev)
+                gs = torch.empty(world * k, device=dev)
+                gi = torch.empty(world * k, dtype=torch.int64, device=dev)
+                dist.all_gather_into_tensor(gs, pad_s)
+                dist.all_gather_into_tensor(gi, pad_i)
+                gs, gi = gs.cpu().numpy(), gi.cpu().numpy()
+                keep = gi >= 0
+                o = np.lexsort((gi[keep], -gs[keep].astype(np.float64)))[:k]
+                return gs[keep][o], gi[keep][o]
+            ds, di = gather(ds, di)
+            ss, si = gather(ss, si)
+            all_s = None
+        r = T.dense_lists_agree(ts[0][b], ti[0][b], ds, di, all_scores=all_s, id_offset=lo)
+        if all_s is None and not r["ids_equal"]:
+            # sharded: near-ties are judged on the gathered checker scores of the same ids
+            ref = dict(zip(di.tolist(), ds.tolist()))
+            r["explained"] = all(abs(ref.get(int(g), 9e9) - float(e)) <= T.TIE_EPS * max(1.0, abs(float(e))) or int(g) == int(h)
+                                 for g, e, h in zip(ti[0][b][:len(di)], ds, di))
+        res["dense_ids_equal"] += int(r["ids_equal"])
+        res["dense_explained_by_near_ties"] += int(r["explained"] and not r["ids_equal"])
+        res["max_rel_score_err"] = max(res["max_rel_score_err"], r["max_rel_err"])
+        c = len(si)
+        s_ok = int(tc[1][b]) == c and np.array_equal(ti[1][b][:c], si)
+        res["sparse_ids_equal"] += int(s_ok)
+        res["sparse_scores_bit_equal"] += int(s_ok and np.array_equal(ts[1][b][:c].view(np.uint32), ss.view(np.uint32)))
+        # fusion: RRF of the checker's lists (of the engine's dense list where it differs by an explained near-tie)
+        dl = di if r["ids_equal"] else ti[0][b][:int(tc[0][b])]
+        es, ei = T.rrf([dl, si], k)
+        res["fused_ids_equal"] += int(int(fc[b]) == len(ei) and np.array_equal(fi[b][:len(ei)], ei)
+                                      and np.array_equal(fs[b][:len(ei)], es))
+    res["ids_equal"] = bool(res["dense_ids_equal"] + res["dense_explained_by_near_ties"] == len(rows)
+                            and res["sparse_ids_equal"] == len(rows) and res["fused_ids_equal"] == len(rows))
+    if world > 1:
+        # every rank holds the same fused lists
+        h = torch.from_numpy(fi.astype(np.int64)).to(dev)
+        hs = torch.stack([h.sum(), (h * torch.arange(1, h.numel() + 1, device=dev).view_as(h)).sum()])
+        allh = torch.empty(world * 2, dtype=torch.int64, device=dev)
+        dist.all_gather_into_tensor(allh, hs)
+        res["ranks_agree"] = bool((allh.view(world, 2) == hs[None]).all().item())
+        res["ids_equal"] = res["ids_equal"] and res["ranks_agree"]
+    return res
 
 
 # ------------------------------------------------------------------------------------ our arm
@@ -176,6 +271,10 @@ def main():
     tdt = torch.bfloat16 if args.dtype == "bf16" else torch.float16
     lo, hi = shard_bounds(args.n, world, rank)
     n_loc = hi - lo
+    k = args.k
+    # raw corpus tensors are kept for the parity check when they fit beside the engine's copies
+    est_gb = (2 * n_loc * args.d * 2 + 2.4 * n_loc * 256 * 8) / 1e9
+    keep_raw = args.parity_queries > 0 and est_gb < 125
 
     # ---- corpus shard, built in HBM
     eng = Engine(local)
@@ -183,9 +282,12 @@ def main():
     q_dev = synth.dense_queries_torch(x, args.batch)
     if world > 1:
         dist.broadcast(q_dev, 0)
-    cpu_x = x[: min(args.cpu_sample_rows, n_loc)].float().cpu().numpy() if rank == 0 else None
+    cpu_rows = min(args.cpu_sample_rows, n_loc)
+    cpu_x = x[:cpu_rows].float().cpu().numpy() if rank == 0 and world == 1 and not args.no_cpu_baseline else None
     eng.dense_set("dense", x)
-    del x
+    if not keep_raw:
+        del x
+        x = None
     torch.cuda.empty_cache()
     tp, doc, w = synth.zipf_corpus_torch(n_loc, args.vocab, args.doc_len, dev, seed=synth.SEED_CORPUS + rank)
     df = (tp[1:] - tp[:-1]).clone()
@@ -194,30 +296,47 @@ def main():
     gptr = torch.zeros_like(tp)
     gptr[1:] = torch.cumsum(df, 0)
     qp, qt, qv = synth.sparse_queries_torch(gptr, args.batch, args.q_terms)
+    t0 = time.perf_counter()
     eng.sparse_set_csr("sparse", tp, doc, w, n_loc)
+    torch.cuda.synchronize()
+    sparse_index_s = time.perf_counter() - t0
     # algorithmic BM25 bytes of this batch on this shard: sum_t df_t * 8 B
     ldf = (tp[1:] - tp[:-1])
     bm25_bytes = float(ldf[qt.to(dev).long()].sum().item()) * 8.0
     cpu_csr = None
-    if rank == 0 and not args.no_cpu_baseline and world == 1:
-        ns = min(args.cpu_sample_rows, n_loc)
-        keep = doc < ns
+    if cpu_x is not None:
+        keep = doc < cpu_rows
         term_of = torch.repeat_interleave(torch.arange(args.vocab, device=dev), ldf)
         sp = torch.zeros(args.vocab + 1, dtype=torch.int64, device=dev)
         sp[1:] = torch.cumsum(torch.bincount(term_of[keep], minlength=args.vocab), 0)
-        cpu_csr = (sp.cpu().numpy(), doc[keep].cpu().numpy().astype(np.uint32), w[keep].cpu().numpy(), ns)
+        cpu_csr = (sp.cpu().numpy(), doc[keep].cpu().numpy().astype(np.uint32), w[keep].cpu().numpy(), cpu_rows)
         del term_of, keep
-    del tp, doc, w
+    if not keep_raw:
+        del tp, doc, w
+        tp = doc = w = None
     torch.cuda.empty_cache()
 
-    sh = ShardedHybrid(eng, rank, world, lo)
+    # ---- payload filter (c5): Bernoulli(selectivity), seed 4242 + rank, the same bits for both spaces
+    mask_id, mask_t, sel_real = 0, None, None
+    if args.selectivity:
+        g = torch.Generator(device=dev)
+        g.manual_seed(synth.SEED_MASK + rank)
+        mask_t = torch.rand(n_loc, generator=g, device=dev) < args.selectivity
+        eng.mask_set(1, mask_t.cpu().numpy())
+        mask_id = 1
+        sel_real = float(mask_t.float().mean().item())
+        eng.sparse_compact_after(0)            # the filter is fixed for the whole run: build its index on first use
+
+    max_batch = max(args.batch, 1)
+    sh = ShardedHybrid(eng, rank, world, lo, exchange=args.exchange if world > 1 else "collective",
+                       max_batch=max_batch, max_k=max(k, 16))
     qp_d, qt_d, qv_d = qp.to(dev), qt.to(dev), qv.to(dev)
-    k = args.k
+    mt = args.q_terms
 
     def step_dev():
         if world == 1:
-            return eng.hybrid_topk("dense", "sparse", q_dev, qp_d, qt_d, qv_d, k)
-        return sh.hybrid_topk("dense", "sparse", q_dev, qp_d, qt_d, qv_d, k)
+            return eng.hybrid_topk("dense", "sparse", q_dev, qp_d, qt_d, qv_d, k, mask_id=mask_id, max_terms=mt)
+        return sh.hybrid_topk("dense", "sparse", q_dev, qp_d, qt_d, qv_d, k, mask_id=mask_id, max_terms=mt)
 
     def barrier():
         if world > 1:
@@ -237,6 +356,10 @@ def main():
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         return float(ms.item()), out
 
+    # the first call under a filter builds the filter-compacted dense copy and sparse index (c5): timed apart
+    first_call_ms = None
+    if mask_id:
+        first_call_ms, _ = timed(step_dev, 1)
     eng.profile_enable(True)
     for _ in range(args.warmup):
         step_dev()
@@ -245,11 +368,39 @@ def main():
     clocks = ClockSampler(local)
     if rank == 0:
         clocks.start()
-    ms_total, _ = timed(step_dev, args.steps)
+    ms_total, last = timed(step_dev, args.steps)
     stage_ms, stage_calls, launches = eng.profile_read()
     clk = clocks.stop() if rank == 0 else None
     ms_step = ms_total / args.steps
     value = args.batch / (ms_step * 1e-3)
+    last = [t.clone() for t in last[:3]]
+
+    # ---- parity of the timed step's answers (outside the timed region)
+    parity = None
+    if args.parity_queries > 0:
+        if not keep_raw:
+            parity = {"skipped": f"raw corpus tensors not kept beside the engine's copies (~{est_gb:.0f} GB per GPU)"}
+        else:
+            eng.profile_enable(False)
+            if world == 1:
+                keys = eng.shard_local_lists("dense", "sparse", q_dev, qp_d, qt_d, qv_d, k, mask_id=mask_id, max_terms=mt)
+                ans = eng.shard_fuse(keys[None].contiguous(), k, stages=True)
+            else:
+                ans = sh.hybrid_topk("dense", "sparse", q_dev, qp_d, qt_d, qv_d, k, mask_id=mask_id, max_terms=mt, stages=True)
+            same = all(bool(torch.equal(a, b)) for a, b in zip(last, ans[:3]))
+            parity = parity_check(args, rank, world, dev, (x, tp, doc, w), (q_dev, qp.numpy(), qt.numpy(), qv.numpy()),
+                                  ans, lo, mask_t)
+            parity["staged_call_equals_timed_call"] = same
+            if world > 1 and args.exchange == "peer":
+                # the peer exchange against the collective one (NCCL all-gather of the same keys)
+                col = sh.hybrid_topk("dense", "sparse", q_dev, qp_d, qt_d, qv_d, k, mask_id=mask_id, max_terms=mt,
+                                     exchange="collective")
+                parity["peer_equals_collective"] = all(bool(torch.equal(a, b)) for a, b in zip(last, col[:3]))
+                parity["ids_equal"] = parity["ids_equal"] and parity["peer_equals_collective"]
+            parity["ids_equal"] = bool(parity["ids_equal"] and same)
+            eng.profile_enable(True)
+    x = tp = doc = w = None
+    torch.cuda.empty_cache()
 
     # ---- end to end: host buffers through the public call, copies inside the timed region
     e2e = None
@@ -259,29 +410,32 @@ def main():
         qp_h, qt_h, qv_h = qp.pin_memory(), qt.pin_memory(), qv.pin_memory()
         h2d = q_host.numel() * 4 + qp_h.numel() * 4 + qt_h.numel() * 4 + qv_h.numel() * 8
         d2h = args.batch * k * (8 + 8) + args.batch * 4
+        qn, qpn, qtn, qvn = q_host.numpy(), qp_h.numpy(), qt_h.numpy(), qv_h.numpy()
         if world == 1:
-            qn, qpn, qtn, qvn = q_host.numpy(), qp_h.numpy(), qt_h.numpy(), qv_h.numpy()
-
             def step_host():
-                return eng.hybrid_topk("dense", "sparse", qn, qpn, qtn, qvn, k)
+                return eng.hybrid_topk("dense", "sparse", qn, qpn, qtn, qvn, k, mask_id=mask_id)
+        elif args.exchange == "peer":
+            def step_host():        # every rank: H2D of the batch, sharded call, D2H of the (identical) result
+                return sh.hybrid_topk("dense", "sparse", qn, qpn, qtn, qvn, k, mask_id=mask_id)
         else:
             def step_host():
                 s, i, c = sh.hybrid_topk("dense", "sparse", q_host.to(dev, non_blocking=True),
                                          qp_h.to(dev, non_blocking=True), qt_h.to(dev, non_blocking=True),
-                                         qv_h.to(dev, non_blocking=True), k)
+                                         qv_h.to(dev, non_blocking=True), k, mask_id=mask_id, max_terms=mt)
                 return s.cpu(), i.cpu(), c.cpu()
         for _ in range(max(1, args.warmup)):
             step_host()
         barrier()
         t0 = time.perf_counter()
         for _ in range(args.steps):
-            step_host()
+            out_h = step_host()
         barrier()
         dt = torch.tensor([time.perf_counter() - t0], device=dev)
         if world > 1:
             dist.all_reduce(dt, op=dist.ReduceOp.MAX)
         e2e = {"value": args.batch * args.steps / float(dt.item()), "unit": UNIT, "h2d_bytes_per_step": int(h2d),
-               "d2h_bytes_per_step": int(d2h)}
+               "d2h_bytes_per_step": int(d2h), "copies": "per rank (every rank uploads the batch and downloads the result)",
+               "equals_device_call": bool(np.array_equal(np.asarray(out_h[1]), last[1].cpu().numpy()))}
 
     # ---- batch-1 latency (the metric's second half): p50 over single-query hybrid calls
     b1 = None
@@ -292,21 +446,23 @@ def main():
 
         def step_b1():
             if world == 1:
-                return eng.hybrid_topk("dense", "sparse", q1, qp1, qt1, qv1, k)
-            return sh.hybrid_topk("dense", "sparse", q1, qp1, qt1, qv1, k)
+                return eng.hybrid_topk("dense", "sparse", q1, qp1, qt1, qv1, k, mask_id=mask_id, max_terms=mt)
+            return sh.hybrid_topk("dense", "sparse", q1, qp1, qt1, qv1, k, mask_id=mask_id, max_terms=mt)
         for _ in range(3):
             step_b1()
         lat = []
         for _ in range(args.b1_iters):
             ms1, _ = timed(step_b1, 1)
             lat.append(ms1)
+        rows_scanned = n_loc * (sel_real if sel_real else 1.0)
+        floor_bytes = rows_scanned * args.d * 2 + (n_loc / 8 if sel_real else 0)
         b1 = {"p50_ms": float(np.median(lat)), "p95_ms": float(np.percentile(lat, 95)), "iters": args.b1_iters,
-              "hbm_floor_ms": n_loc * args.d * 2 / (peaks["hbm_gbs"] * 1e9) * 1e3}
-        if world == 1:
-            # (N > 1 was tried with the all-gather inside the graph: 1.90 -> 1.76 ms at 2 GPUs, but the process group
-            # then hangs at teardown, so the sharded path stays eager)
-            # the same call captured once in a CUDA graph and replayed (the call is stream-ordered and allocation-free
-            # after warm-up): what a serving loop with fixed query buffers pays per query, launch overhead removed
+              "hbm_floor_ms": floor_bytes / (peaks["hbm_gbs"] * 1e9) * 1e3,
+              "hbm_floor": "dense rows that pass the filter x d x 2 B (+ N/8 mask bytes) at the measured copy bandwidth"}
+        if world == 1 or args.exchange == "peer":
+            # the same call captured once in a CUDA graph and replayed (stream-ordered and allocation-free after warm-up;
+            # the peer exchange has no collective inside, so the sharded call captures too): what a serving loop with
+            # fixed query buffers pays per query, launch overhead removed
             try:
                 eng.profile_enable(False)        # stage events cannot be read back from a captured call
                 eager = [t.clone() for t in step_b1()]
@@ -316,6 +472,7 @@ def main():
                     for _ in range(3):
                         step_b1()
                 torch.cuda.current_stream().wait_stream(side)
+                barrier()
                 graph = torch.cuda.CUDAGraph()
                 with torch.cuda.graph(graph):
                     captured = step_b1()
@@ -328,9 +485,23 @@ def main():
                     glat.append(ms1)
                 b1["graph_replay_p50_ms"] = float(np.median(glat))
                 b1["graph_replay_equals_eager"] = same
+                barrier()
+                del graph
             except Exception as ex:      # noqa: BLE001 -- an extra; the eager numbers above stand
                 b1["graph_replay_p50_ms"] = None
                 b1["graph_replay_error"] = str(ex)[:200]
+
+    # ---- c5: the same batch without the filter, for the filtered / unfiltered comparison
+    unfiltered = None
+    if mask_id:
+        def step_nomask():
+            if world == 1:
+                return eng.hybrid_topk("dense", "sparse", q_dev, qp_d, qt_d, qv_d, k, max_terms=mt)
+            return sh.hybrid_topk("dense", "sparse", q_dev, qp_d, qt_d, qv_d, k, max_terms=mt)
+        step_nomask()
+        ms_u, _ = timed(step_nomask, max(2, args.steps // 4))
+        ms_u /= max(2, args.steps // 4)
+        unfiltered = {"ms_per_step": ms_u, "value": args.batch / (ms_u * 1e-3), "unit": UNIT}
 
     # ---- CPU baseline (rank 0, N=1): bounded sample of the same workload on the host cores
     cpu = None
@@ -340,25 +511,33 @@ def main():
         torch.set_num_threads(cores)
         bs = min(args.cpu_sample_queries, args.batch)
         sp, sdoc, sw, ns = cpu_csr
-        qs = q_dev[:bs].to(tdt).float().cpu().numpy()
+        qs = q_dev[:bs].cpu().numpy()
         qpn, qtn, qvn = qp[: bs + 1].numpy(), qt[: int(qp[bs])].numpy(), qv[: int(qp[bs])].numpy()
         fast_cpu.hybrid_batch(cpu_x[:ns], qs[:8], sp, sdoc, sw, ns, qpn[:9], qtn, qvn, k, threads=cores)  # warm
         t0 = time.perf_counter()
-        fast_cpu.hybrid_batch(cpu_x[:ns], qs, sp, sdoc, sw, ns, qpn, qtn, qvn, k, threads=cores)
-        dt = time.perf_counter() - t0
+        reps = 0
+        while reps < 3 or time.perf_counter() - t0 < 10.0:
+            fast_cpu.hybrid_batch(cpu_x[:ns], qs, sp, sdoc, sw, ns, qpn, qtn, qvn, k, threads=cores)
+            reps += 1
+            if reps >= 40:
+                break
+        dt = (time.perf_counter() - t0) / reps
         cpu = {"value": bs / dt * (ns / args.n), "unit": UNIT, "cores": cores, "kind": "port",
-               "sample": f"{bs} queries x {ns} rows/docs ({dt:.1f} s CPU wall), QPS scaled by {ns}/{args.n} (cost linear in N)"}
+               "sample": f"{bs} queries x {ns} rows/docs, {reps} passes ({dt * reps:.1f} s CPU wall), QPS scaled by "
+                         f"{ns}/{args.n} (cost linear in N); the --impl reference arm times the same sample"}
 
     if rank == 0:
         dense_ms = stage_ms["dense_scan"] / max(1, stage_calls["dense_scan"])
-        flops = 2.0 * n_loc * args.d * args.batch
+        n_scan = n_loc * (sel_real if sel_real else 1.0)          # rows the tensor-core scan really multiplies
+        flops = 2.0 * n_scan * args.d * args.batch
         ach = flops / (dense_ms * 1e-3) / 1e12 if dense_ms > 0 else 0.0
         bm_ms = stage_ms["sparse_scan"] / max(1, stage_calls["sparse_scan"])
+        bm_bytes = bm25_bytes * (sel_real if sel_real else 1.0)   # postings of the documents that pass the filter
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": args.dtype, "data": "synthetic", "config": config_dict(args, world),
-            "e2e": e2e, "gpu_launches": int(launches), "clocks": clk,
+            "e2e": e2e, "gpu_launches": int(launches), "clocks": clk, "parity": parity,
             "roofline": {"kernel": "dense_umma_kernel (tcgen05 scan + fused top-k)", "bound": "tensor", "achieved": ach,
                          "peak": peaks["tflops"], "unit": "TFLOP/s", "frac": ach / peaks["tflops"],
                          "peak_kind": f"{peaks['source']} sustained cuBLAS bf16", "traffic": ncu_traffic("dense_umma_kernel", world),
@@ -369,15 +548,23 @@ def main():
                          "frac_of_nominal_2250": ach / 2250.0},
             "cpu_baseline": cpu, "batch1": b1,
             "stages_ms_per_step": {s: stage_ms[s] / args.steps for s in stage_ms},
+            # N > 1: signal + fuse kernels of the sharded call, i.e. the exchange as this rank sees it -- it includes
+            # the wait for the slowest peer's lists
+            "exchange_ms": (stage_ms["merge"] / args.steps) if world > 1 else 0.0,
+            "exchange": (args.exchange if world > 1 else None),
+            "sparse_index_build_s": sparse_index_s,
             # second kernel of the step: the sparse scan against the HBM roofline, on the ALGORITHMIC bytes an
             # exhaustive posting scan reads (sum_t df_t * 8 B); `traffic` = DRAM bytes the pruning kernel really moves
             "bm25": {"kernel": "bm25x_scan_kernel (bitmap-filter BM25 scan + fused top-k)", "bound": "hbm",
-                     "algorithmic_bytes_per_step": bm25_bytes, "ms": bm_ms,
-                     "achieved_gbs": bm25_bytes / (bm_ms * 1e-3) / 1e9 if bm_ms > 0 else None,
+                     "algorithmic_bytes_per_step": bm_bytes, "ms": bm_ms,
+                     "achieved_gbs": bm_bytes / (bm_ms * 1e-3) / 1e9 if bm_ms > 0 else None,
                      "peak_gbs": peaks["hbm_gbs"],
-                     "frac": bm25_bytes / (bm_ms * 1e-3) / 1e9 / peaks["hbm_gbs"] if bm_ms > 0 else None,
+                     "frac": bm_bytes / (bm_ms * 1e-3) / 1e9 / peaks["hbm_gbs"] if bm_ms > 0 else None,
                      "traffic": ncu_traffic("bm25x_scan_kernel", world)},
         }
+        if mask_id:
+            line["filter"] = {"selectivity": sel_real, "first_call_ms_incl_compacted_copy_and_index_build": first_call_ms,
+                              "unfiltered": unfiltered}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()

@@ -267,10 +267,14 @@ class OracleCollection:
         self.n = max(self.n, csr.n_docs)
 
     def prep_query(self, name: str, q: Sequence[float]) -> np.ndarray:
+        """The query stays float32 whatever the storage dtype of the space: qdrant holds the query vector the
+        reference sends (qdrant_handler.py:363-369, a Python float list) in float32 and only the STORED vectors
+        carry a datatype.  (Round 1 rounded it to the storage dtype on both sides; the engine now only feeds the
+        rounded copy to its 16-bit tensor-core scan and re-scores the candidates with the float32 query.)"""
         q = np.asarray(q, dtype=np.float32)
         if self.distance[name] == "cosine":
             q = normalize_rows(q[None, :])[0]
-        return round_storage(q, self.storage[name])
+        return q
 
 
 @dataclass
@@ -283,9 +287,19 @@ class Node:
     mask: Optional[np.ndarray] = None
 
 
-def run_node(col: OracleCollection, node: Node, rrf_tie: str = "id") -> Tuple[np.ndarray, np.ndarray]:
-    """Item 5: bottom-up evaluation of the prefetch tree.  Returns (scores, ids)."""
-    child = [run_node(col, c, rrf_tie) for c in node.prefetch]
+def run_node(col: OracleCollection, node: Node, rrf_tie: str = "id", propagate: bool = False,
+             _inherited: Optional[np.ndarray] = None) -> Tuple[np.ndarray, np.ndarray]:
+    """Item 5: bottom-up evaluation of the prefetch tree.  Returns (scores, ids).
+    propagate=False is qdrant-client LOCAL mode: a filter acts on the node that carries it.  propagate=True is the
+    Qdrant SERVER's planner, which merges a request's filter into every prefetch below it (the reference talks to a
+    server and passes query_filter at the root, qdrant_handler.py:363-372) -- restated from upstream knowledge like the
+    rest of this file, pinned by tests/golden/kat.json: tree.final_masked_server."""
+    own = node.mask
+    if _inherited is not None:
+        own = _inherited if own is None else (own & _inherited)
+    child = [run_node(col, c, rrf_tie, propagate, own if propagate else None) for c in node.prefetch]
+    if _inherited is not None:
+        node = Node(node.query, node.using, node.limit, node.prefetch, own)
     if isinstance(node.query, str) and node.query == "rrf":
         lim = node.limit if node.limit is not None else DEFAULT_FUSION_LIMIT
         s, i = rrf([c[1] for c in child], limit=lim, tie=rrf_tie)

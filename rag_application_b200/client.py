@@ -49,8 +49,25 @@ def _normalize_rows(x: np.ndarray) -> np.ndarray:
 
 
 # ------------------------------------------------------------------------------ payload filters
+_UNSUPPORTED_COND = ("values_count", "geo_bounding_box", "geo_radius", "geo_polygon", "is_empty", "is_null", "nested")
+_UNSUPPORTED_MATCH = ("text", "except", "except_", "phrase")
+
+
 def _match_column(col: List[Any], cond) -> np.ndarray:
     match, rng = _get(cond, "match"), _get(cond, "range")
+    # anything this compiler does not evaluate is refused, never silently matched (the reference builds
+    # Filter(**filters) from an arbitrary dict, qdrant_handler.py:297)
+    for f in _UNSUPPORTED_COND:
+        if _get(cond, f) is not None:
+            raise NotImplementedError(f"filter condition {f!r} is not supported")
+    if match is None and rng is None:
+        raise NotImplementedError(f"field condition on {_get(cond, 'key')!r} carries neither match nor range")
+    if match is not None:
+        for f in _UNSUPPORTED_MATCH:
+            if _get(match, f) is not None:
+                raise NotImplementedError(f"match.{f} is not supported (match.value / match.any only)")
+        if _get(match, "any") is None and _get(match, "value") is None:
+            raise NotImplementedError("match carries neither value nor any")
     out = np.ones(len(col), dtype=bool)
     if match is not None:
         if _get(match, "any") is not None:
@@ -213,6 +230,15 @@ class _Collection:
                 for lst in self.sparse_rows.values():
                     lst.append(None)
             self.payloads[row] = payload
+            # an upsert replaces the whole point (qdrant): named vectors the new point does not carry are gone
+            for vname, lst in self.dense_rows.items():
+                if vname not in dense and lst[row] is not None:
+                    lst[row] = None
+                    self.dense_in_hbm[vname] = 0              # presence changed: re-upload the space at the next commit
+            for vname, lst in self.sparse_rows.items():
+                if vname not in sparse and lst[row] is not None:
+                    lst[row] = None
+                    self.sparse_dirty[vname] = True
             for vname, a in dense.items():
                 self.dense_rows[vname][row] = a
                 if row < self.dense_in_hbm.get(vname, 0):
@@ -326,7 +352,10 @@ class B200QdrantCore:
     MAX_MASKS = 64
 
     def __init__(self, device: int = 0, storage: Optional[str] = None, engine_factory: Optional[Callable] = None,
-                 rrf_tie: str = "id"):
+                 rrf_tie: str = "id", filter_propagation: str = "server"):
+        if filter_propagation not in ("server", "local"):
+            raise ValueError("filter_propagation must be 'server' or 'local'")
+        self.filter_propagation = filter_propagation
         if engine_factory is None:
             from .engine import Engine      # fails loudly if libbrag.so / a B200 is missing
             engine_factory = Engine
@@ -468,18 +497,28 @@ class B200QdrantCore:
         s, i = np.concatenate(ss)[None, :], np.concatenate(ii)[None, :]
         return s, i, np.array([s.shape[1]], np.int32)
 
-    def _run(self, col: _Collection, query, using, limit, prefetch, flt) -> Tuple[np.ndarray, np.ndarray]:
-        """Bottom-up evaluation of one Prefetch / top-level request -> (scores, rows), best first."""
+    def _run(self, col: _Collection, query, using, limit, prefetch, flt, inherited=(None, None)
+             ) -> Tuple[np.ndarray, np.ndarray]:
+        """Bottom-up evaluation of one Prefetch / top-level request -> (scores, rows), best first.
+        inherited = (mask, cache key) of the ancestors' filters: a Qdrant SERVER merges the filter of a request into
+        every prefetch below it (the reference talks to a server and passes query_filter at the root,
+        qdrant_handler.py:363-372), so with filter_propagation="server" every leaf scan already runs under it;
+        "local" keeps qdrant-client local mode's behaviour (a filter acts only on the node that carries it)."""
         n = len(col)
         limit = DEFAULT_LIMIT if limit is None else int(limit)
         empty = (np.zeros(0, np.float64), np.zeros(0, np.int64))
+        fmask = None if flt is None else compile_filter(flt, col.payloads, col.ids)
+        fkey = self._filter_key(flt)
+        if inherited[0] is not None:
+            fmask = inherited[0] if fmask is None else (fmask & inherited[0])
+            fkey = (inherited[1], fkey)
+        down = (fmask, fkey) if self.filter_propagation == "server" else (None, None)
         if prefetch is None:
             kids = []
         else:
             plist = prefetch if isinstance(prefetch, (list, tuple)) else [prefetch]
             kids = [self._run(col, _get(p, "query"), _get(p, "using"), _get(p, "limit"), _get(p, "prefetch"),
-                              _get(p, "filter")) for p in plist]
-        fmask = None if flt is None else compile_filter(flt, col.payloads, col.ids)
+                              _get(p, "filter"), down) for p in plist]
 
         fusion = _get(query, "fusion")
         if fusion is not None:
@@ -516,7 +555,7 @@ class B200QdrantCore:
             terms, vals = self._sparse_query(col, using, query)
             if len(terms) == 0 or col.n_sparse.get(using, 0) == 0:
                 return empty
-            mask, key = fmask, self._filter_key(flt)
+            mask, key = fmask, fkey
             if cand is not None:
                 cm = np.zeros(n, dtype=bool)
                 cm[cand] = True
@@ -537,7 +576,7 @@ class B200QdrantCore:
             present = col.present.get(using)
             if present is not None and not present.any():
                 return empty
-            mask, key = fmask, self._filter_key(flt)
+            mask, key = fmask, fkey
             if present is not None:
                 mask, key = (present if mask is None else (present & mask)), (("present", using, key))
             if cand is not None:
@@ -605,15 +644,27 @@ class B200QdrantCore:
                 vals.append(v)
                 ptr.append(ptr[-1] + len(t))
             fmask = None if query_filter is None else compile_filter(query_filter, col.payloads, col.ids)
-            mid = self._mask_id(col, fmask, self._filter_key(query_filter))
+            fkey = self._filter_key(query_filter)
+            mid = self._mask_id(col, fmask, fkey)
             k = min(int(limit), len(col))
             if k > self.ENGINE_MAX_K:
                 raise ValueError(f"hybrid_search_batch: limit {k} exceeds the engine's {self.ENGINE_MAX_K}-entry lists; "
                                  "use query_points (paged) for longer lists")
-            s, i, c = self.engine.hybrid_topk(col.space(using_dense), col.space(using_sparse), Q,
-                                              np.asarray(ptr, np.int32),
-                                              np.concatenate(terms) if terms else np.zeros(0, np.int32),
-                                              np.concatenate(vals) if vals else np.zeros(0, np.float64), k, mid)
+            q_ptr = np.asarray(ptr, np.int32)
+            q_terms = np.concatenate(terms) if terms else np.zeros(0, np.int32)
+            q_vals = np.concatenate(vals) if vals else np.zeros(0, np.float64)
+            present = col.present.get(using_dense)
+            if present is None:
+                s, i, c = self.engine.hybrid_topk(col.space(using_dense), col.space(using_sparse), Q, q_ptr, q_terms,
+                                                  q_vals, k, mid)
+            else:
+                # some points lack the dense vector (zero rows in HBM): they stay out of the dense list only, so the
+                # two stages run under different masks and are fused by brag_rrf
+                dmid = self._mask_id(col, present if fmask is None else (fmask & present), ("present", using_dense, fkey))
+                _, di, dc = self.engine.dense_topk(col.space(using_dense), Q, k, dmid)
+                _, si, sc = self.engine.sparse_topk(col.space(using_sparse), q_ptr, q_terms, q_vals, k, mid)
+                s, i, c = self.engine.rrf(np.stack([np.asarray(di), np.asarray(si)]),
+                                          np.stack([np.asarray(dc), np.asarray(sc)]), k, 0)
             s, i, c = np.asarray(s), np.asarray(i), np.asarray(c)
             return [self._points(col, s[b, :int(c[b])], i[b, :int(c[b])], with_payload) for b in range(len(sparse_queries))]
 
@@ -625,8 +676,9 @@ class B200QdrantClient:
     mutations / queries of one client are serialised (interleaved awaits are safe)."""
 
     def __init__(self, device: int = 0, storage: Optional[str] = None, engine_factory: Optional[Callable] = None,
-                 rrf_tie: str = "id", **_ignored):
-        self._core = B200QdrantCore(device=device, storage=storage, engine_factory=engine_factory, rrf_tie=rrf_tie)
+                 rrf_tie: str = "id", filter_propagation: str = "server", **_ignored):
+        self._core = B200QdrantCore(device=device, storage=storage, engine_factory=engine_factory, rrf_tie=rrf_tie,
+                                    filter_propagation=filter_propagation)
 
     @property
     def core(self) -> B200QdrantCore:

@@ -467,7 +467,8 @@ void dense_topk_dev(brag_engine* e, DenseSpace& s, const float* Q, int B, int k,
     }
     {
         StageTimer t(e, 1, st);
-        CK(brag::rescore_keys(X, s.dtype, n, s.d, qs, B, cand, k_sel, cand2, st));
+        // exact scores: float64 dot of the stored row with the caller's float32 query (the rounded copy only fed the scan)
+        CK(brag::rescore_keys(X, s.dtype, n, s.d, Q, B, cand, k_sel, cand2, st));
         if (compact) {
             CK(brag::remap_keys(cand2, (int64_t)B * k_sel, s.cp_rowmap, st));
             e->kernel_launches += 1;
@@ -485,12 +486,10 @@ void dense_rescore_dev(brag_engine* e, DenseSpace& s, const float* Q, int B, con
                        cudaStream_t st) {
     REQUIRE(B >= 1 && k >= 1 && m >= 1 && m <= 8192 && k <= 8192, "dense_rescore: need m,k in [1,8192]");
     StageTimer t(e, 1, st);
-    float* qs = e->qs.as<float>((size_t)B * s.d);
     uint64_t* keys = e->keys1.as<uint64_t>((size_t)B * m);
-    CK(brag::round_queries(Q, B, s.d, s.dtype, qs, nullptr, B, st));
-    CK(brag::rescore_cands(s.x, s.dtype, s.n, s.d, qs, B, cand, m, e->id_offset, mask, keys, st));
+    CK(brag::rescore_cands(s.x, s.dtype, s.n, s.d, Q, B, cand, m, e->id_offset, mask, keys, st));
     CK(brag::finalize_keys(keys, B, m, k, true, e->id_offset, out_scores, out_ids, out_counts, st));
-    e->kernel_launches += 3;
+    e->kernel_launches += 2;
 }
 
 // longest query of a batch whose q_ptr lives on the device (one small D2H copy + stream sync)

@@ -102,12 +102,24 @@ def run_reference_flow(engine_factory=None, rtol=1e-5):
         assert [p.id for p in got] == [f"chunk-{r:04d}" for _, r in exp]
         np.testing.assert_allclose([p.score for p in got], [s for s, _ in exp], rtol=rtol, atol=1e-6)
         assert got[0].payload["content"] == f"text {exp[0][1]}"
-        # top-level payload filter (query_filter applies only at the top level)
+        # root payload filter: a Qdrant server (what the reference talks to) merges it into every prefetch -- the
+        # client's default; filter_propagation="local" keeps qdrant-client local mode (top level only)
         mask = np.array(c["mask"], bool)
         keep_rows = [int(i) for i in np.nonzero(mask)[0]]
         flt = M.Filter(must=[M.FieldCondition(key="row", match=M.MatchAny(any=keep_rows))])
         got = await reference_hybrid_search(client, user, q.tolist(), sv, sp, query_filter=flt)
+        assert [p.payload["row"] for p in got] == [r for _, r in c["final_masked_server"]]
+        client.core.filter_propagation = "local"
+        got = await reference_hybrid_search(client, user, q.tolist(), sv, sp, query_filter=flt)
         assert [p.payload["row"] for p in got] == [r for _, r in c["final_masked"]]
+        client.core.filter_propagation = "server"
+        # the batched shape and the tree of the same shape agree under a filter too
+        fb = await client.hybrid_search_batch(user, q[None, :], [sv], limit=10, query_filter=flt)
+        fo = await client.query_points(
+            collection_name=user, query=M.FusionQuery(fusion=M.Fusion.RRF), limit=10, query_filter=flt,
+            prefetch=[M.Prefetch(query=q.tolist(), using="dense", limit=10),
+                      M.Prefetch(query=M.SparseVector(indices=c["q_idx"], values=c["q_val"]), using="sparse", limit=10)])
+        assert [p.id for p in fb[0]] == [p.id for p in fo.points] and all(mask[int(p.id[-4:])] for p in fb[0])
         assert (await client.count(collection_name=user, count_filter=flt)).count == int(mask.sum())
         # Filter(**dict) spelling the reference uses (qdrant_handler.py:297)
         flt2 = M.Filter(**{"must": [{"key": "page_number", "match": {"value": 3}}]})

@@ -103,7 +103,7 @@ class OracleEngine:
     def dense_topk(self, name, Q, k, mask_id=0):
         self.calls.append(("dense_topk", name, k))
         x = self.dense[name]
-        q = O.round_storage(_np(Q).astype(np.float32), self.dtype[name])
+        q = _np(Q).astype(np.float32)      # the query stays float32 (oracle.prep_query)
         out = []
         for b in range(q.shape[0]):
             s, i = O.dense_topk(x, q[b], k, mask=self._mask(mask_id, x.shape[0]))
@@ -113,7 +113,7 @@ class OracleEngine:
     def dense_rescore(self, name, Q, cand, k, mask_id=0):
         self.calls.append(("dense_rescore", name, k))
         x = self.dense[name]
-        q = O.round_storage(_np(Q).astype(np.float32), self.dtype[name])
+        q = _np(Q).astype(np.float32)      # the query stays float32 (oracle.prep_query)
         cand = _np(cand)
         out = []
         for b in range(q.shape[0]):

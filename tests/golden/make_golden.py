@@ -179,10 +179,21 @@ def case_tree(seed=7, n=200, d=768, V=60):
     cand = [i for _, i in p4] + [i for _, i in f1]
     r = bf_dense(rows, q, sp["final_limit"], True, cand=cand)
     rm = bf_dense(rows, q, sp["final_limit"], True, cand=cand, mask=mask)
+    # the same request answered with SERVER semantics: Qdrant merges the root query_filter into every prefetch
+    # (the reference talks to a server, qdrant_session.py:21), so every stage ranks only the passing rows
+    m1 = bf_dense(pre(64), q[:64], sp["matryoshka_64_limit"], True, mask=mask)
+    m2 = bf_dense(pre(128), q[:128], sp["matryoshka_128_limit"], True, cand=[i for _, i in m1], mask=mask)
+    m3 = bf_dense(pre(256), q[:256], sp["matryoshka_256_limit"], True, cand=[i for _, i in m2], mask=mask)
+    m4 = bf_dense(rows, q, sp["dense_limit"], True, cand=[i for _, i in m3], mask=mask)
+    n1 = bf_dense(quant_rows, bf_quant(q), sp["quantized_limit"], True, mask=mask)
+    n2 = bf_dense(rows, q, sp["dense_limit"], True, cand=[i for _, i in n1], mask=mask)
+    t1 = bf_sparse(docs, q_idx, q_val, sp["sparse_limit"], mask=mask)
+    g1 = bf_rrf([[i for _, i in n2], [i for _, i in t1]], 10)
+    rs = bf_dense(rows, q, sp["final_limit"], True, cand=[i for _, i in m4] + [i for _, i in g1], mask=mask)
     return {"seed": seed, "n": n, "d": d, "V": V, "search_params": sp,
             "docs": docs, "q_idx": q_idx, "q_val": q_val, "mask": mask,
             "stages": {"P1": p1, "P4": p4, "Q1": q1, "Q2": q2, "S1": s1, "F1": f1},
-            "final": r, "final_masked": rm,
+            "final": r, "final_masked": rm, "final_masked_server": rs,
             "note": "dense rows/query are regenerated from the seed by the test (PCG64, same draws)"}
 
 

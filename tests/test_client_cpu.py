@@ -73,3 +73,52 @@ def test_errors_and_edge_cases():
 
 def test_limits_above_the_engine_list_length_on_oracle_engine():
     run_long_limits(engine_factory=OracleEngine)
+
+
+def test_unsupported_filter_conditions_are_refused():
+    """A condition the compiler does not evaluate raises instead of matching everything."""
+    import pytest
+    from rag_application_b200.client import compile_filter
+    payloads = [{"a": 1, "t": "x y"}, {"a": 2}, None]
+    ids = [0, 1, 2]
+    for bad in ({"must": [{"key": "t", "match": {"text": "x"}}]},
+                {"must": [{"key": "a", "match": {"except": [1]}}]},
+                {"must": [{"key": "a", "values_count": {"gt": 1}}]},
+                {"must_not": [{"key": "a", "is_empty": True}]},
+                {"should": [{"key": "a"}]},
+                {"must": [{"key": "a", "match": {}}]}):
+        with pytest.raises(NotImplementedError):
+            compile_filter(bad, payloads, ids)
+    assert compile_filter({"must": [{"key": "a", "match": {"value": 1}}]}, payloads, ids).tolist() == [True, False, False]
+
+
+def test_upsert_replaces_the_whole_point_and_batch_skips_points_without_the_dense_vector():
+    import asyncio
+    import numpy as np
+    from _oracle_engine import OracleEngine
+    from rag_application_b200 import models as M
+    from rag_application_b200.client import B200QdrantClient
+
+    async def flow():
+        cl = B200QdrantClient(engine_factory=OracleEngine)
+        await cl.create_collection(collection_name="c", vectors_config={"dense": M.VectorParams(size=4, distance=M.Distance.DOT)},
+                                   sparse_vectors_config={"sparse": M.SparseVectorParams()})
+        rng = np.random.default_rng(3)
+        pts = [M.PointStruct(id=i, vector={"dense": rng.standard_normal(4).tolist(), "sparse": {"indices": [1, 2 + i % 3], "values": [1.0, 0.5]}},
+                             payload={"i": i}) for i in range(12)]
+        await cl.upsert(collection_name="c", points=pts)
+        q = [1.0, 0.0, 0.0, 0.0]
+        before = await cl.query_points(collection_name="c", query=q, using="dense", limit=12)
+        assert len(before.points) == 12
+        # overwrite point 5 with a sparse-only point: its dense vector is gone, not kept
+        await cl.upsert(collection_name="c", points=[M.PointStruct(id=5, vector={"sparse": {"indices": [1], "values": [9.0]}}, payload={"i": 5})])
+        after = await cl.query_points(collection_name="c", query=q, using="dense", limit=12)
+        assert 5 not in [p.id for p in after.points] and len(after.points) == 11
+        sv = {"indices": [1], "values": [1.0]}
+        batch = await cl.hybrid_search_batch("c", np.array([q], np.float32), [sv], limit=12)
+        one = await cl.query_points(collection_name="c", query=M.FusionQuery(fusion=M.Fusion.RRF), limit=12,
+                                    prefetch=[M.Prefetch(query=q, using="dense", limit=12),
+                                              M.Prefetch(query=M.SparseVector(**sv), using="sparse", limit=12)])
+        assert [p.id for p in batch[0]] == [p.id for p in one.points]
+        assert 5 in [p.id for p in batch[0]]            # still a sparse hit
+    asyncio.run(flow())

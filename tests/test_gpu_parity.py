@@ -53,7 +53,7 @@ def test_dense_gemv(engine, dtype, n, d, B):
     for k in (10, 100):
         s, i, c = engine.dense_topk("t", q, k)
         for b in range(B):
-            check_dense(xs, O.round_storage(q[b], dtype), k, s[b], i[b], int(c[b]))
+            check_dense(xs, q[b], k, s[b], i[b], int(c[b]))
     engine.force_dense_path(None)
 
 
@@ -71,7 +71,7 @@ def test_dense_tcgen05(engine, dtype, n, d, B):
     s, i, c = engine.dense_topk("t", q, k)
     engine.force_dense_path(None)
     for b in range(0, B, max(1, B // 16)):
-        check_dense(xs, O.round_storage(q[b], dtype), k, s[b], i[b], int(c[b]))
+        check_dense(xs, q[b], k, s[b], i[b], int(c[b]))
 
 
 @pytest.mark.parametrize("masked", [False, True])
@@ -92,7 +92,7 @@ def test_dense_tcgen05_seeded_two_phase(engine, masked):
     engine.force_dense_path(None)
     assert np.array_equal(i[:8], i0) and np.array_equal(s[:8], s0)
     for b in range(0, B, 13):
-        check_dense(xs, O.round_storage(q[b], "bf16"), k, s[b], i[b], int(c[b]), mask=mask)
+        check_dense(xs, q[b], k, s[b], i[b], int(c[b]), mask=mask)
 
 
 @pytest.mark.parametrize("n,B", [(50_001, 512), (38_000, 256), (160_000, 1024)])
@@ -114,7 +114,7 @@ def test_dense_tcgen05_shared_row_ranges(engine, n, B):
     engine.force_dense_path(None)
     assert np.array_equal(i[rows], i0) and np.array_equal(s[rows], s0)
     for b in range(5, B, 61):
-        check_dense(xs, O.round_storage(q[b], "f16"), k, s[b], i[b], int(c[b]), mask=mask)
+        check_dense(xs, q[b], k, s[b], i[b], int(c[b]), mask=mask)
 
 
 def test_dense_paths_agree(engine):
@@ -146,7 +146,7 @@ def test_dense_mask_and_offset(engine, path):
     engine.force_dense_path(None)
     engine.set_id_offset(0)
     for b in range(0, B, max(1, B // 8)):
-        check_dense(xs, O.round_storage(q[b], "f16"), k, s[b], i[b], int(c[b]), mask=mask, id_offset=1_000_000)
+        check_dense(xs, q[b], k, s[b], i[b], int(c[b]), mask=mask, id_offset=1_000_000)
     # a mask that keeps fewer rows than k: short list, padded with -1
     tiny = np.zeros(n, dtype=bool)
     tiny[[5, 77, 4000]] = True
@@ -180,7 +180,7 @@ def test_dense_filter_compacted_copy(engine, B):
         assert np.array_equal(i, i3) and np.array_equal(s.view(np.uint32), s3.view(np.uint32)) and np.array_equal(c, c3)
         assert mask[i[np.arange(k)[None, :] < c[:, None]]].all()
         for b in range(0, B, max(1, B // 8)):
-            check_dense(xs, O.round_storage(q[b], "bf16"), k, s[b], i[b], int(c[b]), mask=mask)
+            check_dense(xs, q[b], k, s[b], i[b], int(c[b]), mask=mask)
 
 
 @pytest.mark.parametrize("k", [416, 417, 512])
@@ -198,7 +198,7 @@ def test_dense_longest_lists_on_16bit_storage(engine, k, dtype, d):
     for mid, m in ((0, None), (4, mask)):
         s, i, c = engine.dense_topk("x", q, k, mask_id=mid)
         for b in range(3):
-            check_dense(xs, O.round_storage(q[b], dtype), k, s[b], i[b], int(c[b]), mask=m)
+            check_dense(xs, q[b], k, s[b], i[b], int(c[b]), mask=m)
 
 
 @pytest.mark.parametrize("k", [300, 512])
@@ -698,6 +698,13 @@ def test_logical_shards_on_one_gpu_match_unsharded(engine, G):
     ids = np.stack([merged[0][1], merged[1][1]])
     cnt = np.stack([merged[0][2], merged[1][2]])
     s, i, c = engine.rrf(ids, cnt, k)
+    # the same through the sharded tail kernels (brag_shard_local_lists on every shard -> brag_shard_fuse)
+    keys = np.stack([e.shard_local_lists("dense", "sparse", q, q_ptr, q_terms, q_vals, k) for e in shards])
+    fs, fi, fc, (ts, ti, tc) = engine.shard_fuse(keys, k, stages=True)
     for e in shards:
         e.close()
     assert np.array_equal(c, ec) and np.array_equal(i, ei) and np.array_equal(s, es)
+    assert np.array_equal(fc, ec) and np.array_equal(fi, ei) and np.array_equal(fs, es)
+    for l in range(2):
+        assert np.array_equal(ti[l], merged[l][1]) and np.array_equal(tc[l], merged[l][2])
+        assert np.array_equal(ts[l].view(np.uint32), merged[l][0].view(np.uint32))

@@ -148,6 +148,10 @@ def test_reference_tree(kat):
     s, i = O.run_node(col, O.reference_tree(q, c["q_idx"], c["q_val"], sp, mask=mask))
     assert_ranked(pairs(s, i), c["final_masked"])
     assert all(mask[j] for j in i)
+    # server semantics: the root filter reaches every prefetch
+    s, i = O.run_node(col, O.reference_tree(q, c["q_idx"], c["q_val"], sp, mask=mask), propagate=True)
+    assert_ranked(pairs(s, i), c["final_masked_server"])
+    assert all(mask[j] for j in i) and len(i) == sp["final_limit"]
 
 
 # ------------------------------------------------------------------ (7) shard invariance (oracle level)
