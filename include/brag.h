@@ -177,6 +177,15 @@ int brag_shard_hybrid_topk(brag_engine* e, const char* dense_name, const char* s
                            int32_t on_device, void* stream);
 int brag_shard_close(brag_engine* e);
 
+/* Index persistence (the reference keeps Qdrant's index on a volume, docker-compose.yml:30-31, and
+ * reopens a user's collection at start-up, qdrant_handler.py:94-100).  brag_save writes every dense and sparse space of
+ * the engine -- rows, postings AND the scan indexes built from them -- to one flat file (header, section table,
+ * 4096-byte-aligned raw arrays; written to path.tmp and renamed); brag_load puts them back into HBM with nothing to
+ * rebuild and restores the id offset.  Spaces of the same name are replaced, others stay.  Filter masks and
+ * filter-compacted copies are query state and are not saved.  One file per engine, i.e. per shard. */
+int brag_save(brag_engine* e, const char* path);
+int brag_load(brag_engine* e, const char* path);
+
 /* Per-stage device timing (CUDA events on the call's stream).  Stages: 0 dense scan,
  * 1 dense select+rescore, 2 sparse scan, 3 sparse select, 4 rrf, 5 merge / sharded signal + fuse (includes the wait
  * for the slowest peer).

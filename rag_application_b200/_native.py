@@ -42,6 +42,8 @@ PROTOTYPES = {
     "brag_shard_hybrid_topk": (C.c_int, [c_p, C.c_char_p, C.c_char_p, c_p, c_p, c_p, c_p, i32, i32, i32, i32, c_p, c_p, c_p,
                                          c_p, c_p, c_p, i32, c_p]),
     "brag_shard_close": (C.c_int, [c_p]),
+    "brag_save": (C.c_int, [c_p, C.c_char_p]),
+    "brag_load": (C.c_int, [c_p, C.c_char_p]),
     "brag_profile_enable": (C.c_int, [c_p, i32]),
     "brag_profile_read": (C.c_int, [c_p, c_p, c_p, c_p]),
     "brag_profile_reset": (C.c_int, [c_p]),

@@ -347,19 +347,26 @@ class _Collection:
 # ------------------------------------------------------------------------------ synchronous core
 class B200QdrantCore:
     """Synchronous implementation; `B200QdrantClient` below wraps it in the async surface the
-    reference awaits.  One engine (one GPU) per client; spaces are named '<collection>\\x1f<vector>'."""
+    reference awaits.  One engine per client: one GPU (`device`), or every collection row-sharded over several
+    (`devices=[0, 1, ...]`, multi.py); spaces are named '<collection>\\x1f<vector>'."""
 
     MAX_MASKS = 64
 
     def __init__(self, device: int = 0, storage: Optional[str] = None, engine_factory: Optional[Callable] = None,
-                 rrf_tie: str = "id", filter_propagation: str = "server"):
+                 rrf_tie: str = "id", filter_propagation: str = "server", devices: Optional[Sequence[int]] = None,
+                 shard_block_rows: int = 1 << 16):
         if filter_propagation not in ("server", "local"):
             raise ValueError("filter_propagation must be 'server' or 'local'")
         self.filter_propagation = filter_propagation
         if engine_factory is None:
             from .engine import Engine      # fails loudly if libbrag.so / a B200 is missing
             engine_factory = Engine
-        self.engine = engine_factory(device)
+        if devices is not None and len(devices) > 1:
+            # every collection row-sharded over several GPUs behind the same engine contract (multi.py)
+            from .multi import MultiEngine
+            self.engine = MultiEngine(list(devices), engine_factory, shard_block_rows)
+        else:
+            self.engine = engine_factory(devices[0] if devices else device)
         self.default_storage = storage
         self.rrf_tie = 0 if rrf_tie == "id" else 1
         self.collections: Dict[str, _Collection] = {}
@@ -369,6 +376,39 @@ class B200QdrantCore:
 
     def close(self):
         self.engine.close()
+
+    # ---------------------------------------------------------------- persistence
+    def save(self, path: str):
+        """Write every collection to the directory `path`: the engine's flat index file(s) (brag_save: rows, postings
+        and the built scan indexes, one file per GPU) and the host-side tables (ids, payloads, vocabularies) -- what
+        Qdrant keeps on its volume (docker-compose.yml:30-31).  `load` reopens them without re-uploading or
+        rebuilding anything (qdrant_handler.py:94-100 finds the user's collection again at start-up)."""
+        import os
+        import pickle
+        with self._lock:
+            os.makedirs(path, exist_ok=True)
+            for col in self.collections.values():
+                col.commit(self.engine)
+            self.engine.save(os.path.join(path, "index.brag"))
+            state = {"format": 1, "collections": self.collections, "engine": self.engine.host_state()}
+            tmp = os.path.join(path, "host.pkl.tmp")
+            with open(tmp, "wb") as f:
+                pickle.dump(state, f, protocol=4)
+            os.replace(tmp, os.path.join(path, "host.pkl"))
+
+    def load(self, path: str):
+        import os
+        import pickle
+        with self._lock:
+            with open(os.path.join(path, "host.pkl"), "rb") as f:
+                state = pickle.load(f)
+            if state.get("format") != 1:
+                raise ValueError("unknown collection file format")
+            self.engine.load(os.path.join(path, "index.brag"), state["engine"])
+            for name, col in state["collections"].items():
+                col.mask_cache = {}
+                self.collections[name] = col
+            self._mask_owner.clear()
 
     # ---------------------------------------------------------------- collection management
     def get_collections(self) -> M.CollectionsResponse:
@@ -676,9 +716,11 @@ class B200QdrantClient:
     mutations / queries of one client are serialised (interleaved awaits are safe)."""
 
     def __init__(self, device: int = 0, storage: Optional[str] = None, engine_factory: Optional[Callable] = None,
-                 rrf_tie: str = "id", filter_propagation: str = "server", **_ignored):
+                 rrf_tie: str = "id", filter_propagation: str = "server", devices: Optional[Sequence[int]] = None,
+                 shard_block_rows: int = 1 << 16, **_ignored):
         self._core = B200QdrantCore(device=device, storage=storage, engine_factory=engine_factory, rrf_tie=rrf_tie,
-                                    filter_propagation=filter_propagation)
+                                    filter_propagation=filter_propagation, devices=devices,
+                                    shard_block_rows=shard_block_rows)
 
     @property
     def core(self) -> B200QdrantCore:
@@ -713,6 +755,12 @@ class B200QdrantClient:
 
     async def hybrid_search_batch(self, collection_name: str, *a, **kw):
         return await self._call(self._core.hybrid_search_batch, collection_name, *a, **kw)
+
+    async def save(self, path: str):
+        return await self._call(self._core.save, path)
+
+    async def load(self, path: str):
+        return await self._call(self._core.load, path)
 
     async def close(self):
         await self._call(self._core.close)

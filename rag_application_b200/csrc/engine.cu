@@ -451,13 +451,14 @@ void dense_topk_dev(brag_engine* e, DenseSpace& s, const float* Q, int B, int k,
                                      e->tmap_q, st, &launches, xb));
             e->kernel_launches += 1 + launches;
         } else {
-            CK(brag::round_queries(Q, B, s.d, s.dtype, qs, nullptr, B, st));
+            // the GEMV scan multiplies in float32 anyway: it takes the caller's float32 query as it is, so its
+            // candidates are ranked by (almost) the exact score whatever the storage dtype
             const int64_t ngroups = (s.n + 31) / 32;
             int grid = (int)std::min<int64_t>((int64_t)e->num_sms * 2, std::max<int64_t>(1, (ngroups + 15) / 16));
             const int P = grid;
             uint64_t* part = e->part.as<uint64_t>((size_t)P * B * k_sel);
             int launches = 0;
-            CK(brag::dense_gemv_scan(s.x, s.dtype, s.n, s.d, qs, B, mask, k_sel, part, grid, st, &launches));
+            CK(brag::dense_gemv_scan(s.x, s.dtype, s.n, s.d, Q, B, mask, k_sel, part, grid, st, &launches));
             size_t tmp = brag::merge_tmp_elems(P, B, k_sel);
             uint64_t* ta = e->tmp_a.as<uint64_t>(tmp);
             uint64_t* tb = e->tmp_b.as<uint64_t>(tmp);
@@ -1487,6 +1488,239 @@ int brag_force_dense_path(brag_engine* e, int32_t path) {
         REQUIRE(e && path >= -1 && path <= 2, "brag_force_dense_path: path must be -1, 0, 1 or 2");
         e->force_path = path == 2 ? 1 : path;
         e->no_compact = path == 2;
+    });
+}
+
+}  // extern "C"
+
+// ---- index persistence (the reference keeps its index on a volume, docker-compose.yml:30-31, and
+// reopens per-user collections, qdrant_handler.py:94-100) ------------------------------------------
+// One flat file per engine (= per shard): a header, a section table, then 4096-byte-aligned raw arrays exactly as they
+// live in HBM -- the dense rows, the postings AND the scan indexes built from them (sub-tile offsets, weight bounds,
+// class thresholds, term maps), so loading is a straight copy with nothing to rebuild.
+namespace {
+
+constexpr char PERSIST_MAGIC[8] = {'B', 'R', 'A', 'G', 'I', 'D', 'X', '2'};
+
+struct PersistSection {
+    char name[96];
+    int32_t kind;             // 0 dense rows, 1 sparse array
+    int32_t which;            // sparse: 0 term_ptr 1 post 2 sub_off 3 wrange 4 tau 5 bm_row 6 bits 7 bits_hi
+    int64_t a, b, c, d;       // dense: n, d, dtype, 0      sparse (on `which` 0): V, n_docs, nnz, n_dense | bitmap_ok << 32
+    uint64_t offset, bytes;
+};
+
+struct PersistHeader {
+    char magic[8];
+    int64_t id_offset;
+    int64_t n_sections;
+    uint64_t data_offset;
+};
+
+struct FileCloser {
+    FILE* f;
+    ~FileCloser() { if (f) fclose(f); }
+};
+
+void write_device_array(FILE* f, const void* dev, size_t bytes, void* stage, size_t stage_bytes) {
+    for (size_t off = 0; off < bytes; off += stage_bytes) {
+        const size_t n = std::min(stage_bytes, bytes - off);
+        CK(cudaMemcpy(stage, static_cast<const char*>(dev) + off, n, cudaMemcpyDeviceToHost));
+        REQUIRE(fwrite(stage, 1, n, f) == n, "brag_save: short write");
+    }
+}
+
+void read_device_array(FILE* f, void* dev, size_t bytes, void* stage, size_t stage_bytes) {
+    for (size_t off = 0; off < bytes; off += stage_bytes) {
+        const size_t n = std::min(stage_bytes, bytes - off);
+        REQUIRE(fread(stage, 1, n, f) == n, "brag_load: short read (truncated file)");
+        CK(cudaMemcpy(static_cast<char*>(dev) + off, stage, n, cudaMemcpyHostToDevice));
+    }
+}
+
+void pad_to(FILE* f, uint64_t target) {
+    static const char zeros[4096] = {0};
+    long at = ftell(f);
+    REQUIRE(at >= 0 && (uint64_t)at <= target, "brag_save: layout error");
+    uint64_t left = target - (uint64_t)at;
+    while (left) {
+        const size_t n = (size_t)std::min<uint64_t>(left, sizeof zeros);
+        REQUIRE(fwrite(zeros, 1, n, f) == n, "brag_save: short write");
+        left -= n;
+    }
+}
+
+struct SparseArrays {
+    const void* ptr[8];
+    size_t bytes[8];
+};
+
+SparseArrays sparse_arrays(const SparseSpace& s) {
+    const size_t ns1 = (size_t)((s.n_docs + brag::BM25_SUB - 1) / brag::BM25_SUB + 1);
+    const size_t row_bytes = (size_t)brag::bm25x_row_words(s.n_docs) * 4;
+    SparseArrays a;
+    a.ptr[0] = s.term_ptr; a.bytes[0] = (size_t)(s.V + 1) * sizeof(int64_t);
+    a.ptr[1] = s.post;     a.bytes[1] = (size_t)s.nnz * sizeof(uint2);
+    a.ptr[2] = s.sub_off;  a.bytes[2] = (size_t)s.V * ns1 * sizeof(uint32_t);
+    a.ptr[3] = s.wrange;   a.bytes[3] = (size_t)s.V * sizeof(float2);
+    a.ptr[4] = s.tau;      a.bytes[4] = (size_t)s.V * sizeof(float);
+    a.ptr[5] = s.bm_row;   a.bytes[5] = (size_t)s.V * sizeof(int32_t);
+    a.ptr[6] = s.bits;     a.bytes[6] = (size_t)s.n_dense * row_bytes;
+    a.ptr[7] = s.bits_hi;  a.bytes[7] = (size_t)s.n_dense * row_bytes;
+    return a;
+}
+
+}  // namespace
+
+extern "C" {
+
+int brag_save(brag_engine* e, const char* path) {
+    return guarded([&] {
+        REQUIRE(e && path, "brag_save: NULL argument");
+        use_device(e);
+        CK(cudaDeviceSynchronize());
+        std::vector<PersistSection> secs;
+        std::vector<const void*> src;
+        auto add = [&](const std::string& name, int kind, int which, int64_t a, int64_t b, int64_t c, int64_t d,
+                       const void* p, size_t bytes) {
+            PersistSection s;
+            std::memset(&s, 0, sizeof s);
+            REQUIRE(name.size() < sizeof s.name, "brag_save: space name too long");
+            std::memcpy(s.name, name.data(), name.size());
+            s.kind = kind; s.which = which; s.a = a; s.b = b; s.c = c; s.d = d; s.bytes = bytes;
+            secs.push_back(s);
+            src.push_back(p);
+        };
+        for (auto& kv : e->dense)
+            add(kv.first, 0, 0, kv.second.n, kv.second.d, kv.second.dtype, 0, kv.second.x,
+                (size_t)kv.second.n * kv.second.d * (kv.second.dtype == 0 ? 4 : 2));
+        for (auto& kv : e->sparse) {
+            const SparseSpace& s = kv.second;
+            const SparseArrays arr = sparse_arrays(s);
+            for (int w = 0; w < 8; ++w)
+                add(kv.first, 1, w, s.V, s.n_docs, s.nnz, (int64_t)s.n_dense | ((int64_t)(s.bitmap_ok ? 1 : 0) << 32),
+                    arr.ptr[w], arr.bytes[w]);
+        }
+        PersistHeader h;
+        std::memcpy(h.magic, PERSIST_MAGIC, 8);
+        h.id_offset = e->id_offset;
+        h.n_sections = (int64_t)secs.size();
+        auto up = [](uint64_t x) { return (x + 4095) & ~(uint64_t)4095; };
+        h.data_offset = up(sizeof h + secs.size() * sizeof(PersistSection));
+        uint64_t at = h.data_offset;
+        for (auto& s : secs) { s.offset = at; at = up(at + s.bytes); }
+        const std::string tmp = std::string(path) + ".tmp";
+        FILE* f = fopen(tmp.c_str(), "wb");
+        REQUIRE(f != nullptr, std::string("brag_save: cannot open ") + tmp);
+        FileCloser fc{f};
+        const size_t stage_bytes = (size_t)64 << 20;
+        void* stage = nullptr;
+        CK(cudaMallocHost(&stage, stage_bytes));
+        try {
+            REQUIRE(fwrite(&h, sizeof h, 1, f) == 1, "brag_save: short write");
+            if (!secs.empty()) REQUIRE(fwrite(secs.data(), sizeof(PersistSection), secs.size(), f) == secs.size(), "brag_save: short write");
+            for (size_t i = 0; i < secs.size(); ++i) {
+                pad_to(f, secs[i].offset);
+                if (secs[i].bytes) write_device_array(f, src[i], secs[i].bytes, stage, stage_bytes);
+            }
+        } catch (...) {
+            cudaFreeHost(stage);
+            throw;
+        }
+        cudaFreeHost(stage);
+        REQUIRE(fflush(f) == 0, "brag_save: flush failed");
+        fclose(f);
+        fc.f = nullptr;
+        REQUIRE(rename(tmp.c_str(), path) == 0, "brag_save: cannot move the finished file into place");
+    });
+}
+
+int brag_load(brag_engine* e, const char* path) {
+    return guarded([&] {
+        REQUIRE(e && path, "brag_load: NULL argument");
+        use_device(e);
+        FILE* f = fopen(path, "rb");
+        REQUIRE(f != nullptr, std::string("brag_load: cannot open ") + path);
+        FileCloser fc{f};
+        PersistHeader h;
+        REQUIRE(fread(&h, sizeof h, 1, f) == 1 && std::memcmp(h.magic, PERSIST_MAGIC, 8) == 0,
+                "brag_load: not an index file of this library version");
+        REQUIRE(h.n_sections >= 0 && h.n_sections < (1 << 20), "brag_load: corrupt header");
+        std::vector<PersistSection> secs((size_t)h.n_sections);
+        if (!secs.empty()) REQUIRE(fread(secs.data(), sizeof(PersistSection), secs.size(), f) == secs.size(), "brag_load: truncated section table");
+        CK(cudaDeviceSynchronize());
+        const size_t stage_bytes = (size_t)64 << 20;
+        void* stage = nullptr;
+        CK(cudaMallocHost(&stage, stage_bytes));
+        std::map<std::string, SparseSpace> loading;
+        try {
+            for (auto& s : secs) {
+                s.name[sizeof s.name - 1] = 0;
+                const std::string name(s.name);
+                REQUIRE(fseek(f, (long)s.offset, SEEK_SET) == 0, "brag_load: seek failed");
+                if (s.kind == 0) {
+                    auto it = e->dense.find(name);
+                    if (it != e->dense.end()) { free_dense(it->second); e->dense.erase(it); }
+                    DenseSpace ds;
+                    ds.n = s.a; ds.cap = s.a; ds.d = (int)s.b; ds.dtype = (int)s.c;
+                    REQUIRE(ds.n >= 1 && ds.d >= 1 && ds.dtype >= 0 && ds.dtype <= 2 &&
+                            s.bytes == (uint64_t)ds.n * ds.d * (ds.dtype == 0 ? 4 : 2), "brag_load: corrupt dense section");
+                    CK(cudaMalloc(&ds.x, s.bytes));
+                    try {
+                        read_device_array(f, ds.x, s.bytes, stage, stage_bytes);
+                    } catch (...) {
+                        cudaFree(ds.x);
+                        throw;
+                    }
+                    ds.umma_ok = brag::dense_umma_supported(ds.dtype, ds.d, ds.n) &&
+                                 brag::make_tmap_2d(ds.tmap_x, ds.x, ds.n, ds.d, 256) == cudaSuccess;
+                    e->dense[name] = ds;
+                } else if (s.kind == 1) {
+                    SparseSpace& sp = loading[name];
+                    sp.V = s.a; sp.n_docs = s.b; sp.nnz = s.c;
+                    sp.n_dense = (int)(s.d & 0xFFFFFFFFll);
+                    sp.bitmap_ok = ((s.d >> 32) & 1) != 0;
+                    REQUIRE(s.which >= 0 && s.which < 8 && sp.V >= 1 && sp.n_docs >= 1, "brag_load: corrupt sparse section");
+                    REQUIRE(sparse_arrays(sp).bytes[s.which] == s.bytes, "brag_load: sparse section has the wrong size");
+                    void* p = nullptr;
+                    CK(cudaMalloc(&p, std::max<size_t>(s.bytes, 256)));
+                    switch (s.which) {
+                        case 0: sp.term_ptr = static_cast<int64_t*>(p); break;
+                        case 1: sp.post = static_cast<uint2*>(p); break;
+                        case 2: sp.sub_off = static_cast<uint32_t*>(p); break;
+                        case 3: sp.wrange = static_cast<float2*>(p); break;
+                        case 4: sp.tau = static_cast<float*>(p); break;
+                        case 5: sp.bm_row = static_cast<int32_t*>(p); break;
+                        case 6: sp.bits = static_cast<uint32_t*>(p); break;
+                        default: sp.bits_hi = static_cast<uint32_t*>(p); break;
+                    }
+                    if (s.bytes) read_device_array(f, p, s.bytes, stage, stage_bytes);
+                    if (s.which == 0) {
+                        sp.term_ptr_host.resize((size_t)sp.V + 1);
+                        CK(cudaMemcpy(sp.term_ptr_host.data(), sp.term_ptr, (size_t)(sp.V + 1) * sizeof(int64_t), cudaMemcpyDeviceToHost));
+                        REQUIRE(sp.term_ptr_host[0] == 0 && sp.term_ptr_host[(size_t)sp.V] == sp.nnz, "brag_load: corrupt term_ptr");
+                    }
+                } else {
+                    throw BragError("brag_load: unknown section kind");
+                }
+            }
+            for (auto& kv : loading) {
+                SparseSpace& sp = kv.second;
+                REQUIRE(sp.term_ptr && sp.post && sp.sub_off && sp.wrange && sp.tau && sp.bm_row && sp.bits && sp.bits_hi,
+                        "brag_load: a sparse space is missing sections");
+            }
+        } catch (...) {
+            cudaFreeHost(stage);
+            for (auto& kv : loading) free_sparse(kv.second);
+            throw;
+        }
+        cudaFreeHost(stage);
+        for (auto& kv : loading) {
+            auto it = e->sparse.find(kv.first);
+            if (it != e->sparse.end()) { free_sparse(it->second); e->sparse.erase(it); }
+            e->sparse[kv.first] = std::move(kv.second);
+        }
+        e->id_offset = h.id_offset;
     });
 }
 

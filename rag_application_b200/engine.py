@@ -348,6 +348,21 @@ class Engine:
     def shard_close(self):
         _native.check(self._lib.brag_shard_close(self._h))
 
+    # ------------------------------------------------------------------ persistence
+    def save(self, path: str):
+        """Every space of this engine (rows, postings, built scan indexes) -> one flat file."""
+        _native.check(self._lib.brag_save(self._h, str(path).encode()))
+
+    def load(self, path: str, host_state: Optional[dict] = None):
+        """Spaces of a file written by save() back into HBM (nothing is rebuilt).  `host_state`: what host_state()
+        returned when the file was written (the {dense name: (n, d, dtype)} table dense_append / dense_update need)."""
+        _native.check(self._lib.brag_load(self._h, str(path).encode()))
+        if host_state:
+            self._spaces.update({k: tuple(v) for k, v in host_state["spaces"].items()})
+
+    def host_state(self) -> dict:
+        return {"spaces": dict(self._spaces)}
+
     # ------------------------------------------------------------------ introspection
     def profile_enable(self, on: bool = True):
         _native.check(self._lib.brag_profile_enable(self._h, int(on)))

@@ -81,11 +81,11 @@ async def reference_hybrid_search(client, user_id, dense_vector, sparse_vector, 
     return res.points
 
 
-def run_reference_flow(engine_factory=None, rtol=1e-5):
+def run_reference_flow(engine_factory=None, rtol=1e-5, **client_kw):
     c, x, q = load_tree_case()
 
     async def flow():
-        client = B200QdrantClient(engine_factory=engine_factory)
+        client = B200QdrantClient(engine_factory=engine_factory, **client_kw)
         user = "user-42"
         assert [col.name for col in (await client.get_collections()).collections] == []
         await reference_create_collection(client, user)
@@ -152,7 +152,7 @@ def run_reference_flow(engine_factory=None, rtol=1e-5):
     asyncio.run(flow())
 
 
-def run_incremental_upsert(engine_factory=None, storage=None):
+def run_incremental_upsert(engine_factory=None, storage=None, **client_kw):
     """points upserted after the first query are appended / overwritten in HBM
     (brag_dense_append / brag_dense_update / brag_sparse_append) and must answer exactly like a collection uploaded
     in one go; overwriting a stored sparse vector falls back to a rebuild of that space."""
@@ -168,7 +168,7 @@ def run_incremental_upsert(engine_factory=None, storage=None):
                              payload={"i": int(i)})
 
     def make():
-        kw = {"engine_factory": engine_factory} if engine_factory else {}
+        kw = dict({"engine_factory": engine_factory} if engine_factory else {}, **client_kw)
         core = B200QdrantCore(storage=storage, **kw)
         core.create_collection("c", vectors_config={"dense": M.VectorParams(size=d, distance=M.Distance.COSINE)},
                                sparse_vectors_config={"sparse": M.SparseVectorParams()})
@@ -221,7 +221,7 @@ def run_incremental_upsert(engine_factory=None, storage=None):
     full.close()
 
 
-def run_long_limits(engine_factory=None, storage=None):
+def run_long_limits(engine_factory=None, storage=None, **client_kw):
     """Prefetch limits above the engine's list length (the reference lets an LLM choose them,
     hybrid_search_workflow.py:28-66) are served in pages: ids must come back in exactly the brute-force order."""
     from rag_application_b200.client import B200QdrantCore
@@ -229,7 +229,7 @@ def run_long_limits(engine_factory=None, storage=None):
     n, d, V = 1500, 32, 300
     x = rng.standard_normal((n, d)).astype(np.float32)
     sp = [(np.sort(rng.choice(V, 6, replace=False)), (rng.random(6) + 0.1).astype(np.float32)) for _ in range(n)]
-    kw = {"engine_factory": engine_factory} if engine_factory else {}
+    kw = dict({"engine_factory": engine_factory} if engine_factory else {}, **client_kw)
     core = B200QdrantCore(storage=storage, **kw)
     core.create_collection("c", vectors_config={"dense": M.VectorParams(size=d, distance=M.Distance.COSINE)},
                            sparse_vectors_config={"sparse": M.SparseVectorParams()})
@@ -286,3 +286,50 @@ def run_long_limits(engine_factory=None, storage=None):
     worst_kept = min(p.score for p in got)
     assert all(sc[i] <= worst_kept + 1e-6 for i in range(n) if hit[i] and i not in set(ids))
     core.close()
+
+
+def run_save_load(tmpdir, engine_factory=None, storage=None, **client_kw):
+    """SURVEY 8 f2 persistence: save -> a NEW client -> load answers exactly like the one that saved, and goes on taking
+    incremental upserts (the loaded spaces are appended to in HBM, not re-uploaded)."""
+    from rag_application_b200.client import B200QdrantCore
+    rng = np.random.Generator(np.random.PCG64(123))
+    n, d = 700, 64
+    x = rng.standard_normal((n + 40, d)).astype(np.float32)
+    sp = [(np.sort(rng.choice(400, 6, replace=False)), rng.random(6).astype(np.float32) + 0.1) for _ in range(n + 40)]
+    kw = dict({"engine_factory": engine_factory} if engine_factory else {}, **client_kw)
+
+    def point(i):
+        return M.PointStruct(id=f"p{i}", vector={"dense": x[i].tolist(),
+                                                 "sparse": M.SparseVector(indices=sp[i][0].tolist(), values=sp[i][1].tolist())},
+                             payload={"i": int(i), "page_number": int(i % 4)})
+
+    def ask(core, flt=None):
+        r = core.query_points("c", prefetch=[M.Prefetch(query=x[9].tolist(), using="dense", limit=40),
+                                             M.Prefetch(query=M.SparseVector(indices=sp[3][0].tolist(), values=sp[3][1].tolist()),
+                                                        using="sparse", limit=40)],
+                              query=M.FusionQuery(fusion=M.Fusion.RRF), limit=20, query_filter=flt).points
+        return [(p.id, p.score, p.payload["i"]) for p in r]
+
+    a = B200QdrantCore(storage=storage, **kw)
+    a.create_collection("c", vectors_config={"dense": M.VectorParams(size=d, distance=M.Distance.COSINE)},
+                        sparse_vectors_config={"sparse": M.SparseVectorParams(modifier=M.Modifier.IDF)})
+    a.upsert("c", [point(i) for i in range(n)])
+    flt = M.Filter(must=[M.FieldCondition(key="page_number", match=M.MatchValue(value=2))])
+    want, want_f = ask(a), ask(a, flt)
+    a.save(str(tmpdir))
+    b = B200QdrantCore(storage=storage, **kw)
+    calls = []
+    for name in ("dense_set", "sparse_set_csr"):
+        orig = getattr(b.engine, name)
+        setattr(b.engine, name, (lambda o, nm: (lambda *aa, **k: (calls.append(nm), o(*aa, **k))[1]))(orig, name))
+    b.load(str(tmpdir))
+    assert [c.name for c in b.get_collections().collections] == ["c"] and b.get_collection("c").points_count == n
+    assert ask(b) == want and ask(b, flt) == want_f
+    assert calls == [], "load must not re-upload or rebuild a space"
+    # both go on: the same upserts give the same answers (append path on the loaded spaces)
+    for core in (a, b):
+        core.upsert("c", [point(i) for i in range(n, n + 40)])
+    assert ask(b) == ask(a) and ask(b, flt) == ask(a, flt)
+    assert calls == []
+    a.close()
+    b.close()

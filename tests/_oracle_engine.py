@@ -23,6 +23,22 @@ class OracleEngine:
     def close(self):
         pass
 
+    def save(self, path):
+        """CPU mirror of brag_save / brag_load (a pickle instead of the flat file)."""
+        import pickle
+        with open(path, "wb") as f:
+            pickle.dump({"dense": self.dense, "dtype": self.dtype, "sparse": self.sparse, "id_offset": self.id_offset}, f)
+
+    def load(self, path, host_state=None):
+        import pickle
+        with open(path, "rb") as f:
+            st = pickle.load(f)
+        self.dense.update(st["dense"]); self.dtype.update(st["dtype"]); self.sparse.update(st["sparse"])
+        self.id_offset = st["id_offset"]
+
+    def host_state(self):
+        return {"spaces": {}}
+
     def set_id_offset(self, off):
         self.id_offset = int(off)
 

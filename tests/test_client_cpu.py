@@ -122,3 +122,37 @@ def test_upsert_replaces_the_whole_point_and_batch_skips_points_without_the_dens
         assert [p.id for p in batch[0]] == [p.id for p in one.points]
         assert 5 in [p.id for p in batch[0]]            # still a sparse hit
     asyncio.run(flow())
+
+
+def test_client_flows_on_a_row_sharded_collection():
+    """B200QdrantClient(devices=[...]): the same reference flows, every collection row-sharded over three engines
+    (multi.py, blocks of 16 rows so the 200-point corpus really spreads) -- identical answers."""
+    from _client_cases import run_incremental_upsert, run_long_limits, run_reference_flow
+    from _oracle_engine import OracleEngine
+    kw = dict(engine_factory=OracleEngine, devices=[0, 1, 2], shard_block_rows=16)
+    run_reference_flow(**kw)
+    run_incremental_upsert(**kw)
+    run_long_limits(**kw)
+
+
+def test_multi_engine_row_mapping():
+    from _oracle_engine import OracleEngine
+    from rag_application_b200.multi import MultiEngine
+    import numpy as np
+    m = MultiEngine([0, 1, 2], OracleEngine, block_rows=8)
+    rows = np.arange(1000)
+    sh, loc = m._shard_of(rows), m._local_of(rows)
+    for g in range(3):
+        mine = rows[sh == g]
+        assert np.array_equal(m._global_of(g, loc[sh == g]), mine)
+        assert np.array_equal(loc[sh == g], np.arange(len(mine)))          # local rows are dense and keep the order
+        for n in (0, 5, 8, 23, 24, 25, 1000):
+            assert m._local_n(g, n) == int((mine < n).sum())
+    m.close()
+
+
+def test_save_load_on_oracle_engine(tmp_path):
+    from _client_cases import run_save_load
+    from _oracle_engine import OracleEngine
+    run_save_load(tmp_path / "one", engine_factory=OracleEngine)
+    run_save_load(tmp_path / "three", engine_factory=OracleEngine, devices=[0, 1, 2], shard_block_rows=16)

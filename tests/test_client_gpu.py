@@ -42,3 +42,9 @@ def test_dense_append_update_equal_a_fresh_upload(engine):
         want = engine.dense_topk("ref", q, 50)
         for a, b in zip(got, want):
             assert np.array_equal(a, b)
+
+
+def test_save_load_on_b200(tmp_path):
+    from _client_cases import run_save_load
+    run_save_load(tmp_path / "bf16", storage="bf16")
+    run_save_load(tmp_path / "f32")

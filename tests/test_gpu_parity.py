@@ -708,3 +708,44 @@ def test_logical_shards_on_one_gpu_match_unsharded(engine, G):
     for l in range(2):
         assert np.array_equal(ti[l], merged[l][1]) and np.array_equal(tc[l], merged[l][2])
         assert np.array_equal(ts[l].view(np.uint32), merged[l][0].view(np.uint32))
+
+
+def test_save_load_bit_equal(engine, tmp_path):
+    """brag_save -> a new engine -> brag_load answers bit for bit like the engine that saved (dense through
+    both scans, sparse through both kernels -- i.e. the saved scan indexes are the ones in use -- and the fused call)."""
+    from rag_application_b200 import Engine
+    n, d, k, B, V = 30_000, 128, 60, 40, 3000
+    x = synth.dense_corpus(n, d, seed=71, clustered=True)
+    q = synth.dense_queries(x, B, seed=72)
+    ptr, doc, w, _ = synth.zipf_corpus(n, V, 70, seed=73)
+    qp, qt, qv = synth.sparse_queries(ptr, doc, n, B, 8, "zipf", seed=74, skip_top=8)
+    a = Engine(0)
+    b = Engine(0)
+    try:
+        a.set_id_offset(1000)
+        a.dense_set("d16", x, "bf16")
+        a.dense_set("d32", x[:5000], "f32")
+        a.sparse_set_csr("s", ptr, doc, w, n)
+        path = str(tmp_path / "index.brag")
+        a.save(path)
+        b.load(path, a.host_state())
+
+        def answers(e):
+            out = [e.dense_topk("d16", q, k), e.dense_topk("d32", q[:4], k), e.hybrid_topk("d16", "s", q, qp, qt, qv, k)]
+            for p in ("scatter", "bitmap"):
+                e.force_sparse_path(p)
+                out.append(e.sparse_topk("s", qp, qt, qv, k))
+            e.force_sparse_path(None)
+            return out
+        for ra, rb in zip(answers(a), answers(b)):
+            for ta, tb in zip(ra, rb):
+                assert np.array_equal(np.asarray(ta).view(np.uint8), np.asarray(tb).view(np.uint8))
+        assert int(b.dense_topk("d16", q[:1], 1)[1][0, 0]) >= 1000            # the id offset came back too
+        # the loaded spaces take appends like uploaded ones
+        b.dense_append("d16", x[:16])
+        assert b.dense_topk("d16", q[:2], k)[2].tolist() == [k, k]
+        with pytest.raises(Exception):
+            b.load(str(tmp_path / "missing.brag"))
+    finally:
+        a.close()
+        b.close()
