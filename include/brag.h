@@ -209,6 +209,12 @@ int brag_force_sparse_path(brag_engine* e, int32_t path);
  * filter from then on (results identical).  Only calls with B >= 32 count towards `queries` (single queries are
  * latency-bound either way).  Default 256; 0 = build on first use; < 0 = never (an index already built is bypassed). */
 int brag_sparse_compact_after(brag_engine* e, int64_t queries);
+/* Per-(term, 2048-document sub-tile) posting offsets are kept only for terms with at least min_df postings; the short
+ * lists of the other terms are searched by the scans (results identical).  0 = automatic: a row only where the term's
+ * postings outweigh it (df >= (n_docs / 2048 + 2) / 2), so the table never exceeds the postings whatever the
+ * vocabulary.  Applies to sparse spaces uploaded afterwards; the parity tests force the searched form with a large
+ * value. */
+int brag_sparse_offsets_min_df(brag_engine* e, int64_t min_df);
 /* Which filter the space's compacted index was built for (0 = none built) and how many documents it holds. */
 int brag_sparse_compact_info(brag_engine* e, const char* name, int32_t* mask_id, int64_t* n_docs);
 

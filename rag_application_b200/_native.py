@@ -51,6 +51,7 @@ PROTOTYPES = {
     "brag_force_dense_path": (C.c_int, [c_p, i32]),
     "brag_force_sparse_path": (C.c_int, [c_p, i32]),
     "brag_sparse_compact_after": (C.c_int, [c_p, i64]),
+    "brag_sparse_offsets_min_df": (C.c_int, [c_p, i64]),
     "brag_sparse_compact_info": (C.c_int, [c_p, C.c_char_p, c_p, c_p]),
     "brag_rerank_meanpool": (C.c_int, [c_p, c_p, i32, c_p, i32, i32, i32, c_p, c_p, i32, c_p]),
     "brag_sparse_append": (C.c_int, [c_p, C.c_char_p, c_p, c_p, c_p, c_p, i64, i64]),

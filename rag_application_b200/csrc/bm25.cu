@@ -59,11 +59,12 @@ cudaError_t bm25_interleave(const uint32_t* doc, const float* w, int64_t nnz, ui
 }
 
 __global__ void bm25_suboff_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict__ post,
-                                   int64_t V, int ns1, uint32_t* __restrict__ sub_off) {
+                                   const int32_t* __restrict__ row_terms, int64_t n_rows, int ns1,
+                                   uint32_t* __restrict__ sub_off) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= V * ns1) return;
-    const int64_t t = i / ns1;
-    const int j = (int)(i - t * ns1);
+    if (i >= n_rows * ns1) return;
+    const int64_t t = row_terms[i / ns1];
+    const int j = (int)(i % ns1);
     const int64_t lo0 = term_ptr[t], hi0 = term_ptr[t + 1];
     const uint64_t target = (uint64_t)j * BM25_SUB;
     int64_t lo = lo0, hi = hi0;
@@ -74,19 +75,19 @@ __global__ void bm25_suboff_kernel(const int64_t* __restrict__ term_ptr, const u
     sub_off[i] = (uint32_t)(lo - lo0);
 }
 
-cudaError_t bm25_build_suboffsets(const int64_t* term_ptr, const uint2* post, int64_t V, int64_t n_docs,
-                                  uint32_t* sub_off, cudaStream_t st) {
+cudaError_t bm25_build_suboffsets(const int64_t* term_ptr, const uint2* post, const int32_t* row_terms, int64_t n_rows,
+                                  int64_t n_docs, uint32_t* sub_off, cudaStream_t st) {
     const int ns1 = (int)((n_docs + BM25_SUB - 1) / BM25_SUB) + 1;
-    const int64_t total = V * ns1;
+    const int64_t total = n_rows * ns1;
     if (total == 0) return cudaSuccess;
     const int64_t blocks = (total + 255) / 256;
-    bm25_suboff_kernel<<<(unsigned)blocks, 256, 0, st>>>(term_ptr, post, V, ns1, sub_off);
+    bm25_suboff_kernel<<<(unsigned)blocks, 256, 0, st>>>(term_ptr, post, row_terms, n_rows, ns1, sub_off);
     return cudaGetLastError();
 }
 
 __global__ void __launch_bounds__(BM_THREADS, 1)
 bm25_scan_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict__ post,
-                 const uint32_t* __restrict__ sub_off, int64_t V,
+                 const uint32_t* __restrict__ sub_off, const int32_t* __restrict__ sub_row, int64_t V,
                  int64_t n_docs, const int32_t* __restrict__ q_ptr, const int32_t* __restrict__ q_terms,
                  const double* __restrict__ q_vals, int B, const uint32_t* __restrict__ mask, int k_sel,
                  int lcap, int nw, uint64_t* __restrict__ part, int splits, int* __restrict__ work_counter,
@@ -145,18 +146,31 @@ bm25_scan_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict__
 
         // first term group of the query: term row, query value and posting base are the same for every
         // sub-tile, and the (lo, hi) offsets of the NEXT sub-tile are fetched while this one is processed
-        int t0 = -1;
+        int t0 = -1, srow0 = -1;
         double qv0 = 0.0;
         int64_t tp0 = 0;
+        uint32_t df0 = 0, cur0 = 0;       // row-less term: list length, where the last search ended
         if (lane < min(BM_TG, qe - qb)) {
             const int t = q_terms[qb + lane];
-            if (t >= 0 && t < V) { t0 = t; qv0 = q_vals[qb + lane]; tp0 = __ldg(term_ptr + t); }
+            if (t >= 0 && t < V) {
+                t0 = t; qv0 = q_vals[qb + lane]; tp0 = __ldg(term_ptr + t);
+                srow0 = __ldg(sub_row + t);
+                df0 = (uint32_t)(__ldg(term_ptr + t + 1) - tp0);
+            }
         }
+        // posting range of this lane's term inside sub-tile s: table row, or a forward search of the short list
+        auto range_of = [&](int s, uint32_t& lo, uint32_t& hi) {
+            if (srow0 >= 0) {
+                lo = __ldg(sub_off + (size_t)srow0 * ns1 + s);
+                hi = __ldg(sub_off + (size_t)srow0 * ns1 + s + 1);
+            } else {
+                lo = list_lower_bound(post + tp0, cur0, df0, (uint32_t)s * BM25_SUB);
+                hi = list_lower_bound(post + tp0, lo, df0, (uint32_t)(s + 1) * BM25_SUB);
+                cur0 = hi;
+            }
+        };
         uint32_t lo_nx = 0, hi_nx = 0;
-        if (t0 >= 0 && j_begin + warp < j_end) {
-            lo_nx = __ldg(sub_off + (size_t)t0 * ns1 + (j_begin + warp));
-            hi_nx = __ldg(sub_off + (size_t)t0 * ns1 + (j_begin + warp) + 1);
-        }
+        if (t0 >= 0 && j_begin + warp < j_end) range_of(j_begin + warp, lo_nx, hi_nx);
         for (int j = j_begin + warp; j < j_end; j += nw) {
             const uint32_t sub_base = (uint32_t)j * BM25_SUB;
             // the query's global bound: k_sel-th best score over everything any warp has pushed so far
@@ -164,10 +178,7 @@ bm25_scan_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict__
             const double pre = (g != 0u) ? fmax(pre_local, prefilter_of_score(ordered_f32(g))) : pre_local;
             bool any = false;
             const uint32_t lo_cur = lo_nx, hi_cur = hi_nx;
-            if (t0 >= 0 && j + nw < j_end) {
-                lo_nx = __ldg(sub_off + (size_t)t0 * ns1 + (j + nw));
-                hi_nx = __ldg(sub_off + (size_t)t0 * ns1 + (j + nw) + 1);
-            }
+            if (t0 >= 0 && j + nw < j_end) range_of(j + nw, lo_nx, hi_nx);
             for (int tg = qb; tg < qe; tg += BM_TG) {
                 const int nq = min(BM_TG, qe - tg);
                 // ---- segment setup: lane l < nq owns term tg + l
@@ -179,10 +190,19 @@ bm25_scan_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict__
                 } else if (lane < nq) {
                     const int t = q_terms[tg + lane];
                     if (t >= 0 && t < V) {
-                        const uint32_t lo = __ldg(sub_off + (size_t)t * ns1 + j);
-                        const uint32_t hi = __ldg(sub_off + (size_t)t * ns1 + j + 1);
+                        const int srow = __ldg(sub_row + t);
+                        const int64_t tp = __ldg(term_ptr + t);
+                        uint32_t lo, hi;
+                        if (srow >= 0) {
+                            lo = __ldg(sub_off + (size_t)srow * ns1 + j);
+                            hi = __ldg(sub_off + (size_t)srow * ns1 + j + 1);
+                        } else {
+                            const uint32_t df = (uint32_t)(__ldg(term_ptr + t + 1) - tp);
+                            lo = list_lower_bound(post + tp, 0u, df, sub_base);
+                            hi = list_lower_bound(post + tp, lo, df, sub_base + BM25_SUB);
+                        }
                         n = hi - lo;
-                        base = __ldg(term_ptr + t) + lo;
+                        base = tp + lo;
                         qv = q_vals[tg + lane];
                     }
                 }
@@ -373,7 +393,7 @@ cudaError_t bm25_init_device() {
                                 cudaSharedmemCarveoutMaxShared);
 }
 
-cudaError_t bm25_scan(const int64_t* term_ptr, const uint2* post, const uint32_t* sub_off,
+cudaError_t bm25_scan(const int64_t* term_ptr, const uint2* post, const uint32_t* sub_off, const int32_t* sub_row,
                       int64_t V, int64_t n_docs, const int32_t* q_ptr, const int32_t* q_terms,
                       const double* q_vals, int B, const uint32_t* mask, int k_sel, uint64_t* part,
                       const Bm25Plan& plan, void* scratch, cudaStream_t st, const ShardBounds& xb) {
@@ -388,7 +408,7 @@ cudaError_t bm25_scan(const int64_t* term_ptr, const uint2* post, const uint32_t
     uint32_t* fine = reinterpret_cast<uint32_t*>(sp + 256 + plan.gthr_bytes + plan.coarse_bytes);
     cudaError_t e = cudaMemsetAsync(scratch, 0, plan.scratch_bytes, st);
     if (e != cudaSuccess) return e;
-    bm25_scan_kernel<<<plan.grid, (plan.workers + 1) * 32, smem, st>>>(term_ptr, post, sub_off, V, n_docs, q_ptr, q_terms,
+    bm25_scan_kernel<<<plan.grid, (plan.workers + 1) * 32, smem, st>>>(term_ptr, post, sub_off, sub_row, V, n_docs, q_ptr, q_terms,
                                                           q_vals, B, mask, k_sel, lcap, plan.workers, part, plan.splits,
                                                           work_counter, gthr, coarse, fine, xb);
     return cudaGetLastError();

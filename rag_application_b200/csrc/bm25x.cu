@@ -297,7 +297,8 @@ __device__ __forceinline__ void sts_zero_words(uint32_t* p) {
 template <int MAXT, int SUBS>
 __global__ void __launch_bounds__(bx_max_threads(MAXT, SUBS), 1)
 bm25x_scan_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict__ post,
-                  const uint32_t* __restrict__ sub_off, const int32_t* __restrict__ bm_row,
+                  const uint32_t* __restrict__ sub_off, const int32_t* __restrict__ sub_row,
+                  const int32_t* __restrict__ bm_row,
                   const uint32_t* __restrict__ bits, const uint32_t* __restrict__ bits_hi,
                   const float2* __restrict__ wrange, const float* __restrict__ tau, int64_t V, int64_t n_docs,
                   const int32_t* __restrict__ q_ptr, const int32_t* __restrict__ q_terms,
@@ -394,10 +395,11 @@ bm25x_scan_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict_
         if (lane == 0) *cntp = 0;
 
         // ---- per-query term setup: lane l < nq owns term l
-        int t0 = -1, row0 = -1;
+        int t0 = -1, row0 = -1, srow0 = -1;
         double qv0 = 0.0, ua = 0.0, ue = 0.0;     // bound of a low-class posting; extra of a high-class one
         float tau0 = 0.f;
         int64_t tp0 = 0;
+        uint32_t df0 = 0, cur0 = 0;               // term without an offset row: list length, end of the last search
         if (lane < nq) {
             const int t = q_terms[qb + lane];
             if (t >= 0 && t < V) {
@@ -405,6 +407,8 @@ bm25x_scan_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict_
                 qv0 = q_vals[qb + lane];
                 tp0 = __ldg(term_ptr + t);
                 row0 = __ldg(bm_row + t);
+                srow0 = __ldg(sub_row + t);
+                df0 = (uint32_t)(__ldg(term_ptr + t + 1) - tp0);
                 tau0 = __ldg(tau + t);
                 const float2 wr = __ldg(wrange + t);
                 // low class: w in [min, tau]; high class: w in (tau, max]
@@ -433,15 +437,23 @@ bm25x_scan_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict_
         sa *= 1.0 + 1e-12;
         se *= 1.0 + 1e-12;
         const unsigned sparse_terms = __ballot_sync(0xFFFFFFFFu, t0 >= 0 && row0 < 0);
-        const uint32_t* so = sub_off + (size_t)max(t0, 0) * ns1;     // this lane's row of the offset table
+        const uint32_t* so = sub_off + (size_t)max(srow0, 0) * ns1;     // this lane's row of the offset table
+        // posting range of this lane's term inside sub-tiles [s_lo, s_hi): table row, or (rare terms, bm25_common.cuh)
+        // a forward search of the short list
+        auto range_of = [&](int s_lo, int s_hi, uint32_t& lo, uint32_t& hi) {
+            if (srow0 >= 0) {
+                lo = __ldg(so + s_lo);
+                hi = __ldg(so + s_hi);
+            } else {
+                lo = list_lower_bound(post + tp0, cur0, df0, (uint32_t)s_lo * BM25_SUB);
+                hi = list_lower_bound(post + tp0, lo, df0, (uint32_t)min((int64_t)s_hi * BM25_SUB, (int64_t)0xFFFFFFFFll));
+                cur0 = hi;
+            }
+        };
         __syncwarp();
 
         uint32_t lo_nx = 0, hi_nx = 0;
-        if (t0 >= 0 && j_first < j_end) {
-            const int s_lo = j_first * SUBS;
-            lo_nx = __ldg(so + s_lo);
-            hi_nx = __ldg(so + min(ns, s_lo + SUBS));
-        }
+        if (t0 >= 0 && j_first < j_end) range_of(j_first * SUBS, min(ns, j_first * SUBS + SUBS), lo_nx, hi_nx);
         uint32_t g_seen = 0u;
         double pre_g = -INFINITY;
         // one scored-but-not-yet-summed candidate per lane, carried from a scoring round to the next one
@@ -474,11 +486,8 @@ bm25x_scan_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict_
             if (g != g_seen) { g_seen = g; pre_g = prefilter_of_score(ordered_f32(g)); }
             double pre_eff = fmax(pre_local, pre_g);
             const uint32_t lo_cur = lo_nx, hi_cur = hi_nx;
-            if (t0 >= 0 && j + j_stride < j_end) {
-                const int s_lo = (j + j_stride) * SUBS;
-                lo_nx = __ldg(so + s_lo);
-                hi_nx = __ldg(so + min(ns, s_lo + SUBS));
-            }
+            if (t0 >= 0 && j + j_stride < j_end)
+                range_of((j + j_stride) * SUBS, min(ns, (j + j_stride) * SUBS + SUBS), lo_nx, hi_nx);
             const uint32_t n = (t0 >= 0) ? hi_cur - lo_cur : 0u;
             const unsigned active = __ballot_sync(0xFFFFFFFFu, n != 0u);
             // a document needs (terms present) + (terms in their high class) >= m to beat the bound
@@ -780,7 +789,7 @@ Bm25Plan bm25x_plan(int64_t n_docs, int B, int k_sel, int max_terms, int num_sms
 }
 
 struct BxArgs {
-    const int64_t* term_ptr; const uint2* post; const uint32_t* sub_off; const int32_t* bm_row; const uint32_t* bits;
+    const int64_t* term_ptr; const uint2* post; const uint32_t* sub_off; const int32_t* sub_row; const int32_t* bm_row; const uint32_t* bits;
     const uint32_t* bits_hi; const float2* wrange; const float* tau; int64_t V, n_docs; const int32_t *q_ptr, *q_terms; const double* q_vals; int B;
     const uint32_t* mask; int k_sel; uint64_t* part; const Bm25Plan* plan; void* scratch; cudaStream_t st;
     ShardBounds xb;
@@ -802,13 +811,13 @@ static cudaError_t bx_launch(const BxArgs& a) {
     if (plan.seed_tiles > 0) {
         const int seed_items = (a.B + plan.seed_qpi - 1) / plan.seed_qpi;
         bm25x_scan_kernel<MAXT, SUBS><<<std::min(seed_items, plan.grid), (plan.workers + 1) * 32, smem, a.st>>>(
-            a.term_ptr, a.post, a.sub_off, a.bm_row, a.bits, a.bits_hi, a.wrange, a.tau, a.V, a.n_docs, a.q_ptr, a.q_terms,
+            a.term_ptr, a.post, a.sub_off, a.sub_row, a.bm_row, a.bits, a.bits_hi, a.wrange, a.tau, a.V, a.n_docs, a.q_ptr, a.q_terms,
             a.q_vals, a.B, a.mask, a.k_sel, lcap, plan.workers, a.part, plan.splits, plan.seed_tiles, plan.seed_qpi, 1, bx_mgr_sleep(),
             work_counter + 1, gthr, coarse, fine, ShardBounds());
         if ((e = cudaGetLastError()) != cudaSuccess) return e;
     }
     bm25x_scan_kernel<MAXT, SUBS><<<plan.grid, (plan.workers + 1) * 32, smem, a.st>>>(
-        a.term_ptr, a.post, a.sub_off, a.bm_row, a.bits, a.bits_hi, a.wrange, a.tau, a.V, a.n_docs, a.q_ptr, a.q_terms,
+        a.term_ptr, a.post, a.sub_off, a.sub_row, a.bm_row, a.bits, a.bits_hi, a.wrange, a.tau, a.V, a.n_docs, a.q_ptr, a.q_terms,
         a.q_vals, a.B, a.mask, a.k_sel, lcap, plan.workers, a.part, plan.splits, plan.seed_tiles, plan.seed_qpi, 0, bx_mgr_sleep(),
         work_counter, gthr, coarse, fine, a.xb);
     return cudaGetLastError();
@@ -841,14 +850,15 @@ cudaError_t bm25x_init_device() {
     return e;
 }
 
-cudaError_t bm25x_scan(const int64_t* term_ptr, const uint2* post, const uint32_t* sub_off, const int32_t* bm_row,
+cudaError_t bm25x_scan(const int64_t* term_ptr, const uint2* post, const uint32_t* sub_off, const int32_t* sub_row,
+                       const int32_t* bm_row,
                        const uint32_t* bits, const uint32_t* bits_hi, const float2* wrange, const float* tau, int64_t V,
                        int64_t n_docs, const int32_t* q_ptr,
                        const int32_t* q_terms, const double* q_vals, int B, int max_terms, const uint32_t* mask,
                        int k_sel, uint64_t* part, const Bm25Plan& plan, void* scratch, cudaStream_t st,
                        const ShardBounds& xb) {
     if (!bm25x_supported(max_terms, k_sel)) return cudaErrorInvalidValue;
-    const BxArgs a{term_ptr, post, sub_off, bm_row, bits, bits_hi, wrange, tau, V, n_docs, q_ptr, q_terms, q_vals, B,
+    const BxArgs a{term_ptr, post, sub_off, sub_row, bm_row, bits, bits_hi, wrange, tau, V, n_docs, q_ptr, q_terms, q_vals, B,
                    mask, k_sel, part, &plan, scratch, st, xb};
     switch (bx_maxt(max_terms)) {
         case 8: return bx_launch_subs<8>(a);

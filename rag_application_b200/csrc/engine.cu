@@ -86,7 +86,9 @@ struct DenseSpace {
 struct SparseSpace {
     int64_t* term_ptr = nullptr;
     uint2* post = nullptr;      // interleaved (doc id, weight bits)
-    uint32_t* sub_off = nullptr;
+    uint32_t* sub_off = nullptr;   // [n_sub][n_docs / 2048 + 2] offsets of the terms that have a row (bm25_common.cuh)
+    int32_t* sub_row = nullptr;    // [V] row of a term in sub_off, or -1 (rare term: its short list is searched)
+    int64_t n_sub = 0;
     // bitmap-filter scan (bm25x.cu): per-term weight range, document maps of the dense terms
     float2* wrange = nullptr;
     float* tau = nullptr;
@@ -147,6 +149,7 @@ struct brag_engine {
     int64_t id_offset = 0;
     int force_path = -1;
     bool no_compact = false;       // parity tests: scan the full space under a filter
+    int64_t suboff_min_df = 0;            // 0 = automatic; tests force rare-term searches with a large value
     int64_t sparse_compact_after = 256;   // queries under one filter before its sparse copy is built; < 0 never
     uint64_t mask_epoch = 0;
     int force_sparse_path = -1;    // -1 auto, 0 scatter-accumulate (bm25.cu), 1 bitmap filter (bm25x.cu)
@@ -233,6 +236,7 @@ void free_sparse(SparseSpace& s) {
     if (s.term_ptr) cudaFree(s.term_ptr);
     if (s.post) cudaFree(s.post);
     if (s.sub_off) cudaFree(s.sub_off);
+    if (s.sub_row) cudaFree(s.sub_row);
     if (s.wrange) cudaFree(s.wrange);
     if (s.tau) cudaFree(s.tau);
     if (s.bits_hi) cudaFree(s.bits_hi);
@@ -286,10 +290,27 @@ void build_bitmap_index(SparseSpace& s) {
 }
 
 // everything the scans need beside term_ptr / post (both already on the device)
-void build_sparse_index(SparseSpace& s) {
+void build_sparse_index(SparseSpace& s, int64_t suboff_min_df) {
     const int64_t ns1 = (s.n_docs + brag::BM25_SUB - 1) / brag::BM25_SUB + 1;
-    CK(cudaMalloc(&s.sub_off, (size_t)s.V * ns1 * sizeof(uint32_t)));
-    CK(brag::bm25_build_suboffsets(s.term_ptr, s.post, s.V, s.n_docs, s.sub_off, 0));
+    // an offset row (4 * ns1 bytes) only for terms whose postings (8 * df bytes) outweigh it: the table then never
+    // exceeds the postings, whatever the vocabulary (a hashed-stem vocabulary is millions of rare terms)
+    const int64_t min_df = suboff_min_df > 0 ? suboff_min_df : std::max<int64_t>(1, (ns1 + 1) / 2);
+    std::vector<int32_t> rows((size_t)s.V, -1), terms;
+    for (int64_t t = 0; t < s.V; ++t)
+        if (s.term_ptr_host[t + 1] - s.term_ptr_host[t] >= min_df) { rows[(size_t)t] = (int32_t)terms.size(); terms.push_back((int32_t)t); }
+    s.n_sub = (int64_t)terms.size();
+    CK(cudaMalloc(&s.sub_row, (size_t)s.V * sizeof(int32_t)));
+    CK(cudaMemcpy(s.sub_row, rows.data(), (size_t)s.V * sizeof(int32_t), cudaMemcpyHostToDevice));
+    CK(cudaMalloc(&s.sub_off, std::max<size_t>(256, (size_t)s.n_sub * ns1 * sizeof(uint32_t))));
+    if (s.n_sub) {
+        int32_t* dterms = nullptr;
+        CK(cudaMalloc(&dterms, terms.size() * sizeof(int32_t)));
+        cudaError_t ce = cudaMemcpy(dterms, terms.data(), terms.size() * sizeof(int32_t), cudaMemcpyHostToDevice);
+        if (ce == cudaSuccess) ce = brag::bm25_build_suboffsets(s.term_ptr, s.post, dterms, s.n_sub, s.n_docs, s.sub_off, 0);
+        if (ce == cudaSuccess) ce = cudaDeviceSynchronize();
+        cudaFree(dterms);
+        CK(ce);
+    }
     build_bitmap_index(s);
     CK(cudaDeviceSynchronize());
 }
@@ -398,7 +419,7 @@ bool ensure_sparse_compact(brag_engine* e, SparseSpace& s, int mask_id, const ui
         CK(cudaMalloc(&s.cp_rowmap, (size_t)nc * sizeof(uint32_t)));
         CK(brag::compact_rowmap(mask, s.n_docs, prefix, s.cp_rowmap, st));
         CK(cudaStreamSynchronize(st));
-        build_sparse_index(*c);
+        build_sparse_index(*c, e->suboff_min_df);
         e->kernel_launches += 8;
     } catch (const CudaOom&) {
         free_sparse(*c);
@@ -555,10 +576,10 @@ void sparse_topk_dev(brag_engine* e, SparseSpace& full, const int32_t* q_ptr, co
     {
         StageTimer t(e, 2, st);
         if (bitmap)
-            CK(brag::bm25x_scan(s.term_ptr, s.post, s.sub_off, s.bm_row, s.bits, s.bits_hi, s.wrange, s.tau, s.V, s.n_docs, q_ptr, q_terms,
+            CK(brag::bm25x_scan(s.term_ptr, s.post, s.sub_off, s.sub_row, s.bm_row, s.bits, s.bits_hi, s.wrange, s.tau, s.V, s.n_docs, q_ptr, q_terms,
                                 q_vals, B, max_terms, mask, k, part, plan, scratch, st, xb));
         else
-            CK(brag::bm25_scan(s.term_ptr, s.post, s.sub_off, s.V, s.n_docs, q_ptr, q_terms, q_vals, B, mask, k,
+            CK(brag::bm25_scan(s.term_ptr, s.post, s.sub_off, s.sub_row, s.V, s.n_docs, q_ptr, q_terms, q_vals, B, mask, k,
                                part, plan, scratch, st, xb));
         e->kernel_launches += 1 + ((bitmap && plan.seed_tiles > 0) ? 1 : 0);
     }
@@ -834,7 +855,7 @@ int brag_sparse_set_csr(brag_engine* e, const char* name, const int64_t* term_pt
                     CK(ce);
                 }
             }
-            build_sparse_index(s);
+            build_sparse_index(s, e->suboff_min_df);
         } catch (...) {
             free_sparse(s);
             throw;
@@ -908,7 +929,7 @@ int brag_sparse_append(brag_engine* e, const char* name, const int64_t* delta_te
             free_sparse(s);
             old_freed = true;
             g.term_ptr_host = std::move(new_ptr);
-            build_sparse_index(g);
+            build_sparse_index(g, e->suboff_min_df);
         } catch (...) {
             if (d_dst_start) cudaFree(d_dst_start);
             if (d_ddst) cudaFree(d_ddst);
@@ -1473,6 +1494,13 @@ int brag_sparse_compact_after(brag_engine* e, int64_t queries) {
     });
 }
 
+int brag_sparse_offsets_min_df(brag_engine* e, int64_t min_df) {
+    return guarded([&] {
+        REQUIRE(e && min_df >= 0, "brag_sparse_offsets_min_df: bad arguments");
+        e->suboff_min_df = min_df;
+    });
+}
+
 int brag_sparse_compact_info(brag_engine* e, const char* name, int32_t* mask_id, int64_t* n_docs) {
     return guarded([&] {
         REQUIRE(e && name && mask_id && n_docs, "brag_sparse_compact_info: NULL argument");
@@ -1505,8 +1533,8 @@ constexpr char PERSIST_MAGIC[8] = {'B', 'R', 'A', 'G', 'I', 'D', 'X', '2'};
 struct PersistSection {
     char name[96];
     int32_t kind;             // 0 dense rows, 1 sparse array
-    int32_t which;            // sparse: 0 term_ptr 1 post 2 sub_off 3 wrange 4 tau 5 bm_row 6 bits 7 bits_hi
-    int64_t a, b, c, d;       // dense: n, d, dtype, 0      sparse (on `which` 0): V, n_docs, nnz, n_dense | bitmap_ok << 32
+    int32_t which;            // sparse: 0 term_ptr 1 post 2 sub_off 3 wrange 4 tau 5 bm_row 6 bits 7 bits_hi 8 sub_row
+    int64_t a, b, c, d;       // dense: n, d, dtype, 0      sparse: V, n_docs, nnz, n_dense | bitmap_ok << 31 | n_sub << 32
     uint64_t offset, bytes;
 };
 
@@ -1550,9 +1578,10 @@ void pad_to(FILE* f, uint64_t target) {
     }
 }
 
+constexpr int N_SPARSE_ARRAYS = 9;
 struct SparseArrays {
-    const void* ptr[8];
-    size_t bytes[8];
+    const void* ptr[N_SPARSE_ARRAYS];
+    size_t bytes[N_SPARSE_ARRAYS];
 };
 
 SparseArrays sparse_arrays(const SparseSpace& s) {
@@ -1561,12 +1590,13 @@ SparseArrays sparse_arrays(const SparseSpace& s) {
     SparseArrays a;
     a.ptr[0] = s.term_ptr; a.bytes[0] = (size_t)(s.V + 1) * sizeof(int64_t);
     a.ptr[1] = s.post;     a.bytes[1] = (size_t)s.nnz * sizeof(uint2);
-    a.ptr[2] = s.sub_off;  a.bytes[2] = (size_t)s.V * ns1 * sizeof(uint32_t);
+    a.ptr[2] = s.sub_off;  a.bytes[2] = (size_t)s.n_sub * ns1 * sizeof(uint32_t);
     a.ptr[3] = s.wrange;   a.bytes[3] = (size_t)s.V * sizeof(float2);
     a.ptr[4] = s.tau;      a.bytes[4] = (size_t)s.V * sizeof(float);
     a.ptr[5] = s.bm_row;   a.bytes[5] = (size_t)s.V * sizeof(int32_t);
     a.ptr[6] = s.bits;     a.bytes[6] = (size_t)s.n_dense * row_bytes;
     a.ptr[7] = s.bits_hi;  a.bytes[7] = (size_t)s.n_dense * row_bytes;
+    a.ptr[8] = s.sub_row;  a.bytes[8] = (size_t)s.V * sizeof(int32_t);
     return a;
 }
 
@@ -1597,9 +1627,9 @@ int brag_save(brag_engine* e, const char* path) {
         for (auto& kv : e->sparse) {
             const SparseSpace& s = kv.second;
             const SparseArrays arr = sparse_arrays(s);
-            for (int w = 0; w < 8; ++w)
-                add(kv.first, 1, w, s.V, s.n_docs, s.nnz, (int64_t)s.n_dense | ((int64_t)(s.bitmap_ok ? 1 : 0) << 32),
-                    arr.ptr[w], arr.bytes[w]);
+            for (int w = 0; w < N_SPARSE_ARRAYS; ++w)
+                add(kv.first, 1, w, s.V, s.n_docs, s.nnz,
+                    (int64_t)s.n_dense | ((int64_t)(s.bitmap_ok ? 1 : 0) << 31) | (s.n_sub << 32), arr.ptr[w], arr.bytes[w]);
         }
         PersistHeader h;
         std::memcpy(h.magic, PERSIST_MAGIC, 8);
@@ -1678,9 +1708,10 @@ int brag_load(brag_engine* e, const char* path) {
                 } else if (s.kind == 1) {
                     SparseSpace& sp = loading[name];
                     sp.V = s.a; sp.n_docs = s.b; sp.nnz = s.c;
-                    sp.n_dense = (int)(s.d & 0xFFFFFFFFll);
-                    sp.bitmap_ok = ((s.d >> 32) & 1) != 0;
-                    REQUIRE(s.which >= 0 && s.which < 8 && sp.V >= 1 && sp.n_docs >= 1, "brag_load: corrupt sparse section");
+                    sp.n_dense = (int)(s.d & 0x7FFFFFFFll);
+                    sp.bitmap_ok = ((s.d >> 31) & 1) != 0;
+                    sp.n_sub = s.d >> 32;
+                    REQUIRE(s.which >= 0 && s.which < N_SPARSE_ARRAYS && sp.V >= 1 && sp.n_docs >= 1, "brag_load: corrupt sparse section");
                     REQUIRE(sparse_arrays(sp).bytes[s.which] == s.bytes, "brag_load: sparse section has the wrong size");
                     void* p = nullptr;
                     CK(cudaMalloc(&p, std::max<size_t>(s.bytes, 256)));
@@ -1692,7 +1723,8 @@ int brag_load(brag_engine* e, const char* path) {
                         case 4: sp.tau = static_cast<float*>(p); break;
                         case 5: sp.bm_row = static_cast<int32_t*>(p); break;
                         case 6: sp.bits = static_cast<uint32_t*>(p); break;
-                        default: sp.bits_hi = static_cast<uint32_t*>(p); break;
+                        case 7: sp.bits_hi = static_cast<uint32_t*>(p); break;
+                        default: sp.sub_row = static_cast<int32_t*>(p); break;
                     }
                     if (s.bytes) read_device_array(f, p, s.bytes, stage, stage_bytes);
                     if (s.which == 0) {
@@ -1706,7 +1738,7 @@ int brag_load(brag_engine* e, const char* path) {
             }
             for (auto& kv : loading) {
                 SparseSpace& sp = kv.second;
-                REQUIRE(sp.term_ptr && sp.post && sp.sub_off && sp.wrange && sp.tau && sp.bm_row && sp.bits && sp.bits_hi,
+                REQUIRE(sp.term_ptr && sp.post && sp.sub_off && sp.sub_row && sp.wrange && sp.tau && sp.bm_row && sp.bits && sp.bits_hi,
                         "brag_load: a sparse space is missing sections");
             }
         } catch (...) {

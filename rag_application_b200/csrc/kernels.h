@@ -133,8 +133,10 @@ cudaError_t sparse_compact_select(const uint2* post, int64_t nnz, const uint32_t
 constexpr int BM25_SUB = 2048;  // documents per warp sub-tile
 // postings are stored interleaved: post[i] = (doc id, float32 weight bits)
 cudaError_t bm25_interleave(const uint32_t* doc, const float* w, int64_t nnz, uint2* post, cudaStream_t st);
-cudaError_t bm25_build_suboffsets(const int64_t* term_ptr, const uint2* post, int64_t V, int64_t n_docs,
-                                  uint32_t* sub_off, cudaStream_t st);
+// sub_off: [n_rows][n_docs / 2048 + 2] first posting of every 2048-document sub-tile, for the terms row_terms[0..n_rows)
+// (the terms whose postings outweigh such a row; the others are searched, bm25_common.cuh)
+cudaError_t bm25_build_suboffsets(const int64_t* term_ptr, const uint2* post, const int32_t* row_terms, int64_t n_rows,
+                                  int64_t n_docs, uint32_t* sub_off, cudaStream_t st);
 struct Bm25Plan {
     int splits; int lists_per_query; int grid; int workers;
     int visits_per_list;    // tiles a worker warp visits per work item (bm25x: the first one runs without a bound)
@@ -144,7 +146,7 @@ struct Bm25Plan {
 };
 Bm25Plan bm25_plan(int64_t n_docs, int B, int k_sel, int num_sms);
 // part: [lists_per_query][B][k_sel]; scratch: plan.scratch_bytes (work counter | bounds | histograms)
-cudaError_t bm25_scan(const int64_t* term_ptr, const uint2* post, const uint32_t* sub_off,
+cudaError_t bm25_scan(const int64_t* term_ptr, const uint2* post, const uint32_t* sub_off, const int32_t* sub_row,
                       int64_t V, int64_t n_docs, const int32_t* q_ptr, const int32_t* q_terms,
                       const double* q_vals, int B, const uint32_t* mask, int k_sel, uint64_t* part,
                       const Bm25Plan& plan, void* scratch, cudaStream_t st, const ShardBounds& xb);
@@ -163,7 +165,8 @@ int64_t bm25x_row_words(int64_t n_docs);     // words per stored map row (sub-ti
 bool bm25x_supported(int max_terms, int k_sel);
 Bm25Plan bm25x_plan(int64_t n_docs, int B, int k_sel, int max_terms, int num_sms);
 // bm_row[t] = bitmap row of term t or -1; max_terms = longest query of the batch (<= 32)
-cudaError_t bm25x_scan(const int64_t* term_ptr, const uint2* post, const uint32_t* sub_off, const int32_t* bm_row,
+cudaError_t bm25x_scan(const int64_t* term_ptr, const uint2* post, const uint32_t* sub_off, const int32_t* sub_row,
+                       const int32_t* bm_row,
                        const uint32_t* bits, const uint32_t* bits_hi, const float2* wrange, const float* tau, int64_t V,
                        int64_t n_docs, const int32_t* q_ptr, const int32_t* q_terms, const double* q_vals, int B,
                        int max_terms, const uint32_t* mask, int k_sel, uint64_t* part, const Bm25Plan& plan,

@@ -388,6 +388,10 @@ class Engine:
         """Queries one filter serves before the index of its passing documents is built (0: first use, < 0: never)."""
         _native.check(self._lib.brag_sparse_compact_after(self._h, int(queries)))
 
+    def sparse_offsets_min_df(self, min_df: int):
+        """Terms with fewer postings get no per-sub-tile offset row (their lists are searched); 0 = automatic."""
+        _native.check(self._lib.brag_sparse_offsets_min_df(self._h, int(min_df)))
+
     def sparse_compact_info(self, name: str):
         """(mask_id the compacted index of this space was built for or 0, documents it holds)."""
         mid, nd = C.c_int32(0), C.c_int64(0)

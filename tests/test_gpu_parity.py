@@ -749,3 +749,74 @@ def test_save_load_bit_equal(engine, tmp_path):
     finally:
         a.close()
         b.close()
+
+
+@pytest.mark.parametrize("masked", [False, True])
+def test_sparse_rare_terms_without_offset_rows(engine, masked):
+    """Terms whose postings do not outweigh a per-sub-tile offset row get none (the table was V x N/2048
+    words whatever the vocabulary); the scans search their short lists instead.  Forced for every term here: both
+    kernels, long and short queries, must answer bit for bit like the index with a full table, and like the oracle."""
+    n_docs, V, L, k, B = 60_000, 4000, 60, 50, 48
+    ptr, doc, w, _ = synth.zipf_corpus(n_docs, V, L, seed=201)
+    qp, qt, qv = synth.sparse_queries(ptr, doc, n_docs, B, 8, "zipf", seed=202, skip_top=8)
+    qp2, qt2, qv2 = synth.sparse_queries(ptr, doc, n_docs, 6, 24, "doc", seed=203)       # > 16 terms: second term group
+    mask = synth.random_mask(n_docs, 0.4) if masked else None
+    if masked:
+        engine.mask_set(6, mask)
+    mid = 6 if masked else 0
+    engine.sparse_set_csr("full", ptr, doc, w, n_docs)
+    engine.sparse_offsets_min_df(1 << 40)
+    engine.sparse_set_csr("rare", ptr, doc, w, n_docs)
+    engine.sparse_offsets_min_df(300)                      # mixed: head terms keep rows, the tail is searched
+    engine.sparse_set_csr("mixed", ptr, doc, w, n_docs)
+    engine.sparse_offsets_min_df(0)
+    csr = O.CSR(ptr, doc, w, n_docs)
+    try:
+        for path in ("scatter", "bitmap"):
+            engine.force_sparse_path(path)
+            for (a, b_, c_) in ((qp, qt, qv), (qp2, qt2, qv2)):
+                want = engine.sparse_topk("full", a, b_, c_, k, mask_id=mid)
+                for name in ("rare", "mixed"):
+                    got = engine.sparse_topk(name, a, b_, c_, k, mask_id=mid)
+                    assert np.array_equal(got[2], want[2]) and np.array_equal(got[1], want[1]), (path, name)
+                    assert np.array_equal(got[0].view(np.uint32), want[0].view(np.uint32)), (path, name)
+                for b in range(0, len(a) - 1, 5):
+                    es, ei = O.sparse_topk(csr, b_[a[b]:a[b + 1]], c_[a[b]:a[b + 1]], k, mask=mask)
+                    assert int(want[2][b]) == len(ei) and np.array_equal(want[1][b][:len(ei)], ei)
+    finally:
+        engine.force_sparse_path(None)
+        for name in ("full", "rare", "mixed"):
+            engine.sparse_drop(name)
+
+
+def test_sparse_index_footprint_with_a_hashed_vocabulary(engine):
+    """2 M distinct term rows (what murmur3-hashed stems give) over 300 k documents: the index must stay within a small
+    multiple of the postings (round 1: 2 M x 148 offset words = 1.2 GB beside 100 MB of postings)."""
+    import torch
+    rng = np.random.default_rng(5)
+    n_docs, V, per_doc = 300_000, 2_000_000, 40
+    term = np.concatenate([rng.integers(0, 2000, (n_docs, per_doc // 2)),              # a frequent head ...
+                           rng.integers(0, V, (n_docs, per_doc // 2))], axis=1)       # ... and a long hashed tail
+    key = np.unique(term.astype(np.int64) * n_docs + np.arange(n_docs)[:, None])
+    t, d = key // n_docs, (key % n_docs).astype(np.uint32)
+    ptr = np.zeros(V + 1, np.int64)
+    np.add.at(ptr, t + 1, 1)
+    ptr = np.cumsum(ptr)
+    w = (rng.random(len(d)).astype(np.float32) + 0.1)
+    torch.cuda.synchronize()
+    free0, _ = torch.cuda.mem_get_info()
+    engine.sparse_set_csr("hv", ptr, d, w, n_docs)
+    free1, _ = torch.cuda.mem_get_info()
+    used, postings = free0 - free1, len(d) * 8
+    assert used < 4 * postings + (64 << 20), (used, postings)
+    q_terms = np.sort(np.concatenate([rng.choice(2000, 3, replace=False), 2000 + rng.choice(V - 2000, 5, replace=False)])).astype(np.int32)
+    q_ptr = np.array([0, 8], np.int32)
+    q_vals = np.ones(8)
+    csr = O.CSR(ptr, d, w, n_docs)
+    es, ei = O.sparse_topk(csr, q_terms, q_vals, 20)
+    for path in ("scatter", "bitmap"):
+        engine.force_sparse_path(path)
+        s, i, c = engine.sparse_topk("hv", q_ptr, q_terms, q_vals, 20)
+        assert int(c[0]) == len(ei) and np.array_equal(i[0][:len(ei)], ei) and np.array_equal(s[0][:len(ei)].view(np.uint32), es.view(np.uint32))
+    engine.force_sparse_path(None)
+    engine.sparse_drop("hv")
