@@ -31,7 +31,12 @@ extern "C" {
 
 typedef struct brag_engine brag_engine;
 
-enum brag_dtype { BRAG_F32 = 0, BRAG_F16 = 1, BRAG_BF16 = 2 };
+/* Storage of a dense space.  BRAG_I8 is the reference's "quantized" vector (qdrant_handler.py:144-146: int8 values held
+ * in a COSINE space): rows are raw int8, d a multiple of 128, and the space ALWAYS scores by the cosine of the integer
+ * vectors -- exact int32 dot, score = float32(dot / (sqrt(sum x^2) * sqrt(sum q^2))) evaluated in float64, 0 for a
+ * zero row or query.  Its queries are float32 arrays holding integer values in [-128, 127] (what the reference
+ * sends, :300-302); k <= 416. */
+enum brag_dtype { BRAG_F32 = 0, BRAG_F16 = 1, BRAG_BF16 = 2, BRAG_I8 = 3 };
 enum brag_rrf_tie { BRAG_TIE_ID = 0, BRAG_TIE_FIRST_SEEN = 1 };
 
 /* Engine lifecycle.  Replaces AsyncQdrantClient(url=...) (qdrant_session.py:21). */

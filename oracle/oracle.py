@@ -41,7 +41,7 @@ def round_storage(x: np.ndarray, dtype: str) -> np.ndarray:
 
     bf16 is round-to-nearest-even on the upper 16 bits (what the device converter does)."""
     x = np.ascontiguousarray(x, dtype=np.float32)
-    if dtype == "f32":
+    if dtype in ("f32", "i8"):              # int8 spaces hold the integer values the caller sent
         return x
     if dtype == "f16":
         return x.astype(np.float16).astype(np.float32)
@@ -76,6 +76,24 @@ def dense_scores(x_stored: np.ndarray, q_stored: np.ndarray) -> np.ndarray:
     return (x_stored.astype(np.float64) @ q_stored.astype(np.float64)).astype(np.float32)
 
 
+def int8_cosine_scores(x_int: np.ndarray, q_int: np.ndarray) -> np.ndarray:
+    """Row a9 with int8 STORAGE (include/brag.h BRAG_I8): cosine of the integer vectors the reference builds
+    (qdrant_handler.py:144-146 rows, :300-302 query).  Exact integer dot and squared norms, then one float64
+    expression dot / (sqrt(ssx) * sqrt(ssq)) rounded to float32; a zero row or query scores 0.  (Qdrant holding the
+    same values in a float32 COSINE space normalises rows and query in float32 first; the two differ by float32
+    rounding of the norms, ~1e-7 relative -- tests/test_oracle_kat.py pins that bound.)"""
+    xi = np.asarray(x_int).astype(np.int64)
+    qi = np.asarray(q_int).astype(np.int64)
+    dot = xi @ qi
+    ssx = (xi * xi).sum(axis=-1)
+    ssq = int((qi * qi).sum())
+    den = np.sqrt(ssx.astype(np.float64)) * np.sqrt(np.float64(ssq))
+    out = np.zeros(dot.shape, np.float64)
+    ok = den != 0.0
+    out[ok] = dot[ok].astype(np.float64) / den[ok]
+    return out.astype(np.float32)
+
+
 def topk_order(scores: np.ndarray, ids: np.ndarray, k: int) -> np.ndarray:
     """Indices of the k best entries under (score desc, id asc)."""
     order = np.lexsort((ids, -scores.astype(np.float64)))
@@ -83,15 +101,17 @@ def topk_order(scores: np.ndarray, ids: np.ndarray, k: int) -> np.ndarray:
 
 
 def dense_topk(x_stored: np.ndarray, q_stored: np.ndarray, k: int,
-               mask: Optional[np.ndarray] = None, cand: Optional[np.ndarray] = None
+               mask: Optional[np.ndarray] = None, cand: Optional[np.ndarray] = None, int8: bool = False
                ) -> Tuple[np.ndarray, np.ndarray]:
     """Rows a1/a2/a5: full or candidate-restricted scan, bitmask predicate, top-k.
-    mask: bool [N] (True = keep).  cand: int row ids (union semantics: duplicates dropped)."""
+    mask: bool [N] (True = keep).  cand: int row ids (union semantics: duplicates dropped).
+    int8: the space is stored as int8 (scores = int8_cosine_scores)."""
     n = x_stored.shape[0]
     ids = np.arange(n, dtype=np.int64) if cand is None else np.unique(np.asarray(cand, dtype=np.int64))
     if mask is not None:
         ids = ids[mask[ids]]
-    s = dense_scores(x_stored[ids], q_stored) if len(ids) else np.zeros(0, np.float32)
+    score = int8_cosine_scores if int8 else dense_scores
+    s = score(x_stored[ids], q_stored) if len(ids) else np.zeros(0, np.float32)
     o = topk_order(s, ids, k)
     return s[o], ids[o]
 
@@ -254,9 +274,13 @@ class OracleCollection:
 
     def add_dense(self, name: str, x: np.ndarray, distance: str = "cosine", storage: str = "f32"):
         x = np.asarray(x, dtype=np.float32)
-        if distance == "cosine":
-            x = normalize_rows(x)
-        self.dense[name] = round_storage(x, storage)
+        if storage == "i8":
+            assert distance == "cosine" and np.array_equal(np.rint(x), x) and np.abs(x).max(initial=0) <= 128
+            self.dense[name] = x                          # the integer values; scored by int8_cosine_scores
+        else:
+            if distance == "cosine":
+                x = normalize_rows(x)
+            self.dense[name] = round_storage(x, storage)
         self.distance[name] = distance
         self.storage[name] = storage
         self.n = x.shape[0]
@@ -272,7 +296,7 @@ class OracleCollection:
         carry a datatype.  (Round 1 rounded it to the storage dtype on both sides; the engine now only feeds the
         rounded copy to its 16-bit tensor-core scan and re-scores the candidates with the float32 query.)"""
         q = np.asarray(q, dtype=np.float32)
-        if self.distance[name] == "cosine":
+        if self.distance[name] == "cosine" and self.storage[name] != "i8":
             q = normalize_rows(q[None, :])[0]
         return q
 
@@ -319,7 +343,7 @@ def run_node(col: OracleCollection, node: Node, rrf_tie: str = "id", propagate: 
             vals = apply_idf(csr, terms, vals)
         return sparse_topk(csr, terms, vals, lim, mask=node.mask, cand=cand)
     q = col.prep_query(node.using, node.query)
-    return dense_topk(col.dense[node.using], q, lim, mask=node.mask, cand=cand)
+    return dense_topk(col.dense[node.using], q, lim, mask=node.mask, cand=cand, int8=col.storage[node.using] == "i8")
 
 
 def reference_tree(dense_vector: Sequence[float], sparse_terms: Sequence[int], sparse_vals: Sequence[float],

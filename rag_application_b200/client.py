@@ -26,7 +26,20 @@ from . import models as M
 
 EPS32 = float(np.finfo(np.float32).eps)
 DEFAULT_LIMIT = 10          # qdrant's default `limit` (also used by a fusion prefetch that omits it)
-_STORAGE = {None: "f32", "float32": "f32", "float16": "f16", "bfloat16": "bf16", "f32": "f32", "f16": "f16", "bf16": "bf16"}
+_STORAGE = {None: "f32", "float32": "f32", "float16": "f16", "bfloat16": "bf16", "f32": "f32", "f16": "f16", "bf16": "bf16",
+            "i8": "i8", "int8": "i8"}
+
+
+def _prep_rows(x: np.ndarray, dist: str, storage: str) -> np.ndarray:
+    """Rows as the engine stores them: L2-normalised for COSINE spaces, except int8 storage, which keeps the integer
+    values the caller sent (the reference's `quantized` vector, qdrant_handler.py:144-146) and scores by their cosine
+    in the engine (include/brag.h: BRAG_I8)."""
+    if storage == "i8":
+        r = np.rint(x)
+        if not (np.array_equal(r, x) and (x.size == 0 or (r.min() >= -128 and r.max() <= 127))):
+            raise ValueError("a vector stored as int8 must hold integer values in [-128, 127]")
+        return np.asarray(x, np.float32)
+    return _normalize_rows(x) if dist == "cosine" else x
 
 
 def _get(obj, name, default=None):
@@ -154,7 +167,7 @@ def compile_filter(flt, payloads: List[Optional[dict]], ids: List[Any]) -> np.nd
 # ------------------------------------------------------------------------------ collection (host side)
 class _Collection:
     def __init__(self, name: str, vectors_config: Dict[str, Any], sparse_config: Optional[Dict[str, Any]],
-                 default_storage: Optional[str]):
+                 default_storage: Optional[str], storage_overrides: Optional[Dict[str, str]] = None):
         self.name = name
         self.dense_cfg: Dict[str, Tuple[int, str, str]] = {}     # vector name -> (size, distance, storage)
         for vname, vp in (vectors_config or {}).items():
@@ -162,7 +175,10 @@ class _Collection:
             if dist not in ("cosine", "dot"):
                 raise ValueError(f"distance {dist!r} of vector {vname!r} is not supported (Cosine / Dot only)")
             storage = _STORAGE[_enum_value(_get(vp, "datatype"))] if _get(vp, "datatype") else (default_storage or "f32")
-            self.dense_cfg[vname] = (int(_get(vp, "size")), dist, _STORAGE[storage])
+            storage = _STORAGE[(storage_overrides or {}).get(vname, storage)]
+            if storage == "i8" and (dist != "cosine" or int(_get(vp, "size")) % 128 != 0):
+                raise ValueError(f"vector {vname!r}: int8 storage needs a Cosine space whose size is a multiple of 128")
+            self.dense_cfg[vname] = (int(_get(vp, "size")), dist, storage)
         self.sparse_cfg: Dict[str, str] = {}                      # vector name -> "none" | "idf"
         for vname, sp in (sparse_config or {}).items():
             self.sparse_cfg[vname] = str(_enum_value(_get(sp, "modifier") or "none")).lower()
@@ -290,19 +306,17 @@ class _Collection:
                 # place (brag_dense_append / brag_dense_update) instead of re-uploading the space
                 if n > n_old:
                     xa = np.stack(rows[n_old:]).astype(np.float32)
-                    engine.dense_append(self.space(vname), _normalize_rows(xa) if dist == "cosine" else xa)
+                    engine.dense_append(self.space(vname), _prep_rows(xa, dist, storage))
                 dirty = sorted(self.dense_dirty[vname])
                 if dirty:
                     xu = np.stack([rows[i] for i in dirty]).astype(np.float32)
-                    engine.dense_update(self.space(vname), dirty, _normalize_rows(xu) if dist == "cosine" else xu)
+                    engine.dense_update(self.space(vname), dirty, _prep_rows(xu, dist, storage))
             else:
                 x = np.zeros((n, size), dtype=np.float32)
                 for i, r in enumerate(rows):
                     if r is not None:
                         x[i] = r
-                if dist == "cosine":
-                    x = _normalize_rows(x)
-                engine.dense_set(self.space(vname), x, storage)
+                engine.dense_set(self.space(vname), _prep_rows(x, dist, storage), storage)
             self.present[vname] = None if have.all() else have
             self.dense_in_hbm[vname] = n
             self.dense_dirty[vname].clear()
@@ -354,7 +368,11 @@ class B200QdrantCore:
 
     def __init__(self, device: int = 0, storage: Optional[str] = None, engine_factory: Optional[Callable] = None,
                  rrf_tie: str = "id", filter_propagation: str = "server", devices: Optional[Sequence[int]] = None,
-                 shard_block_rows: int = 1 << 16):
+                 shard_block_rows: int = 1 << 16, storage_overrides: Optional[Dict[str, str]] = None):
+        # storage_overrides: vector name -> "f32" | "f16" | "bf16" | "i8" for every collection of this client, e.g.
+        # {"quantized": "i8"}: the reference's int8 vector (qdrant_handler.py:144-146) kept as int8 rows and scanned
+        # by the kind::i8 tensor-core kernel instead of as one more float space
+        self.storage_overrides = dict(storage_overrides or {})
         if filter_propagation not in ("server", "local"):
             raise ValueError("filter_propagation must be 'server' or 'local'")
         self.filter_propagation = filter_propagation
@@ -426,7 +444,8 @@ class B200QdrantCore:
             if vectors_config is not None and not isinstance(vectors_config, dict):
                 vectors_config = {"": vectors_config}
             self.collections[collection_name] = _Collection(collection_name, vectors_config or {},
-                                                            sparse_vectors_config, self.default_storage)
+                                                            sparse_vectors_config, self.default_storage,
+                                                            self.storage_overrides)
             return True
 
     def delete_collection(self, collection_name: str, **_ignored) -> bool:
@@ -507,20 +526,22 @@ class B200QdrantCore:
         return pos.astype(np.int32), val
 
     ENGINE_MAX_K = 512          # longest list one brag_dense_topk / brag_sparse_topk call returns
+    ENGINE_MAX_K_I8 = 416       # ... from an int8 space (tensor-core scan only, include/brag.h)
     ENGINE_MAX_CAND = 8192      # candidates (and results) of one brag_dense_rescore call
 
-    def _paged(self, col: _Collection, limit: int, mask: Optional[np.ndarray], key, call):
+    def _paged(self, col: _Collection, limit: int, mask: Optional[np.ndarray], key, call, max_k: Optional[int] = None):
         """One ranked list of `limit` entries for one query.  The reference's prefetch limits are free parameters (an
         LLM picks them per query, hybrid_search_workflow.py:28-66) and may exceed the engine's list length: longer
         lists are served in pages, each page a scan under the filter minus the rows already returned.  Every page is
         the best of what is left under (score desc, id asc), so the concatenation is exactly the long list."""
-        if limit <= self.ENGINE_MAX_K:
+        max_k = max_k or self.ENGINE_MAX_K
+        if limit <= max_k:
             return call(limit, self._mask_id(col, mask, key))
         left = np.ones(len(col), dtype=bool) if mask is None else mask.copy()
         ss, ii = [], []
         got = 0
         while got < limit:
-            want = min(self.ENGINE_MAX_K, limit - got)
+            want = min(max_k, limit - got)
             s, i, c = call(want, self._mask_id(col, left, None))
             c0 = int(np.asarray(c)[0])
             if c0 == 0:
@@ -607,12 +628,12 @@ class B200QdrantCore:
             using = "" if using is None else using
             if using not in col.dense_cfg:
                 raise ValueError(f"Not existing vector name error: {using}")
-            size, dist, _ = col.dense_cfg[using]
+            size, dist, storage = col.dense_cfg[using]
             q = np.asarray(query, dtype=np.float32).reshape(1, -1)
             if q.shape[1] != size:
                 raise ValueError(f"query for {using!r}: expected dim {size}, got {q.shape[1]}")
-            if dist == "cosine":
-                q = _normalize_rows(q)
+            q = _prep_rows(q, dist, storage)
+            max_k = self.ENGINE_MAX_K_I8 if storage == "i8" else self.ENGINE_MAX_K
             present = col.present.get(using)
             if present is not None and not present.any():
                 return empty
@@ -638,7 +659,7 @@ class B200QdrantCore:
                     s, i, c = s[o][None, :], i[o][None, :], np.array([len(o)], np.int32)
             else:
                 s, i, c = self._paged(col, min(limit, n), mask, key,
-                                      lambda kk, mid: self.engine.dense_topk(col.space(using), q, kk, mid))
+                                      lambda kk, mid: self.engine.dense_topk(col.space(using), q, kk, mid), max_k)
         c0 = int(np.asarray(c)[0])
         return np.asarray(s)[0, :c0].astype(np.float64), np.asarray(i)[0, :c0].astype(np.int64)
 
@@ -673,10 +694,8 @@ class B200QdrantCore:
         with self._lock:
             col = self._col(collection_name)
             col.commit(self.engine)
-            size, dist, _ = col.dense_cfg[using_dense]
-            Q = np.asarray(dense_queries, dtype=np.float32).reshape(len(sparse_queries), size)
-            if dist == "cosine":
-                Q = _normalize_rows(Q)
+            size, dist, storage = col.dense_cfg[using_dense]
+            Q = _prep_rows(np.asarray(dense_queries, dtype=np.float32).reshape(len(sparse_queries), size), dist, storage)
             terms, vals, ptr = [], [], [0]
             for sq in sparse_queries:
                 t, v = self._sparse_query(col, using_sparse, sq)
@@ -717,10 +736,10 @@ class B200QdrantClient:
 
     def __init__(self, device: int = 0, storage: Optional[str] = None, engine_factory: Optional[Callable] = None,
                  rrf_tie: str = "id", filter_propagation: str = "server", devices: Optional[Sequence[int]] = None,
-                 shard_block_rows: int = 1 << 16, **_ignored):
+                 shard_block_rows: int = 1 << 16, storage_overrides: Optional[Dict[str, str]] = None, **_ignored):
         self._core = B200QdrantCore(device=device, storage=storage, engine_factory=engine_factory, rrf_tie=rrf_tie,
                                     filter_propagation=filter_propagation, devices=devices,
-                                    shard_block_rows=shard_block_rows)
+                                    shard_block_rows=shard_block_rows, storage_overrides=storage_overrides)
 
     @property
     def core(self) -> B200QdrantCore:

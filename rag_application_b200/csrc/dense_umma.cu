@@ -110,12 +110,30 @@ __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
-__device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "setp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
-        ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc) : "memory");
+// KIND: 0 = kind::f16 (f16 / bf16 operands, f32 accumulate), 1 = kind::tf32 (float32 storage), 2 = kind::i8 (int8
+// operands, exact int32 accumulate).  Every kind consumes 32 bytes of K per instruction and one 128-byte swizzle atom
+// per pipeline stage, so the pipeline below is the same for all three.
+template <int KIND>
+__device__ __forceinline__ void umma_issue(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
+    if constexpr (KIND == 0) {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "setp.ne.b32 p, %4, 0;\n\t"
+            "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+            ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc) : "memory");
+    } else if constexpr (KIND == 1) {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "setp.ne.b32 p, %4, 0;\n\t"
+            "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+            ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc) : "memory");
+    } else {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "setp.ne.b32 p, %4, 0;\n\t"
+            "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n\t}"
+            ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc) : "memory");
+    }
 }
 __device__ __forceinline__ void tmem_ld32_issue(uint32_t taddr, uint32_t (&v)[32]) {
     asm volatile(
@@ -189,13 +207,20 @@ __device__ __forceinline__ void um_compact(unsigned bal, uint64_t* my_list, uint
 // lists  : [grid][n_qblocks][128][UM_CAP] keys (unsorted), counts: [grid][B] entries used
 // gthr   : [B] order-preserving uint32 score bounds (0 = none yet)
 // coarse : [B][HIST_COARSE_BINS], fine: [B][HIST_FINE_BINS] row counts per score bin
+// I8 (KIND 2): scores are cosines of integer vectors, idot * xinv[row] * qinv[query] (xinv / qinv = inverse norms).
+// The accumulators stay int32; a 32-column group is first tested in the integer domain against
+// Ti = floor(bound / (qinv * xinv_max)) (three-input integer max, one vote), and only the columns that pass are scaled
+// by their own row's inverse norm and compared with the bound itself.
+template <int KIND>
 __global__ void __launch_bounds__(UM_THREADS, 1)
 dense_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_x,
-                  int64_t n, int d, int B, int qb_base, int n_qblocks, float4* __restrict__ seedv, int seed_tiles,
+                  int64_t n, int n_kb, int B, int qb_base, int n_qblocks, float4* __restrict__ seedv, int seed_tiles,
                   int64_t rows_per_chunk, int share,
                   const uint32_t* __restrict__ mask, int k_sel, uint32_t idesc, uint64_t* __restrict__ lists,
                   int* __restrict__ counts, uint32_t* __restrict__ gthr, uint32_t* __restrict__ coarse,
-                  uint32_t* __restrict__ fine, const ShardBounds xb) {
+                  uint32_t* __restrict__ fine, const ShardBounds xb, const float* __restrict__ xinv,
+                  const float* __restrict__ qinv, float xinv_max) {
+    constexpr int KELEMS = KIND == 0 ? 64 : (KIND == 1 ? 32 : 128);      // elements in one 128-byte K slice
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     UmSmem& S = *reinterpret_cast<UmSmem*>(smem_raw);   // keeps the shared address space (LDS/STS in the sort)
     if ((smem_u32(smem_raw) & 1023u) != 0u) __trap();   // 128B-swizzle atoms need 1024-byte alignment
@@ -214,7 +239,6 @@ dense_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
     const int64_t row_begin = (int64_t)((int)blockIdx.x / sh) * rows_per_chunk;
     const int64_t row_end = min(n, row_begin + (seeding ? (int64_t)UM_BN : rows_per_chunk));
     const int n_tiles = row_end > row_begin ? (int)((row_end - row_begin + UM_BN - 1) / UM_BN) : 0;
-    const int n_kb = d / UM_BK;
 
     if (warp == 0 && lane == 0) {
         for (int s = 0; s < UM_STAGES; ++s) { mbar_init(&S.full[s], 1); mbar_init(&S.empty[s], 1); }
@@ -245,8 +269,8 @@ dense_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
                         mbar_expect_tx(&S.full[stage], UM_A_BYTES + UM_B_BYTES);
                         // queries stay hot in L2 for the whole scan; an X tile is wanted until its last
                         // query block has used it, then it should leave first
-                        tma_load_2d(S.a[stage], &tmap_q, kb * UM_BK, (qb_base + qb) * UM_BM, &S.full[stage], L2_EVICT_LAST);
-                        tma_load_2d(S.b[stage], &tmap_x, kb * UM_BK, row0, &S.full[stage],
+                        tma_load_2d(S.a[stage], &tmap_q, kb * KELEMS, (qb_base + qb) * UM_BM, &S.full[stage], L2_EVICT_LAST);
+                        tma_load_2d(S.b[stage], &tmap_x, kb * KELEMS, row0, &S.full[stage],
                                     (qb + 1 < qb_hi || sh > 1) ? L2_EVICT_NORMAL : L2_EVICT_FIRST);
                         if (++stage == UM_STAGES) { stage = 0; phase ^= 1; }
                     }
@@ -273,7 +297,7 @@ dense_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
 #pragma unroll
                     for (int k = 0; k < UM_BK / 16; ++k) {
                         // +32 bytes per 16-element K step inside the swizzle atom (>>4 => +2)
-                        umma_f16(tmem_d, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc, (kb | k) ? 1u : 0u);
+                        umma_issue<KIND>(tmem_d, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc, (kb | k) ? 1u : 0u);
                     }
                     umma_commit(&S.empty[stage]);
                     if (kb == n_kb - 1) umma_commit(&S.tfull[as]);
@@ -326,12 +350,17 @@ dense_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
                         tmem_ld_wait(v);
 #pragma unroll
                         for (int i = 0; i < 32; ++i) {
-                            float a = ((cm >> i) & 1u) ? __uint_as_float(v[i]) : -INFINITY;
+                            float a;
+                            if constexpr (KIND == 2) a = ((cm >> i) & 1u) ? (float)(int)v[i] * __ldg(xinv + min(r0 + i, n - 1)) : -INFINITY;
+                            else a = ((cm >> i) & 1u) ? __uint_as_float(v[i]) : -INFINITY;
                             float hi = fmaxf(t0, a); a = fminf(t0, a); t0 = hi;
                             hi = fmaxf(t1, a); a = fminf(t1, a); t1 = hi;
                             hi = fmaxf(t2, a); a = fminf(t2, a); t2 = hi;
                             t3 = fmaxf(t3, a);
                         }
+                    }
+                    if constexpr (KIND == 2) {
+                        if (q_valid) { const float qi = __ldg(qinv + b); t0 *= qi; t1 *= qi; t2 *= qi; t3 *= qi; }
                     }
                     if (q_valid) seedv[(size_t)b * seed_tiles + blockIdx.x] = make_float4(t0, t1, t2, t3);
                     tc_fence_before();
@@ -350,7 +379,53 @@ dense_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
                 float eff = thr;
                 if (g != 0u) eff = fmaxf(eff, nextafterf(ordered_f32(g), -INFINITY));   // keeps score >= bound
                 const uint32_t taddr = lane_taddr + (uint32_t)(as * UM_BN);
+                // I8: the same threshold in the integer domain of the accumulators.  score = idot * xinv[row] * qinv
+                // <= idot * xinv_max * qinv for idot >= 0, so score > eff needs idot > eff / (qinv * xinv_max); a
+                // non-positive threshold lets every column through to the exact test.
+                float my_qinv = 1.f, qsc = 1.f;
+                int Ti = 0;
+                if constexpr (KIND == 2) {
+                    my_qinv = q_valid ? __ldg(qinv + b) : 1.f;
+                    qsc = 1.f / (my_qinv * xinv_max);
+                }
+                auto int_threshold = [&](float e) {
+                    return e > 0.f ? __float2int_rd(e * qsc * 0.999999f) - 1 : (int)0x80000000;
+                };
+                if constexpr (KIND == 2) Ti = int_threshold(eff);
                 auto process = [&](uint32_t (&v)[32], int col0) {
+                    if constexpr (KIND == 2) {
+                        int c0 = __vimax3_s32((int)v[0], (int)v[1], (int)v[2]), c1 = __vimax3_s32((int)v[8], (int)v[9], (int)v[10]);
+                        int c2 = __vimax3_s32((int)v[16], (int)v[17], (int)v[18]), c3 = __vimax3_s32((int)v[24], (int)v[25], (int)v[26]);
+                        c0 = __vimax3_s32(c0, (int)v[3], (int)v[4]);   c1 = __vimax3_s32(c1, (int)v[11], (int)v[12]);
+                        c2 = __vimax3_s32(c2, (int)v[19], (int)v[20]); c3 = __vimax3_s32(c3, (int)v[27], (int)v[28]);
+                        c0 = __vimax3_s32(c0, (int)v[5], (int)v[6]);   c1 = __vimax3_s32(c1, (int)v[13], (int)v[14]);
+                        c2 = __vimax3_s32(c2, (int)v[21], (int)v[22]); c3 = __vimax3_s32(c3, (int)v[29], (int)v[30]);
+                        c0 = __vimax3_s32(c0, (int)v[7], (int)v[15]);  c2 = __vimax3_s32(c2, (int)v[23], (int)v[31]);
+                        if (!__any_sync(0xFFFFFFFFu, __vimax3_s32(c0, c1, max(c2, c3)) > Ti)) return;
+                        const int64_t r0 = row0 + col0;
+                        uint32_t cm = (row_end - r0 >= 32) ? 0xFFFFFFFFu : (row_end > r0 ? (1u << (int)(row_end - r0)) - 1u : 0u);
+                        if (mask != nullptr) cm &= __ldg(mask + (r0 >> 5));
+                        uint32_t m = 0u;
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) m |= ((int)v[i] > Ti) ? (1u << i) : 0u;
+                        m &= cm;
+                        uint32_t mw = __reduce_or_sync(0xFFFFFFFFu, m);
+                        while (mw) {
+                            const int i = __ffs(mw) - 1;
+                            mw &= mw - 1;
+                            const int iv = (int)tmem_ld1(taddr + (uint32_t)(col0 + i));
+                            if ((m >> i) & 1u) {
+                                const float s = (float)iv * __ldg(xinv + r0 + i) * my_qinv;   // same two roundings as the seeding pass
+                                if (s > eff) {
+                                    const uint64_t key = make_key(s, (uint32_t)(r0 + i));
+                                    __stcg(my_list + cnt, key);
+                                    ++cnt;
+                                    hist_count(coarse, fine, b, (uint32_t)(key >> 32));
+                                }
+                            }
+                        }
+                        return;
+                    }
                     // rows of this 32-column group that exist and pass the payload filter (tiles start on
                     // multiples of 256 rows, so a group is exactly one filter word): warp-uniform
                     // most groups hold no candidate for any of the warp's 32 queries: the group's maximum (three-input
@@ -398,6 +473,7 @@ dense_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
                     if (bal) {   // list full (pathological): sort locally, keep k_sel, tighten the local bound
                         um_compact(bal, my_list, my_list, cnt, thr, sbuf, k_sel, lane);
                         eff = fmaxf(eff, thr);
+                        if constexpr (KIND == 2) Ti = int_threshold(eff);
                     }
                     if (__any_sync(0xFFFFFFFFu, q_valid && g == 0u)) {
                         // warm-up: no bound yet -- pick it up as soon as the manager publishes one, so the
@@ -405,6 +481,7 @@ dense_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
                         if (q_valid && g == 0u) {
                             g = __ldcg(gthr + b);
                             if (g != 0u) eff = fmaxf(eff, nextafterf(ordered_f32(g), -INFINITY));
+                            if constexpr (KIND == 2) Ti = int_threshold(eff);
                         }
                     }
                     tmem_ld_wait(va);
@@ -516,8 +593,11 @@ dense_umma_select_kernel(const uint64_t* __restrict__ lists, const int* __restri
 }
 
 // ------------------------------------------------------------------ host side
+// dtype: BRAG_F32 (0, kind::tf32), BRAG_F16 / BRAG_BF16 (1 / 2, kind::f16), BRAG_I8 (3, kind::i8).  A row must be a
+// whole number of 128-byte K slices.
+static int um_esz(int dtype) { return dtype == 0 ? 4 : (dtype == 3 ? 1 : 2); }
 bool dense_umma_supported(int dtype, int d, int64_t n) {
-    return (dtype == 1 || dtype == 2) && d % UM_BK == 0 && d >= UM_BK && n >= 1;
+    return dtype >= 0 && dtype <= 3 && d >= 1 && ((int64_t)d * um_esz(dtype)) % 128 == 0 && n >= 1;
 }
 
 int dense_umma_max_ksel() { return UM_CAP - 64; }
@@ -579,16 +659,20 @@ static EncodeTiledFn get_encode() {
     return fn;
 }
 
-// the dtype of the map only matters for OOB fill / element size: both 16-bit types move as raw bits
-cudaError_t make_tmap_2d(void* tmap_out, const void* base, int64_t rows, int d, int box_rows) {
+// [rows, d] row-major matrix of `dtype`, box = [box_rows, one 128-byte K slice], 128-byte swizzle.  (16-bit floats
+// move as raw bits: the map's element type only matters for the element size and OOB fill.)
+cudaError_t make_tmap_2d(void* tmap_out, const void* base, int64_t rows, int d, int box_rows, int dtype) {
     EncodeTiledFn enc = get_encode();
     if (!enc) return cudaErrorNotSupported;
+    const int esz = um_esz(dtype);
+    const CUtensorMapDataType dt = esz == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32
+                                            : (esz == 1 ? CU_TENSOR_MAP_DATA_TYPE_UINT8 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16);
     CUtensorMap tm;
     cuuint64_t gdim[2] = {(cuuint64_t)d, (cuuint64_t)rows};
-    cuuint64_t gstride[1] = {(cuuint64_t)d * 2};
-    cuuint32_t box[2] = {(cuuint32_t)UM_BK, (cuuint32_t)box_rows};
+    cuuint64_t gstride[1] = {(cuuint64_t)d * esz};
+    cuuint32_t box[2] = {(cuuint32_t)(128 / esz), (cuuint32_t)box_rows};
     cuuint32_t estr[2] = {1, 1};
-    CUresult r = enc(&tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gdim, gstride, box, estr,
+    CUresult r = enc(&tm, dt, 2, const_cast<void*>(base), gdim, gstride, box, estr,
                      CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return cudaErrorInvalidValue;
@@ -598,21 +682,44 @@ cudaError_t make_tmap_2d(void* tmap_out, const void* base, int64_t rows, int d, 
 
 // kernel attributes are per device: brag_create calls this with the engine's device current
 cudaError_t dense_umma_init_device() {
-    cudaError_t e = cudaFuncSetAttribute(dense_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(UmSmem));
+    cudaError_t e = cudaFuncSetAttribute(dense_umma_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(UmSmem));
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(dense_umma_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(UmSmem));
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(dense_umma_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(UmSmem));
     if (e != cudaSuccess) return e;
     return cudaFuncSetAttribute(dense_umma_select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SELK_CAP * 8);
 }
 
+template <int KIND>
+static void um_launch(int grid, size_t smem, cudaStream_t st, const CUtensorMap& tq, const CUtensorMap& tx, int64_t n, int n_kb,
+                      int B, int qb0, int nqb, float4* seedv, int n_seed, int64_t rows_per_chunk, int share, const uint32_t* mask,
+                      int k_sel, uint32_t idesc, uint64_t* lists, int* counts, uint32_t* gthr, uint32_t* coarse,
+                      uint32_t* fine, const ShardBounds& xb, const UmmaI8& i8) {
+    dense_umma_kernel<KIND><<<grid, UM_THREADS, smem, st>>>(tq, tx, n, n_kb, B, qb0, nqb, seedv, n_seed, rows_per_chunk, share,
+                                                           mask, k_sel, idesc, lists, counts, gthr, coarse, fine, xb,
+                                                           i8.xinv, i8.qinv, i8.xinv_max);
+}
+
 cudaError_t dense_umma_scan(const void* X16, int dtype, int64_t n, int d, const void* Q16, int B,
                             const uint32_t* mask, int k_sel, uint64_t* cand, void* scratch, const UmmaPlan& plan,
-                            void* tmap_x, void* tmap_q, cudaStream_t st, int* launches, const ShardBounds& xb) {
+                            void* tmap_x, void* tmap_q, cudaStream_t st, int* launches, const ShardBounds& xb,
+                            const UmmaI8& i8) {
     (void)X16; (void)Q16;
     const size_t smem = sizeof(UmSmem);
     CUtensorMap tq, tx;
     memcpy(&tq, tmap_q, sizeof tq);
     memcpy(&tx, tmap_x, sizeof tx);
-    const uint32_t fmt = (dtype == 2) ? 1u : 0u;  // BF16 : F16
-    const uint32_t idesc = (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(UM_BN >> 3) << 17) | ((uint32_t)(UM_BM >> 4) << 24);
+    // instruction descriptor: accumulator format (f32 / s32), operand format, N, M (cute/arch/mma_sm100_desc.hpp layout)
+    const int kind = dtype == 0 ? 1 : (dtype == 3 ? 2 : 0);
+    const uint32_t cfmt = kind == 2 ? 2u : 1u;
+    const uint32_t fmt = kind == 1 ? 2u : (kind == 2 ? 1u : (dtype == 2 ? 1u : 0u));   // TF32 | signed 8-bit | BF16 : F16
+    const uint32_t idesc = (cfmt << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(UM_BN >> 3) << 17) | ((uint32_t)(UM_BM >> 4) << 24);
+    const int n_kb = (int)((int64_t)d * um_esz(dtype) / 128);
+    auto launch = [&](int grid, int qb0, int nqb, float4* seedv, int n_seed, int64_t rows_per_chunk, int share,
+                      uint64_t* lists, int* counts, uint32_t* gthr, uint32_t* coarse, uint32_t* fine, const ShardBounds& b) {
+        if (kind == 0) um_launch<0>(grid, smem, st, tq, tx, n, n_kb, B, qb0, nqb, seedv, n_seed, rows_per_chunk, share, mask, k_sel, idesc, lists, counts, gthr, coarse, fine, b, i8);
+        else if (kind == 1) um_launch<1>(grid, smem, st, tq, tx, n, n_kb, B, qb0, nqb, seedv, n_seed, rows_per_chunk, share, mask, k_sel, idesc, lists, counts, gthr, coarse, fine, b, i8);
+        else um_launch<2>(grid, smem, st, tq, tx, n, n_kb, B, qb0, nqb, seedv, n_seed, rows_per_chunk, share, mask, k_sel, idesc, lists, counts, gthr, coarse, fine, b, i8);
+    };
     uint8_t* sp = reinterpret_cast<uint8_t*>(scratch);
     uint64_t* lists = reinterpret_cast<uint64_t*>(sp);
     int* counts = reinterpret_cast<int*>(sp + plan.list_bytes);
@@ -632,8 +739,7 @@ cudaError_t dense_umma_scan(const void* X16, int dtype, int64_t n, int d, const 
         const int nqb = std::min(UM_MAXQB, plan.n_qblocks - qb0);
         const int nq = std::min(B - qb0 * UM_BM, nqb * UM_BM);
         if (n_seed > 0) {
-            dense_umma_kernel<<<n_seed, UM_THREADS, smem, st>>>(tq, tx, n, d, B, qb0, nqb, seedv, n_seed, seed_stride, 1, mask,
-                                                               k_sel, idesc, lists, counts, gthr, coarse, fine, ShardBounds());
+            launch(n_seed, qb0, nqb, seedv, n_seed, seed_stride, 1, lists, counts, gthr, coarse, fine, ShardBounds());
             if ((err = cudaGetLastError()) != cudaSuccess) return err;
             um_seed_bound_kernel<<<nq, 256, 0, st>>>(seedv, n_seed, qb0 * UM_BM, qb0 * UM_BM + nq, k_sel, gthr);
             if ((err = cudaGetLastError()) != cudaSuccess) return err;
@@ -642,8 +748,7 @@ cudaError_t dense_umma_scan(const void* X16, int dtype, int64_t n, int d, const 
         // CTAs sharing a row range (see the kernel): only when the query blocks and the grid split evenly
         const int share = (um_share() > 1 && nqb % um_share() == 0 && n_main % um_share() == 0 && n_tiles >= n_main) ? um_share() : 1;
         const int64_t rows_per_chunk = (n_tiles + n_main / share - 1) / (n_main / share) * UM_BN;
-        dense_umma_kernel<<<n_main, UM_THREADS, smem, st>>>(tq, tx, n, d, B, qb0, nqb, nullptr, 0, rows_per_chunk, share, mask,
-                                                           k_sel, idesc, lists, counts, gthr, coarse, fine, xb);
+        launch(n_main, qb0, nqb, nullptr, 0, rows_per_chunk, share, lists, counts, gthr, coarse, fine, xb);
         if ((err = cudaGetLastError()) != cudaSuccess) return err;
         // final bounds from the complete histograms (a CTA's manager stops with its own CTA, so the bounds it left
         // may predate the last pushes of the others): the selection then gathers ~k_sel keys per query, not more

@@ -72,6 +72,13 @@ struct DenseSpace {
     int dtype = 0;
     bool umma_ok = false;
     alignas(64) unsigned char tmap_x[128];
+    // int8 spaces (BRAG_I8): inverse row norms for the scan's epilogue, and the largest of them
+    float* xinv = nullptr;
+    int64_t xinv_cap = 0;
+    float xinv_max = 0.f;
+    float* cp_xinv = nullptr;
+    int64_t cp_xinv_cap = 0;
+    float cp_xinv_max = 0.f;
     // filter-compacted copy (compact.cu) of the rows passing the filter (mask_id, version) last scanned with
     int cp_mask_id = 0;
     uint64_t cp_version = 0;
@@ -202,6 +209,39 @@ struct StageTimer {
 void use_device(brag_engine* e) { CK(cudaSetDevice(e->device)); }
 
 int k_select(int k) { return std::min(512, ((k + 32) + 3) / 4 * 4); }
+inline int dtype_bytes(int dtype) { return dtype == 0 ? 4 : (dtype == 3 ? 1 : 2); }
+
+// inverse row norms of an int8 matrix (grow-only buffer) and their maximum
+void i8_norms(const void* x, int64_t n, int d, float*& xinv, int64_t& cap, float& xinv_max) {
+    if (n > cap) {
+        if (xinv) CK(cudaFree(xinv));
+        xinv = nullptr;
+        cap = 0;
+        CK(cudaMalloc(&xinv, (size_t)(n + n / 2 + 64) * sizeof(float)));
+        cap = n + n / 2 + 64;
+    }
+    uint32_t* mx = nullptr;
+    CK(cudaMalloc(&mx, sizeof(uint32_t)));
+    cudaError_t ce = cudaMemset(mx, 0, sizeof(uint32_t));
+    if (ce == cudaSuccess) ce = brag::i8_row_inv_norms(x, n, d, xinv, mx, 0);
+    uint32_t bits = 0;
+    if (ce == cudaSuccess) ce = cudaMemcpy(&bits, mx, sizeof(uint32_t), cudaMemcpyDeviceToHost);
+    cudaFree(mx);
+    CK(ce);
+    memcpy(&xinv_max, &bits, sizeof(float));
+}
+
+// after the rows of a space changed: the scan's tensor map and, for int8 storage, the row norms
+void refresh_dense(DenseSpace& s) {
+    s.umma_ok = brag::dense_umma_supported(s.dtype, s.d, s.n) &&
+                brag::make_tmap_2d(s.tmap_x, s.x, s.n, s.d, 256, s.dtype) == cudaSuccess;
+    if (s.dtype == 3) {
+        REQUIRE(s.umma_ok, "int8 spaces are scanned by the tensor-core kernel only: d must be a multiple of 128");
+        i8_norms(s.x, s.n, s.d, s.xinv, s.xinv_cap, s.xinv_max);
+    }
+    s.cp_mask_id = 0;                                     // any filter-compacted copy is stale
+    s.cp_use = false;
+}
 
 const uint32_t* mask_ptr(brag_engine* e, int mask_id, int64_t need_bits) {
     if (mask_id == 0) return nullptr;
@@ -226,9 +266,13 @@ void free_dense(DenseSpace& s) {
     if (s.x) cudaFree(s.x);
     if (s.cp_x) cudaFree(s.cp_x);
     if (s.cp_rowmap) cudaFree(s.cp_rowmap);
+    if (s.xinv) cudaFree(s.xinv);
+    if (s.cp_xinv) cudaFree(s.cp_xinv);
     s.x = nullptr;
     s.cp_x = nullptr;
     s.cp_rowmap = nullptr;
+    s.xinv = s.cp_xinv = nullptr;
+    s.xinv_cap = s.cp_xinv_cap = 0;
 }
 void free_sparse(SparseSpace& s) {
     if (s.cp) { free_sparse(*s.cp); delete s.cp; }
@@ -346,7 +390,7 @@ bool ensure_compact(brag_engine* e, DenseSpace& s, int mask_id, const uint32_t* 
     CK(cudaStreamSynchronize(st));
     e->kernel_launches += 2;
     if ((int64_t)nc * 2 > s.n || nc < 4096 || !brag::dense_umma_supported(s.dtype, s.d, nc)) return false;
-    const size_t row_bytes = (size_t)s.d * 2;
+    const size_t row_bytes = (size_t)s.d * dtype_bytes(s.dtype);
     const size_t need_x = (size_t)nc * row_bytes, need_map = (size_t)nc * sizeof(uint32_t);
     if (need_x > s.cp_x_cap) {
         if (s.cp_x) CK(cudaFree(s.cp_x));
@@ -363,7 +407,12 @@ bool ensure_compact(brag_engine* e, DenseSpace& s, int mask_id, const uint32_t* 
         s.cp_rowmap_cap = need_map;
     }
     CK(brag::compact_rows(s.x, (int)row_bytes, mask, s.n, prefix, nc, s.cp_rowmap, s.cp_x, st));
-    if (brag::make_tmap_2d(s.cp_tmap, s.cp_x, nc, s.d, 256) != cudaSuccess) return false;
+    if (brag::make_tmap_2d(s.cp_tmap, s.cp_x, nc, s.d, 256, s.dtype) != cudaSuccess) return false;
+    if (s.dtype == 3) {
+        CK(cudaStreamSynchronize(st));
+        i8_norms(s.cp_x, nc, s.d, s.cp_xinv, s.cp_xinv_cap, s.cp_xinv_max);
+        e->kernel_launches += 1;
+    }
     e->kernel_launches += 2;
     s.cp_n = nc;
     s.cp_use = true;
@@ -443,7 +492,7 @@ void dense_topk_dev(brag_engine* e, DenseSpace& s, const float* Q, int B, int k,
     const int k_sel = k_select(k);
     int path = pick_path(e, s, B);
     if (path == 1 && k_sel > brag::dense_umma_max_ksel()) path = 0;     // k > 416: the GEMV scan holds longer lists
-    float* qs = e->qs.as<float>((size_t)B * s.d);
+    REQUIRE(s.dtype != 3 || path == 1, "dense_topk: int8 spaces take k <= 416 (tensor-core scan only)");
     uint64_t* cand = e->keys1.as<uint64_t>((size_t)B * k_sel);
     uint64_t* cand2 = e->keys2.as<uint64_t>((size_t)B * k_sel);
     // rows actually scanned: the whole space, or its filter-compacted copy
@@ -458,18 +507,25 @@ void dense_topk_dev(brag_engine* e, DenseSpace& s, const float* Q, int B, int k,
             compact = true;
             X = s.cp_x; n = s.cp_n; tmap_x = s.cp_tmap; scan_mask = nullptr;
         }
+        brag::UmmaI8 i8;
+        if (s.dtype == 3) {
+            i8.xinv = compact ? s.cp_xinv : s.xinv;
+            i8.xinv_max = compact ? s.cp_xinv_max : s.xinv_max;
+        }
         if (path == 1) {
             // tcgen05 scan; the per-query selection is part of the scan (no partial lists to merge)
             brag::UmmaPlan plan;
             CK(brag::dense_umma_plan(n, s.d, B, k_sel, e->num_sms, &plan));
             const int Bpad = plan.n_qblocks * 128;
-            void* q16 = e->q16.ensure((size_t)Bpad * s.d * 2);
-            CK(brag::round_queries(Q, B, s.d, s.dtype, qs, q16, Bpad, st));
-            CK(brag::make_tmap_2d(e->tmap_q, q16, Bpad, s.d, 128));
+            void* q16 = e->q16.ensure((size_t)Bpad * s.d * dtype_bytes(s.dtype));
+            float* qinv = s.dtype == 3 ? e->qs.as<float>((size_t)B) : nullptr;
+            i8.qinv = qinv;
+            CK(brag::scan_queries(Q, B, s.d, s.dtype, q16, Bpad, qinv, st));
+            CK(brag::make_tmap_2d(e->tmap_q, q16, Bpad, s.d, 128, s.dtype));
             void* scratch = e->umma_scratch.ensure(plan.scratch_bytes);
             int launches = 0;
             CK(brag::dense_umma_scan(X, s.dtype, n, s.d, q16, B, scan_mask, k_sel, cand, scratch, plan, tmap_x,
-                                     e->tmap_q, st, &launches, xb));
+                                     e->tmap_q, st, &launches, xb, i8));
             e->kernel_launches += 1 + launches;
         } else {
             // the GEMV scan multiplies in float32 anyway: it takes the caller's float32 query as it is, so its
@@ -730,8 +786,9 @@ int brag_dense_set(brag_engine* e, const char* name, const void* rows, int64_t n
                    int32_t on_device) {
     return guarded([&] {
         REQUIRE(e && name && rows, "brag_dense_set: NULL argument");
-        REQUIRE(dtype >= 0 && dtype <= 2, "brag_dense_set: dtype must be BRAG_F32/F16/BF16");
-        const int esz = dtype == 0 ? 4 : 2;
+        REQUIRE(dtype >= 0 && dtype <= 3, "brag_dense_set: dtype must be BRAG_F32/F16/BF16/I8");
+        const int esz = dtype_bytes(dtype);
+        REQUIRE(dtype != 3 || d % 128 == 0, "brag_dense_set: int8 rows must be a multiple of 128 elements");
         REQUIRE(n >= 1 && n < (int64_t)0xFFFFFFFFll, "brag_dense_set: need 1 <= n < 2^32-1");
         REQUIRE(d >= 1 && (d * esz) % 16 == 0, "brag_dense_set: row bytes must be a multiple of 16");
         REQUIRE(d * esz / 16 <= 256, "brag_dense_set: d too large (row > 4096 bytes)");
@@ -744,11 +801,7 @@ int brag_dense_set(brag_engine* e, const char* name, const void* rows, int64_t n
         CK(cudaMalloc(&s.x, bytes));
         cudaError_t ce = cudaMemcpy(s.x, rows, bytes, on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice);
         if (ce != cudaSuccess) { cudaFree(s.x); CK(ce); }
-        s.umma_ok = brag::dense_umma_supported(dtype, d, n);
-        if (s.umma_ok) {
-            cudaError_t te = brag::make_tmap_2d(s.tmap_x, s.x, n, d, 256);
-            if (te != cudaSuccess) s.umma_ok = false;
-        }
+        try { refresh_dense(s); } catch (...) { free_dense(s); throw; }
         e->dense[name] = s;
     });
 }
@@ -763,7 +816,7 @@ int brag_dense_append(brag_engine* e, const char* name, const void* rows, int64_
         DenseSpace& s = it->second;
         REQUIRE(s.d == d && s.dtype == dtype, "brag_dense_append: dimension / storage type differ from the space");
         REQUIRE(s.n + n_new < (int64_t)0xFFFFFFFFll, "brag_dense_append: too many rows");
-        const size_t row_bytes = (size_t)d * (dtype == 0 ? 4 : 2);
+        const size_t row_bytes = (size_t)d * dtype_bytes(dtype);
         CK(cudaDeviceSynchronize());                      // no scan may still read the buffer that is about to move
         if (s.n + n_new > s.cap) {
             const int64_t cap = std::max<int64_t>(s.n + n_new, s.cap * 2);
@@ -778,10 +831,7 @@ int brag_dense_append(brag_engine* e, const char* name, const void* rows, int64_
         CK(cudaMemcpy(static_cast<char*>(s.x) + (size_t)s.n * row_bytes, rows, (size_t)n_new * row_bytes,
                       on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice));
         s.n += n_new;
-        s.umma_ok = brag::dense_umma_supported(s.dtype, s.d, s.n) &&
-                    brag::make_tmap_2d(s.tmap_x, s.x, s.n, s.d, 256) == cudaSuccess;
-        s.cp_mask_id = 0;                                 // any filter-compacted copy is stale
-        s.cp_use = false;
+        refresh_dense(s);
     });
 }
 
@@ -790,7 +840,7 @@ int brag_dense_update(brag_engine* e, const char* name, const int64_t* row_ids, 
         REQUIRE(e && name && row_ids && rows && m >= 1, "brag_dense_update: bad arguments");
         use_device(e);
         DenseSpace& s = dense_space(e, name);
-        const size_t row_bytes = (size_t)s.d * (s.dtype == 0 ? 4 : 2);
+        const size_t row_bytes = (size_t)s.d * dtype_bytes(s.dtype);
         for (int64_t i = 0; i < m; ++i)
             REQUIRE(row_ids[i] >= 0 && row_ids[i] < s.n, "brag_dense_update: row id out of range");
         CK(cudaDeviceSynchronize());
@@ -798,6 +848,7 @@ int brag_dense_update(brag_engine* e, const char* name, const int64_t* row_ids, 
             CK(cudaMemcpyAsync(static_cast<char*>(s.x) + (size_t)row_ids[i] * row_bytes,
                                static_cast<const char*>(rows) + (size_t)i * row_bytes, row_bytes, cudaMemcpyHostToDevice, 0));
         CK(cudaDeviceSynchronize());
+        if (s.dtype == 3) i8_norms(s.x, s.n, s.d, s.xinv, s.xinv_cap, s.xinv_max);
         s.cp_mask_id = 0;
         s.cp_use = false;
     });
@@ -1623,7 +1674,7 @@ int brag_save(brag_engine* e, const char* path) {
         };
         for (auto& kv : e->dense)
             add(kv.first, 0, 0, kv.second.n, kv.second.d, kv.second.dtype, 0, kv.second.x,
-                (size_t)kv.second.n * kv.second.d * (kv.second.dtype == 0 ? 4 : 2));
+                (size_t)kv.second.n * kv.second.d * dtype_bytes(kv.second.dtype));
         for (auto& kv : e->sparse) {
             const SparseSpace& s = kv.second;
             const SparseArrays arr = sparse_arrays(s);
@@ -1693,8 +1744,8 @@ int brag_load(brag_engine* e, const char* path) {
                     if (it != e->dense.end()) { free_dense(it->second); e->dense.erase(it); }
                     DenseSpace ds;
                     ds.n = s.a; ds.cap = s.a; ds.d = (int)s.b; ds.dtype = (int)s.c;
-                    REQUIRE(ds.n >= 1 && ds.d >= 1 && ds.dtype >= 0 && ds.dtype <= 2 &&
-                            s.bytes == (uint64_t)ds.n * ds.d * (ds.dtype == 0 ? 4 : 2), "brag_load: corrupt dense section");
+                    REQUIRE(ds.n >= 1 && ds.d >= 1 && ds.dtype >= 0 && ds.dtype <= 3 &&
+                            s.bytes == (uint64_t)ds.n * ds.d * dtype_bytes(ds.dtype), "brag_load: corrupt dense section");
                     CK(cudaMalloc(&ds.x, s.bytes));
                     try {
                         read_device_array(f, ds.x, s.bytes, stage, stage_bytes);
@@ -1702,8 +1753,7 @@ int brag_load(brag_engine* e, const char* path) {
                         cudaFree(ds.x);
                         throw;
                     }
-                    ds.umma_ok = brag::dense_umma_supported(ds.dtype, ds.d, ds.n) &&
-                                 brag::make_tmap_2d(ds.tmap_x, ds.x, ds.n, ds.d, 256) == cudaSuccess;
+                    refresh_dense(ds);
                     e->dense[name] = ds;
                 } else if (s.kind == 1) {
                     SparseSpace& sp = loading[name];

@@ -28,7 +28,14 @@ struct UmmaPlan {
     size_t list_bytes, count_bytes, gthr_bytes, coarse_bytes, fine_bytes, seed_bytes;
     size_t scratch_bytes;   // lists | counts | per-query bounds | coarse + fine score histograms
 };
+// dtype 0 float32 (kind::tf32), 1 / 2 float16 / bfloat16 (kind::f16), 3 int8 (kind::i8, exact int32 dots)
 bool dense_umma_supported(int dtype, int d, int64_t n);
+// int8 spaces: scores are cosines of integer vectors, idot * xinv[row] * qinv[query]
+struct UmmaI8 {
+    const float* xinv = nullptr;    // [n] inverse norms of the stored rows
+    const float* qinv = nullptr;    // [B] inverse norms of the (quantised) queries
+    float xinv_max = 0.f;           // largest xinv over the space
+};
 // longest candidate list (k + selection margin) the tcgen05 scan keeps per (CTA, query); longer ones take the GEMV scan
 int dense_umma_max_ksel();
 cudaError_t dense_umma_plan(int64_t n, int d, int B, int k_sel, int num_sms, UmmaPlan* plan);
@@ -37,9 +44,9 @@ cudaError_t dense_umma_plan(int64_t n, int d, int B, int k_sel, int num_sms, Umm
 cudaError_t dense_umma_scan(const void* X16, int dtype, int64_t n, int d, const void* Q16, int B,
                             const uint32_t* mask, int k_sel, uint64_t* cand, void* scratch,
                             const UmmaPlan& plan, void* tmap_x, void* tmap_q, cudaStream_t st, int* launches,
-                            const ShardBounds& xb);
-// builds a CUtensorMap (128 bytes) for a [rows, d] 16-bit row-major matrix, box = [box_rows, 64]
-cudaError_t make_tmap_2d(void* tmap_out, const void* base, int64_t rows, int d, int box_rows);
+                            const ShardBounds& xb, const UmmaI8& i8);
+// builds a CUtensorMap (128 bytes) for a [rows, d] row-major matrix of `dtype`, box = [box_rows, one 128-byte K slice]
+cudaError_t make_tmap_2d(void* tmap_out, const void* base, int64_t rows, int d, int box_rows, int dtype);
 
 // ---- select.cu
 // multi-level merge of P key lists per query: in [P][B][kk] -> out [B][kout] sorted desc
@@ -50,9 +57,11 @@ cudaError_t merge_key_lists(const uint64_t* in, int P, int B, int kk, uint64_t* 
 cudaError_t publish_bounds(const uint32_t* coarse, const uint32_t* fine, uint32_t* gthr, int B, int k, cudaStream_t st,
                            const ShardBounds& xb);
 size_t merge_tmp_elems(int P, int B, int kk);
-// round queries to the storage dtype: Qs f32 (rounded values) and optional 16-bit copy (padded rows zero)
-cudaError_t round_queries(const float* Q, int B, int d, int dtype, float* Qs, void* Q16, int Bpad,
-                          cudaStream_t st);
+// the tensor-core scan's copy of the queries in the stored element type, [Bpad, d] with zero padding rows
+// (dtype 3 also writes qinv[B], the inverse norms of the int8 queries)
+cudaError_t scan_queries(const float* Q, int B, int d, int dtype, void* out, int Bpad, float* qinv, cudaStream_t st);
+// int8 spaces: xinv[n] inverse row norms; *max_bits = atomicMax of their bit patterns (caller zeroes it first)
+cudaError_t i8_row_inv_norms(const void* X, int64_t n, int d, float* xinv, uint32_t* max_bits, cudaStream_t st);
 // keys_in [B][m] (rows from a scan) -> re-scored keys (f64 accumulate, f32 score), 0 stays 0
 cudaError_t rescore_keys(const void* X, int dtype, int64_t n, int d, const float* Qs, int B,
                          const uint64_t* keys_in, int m, uint64_t* keys_out, cudaStream_t st);

@@ -103,26 +103,69 @@ cudaError_t merge_key_lists(const uint64_t* in, int P, int B, int kk, uint64_t* 
     return cudaSuccess;
 }
 
-// ------------------------------------------------------------------ query rounding
-__global__ void round_queries_kernel(const float* __restrict__ Q, int B, int d, int dtype,
-                                     float* __restrict__ Qs, uint16_t* __restrict__ Q16, int Bpad) {
-    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    const size_t total = (size_t)Bpad * d;
-    if (i >= total) return;
-    const int b = (int)(i / d);
-    float v = (b < B) ? Q[i] : 0.0f;
-    uint16_t bits = 0;
-    if (dtype == 1) { __half h = __float2half_rn(v); v = __half2float(h); bits = __half_as_ushort(h); }
-    else if (dtype == 2) { __nv_bfloat16 h = __float2bfloat16_rn(v); v = __bfloat162float(h); bits = __bfloat16_as_ushort(h); }
-    if (b < B) Qs[i] = v;
-    if (Q16) Q16[i] = bits;
+// ------------------------------------------------------------------ scan copies of the queries
+// The tensor-core scan reads the queries in the element type of the stored rows, zero padded to whole 128-query
+// blocks: 16-bit roundings (f16 / bf16 storage), the float32 values as they are (tf32 reads their upper 19 bits), or
+// int8 (int8 storage: the caller sends integer-valued queries, qdrant_handler.py:300-302) with the inverse norm of each
+// query.  Only the scan sees this copy; candidates are re-scored from the caller's float32 queries.
+__global__ void scan_queries_kernel(const float* __restrict__ Q, int B, int d, int dtype, void* __restrict__ out,
+                                    int Bpad, float* __restrict__ qinv) {
+    const int w = (int)(((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
+    const int lane = threadIdx.x & 31;
+    if (w >= Bpad) return;
+    const float* q = Q + (size_t)w * d;
+    int ss = 0;
+    for (int j = lane; j < d; j += 32) {
+        const float v = (w < B) ? q[j] : 0.0f;
+        const size_t i = (size_t)w * d + j;
+        if (dtype == 0) reinterpret_cast<float*>(out)[i] = v;
+        else if (dtype == 1) reinterpret_cast<uint16_t*>(out)[i] = __half_as_ushort(__float2half_rn(v));
+        else if (dtype == 2) reinterpret_cast<uint16_t*>(out)[i] = __bfloat16_as_ushort(__float2bfloat16_rn(v));
+        else {
+            const int iv = max(-128, min(127, __float2int_rn(v)));
+            reinterpret_cast<int8_t*>(out)[i] = (int8_t)iv;
+            ss += iv * iv;
+        }
+    }
+    if (dtype == 3 && qinv != nullptr) {
+#pragma unroll
+        for (int off = 16; off >= 1; off >>= 1) ss += __shfl_xor_sync(0xFFFFFFFFu, ss, off);
+        if (lane == 0 && w < B) qinv[w] = ss > 0 ? (float)(1.0 / sqrt((double)ss)) : 0.0f;
+    }
 }
 
-cudaError_t round_queries(const float* Q, int B, int d, int dtype, float* Qs, void* Q16, int Bpad,
-                          cudaStream_t st) {
-    size_t total = (size_t)Bpad * d;
-    int blocks = (int)((total + 255) / 256);
-    round_queries_kernel<<<blocks, 256, 0, st>>>(Q, B, d, dtype, Qs, reinterpret_cast<uint16_t*>(Q16), Bpad);
+cudaError_t scan_queries(const float* Q, int B, int d, int dtype, void* out, int Bpad, float* qinv, cudaStream_t st) {
+    const int blocks = (Bpad * 32 + 255) / 256;
+    scan_queries_kernel<<<blocks, 256, 0, st>>>(Q, B, d, dtype, out, Bpad, qinv);
+    return cudaGetLastError();
+}
+
+// int8 spaces: inverse norm of every stored row, and the largest of them (positive floats order like their bits)
+__global__ void i8_row_inv_norms_kernel(const int8_t* __restrict__ X, int64_t n, int d, float* __restrict__ xinv,
+                                        uint32_t* __restrict__ max_bits) {
+    const int64_t w = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (w >= n) return;
+    const uint4* row = reinterpret_cast<const uint4*>(X + (size_t)w * d);
+    int ss = 0;
+    for (int c = lane; c < d / 16; c += 32) {
+        const uint4 v = __ldg(row + c);
+        ss = __dp4a((int)v.x, (int)v.x, ss); ss = __dp4a((int)v.y, (int)v.y, ss);
+        ss = __dp4a((int)v.z, (int)v.z, ss); ss = __dp4a((int)v.w, (int)v.w, ss);
+    }
+#pragma unroll
+    for (int off = 16; off >= 1; off >>= 1) ss += __shfl_xor_sync(0xFFFFFFFFu, ss, off);
+    if (lane == 0) {
+        const float inv = ss > 0 ? (float)(1.0 / sqrt((double)ss)) : 0.0f;
+        xinv[w] = inv;
+        atomicMax(max_bits, __float_as_uint(inv));
+    }
+}
+
+cudaError_t i8_row_inv_norms(const void* X, int64_t n, int d, float* xinv, uint32_t* max_bits, cudaStream_t st) {
+    if (n <= 0) return cudaSuccess;
+    const int blocks = (int)((n * 32 + 255) / 256);
+    i8_row_inv_norms_kernel<<<blocks, 256, 0, st>>>(reinterpret_cast<const int8_t*>(X), n, d, xinv, max_bits);
     return cudaGetLastError();
 }
 
@@ -149,11 +192,45 @@ __device__ __forceinline__ double row_dot_f64(const uint4* __restrict__ X, int64
     return acc;
 }
 
+// int8 rows (cosine of integer vectors): exact integer dot and squared norms, then ONE float64 expression
+// idot / (sqrt(ssx) * sqrt(ssq)) -- every operation correctly rounded, so the oracle's numpy float64 line gives the
+// same bits.  A zero row or query scores 0.
+__device__ __forceinline__ double row_dot_i8(const uint4* __restrict__ X, int64_t row, int d,
+                                             const float* __restrict__ q, int lane) {
+    const int C = d / 16;
+    int dot = 0, ssx = 0, ssq = 0;
+    for (int c = lane; c < C; c += 32) {
+        const uint4 v = __ldg(X + (size_t)row * C + c);
+        const uint32_t w4[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            uint32_t qp = 0;
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                const int qi = max(-128, min(127, __float2int_rn(q[c * 16 + j * 4 + e])));
+                qp |= ((uint32_t)qi & 0xFFu) << (8 * e);
+            }
+            dot = __dp4a((int)w4[j], (int)qp, dot);
+            ssx = __dp4a((int)w4[j], (int)w4[j], ssx);
+            ssq = __dp4a((int)qp, (int)qp, ssq);
+        }
+    }
+#pragma unroll
+    for (int off = 16; off >= 1; off >>= 1) {
+        dot += __shfl_xor_sync(0xFFFFFFFFu, dot, off);
+        ssx += __shfl_xor_sync(0xFFFFFFFFu, ssx, off);
+        ssq += __shfl_xor_sync(0xFFFFFFFFu, ssq, off);
+    }
+    if (ssx == 0 || ssq == 0) return 0.0;
+    return (double)dot / (sqrt((double)ssx) * sqrt((double)ssq));
+}
+
 __device__ __forceinline__ double row_dot_any(const void* X, int dtype, int64_t row, int d, const float* q,
                                               int lane) {
     const uint4* X4 = reinterpret_cast<const uint4*>(X);
     if (dtype == 0) return row_dot_f64<0>(X4, row, d, q, lane);
     if (dtype == 1) return row_dot_f64<1>(X4, row, d, q, lane);
+    if (dtype == 3) return row_dot_i8(X4, row, d, q, lane);
     return row_dot_f64<2>(X4, row, d, q, lane);
 }
 

@@ -13,14 +13,20 @@ import numpy as np
 
 from . import _native
 
-DTYPES = {"f32": 0, "f16": 1, "bf16": 2}
+DTYPES = {"f32": 0, "f16": 1, "bf16": 2, "i8": 3}
 STAGES = ("dense_scan", "dense_select", "sparse_scan", "sparse_select", "rrf", "merge")
 TIE_ID, TIE_FIRST_SEEN = 0, 1
 
 
 def to_storage(x: np.ndarray, dtype: str) -> np.ndarray:
-    """float32 rows -> storage bits (f32: float32, f16: float16, bf16: uint16 RNE bits)."""
+    """float32 rows -> storage bits (f32: float32, f16: float16, bf16: uint16 RNE bits, i8: int8 -- the rows of an
+    int8 space are the integer values themselves, e.g. the reference's `quantized` vector, qdrant_handler.py:144-146)."""
     x = np.ascontiguousarray(x, dtype=np.float32)
+    if dtype == "i8":
+        r = np.rint(x)
+        if not (np.array_equal(r, x) and r.min(initial=0) >= -128 and r.max(initial=0) <= 127):
+            raise ValueError("int8 storage takes integer values in [-128, 127]")
+        return r.astype(np.int8)
     if dtype == "f32":
         return x
     if dtype == "f16":
@@ -79,7 +85,7 @@ class Engine:
         already in the storage dtype (float32 / float16 / bfloat16)."""
         if _is_torch_cuda(rows):
             import torch
-            tmap = {torch.float32: "f32", torch.float16: "f16", torch.bfloat16: "bf16"}
+            tmap = {torch.float32: "f32", torch.float16: "f16", torch.bfloat16: "bf16", torch.int8: "i8"}
             dtype = tmap[rows.dtype]
             rows = rows.contiguous()
             n, d = rows.shape

@@ -122,7 +122,7 @@ class OracleEngine:
         q = _np(Q).astype(np.float32)      # the query stays float32 (oracle.prep_query)
         out = []
         for b in range(q.shape[0]):
-            s, i = O.dense_topk(x, q[b], k, mask=self._mask(mask_id, x.shape[0]))
+            s, i = O.dense_topk(x, q[b], k, mask=self._mask(mask_id, x.shape[0]), int8=self.dtype[name] == "i8")
             out.append((s, i + self.id_offset))
         return self._wrap(Q, *self._pad(out, k))
 
@@ -135,7 +135,7 @@ class OracleEngine:
         for b in range(q.shape[0]):
             cb = cand[b][cand[b] >= 0] - self.id_offset
             cb = cb[(cb >= 0) & (cb < x.shape[0])]
-            s, i = O.dense_topk(x, q[b], k, mask=self._mask(mask_id, x.shape[0]), cand=cb)
+            s, i = O.dense_topk(x, q[b], k, mask=self._mask(mask_id, x.shape[0]), cand=cb, int8=self.dtype[name] == "i8")
             out.append((s, i + self.id_offset))
         return self._wrap(Q, *self._pad(out, k))
 
