@@ -318,6 +318,7 @@ bm25x_scan_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict_
 
     if (warp == nw) {
         // ===== bound manager (last warp): queries blockIdx.x, blockIdx.x + gridDim.x, ...
+        if (seed_mode) return;                             // a seed launch publishes its bounds itself
         while (true) {
             const int done = *reinterpret_cast<volatile int*>(&s_done);
             for (int q = (int)blockIdx.x; q < B; q += (int)gridDim.x) {
@@ -345,12 +346,16 @@ bm25x_scan_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict_
     const int ns = (int)((n_docs + BM25_SUB - 1) / BM25_SUB);
     const int ns1 = ns + 1;
     const int nt = (ns + SUBS - 1) / SUBS;                    // tiles of SUBS sub-tiles
-    // Seed launch (seed_mode): work item = seed_qpi queries, warp w scans the first seed_tiles tiles for query
-    // item * seed_qpi + w and writes list number splits * nw.  Main launch: tiles [seed_tiles, nt) in `splits` ranges,
-    // work item = (range, query, slot w) claimed by one warp, which takes every nw-th tile of the range starting at the
-    // w-th and writes list range * nw + w.  The seed's bound
-    // (k-th best of its few thousand documents) keeps the main launch's first visits from scoring every document.
-    const int nt_per_split = (nt - seed_tiles + splits - 1) / splits;
+    // Seed launch (seed_mode): a SAMPLE that only produces a starting bound.  Work item = seed_qpi queries; warp w
+    // visits seed_tiles tiles spread over the corpus for query item * seed_qpi + w and, in each, scores just the
+    // ~k_sel documents with the highest (terms present + terms in their high class) count -- the likely best of the
+    // tile.  The k_sel-th best score it found is a valid lower bound of the query's k_sel-th best overall (those
+    // documents exist), published straight into gthr; no list is written and no histogram is touched, because the
+    // main launch scans every tile, the sampled ones included.  Main launch: tiles [0, nt) in `splits` ranges, work
+    // item = (range, query, slot w) claimed by one warp, which takes every nw-th tile of the range starting at the
+    // w-th and writes list range * nw + w.  The seed's bound keeps the main launch's first visits from scoring every
+    // document that shares a term with the query.
+    const int nt_per_split = (nt + splits - 1) / splits;
     const size_t row_words = (size_t)((ns + 3) / 4 * 4) * BX_WORDS;
     const int n_items = seed_mode ? (B + seed_qpi - 1) / seed_qpi : splits * B;
     const double sentinel = __longlong_as_double((long long)BX_SENTINEL);
@@ -378,13 +383,15 @@ bm25x_scan_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict_
         int q, j_first, j_end, j_stride, slot;
         if (seed_mode) {
             q = item * seed_qpi + warp;
-            j_first = 0; j_stride = 1; slot = splits * nw;
-            j_end = (warp < seed_qpi && q < B) ? min(seed_tiles, nt) : 0;
+            // sampled tiles: seed_tiles of them, evenly spaced, shifted per query so a batch does not pile on one tile
+            j_stride = max(1, nt / seed_tiles);
+            j_first = (q * 7) % j_stride; slot = 0;
+            j_end = (warp < seed_qpi && q < B) ? min(nt, j_first + seed_tiles * j_stride) : 0;
             if (j_end == 0) continue;                      // idle warp of a seed item (no CTA-wide sync below)
         } else {
             const int split = item / B;
             q = item - split * B;
-            const int j_begin = seed_tiles + split * nt_per_split;
+            const int j_begin = split * nt_per_split;
             j_first = j_begin + wslot; j_stride = nw; slot = split * nw + wslot;
             j_end = min(nt, j_begin + nt_per_split);
         }
@@ -472,7 +479,7 @@ bm25x_scan_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict_
                     const uint64_t key = make_key((float)acc, pdg);
                     if (key > thr && (uint32_t)(key >> 32) >= g_now) {
                         list[atomicAdd(cntp, 1)] = key;
-                        hist_count(coarse, fine, q, (uint32_t)(key >> 32));
+                        if (!seed_mode) hist_count(coarse, fine, q, (uint32_t)(key >> 32));
                     }
                 }
                 phit = 0u;
@@ -589,28 +596,43 @@ bm25x_scan_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict_
                     for (int p = 2; p < PLANES; ++p) { const uint32_t t_ = cn[p][w] & k; cn[p][w] ^= k; k = t_; }
                 }
             }
-            // count >= m, bit-slice compare from the top plane down; then the payload filter
-            uint32_t cand[WPL];
-            int own_c = 0;
+            // count >= m, bit-slice compare from the top plane down, under the payload filter
+            uint32_t keep[WPL];
 #pragma unroll
-            for (int w = 0; w < WPL; ++w) {
-                uint32_t gt = 0u, eq = 0xFFFFFFFFu;
-#pragma unroll
-                for (int p = PLANES - 1; p >= 0; --p) {
-                    if ((m >> p) & 1) eq &= cn[p][w];
-                    else { gt |= eq & cn[p][w]; eq &= ~cn[p][w]; }
-                }
-                cand[w] = (m >> PLANES) ? 0u : (gt | eq);
-            }
+            for (int w = 0; w < WPL; ++w) keep[w] = 0xFFFFFFFFu;
             if (mask != nullptr) {
 #pragma unroll
                 for (int w = 0; w < WPL; w += 2) {
                     const uint2 mw = __ldg(reinterpret_cast<const uint2*>(mask + (tile_base >> 5) + WPL * lane + w));
-                    cand[w] &= mw.x; cand[w + 1] &= mw.y;
+                    keep[w] = mw.x; keep[w + 1] = mw.y;
                 }
             }
+            uint32_t cand[WPL];
+            auto count_ge = [&](int mm) {
+                int c = 0;
 #pragma unroll
-            for (int w = 0; w < WPL; ++w) own_c += __popc(cand[w]);
+                for (int w = 0; w < WPL; ++w) {
+                    uint32_t gt = 0u, eq = 0xFFFFFFFFu;
+#pragma unroll
+                    for (int p = PLANES - 1; p >= 0; --p) {
+                        if ((mm >> p) & 1) eq &= cn[p][w];
+                        else { gt |= eq & cn[p][w]; eq &= ~cn[p][w]; }
+                    }
+                    cand[w] = ((mm >> PLANES) ? 0u : (gt | eq)) & keep[w];
+                    c += __popc(cand[w]);
+                }
+                return c;
+            };
+            int own_c = count_ge(m);
+            if (seed_mode && __reduce_add_sync(0xFFFFFFFFu, own_c) > k_sel) {
+                // sample: the largest count threshold that still leaves k_sel documents of this tile
+                int lo = m, hi = 2 * nq;
+                while (lo < hi) {
+                    const int mid = (lo + hi + 1) >> 1;
+                    if (__reduce_add_sync(0xFFFFFFFFu, count_ge(mid)) >= k_sel) lo = mid; else hi = mid - 1;
+                }
+                own_c = count_ge(lo);
+            }
 
             // ---- phase 3: score the survivors, 32 at a time (compacted through clist so every lane has one)
             int pos = own_c;                                  // -> exclusive prefix of own_c
@@ -718,6 +740,10 @@ bm25x_scan_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict_
         if (*cntp > lcap - 32) warp_compact(list, cntp, lcap, k_sel, thr, lane);
         flush_pending(fmax(pre_local, pre_g), g_seen);
         warp_compact(list, cntp, lcap, k_sel, thr, lane);
+        if (seed_mode) {
+            publish_bound(gthr, q, (uint32_t)(thr >> 32), xb, lane);   // thr: the k_sel-th best key, 0 if fewer were found
+            continue;
+        }
         uint64_t* out = part + ((size_t)slot * B + q) * k_sel;
         for (int i = lane; i < k_sel; i += 32) out[i] = list[i];
         __syncwarp();
@@ -762,12 +788,11 @@ Bm25Plan bm25x_plan(int64_t n_docs, int B, int k_sel, int max_terms, int num_sms
     static const int wcap = [] { const char* e = getenv("BRAG_BX_WORKERS"); return e ? atoi(e) : 0; }();
     if (wcap > 0) p.workers = std::min(p.workers, wcap);
     const int resident = num_sms;
-    // seed launch: BRAG_BX_SEED tiles per query (default 2; measured at C4 / a 1.25 M-document shard: 8.6 / 2.48 ms
-    // without, 8.0 / 1.88 ms with), when the corpus has tiles to spare
+    // seed launch: BRAG_BX_SEED sampled tiles per query (default 2), when the corpus has tiles to spare
     static const int seed_cfg = [] { const char* e = getenv("BRAG_BX_SEED"); const int v = e ? atoi(e) : 2; return v < 0 ? 0 : (v > 4 ? 4 : v); }();
     p.seed_tiles = (nt >= 32) ? seed_cfg : 0;
     p.seed_qpi = std::max(1, std::min(p.workers, (B + resident - 1) / resident));
-    const int nt_main = nt - p.seed_tiles;
+    const int nt_main = nt;
     // ranges per query: enough items to keep every SM busy ~8 times over (BRAG_BX_ITEMS_PER_SM overrides; tuning knob)
     static const int items_per_sm = [] { const char* e = getenv("BRAG_BX_ITEMS_PER_SM"); const int v = e ? atoi(e) : 8; return v < 1 ? 1 : (v > 64 ? 64 : v); }();
     int splits = (resident * items_per_sm + B - 1) / B;
@@ -777,7 +802,7 @@ Bm25Plan bm25x_plan(int64_t n_docs, int B, int k_sel, int max_terms, int num_sms
     if (splits > resident) splits = resident;     // batch 1: one split per SM
     p.splits = splits;
     p.visits_per_list = nt_main / (splits * p.workers);
-    p.lists_per_query = splits * p.workers + (p.seed_tiles ? 1 : 0);
+    p.lists_per_query = splits * p.workers;
     int64_t items = (int64_t)splits * B;
     p.grid = (int)(items < resident ? items : resident);
     auto up = [](size_t x) { return (x + 255) & ~(size_t)255; };

@@ -13,6 +13,27 @@ def test_reference_flow_on_oracle_engine():
     run_reference_flow(engine_factory=OracleEngine)
 
 
+def test_reference_flow_with_the_quantized_space_stored_as_int8():
+    """storage_overrides={"quantized": "i8"}: the reference's int8 vector kept as int8 rows; same golden
+    answers, and what cannot be held as int8 is refused."""
+    run_reference_flow(engine_factory=OracleEngine, storage_overrides={"quantized": "i8"})
+    core = B200QdrantCore(engine_factory=OracleEngine, storage_overrides={"q8": "i8", "bad": "i8"})
+    with pytest.raises(ValueError):
+        core.create_collection("c", vectors_config={"bad": M.VectorParams(size=96, distance=M.Distance.COSINE)})
+    with pytest.raises(ValueError):
+        core.create_collection("c", vectors_config={"q8": M.VectorParams(size=128, distance=M.Distance.DOT)})
+    core.create_collection("c", vectors_config={"q8": M.VectorParams(size=128, distance=M.Distance.COSINE)})
+    core.upsert("c", points=[M.PointStruct(id=1, vector={"q8": [0.5] * 128}, payload={})])
+    with pytest.raises(ValueError):
+        core.query_points("c", query=[1.0] * 128, using="q8", limit=1)          # rows are not integer-valued
+    core.upsert("c", points=[M.PointStruct(id=1, vector={"q8": [3.0] * 128}, payload={}),
+                             M.PointStruct(id=2, vector={"q8": [-3.0] * 128}, payload={})])
+    with pytest.raises(ValueError):
+        core.query_points("c", query=[0.25] * 128, using="q8", limit=1)         # nor may the query be fractional
+    res = core.query_points("c", query=[7.0] * 128, using="q8", limit=2)
+    assert [(p.id, p.score) for p in res.points] == [(1, 1.0), (2, -1.0)]
+
+
 def test_incremental_upsert_on_oracle_engine():
     run_incremental_upsert(engine_factory=OracleEngine)
 

@@ -11,6 +11,11 @@ def test_reference_flow_on_b200():
     run_reference_flow(engine_factory=None)
 
 
+def test_reference_flow_with_the_quantized_space_stored_as_int8_on_b200():
+    """SURVEY 8 a9: Q1 of the reference's tree runs on int8 rows through the kind::i8 scan."""
+    run_reference_flow(engine_factory=None, storage_overrides={"quantized": "i8"})
+
+
 def test_limits_above_the_engine_list_length_on_b200():
     from _client_cases import run_long_limits
     run_long_limits()

@@ -74,6 +74,107 @@ def test_dense_tcgen05(engine, dtype, n, d, B):
         check_dense(xs, q[b], k, s[b], i[b], int(c[b]))
 
 
+@pytest.mark.parametrize("n,d", [(300, 64), (20000, 384), (9000, 1024), (70000, 96)])
+@pytest.mark.parametrize("B", [1, 16, 200])
+def test_dense_tcgen05_tf32_on_float32_storage(engine, n, d, B):
+    """float32 spaces (the reference's own datatype, qdrant_handler.py:57-79) are scanned by the same kernel with
+    kind::tf32 (rows a whole number of 32-element K slices); candidates are re-scored exactly as before, so the
+    answer equals the GEMV path's and the oracle's."""
+    x = synth.dense_corpus(n, d, seed=5 + n, clustered=True)
+    q = synth.dense_queries(x, B, seed=9)
+    engine.dense_set("t", x, "f32")
+    assert engine.dense_path("t", B) == "tcgen05"
+    k = 100
+    s, i, c = engine.dense_topk("t", q, k)
+    engine.force_dense_path("gemv")
+    s0, i0, c0 = engine.dense_topk("t", q, k)
+    engine.force_dense_path(None)
+    assert np.array_equal(i, i0) and np.array_equal(c, c0) and np.array_equal(s.view(np.uint32), s0.view(np.uint32))
+    for b in range(0, B, max(1, B // 16)):
+        check_dense(x, q[b], k, s[b], i[b], int(c[b]))
+
+
+def _int8_rows(n, d, seed, B=0):
+    """Unit-norm float rows quantised the way the reference does (qdrant_handler.py:144-146), as float32 arrays."""
+    x = O.normalize_rows(synth.dense_corpus(n, d, seed=seed, clustered=True))
+    xi = O.quantize_int8(x).astype(np.float32)
+    if not B:
+        return xi
+    q = O.normalize_rows(synth.dense_queries(x, B, seed=seed + 1))
+    return xi, O.quantize_int8(q).astype(np.float32)
+
+
+def check_int8(xi, qi, k, s, i, c, mask=None, id_offset=0):
+    """int8 spaces are integer work: ids, counts AND score bits equal the oracle's (exact int dot, one float64
+    normalisation)."""
+    es, ei = O.dense_topk(xi, qi, k, mask=mask, int8=True)
+    assert int(c) == len(ei)
+    assert np.array_equal(i[:len(ei)] - id_offset, ei), (i[:len(ei)][:8], ei[:8])
+    assert np.array_equal(s[:len(ei)].view(np.uint32), es.view(np.uint32))
+    assert np.all(i[len(ei):] == -1)
+
+
+@pytest.mark.parametrize("n,d", [(300, 128), (20000, 768), (9000, 1024), (160_000, 128)])
+@pytest.mark.parametrize("B", [1, 16, 200])
+def test_dense_int8_space_bit_exact(engine, n, d, B):
+    """SURVEY 8 a9: the `quantized` space held as int8 rows and scanned with tcgen05 kind::i8 (exact int32 dots)."""
+    xi, qi = _int8_rows(n, d, 100 + n, B)
+    engine.dense_set("q8", xi, "i8")
+    assert engine.dense_path("q8", B) == "tcgen05"
+    for k in (10, 100):
+        s, i, c = engine.dense_topk("q8", qi, k)
+        for b in range(0, B, max(1, B // 16)):
+            check_int8(xi, qi[b], k, s[b], i[b], c[b])
+
+
+def test_dense_int8_mask_offset_append_update_rescore(engine):
+    n, d, B, k = 30000, 256, 40, 60
+    xi, qi = _int8_rows(n, d, 300, B)
+    engine.dense_set("q8", xi[:20000], "i8")
+    engine.dense_append("q8", xi[20000:])
+    xi[[3, 777, 25000]] = xi[[9, 9, 9]]                     # overwritten rows tie exactly: lower id first
+    engine.dense_update("q8", [3, 777, 25000], xi[[3, 777, 25000]])
+    engine.set_id_offset(5_000_000)
+    try:
+        for sel in (1.0, 0.3, 0.01):                        # unfiltered, compacted copy, masked scan
+            mask = None if sel == 1.0 else synth.random_mask(n, sel, seed=7)
+            if mask is not None:
+                engine.mask_set(6, mask)
+            s, i, c = engine.dense_topk("q8", qi, k, mask_id=0 if mask is None else 6)
+            for b in range(0, B, 5):
+                check_int8(xi, qi[b], k, s[b], i[b], c[b], mask=mask, id_offset=5_000_000)
+        s, i, c = engine.dense_topk("q8", xi[9:10], 4)
+        assert (i[0] - 5_000_000).tolist() == [3, 9, 777, 25000] and np.all(s[0] == np.float32(1.0))
+    finally:
+        engine.set_id_offset(0)
+    rng = np.random.default_rng(1)
+    cand = rng.integers(0, n, size=(B, 70)).astype(np.int64)
+    cand[:, 60:] = -1
+    s, i, c = engine.dense_rescore("q8", qi, cand, 30)
+    for b in range(0, B, 7):
+        es, ei = O.dense_topk(xi, qi[b], 30, cand=cand[b][cand[b] >= 0], int8=True)
+        assert int(c[b]) == len(ei) and np.array_equal(i[b][:len(ei)], ei)
+        assert np.array_equal(s[b][:len(ei)].view(np.uint32), es.view(np.uint32))
+    # a zero row and a zero query score 0, never NaN
+    z = xi[:256].copy()
+    z[5] = 0
+    engine.dense_set("z8", z, "i8")
+    s, i, c = engine.dense_topk("z8", np.zeros((1, d), np.float32), 3)
+    assert int(c[0]) == 3 and i[0].tolist() == [0, 1, 2] and np.all(s[0] == 0)
+    s, i, c = engine.dense_topk("z8", qi[:1], 256)
+    assert int(c[0]) == 256 and np.isfinite(s[0]).all() and s[0][list(i[0]).index(5)] == 0
+
+
+def test_dense_int8_rejects_what_it_cannot_hold(engine):
+    with pytest.raises(ValueError):
+        engine.dense_set("bad", np.full((4, 128), 0.5, np.float32), "i8")       # not integer-valued
+    with pytest.raises(Exception):
+        engine.dense_set("bad", np.zeros((4, 96), np.float32), "i8")            # rows not a multiple of 128
+    engine.dense_set("ok", _int8_rows(600, 128, 1), "i8")
+    with pytest.raises(Exception):
+        engine.dense_topk("ok", np.ones((1, 128), np.float32), 500)               # k > 416 on an int8 space
+
+
 @pytest.mark.parametrize("masked", [False, True])
 def test_dense_tcgen05_seeded_two_phase(engine, masked):
     """Corpora of >= 4*148 tiles take the two-phase scan (seeding scan -> per-query bound -> main scan)."""

@@ -105,6 +105,33 @@ def test_quantize_trunc(kat):
     assert O.quantize_int8([0.999, -0.5, 1.0]).tolist() == [126, -63, 127]
 
 
+def test_int8_cosine_by_hand_and_against_the_float_space(kat):
+    """int8 STORAGE of the `quantized` space (BRAG_I8): hand-computed cosines, zero vectors, and how far the scores are
+    from the same values held in a float32 COSINE space (float32 rounding of the norms only); Q1 of the reference tree
+    is the same ranked list either way."""
+    x = np.zeros((4, 8), np.float32)
+    x[0, :2] = [3, 4]
+    x[1, :2] = [4, 3]
+    x[2, :3] = [-3, -4, 12]
+    q = np.zeros(8, np.float32)
+    q[:2] = [4, 3]
+    s = O.int8_cosine_scores(x, q)
+    assert s.tolist() == [np.float32(24 / 25), np.float32(1.0), np.float32(-24 / 65), 0.0]
+    assert O.int8_cosine_scores(x, np.zeros(8, np.float32)).tolist() == [0.0] * 4
+    es, ei = O.dense_topk(x, q, 3, int8=True)
+    assert ei.tolist() == [1, 0, 3] and es.tolist() == [np.float32(1.0), np.float32(0.96), 0.0]
+    c = kat["tree"]
+    xt, qt = _tree_inputs(c)
+    xi = np.stack([O.quantize_int8(r) for r in xt]).astype(np.float32)
+    qi = O.quantize_int8(qt).astype(np.float32)
+    f32_space = O.dense_scores(O.normalize_rows(xi), O.normalize_rows(qi[None])[0])
+    i8_space = O.int8_cosine_scores(xi, qi)
+    assert np.abs(f32_space - i8_space).max() <= 3e-7
+    lim = c["search_params"]["quantized_limit"]
+    _, ids = O.dense_topk(xi, qi, lim, int8=True)
+    assert ids.tolist() == [r for _, r in c["stages"]["Q1"]]
+
+
 # ------------------------------------------------------------------ (4) the reference's prefetch tree
 def _tree_inputs(c):
     rng = np.random.Generator(np.random.PCG64(c["seed"]))
