@@ -232,13 +232,23 @@ dense_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
     const int chunk = (int)blockIdx.x;
     // share > 1 (main launch only): `share` neighbouring CTAs scan the SAME rows, each against its own 1/share of the
     // query blocks, so the X tiles in flight at any moment are 148/share instead of 148 (they fit L2 and are read from
-    // HBM once).  Lists / counts stay per CTA; the query blocks a CTA never sees keep count 0.
+    // HBM once).  Lists / counts stay per CTA; the query blocks a CTA never sees keep count 0.  An odd number of query
+    // blocks under share = 2: the even part is dealt block by block, and the last block (qx) is split by ROWS instead
+    // -- the first CTA of the pair takes it for the first half of the tiles, the second for the rest -- so both do
+    // the same work and every X tile is still fetched by both at about the same time.
     const int sh = seeding ? 1 : share;
     const int part = (int)blockIdx.x % sh;
-    const int qb_lo = part * n_qblocks / sh, qb_hi = (part + 1) * n_qblocks / sh;
+    const bool odd = sh == 2 && (n_qblocks & 1);
+    const int n_even = odd ? n_qblocks - 1 : n_qblocks;
+    const int qb_lo = part * n_even / sh, qb_hi = (part + 1) * n_even / sh;
+    const int qx = n_qblocks - 1;
     const int64_t row_begin = (int64_t)((int)blockIdx.x / sh) * rows_per_chunk;
     const int64_t row_end = min(n, row_begin + (seeding ? (int64_t)UM_BN : rows_per_chunk));
     const int n_tiles = row_end > row_begin ? (int)((row_end - row_begin + UM_BN - 1) / UM_BN) : 0;
+    const int x_lo = odd ? (part == 0 ? 0 : (n_tiles + 1) / 2) : 0;          // tiles [x_lo, x_hi) also take block qx
+    const int x_hi = odd ? (part == 0 ? (n_tiles + 1) / 2 : n_tiles) : 0;
+    // the (tile, query block) units of this CTA, in the order all three roles walk them:
+    //   for t: blocks qb_lo .. qb_hi-1, then qx if x_lo <= t < x_hi
 
     if (warp == 0 && lane == 0) {
         for (int s = 0; s < UM_STAGES; ++s) { mbar_init(&S.full[s], 1); mbar_init(&S.empty[s], 1); }
@@ -263,7 +273,9 @@ dense_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
             uint32_t phase = 0;
             for (int t = 0; t < n_tiles; ++t) {
                 const int row0 = (int)(row_begin + (int64_t)t * UM_BN);
-                for (int qb = qb_lo; qb < qb_hi; ++qb) {
+                const int n_blk = qb_hi - qb_lo + ((t >= x_lo && t < x_hi) ? 1 : 0);
+                for (int iq = 0; iq < n_blk; ++iq) {
+                    const int qb = (iq < qb_hi - qb_lo) ? qb_lo + iq : qx;
                     for (int kb = 0; kb < n_kb; ++kb) {
                         mbar_wait(&S.empty[stage], phase ^ 1);
                         mbar_expect_tx(&S.full[stage], UM_A_BYTES + UM_B_BYTES);
@@ -271,7 +283,7 @@ dense_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
                         // query block has used it, then it should leave first
                         tma_load_2d(S.a[stage], &tmap_q, kb * KELEMS, (qb_base + qb) * UM_BM, &S.full[stage], L2_EVICT_LAST);
                         tma_load_2d(S.b[stage], &tmap_x, kb * KELEMS, row0, &S.full[stage],
-                                    (qb + 1 < qb_hi || sh > 1) ? L2_EVICT_NORMAL : L2_EVICT_FIRST);
+                                    (iq + 1 < n_blk || sh > 1) ? L2_EVICT_NORMAL : L2_EVICT_FIRST);
                         if (++stage == UM_STAGES) { stage = 0; phase ^= 1; }
                     }
                 }
@@ -282,7 +294,7 @@ dense_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
         if (lane == 0) {
             int stage = 0;
             uint32_t phase = 0;
-            const int n_units = n_tiles * (qb_hi - qb_lo);   // unit = (X tile, query block)
+            const int n_units = n_tiles * (qb_hi - qb_lo) + max(0, min(x_hi, n_tiles) - x_lo);   // unit = (X tile, query block)
             for (int u = 0; u < n_units; ++u) {
                 const int as = u & 1;
                 const uint32_t aphase = (uint32_t)(u >> 1) & 1;
@@ -329,7 +341,9 @@ dense_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
         int u = 0;
         for (int t = 0; t < n_tiles; ++t) {
             const int64_t row0 = row_begin + (int64_t)t * UM_BN;
-            for (int qb = qb_lo; qb < qb_hi; ++qb, ++u) {
+            const int n_blk = qb_hi - qb_lo + ((t >= x_lo && t < x_hi) ? 1 : 0);
+            for (int iq = 0; iq < n_blk; ++iq, ++u) {
+                const int qb = (iq < qb_hi - qb_lo) ? qb_lo + iq : qx;
                 const int as = u & 1;
                 const uint32_t aphase = (uint32_t)(u >> 1) & 1;
                 const int b = (qb_base + qb) * UM_BM + qidx;
@@ -746,7 +760,8 @@ cudaError_t dense_umma_scan(const void* X16, int dtype, int64_t n, int d, const 
             nl += 2;
         }
         // CTAs sharing a row range (see the kernel): only when the query blocks and the grid split evenly
-        const int share = (um_share() > 1 && nqb % um_share() == 0 && n_main % um_share() == 0 && n_tiles >= n_main) ? um_share() : 1;
+        const bool splits = nqb % um_share() == 0 || (um_share() == 2 && nqb >= 3);   // odd counts: the last block is split by rows
+        const int share = (um_share() > 1 && splits && n_main % um_share() == 0 && n_tiles >= n_main) ? um_share() : 1;
         const int64_t rows_per_chunk = (n_tiles + n_main / share - 1) / (n_main / share) * UM_BN;
         launch(n_main, qb0, nqb, nullptr, 0, rows_per_chunk, share, lists, counts, gthr, coarse, fine, xb);
         if ((err = cudaGetLastError()) != cudaSuccess) return err;

@@ -489,6 +489,7 @@ void dense_topk_dev(brag_engine* e, DenseSpace& s, const float* Q, int B, int k,
                     const ListSink* sink = nullptr) {
     const brag::ShardBounds xb = sink ? sink->xb : brag::ShardBounds();
     REQUIRE(B >= 1 && k >= 1 && k <= 512, "dense_topk: need B >= 1 and 1 <= k <= 512");
+    REQUIRE((reinterpret_cast<uintptr_t>(Q) & 15) == 0, "dense_topk: the query array must be 16-byte aligned");
     const int k_sel = k_select(k);
     int path = pick_path(e, s, B);
     if (path == 1 && k_sel > brag::dense_umma_max_ksel()) path = 0;     // k > 416: the GEMV scan holds longer lists
@@ -563,6 +564,7 @@ void dense_rescore_dev(brag_engine* e, DenseSpace& s, const float* Q, int B, con
                        const uint32_t* mask, float* out_scores, int64_t* out_ids, int32_t* out_counts,
                        cudaStream_t st) {
     REQUIRE(B >= 1 && k >= 1 && m >= 1 && m <= 8192 && k <= 8192, "dense_rescore: need m,k in [1,8192]");
+    REQUIRE((reinterpret_cast<uintptr_t>(Q) & 15) == 0, "dense_rescore: the query array must be 16-byte aligned");
     StageTimer t(e, 1, st);
     uint64_t* keys = e->keys1.as<uint64_t>((size_t)B * m);
     CK(brag::rescore_cands(s.x, s.dtype, s.n, s.d, Q, B, cand, m, e->id_offset, mask, keys, st));

@@ -175,17 +175,34 @@ __device__ __forceinline__ double row_dot_f64(const uint4* __restrict__ X, int64
                                               const float* __restrict__ q, int lane) {
     constexpr int EPC = (DT == 0) ? 4 : 8;
     const int C = d / EPC;
+    const uint4* rp = X + (size_t)row * C;
+    const float4* q4 = reinterpret_cast<const float4*>(q);      // d * 4 bytes is a multiple of 16 and so is every row of Q
     double acc = 0.0;
-    for (int c = lane; c < C; c += 32) {
-        uint4 v = __ldg(X + (size_t)row * C + c);
-        float f[8];
-        if constexpr (DT == 0) {
-            f[0] = __uint_as_float(v.x); f[1] = __uint_as_float(v.y); f[2] = __uint_as_float(v.z); f[3] = __uint_as_float(v.w);
-        } else {
-            Unpack<DT>::run(v, f);
-        }
+    // four 16-byte chunks of the row in flight per lane (a candidate row is a cold, random read); the sum still runs
+    // over this lane's chunks in ascending order
+    for (int c0 = lane; c0 < C; c0 += 128) {
+        uint4 v[4];
 #pragma unroll
-        for (int e = 0; e < EPC; ++e) acc += (double)f[e] * (double)q[c * EPC + e];
+        for (int u = 0; u < 4; ++u) v[u] = (c0 + 32 * u < C) ? __ldg(rp + c0 + 32 * u) : make_uint4(0u, 0u, 0u, 0u);
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int c = c0 + 32 * u;
+            if (c >= C) break;
+            float f[8];
+            if constexpr (DT == 0) {
+                f[0] = __uint_as_float(v[u].x); f[1] = __uint_as_float(v[u].y); f[2] = __uint_as_float(v[u].z); f[3] = __uint_as_float(v[u].w);
+                const float4 qa = __ldg(q4 + c);
+                acc += (double)f[0] * (double)qa.x; acc += (double)f[1] * (double)qa.y;
+                acc += (double)f[2] * (double)qa.z; acc += (double)f[3] * (double)qa.w;
+            } else {
+                Unpack<DT>::run(v[u], f);
+                const float4 qa = __ldg(q4 + 2 * c), qb = __ldg(q4 + 2 * c + 1);
+                acc += (double)f[0] * (double)qa.x; acc += (double)f[1] * (double)qa.y;
+                acc += (double)f[2] * (double)qa.z; acc += (double)f[3] * (double)qa.w;
+                acc += (double)f[4] * (double)qb.x; acc += (double)f[5] * (double)qb.y;
+                acc += (double)f[6] * (double)qb.z; acc += (double)f[7] * (double)qb.w;
+            }
+        }
     }
 #pragma unroll
     for (int off = 16; off >= 1; off >>= 1) acc += __shfl_xor_sync(0xFFFFFFFFu, acc, off);

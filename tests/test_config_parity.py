@@ -61,7 +61,7 @@ def test_c1_reference_cpu_config(engine):
     qp, qt, qv = synth.sparse_queries(ptr, doc, n, B, 8, "zipf", seed=synth.SEED_QUERY)
     engine.dense_set("c1d", x, "f32")
     engine.sparse_set_csr("c1s", ptr, doc, w, n)
-    assert engine.dense_path("c1d", B) == "gemv"                  # float32 storage
+    assert engine.dense_path("c1d", B) == "tcgen05"               # float32 storage: the kind::tf32 scan
     s, i, c = engine.hybrid_topk("c1d", "c1s", q, qp, qt, qv, k)
     ds, di, dc = engine.dense_topk("c1d", q, k)
     ss, si, sc = engine.sparse_topk("c1s", qp, qt, qv, k)

@@ -196,10 +196,11 @@ def test_dense_tcgen05_seeded_two_phase(engine, masked):
         check_dense(xs, q[b], k, s[b], i[b], int(c[b]), mask=mask)
 
 
-@pytest.mark.parametrize("n,B", [(50_001, 512), (38_000, 256), (160_000, 1024)])
+@pytest.mark.parametrize("n,B", [(50_001, 512), (38_000, 256), (160_000, 1024), (50_001, 384), (38_500, 600), (160_000, 896)])
 def test_dense_tcgen05_shared_row_ranges(engine, n, B):
-    """Even numbers of query blocks on corpora of >= 148 tiles: pairs of CTAs scan the same rows, each against half of
-    the query blocks (dense_umma.cu: share).  Ragged last chunk, payload filter, every query block checked."""
+    """Corpora of >= 148 tiles: pairs of CTAs scan the same rows, each against half of the query blocks
+    (dense_umma.cu: share); with an odd number of blocks (B = 384, 600, 896 -> 3, 5, 7 blocks)
+    the last block is split between the pair by rows.  Ragged last chunk, payload filter, every query block checked."""
     d, k = 64, 100
     x = synth.dense_corpus(n, d, seed=81, clustered=True)
     q = synth.dense_queries(x, B, seed=82)

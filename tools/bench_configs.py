@@ -145,6 +145,56 @@ if "--c5" in sys.argv:
         print(json.dumps(out, indent=1))
         sys.exit(0)
 
+# ---- the three full scans of the reference's tree at 1 M points (qdrant_handler.py:305-372): P1 = matryoshka_64
+#      (float32, kind::tf32), Q1 = `quantized` (int8 rows, kind::i8; and the float32 space it replaces), S1 = C3 below
+def leaf_scan(label, name, nbytes, flop_per_query, qs, tensor_scale=1.0):
+    for B in (1, 1024):
+        qb = qs[:B].contiguous()
+        p50, best = timeit(lambda: eng.dense_topk(name, qb, k))
+        scan = stage_ms(lambda: eng.dense_topk(name, qb, k), "dense_scan")
+        rec = {"call_p50_ms": p50, "scan_kernel_ms": scan, "path": eng.dense_path(name, B), "bytes": nbytes}
+        if B == 1:
+            rec.update(bound="hbm", achieved_gbs=nbytes / (scan * 1e-3) / 1e9, frac=nbytes / (scan * 1e-3) / 1e9 / peaks["hbm_gbs"])
+        else:
+            ach = flop_per_query * B / (scan * 1e-3) / 1e12
+            rec.update(bound="tensor", achieved_tops=ach, peak_note=f"measured sustained bf16 x {tensor_scale} (nominal ratio of this MMA kind)",
+                       frac_sustained=ach / (peaks["bf16_tflops_sustained"] * tensor_scale),
+                       hbm_gbs=nbytes / (scan * 1e-3) / 1e9)
+        out[f"{label}_B{B}"] = rec
+
+
+n1 = 1 << 20
+x = synth.dense_corpus_torch(n1, 768, torch.float32, dev)
+q = synth.dense_queries_torch(x, 1024)
+xm = x[:, :64].contiguous()
+xm = xm / xm.norm(dim=1, keepdim=True)
+eng.dense_set("p1", xm)
+qm = q[:, :64].contiguous()
+leaf_scan("P1_matryoshka64_1Mx64_f32_tf32", "p1", n1 * 64 * 4, 2.0 * n1 * 64, qm / qm.norm(dim=1, keepdim=True), tensor_scale=0.5)
+eng.dense_drop("p1")
+del xm
+xi = (x * 127).to(torch.int8)                       # truncation toward zero, like numpy's astype(int8)
+qi = (q * 127).to(torch.int8).to(torch.float32)
+eng.dense_set("q1", xi)
+leaf_scan("Q1_quantized_1Mx768_int8_i8", "q1", n1 * 768, 2.0 * n1 * 768, qi, tensor_scale=2.0)
+eng.dense_drop("q1")
+xf = xi.to(torch.float32)
+xf = xf / xf.norm(dim=1, keepdim=True)
+del xi
+qf = (qi / qi.norm(dim=1, keepdim=True)).contiguous()
+eng.dense_set("q1f", xf)
+leaf_scan("Q1_quantized_1Mx768_as_float32_tf32", "q1f", n1 * 768 * 4, 2.0 * n1 * 768, qf, tensor_scale=0.5)
+eng.force_dense_path("gemv")
+for B in (1, 8):
+    qb = qf[:B].contiguous()
+    scan = stage_ms(lambda: eng.dense_topk("q1f", qb, k), "dense_scan")
+    out[f"Q1_quantized_1Mx768_as_float32_gemv_B{B}"] = {"scan_kernel_ms": scan, "achieved_gbs": n1 * 768 * 4 / (scan * 1e-3) / 1e9,
+                                                       "frac": n1 * 768 * 4 / (scan * 1e-3) / 1e9 / peaks["hbm_gbs"]}
+eng.force_dense_path(None)
+eng.dense_drop("q1f")
+del x, xf, q, qi, qf
+torch.cuda.empty_cache()
+
 # ---- C3: BM25 top-100 over 1M docs, 50k-term Zipf vocab, 8-term queries, batch 1024
 nd, V = 1 << 20, 50000
 tp, doc, w = synth.zipf_corpus_torch(nd, V, 285, dev)
