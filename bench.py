@@ -37,7 +37,7 @@ def parse():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="c4", choices=["c4", "c5"],
                     help="c4 = BASELINE configs[3] (the metric's config, default); c5 = configs[4]: 100M x 384 f16 + 10%% filter")
-    ap.add_argument("--n", type=int, default=None, help="corpus rows / documents (whole job)")
+    ap.add_argument("--n", "--rows", dest="n", type=int, default=None, help="corpus rows / documents (whole job); --rows under torchrun, whose parser takes --n for itself")
     ap.add_argument("--d", type=int, default=None)
     ap.add_argument("--batch", type=int, default=None)
     ap.add_argument("--k", type=int, default=100)
@@ -534,7 +534,7 @@ def main():
         bm_ms = stage_ms["sparse_scan"] / max(1, stage_calls["sparse_scan"])
         bm_bytes = bm25_bytes * (sel_real if sel_real else 1.0)   # postings of the documents that pass the filter
         line = {
-            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "metric": METRIC if args.workload == "c4" else "hybrid top-100 QPS @100Mx384 batch 4096, 10% payload filter (BASELINE configs[4])", "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": args.dtype, "data": "synthetic", "config": config_dict(args, world),
             "e2e": e2e, "gpu_launches": int(launches), "clocks": clk, "parity": parity,

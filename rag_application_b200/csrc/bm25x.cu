@@ -739,13 +739,18 @@ bm25x_scan_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict_
         // ---- the last round's candidates, then emit this warp's list for (split, warp, q)
         if (*cntp > lcap - 32) warp_compact(list, cntp, lcap, k_sel, thr, lane);
         flush_pending(fmax(pre_local, pre_g), g_seen);
-        warp_compact(list, cntp, lcap, k_sel, thr, lane);
         if (seed_mode) {
+            warp_compact(list, cntp, lcap, k_sel, thr, lane);
             publish_bound(gthr, q, (uint32_t)(thr >> 32), xb, lane);   // thr: the k_sel-th best key, 0 if fewer were found
             continue;
         }
+        // the merge that follows sorts whatever it gathers, so a list of <= k_sel keys leaves unsorted (under a warm
+        // global bound an item keeps a dozen keys: the 256-key bitonic sort was most of an item's fixed cost)
+        __syncwarp();
+        if (*cntp > k_sel) warp_compact(list, cntp, lcap, k_sel, thr, lane);
+        const int n_keep = *cntp;
         uint64_t* out = part + ((size_t)slot * B + q) * k_sel;
-        for (int i = lane; i < k_sel; i += 32) out[i] = list[i];
+        for (int i = lane; i < k_sel; i += 32) out[i] = i < n_keep ? list[i] : 0ull;
         __syncwarp();
     }
     if (lane == 0) atomicAdd(&s_done, 1);             // the manager leaves once all nw worker warps are done

@@ -158,6 +158,22 @@ __device__ __forceinline__ void tmem_ld_wait(uint32_t (&v)[32]) {
 }
 
 // one column for every lane of the warp's TMEM quarter (warp-collective; used on the rare hit path)
+// v[i] for a run-time i without local memory: a 5-level tree of selects over statically indexed registers (31 SELs).
+// The hit path used to re-read the column from TMEM (tcgen05.ld is warp-collective, so every hit column cost the whole
+// warp a dependent TMEM round trip); now each lane pulls its own hits out of the registers it already holds.
+__device__ __forceinline__ uint32_t sel32(const uint32_t (&v)[32], int i) {
+    uint32_t a[16], b[8], c[4], d[2];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) a[j] = (i & 1) ? v[2 * j + 1] : v[2 * j];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) b[j] = (i & 2) ? a[2 * j + 1] : a[2 * j];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) c[j] = (i & 4) ? b[2 * j + 1] : b[2 * j];
+#pragma unroll
+    for (int j = 0; j < 2; ++j) d[j] = (i & 8) ? c[2 * j + 1] : c[2 * j];
+    return (i & 16) ? d[1] : d[0];
+}
+
 __device__ __forceinline__ uint32_t tmem_ld1(uint32_t taddr) {
     uint32_t r;
     asm volatile("tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];\n\ttcgen05.wait::ld.sync.aligned;"
@@ -423,21 +439,19 @@ dense_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
 #pragma unroll
                         for (int i = 0; i < 32; ++i) m |= ((int)v[i] > Ti) ? (1u << i) : 0u;
                         m &= cm;
-                        uint32_t mw = __reduce_or_sync(0xFFFFFFFFu, m);
-                        while (mw) {
-                            const int i = __ffs(mw) - 1;
-                            mw &= mw - 1;
-                            const int iv = (int)tmem_ld1(taddr + (uint32_t)(col0 + i));
-                            if ((m >> i) & 1u) {
-                                const float s = (float)iv * __ldg(xinv + r0 + i) * my_qinv;   // same two roundings as the seeding pass
-                                if (s > eff) {
-                                    const uint64_t key = make_key(s, (uint32_t)(r0 + i));
-                                    __stcg(my_list + cnt, key);
-                                    ++cnt;
-                                    hist_count(coarse, fine, b, (uint32_t)(key >> 32));
-                                }
+                        while (m) {                                    // this lane's own hits (rare, lanes diverge)
+                            const int i = __ffs(m) - 1;
+                            m &= m - 1;
+                            const int iv = (int)sel32(v, i);
+                            const float s = (float)iv * __ldg(xinv + r0 + i) * my_qinv;   // same two roundings as the seeding pass
+                            if (s > eff) {
+                                const uint64_t key = make_key(s, (uint32_t)(r0 + i));
+                                __stcg(my_list + cnt, key);
+                                ++cnt;
+                                hist_count(coarse, fine, b, (uint32_t)(key >> 32));
                             }
                         }
+                        __syncwarp();
                         return;
                     }
                     // rows of this 32-column group that exist and pass the payload filter (tiles start on
@@ -466,18 +480,15 @@ dense_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
 #pragma unroll
                     for (int i = 0; i < 32; ++i) m |= (__uint_as_float(v[i]) > eff) ? (1u << i) : 0u;
                     m &= cm;
-                    uint32_t mw = __reduce_or_sync(0xFFFFFFFFu, m);
-                    while (mw) {                                   // rare: columns where some query has a hit
-                        const int i = __ffs(mw) - 1;
-                        mw &= mw - 1;
-                        const float s = __uint_as_float(tmem_ld1(taddr + (uint32_t)(col0 + i)));
-                        if ((m >> i) & 1u) {
-                            const uint64_t key = make_key(s, (uint32_t)(r0 + i));
-                            __stcg(my_list + cnt, key);
-                            ++cnt;
-                            hist_count(coarse, fine, b, (uint32_t)(key >> 32));
-                        }
+                    while (m) {                                    // this lane's own hits (rare, lanes diverge)
+                        const int i = __ffs(m) - 1;
+                        m &= m - 1;
+                        const uint64_t key = make_key(__uint_as_float(sel32(v, i)), (uint32_t)(r0 + i));
+                        __stcg(my_list + cnt, key);
+                        ++cnt;
+                        hist_count(coarse, fine, b, (uint32_t)(key >> 32));
                     }
+                    __syncwarp();
                 };
                 uint32_t va[32], vb[32];
                 tmem_ld32_issue(taddr, va);
