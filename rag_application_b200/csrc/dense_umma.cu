@@ -27,6 +27,7 @@
 
 #include "common.cuh"
 #include "kernels.h"
+#include "rescore.cuh"
 
 namespace brag {
 
@@ -539,15 +540,6 @@ dense_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
     }
 }
 
-// Publishes every query's bound from its histograms (one warp per query): run after the seed launch so that the
-// main launch starts with the seed rows' k_sel-th best score instead of flooding its first tile into the lists.
-__global__ void um_bound_kernel(const uint32_t* __restrict__ coarse, const uint32_t* __restrict__ fine,
-                                uint32_t* __restrict__ gthr, int q_lo, int q_hi, int k_sel, const ShardBounds xb) {
-    const int q = q_lo + (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5);
-    if (q >= q_hi) return;
-    publish_bound(gthr, q, hist_bound(coarse, fine, q, (uint32_t)k_sel, (int)(threadIdx.x & 31)), xb, (int)(threadIdx.x & 31));
-}
-
 // Seed bound: per query, the k_sel-th largest of the seed_tiles * 4 per-tile best scores.  They are scores of
 // distinct rows, so at least k_sel rows reach that value: a valid starting bound for the main launch, about the
 // k_sel-th best of seed_tiles * 256 rows.  One CTA per query, bitonic sort of <= 1024 values in shared memory.
@@ -568,53 +560,155 @@ um_seed_bound_kernel(const float4* __restrict__ seedv, int seed_tiles, int q_lo,
     }
 }
 
-// ------------------------------------------------------------------ final per-query selection
-// Gathers, from the n_chunks unsorted (CTA, query) lists, the candidates that reach the query's
-// final bound (at least k_sel of them do), sorts them and writes the best k_sel keys.
-constexpr int SELK_THREADS = 256;
+// ------------------------------------------------------------------ tail of the scan, one CTA per query
+// One launch where there were four (bound, selection, re-score, finalize):
+//   1. the bound of the query's complete histograms (a CTA's manager stops with its own CTA, so the bound it left may
+//      predate the last pushes of the others) -- published like every bound, also to the peers of a sharded call;
+//   2. the candidates of the n_chunks unsorted (CTA, query) lists that reach it (at least k_sel of them do on a single
+//      GPU), sorted, the best k_sel kept;
+//   3. those re-scored exactly: float64 dot of the stored row with the caller's float32 query (rescore.cuh), one warp
+//      per candidate;
+//   4. either the re-scored keys (local rows) to keys_out [B][k_sel] -- sharded calls and filter-compacted copies go
+//      on from there -- or, when keys_out is NULL, the final list itself: sorted, unpacked, ids offset, count.
+constexpr int SELK_MAX_THREADS = 1024;   // launched with 512 threads, 1024 for batches of <= 64 queries (the re-score is
+                                         // one warp per candidate: a small batch has no other CTAs to hide its latency)
 constexpr int SELK_CAP = 8192;     // 64 KB of keys; 8 lists (<= 8 * UM_CAP entries) are added per round
+constexpr int SELK_RES = 512;      // re-scored keys (k_sel <= 512)
+constexpr int SELK_MAXCHUNKS = 256;
+constexpr int SELK_RANK_MAX = 1024;   // gathered keys up to which the selection ranks instead of sorting
 
-__global__ void __launch_bounds__(SELK_THREADS)
-dense_umma_select_kernel(const uint64_t* __restrict__ lists, const int* __restrict__ counts,
-                         const uint32_t* __restrict__ gthr, int n_chunks, int B, int qb_base, int n_qblocks,
-                         int k_sel, uint64_t* __restrict__ out) {
+__global__ void __launch_bounds__(SELK_MAX_THREADS)
+dense_umma_tail_kernel(const uint64_t* __restrict__ lists, const int* __restrict__ counts,
+                       const uint32_t* __restrict__ coarse, const uint32_t* __restrict__ fine,
+                       uint32_t* __restrict__ gthr, const ShardBounds xb, int n_chunks, int B, int qb_base, int n_qblocks,
+                       int k_sel, const void* __restrict__ X, int dtype, int64_t n, int d, const float* __restrict__ Q,
+                       uint64_t* __restrict__ keys_out, int k, int64_t id_offset, float* __restrict__ out_scores,
+                       int64_t* __restrict__ out_ids, int32_t* __restrict__ out_counts) {
     extern __shared__ __align__(16) uint8_t smem_raw[];
     uint64_t* a = reinterpret_cast<uint64_t*>(smem_raw);
-    __shared__ int fill;
+    uint64_t* res = a + SELK_CAP;
+    __shared__ int fill, total, count;
+    __shared__ uint32_t s_bound;
+    __shared__ int s_cnt[SELK_MAXCHUNKS];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int SELK_THREADS = (int)blockDim.x;
     const int b = qb_base * UM_BM + blockIdx.x;
     if (b >= B) return;
     const int qb = blockIdx.x / UM_BM, qidx = blockIdx.x % UM_BM;
-    const uint32_t bound = gthr[b];
-    if (tid == 0) fill = 0;
+    if (tid == 0) { fill = 0; total = 0; count = 0; }
     __syncthreads();
-    for (int c0 = 0; c0 < n_chunks; c0 += SELK_THREADS / 32) {
-        if (fill + (SELK_THREADS / 32) * UM_CAP > SELK_CAP) {       // uniform: fill is stable here
-            const int f = fill;
-            const int n2 = next_pow2(max(f, 32));
-            for (int i = f + tid; i < n2; i += SELK_THREADS) a[i] = 0ull;
-            __syncthreads();
-            bitonic_desc(a, n2, tid, SELK_THREADS, [] { __syncthreads(); });
-            if (tid == 0) fill = min(f, k_sel);
-            __syncthreads();
+    if (warp == 0) {
+        publish_bound(gthr, b, hist_bound(coarse, fine, b, (uint32_t)k_sel, lane), xb, lane);
+        __syncwarp();
+        if (lane == 0) s_bound = *reinterpret_cast<volatile uint32_t*>(gthr + b);
+    } else {
+        int t = 0;
+        for (int c = tid - 32; c < n_chunks; c += SELK_THREADS - 32) {
+            const int v = min(__ldcg(counts + (size_t)c * B + b), UM_CAP);
+            if (c < SELK_MAXCHUNKS) s_cnt[c] = v;
+            t += v;
         }
-        const int chunk = c0 + warp;
-        if (chunk < n_chunks) {
-            const int c = min(counts[(size_t)chunk * B + b], UM_CAP);
-            const uint64_t* src = lists + (((size_t)chunk * n_qblocks + qb) * UM_BM + qidx) * UM_CAP;
-            for (int i = lane; i < c; i += 32) {
-                const uint64_t key = __ldcg(src + i);
-                if ((uint32_t)(key >> 32) >= bound) a[atomicAdd(&fill, 1)] = key;
+        if (t) atomicAdd(&total, t);
+    }
+    __syncthreads();
+    const uint32_t bound = s_bound;
+    const uint64_t* my_lists = lists + ((size_t)qb * UM_BM + qidx) * UM_CAP;
+    const size_t chunk_stride = (size_t)n_qblocks * UM_BM * UM_CAP;
+    // the usual case: few keys reach the final bound, whatever the lists hold (a batch without a seed launch floods
+    // its first tiles into them); the warps stream their chunks' lists without meeting in between
+    for (int chunk = warp; chunk < n_chunks; chunk += SELK_THREADS / 32) {
+        const int c = chunk < SELK_MAXCHUNKS ? s_cnt[chunk] : min(__ldcg(counts + (size_t)chunk * B + b), UM_CAP);
+        const uint64_t* src = my_lists + (size_t)chunk * chunk_stride;
+        for (int i = lane; i < c; i += 32) {
+            const uint64_t key = __ldcg(src + i);
+            if ((uint32_t)(key >> 32) >= bound) {
+                const int slot = atomicAdd(&fill, 1);
+                if (slot < SELK_CAP) a[slot] = key;
             }
         }
+    }
+    __syncthreads();
+    if (fill > SELK_CAP) {
+        // more than the buffer holds (only without any bound): rounds of 8 lists, keeping the best k_sel in between
         __syncthreads();
+        if (tid == 0) fill = 0;
+        __syncthreads();
+        for (int c0 = 0; c0 < n_chunks; c0 += 8) {           // 8 warps gather: 8 * UM_CAP keys at most per round
+            if (fill + 8 * UM_CAP > SELK_CAP) {       // uniform: fill is stable here
+                const int f = fill;
+                const int n2 = next_pow2(max(f, 32));
+                for (int i = f + tid; i < n2; i += SELK_THREADS) a[i] = 0ull;
+                __syncthreads();
+                bitonic_desc(a, n2, tid, SELK_THREADS, [] { __syncthreads(); });
+                if (tid == 0) fill = min(f, k_sel);
+                __syncthreads();
+            }
+            const int chunk = c0 + warp;
+            if (warp < 8 && chunk < n_chunks) {
+                const int c = min(__ldcg(counts + (size_t)chunk * B + b), UM_CAP);
+                const uint64_t* src = my_lists + (size_t)chunk * chunk_stride;
+                for (int i = lane; i < c; i += 32) {
+                    const uint64_t key = __ldcg(src + i);
+                    if ((uint32_t)(key >> 32) >= bound) a[atomicAdd(&fill, 1)] = key;
+                }
+            }
+            __syncthreads();
+        }
     }
     const int f = fill;
-    const int n2 = next_pow2(max(f, 32));
-    for (int i = f + tid; i < n2; i += SELK_THREADS) a[i] = 0ull;
+    // the best k_sel of the gathered keys: by rank (keys are distinct: count the greater ones, no barriers) when
+    // there are few, else a sort
+    const int n_res = min(f, k_sel);
+    uint64_t* top = a + SELK_CAP - SELK_RES;          // their slots, past anything the gather filled in the rank case
+    if (f <= SELK_RANK_MAX) {
+        for (int i = tid; i < f; i += SELK_THREADS) {
+            const uint64_t x = a[i];
+            int r = 0;
+            for (int j = 0; j < f; ++j) r += a[j] > x ? 1 : 0;
+            if (r < k_sel) top[r] = x;
+        }
+    } else {
+        const int n2 = next_pow2(max(f, 32));
+        for (int i = f + tid; i < n2; i += SELK_THREADS) a[i] = 0ull;
+        __syncthreads();
+        bitonic_desc(a, n2, tid, SELK_THREADS, [] { __syncthreads(); });
+        top = a;
+    }
     __syncthreads();
-    bitonic_desc(a, n2, tid, SELK_THREADS, [] { __syncthreads(); });
-    for (int i = tid; i < k_sel; i += SELK_THREADS) out[(size_t)b * k_sel + i] = (i < n2) ? a[i] : 0ull;
+    // exact scores of those candidates
+    for (int i = warp; i < n_res; i += SELK_THREADS / 32) {
+        const uint64_t key = top[i];
+        uint64_t out = 0ull;
+        if (key != 0ull) {
+            const uint32_t row = key_row(key);
+            if ((int64_t)row < n) out = make_key((float)row_dot_any(X, dtype, row, d, Q + (size_t)b * d, lane), row);
+        }
+        if (lane == 0) res[i] = out;
+    }
+    __syncthreads();
+    if (keys_out != nullptr) {
+        for (int i = tid; i < k_sel; i += SELK_THREADS) keys_out[(size_t)b * k_sel + i] = i < n_res ? res[i] : 0ull;
+        return;
+    }
+    // final order by rank again (a re-scored key keeps its row, so keys stay distinct; 0 = a row that did not exist)
+    for (int i = tid; i < k; i += SELK_THREADS) {
+        out_scores[(size_t)b * k + i] = -INFINITY;
+        out_ids[(size_t)b * k + i] = -1;
+    }
+    __syncthreads();
+    for (int i = tid; i < n_res; i += SELK_THREADS) {
+        const uint64_t x = res[i];
+        if (x == 0ull) continue;
+        int r = 0;
+        for (int j = 0; j < n_res; ++j) r += res[j] > x ? 1 : 0;
+        if (r < k) {
+            out_scores[(size_t)b * k + r] = key_score(x);
+            out_ids[(size_t)b * k + r] = (int64_t)key_row(x) + id_offset;
+            atomicAdd(&count, 1);
+        }
+    }
+    __syncthreads();
+    if (tid == 0) out_counts[b] = count;
 }
 
 // ------------------------------------------------------------------ host side
@@ -711,7 +805,7 @@ cudaError_t dense_umma_init_device() {
     if (e == cudaSuccess) e = cudaFuncSetAttribute(dense_umma_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(UmSmem));
     if (e == cudaSuccess) e = cudaFuncSetAttribute(dense_umma_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(UmSmem));
     if (e != cudaSuccess) return e;
-    return cudaFuncSetAttribute(dense_umma_select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SELK_CAP * 8);
+    return cudaFuncSetAttribute(dense_umma_tail_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (SELK_CAP + SELK_RES) * 8);
 }
 
 template <int KIND>
@@ -724,11 +818,36 @@ static void um_launch(int grid, size_t smem, cudaStream_t st, const CUtensorMap&
                                                            i8.xinv, i8.qinv, i8.xinv_max);
 }
 
-cudaError_t dense_umma_scan(const void* X16, int dtype, int64_t n, int d, const void* Q16, int B,
-                            const uint32_t* mask, int k_sel, uint64_t* cand, void* scratch, const UmmaPlan& plan,
-                            void* tmap_x, void* tmap_q, cudaStream_t st, int* launches, const ShardBounds& xb,
-                            const UmmaI8& i8) {
-    (void)X16; (void)Q16;
+namespace {
+struct UmScratch {
+    uint64_t* lists; int* counts; uint32_t *gthr, *coarse, *fine; float4* seedv;
+};
+UmScratch um_scratch(void* scratch, const UmmaPlan& plan) {
+    uint8_t* sp = reinterpret_cast<uint8_t*>(scratch);
+    UmScratch u;
+    u.lists = reinterpret_cast<uint64_t*>(sp);
+    u.counts = reinterpret_cast<int*>(sp + plan.list_bytes);
+    u.gthr = reinterpret_cast<uint32_t*>(sp + plan.list_bytes + plan.count_bytes);
+    u.coarse = reinterpret_cast<uint32_t*>(sp + plan.list_bytes + plan.count_bytes + plan.gthr_bytes);
+    u.fine = reinterpret_cast<uint32_t*>(sp + plan.list_bytes + plan.count_bytes + plan.gthr_bytes + plan.coarse_bytes);
+    u.seedv = reinterpret_cast<float4*>(sp + plan.list_bytes + plan.count_bytes + plan.gthr_bytes + plan.coarse_bytes + plan.fine_bytes);
+    return u;
+}
+}  // namespace
+
+// query groups of <= UM_MAXQB blocks (1024 queries): each group is one pass over the corpus (scan, then tail; the
+// candidate lists are reused by the next group)
+int dense_umma_groups(const UmmaPlan& plan) { return (plan.n_qblocks + UM_MAXQB - 1) / UM_MAXQB; }
+
+// bounds and histograms of every query of the batch: once per call, before the first group
+cudaError_t dense_umma_clear(void* scratch, const UmmaPlan& plan, cudaStream_t st) {
+    const UmScratch u = um_scratch(scratch, plan);
+    return cudaMemsetAsync(u.gthr, 0, plan.gthr_bytes + plan.coarse_bytes + plan.fine_bytes, st);
+}
+
+cudaError_t dense_umma_scan(int dtype, int64_t n, int d, int B, const uint32_t* mask, int k_sel, void* scratch,
+                            const UmmaPlan& plan, void* tmap_x, void* tmap_q, int group, cudaStream_t st, int* launches,
+                            const ShardBounds& xb, const UmmaI8& i8) {
     const size_t smem = sizeof(UmSmem);
     CUtensorMap tq, tx;
     memcpy(&tq, tmap_q, sizeof tq);
@@ -739,55 +858,49 @@ cudaError_t dense_umma_scan(const void* X16, int dtype, int64_t n, int d, const 
     const uint32_t fmt = kind == 1 ? 2u : (kind == 2 ? 1u : (dtype == 2 ? 1u : 0u));   // TF32 | signed 8-bit | BF16 : F16
     const uint32_t idesc = (cfmt << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(UM_BN >> 3) << 17) | ((uint32_t)(UM_BM >> 4) << 24);
     const int n_kb = (int)((int64_t)d * um_esz(dtype) / 128);
-    auto launch = [&](int grid, int qb0, int nqb, float4* seedv, int n_seed, int64_t rows_per_chunk, int share,
-                      uint64_t* lists, int* counts, uint32_t* gthr, uint32_t* coarse, uint32_t* fine, const ShardBounds& b) {
-        if (kind == 0) um_launch<0>(grid, smem, st, tq, tx, n, n_kb, B, qb0, nqb, seedv, n_seed, rows_per_chunk, share, mask, k_sel, idesc, lists, counts, gthr, coarse, fine, b, i8);
-        else if (kind == 1) um_launch<1>(grid, smem, st, tq, tx, n, n_kb, B, qb0, nqb, seedv, n_seed, rows_per_chunk, share, mask, k_sel, idesc, lists, counts, gthr, coarse, fine, b, i8);
-        else um_launch<2>(grid, smem, st, tq, tx, n, n_kb, B, qb0, nqb, seedv, n_seed, rows_per_chunk, share, mask, k_sel, idesc, lists, counts, gthr, coarse, fine, b, i8);
+    const UmScratch u = um_scratch(scratch, plan);
+    auto launch = [&](int grid, int qb0, int nqb, float4* seedv, int n_seed, int64_t rows_per_chunk, int share, const ShardBounds& b) {
+        if (kind == 0) um_launch<0>(grid, smem, st, tq, tx, n, n_kb, B, qb0, nqb, seedv, n_seed, rows_per_chunk, share, mask, k_sel, idesc, u.lists, u.counts, u.gthr, u.coarse, u.fine, b, i8);
+        else if (kind == 1) um_launch<1>(grid, smem, st, tq, tx, n, n_kb, B, qb0, nqb, seedv, n_seed, rows_per_chunk, share, mask, k_sel, idesc, u.lists, u.counts, u.gthr, u.coarse, u.fine, b, i8);
+        else um_launch<2>(grid, smem, st, tq, tx, n, n_kb, B, qb0, nqb, seedv, n_seed, rows_per_chunk, share, mask, k_sel, idesc, u.lists, u.counts, u.gthr, u.coarse, u.fine, b, i8);
     };
-    uint8_t* sp = reinterpret_cast<uint8_t*>(scratch);
-    uint64_t* lists = reinterpret_cast<uint64_t*>(sp);
-    int* counts = reinterpret_cast<int*>(sp + plan.list_bytes);
-    uint32_t* gthr = reinterpret_cast<uint32_t*>(sp + plan.list_bytes + plan.count_bytes);
-    uint32_t* coarse = reinterpret_cast<uint32_t*>(sp + plan.list_bytes + plan.count_bytes + plan.gthr_bytes);
-    uint32_t* fine = reinterpret_cast<uint32_t*>(sp + plan.list_bytes + plan.count_bytes + plan.gthr_bytes + plan.coarse_bytes);
-    cudaError_t err = cudaMemsetAsync(gthr, 0, plan.gthr_bytes + plan.coarse_bytes + plan.fine_bytes, st);
-    if (err != cudaSuccess) return err;
-    float4* seedv = reinterpret_cast<float4*>(sp + plan.list_bytes + plan.count_bytes + plan.gthr_bytes + plan.coarse_bytes +
-                                              plan.fine_bytes);
+    cudaError_t err;
     const int64_t n_tiles = (n + UM_BN - 1) / UM_BN;
     const int n_seed = plan.n_seed, n_main = plan.n_chunks;
     const int64_t seed_stride = n_seed > 0 ? (n_tiles / n_seed) * UM_BN : 0;      // rows between seed tiles
     int nl = 0;
-    // query groups of <= UM_MAXQB blocks (1024 queries): each group is one pass over the corpus
-    for (int qb0 = 0; qb0 < plan.n_qblocks; qb0 += UM_MAXQB) {
-        const int nqb = std::min(UM_MAXQB, plan.n_qblocks - qb0);
-        const int nq = std::min(B - qb0 * UM_BM, nqb * UM_BM);
-        if (n_seed > 0) {
-            launch(n_seed, qb0, nqb, seedv, n_seed, seed_stride, 1, lists, counts, gthr, coarse, fine, ShardBounds());
-            if ((err = cudaGetLastError()) != cudaSuccess) return err;
-            um_seed_bound_kernel<<<nq, 256, 0, st>>>(seedv, n_seed, qb0 * UM_BM, qb0 * UM_BM + nq, k_sel, gthr);
-            if ((err = cudaGetLastError()) != cudaSuccess) return err;
-            nl += 2;
-        }
-        // CTAs sharing a row range (see the kernel): only when the query blocks and the grid split evenly
-        const bool splits = nqb % um_share() == 0 || (um_share() == 2 && nqb >= 3);   // odd counts: the last block is split by rows
-        const int share = (um_share() > 1 && splits && n_main % um_share() == 0 && n_tiles >= n_main) ? um_share() : 1;
-        const int64_t rows_per_chunk = (n_tiles + n_main / share - 1) / (n_main / share) * UM_BN;
-        launch(n_main, qb0, nqb, nullptr, 0, rows_per_chunk, share, lists, counts, gthr, coarse, fine, xb);
+    const int qb0 = group * UM_MAXQB;
+    const int nqb = std::min(UM_MAXQB, plan.n_qblocks - qb0);
+    const int nq = std::min(B - qb0 * UM_BM, nqb * UM_BM);
+    if (n_seed > 0) {
+        launch(n_seed, qb0, nqb, u.seedv, n_seed, seed_stride, 1, ShardBounds());
         if ((err = cudaGetLastError()) != cudaSuccess) return err;
-        // final bounds from the complete histograms (a CTA's manager stops with its own CTA, so the bounds it left
-        // may predate the last pushes of the others): the selection then gathers ~k_sel keys per query, not more
-        um_bound_kernel<<<(nq + 7) / 8, 256, 0, st>>>(coarse, fine, gthr, qb0 * UM_BM, qb0 * UM_BM + nq, k_sel, xb);
-        if ((err = cudaGetLastError()) != cudaSuccess) return err;
-        ++nl;
-        dense_umma_select_kernel<<<nq, SELK_THREADS, SELK_CAP * 8, st>>>(lists, counts, gthr, plan.n_chunks, B, qb0, nqb,
-                                                                        k_sel, cand);
+        um_seed_bound_kernel<<<nq, 256, 0, st>>>(u.seedv, n_seed, qb0 * UM_BM, qb0 * UM_BM + nq, k_sel, u.gthr);
         if ((err = cudaGetLastError()) != cudaSuccess) return err;
         nl += 2;
     }
+    // CTAs sharing a row range (see the kernel): the query blocks split evenly, or (share = 2) the odd block by rows
+    const bool splits = nqb % um_share() == 0 || (um_share() == 2 && nqb >= 3);
+    const int share = (um_share() > 1 && splits && n_main % um_share() == 0 && n_tiles >= n_main) ? um_share() : 1;
+    const int64_t rows_per_chunk = (n_tiles + n_main / share - 1) / (n_main / share) * UM_BN;
+    launch(n_main, qb0, nqb, nullptr, 0, rows_per_chunk, share, xb);
+    if ((err = cudaGetLastError()) != cudaSuccess) return err;
+    ++nl;
     if (launches) *launches = nl;
     return cudaSuccess;
+}
+
+cudaError_t dense_umma_tail(int B, int k_sel, void* scratch, const UmmaPlan& plan, int group, const UmmaTail& t,
+                            cudaStream_t st, const ShardBounds& xb) {
+    if (plan.n_chunks > SELK_MAXCHUNKS * 64 || k_sel > SELK_RES || t.k > SELK_RES) return cudaErrorInvalidValue;
+    const UmScratch u = um_scratch(scratch, plan);
+    const int qb0 = group * UM_MAXQB;
+    const int nqb = std::min(UM_MAXQB, plan.n_qblocks - qb0);
+    const int nq = std::min(B - qb0 * UM_BM, nqb * UM_BM);
+    dense_umma_tail_kernel<<<nq, B <= 64 ? 1024 : 512, (SELK_CAP + SELK_RES) * 8, st>>>(
+        u.lists, u.counts, u.coarse, u.fine, u.gthr, xb, plan.n_chunks, B, qb0, nqb, k_sel, t.X, t.dtype, t.n, t.d, t.Q,
+        t.keys_out, t.k, t.id_offset, t.out_scores, t.out_ids, t.out_counts);
+    return cudaGetLastError();
 }
 
 }  // namespace brag

@@ -6,6 +6,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <map>
+#include <optional>
 #include <stdexcept>
 #include <string>
 #include <vector>
@@ -502,20 +503,24 @@ void dense_topk_dev(brag_engine* e, DenseSpace& s, const float* Q, int B, int k,
     void* tmap_x = s.tmap_x;
     const uint32_t* scan_mask = mask;
     bool compact = false;
-    {
-        StageTimer t(e, 0, st);
-        if (path == 1 && mask != nullptr && !e->no_compact && ensure_compact(e, s, mask_id, mask, st)) {
-            compact = true;
-            X = s.cp_x; n = s.cp_n; tmap_x = s.cp_tmap; scan_mask = nullptr;
-        }
+    bool finished = false;                 // the scan's tail already wrote the final list
+    if (path == 1) {
+        // tcgen05 scan; selection and exact re-score are its tail kernel (no partial lists to merge)
+        brag::UmmaPlan plan;
+        void* scratch = nullptr;
         brag::UmmaI8 i8;
-        if (s.dtype == 3) {
-            i8.xinv = compact ? s.cp_xinv : s.xinv;
-            i8.xinv_max = compact ? s.cp_xinv_max : s.xinv_max;
-        }
-        if (path == 1) {
-            // tcgen05 scan; the per-query selection is part of the scan (no partial lists to merge)
-            brag::UmmaPlan plan;
+        // (one stage-0 interval per group; the first one includes the preparation)
+        std::optional<StageTimer> t0;
+        t0.emplace(e, 0, st);
+        {
+            if (mask != nullptr && !e->no_compact && ensure_compact(e, s, mask_id, mask, st)) {
+                compact = true;
+                X = s.cp_x; n = s.cp_n; tmap_x = s.cp_tmap; scan_mask = nullptr;
+            }
+            if (s.dtype == 3) {
+                i8.xinv = compact ? s.cp_xinv : s.xinv;
+                i8.xinv_max = compact ? s.cp_xinv_max : s.xinv_max;
+            }
             CK(brag::dense_umma_plan(n, s.d, B, k_sel, e->num_sms, &plan));
             const int Bpad = plan.n_qblocks * 128;
             void* q16 = e->q16.ensure((size_t)Bpad * s.d * dtype_bytes(s.dtype));
@@ -523,12 +528,34 @@ void dense_topk_dev(brag_engine* e, DenseSpace& s, const float* Q, int B, int k,
             i8.qinv = qinv;
             CK(brag::scan_queries(Q, B, s.d, s.dtype, q16, Bpad, qinv, st));
             CK(brag::make_tmap_2d(e->tmap_q, q16, Bpad, s.d, 128, s.dtype));
-            void* scratch = e->umma_scratch.ensure(plan.scratch_bytes);
-            int launches = 0;
-            CK(brag::dense_umma_scan(X, s.dtype, n, s.d, q16, B, scan_mask, k_sel, cand, scratch, plan, tmap_x,
-                                     e->tmap_q, st, &launches, xb, i8));
-            e->kernel_launches += 1 + launches;
-        } else {
+            scratch = e->umma_scratch.ensure(plan.scratch_bytes);
+            CK(brag::dense_umma_clear(scratch, plan, st));
+            e->kernel_launches += 1;
+        }
+        brag::UmmaTail tail;
+        tail.X = X; tail.dtype = s.dtype; tail.n = n; tail.d = s.d; tail.Q = Q;
+        tail.k = k; tail.id_offset = e->id_offset;
+        finished = !compact && !sink;      // otherwise the re-scored keys go on to the row remap / the shard push
+        if (finished) { tail.out_scores = out_scores; tail.out_ids = out_ids; tail.out_counts = out_counts; }
+        else tail.keys_out = cand2;
+        for (int g = 0; g < brag::dense_umma_groups(plan); ++g) {
+            {
+                if (!t0) t0.emplace(e, 0, st);
+                int launches = 0;
+                CK(brag::dense_umma_scan(s.dtype, n, s.d, B, scan_mask, k_sel, scratch, plan, tmap_x, e->tmap_q, g, st,
+                                         &launches, xb, i8));
+                e->kernel_launches += launches;
+                t0.reset();
+            }
+            {
+                StageTimer t(e, 1, st);
+                CK(brag::dense_umma_tail(B, k_sel, scratch, plan, g, tail, st, xb));
+                e->kernel_launches += 1;
+            }
+        }
+    } else {
+        {
+            StageTimer t(e, 0, st);
             // the GEMV scan multiplies in float32 anyway: it takes the caller's float32 query as it is, so its
             // candidates are ranked by (almost) the exact score whatever the storage dtype
             const int64_t ngroups = (s.n + 31) / 32;
@@ -543,11 +570,13 @@ void dense_topk_dev(brag_engine* e, DenseSpace& s, const float* Q, int B, int k,
             CK(brag::merge_key_lists(part, P, B, k_sel, ta, tb, cand, k_sel, st, &launches));
             e->kernel_launches += 1 + launches;
         }
-    }
-    {
         StageTimer t(e, 1, st);
-        // exact scores: float64 dot of the stored row with the caller's float32 query (the rounded copy only fed the scan)
+        // exact scores: float64 dot of the stored row with the caller's float32 query
         CK(brag::rescore_keys(X, s.dtype, n, s.d, Q, B, cand, k_sel, cand2, st));
+        e->kernel_launches += 1;
+    }
+    if (!finished) {
+        StageTimer t(e, 1, st);
         if (compact) {
             CK(brag::remap_keys(cand2, (int64_t)B * k_sel, s.cp_rowmap, st));
             e->kernel_launches += 1;
@@ -556,7 +585,7 @@ void dense_topk_dev(brag_engine* e, DenseSpace& s, const float* Q, int B, int k,
             CK(brag::shard_finalize_push(cand2, B, k_sel, k, e->id_offset, sink->list, sink->local_out, sink->push, st));
         else
             CK(brag::finalize_keys(cand2, B, k_sel, k, false, e->id_offset, out_scores, out_ids, out_counts, st));
-        e->kernel_launches += 2;
+        e->kernel_launches += 1;
     }
 }
 

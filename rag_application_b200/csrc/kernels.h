@@ -39,12 +39,30 @@ struct UmmaI8 {
 // longest candidate list (k + selection margin) the tcgen05 scan keeps per (CTA, query); longer ones take the GEMV scan
 int dense_umma_max_ksel();
 cudaError_t dense_umma_plan(int64_t n, int d, int B, int k_sel, int num_sms, UmmaPlan* plan);
-// X16: [n, d] f16/bf16; Q16: [Bpad, d] same dtype (Bpad = n_qblocks*128, zero padded).
-// cand: [B][k_sel] keys, best first (0 = empty slot).
-cudaError_t dense_umma_scan(const void* X16, int dtype, int64_t n, int d, const void* Q16, int B,
-                            const uint32_t* mask, int k_sel, uint64_t* cand, void* scratch,
-                            const UmmaPlan& plan, void* tmap_x, void* tmap_q, cudaStream_t st, int* launches,
+// A call = dense_umma_clear once, then for every group of <= 1024 queries (dense_umma_groups): dense_umma_scan (seed
+// launch + main launch over the whole space; tmap_x / tmap_q: tensor maps of the [n, d] rows and of the [Bpad, d] scan
+// copy of the queries, Bpad = n_qblocks * 128, zero padded) and dense_umma_tail (final bound, selection, exact re-score,
+// and either the re-scored keys or the final list).
+int dense_umma_groups(const UmmaPlan& plan);
+cudaError_t dense_umma_clear(void* scratch, const UmmaPlan& plan, cudaStream_t st);
+cudaError_t dense_umma_scan(int dtype, int64_t n, int d, int B, const uint32_t* mask, int k_sel, void* scratch,
+                            const UmmaPlan& plan, void* tmap_x, void* tmap_q, int group, cudaStream_t st, int* launches,
                             const ShardBounds& xb, const UmmaI8& i8);
+struct UmmaTail {
+    const void* X = nullptr;        // the rows that were scanned, for the exact re-score
+    int dtype = 0;
+    int64_t n = 0;
+    int d = 0;
+    const float* Q = nullptr;       // [B, d] the caller's float32 queries
+    uint64_t* keys_out = nullptr;   // [B][k_sel] re-scored keys with local rows; NULL = write the final list below
+    int k = 0;
+    int64_t id_offset = 0;
+    float* out_scores = nullptr;    // [B][k]
+    int64_t* out_ids = nullptr;     // [B][k]
+    int32_t* out_counts = nullptr;  // [B]
+};
+cudaError_t dense_umma_tail(int B, int k_sel, void* scratch, const UmmaPlan& plan, int group, const UmmaTail& t,
+                            cudaStream_t st, const ShardBounds& xb);
 // builds a CUtensorMap (128 bytes) for a [rows, d] row-major matrix of `dtype`, box = [box_rows, one 128-byte K slice]
 cudaError_t make_tmap_2d(void* tmap_out, const void* base, int64_t rows, int d, int box_rows, int dtype);
 

@@ -337,6 +337,20 @@ def test_dense_exact_ties_broken_by_id(engine):
     assert list(i[0]) == [7, 100, 101, 102, 103]
 
 
+@pytest.mark.parametrize("B", [1, 3, 130])
+def test_dense_every_row_ties(engine, B):
+    """A corpus of identical rows: every candidate reaches every bound, so the per-CTA lists overflow and the tail
+    kernel's selection takes its multi-round path; the answer is still the lowest ids, in order."""
+    n, d, k = 40_000, 64, 50
+    x = np.tile(synth.dense_corpus(1, d, seed=5), (n, 1))
+    q = np.tile(x[:1], (B, 1))
+    for dtype in ("f16", "f32"):
+        engine.dense_set("ties", x, dtype)
+        s, i, c = engine.dense_topk("ties", q, k)
+        assert np.all(c == k) and np.array_equal(i, np.tile(np.arange(k), (B, 1)))
+        assert np.all(s == s[0, 0])
+
+
 def test_dense_rescore_union_dedup_mask(engine):
     n, d = 3000, 768
     x = synth.dense_corpus(n, d, seed=31)
