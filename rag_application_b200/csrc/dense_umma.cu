@@ -572,10 +572,13 @@ um_seed_bound_kernel(const float4* __restrict__ seedv, int seed_tiles, int q_lo,
 //      on from there -- or, when keys_out is NULL, the final list itself: sorted, unpacked, ids offset, count.
 constexpr int SELK_MAX_THREADS = 1024;   // launched with 512 threads, 1024 for batches of <= 64 queries (the re-score is
                                          // one warp per candidate: a small batch has no other CTAs to hide its latency)
-constexpr int SELK_CAP = 8192;     // 64 KB of keys; 8 lists (<= 8 * UM_CAP entries) are added per round
+constexpr int SELK_CAP = 2048;     // keys gathered per query (16 KB: four CTAs per SM); a few hundred reach the bound
+constexpr int SELK_GW = SELK_CAP / 2 / UM_CAP;   // lists added per round of the overflow path
+static_assert(SELK_GW >= 1, "a round must take at least one full list");
 constexpr int SELK_RES = 512;      // re-scored keys (k_sel <= 512)
 constexpr int SELK_MAXCHUNKS = 256;
 constexpr int SELK_RANK_MAX = 1024;   // gathered keys up to which the selection ranks instead of sorting
+static_assert(SELK_RANK_MAX + SELK_RES <= SELK_CAP, "the ranked keys are placed behind the gathered ones");
 
 __global__ void __launch_bounds__(SELK_MAX_THREADS)
 dense_umma_tail_kernel(const uint64_t* __restrict__ lists, const int* __restrict__ counts,
@@ -629,12 +632,12 @@ dense_umma_tail_kernel(const uint64_t* __restrict__ lists, const int* __restrict
     }
     __syncthreads();
     if (fill > SELK_CAP) {
-        // more than the buffer holds (only without any bound): rounds of 8 lists, keeping the best k_sel in between
+        // more than the buffer holds (mass ties, or no bound at all): rounds of lists, keeping the best k_sel in between
         __syncthreads();
         if (tid == 0) fill = 0;
         __syncthreads();
-        for (int c0 = 0; c0 < n_chunks; c0 += 8) {           // 8 warps gather: 8 * UM_CAP keys at most per round
-            if (fill + 8 * UM_CAP > SELK_CAP) {       // uniform: fill is stable here
+        for (int c0 = 0; c0 < n_chunks; c0 += SELK_GW) {     // SELK_GW warps gather: SELK_GW * UM_CAP keys at most per round
+            if (fill + SELK_GW * UM_CAP > SELK_CAP) {       // uniform: fill is stable here
                 const int f = fill;
                 const int n2 = next_pow2(max(f, 32));
                 for (int i = f + tid; i < n2; i += SELK_THREADS) a[i] = 0ull;
@@ -644,7 +647,7 @@ dense_umma_tail_kernel(const uint64_t* __restrict__ lists, const int* __restrict
                 __syncthreads();
             }
             const int chunk = c0 + warp;
-            if (warp < 8 && chunk < n_chunks) {
+            if (warp < SELK_GW && chunk < n_chunks) {
                 const int c = min(__ldcg(counts + (size_t)chunk * B + b), UM_CAP);
                 const uint64_t* src = my_lists + (size_t)chunk * chunk_stride;
                 for (int i = lane; i < c; i += 32) {

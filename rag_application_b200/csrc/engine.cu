@@ -672,27 +672,26 @@ void sparse_topk_dev(brag_engine* e, SparseSpace& full, const int32_t* q_ptr, co
     }
     {
         StageTimer t(e, 3, st);
-        size_t tmp = brag::merge_tmp_elems(P, B, k);
-        uint64_t* ta = e->tmp_a.as<uint64_t>(tmp);
-        uint64_t* tb = e->tmp_b.as<uint64_t>(tmp);
         int launches = 0;
         // both sparse kernels keep [work counters | bounds | coarse | fine histograms] in `scratch`: the bound of the
-        // complete histograms lets the merge drop all but a few hundred of the P * k keys before it sorts
+        // complete histograms lets the tail drop all but a few hundred of the P * k keys before it orders them
         uint8_t* sp = reinterpret_cast<uint8_t*>(scratch);
         uint32_t* gthr = reinterpret_cast<uint32_t*>(sp + 256);
         const uint32_t* coarse = reinterpret_cast<const uint32_t*>(sp + 256 + plan.gthr_bytes);
         const uint32_t* fine = reinterpret_cast<const uint32_t*>(sp + 256 + plan.gthr_bytes + plan.coarse_bytes);
-        CK(brag::publish_bounds(coarse, fine, gthr, B, k, st, xb));
-        CK(brag::merge_key_lists(part, P, B, k, ta, tb, merged, k, st, &launches, gthr));
+        const bool finished = !compact && !sink;
+        CK(brag::sparse_tail(part, P, B, k, coarse, fine, gthr, xb, k, finished ? nullptr : merged, e->id_offset, out_scores,
+                             out_ids, out_counts, st));
         if (compact) {
             CK(brag::remap_keys(merged, (int64_t)B * k, full.cp_rowmap, st));
             launches += 1;
         }
         if (sink)
             CK(brag::shard_finalize_push(merged, B, k, k, e->id_offset, sink->list, sink->local_out, sink->push, st));
-        else
+        else if (!finished)
             CK(brag::finalize_keys(merged, B, k, k, false, e->id_offset, out_scores, out_ids, out_counts, st));
-        e->kernel_launches += launches + 2;
+        launches += finished ? 0 : 1;
+        e->kernel_launches += launches + 1;
     }
 }
 

@@ -74,6 +74,11 @@ cudaError_t merge_key_lists(const uint64_t* in, int P, int B, int kk, uint64_t* 
 // gthr[q] = max(gthr[q], bound of query q's complete score histograms) -- see common.cuh
 cudaError_t publish_bounds(const uint32_t* coarse, const uint32_t* fine, uint32_t* gthr, int B, int k, cudaStream_t st,
                            const ShardBounds& xb);
+// tail of a sparse scan (select.cu): final bound + merge of the P lists [P][B][kk] + the final list (keys_out NULL) or
+// its best k keys with local rows (keys_out [B][k])
+cudaError_t sparse_tail(const uint64_t* part, int P, int B, int kk, const uint32_t* coarse, const uint32_t* fine,
+                        uint32_t* gthr, const ShardBounds& xb, int k, uint64_t* keys_out, int64_t id_offset,
+                        float* out_scores, int64_t* out_ids, int32_t* out_counts, cudaStream_t st);
 size_t merge_tmp_elems(int P, int B, int kk);
 // the tensor-core scan's copy of the queries in the stored element type, [Bpad, d] with zero padding rows
 // (dtype 3 also writes qinv[B], the inverse norms of the int8 queries)

@@ -56,6 +56,108 @@ merge_keys_kernel(const uint64_t* __restrict__ in, int P, int B, int kk, int GP,
     for (int i = tid; i < kout; i += SEL_THREADS) o[i] = a[i];
 }
 
+// ------------------------------------------------------------------ tail of a sparse scan, one CTA per query
+// One launch where there were three (bound, merge, finalize): the bound of the query's complete histograms (published
+// like every bound, also to the peers of a sharded call), the keys of the P per-warp lists that reach it -- a few
+// hundred of the P * kk slots -- ordered by rank (keys are distinct: count the greater ones, no barriers), and either
+// the best k as keys with local rows (keys_out: filter-compacted indexes and sharded calls go on from there) or the
+// final list itself.  The lists' scores are already exact (float64 sums rounded once), so there is no re-score.
+constexpr int STAIL_CAP = 2048;           // keys gathered per query (16 KB: four CTAs per SM)
+constexpr int STAIL_RANK_MAX = 1024;
+
+__global__ void __launch_bounds__(1024)
+sparse_tail_kernel(const uint64_t* __restrict__ part, int P, int B, int kk, const uint32_t* __restrict__ coarse,
+                   const uint32_t* __restrict__ fine, uint32_t* __restrict__ gthr, const ShardBounds xb, int k,
+                   uint64_t* __restrict__ keys_out, int64_t id_offset, float* __restrict__ out_scores,
+                   int64_t* __restrict__ out_ids, int32_t* __restrict__ out_counts) {
+    extern __shared__ __align__(16) uint8_t smem_raw[];
+    uint64_t* a = reinterpret_cast<uint64_t*>(smem_raw);
+    __shared__ int fill, count;
+    __shared__ uint32_t s_bound;
+    const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, NT = (int)blockDim.x;
+    if (tid == 0) { fill = 0; count = 0; }
+    if (warp == 0) {
+        publish_bound(gthr, b, hist_bound(coarse, fine, b, (uint32_t)k, lane), xb, lane);
+        __syncwarp();
+        if (lane == 0) s_bound = *reinterpret_cast<volatile uint32_t*>(gthr + b);
+    }
+    __syncthreads();
+    const uint32_t bound = s_bound;
+    const int total = P * kk;
+    for (int i = tid; i < total; i += NT) {
+        const int p = i / kk, j = i - p * kk;
+        const uint64_t v = __ldcg(part + ((size_t)p * B + b) * kk + j);
+        if (v != 0ull && (uint32_t)(v >> 32) >= bound) {
+            const int slot = atomicAdd(&fill, 1);
+            if (slot < STAIL_CAP) a[slot] = v;
+        }
+    }
+    __syncthreads();
+    if (fill > STAIL_CAP) {
+        // more keys reach the bound than the buffer holds (mass ties): rounds of lists, keeping the best k in between
+        __syncthreads();
+        if (tid == 0) fill = 0;
+        __syncthreads();
+        const int R = max(1, (STAIL_CAP / 2) / kk);           // lists per round
+        for (int p0 = 0; p0 < P; p0 += R) {
+            if (fill + R * kk > STAIL_CAP) {                   // uniform: fill is stable here
+                const int f = fill;
+                const int n2 = next_pow2(max(f, 32));
+                for (int i = f + tid; i < n2; i += NT) a[i] = 0ull;
+                __syncthreads();
+                bitonic_desc(a, n2, tid, NT, [] { __syncthreads(); });
+                if (tid == 0) fill = min(f, k);
+                __syncthreads();
+            }
+            const int np = min(R, P - p0);
+            for (int i = tid; i < np * kk; i += NT) {
+                const int p = p0 + i / kk, j = i % kk;
+                const uint64_t v = __ldcg(part + ((size_t)p * B + b) * kk + j);
+                if (v != 0ull && (uint32_t)(v >> 32) >= bound) a[atomicAdd(&fill, 1)] = v;
+            }
+            __syncthreads();
+        }
+    }
+    const int f = fill;
+    const bool ranked = f <= STAIL_RANK_MAX;
+    if (!ranked) {
+        const int n2 = next_pow2(max(f, 32));
+        for (int i = f + tid; i < n2; i += NT) a[i] = 0ull;
+        __syncthreads();
+        bitonic_desc(a, n2, tid, NT, [] { __syncthreads(); });
+    }
+    const int n_out = min(f, k);
+    if (keys_out != nullptr) {
+        for (int i = n_out + tid; i < k; i += NT) keys_out[(size_t)b * k + i] = 0ull;
+    } else {
+        for (int i = n_out + tid; i < k; i += NT) { out_scores[(size_t)b * k + i] = -INFINITY; out_ids[(size_t)b * k + i] = -1; }
+        if (tid == 0) out_counts[b] = n_out;
+    }
+    for (int i = tid; i < f; i += NT) {
+        const uint64_t x = a[i];
+        int r = i;
+        if (ranked) {
+            r = 0;
+            for (int j = 0; j < f; ++j) r += a[j] > x ? 1 : 0;
+        }
+        if (r >= k) continue;
+        if (keys_out != nullptr) keys_out[(size_t)b * k + r] = x;
+        else {
+            out_scores[(size_t)b * k + r] = key_score(x);
+            out_ids[(size_t)b * k + r] = (int64_t)key_row(x) + id_offset;
+        }
+    }
+}
+
+cudaError_t sparse_tail(const uint64_t* part, int P, int B, int kk, const uint32_t* coarse, const uint32_t* fine,
+                        uint32_t* gthr, const ShardBounds& xb, int k, uint64_t* keys_out, int64_t id_offset,
+                        float* out_scores, int64_t* out_ids, int32_t* out_counts, cudaStream_t st) {
+    if (kk > STAIL_CAP / 2 || k > STAIL_CAP / 2 || k > kk) return cudaErrorInvalidValue;
+    sparse_tail_kernel<<<B, B <= 64 ? 1024 : 512, STAIL_CAP * 8, st>>>(part, P, B, kk, coarse, fine, gthr, xb, k, keys_out,
+                                                                     id_offset, out_scores, out_ids, out_counts);
+    return cudaGetLastError();
+}
+
 // One warp per query: bound = highest histogram edge that at least k counted rows reach (common.cuh), published
 // with atomicMax.  Run after a scan so that the selection sees the bound of the COMPLETE histograms.
 __global__ void publish_bounds_kernel(const uint32_t* __restrict__ coarse, const uint32_t* __restrict__ fine,
@@ -369,6 +471,7 @@ cudaError_t merge_scored_lists(const float* scores, const int64_t* ids, const in
 // kernel attributes are per device: brag_create calls this with the engine's device current
 cudaError_t select_init_device() {
     cudaError_t e = cudaFuncSetAttribute(merge_keys_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SEL_MAX * 8);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(sparse_tail_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, STAIL_CAP * 8);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(finalize_keys_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SEL_MAX * 8);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(merge_scored_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SEL_MAX * 8);
     if (e == cudaSuccess)
