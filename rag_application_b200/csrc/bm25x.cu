@@ -11,8 +11,10 @@
 //     terms, c2 of them in their high class, scores at most S_(c1+c2): it needs c1 + c2 >= m, where
 //     m = 1 + #{c : S_c <= bound}.  Valid for any sign of weights and query values;
 //   * per (term, 2048-document sub-tile) the documents containing the term (and those in its high class) are
-//     2048-bit maps: stored at upload for dense terms (df >= N/64: a map is smaller than the postings it stands
-//     for), built in shared memory from the few postings (staged with cp.async) otherwise;
+//     2048-bit maps: stored at upload for dense terms (df >= N/256, within as many bytes as the postings take: the
+//     scan is issue-bound, and building a map from postings costs ~10 instructions per posting where fetching a
+//     stored one costs two cp.async per lane), built in shared memory from the few postings (staged with cp.async)
+//     otherwise;
 //   * c1 + c2 per document is a bit-sliced carry-save sum of the <= 2*MAXT maps (each lane owns 64*SUBS
 //     documents), compared with m bit-slice-wise, and-ed with the payload filter;
 //   * only the surviving documents are scored: weight of term t for document d = posting number

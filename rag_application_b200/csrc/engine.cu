@@ -290,8 +290,8 @@ void free_sparse(SparseSpace& s) {
     s = SparseSpace();
 }
 
-// Index of the bitmap-filter scan: weight range per term, and a document map for every term whose map is
-// smaller than its postings (df >= N/64), densest first, within a quarter of the posting bytes.
+// Index of the bitmap-filter scan: weight range per term, and document maps for the frequent terms (df >= N/256),
+// densest first, within as many bytes as the postings take.
 void build_bitmap_index(SparseSpace& s) {
     CK(cudaMalloc(&s.wrange, (size_t)s.V * sizeof(float2)));
     CK(cudaMalloc(&s.tau, (size_t)s.V * sizeof(float)));
@@ -303,7 +303,11 @@ void build_bitmap_index(SparseSpace& s) {
     cudaFree(flag);
     CK(ce);
     const size_t row_bytes = (size_t)brag::bm25x_row_words(s.n_docs) * 4;
-    const int64_t min_df = std::max<int64_t>(32, s.n_docs / 64);
+    // stored maps: terms with df >= n_docs / BRAG_BX_MAP_DIV, most frequent first, within BRAG_BX_MAP_BYTES bytes per
+    // posting (tuning knobs, read once; see DESIGN 3.3 for the measured trade: map bytes against pool instructions)
+    static const int map_div = [] { const char* e = getenv("BRAG_BX_MAP_DIV"); const int v = e ? atoi(e) : 256; return v < 8 ? 8 : (v > 4096 ? 4096 : v); }();
+    static const int map_bytes = [] { const char* e = getenv("BRAG_BX_MAP_BYTES"); const int v = e ? atoi(e) : 8; return v < 1 ? 1 : (v > 16 ? 16 : v); }();
+    const int64_t min_df = std::max<int64_t>(32, s.n_docs / map_div);
     std::vector<std::pair<int64_t, int32_t>> dense;     // (df, term)
     for (int64_t t = 0; t < s.V; ++t) {
         const int64_t df = s.term_ptr_host[t + 1] - s.term_ptr_host[t];
@@ -312,8 +316,8 @@ void build_bitmap_index(SparseSpace& s) {
     std::sort(dense.begin(), dense.end(), [](const std::pair<int64_t, int32_t>& a, const std::pair<int64_t, int32_t>& b) {
         return a.first != b.first ? a.first > b.first : a.second < b.second;
     });
-    // two maps per dense term (present, high class) within a quarter of the posting bytes
-    const size_t budget = std::max<size_t>((size_t)64 << 20, (size_t)s.nnz * 2);
+    // two maps per dense term (present, high class), together at most as many bytes as the postings themselves
+    const size_t budget = std::max<size_t>((size_t)64 << 20, (size_t)s.nnz * map_bytes);
     while (!dense.empty() && dense.size() * row_bytes * 2 > budget) dense.pop_back();
     std::vector<int32_t> rows((size_t)s.V, -1), terms(dense.size());
     for (size_t r = 0; r < dense.size(); ++r) { rows[(size_t)dense[r].second] = (int32_t)r; terms[r] = dense[r].second; }

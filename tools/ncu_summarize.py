@@ -2,10 +2,10 @@
 """Turn ncu output into the committed profile artefacts.
   launches:  python tools/ncu_summarize.py launches <launches.csv> <tag>
              (from `ncu --metrics gpu__time_duration.sum --clock-control none -k regex:... --csv --log-file launches.csv ...`)
-             -> profiles/r1_launches_c4_<tag>.csv, profiles/r1_launch_shares_c4_<tag>.csv
+             -> profiles/r2_launches_c4_<tag>.csv, profiles/r2_launch_shares_c4_<tag>.csv
   full:      python tools/ncu_summarize.py full <rep.ncu-rep> <tag>
              (from `ncu --set full --clock-control none --import-source on ...`)
-             -> profiles/r1_ncu_summary_c4_<tag>.txt, profiles/ncu_traffic.json"""
+             -> profiles/r2_ncu_summary_c4_<tag>.txt, profiles/ncu_traffic.json"""
 import collections
 import csv
 import json
@@ -15,6 +15,7 @@ import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 PROF = os.path.join(ROOT, "profiles")
+RND = os.environ.get("BRAG_ROUND", "r2")          # prefix of the artefacts written
 
 
 def to_ms(v, u):
@@ -49,16 +50,16 @@ def launches(path, tag):
             key = k + " [seed launch]"
         agg.setdefault(key, []).append(ms)
     tot = sum(sum(v) for v in agg.values())
-    with open(os.path.join(PROF, f"r1_launch_shares_c4_{tag}.csv"), "w") as f:
+    with open(os.path.join(PROF, f"{RND}_launch_shares_c4_{tag}.csv"), "w") as f:
         f.write("kernel,launches,total_ms,avg_ms,share_pct  (ncu --metrics gpu__time_duration.sum --clock-control none; "
                 "bench.py --steps 2 --warmup 1 --no-cpu-baseline --no-e2e --b1-iters 0; includes the one-time index "
-                "build kernels; um_seed_bound_kernel (0.03 ms per step) is outside the capture's kernel filter; cold-cache "
+                "build kernels; cold-cache "
                 "serialised: compare shares)\n")
         for k, v in sorted(agg.items(), key=lambda kv: -sum(kv[1])):
             line = f"\"{k}\",{len(v)},{sum(v):.3f},{sum(v)/len(v):.4f},{100*sum(v)/tot:.2f}"
             f.write(line + "\n")
             print(line)
-    with open(os.path.join(PROF, f"r1_launches_c4_{tag}.csv"), "w") as f:
+    with open(os.path.join(PROF, f"{RND}_launches_c4_{tag}.csv"), "w") as f:
         f.write("id,kernel,grid,block,ms\n")
         for s in seq:
             f.write(f"{s[0]},{s[1]},\"{s[2]}\",\"{s[3]}\",{s[4]:.4f}\n")
@@ -99,7 +100,7 @@ def full(rep, tag):
         dur = to_ms(r[ci["gpu__time_duration.sum"]], rows[1][ci["gpu__time_duration.sum"]])
         if dur > best.get(key, 0):          # the main launch of a kernel that also has a short seed launch
             best[key], traffic[key] = dur, t
-    open(os.path.join(PROF, f"r1_ncu_summary_c4_{tag}.txt"), "w").write("\n".join(out))
+    open(os.path.join(PROF, f"{RND}_ncu_summary_c4_{tag}.txt"), "w").write("\n".join(out))
     json.dump(traffic, open(os.path.join(PROF, "ncu_traffic.json"), "w"), indent=1)
     print("\n".join(out))
     print(traffic)
