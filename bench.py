@@ -411,12 +411,16 @@ def main():
         h2d = q_host.numel() * 4 + qp_h.numel() * 4 + qt_h.numel() * 4 + qv_h.numel() * 8
         d2h = args.batch * k * (8 + 8) + args.batch * 4
         qn, qpn, qtn, qvn = q_host.numpy(), qp_h.numpy(), qt_h.numpy(), qv_h.numpy()
+        # result buffers of a serving loop: pinned, reused by every call
+        out_pin = (torch.empty((args.batch, k), dtype=torch.float64).pin_memory().numpy(),
+                   torch.empty((args.batch, k), dtype=torch.int64).pin_memory().numpy(),
+                   torch.empty((args.batch,), dtype=torch.int32).pin_memory().numpy())
         if world == 1:
             def step_host():
-                return eng.hybrid_topk("dense", "sparse", qn, qpn, qtn, qvn, k, mask_id=mask_id)
+                return eng.hybrid_topk("dense", "sparse", qn, qpn, qtn, qvn, k, mask_id=mask_id, max_terms=mt, out=out_pin)
         elif args.exchange == "peer":
             def step_host():        # every rank: H2D of the batch, sharded call, D2H of the (identical) result
-                return sh.hybrid_topk("dense", "sparse", qn, qpn, qtn, qvn, k, mask_id=mask_id)
+                return sh.hybrid_topk("dense", "sparse", qn, qpn, qtn, qvn, k, mask_id=mask_id, max_terms=mt, out=out_pin)
         else:
             def step_host():
                 s, i, c = sh.hybrid_topk("dense", "sparse", q_host.to(dev, non_blocking=True),

@@ -271,11 +271,22 @@ class Engine:
         return (dev, np.ascontiguousarray(Q, dtype=np.float32), np.ascontiguousarray(q_ptr, dtype=np.int32),
                 np.ascontiguousarray(q_terms, dtype=np.int32), np.ascontiguousarray(q_vals, dtype=np.float64))
 
+    @staticmethod
+    def _check_out(out, B, k):
+        s, i, c = out
+        ok = (s.shape == (B, k) and i.shape == (B, k) and c.shape == (B,) and str(s.dtype).endswith("float64") and
+              str(i.dtype).endswith("int64") and str(c.dtype).endswith("int32"))
+        if not ok:
+            raise ValueError("out must be (float64 [B,k], int64 [B,k], int32 [B]) buffers, C-contiguous")
+        return s, i, c
+
     def hybrid_topk(self, dense_name: str, sparse_name: str, Q, q_ptr, q_terms, q_vals, k: int, mask_id: int = 0,
-                    max_terms: int = -1):
+                    max_terms: int = -1, out=None):
+        """out: optional (scores, ids, counts) buffers to write into and return -- a serving loop reuses (pinned) result
+        buffers instead of paying for fresh pages on every call."""
         dev, Q, q_ptr, q_terms, q_vals = self._hybrid_inputs(Q, q_ptr, q_terms, q_vals)
         B = Q.shape[0]
-        s, i, c = self._outs(B, k, dev, "f64")
+        s, i, c = self._check_out(out, B, k) if out is not None else self._outs(B, k, dev, "f64")
         _native.check(self._lib.brag_hybrid_topk(self._h, dense_name.encode(), sparse_name.encode(), _ptr(Q), _ptr(q_ptr),
                                                  _ptr(q_terms), _ptr(q_vals), B, k, mask_id, int(max_terms), _ptr(s),
                                                  _ptr(i), _ptr(c), int(dev), _stream() if dev else None))
@@ -339,11 +350,11 @@ class Engine:
             _native.check(self._lib.brag_shard_connect(self._h, rank, world, blob, None))
 
     def shard_hybrid_topk(self, dense_name: str, sparse_name: str, Q, q_ptr, q_terms, q_vals, k: int, mask_id: int = 0,
-                          max_terms: int = -1, stages: bool = False):
+                          max_terms: int = -1, stages: bool = False, out=None):
         """Every rank calls this with the same batch, in the same order; identical result on every rank."""
         dev, Q, q_ptr, q_terms, q_vals = self._hybrid_inputs(Q, q_ptr, q_terms, q_vals)
         B = Q.shape[0]
-        s, i, c = self._outs(B, k, dev, "f64")
+        s, i, c = self._check_out(out, B, k) if out is not None else self._outs(B, k, dev, "f64")
         ts, ti, tc = self._stage_outs(B, k, dev, stages)
         _native.check(self._lib.brag_shard_hybrid_topk(self._h, dense_name.encode(), sparse_name.encode(), _ptr(Q),
                                                        _ptr(q_ptr), _ptr(q_terms), _ptr(q_vals), B, k, mask_id,

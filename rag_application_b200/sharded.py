@@ -86,12 +86,12 @@ class ShardedHybrid:
         return out.view((self.world,) + tuple(keys.shape))
 
     def hybrid_topk(self, dense_name, sparse_name, Q, q_ptr, q_terms, q_vals, k, mask_id=0, max_terms=-1,
-                    stages=False, exchange=None):
+                    stages=False, exchange=None, out=None):
         """Device tensors in, device tensors out: (rrf scores f64 [B,k], ids [B,k], counts [B]) -- identical on every
         rank -- plus the merged dense / sparse lists when `stages`."""
         if (exchange or self.exchange) == "peer":
             return self.engine.shard_hybrid_topk(dense_name, sparse_name, Q, q_ptr, q_terms, q_vals, k, mask_id,
-                                                 max_terms=max_terms, stages=stages)
+                                                 max_terms=max_terms, stages=stages, out=out)
         keys = self.engine.shard_local_lists(dense_name, sparse_name, Q, q_ptr, q_terms, q_vals, k, mask_id,
                                              max_terms=max_terms)
         return self.engine.shard_fuse(self.gather_keys(keys), k, stages=stages)
