@@ -348,11 +348,11 @@ bm25x_scan_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict_
     const int ns = (int)((n_docs + BM25_SUB - 1) / BM25_SUB);
     const int ns1 = ns + 1;
     const int nt = (ns + SUBS - 1) / SUBS;                    // tiles of SUBS sub-tiles
-    // Seed launch (seed_mode): a SAMPLE that only produces a starting bound.  Work item = seed_qpi queries; warp w
-    // visits seed_tiles tiles spread over the corpus for query item * seed_qpi + w and, in each, scores just the
+    // Seed launch (seed_mode): a SAMPLE that only produces a starting bound.  Work item = seed_qpi queries; seed_tiles
+    // consecutive warps share a query and visit one tile each (tiles spread over the corpus), scoring just the
     // ~k_sel documents with the highest (terms present + terms in their high class) count -- the likely best of the
-    // tile.  The k_sel-th best score it found is a valid lower bound of the query's k_sel-th best overall (those
-    // documents exist), published straight into gthr; no list is written and no histogram is touched, because the
+    // tile.  The k_sel-th best score of the group's lists together is a valid lower bound of the query's k_sel-th best
+    // overall (those documents exist), published straight into gthr; no list is written and no histogram is touched, because the
     // main launch scans every tile, the sampled ones included.  Main launch: tiles [0, nt) in `splits` ranges, work
     // item = (range, query, slot w) claimed by one warp, which takes every nw-th tile of the range starting at the
     // w-th and writes list range * nw + w.  The seed's bound keeps the main launch's first visits from scoring every
@@ -384,12 +384,15 @@ bm25x_scan_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict_
         }
         int q, j_first, j_end, j_stride, slot;
         if (seed_mode) {
-            q = item * seed_qpi + warp;
-            // sampled tiles: seed_tiles of them, evenly spaced, shifted per query so a batch does not pile on one tile
+            // seed_tiles consecutive warps share a query, one sampled tile each (the tiles are evenly spaced and
+            // shifted per query so a batch does not pile on one tile); the first of them combines the lists below
+            const int qi = warp / seed_tiles, ti = warp - qi * seed_tiles;
+            q = item * seed_qpi + qi;
             j_stride = max(1, nt / seed_tiles);
-            j_first = (q * 7) % j_stride; slot = 0;
-            j_end = (warp < seed_qpi && q < B) ? min(nt, j_first + seed_tiles * j_stride) : 0;
-            if (j_end == 0) continue;                      // idle warp of a seed item (no CTA-wide sync below)
+            slot = 0;
+            if (qi >= seed_qpi || q >= B) continue;        // idle warps of a seed item (whole groups: no partner waits)
+            j_first = (q * 7) % j_stride + ti * j_stride;
+            j_end = min(nt, j_first + 1);
         } else {
             const int split = item / B;
             q = item - split * B;
@@ -742,8 +745,41 @@ bm25x_scan_kernel(const int64_t* __restrict__ term_ptr, const uint2* __restrict_
         if (*cntp > lcap - 32) warp_compact(list, cntp, lcap, k_sel, thr, lane);
         flush_pending(fmax(pre_local, pre_g), g_seen);
         if (seed_mode) {
-            warp_compact(list, cntp, lcap, k_sel, thr, lane);
-            publish_bound(gthr, q, (uint32_t)(thr >> 32), xb, lane);   // thr: the k_sel-th best key, 0 if fewer were found
+            warp_compact(list, cntp, lcap, k_sel, thr, lane);          // sorted, best first; *cntp <= k_sel entries
+            if (seed_tiles == 1) {
+                publish_bound(gthr, q, (uint32_t)(thr >> 32), xb, lane);   // thr: the k_sel-th best key, 0 if fewer were found
+                continue;
+            }
+            // the k_sel-th best of the group's lists together: a key's rank in the union is its index in its own list
+            // plus the number of greater keys in the others (binary searches; keys are distinct documents)
+            const int qi = warp / seed_tiles, ti = warp - qi * seed_tiles;
+            asm volatile("bar.sync %0, %1;" ::"r"(2 + qi), "r"(32 * seed_tiles) : "memory");
+            if (ti == 0) {
+                const size_t wb = bx_warp_bytes(MAXT, SUBS, lcap);
+                int tot = 0;
+                for (int t = 0; t < seed_tiles; ++t) tot += *reinterpret_cast<const int*>(reinterpret_cast<const uint8_t*>(cntp) + t * wb);
+                uint32_t found = 0u;
+                if (tot >= k_sel) {
+                    for (int t = 0; t < seed_tiles; ++t) {
+                        const uint64_t* L = reinterpret_cast<const uint64_t*>(reinterpret_cast<const uint8_t*>(list) + t * wb);
+                        const int c = *reinterpret_cast<const int*>(reinterpret_cast<const uint8_t*>(cntp) + t * wb);
+                        for (int i = lane; i < c; i += 32) {
+                            const uint64_t x = L[i];
+                            int r = i;
+                            for (int t2 = 0; t2 < seed_tiles; ++t2) {
+                                if (t2 == t) continue;
+                                const uint64_t* L2 = reinterpret_cast<const uint64_t*>(reinterpret_cast<const uint8_t*>(list) + t2 * wb);
+                                int lo = 0, hi = *reinterpret_cast<const int*>(reinterpret_cast<const uint8_t*>(cntp) + t2 * wb);
+                                while (lo < hi) { const int mid = (lo + hi) >> 1; if (L2[mid] > x) lo = mid + 1; else hi = mid; }
+                                r += lo;
+                            }
+                            if (r == k_sel - 1) found = (uint32_t)(x >> 32);
+                        }
+                    }
+                }
+                found = __reduce_max_sync(0xFFFFFFFFu, found);
+                publish_bound(gthr, q, found, xb, lane);
+            }
             continue;
         }
         // the merge that follows sorts whatever it gathers, so a list of <= k_sel keys leaves unsorted (under a warm
@@ -798,7 +834,9 @@ Bm25Plan bm25x_plan(int64_t n_docs, int B, int k_sel, int max_terms, int num_sms
     // seed launch: BRAG_BX_SEED sampled tiles per query (default 2), when the corpus has tiles to spare
     static const int seed_cfg = [] { const char* e = getenv("BRAG_BX_SEED"); const int v = e ? atoi(e) : 2; return v < 0 ? 0 : (v > 4 ? 4 : v); }();
     p.seed_tiles = (nt >= 32) ? seed_cfg : 0;
-    p.seed_qpi = std::max(1, std::min(p.workers, (B + resident - 1) / resident));
+    // queries per seed item: seed_tiles warps each
+    p.seed_qpi = std::max(1, std::min(p.workers / std::max(1, p.seed_tiles), (B + resident - 1) / resident));
+    if (p.seed_tiles > 1 && (p.workers < p.seed_tiles || p.seed_qpi > 13)) p.seed_tiles = 1;   // named barriers 2 .. 15
     const int nt_main = nt;
     // ranges per query: enough items to keep every SM busy ~8 times over (BRAG_BX_ITEMS_PER_SM overrides; tuning knob)
     static const int items_per_sm = [] { const char* e = getenv("BRAG_BX_ITEMS_PER_SM"); const int v = e ? atoi(e) : 8; return v < 1 ? 1 : (v > 64 ? 64 : v); }();
