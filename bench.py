@@ -531,9 +531,11 @@ def main():
                          f"{ns}/{args.n} (cost linear in N); the --impl reference arm times the same sample"}
 
     if rank == 0:
-        dense_ms = stage_ms["dense_scan"] / max(1, stage_calls["dense_scan"])
+        # the main launch runs once per group of <= 1024 queries (4 at C5's batch 4096): per-launch figures
+        groups = (args.batch + 1023) // 1024
+        dense_ms = stage_ms["dense_scan"] / args.steps / groups
         n_scan = n_loc * (sel_real if sel_real else 1.0)          # rows the tensor-core scan really multiplies
-        flops = 2.0 * n_scan * args.d * args.batch
+        flops = 2.0 * n_scan * args.d * args.batch / groups
         ach = flops / (dense_ms * 1e-3) / 1e12 if dense_ms > 0 else 0.0
         bm_ms = stage_ms["sparse_scan"] / max(1, stage_calls["sparse_scan"])
         bm_bytes = bm25_bytes * (sel_real if sel_real else 1.0)   # postings of the documents that pass the filter
