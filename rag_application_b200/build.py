@@ -11,7 +11,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(CSRC, "libbrag.so")
 SOURCES = ["engine.cu", "dense_gemv.cu", "dense_umma.cu", "bm25.cu", "bm25x.cu", "select.cu", "shard.cu", "compact.cu", "rerank.cu", "bm25_encode.cu"]
-HEADERS = ["common.cuh", "kernels.h", "bm25_common.cuh", "rrf.cuh", "rescore.cuh", os.path.join("..", "..", "include", "brag.h")]
+HEADERS = ["common.cuh", "kernels.h", "bm25_common.cuh", "rrf.cuh", "rescore.cuh", "shard_push.cuh", os.path.join("..", "..", "include", "brag.h")]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
     "--expt-extended-lambda", "-Xcompiler", "-fPIC",

@@ -28,6 +28,7 @@
 #include "common.cuh"
 #include "kernels.h"
 #include "rescore.cuh"
+#include "shard_push.cuh"
 
 namespace brag {
 
@@ -568,8 +569,9 @@ um_seed_bound_kernel(const float4* __restrict__ seedv, int seed_tiles, int q_lo,
 //      GPU), sorted, the best k_sel kept;
 //   3. those re-scored exactly: float64 dot of the stored row with the caller's float32 query (rescore.cuh), one warp
 //      per candidate;
-//   4. either the re-scored keys (local rows) to keys_out [B][k_sel] -- sharded calls and filter-compacted copies go
-//      on from there -- or, when keys_out is NULL, the final list itself: sorted, unpacked, ids offset, count.
+//   4. the re-scored keys (local rows) to keys_out [B][k_sel] (filter-compacted copies go on from there: their rows
+//      still need the map back), or the final list itself by rank: unpacked with the id offset and the count, or --
+//      sharded calls -- its best k keys with global rows straight into every rank's window (sink).
 constexpr int SELK_MAX_THREADS = 1024;   // launched with 512 threads, 1024 for batches of <= 64 queries (the re-score is
                                          // one warp per candidate: a small batch has no other CTAs to hide its latency)
 constexpr int SELK_CAP = 2048;     // keys gathered per query (16 KB: four CTAs per SM); a few hundred reach the bound
@@ -586,7 +588,7 @@ dense_umma_tail_kernel(const uint64_t* __restrict__ lists, const int* __restrict
                        uint32_t* __restrict__ gthr, const ShardBounds xb, int n_chunks, int B, int qb_base, int n_qblocks,
                        int k_sel, const void* __restrict__ X, int dtype, int64_t n, int d, const float* __restrict__ Q,
                        uint64_t* __restrict__ keys_out, int k, int64_t id_offset, float* __restrict__ out_scores,
-                       int64_t* __restrict__ out_ids, int32_t* __restrict__ out_counts) {
+                       int64_t* __restrict__ out_ids, int32_t* __restrict__ out_counts, const ShardSink sink) {
     extern __shared__ __align__(16) uint8_t smem_raw[];
     uint64_t* a = reinterpret_cast<uint64_t*>(smem_raw);
     uint64_t* res = a + SELK_CAP;
@@ -694,6 +696,21 @@ dense_umma_tail_kernel(const uint64_t* __restrict__ lists, const int* __restrict
         return;
     }
     // final order by rank again (a re-scored key keeps its row, so keys stay distinct; 0 = a row that did not exist)
+    if (sink.on) {
+        int nz = 0;
+        for (int i = tid; i < n_res; i += SELK_THREADS) nz += res[i] != 0ull ? 1 : 0;
+        if (nz) atomicAdd(&count, nz);
+        __syncthreads();
+        for (int r = count + tid; r < k; r += SELK_THREADS) shard_sink_store(sink, B, b, k, r, 0ull, id_offset);
+        for (int i = tid; i < n_res; i += SELK_THREADS) {
+            const uint64_t x = res[i];
+            if (x == 0ull) continue;
+            int r = 0;
+            for (int j = 0; j < n_res; ++j) r += res[j] > x ? 1 : 0;
+            if (r < k) shard_sink_store(sink, B, b, k, r, x, id_offset);
+        }
+        return;
+    }
     for (int i = tid; i < k; i += SELK_THREADS) {
         out_scores[(size_t)b * k + i] = -INFINITY;
         out_ids[(size_t)b * k + i] = -1;
@@ -902,7 +919,7 @@ cudaError_t dense_umma_tail(int B, int k_sel, void* scratch, const UmmaPlan& pla
     const int nq = std::min(B - qb0 * UM_BM, nqb * UM_BM);
     dense_umma_tail_kernel<<<nq, B <= 64 ? 1024 : 512, (SELK_CAP + SELK_RES) * 8, st>>>(
         u.lists, u.counts, u.coarse, u.fine, u.gthr, xb, plan.n_chunks, B, qb0, nqb, k_sel, t.X, t.dtype, t.n, t.d, t.Q,
-        t.keys_out, t.k, t.id_offset, t.out_scores, t.out_ids, t.out_counts);
+        t.keys_out, t.k, t.id_offset, t.out_scores, t.out_ids, t.out_counts, t.sink);
     return cudaGetLastError();
 }
 

@@ -539,9 +539,14 @@ void dense_topk_dev(brag_engine* e, DenseSpace& s, const float* Q, int B, int k,
         brag::UmmaTail tail;
         tail.X = X; tail.dtype = s.dtype; tail.n = n; tail.d = s.d; tail.Q = Q;
         tail.k = k; tail.id_offset = e->id_offset;
-        finished = !compact && !sink;      // otherwise the re-scored keys go on to the row remap / the shard push
-        if (finished) { tail.out_scores = out_scores; tail.out_ids = out_ids; tail.out_counts = out_counts; }
-        else tail.keys_out = cand2;
+        finished = !compact;               // a compacted copy's keys still need the map back to the space's rows
+        if (finished && sink) {
+            tail.sink.on = 1; tail.sink.list = sink->list; tail.sink.local_out = sink->local_out; tail.sink.push = sink->push;
+        } else if (finished) {
+            tail.out_scores = out_scores; tail.out_ids = out_ids; tail.out_counts = out_counts;
+        } else {
+            tail.keys_out = cand2;
+        }
         for (int g = 0; g < brag::dense_umma_groups(plan); ++g) {
             {
                 if (!t0) t0.emplace(e, 0, st);
@@ -683,18 +688,19 @@ void sparse_topk_dev(brag_engine* e, SparseSpace& full, const int32_t* q_ptr, co
         uint32_t* gthr = reinterpret_cast<uint32_t*>(sp + 256);
         const uint32_t* coarse = reinterpret_cast<const uint32_t*>(sp + 256 + plan.gthr_bytes);
         const uint32_t* fine = reinterpret_cast<const uint32_t*>(sp + 256 + plan.gthr_bytes + plan.coarse_bytes);
-        const bool finished = !compact && !sink;
+        const bool finished = !compact;        // a compacted index's keys still need the map back to the space's rows
+        brag::ShardSink sk;
+        if (finished && sink) { sk.on = 1; sk.list = sink->list; sk.local_out = sink->local_out; sk.push = sink->push; }
         CK(brag::sparse_tail(part, P, B, k, coarse, fine, gthr, xb, k, finished ? nullptr : merged, e->id_offset, out_scores,
-                             out_ids, out_counts, st));
-        if (compact) {
+                             out_ids, out_counts, sk, st));
+        if (!finished) {
             CK(brag::remap_keys(merged, (int64_t)B * k, full.cp_rowmap, st));
-            launches += 1;
+            if (sink)
+                CK(brag::shard_finalize_push(merged, B, k, k, e->id_offset, sink->list, sink->local_out, sink->push, st));
+            else
+                CK(brag::finalize_keys(merged, B, k, k, false, e->id_offset, out_scores, out_ids, out_counts, st));
+            launches += 2;
         }
-        if (sink)
-            CK(brag::shard_finalize_push(merged, B, k, k, e->id_offset, sink->list, sink->local_out, sink->push, st));
-        else if (!finished)
-            CK(brag::finalize_keys(merged, B, k, k, false, e->id_offset, out_scores, out_ids, out_counts, st));
-        launches += finished ? 0 : 1;
         e->kernel_launches += launches + 1;
     }
 }

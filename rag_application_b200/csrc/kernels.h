@@ -5,7 +5,22 @@
 
 namespace brag {
 
-struct ShardBounds;     // common.cuh: cross-shard bound exchange of a sharded call (default = none)
+struct ShardBounds;
+// Destination of a sharded call's ranked lists (shard.cu): every rank's peer-mapped window.
+struct ShardPush {
+    uint8_t* const* windows = nullptr;    // device table [world] of window bases (windows[rank] = own)
+    const unsigned* epoch = nullptr;
+    int world = 0, rank = 0;
+    size_t slots_off = 0, slot_bytes = 0, flags_off = 0;
+};
+// What a scan's tail kernel does with a query's final list in a sharded call: the best k keys, rows made global, into
+// local_out [2][B][k] (collective variant) or into slot (epoch parity, rank) of every rank's window (shard_push.cuh).
+struct ShardSink {
+    int on = 0;
+    int list = 0;                          // 0 dense, 1 sparse
+    uint64_t* local_out = nullptr;
+    ShardPush push;
+};     // common.cuh: cross-shard bound exchange of a sharded call (default = none)
 
 // Per-device kernel attributes (opt-in shared memory): brag_create calls these with the engine's device current, so a
 // second engine on another GPU of the same process gets them too.
@@ -55,6 +70,7 @@ struct UmmaTail {
     int d = 0;
     const float* Q = nullptr;       // [B, d] the caller's float32 queries
     uint64_t* keys_out = nullptr;   // [B][k_sel] re-scored keys with local rows; NULL = write the final list below
+    ShardSink sink;                 // sharded call (sink.on): the final list goes to the windows instead
     int k = 0;
     int64_t id_offset = 0;
     float* out_scores = nullptr;    // [B][k]
@@ -78,7 +94,7 @@ cudaError_t publish_bounds(const uint32_t* coarse, const uint32_t* fine, uint32_
 // its best k keys with local rows (keys_out [B][k])
 cudaError_t sparse_tail(const uint64_t* part, int P, int B, int kk, const uint32_t* coarse, const uint32_t* fine,
                         uint32_t* gthr, const ShardBounds& xb, int k, uint64_t* keys_out, int64_t id_offset,
-                        float* out_scores, int64_t* out_ids, int32_t* out_counts, cudaStream_t st);
+                        float* out_scores, int64_t* out_ids, int32_t* out_counts, const ShardSink& sink, cudaStream_t st);
 size_t merge_tmp_elems(int P, int B, int kk);
 // the tensor-core scan's copy of the queries in the stored element type, [Bpad, d] with zero padding rows
 // (dtype 3 also writes qinv[B], the inverse norms of the int8 queries)
@@ -115,12 +131,6 @@ struct ShardWindowLayout {
     size_t total;
 };
 ShardWindowLayout shard_window_layout(int world, int max_batch, int max_k);
-struct ShardPush {
-    uint8_t* const* windows = nullptr;    // device table [world] of window bases (windows[rank] = own)
-    const unsigned* epoch = nullptr;
-    int world = 0, rank = 0;
-    size_t slots_off = 0, slot_bytes = 0, flags_off = 0;
-};
 cudaError_t shard_next_epoch(unsigned* epoch, cudaStream_t st);
 // keys [B][m] (local rows) -> best k per query as keys with global rows, into local_out [2][B][k] (list `list`) or,
 // when local_out is NULL, into slot (epoch parity, rank) of every rank's window

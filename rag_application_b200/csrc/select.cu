@@ -6,6 +6,7 @@
 #include "kernels.h"
 #include "rrf.cuh"
 #include "rescore.cuh"
+#include "shard_push.cuh"
 
 namespace brag {
 
@@ -69,7 +70,7 @@ __global__ void __launch_bounds__(1024)
 sparse_tail_kernel(const uint64_t* __restrict__ part, int P, int B, int kk, const uint32_t* __restrict__ coarse,
                    const uint32_t* __restrict__ fine, uint32_t* __restrict__ gthr, const ShardBounds xb, int k,
                    uint64_t* __restrict__ keys_out, int64_t id_offset, float* __restrict__ out_scores,
-                   int64_t* __restrict__ out_ids, int32_t* __restrict__ out_counts) {
+                   int64_t* __restrict__ out_ids, int32_t* __restrict__ out_counts, const ShardSink sink) {
     extern __shared__ __align__(16) uint8_t smem_raw[];
     uint64_t* a = reinterpret_cast<uint64_t*>(smem_raw);
     __shared__ int fill, count;
@@ -127,7 +128,9 @@ sparse_tail_kernel(const uint64_t* __restrict__ part, int P, int B, int kk, cons
         bitonic_desc(a, n2, tid, NT, [] { __syncthreads(); });
     }
     const int n_out = min(f, k);
-    if (keys_out != nullptr) {
+    if (sink.on) {
+        for (int i = n_out + tid; i < k; i += NT) shard_sink_store(sink, B, b, k, i, 0ull, id_offset);
+    } else if (keys_out != nullptr) {
         for (int i = n_out + tid; i < k; i += NT) keys_out[(size_t)b * k + i] = 0ull;
     } else {
         for (int i = n_out + tid; i < k; i += NT) { out_scores[(size_t)b * k + i] = -INFINITY; out_ids[(size_t)b * k + i] = -1; }
@@ -141,7 +144,8 @@ sparse_tail_kernel(const uint64_t* __restrict__ part, int P, int B, int kk, cons
             for (int j = 0; j < f; ++j) r += a[j] > x ? 1 : 0;
         }
         if (r >= k) continue;
-        if (keys_out != nullptr) keys_out[(size_t)b * k + r] = x;
+        if (sink.on) shard_sink_store(sink, B, b, k, r, x, id_offset);
+        else if (keys_out != nullptr) keys_out[(size_t)b * k + r] = x;
         else {
             out_scores[(size_t)b * k + r] = key_score(x);
             out_ids[(size_t)b * k + r] = (int64_t)key_row(x) + id_offset;
@@ -151,10 +155,10 @@ sparse_tail_kernel(const uint64_t* __restrict__ part, int P, int B, int kk, cons
 
 cudaError_t sparse_tail(const uint64_t* part, int P, int B, int kk, const uint32_t* coarse, const uint32_t* fine,
                         uint32_t* gthr, const ShardBounds& xb, int k, uint64_t* keys_out, int64_t id_offset,
-                        float* out_scores, int64_t* out_ids, int32_t* out_counts, cudaStream_t st) {
+                        float* out_scores, int64_t* out_ids, int32_t* out_counts, const ShardSink& sink, cudaStream_t st) {
     if (kk > STAIL_CAP / 2 || k > STAIL_CAP / 2 || k > kk) return cudaErrorInvalidValue;
     sparse_tail_kernel<<<B, B <= 64 ? 1024 : 512, STAIL_CAP * 8, st>>>(part, P, B, kk, coarse, fine, gthr, xb, k, keys_out,
-                                                                     id_offset, out_scores, out_ids, out_counts);
+                                                                     id_offset, out_scores, out_ids, out_counts, sink);
     return cudaGetLastError();
 }
 

@@ -38,6 +38,26 @@ def test_dense_random_shapes_match_oracle(engine, n, d, k, B, dtype, sel, seed):
 
 
 @settings(max_examples=20, **COMMON)
+@given(n=st.integers(1, 4096), d=st.sampled_from([128, 384, 768, 1024]), k=st.integers(1, 128),
+       B=st.sampled_from([1, 2, 9, 70]), sel=st.sampled_from([None, 0.05, 0.5, 0.9]), seed=st.integers(0, 2 ** 16))
+def test_int8_random_shapes_match_oracle_bit_for_bit(engine, n, d, k, B, sel, seed):
+    """SURVEY 8 a9 on drawn shapes: int8 rows, integer dots -- ids, counts and score bits equal the oracle's."""
+    x = O.normalize_rows(synth.dense_corpus(n, d, seed=seed, clustered=bool(seed & 1)))
+    q = O.normalize_rows(synth.dense_queries(x, B, seed=seed + 1))
+    xi, qi = O.quantize_int8(x).astype(np.float32), O.quantize_int8(q).astype(np.float32)
+    engine.dense_set("h8", xi, "i8")
+    mask = None
+    if sel is not None:
+        mask = synth.random_mask(n, sel, seed=seed + 2)
+        engine.mask_set(9, mask)
+    s, i, c = engine.dense_topk("h8", qi, k, mask_id=9 if mask is not None else 0)
+    for b in range(0, B, max(1, B // 3)):
+        es, ei = O.dense_topk(xi, qi[b], k, mask=mask, int8=True)
+        assert int(c[b]) == len(ei) and np.array_equal(i[b][:len(ei)], ei)
+        assert np.array_equal(s[b][:len(ei)].view(np.uint32), es.view(np.uint32))
+
+
+@settings(max_examples=20, **COMMON)
 @given(n_docs=st.integers(1, 30000), V=st.integers(1, 3000), L=st.integers(1, 80), k=st.integers(1, 128),
        B=st.sampled_from([1, 5, 40]), nt=st.integers(1, 20), path=st.sampled_from(["scatter", "bitmap", None]),
        sel=st.sampled_from([None, 0.1, 0.7]), neg=st.booleans(), seed=st.integers(0, 2 ** 16))
