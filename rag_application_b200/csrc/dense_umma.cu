@@ -49,7 +49,6 @@ constexpr int UM_A_BYTES = UM_BM * UM_BK * 2;  // 16 KB
 constexpr int UM_B_BYTES = UM_BN * UM_BK * 2;  // 32 KB
 constexpr uint32_t UM_TMEM_COLS = 512;
 constexpr int UM_MAXQB = 8;            // query blocks (x128 queries) one launch covers
-constexpr int UM_SEL_CAP = 4096;       // keys per CTA sort in the final per-query selection
 
 struct UmSmem {
     uint8_t a[UM_STAGES][UM_A_BYTES];
@@ -174,13 +173,6 @@ __device__ __forceinline__ uint32_t sel32(const uint32_t (&v)[32], int i) {
 #pragma unroll
     for (int j = 0; j < 2; ++j) d[j] = (i & 8) ? c[2 * j + 1] : c[2 * j];
     return (i & 16) ? d[1] : d[0];
-}
-
-__device__ __forceinline__ uint32_t tmem_ld1(uint32_t taddr) {
-    uint32_t r;
-    asm volatile("tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];\n\ttcgen05.wait::ld.sync.aligned;"
-                 : "=r"(r) : "r"(taddr) : "memory");
-    return r;
 }
 
 // K-major, 128-byte swizzle: 8-row groups are 1024 B apart (SBO); LBO unused; version 1; layout 2.
@@ -547,16 +539,48 @@ dense_umma_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_const
 __global__ void __launch_bounds__(256)
 um_seed_bound_kernel(const float4* __restrict__ seedv, int seed_tiles, int q_lo, int q_hi, int k_sel,
                      uint32_t* __restrict__ gthr) {
+    // k_sel-th largest of <= 1024 ordered-float images by radix select, 8 bits per pass: histogram of the current
+    // digit over the values that still match the prefix, then the digit whose suffix count crosses the rank
+    // (4 passes x 3 barriers; the bitonic sort this replaces took 55)
     __shared__ uint32_t a[1024];
+    __shared__ uint32_t hist[256];
+    __shared__ uint32_t s_prefix, s_rank;
     const int q = q_lo + (int)blockIdx.x;
     if (q >= q_hi) return;
-    const int nv = seed_tiles * 4;
+    const int tid = threadIdx.x;
+    const int nv = min(seed_tiles * 4, 1024);
+    if (nv < k_sel) return;
     const float* src = reinterpret_cast<const float*>(seedv + (size_t)q * seed_tiles);
-    for (int i = threadIdx.x; i < 1024; i += 256) a[i] = (i < nv) ? f32_ordered(src[i]) : 0u;
-    __syncthreads();
-    bitonic_desc(a, 1024, (int)threadIdx.x, 256, [] { __syncthreads(); });
-    if (threadIdx.x == 0 && nv >= k_sel) {
-        const uint32_t v = a[k_sel - 1];
+    for (int i = tid; i < nv; i += 256) a[i] = f32_ordered(src[i]);
+    if (tid == 0) { s_prefix = 0u; s_rank = (uint32_t)k_sel; }      // rank counted from the top, 1-based
+    for (int shift = 24; shift >= 0; shift -= 8) {
+        hist[tid] = 0u;
+        __syncthreads();
+        const uint32_t prefix = s_prefix, himask = shift == 24 ? 0u : (0xFFFFFFFFu << (shift + 8));
+        for (int i = tid; i < nv; i += 256)
+            if ((a[i] & himask) == prefix) atomicAdd(&hist[(a[i] >> shift) & 255u], 1u);
+        __syncthreads();
+        if (tid < 32) {
+            // lane l owns digits 8l .. 8l+7; suffix counts from the top digit down
+            uint32_t own = 0u, c[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) { c[j] = hist[tid * 8 + j]; own += c[j]; }
+            const uint32_t suf = warp_suffix_sum(own, tid);          // values in digits >= 8 * tid
+            const uint32_t rank = s_rank;
+            const unsigned has = __ballot_sync(0xFFFFFFFFu, suf >= rank);
+            const int L = 31 - __clz(has);                           // has != 0: the prefix class holds >= rank values
+            if (tid == L) {
+                uint32_t above = suf - own;                          // values in digits above this lane's
+                int dgt = 7;
+                for (; dgt > 0; --dgt) { if (above + c[dgt] >= rank) break; above += c[dgt]; }
+                s_prefix = prefix | ((uint32_t)(tid * 8 + dgt) << shift);
+                s_rank = rank - above;
+            }
+        }
+        __syncthreads();
+    }
+    if (tid == 0) {
+        const uint32_t v = s_prefix;
         if (v > f32_ordered(-INFINITY)) atomicMax(gthr + q, v);
     }
 }
@@ -912,7 +936,7 @@ cudaError_t dense_umma_scan(int dtype, int64_t n, int d, int B, const uint32_t* 
 
 cudaError_t dense_umma_tail(int B, int k_sel, void* scratch, const UmmaPlan& plan, int group, const UmmaTail& t,
                             cudaStream_t st, const ShardBounds& xb) {
-    if (plan.n_chunks > SELK_MAXCHUNKS * 64 || k_sel > SELK_RES || t.k > SELK_RES) return cudaErrorInvalidValue;
+    if (k_sel > SELK_RES || t.k > SELK_RES) return cudaErrorInvalidValue;
     const UmScratch u = um_scratch(scratch, plan);
     const int qb0 = group * UM_MAXQB;
     const int nqb = std::min(UM_MAXQB, plan.n_qblocks - qb0);

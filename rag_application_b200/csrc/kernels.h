@@ -87,9 +87,6 @@ cudaError_t make_tmap_2d(void* tmap_out, const void* base, int64_t rows, int d, 
 // bound (optional, [B], f32_ordered units): keys whose score image is below it are dropped before sorting
 cudaError_t merge_key_lists(const uint64_t* in, int P, int B, int kk, uint64_t* tmp_a, uint64_t* tmp_b,
                             uint64_t* out, int kout, cudaStream_t st, int* launches, const uint32_t* bound = nullptr);
-// gthr[q] = max(gthr[q], bound of query q's complete score histograms) -- see common.cuh
-cudaError_t publish_bounds(const uint32_t* coarse, const uint32_t* fine, uint32_t* gthr, int B, int k, cudaStream_t st,
-                           const ShardBounds& xb);
 // tail of a sparse scan (select.cu): final bound + merge of the P lists [P][B][kk] + the final list (keys_out NULL) or
 // its best k keys with local rows (keys_out [B][k])
 cudaError_t sparse_tail(const uint64_t* part, int P, int B, int kk, const uint32_t* coarse, const uint32_t* fine,

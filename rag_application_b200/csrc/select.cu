@@ -162,21 +162,6 @@ cudaError_t sparse_tail(const uint64_t* part, int P, int B, int kk, const uint32
     return cudaGetLastError();
 }
 
-// One warp per query: bound = highest histogram edge that at least k counted rows reach (common.cuh), published
-// with atomicMax.  Run after a scan so that the selection sees the bound of the COMPLETE histograms.
-__global__ void publish_bounds_kernel(const uint32_t* __restrict__ coarse, const uint32_t* __restrict__ fine,
-                                      uint32_t* __restrict__ gthr, int B, int k, const ShardBounds xb) {
-    const int q = (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5);
-    if (q >= B) return;
-    publish_bound(gthr, q, hist_bound(coarse, fine, q, (uint32_t)k, (int)(threadIdx.x & 31)), xb, (int)(threadIdx.x & 31));
-}
-
-cudaError_t publish_bounds(const uint32_t* coarse, const uint32_t* fine, uint32_t* gthr, int B, int k, cudaStream_t st,
-                           const ShardBounds& xb) {
-    publish_bounds_kernel<<<(B + 7) / 8, 256, 0, st>>>(coarse, fine, gthr, B, k, xb);
-    return cudaGetLastError();
-}
-
 size_t merge_tmp_elems(int P, int B, int kk) {
     int GP = max(2, SEL_MAX / kk);
     int PG = (P + GP - 1) / GP;
