@@ -391,6 +391,7 @@ class B200QdrantCore:
         self._lock = threading.RLock()
         self._next_mask = 1
         self._mask_owner: Dict[int, Tuple[str, Any]] = {}
+        self._qcache: Dict[Tuple[int, Any], np.ndarray] = {}
 
     def close(self):
         self.engine.close()
@@ -629,10 +630,16 @@ class B200QdrantCore:
             if using not in col.dense_cfg:
                 raise ValueError(f"Not existing vector name error: {using}")
             size, dist, storage = col.dense_cfg[using]
-            q = np.asarray(query, dtype=np.float32).reshape(1, -1)
-            if q.shape[1] != size:
-                raise ValueError(f"query for {using!r}: expected dim {size}, got {q.shape[1]}")
-            q = _prep_rows(q, dist, storage)
+            # the reference passes the SAME Python list to several nodes of one request (qdrant_handler.py:330,346,363:
+            # `dense_vector` three times): converting and normalising a 768-float list costs ~40 us, so once per request
+            ck = (id(query), using)
+            q = self._qcache.get(ck)
+            if q is None:
+                q = np.asarray(query, dtype=np.float32).reshape(1, -1)
+                if q.shape[1] != size:
+                    raise ValueError(f"query for {using!r}: expected dim {size}, got {q.shape[1]}")
+                q = _prep_rows(q, dist, storage)
+                self._qcache[ck] = q
             max_k = self.ENGINE_MAX_K_I8 if storage == "i8" else self.ENGINE_MAX_K
             present = col.present.get(using)
             if present is not None and not present.any():
@@ -679,7 +686,11 @@ class B200QdrantCore:
             col = self._col(collection_name)
             col.commit(self.engine)
             off = int(offset or 0)
-            s, r = self._run(col, query, using, int(limit) + off, prefetch, query_filter)
+            self._qcache = {}                  # prepared dense queries of this request (the tree keeps its lists alive)
+            try:
+                s, r = self._run(col, query, using, int(limit) + off, prefetch, query_filter)
+            finally:
+                self._qcache = {}
             if score_threshold is not None:
                 keep = s >= score_threshold
                 s, r = s[keep], r[keep]
