@@ -152,7 +152,8 @@ int brag_hybrid_topk(brag_engine* e, const char* dense_name, const char* sparse_
  * row), 0 = empty slot: [2 lists (dense, sparse)][B][k].
  *
  * Collective variant (any transport): brag_shard_local_lists on every rank -> all-gather of the key arrays ->
- * brag_shard_fuse on every rank (merge of the G dense lists, merge of the G sparse lists, RRF of the two; one kernel).
+ * brag_shard_fuse on every rank (merge of the G dense lists, merge of the G sparse lists, RRF of the two; one kernel;
+ * it relies on what brag_shard_local_lists writes: every list sorted best first, empties last, rows disjoint across shards).
  * stage_* (all three or none): the two merged lists, [2][B][k] scores / ids and [2][B] counts. */
 int brag_shard_local_lists(brag_engine* e, const char* dense_name, const char* sparse_name, const float* Q,
                            const int32_t* q_ptr, const int32_t* q_terms, const double* q_vals, int32_t B, int32_t k,

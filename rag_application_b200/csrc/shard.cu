@@ -152,34 +152,54 @@ shard_fuse_kernel(const uint64_t* __restrict__ gathered, const ShardPush win, in
     if (tid == 0) n_unique = 0;
     __syncthreads();
     for (int l = 0; l < 2; ++l) {
-        for (int i = tid; i < n2; i += SHF_THREADS) {
-            uint64_t v = 0ull;
-            if (i < n_in) {
-                const int g = i / k, j = i - g * k;
-                const uint64_t* src = gathered != nullptr
-                    ? gathered + (((size_t)g * 2 + l) * B + b) * k
-                    : reinterpret_cast<const uint64_t*>(slots + (size_t)g * win.slot_bytes) + ((size_t)l * B + b) * k;
-                v = gathered != nullptr ? src[j] : __ldcv(src + j);     // peers wrote the window: never a cached copy
+        for (int i = tid; i < n_in; i += SHF_THREADS) {
+            const int g = i / k, j = i - g * k;
+            const uint64_t* src = gathered != nullptr
+                ? gathered + (((size_t)g * 2 + l) * B + b) * k
+                : reinterpret_cast<const uint64_t*>(slots + (size_t)g * win.slot_bytes) + ((size_t)l * B + b) * k;
+            a[i] = gathered != nullptr ? src[j] : __ldcv(src + j);     // peers wrote the window: never a cached copy
+        }
+        if (tid == 0) s_cnt[l] = 0;
+        __syncthreads();
+        // Every shard's list arrives sorted (best first, empties last) and rows are disjoint across shards, so a key's
+        // place in the merged list is its index in its own list plus the number of greater keys in each other list
+        // (a binary search per list): no sort.  (Was a bitonic sort of G * k keys per list.)
+        if (tid < G) {
+            const uint64_t* L = a + tid * k;
+            int lo = 0, hi = k;                              // first empty slot of shard tid's list
+            while (lo < hi) { const int mid = (lo + hi) >> 1; if (L[mid] != 0ull) lo = mid + 1; else hi = mid; }
+            atomicAdd(&s_cnt[l], lo);
+        }
+        for (int i = tid; i < k; i += SHF_THREADS) {
+            fid[l * k + i] = -1;
+            if (stage_scores != nullptr) {
+                stage_scores[((size_t)l * B + b) * k + i] = -INFINITY;
+                stage_ids[((size_t)l * B + b) * k + i] = -1;
             }
-            a[i] = v;
         }
         __syncthreads();
-        bitonic_desc(a, n2, tid, SHF_THREADS, [] { __syncthreads(); });
-        // equal keys cannot come from different shards (rows are disjoint); the first k non-empty keys are the list
-        for (int i = tid; i < k; i += SHF_THREADS) {
-            const uint64_t key = i < n2 ? a[i] : 0ull;
-            const bool ok = key != 0ull;
-            fid[l * k + i] = ok ? (int64_t)key_row(key) : -1;
-            if (stage_scores != nullptr) {
-                stage_scores[((size_t)l * B + b) * k + i] = ok ? key_score(key) : -INFINITY;
-                stage_ids[((size_t)l * B + b) * k + i] = ok ? (int64_t)key_row(key) : -1;
+        for (int i = tid; i < n_in; i += SHF_THREADS) {
+            const uint64_t key = a[i];
+            if (key == 0ull) continue;
+            const int g = i / k;
+            int r = i - g * k;
+            for (int g2 = 0; g2 < G && r < k; ++g2) {
+                if (g2 == g) continue;
+                const uint64_t* L = a + g2 * k;
+                int lo = 0, hi = k;                          // keys of shard g2 greater than this one
+                while (lo < hi) { const int mid = (lo + hi) >> 1; if (L[mid] > key) lo = mid + 1; else hi = mid; }
+                r += lo;
+            }
+            if (r < k) {
+                fid[l * k + r] = (int64_t)key_row(key);
+                if (stage_scores != nullptr) {
+                    stage_scores[((size_t)l * B + b) * k + r] = key_score(key);
+                    stage_ids[((size_t)l * B + b) * k + r] = (int64_t)key_row(key);
+                }
             }
         }
-        if (tid == 0) {                                     // keys are sorted, empties last
-            int lo = 0, hi = min(k, n2);                    // first empty slot among the best k
-            while (lo < hi) { const int mid = (lo + hi) >> 1; if (a[mid] != 0ull) lo = mid + 1; else hi = mid; }
-            s_cnt[l] = lo;
-        }
+        __syncthreads();
+        if (tid == 0) s_cnt[l] = min(s_cnt[l], k);
         __syncthreads();
     }
     // compact the two lists to [c0 | c1] with their ranks, then fuse
