@@ -102,6 +102,19 @@ int brag_dense_rescore(brag_engine* e, const char* name, const float* Q, int32_t
                        float* out_scores, int64_t* out_ids, int32_t* out_counts,
                        int32_t on_device, void* stream);
 
+/* Allocation-free variant of brag_dense_rescore.  It has no counterpart in the reference: it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  Same answers as brag_dense_rescore; device pointers only (Q, cand and the three outputs
+ * live on the engine's GPU, Q 16-byte aligned), stream-ordered on `stream`, never synchronises, and calls no
+ * cudaMalloc / cudaFree or any allocating routine: its [B][m] key scratch is a static device array of
+ * BRAG_NOALLOC_MAX_KEYS keys (512 KB that every GPU loading the library holds until exit).  B * m beyond that limit is
+ * refused with an error.  All calls on one GPU share the array: calls that overlap on the GPU (different streams,
+ * different engines on the same device) race -- order them. */
+#define BRAG_NOALLOC_MAX_KEYS 65536
+int brag_dense_rescore_noalloc(brag_engine* e, const char* name, const float* Q, int32_t B,
+                               const int64_t* cand, int32_t m, int32_t k, int32_t mask_id,
+                               float* out_scores, int64_t* out_ids, int32_t* out_counts, void* stream);
+
 /* Sparse (BM25) top-k: Prefetch(query=SparseVector, using=name, limit=k)
  * (qdrant_handler.py:347-354).  Query b owns q_terms/q_vals[q_ptr[b]:q_ptr[b+1]], term rows
  * strictly ascending; q_vals are float64 (Python floats; IDF already applied by the host).

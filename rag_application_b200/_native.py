@@ -31,6 +31,7 @@ PROTOTYPES = {
     "brag_mask_set": (C.c_int, [c_p, i32, c_p, i64, i32]),
     "brag_dense_topk": (C.c_int, [c_p, C.c_char_p, c_p, i32, i32, i32, c_p, c_p, c_p, i32, c_p]),
     "brag_dense_rescore": (C.c_int, [c_p, C.c_char_p, c_p, i32, c_p, i32, i32, i32, c_p, c_p, c_p, i32, c_p]),
+    "brag_dense_rescore_noalloc": (C.c_int, [c_p, C.c_char_p, c_p, i32, c_p, i32, i32, i32, c_p, c_p, c_p, c_p]),
     "brag_sparse_topk": (C.c_int, [c_p, C.c_char_p, c_p, c_p, c_p, i32, i32, i32, i32, c_p, c_p, c_p, i32, c_p]),
     "brag_rrf": (C.c_int, [c_p, c_p, c_p, i32, i32, i32, i32, i32, c_p, c_p, c_p, i32, c_p]),
     "brag_merge_topk": (C.c_int, [c_p, c_p, c_p, c_p, i32, i32, i32, c_p, c_p, c_p, i32, c_p]),

@@ -169,6 +169,7 @@ struct brag_engine {
     DevBuf h_in[6], h_out[6];      // staging for host-pointer calls
     DevBuf hyb_ids, hyb_counts, hyb_scores, cp_prefix, cp_tmp, cp_chunks, shard_keys;
     ShardState shard;
+    uint64_t* noalloc_keys = nullptr;      // device address of select.cu's static key scratch on this engine's GPU
     std::vector<int32_t> qptr_host;
     alignas(64) unsigned char tmap_q[128];
     // profiling
@@ -786,9 +787,12 @@ int brag_create(int device, brag_engine** out) {
         CK(brag::bm25_init_device());
         CK(brag::bm25x_init_device());
         CK(brag::shard_init_device());
+        uint64_t* noalloc_keys = nullptr;
+        CK(brag::rescore_noalloc_init_device(&noalloc_keys));
         auto* e = new brag_engine();
         e->device = device;
         e->num_sms = prop.multiProcessorCount;
+        e->noalloc_keys = noalloc_keys;
         *out = e;
     });
 }
@@ -1100,6 +1104,28 @@ int brag_dense_topk(brag_engine* e, const char* name, const float* Q, int32_t B,
             to_host(out_counts, dc, (size_t)B, st);
             CK(cudaStreamSynchronize(st));
         }
+    });
+}
+
+static_assert(BRAG_NOALLOC_MAX_KEYS == brag::NOALLOC_MAX_KEYS, "include/brag.h and kernels.h disagree on the static scratch size");
+
+int brag_dense_rescore_noalloc(brag_engine* e, const char* name, const float* Q, int32_t B, const int64_t* cand,
+                               int32_t m, int32_t k, int32_t mask_id, float* out_scores, int64_t* out_ids,
+                               int32_t* out_counts, void* stream) {
+    return guarded([&] {
+        REQUIRE(e && name && Q && cand && out_scores && out_ids && out_counts, "brag_dense_rescore_noalloc: NULL argument");
+        REQUIRE(B >= 1 && k >= 1 && m >= 1 && m <= 8192 && k <= 8192, "brag_dense_rescore_noalloc: need m,k in [1,8192]");
+        REQUIRE((int64_t)B * m <= BRAG_NOALLOC_MAX_KEYS,
+                "brag_dense_rescore_noalloc: B * m exceeds BRAG_NOALLOC_MAX_KEYS (65536), the size of the static scratch; "
+                "split the batch or use brag_dense_rescore");
+        REQUIRE((reinterpret_cast<uintptr_t>(Q) & 15) == 0, "brag_dense_rescore_noalloc: the query array must be 16-byte aligned");
+        use_device(e);
+        DenseSpace& s = dense_space(e, name);
+        const uint32_t* mask = mask_ptr(e, mask_id, s.n);
+        // launches only: no cudaMalloc / cudaFree, no staging buffers, no events, no synchronisation
+        CK(brag::dense_rescore_noalloc(e->noalloc_keys, s.x, s.dtype, s.n, s.d, Q, B, cand, m, k, e->id_offset, mask,
+                                       out_scores, out_ids, out_counts, (cudaStream_t)stream));
+        e->kernel_launches += 2;
     });
 }
 

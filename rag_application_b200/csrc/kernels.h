@@ -26,6 +26,12 @@ struct ShardSink {
 // second engine on another GPU of the same process gets them too.
 cudaError_t dense_umma_init_device();
 cudaError_t select_init_device();
+// allocation-free candidate re-score (select.cu): key scratch in a static device array of NOALLOC_MAX_KEYS keys
+constexpr int NOALLOC_MAX_KEYS = 65536;     // B * m of one call; 512 KB per GPU
+cudaError_t rescore_noalloc_init_device(uint64_t** keys);
+cudaError_t dense_rescore_noalloc(uint64_t* keys, const void* X, int dtype, int64_t n, int d, const float* Q, int B,
+                                  const int64_t* cand, int m, int k, int64_t id_offset, const uint32_t* mask,
+                                  float* out_scores, int64_t* out_ids, int32_t* out_counts, cudaStream_t st);
 cudaError_t bm25_init_device();
 cudaError_t bm25x_init_device();
 cudaError_t shard_init_device();

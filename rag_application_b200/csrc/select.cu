@@ -457,6 +457,40 @@ cudaError_t merge_scored_lists(const float* scores, const int64_t* ids, const in
     return cudaGetLastError();
 }
 
+// ------------------------------------------------------------------ re-score without any allocation
+// brag_dense_rescore_noalloc (include/brag.h): the candidate re-score with its [B][m] key scratch in a file-scope array
+// instead of the engine's grow-only cudaMalloc buffers, for callers that may not allocate (CUDA graph capture, tight
+// serving loops).  512 KB on every GPU that loads the library, until exit.  Every call on a device shares it: calls
+// that overlap on the GPU race.  Nothing has to start at zero -- rescore_cands_kernel writes every slot of its
+// B * m keys (0 for an empty / filtered / out-of-range candidate) before finalize_keys_kernel reads exactly those.
+static __device__ __align__(256) uint64_t g_noalloc_keys[NOALLOC_MAX_KEYS];
+
+// In host code `g_noalloc_keys` is a host-side stand-in, not a device address: the kernels get the address
+// cudaGetSymbolAddress returns for the CURRENT device (brag_create calls this once per engine, device current).
+cudaError_t rescore_noalloc_init_device(uint64_t** keys) {
+    void* p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_keys);
+    if (e != cudaSuccess) return e;
+    *keys = reinterpret_cast<uint64_t*>(p);
+    return cudaSuccess;
+}
+
+// keys: what rescore_noalloc_init_device returned on this device.  Launches only; no allocation, no synchronisation.
+cudaError_t dense_rescore_noalloc(uint64_t* keys, const void* X, int dtype, int64_t n, int d, const float* Q, int B,
+                                  const int64_t* cand, int m, int k, int64_t id_offset, const uint32_t* mask,
+                                  float* out_scores, int64_t* out_ids, int32_t* out_counts, cudaStream_t st) {
+    if (keys == nullptr || (int64_t)B * m > NOALLOC_MAX_KEYS) return cudaErrorInvalidValue;
+    int n2 = 1;
+    while (n2 < (m > k ? m : k)) n2 <<= 1;
+    if (n2 > SEL_MAX) return cudaErrorInvalidValue;
+    const int64_t threads = (int64_t)B * m * 32;
+    rescore_cands_kernel<<<(int)((threads + 255) / 256), 256, 0, st>>>(X, dtype, n, d, Q, B, cand, m, id_offset, mask, keys);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+    finalize_keys_kernel<<<B, SEL_THREADS, (size_t)n2 * 8, st>>>(keys, m, k, 1, id_offset, out_scores, out_ids, out_counts);
+    return cudaGetLastError();
+}
+
 // kernel attributes are per device: brag_create calls this with the engine's device current
 cudaError_t select_init_device() {
     cudaError_t e = cudaFuncSetAttribute(merge_keys_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SEL_MAX * 8);

@@ -203,6 +203,19 @@ class Engine:
                                                    _ptr(i), _ptr(c), int(dev), _stream() if dev else None))
         return s, i, c
 
+    def dense_rescore_noalloc(self, name: str, Q, cand, k: int, out, mask_id: int = 0):
+        """brag_dense_rescore_noalloc: device tensors only, the caller owns the outputs `out` = (float32 [B,k],
+        int64 [B,k], int32 [B]); nothing is allocated here or in the library (static scratch, B * m <= 65536)."""
+        if not (_is_torch_cuda(Q) and _is_torch_cuda(cand) and all(_is_torch_cuda(t) for t in out)):
+            raise ValueError("dense_rescore_noalloc takes CUDA tensors only")
+        if not (Q.is_contiguous() and cand.is_contiguous() and all(t.is_contiguous() for t in out)):
+            raise ValueError("dense_rescore_noalloc takes contiguous tensors (it will not copy)")
+        B, m = cand.shape
+        s, i, c = out
+        _native.check(self._lib.brag_dense_rescore_noalloc(self._h, name.encode(), _ptr(Q), B, _ptr(cand), m, k, mask_id,
+                                                           _ptr(s), _ptr(i), _ptr(c), _stream()))
+        return s, i, c
+
     def sparse_topk(self, name: str, q_ptr, q_terms, q_vals, k: int, mask_id: int = 0, max_terms: int = -1):
         """max_terms: upper bound of the longest query (terms).  Device callers should pass it: without it the engine
         copies q_ptr back and synchronises the stream in the middle of the call."""
