@@ -558,6 +558,11 @@ def main():
             # the wait for the slowest peer's lists
             "exchange_ms": (stage_ms["merge"] / args.steps) if world > 1 else 0.0,
             "exchange": (args.exchange if world > 1 else None),
+            # what one rank stores into its peers' windows per step: both ranked lists (B x k keys of 8 B) to each of the
+            # world - 1 peers, plus one 8-byte flag each; the cross-shard bound words (one atomicMax per improved bound
+            # and peer, at most a few per query and list) are not counted
+            "nvlink_bytes_per_step_per_rank": (int((world - 1) * (2 * args.batch * k * 8 + 8))
+                                               if world > 1 and args.exchange == "peer" else 0),
             "sparse_index_build_s": sparse_index_s,
             # second kernel of the step: the sparse scan against the HBM roofline, on the ALGORITHMIC bytes an
             # exhaustive posting scan reads (sum_t df_t * 8 B); `traffic` = DRAM bytes the pruning kernel really moves
